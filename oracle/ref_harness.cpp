@@ -1,0 +1,363 @@
+/*
+ * ref_harness.cpp -- thin extern "C" doors into the UNMODIFIED reference library.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Compiled by oracle/Makefile together with the reference's own
+ * sources (read in place from /root/reference) into oracle/_ref/libgrok_ref.so.  It contains
+ * no codec arithmetic of its own: every function builds the reference's own objects
+ * (TileComponent, T1, ...) and calls the reference's own entry points, so that the C
+ * restatement in oracle/*.c and the CUDA kernels can be compared with what Grok computes.
+ */
+/* ojph headers first: grk_includes.h poisons malloc/free (same order as t1/t1_ht/T1HT.cpp:20-25) */
+#include "ojph_block_decoder.h"
+#include "ojph_block_encoder.h"
+#include "ojph_mem.h"
+#include "grk_includes.h"
+#include "T1.h"
+#include "WaveletFwd.h"
+#include "mct.h"
+
+/* zeroed raw storage (the reference poisons malloc/calloc/free) */
+template<typename T>
+static T* zalloc(size_t n)
+{
+	void* p = ::operator new(n * sizeof(T));
+	memset(p, 0, n * sizeof(T));
+	return (T*)p;
+}
+static void zfree(void* p)
+{
+	::operator delete(p);
+}
+
+using namespace grk;
+
+namespace
+{
+struct RefTileComp
+{
+	CodingParams cp;
+	TileCodingParams tcp;
+	TileComponentCodingParams tccp;
+	TileComponent tilec;
+	bool ok = false;
+
+	RefTileComp(bool compress, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t numres,
+				uint32_t qmfbid, uint32_t cblkw_exp = 6, uint32_t cblkh_exp = 6, uint8_t prec = 8)
+	{
+		memset(&cp.m_coding_params, 0, sizeof(cp.m_coding_params));
+		tccp.numresolutions = (uint8_t)numres;
+		tccp.cblkw = (uint8_t)cblkw_exp;
+		tccp.cblkh = (uint8_t)cblkh_exp;
+		tccp.qmfbid = (uint8_t)qmfbid;
+		tccp.numgbits = 2;
+		tccp.roishift = 0;
+		for(uint32_t i = 0; i < GRK_J2K_MAXRLVLS; ++i)
+		{
+			tccp.precinctWidthExp[i] = 15;
+			tccp.precinctHeightExp[i] = 15;
+		}
+		for(uint32_t i = 0; i < GRK_J2K_MAXBANDS; ++i)
+		{
+			tccp.stepsizes[i].expn = 10;
+			tccp.stepsizes[i].mant = 0;
+		}
+		grkRectU32 r(x0, y0, x1, y1);
+		if(!tilec.init(compress, true, r, prec, &cp, &tcp, &tccp, nullptr))
+			return;
+		if(!tilec.allocWindowBuffer(r))
+			return;
+		if(!tilec.getBuffer()->alloc())
+			return;
+		ok = true;
+	}
+	int32_t* data()
+	{
+		return tilec.getBuffer()->getHighestBufferResWindowREL()->getBuffer();
+	}
+	uint32_t stride()
+	{
+		return tilec.getBuffer()->getHighestBufferResWindowREL()->stride;
+	}
+};
+} // namespace
+
+extern "C" {
+
+int ref_harness_version(void)
+{
+	return 2;
+}
+
+void ref_set_threads(uint32_t n)
+{
+	ThreadPool::release();
+	ThreadPool::instance(n);
+}
+
+/* row stride the reference gives a tile-component buffer of this width */
+uint32_t ref_stride(uint32_t width)
+{
+	return grkMakeAlignedWidth(width);
+}
+
+/* Whole-tile wavelet transform through the reference's own WaveletFwdImpl::compress /
+ * WaveletReverse::decompress on a real TileComponent.  data: dense (x1-x0) x (y1-y0) plane,
+ * transformed in place (int32 for 5/3, float bits for 9/7). */
+int ref_dwt(int32_t* data, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t numres,
+			uint32_t qmfbid, int forward)
+{
+	ThreadPool::get();
+	RefTileComp tc(forward != 0, x0, y0, x1, y1, numres, qmfbid);
+	if(!tc.ok)
+		return -1;
+	uint32_t w = x1 - x0, h = y1 - y0, s = tc.stride();
+	auto buf = tc.data();
+	for(uint32_t y = 0; y < h; ++y)
+		memcpy(buf + (size_t)y * s, data + (size_t)y * w, sizeof(int32_t) * w);
+	bool rc;
+	if(forward)
+	{
+		WaveletFwdImpl f;
+		rc = f.compress(&tc.tilec, (uint8_t)qmfbid);
+	}
+	else
+	{
+		/* WaveletReverse::decompress only reads p_tcd->wholeTileDecompress
+		 * (transform/WaveletReverse.cpp:2232-2261) */
+		auto tp = zalloc<TileProcessor>(1);
+		tp->wholeTileDecompress = true;
+		WaveletReverse r;
+		rc = r.decompress(tp, &tc.tilec, 0, grkRectU32(x0, y0, x1, y1), (uint8_t)numres,
+						  (uint8_t)qmfbid);
+		zfree(tp);
+	}
+	for(uint32_t y = 0; y < h; ++y)
+		memcpy(data + (size_t)y * w, buf + (size_t)y * s, sizeof(int32_t) * w);
+	return rc ? 0 : -2;
+}
+
+/* forward MCT: mct::compress_rev / compress_irrev (point_transform/mct.cpp:583-596) */
+void ref_mct_fwd(int32_t* c0, int32_t* c1, int32_t* c2, uint64_t n, int irrev)
+{
+	ThreadPool::get();
+	/* the Highway kernels use aligned loads: stage through the reference's aligned allocator */
+	int32_t* src[3] = {c0, c1, c2};
+	int32_t* al[3];
+	for(int i = 0; i < 3; ++i)
+	{
+		al[i] = (int32_t*)grkAlignedMalloc((n + 64) * sizeof(int32_t));
+		memcpy(al[i], src[i], n * sizeof(int32_t));
+	}
+	if(irrev)
+		mct::compress_irrev(al[0], al[1], al[2], n);
+	else
+		mct::compress_rev(al[0], al[1], al[2], n);
+	for(int i = 0; i < 3; ++i)
+	{
+		memcpy(src[i], al[i], n * sizeof(int32_t));
+		grkAlignedFree(al[i]);
+	}
+}
+
+/* inverse MCT fused with DC shift + clamp: mct::decompress_rev / decompress_irrev on a real
+ * Tile (point_transform/mct.cpp:480-513, :544-579). Planes are dense w x h.
+ * mct == 0: per-component DC shift only (mct::decompress_dc_shift_*), numcomps planes. */
+int ref_mct_inv(int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t h, int irrev, int mct_on,
+				const uint8_t* prec, const uint8_t* sgnd, const int32_t* dcshift)
+{
+	ThreadPool::get();
+	std::vector<RefTileComp*> tcs;
+	auto tccps = new TileComponentCodingParams[numcomps];
+	auto tile = new Tile();
+	tile->numcomps = (uint16_t)numcomps;
+	tile->comps = nullptr;
+	/* Tile owns a TileComponent array; we hand it our own, built one by one */
+	auto comps = zalloc<TileComponent>(numcomps);
+	for(uint32_t c = 0; c < numcomps; ++c)
+	{
+		auto t = new RefTileComp(false, 0, 0, w, h, 1, irrev ? 0 : 1);
+		if(!t->ok)
+			return -1;
+		tcs.push_back(t);
+		uint32_t s = t->stride();
+		for(uint32_t y = 0; y < h; ++y)
+			memcpy(t->data() + (size_t)y * s, planes[c] + (size_t)y * w, sizeof(int32_t) * w);
+		memcpy((void*)(comps + c), (void*)&t->tilec, sizeof(TileComponent)); /* shallow alias */
+		tccps[c].m_dc_level_shift = dcshift[c];
+		tccps[c].qmfbid = irrev ? 0 : 1;
+	}
+	tile->comps = comps;
+	auto image = zalloc<GrkImage>(1);
+	auto icomps = zalloc<grk_image_comp>(numcomps);
+	for(uint32_t c = 0; c < numcomps; ++c)
+	{
+		icomps[c].prec = prec[c];
+		icomps[c].sgnd = sgnd[c];
+	}
+	image->comps = icomps;
+	image->numcomps = (uint16_t)numcomps;
+	if(mct_on)
+	{
+		if(irrev)
+			mct::decompress_irrev(tile, image, tccps);
+		else
+			mct::decompress_rev(tile, image, tccps);
+	}
+	else
+	{
+		for(uint32_t c = 0; c < numcomps; ++c)
+		{
+			if(irrev)
+				mct::decompress_dc_shift_irrev(tile, image, tccps, c);
+			else
+				mct::decompress_dc_shift_rev(tile, image, tccps, c);
+		}
+	}
+	for(uint32_t c = 0; c < numcomps; ++c)
+	{
+		uint32_t s = tcs[c]->stride();
+		for(uint32_t y = 0; y < h; ++y)
+			memcpy(planes[c] + (size_t)y * w, tcs[c]->data() + (size_t)y * s, sizeof(int32_t) * w);
+	}
+	tile->comps = nullptr; /* aliases: not ours to destroy through Tile */
+	tile->numcomps = 0;
+	delete tile;
+	zfree(comps);
+	for(auto t : tcs)
+		delete t;
+	delete[] tccps;
+	zfree(icomps);
+	zfree(image);
+	return 0;
+}
+
+} // extern "C"
+
+/* ------------------------------------------------------------------------------------- */
+/* T1 Part-1 (EBCOT + MQ): the reference's T1 object, called the way T1Part1::compress /
+ * T1Part1::decompress call it (t1/t1_part1/T1Part1.cpp:89-161).                          */
+
+extern "C" {
+
+struct ref_pass
+{
+	uint32_t rate;
+	uint32_t len;
+	uint32_t term;
+	double distortiondec;
+};
+
+/* samples: w*h sign-magnitude (as T1Part1::preCompress leaves them). out: >= w*h*4+2 bytes.
+ * returns cumulative distortion; fills numbps, numpasses, passes[<=100]. */
+double ref_t1_encode(const int32_t* samples, uint32_t w, uint32_t h, uint32_t max, uint32_t orient,
+					 uint32_t compno, uint32_t level, uint32_t qmfbid, double stepsize,
+					 uint32_t cblksty, const double* mct_norms, uint32_t mct_numcomps,
+					 int doRateControl, uint8_t* out, uint32_t* numbps, uint32_t* numpasses,
+					 ref_pass* passes, uint32_t* numbytes)
+{
+	T1 t1(true, w, h);
+	t1.alloc(w, h);
+	memcpy(t1.getUncompressedData(), samples, sizeof(int32_t) * w * h);
+	std::vector<uint8_t> buf((size_t)w * h * 4 + 64 + 2, 0);
+	cblk_enc cb;
+	memset(&cb, 0, sizeof(cb));
+	cb.x0 = 0;
+	cb.y0 = 0;
+	cb.x1 = w;
+	cb.y1 = h;
+	cb.data = buf.data() + 2; /* two zero bytes before the stream (t1/Codeblock.h:156-172) */
+	double d = t1.compress_cblk(&cb, max, (uint8_t)orient, (uint16_t)compno, (uint8_t)level,
+								(uint8_t)qmfbid, stepsize, cblksty, mct_norms,
+								(uint16_t)mct_numcomps, doRateControl != 0);
+	*numbps = cb.numbps;
+	*numpasses = cb.numPassesTotal;
+	uint32_t total = 0;
+	for(uint32_t i = 0; i < cb.numPassesTotal; ++i)
+	{
+		passes[i].rate = cb.passes[i].rate;
+		passes[i].len = cb.passes[i].len;
+		passes[i].term = cb.passes[i].term;
+		passes[i].distortiondec = cb.passes[i].distortiondec;
+		total = cb.passes[i].rate;
+	}
+	*numbytes = total;
+	memcpy(out, cb.data, total);
+	t1.code_block_enc_deallocate(&cb);
+	return d;
+}
+
+/* out: w*h int32 as T1::decompress_cblk leaves them (x2 fixed point, before dequantisation) */
+int ref_t1_decode(const uint8_t* data, const uint32_t* seg_len, const uint32_t* seg_passes,
+				  uint32_t numsegs, uint32_t numbps, uint32_t w, uint32_t h, uint32_t orient,
+				  uint32_t cblksty, int32_t* out)
+{
+	T1 t1(false, w, h);
+	DecompressCodeblock cblk;
+	cblk.numbps = (uint8_t)numbps;
+	size_t total = 0;
+	for(uint32_t i = 0; i < numsegs; ++i)
+	{
+		auto seg = cblk.nextSegment();
+		seg->len = seg_len[i];
+		seg->numpasses = seg_passes[i];
+		total += seg_len[i];
+	}
+	memset(out, 0, sizeof(int32_t) * w * h);
+	t1.attachUncompressedData(out, w, h);
+	t1.allocCompressedData(total + grk_cblk_dec_compressed_data_pad_right);
+	auto cd = t1.getCompressedDataBuffer();
+	memcpy(cd, data, total);
+	cd[total] = 0;
+	cd[total + 1] = 0;
+	bool rc = t1.decompress_cblk(&cblk, cd, (uint8_t)orient, cblksty);
+	t1.attachUncompressedData(nullptr, w, h); /* detach: `out` is the caller's */
+	return rc ? 0 : -1;
+}
+
+/* ------------------------------------------------------------------------------------- */
+/* HTJ2K block coder: ojph_encode_codeblock / ojph_decode_codeblock called the way
+ * T1HT::compress / T1HT::decompress call them (t1/t1_ht/T1HT.cpp:109-187).               */
+
+/* samples: w*h uint32 sign-magnitude with the magnitude MSB-aligned as T1HT::preCompress
+ * leaves it. out >= 16384+3072+16 bytes. returns coded length, or -1. */
+int ref_ht_encode(const uint32_t* samples, uint32_t missing_msbs, uint32_t w, uint32_t h,
+				  uint8_t* out)
+{
+	try
+	{
+		ojph::mem_elastic_allocator elastic(1048576);
+		ojph::coded_lists* coded = nullptr;
+		uint32_t lengths[2] = {0, 0};
+		std::vector<uint32_t> buf(samples, samples + (size_t)w * h);
+		ojph::local::ojph_encode_codeblock(buf.data(), missing_msbs, 1, w, h, w, lengths, &elastic,
+										   coded);
+		memcpy(out, coded->buf, lengths[0]);
+		return (int)lengths[0];
+	}
+	catch(...)
+	{
+		return -1;
+	}
+}
+
+/* data: lengths1+lengths2 coded bytes; the harness adds the 8-byte zero pads both sides.
+ * out: w*h uint32 sign-magnitude. returns 0 ok, -1 decoder reported failure. */
+int ref_ht_decode(const uint8_t* data, uint32_t missing_msbs, uint32_t num_passes,
+				  uint32_t lengths1, uint32_t lengths2, uint32_t w, uint32_t h, uint32_t* out)
+{
+	try
+	{
+		size_t total = (size_t)lengths1 + lengths2;
+		std::vector<uint8_t> buf(total + 16, 0);
+		memcpy(buf.data() + 8, data, total);
+		bool rc = ojph::local::ojph_decode_codeblock(buf.data() + 8, out, missing_msbs, num_passes,
+													 lengths1, lengths2, w, h, w);
+		return rc ? 0 : -1;
+	}
+	catch(...)
+	{
+		return -1;
+	}
+}
+
+} // extern "C"
