@@ -1,0 +1,32 @@
+// pipeline.h -- internal (non-exported) host-side declarations shared by the .cu files.
+#pragma once
+#include "dwt.cuh"
+
+// kernels' host launchers
+int grkb_launch_idwt_level(DwtLevelArgs a, int reversible, int ncomp, int fin, cudaStream_t s);
+int grkb_launch_fdwt_level(DwtLevelArgs a, int reversible, int ncomp, int fin, cudaStream_t s);
+int grkb_launch_mct(const MctArgs& p, int mode, cudaStream_t s);
+int grkb_launch_dc(const MctArgs& p, int mode, cudaStream_t s);
+
+// A group of 1 or 3 tile-components that share one geometry, resident on the device.
+struct DwtGroup
+{
+	int ncomp;
+	void* coeff[3]; // Mallat coefficient planes (T1 output / FDWT output)
+	uint32_t coeff_stride;
+	void* scratch[3][2]; // ping-pong planes for the intermediate resolutions
+	uint32_t scratch_stride;
+	void* image[3]; // full-resolution planes: IDWT destination / FDWT source
+	uint32_t image_stride;
+};
+
+// bytes needed for one scratch plane of a tile-component with `numres` resolutions
+size_t grkb_dwt_scratch_bytes(grkb_rect tc, uint32_t numres, uint32_t* stride_out);
+
+// fin: 0 none, 1 DC shift per component, 2 MCT + DC shift (ncomp == 3)
+int grkb_idwt_device(const DwtGroup& g, grkb_rect tc, uint32_t numres, int reversible, int fin,
+					 const int32_t* shift, const int32_t* lo, const int32_t* hi, cudaStream_t s);
+int grkb_fdwt_device(const DwtGroup& g, grkb_rect tc, uint32_t numres, int reversible, int fin,
+					 const int32_t* shift, cudaStream_t s);
+
+void grkb_set_error(const char* fmt, ...);

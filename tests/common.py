@@ -1,0 +1,27 @@
+"""shared test data: geometries and synthetic planes"""
+import numpy as np
+
+# (w, h, x0, y0, numres): odd sizes, width/height 1..5, odd origins (parity 1), ragged strides
+GEOMS = [
+    (64, 64, 0, 0, 3), (33, 17, 0, 0, 4), (1, 5, 0, 0, 3), (5, 1, 1, 1, 3), (3, 2, 0, 0, 2),
+    (100, 77, 13, 7, 6), (7, 13, 5, 9, 5), (256, 135, 0, 0, 6), (17, 1, 0, 1, 3), (1, 17, 1, 0, 2),
+    (2, 2, 0, 0, 2), (4, 4, 1, 1, 3), (5, 5, 3, 3, 2), (250, 31, 0, 0, 3), (241, 40, 1, 0, 3),
+    (481, 66, 2, 3, 4), (512, 270, 0, 0, 6), (37, 300, 0, 1, 5), (8, 8, 0, 0, 4), (9, 300, 1, 1, 6),
+]
+# Degenerate geometries on which the REFERENCE itself misbehaves (documented in DESIGN.md):
+#  * inverse 5/3, a level of height exactly 2 at odd y0 writes dest[1] instead of dest[stride]
+#    (WaveletReverse.cpp:639-649);
+#  * forward, a resolution of zero width and non-zero height reads/writes out of range
+#    (WaveletFwd.cpp:909-957).
+REF_BROKEN = [(2, 2, 1, 1, 2), (3, 3, 1, 0, 6), (1, 17, 1, 0, 3)]
+
+
+def plane(rng, w, h, reversible, amp=2000):
+    if reversible:
+        return rng.integers(-amp, amp, size=(h, w)).astype(np.int32)
+    return (rng.standard_normal((h, w)) * amp / 4).astype(np.float32)
+
+
+def same_bits(a, b):
+    return np.array_equal(np.ascontiguousarray(a).view(np.int32),
+                          np.ascontiguousarray(b).view(np.int32))
