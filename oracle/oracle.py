@@ -142,3 +142,82 @@ def ref_mct_inv(planes, irrev, mct_on, prec, sgnd, shift):
                            _p(np.array(sgnd, dtype=np.uint8)), _p(np.array(shift, dtype=np.int32)))
     assert rc == 0
     return a
+
+
+# ---------------------------------------------------------------- EBCOT / MQ block coder
+
+def to_smr(x):
+    """two's complement int32 array -> sign-magnitude (t1_common.h:84)"""
+    x = np.asarray(x, dtype=np.int64)
+    return np.where(x >= 0, x, (-x) | 0x80000000).astype(np.uint32).view(np.int32)
+
+
+def _t1_encode(is_ref, samples, orient=0, cblksty=0, compno=0, level=0, qmfbid=1, stepsize=1.0,
+               mct_norms=None, rate_control=True):
+    """samples: 2-D int32 sign-magnitude array with 6 fractional bits (T1Part1::preCompress).
+    returns dict(numbps, passes=[(rate,len,term,dist)], data=bytes, distortion)"""
+    s = np.ascontiguousarray(samples, dtype=np.int32)
+    h, w = s.shape
+    mx = int((s.view(np.uint32) & 0x7FFFFFFF).max()) if s.size else 0
+    out = np.zeros(w * h * 4 + 128, dtype=np.uint8)
+    norms = None if mct_norms is None else np.ascontiguousarray(mct_norms, dtype=np.float64)
+    nn = 0 if norms is None else len(norms)
+    args = [_p(s), C.c_uint32(w), C.c_uint32(h), C.c_uint32(mx), C.c_uint32(orient),
+            C.c_uint32(compno), C.c_uint32(level), C.c_uint32(qmfbid), C.c_double(stepsize),
+            C.c_uint32(cblksty), None if norms is None else _p(norms), C.c_uint32(nn),
+            C.c_int(1 if rate_control else 0), _p(out)]
+    if is_ref:
+        numbps, npasses, nbytes = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        passes = (RefPass * 100)()
+        d = ref().ref_t1_encode(*args, C.byref(numbps), C.byref(npasses), passes, C.byref(nbytes))
+        pl = [(passes[i].rate, passes[i].len, int(passes[i].term), passes[i].distortiondec)
+              for i in range(npasses.value)]
+        return dict(numbps=numbps.value, passes=pl, data=out[:nbytes.value].tobytes(), distortion=d)
+    res = OrcEncResult()
+    d = oracle().orc_t1_encode(*args, C.byref(res))
+    pl = [(res.passes[i].rate, res.passes[i].len, int(res.passes[i].term),
+           res.passes[i].distortiondec) for i in range(res.numPassesTotal)]
+    return dict(numbps=res.numbps, passes=pl, data=out[:res.num_bytes].tobytes(), distortion=d)
+
+
+def orc_t1_encode(samples, **kw):
+    return _t1_encode(False, samples, **kw)
+
+
+def ref_t1_encode(samples, **kw):
+    return _t1_encode(True, samples, **kw)
+
+
+def segments_from_passes(passes, numbps, cblksty):
+    """group coding passes into codeword segments the way T2 does (a segment ends at every
+    terminated pass); returns [(len, numpasses)]"""
+    segs, n, ln = [], 0, 0
+    for (rate, plen, term, _d) in passes:
+        n += 1
+        ln += plen
+        if term:
+            segs.append((ln, n))
+            n, ln = 0, 0
+    if n:
+        segs.append((ln, n))
+    return segs
+
+
+def _t1_decode(is_ref, data, segs, numbps, w, h, orient=0, cblksty=0):
+    """returns (rc, int32 h x w array in the decoder's x2 fixed point)"""
+    buf = np.frombuffer(bytes(data) + b"\0" * 8, dtype=np.uint8).copy()
+    sl = np.array([s[0] for s in segs], dtype=np.uint32)
+    sp = np.array([s[1] for s in segs], dtype=np.uint32)
+    out = np.zeros((h, w), dtype=np.int32)
+    fn = ref().ref_t1_decode if is_ref else oracle().orc_t1_decode
+    rc = fn(_p(buf), _p(sl), _p(sp), C.c_uint32(len(segs)), C.c_uint32(numbps), C.c_uint32(w),
+            C.c_uint32(h), C.c_uint32(orient), C.c_uint32(cblksty), _p(out))
+    return rc, out
+
+
+def orc_t1_decode(data, segs, numbps, w, h, **kw):
+    return _t1_decode(False, data, segs, numbps, w, h, **kw)
+
+
+def ref_t1_decode(data, segs, numbps, w, h, **kw):
+    return _t1_decode(True, data, segs, numbps, w, h, **kw)

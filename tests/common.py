@@ -16,6 +16,20 @@ GEOMS = [
 REF_BROKEN = [(2, 2, 1, 1, 2), (3, 3, 1, 0, 6), (1, 17, 1, 0, 3)]
 
 
+def ref_defect(w, h, x0, y0, nr, reversible, forward):
+    """True when the REFERENCE itself misbehaves on this geometry (see REF_BROKEN above), so the
+    oracle -- which implements the transform the standard defines -- cannot be pinned on it."""
+    for lvl in range(nr - 1):
+        rx0, rx1 = -((-x0) >> lvl), -((-(x0 + w)) >> lvl)
+        ry0, ry1 = -((-y0) >> lvl), -((-(y0 + h)) >> lvl)
+        rw, rh = rx1 - rx0, ry1 - ry0
+        if not forward and reversible and rh == 2 and (ry0 & 1) and rw > 0:
+            return True
+        if forward and (rw == 0) != (rh == 0):
+            return True
+    return False
+
+
 def plane(rng, w, h, reversible, amp=2000):
     if reversible:
         return rng.integers(-amp, amp, size=(h, w)).astype(np.int32)

@@ -79,11 +79,22 @@ def test_fused_mct_fdwt(gpu, orc, reversible, mct_on):
 @pytest.mark.parametrize("reversible", [1, 0])
 def test_full_size_roundtrip(gpu, reversible):
     """BASELINE shape B (4096x2160, 5 levels): forward then inverse on the GPU.
-    5/3 must reproduce the input exactly; 9/7 within 1e-3 relative (float lifting)."""
+    5/3 must reproduce the input exactly.  9/7: the reference's synthesis scales high-pass
+    samples by 2/K, not 1/K (WaveletReverse.cpp:365-371; the decoder's step sizes carry the
+    other half, Quantizer.cpp:31-37), so HL and LH are halved and HH quartered in between;
+    then the round trip holds to 1e-3 relative (float lifting)."""
     rng = np.random.default_rng(4096)
-    p = plane(rng, 4096, 2160, reversible, amp=30000)
-    c = gpu.stages.dwt(p, 0, 0, 6, reversible, 1)
-    r = gpu.stages.dwt(c, 0, 0, 6, reversible, 0)
+    w, h, nr = 4096, 2160, 6
+    p = plane(rng, w, h, reversible, amp=30000)
+    c = gpu.stages.dwt(p, 0, 0, nr, reversible, 1)
+    if not reversible:
+        for lvl in range(nr - 1):
+            rw, rh = -((-w) >> lvl), -((-h) >> lvl)
+            lw, lh = -((-w) >> (lvl + 1)), -((-h) >> (lvl + 1))
+            c[:lh, lw:rw] *= 0.5
+            c[lh:rh, :lw] *= 0.5
+            c[lh:rh, lw:rw] *= 0.25
+    r = gpu.stages.dwt(c, 0, 0, nr, reversible, 0)
     if reversible:
         assert np.array_equal(p, r)
     else:

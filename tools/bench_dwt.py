@@ -1,4 +1,5 @@
-"""Device-resident timing of the wavelet kernels (development aid; bench.py is the contract)."""
+"""Device-resident timing of the wavelet kernels (development aid; bench.py is the contract).
+usage: bench_dwt.py [w h numres [rev fwd ncomp mct]]"""
 import ctypes as C
 import json
 import sys
@@ -8,7 +9,8 @@ import grok_b200
 lib = grok_b200.lib
 lib.grkb_bench_dwt.argtypes = [C.c_uint32] * 3 + [C.c_int, C.c_int, C.c_uint32, C.c_int, C.c_uint32,
                                                  C.c_uint32, C.POINTER(C.c_float)]
-PEAK = 6551.7
+PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"] \
+    if os.path.exists(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")) else 6650.0
 
 
 def alg_bytes(w, h, nr, ncomp):
@@ -18,15 +20,18 @@ def alg_bytes(w, h, nr, ncomp):
     return b * ncomp
 
 
-for (w, h, nr) in [(4096, 2160, 6), (2048, 2048, 6), (1024, 1024, 6)]:
-    for rev in (0, 1):
-        for fwd in (0, 1):
-            for (nc, mct) in [(1, 0), (3, 0), (3, 1)]:
-                ms = C.c_float()
-                rc = lib.grkb_bench_dwt(w, h, nr, rev, fwd, nc, mct, 20, 5, C.byref(ms))
-                if rc:
-                    print("ERR", lib.grkb_last_error()); continue
-                gbs = alg_bytes(w, h, nr, nc) / (ms.value * 1e-3) / 1e9
-                print(json.dumps(dict(w=w, h=h, rev=rev, fwd=fwd, ncomp=nc, mct=mct,
-                                      ms=round(ms.value, 4), gbs=round(gbs, 1),
-                                      frac=round(gbs / PEAK, 3))))
+a = [int(x) for x in sys.argv[1:]]
+shapes = [(4096, 2160, 6), (2048, 2048, 6), (1024, 1024, 6)] if len(a) < 3 else [tuple(a[:3])]
+combos = [(rev, fwd, nc, mct) for rev in (0, 1) for fwd in (0, 1) for (nc, mct) in [(1, 0), (3, 0), (3, 1)]] \
+    if len(a) < 7 else [tuple(a[3:7])]
+iters = a[7] if len(a) > 7 else 20
+for (w, h, nr) in shapes:
+    for (rev, fwd, nc, mct) in combos:
+        ms = C.c_float()
+        rc = lib.grkb_bench_dwt(w, h, nr, rev, fwd, nc, mct, iters, 5, C.byref(ms))
+        if rc:
+            print("ERR", lib.grkb_last_error()); continue
+        gbs = alg_bytes(w, h, nr, nc) / (ms.value * 1e-3) / 1e9
+        print(json.dumps(dict(w=w, h=h, rev=rev, fwd=fwd, ncomp=nc, mct=mct,
+                              ms=round(ms.value, 4), gbs=round(gbs, 1),
+                              frac=round(gbs / PEAK, 3))))
