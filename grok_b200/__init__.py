@@ -7,3 +7,4 @@ arithmetic and has no CPU fallback: if the library is missing, importing `lib` r
 """
 from ._lib import lib, LIB_PATH, GrokB200Error  # noqa: F401
 from . import stages  # noqa: F401
+from . import tile  # noqa: F401

@@ -35,3 +35,57 @@ lib.grkb_mct_fdwt_host.argtypes = [_vp, _u32, _u32, _u32, _u32, _u32, _u32, _u32
 def check(rc, what):
     if rc != 0:
         raise GrokB200Error("%s failed (%d): %s" % (what, rc, lib.grkb_last_error().decode()))
+
+
+# ---- section B: tile entry points ------------------------------------------------------------
+
+class Cblk(C.Structure):
+    """grkb_cblk"""
+    _fields_ = [("x", _u32), ("y", _u32), ("w", C.c_uint16), ("h", C.c_uint16),
+                ("comp", C.c_uint8), ("orient", C.c_uint8), ("numbps", C.c_uint8),
+                ("cblk_sty", C.c_uint8), ("roishift", C.c_uint8), ("k_msbs", C.c_uint8),
+                ("numsegs", C.c_uint16), ("seg_first", _u32), ("data_off", _u32),
+                ("data_len", _u32), ("scale", C.c_float)]
+
+
+class Seg(C.Structure):
+    """grkb_seg"""
+    _fields_ = [("len", _u32), ("numpasses", _u32)]
+
+
+class TileParams(C.Structure):
+    """grkb_tile_params"""
+    _fields_ = [("x0", _u32), ("y0", _u32), ("x1", _u32), ("y1", _u32), ("numcomps", _u32),
+                ("numres", _u32), ("reversible", _i32), ("mct", _i32), ("shift", _i32 * 4),
+                ("lo", _i32 * 4), ("hi", _i32 * 4)]
+
+
+class LayoutParams(C.Structure):
+    """grkb_layout_params"""
+    _fields_ = [("x0", _u32), ("y0", _u32), ("x1", _u32), ("y1", _u32), ("numres", _u32),
+                ("cblkw_exp", _u32), ("cblkh_exp", _u32), ("prec_w_exp", _u32 * 33),
+                ("prec_h_exp", _u32 * 33)]
+
+
+class CblkGeom(C.Structure):
+    """grkb_cblk_geom"""
+    _fields_ = [("x", _u32), ("y", _u32), ("cx0", _u32), ("cy0", _u32), ("w", C.c_uint16),
+                ("h", C.c_uint16), ("res", C.c_uint8), ("band", C.c_uint8), ("orient", C.c_uint8),
+                ("level", C.c_uint8), ("precinct", _u32), ("cblkno", _u32)]
+
+
+lib.grkb_tile_layout.argtypes = [C.POINTER(LayoutParams), C.POINTER(CblkGeom), _u32,
+                                 C.POINTER(_u32)]
+lib.grkb_decoder_create.argtypes = [C.POINTER(TileParams), _u32, C.c_size_t, C.POINTER(_vp)]
+lib.grkb_decoder_destroy.argtypes = [_vp]
+lib.grkb_decoder_destroy.restype = None
+lib.grkb_decoder_decode.argtypes = [_vp, _vp, _u32, _vp, _u32, _vp, C.c_size_t, _vp, _u32,
+                                    C.POINTER(_u32)]
+lib.grkb_decoder_time_device.argtypes = [_vp, _u32, _u32, C.POINTER(C.c_float), C.POINTER(_u32)]
+lib.grkb_decoder_download.argtypes = [_vp, _vp, _u32]
+lib.grkb_t1_decode_host.argtypes = [_vp, _u32, _vp, _u32, _vp, C.c_size_t, _vp, _u32, _u32, _u32,
+                                    _int, C.POINTER(_u32)]
+lib.grkb_host_alloc.argtypes = [C.c_size_t]
+lib.grkb_host_alloc.restype = _vp
+lib.grkb_host_free.argtypes = [_vp]
+lib.grkb_host_free.restype = None

@@ -39,7 +39,8 @@ size_t grkb_dwt_scratch_bytes(grkb_rect tc, uint32_t numres, uint32_t* stride_ou
 }
 
 int grkb_idwt_device(const DwtGroup& g, grkb_rect tc, uint32_t numres, int reversible, int fin,
-					 const int32_t* shift, const int32_t* lo, const int32_t* hi, cudaStream_t s)
+					 const int32_t* shift, const int32_t* lo, const int32_t* hi, cudaStream_t s,
+					 cudaEvent_t* ev_last, uint32_t* launches)
 {
 	const uint32_t W = tc.x1 - tc.x0, Hh = tc.y1 - tc.y0;
 	if(W == 0 || Hh == 0)
@@ -119,6 +120,10 @@ int grkb_idwt_device(const DwtGroup& g, grkb_rect tc, uint32_t numres, int rever
 				a.hi[c] = hi[c < g.ncomp ? c : 0];
 			}
 		}
+		if(last && ev_last)
+			cudaEventRecord(ev_last[0], s);
+		if(launches)
+			*launches += (g.ncomp == 3) ? 1 : (uint32_t)g.ncomp;
 		if(g.ncomp == 3)
 		{
 			if(grkb_launch_idwt_level(a, reversible, 3, lfin == 2 ? 2 : 0, s))
@@ -142,6 +147,8 @@ int grkb_idwt_device(const DwtGroup& g, grkb_rect tc, uint32_t numres, int rever
 					return -1;
 			}
 		}
+		if(last && ev_last)
+			cudaEventRecord(ev_last[1], s);
 		for(int c = 0; c < g.ncomp; ++c)
 			ll[c] = a.pl[c].full;
 		ll_stride = last ? g.image_stride : g.scratch_stride;

@@ -25,7 +25,9 @@ size_t grkb_dwt_scratch_bytes(grkb_rect tc, uint32_t numres, uint32_t* stride_ou
 
 // fin: 0 none, 1 DC shift per component, 2 MCT + DC shift (ncomp == 3)
 int grkb_idwt_device(const DwtGroup& g, grkb_rect tc, uint32_t numres, int reversible, int fin,
-					 const int32_t* shift, const int32_t* lo, const int32_t* hi, cudaStream_t s);
+					 const int32_t* shift, const int32_t* lo, const int32_t* hi, cudaStream_t s,
+					 cudaEvent_t* ev_last = nullptr, uint32_t* launches = nullptr);
+// ev_last: optional pair of events recorded around the last (largest) level's kernel
 int grkb_fdwt_device(const DwtGroup& g, grkb_rect tc, uint32_t numres, int reversible, int fin,
 					 const int32_t* shift, cudaStream_t s);
 

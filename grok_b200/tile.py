@@ -1,0 +1,143 @@
+"""numpy-facing wrappers of the tile-level C-ABI (include/grk_b200.h, section B): code-block
+layout, descriptor tables and the whole-tile decoder.  No codec arithmetic here."""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import lib, check, Cblk, Seg, TileParams, LayoutParams, CblkGeom, GrokB200Error
+
+CBLKSTY_HT = 0x40
+
+CBLK_DTYPE = np.dtype([("x", "<u4"), ("y", "<u4"), ("w", "<u2"), ("h", "<u2"), ("comp", "u1"),
+                       ("orient", "u1"), ("numbps", "u1"), ("cblk_sty", "u1"), ("roishift", "u1"),
+                       ("k_msbs", "u1"), ("numsegs", "<u2"), ("seg_first", "<u4"),
+                       ("data_off", "<u4"), ("data_len", "<u4"), ("scale", "<f4")])
+assert CBLK_DTYPE.itemsize == C.sizeof(Cblk)
+SEG_DTYPE = np.dtype([("len", "<u4"), ("numpasses", "<u4")])
+GEOM_DTYPE = np.dtype([("x", "<u4"), ("y", "<u4"), ("cx0", "<u4"), ("cy0", "<u4"), ("w", "<u2"),
+                       ("h", "<u2"), ("res", "u1"), ("band", "u1"), ("orient", "u1"),
+                       ("level", "u1"), ("precinct", "<u4"), ("cblkno", "<u4")])
+assert GEOM_DTYPE.itemsize == C.sizeof(CblkGeom)
+
+
+def layout(x0, y0, x1, y1, numres, cblkw_exp=6, cblkh_exp=6, prec_w_exp=None, prec_h_exp=None):
+    """code blocks of one tile-component in the reference's walking order (structured array)"""
+    p = LayoutParams()
+    p.x0, p.y0, p.x1, p.y1, p.numres = x0, y0, x1, y1, numres
+    p.cblkw_exp, p.cblkh_exp = cblkw_exp, cblkh_exp
+    for r in range(33):
+        p.prec_w_exp[r] = 15 if prec_w_exp is None else (prec_w_exp[r] if r < len(prec_w_exp) else 15)
+        p.prec_h_exp[r] = 15 if prec_h_exp is None else (prec_h_exp[r] if r < len(prec_h_exp) else 15)
+    n = C.c_uint32()
+    check(lib.grkb_tile_layout(C.byref(p), None, 0, C.byref(n)), "grkb_tile_layout")
+    out = np.zeros(n.value, dtype=GEOM_DTYPE)
+    if n.value:
+        check(lib.grkb_tile_layout(C.byref(p), out.ctypes.data_as(C.POINTER(CblkGeom)), n.value,
+                                   C.byref(n)), "grkb_tile_layout")
+    return out
+
+
+def clamp_range(prec, sgnd):
+    if sgnd:
+        return -(1 << (prec - 1)), (1 << (prec - 1)) - 1
+    return 0, (1 << prec) - 1
+
+
+def tile_params(x0, y0, x1, y1, numcomps, numres, reversible, mct, prec, sgnd=0):
+    p = TileParams()
+    p.x0, p.y0, p.x1, p.y1 = x0, y0, x1, y1
+    p.numcomps, p.numres, p.reversible, p.mct = numcomps, numres, int(reversible), int(mct)
+    lo, hi = clamp_range(prec, sgnd)
+    for c in range(numcomps):
+        p.shift[c] = 0 if sgnd else 1 << (prec - 1)
+        p.lo[c], p.hi[c] = lo, hi
+    return p
+
+
+class PinnedArray:
+    """numpy view of page-locked host memory from grkb_host_alloc"""
+
+    def __init__(self, shape, dtype):
+        self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self.ptr = lib.grkb_host_alloc(max(self.nbytes, 1))
+        if not self.ptr:
+            raise GrokB200Error("grkb_host_alloc failed: " + lib.grkb_last_error().decode())
+        buf = (C.c_uint8 * max(self.nbytes, 1)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            lib.grkb_host_free(self.ptr)
+            self.ptr = None
+
+
+class TileDecoder:
+    """grkb_decoder: device-resident state for one tile geometry"""
+
+    def __init__(self, params, max_blocks=0, max_bytes=0):
+        self.params = params
+        self.h = C.c_void_p()
+        check(lib.grkb_decoder_create(C.byref(params), max_blocks, max_bytes, C.byref(self.h)),
+              "grkb_decoder_create")
+        self.W, self.H = params.x1 - params.x0, params.y1 - params.y0
+
+    def close(self):
+        if self.h:
+            lib.grkb_decoder_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def decode(self, blocks, segs, data, out=None, download=True):
+        """blocks: CBLK_DTYPE array, segs: SEG_DTYPE array, data: uint8 array (byte pool).
+        out: optional list of int32 (H, stride) arrays to receive the planes."""
+        blocks = np.ascontiguousarray(blocks, dtype=CBLK_DTYPE)
+        segs = np.ascontiguousarray(segs, dtype=SEG_DTYPE)
+        nc = self.params.numcomps
+        ptrs = None
+        stride = 0
+        if download:
+            if out is None:
+                out = [np.empty((self.H, self.W), dtype=np.int32) for _ in range(nc)]
+            stride = out[0].strides[0] // 4
+            ptrs = (C.c_void_p * nc)(*[o.ctypes.data for o in out])
+        st = C.c_uint32()
+        check(lib.grkb_decoder_decode(self.h, blocks.ctypes.data, len(blocks), segs.ctypes.data,
+                                      len(segs), data.ctypes.data, data.size, ptrs, stride,
+                                      C.byref(st)), "grkb_decoder_decode")
+        self.rejected = st.value
+        return out
+
+    def time_device(self, iters, warmup):
+        ms = (C.c_float * 4)()
+        n = C.c_uint32()
+        check(lib.grkb_decoder_time_device(self.h, iters, warmup, ms, C.byref(n)),
+              "grkb_decoder_time_device")
+        return dict(total_ms=ms[0], t1_ms=ms[1], dwt_ms=ms[2], dwt_last_ms=ms[3], launches=n.value)
+
+    def download(self):
+        nc = self.params.numcomps
+        out = [np.empty((self.H, self.W), dtype=np.int32) for _ in range(nc)]
+        ptrs = (C.c_void_p * nc)(*[o.ctypes.data for o in out])
+        check(lib.grkb_decoder_download(self.h, ptrs, self.W), "grkb_decoder_download")
+        return out
+
+
+def t1_decode(blocks, segs, data, planes, reversible):
+    """block decoder alone: writes the dequantised blocks into copies of `planes` (list of 2-D
+    int32/float32 arrays of identical shape) and returns them with the reject count"""
+    blocks = np.ascontiguousarray(blocks, dtype=CBLK_DTYPE)
+    segs = np.ascontiguousarray(segs, dtype=SEG_DTYPE)
+    a = [np.ascontiguousarray(p).copy() for p in planes]
+    h, w = a[0].shape
+    ptrs = (C.c_void_p * len(a))(*[p.ctypes.data for p in a])
+    st = C.c_uint32()
+    check(lib.grkb_t1_decode_host(blocks.ctypes.data, len(blocks), segs.ctypes.data, len(segs),
+                                  data.ctypes.data, data.size, ptrs, len(a), w, h, int(reversible),
+                                  C.byref(st)), "grkb_t1_decode_host")
+    return a, st.value

@@ -91,6 +91,136 @@ int grkb_mct_fdwt_host(void* const* planes, uint32_t ncomp, uint32_t stride, uin
 					   uint32_t y0, uint32_t x1, uint32_t y1, uint32_t numres, int reversible,
 					   int mct, const int32_t* shift);
 
+/* B. tile entry points --------------------------------------------------------------------- */
+
+/* One code block of a tile, as the reference's schedulers describe it
+ * (DecompressBlockExec / CompressBlockExec, src/lib/jp2/t1/BlockExec.h:22-84, filled by
+ * T1DecompressScheduler::prepareScheduleDecompress, t1/T1DecompressScheduler.cpp:27-75).
+ * Coordinates are relative to the tile-component buffer (Mallat layout above), i.e. the band
+ * offset is already included: x = cblk.x0 - band.x0 (+ w_{r-1} for HL/HH), same for y. */
+typedef struct grkb_cblk
+{
+	uint32_t x, y; /* top-left sample in the tile-component buffer */
+	uint16_t w, h; /* block size (w*h <= 4096, both <= 1024) */
+	uint8_t comp; /* component index */
+	uint8_t orient; /* 0 LL, 1 HL, 2 LH, 3 HH */
+	uint8_t numbps; /* MQ: cblk->numbps (magnitude bit-planes to decode / produced by encode) */
+	uint8_t cblk_sty; /* GRKB_CBLKSTY_* (mode switches; HT blocks: GRKB_CBLKSTY_HT) */
+	uint8_t roishift; /* region-of-interest up-shift (decode) */
+	uint8_t k_msbs; /* HT: band->numbps - cblk->numbps (missing MSBs), BlockExec.h:40 */
+	uint16_t numsegs; /* decode: codeword segments of this block (0: block not coded) */
+	uint32_t seg_first; /* decode: index of the first segment in the segment table */
+	uint32_t data_off; /* byte offset of the block's first byte in the byte pool */
+	uint32_t data_len; /* decode: total bytes; encode: capacity on input, bytes on output */
+	float scale; /* decode 9/7: MQ stepsize/2, HT stepsize (PostDecompressFilters.h:66-89,161-177);
+				  * encode 9/7: band stepsize (T1Part1.cpp:75-76) */
+} grkb_cblk;
+
+typedef struct grkb_seg
+{
+	uint32_t len; /* bytes of this codeword segment */
+	uint32_t numpasses; /* coding passes in it */
+} grkb_seg;
+
+#define GRKB_CBLKSTY_LAZY 0x01
+#define GRKB_CBLKSTY_RESET 0x02
+#define GRKB_CBLKSTY_TERMALL 0x04
+#define GRKB_CBLKSTY_VSC 0x08
+#define GRKB_CBLKSTY_PTERM 0x10
+#define GRKB_CBLKSTY_SEGSYM 0x20
+#define GRKB_CBLKSTY_HT 0x40
+
+#define GRKB_MAX_COMPS 4
+
+/* Geometry and sample format of one tile (all components share the tile-component rectangle:
+ * no sub-sampling in this round). */
+typedef struct grkb_tile_params
+{
+	uint32_t x0, y0, x1, y1; /* tile-component rectangle, canvas coordinates */
+	uint32_t numcomps; /* 1..GRKB_MAX_COMPS */
+	uint32_t numres; /* resolutions = decomposition levels + 1 */
+	int32_t reversible; /* 1: 5/3 + RCT, 0: 9/7 + ICT */
+	int32_t mct; /* 1: components 0..2 go through the RCT/ICT */
+	int32_t shift[GRKB_MAX_COMPS]; /* DC level shift (tccp->m_dc_level_shift) */
+	int32_t lo[GRKB_MAX_COMPS], hi[GRKB_MAX_COMPS]; /* clamp range (mct.cpp:556-571) */
+} grkb_tile_params;
+
+/* Code-block layout of one tile-component, in the reference's walking order (resolution ->
+ * band -> precinct -> code block; TileComponent::init, tile/TileComponent.cpp:69-167,
+ * t1/Resolution.h:38-80, t1/Precinct.h:44-69).  Host-only helper: no device involved. */
+typedef struct grkb_layout_params
+{
+	uint32_t x0, y0, x1, y1; /* tile-component rectangle, canvas coordinates */
+	uint32_t numres;
+	uint32_t cblkw_exp, cblkh_exp; /* log2 nominal code-block size */
+	uint32_t prec_w_exp[33], prec_h_exp[33]; /* log2 precinct size per resolution (15 = none) */
+} grkb_layout_params;
+
+typedef struct grkb_cblk_geom
+{
+	uint32_t x, y; /* position in the tile-component buffer (Mallat layout) */
+	uint32_t cx0, cy0; /* position in band coordinates (cblk->x0, cblk->y0) */
+	uint16_t w, h; /* may be 0 for degenerate blocks the reference also enumerates */
+	uint8_t res, band, orient, level; /* resolution, band index in it, orientation, decomposition level */
+	uint32_t precinct, cblkno;
+} grkb_cblk_geom;
+
+/* Fills out[0..cap) and *count (total blocks; call with out == NULL to size).  Returns 0, or -2
+ * if cap was too small. */
+int grkb_tile_layout(const grkb_layout_params* p, grkb_cblk_geom* out, uint32_t cap,
+					 uint32_t* count);
+
+typedef struct grkb_decoder grkb_decoder;
+
+/* Creates a tile decoder for one geometry on the calling thread's device: device planes, pinned
+ * staging and a stream.  max_blocks / max_bytes bound the per-tile descriptor table and byte
+ * pool (they grow on demand if exceeded). */
+int grkb_decoder_create(const grkb_tile_params* p, uint32_t max_blocks, size_t max_bytes,
+						grkb_decoder** out);
+void grkb_decoder_destroy(grkb_decoder* d);
+
+/* Whole-tile decode, the device side of TileProcessor::decompressT1 + mctDecompress
+ * (src/lib/jp2/tile/TileProcessor.cpp:334-383, :457-504) for all components at once:
+ * H2D of descriptors and code-block bytes, T1 (EBCOT/MQ or HT per block) with dequantisation
+ * fused into the store, inverse wavelet of every component, inverse MCT + DC shift + clamp fused
+ * into the last level, D2H of the int32 planes.
+ *   blocks/segs/bytes  host memory (bytes may be pinned; it is staged through pinned memory
+ *                      otherwise)
+ *   planes[c]          host destination, `stride` samples per row, (x1-x0) x (y1-y0) samples;
+ *                      NULL planes: results stay on the device (see grkb_decoder_download)
+ * status_out (may be NULL): number of blocks the coder rejected (they decode as zeros, the
+ * reference fails the tile: T1.cpp:1373-1377, ojph_block_decoder.cpp:1029-1043). */
+int grkb_decoder_decode(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
+						const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
+						int32_t* const* planes, uint32_t stride, uint32_t* status_out);
+
+/* Re-runs the device stages (T1, wavelet, MCT) of the last tile given to grkb_decoder_decode,
+ * inputs already resident in HBM, no host copies: `iters` passes after `warmup`, timed with CUDA
+ * events on the decoder's stream.  ms[0] = mean whole pass, ms[1] = mean T1 kernels,
+ * ms[2] = mean of all wavelet levels, ms[3] = mean of the last (largest) wavelet level kernel.
+ * launches_out (may be NULL): kernels launched per pass. */
+int grkb_decoder_time_device(grkb_decoder* d, uint32_t iters, uint32_t warmup, float ms[4],
+							 uint32_t* launches_out);
+
+/* Copies the decoded planes of the last pass to host memory. */
+int grkb_decoder_download(grkb_decoder* d, int32_t* const* planes, uint32_t stride);
+
+/* Stage-level door for the block decoder alone (parity tests): decodes `nblocks` blocks into a
+ * dense plane set exactly as T1Part1::decompress / T1HT::decompress + postProcess would
+ * (t1/t1_part1/T1Part1.cpp:133-161, t1/t1_ht/T1HT.cpp:134-187, tile/TileComponent.cpp:333-430).
+ * planes[c]: host int32/float planes of plane_h rows x stride samples, written only inside the
+ * block rectangles.  reversible selects the /2 (1) or x scale (0) dequantiser. */
+int grkb_t1_decode_host(const grkb_cblk* blocks, uint32_t nblocks, const grkb_seg* segs,
+						uint32_t nsegs, const uint8_t* bytes, size_t nbytes, void* const* planes,
+						uint32_t numcomps, uint32_t stride, uint32_t plane_h, int reversible,
+						uint32_t* status_out);
+
+/* Page-locked host memory for byte pools and output planes: copies to and from it are true
+ * asynchronous DMA (the decoder accepts any host pointer, pageable ones are staged by the
+ * driver). */
+void* grkb_host_alloc(size_t bytes);
+void grkb_host_free(void* p);
+
 /* C. diagnostics ------------------------------------------------------------------------------ */
 
 /* Times the device-resident wavelet back end (forward == 0: inverse DWT [+ fused inverse MCT])

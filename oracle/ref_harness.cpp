@@ -361,3 +361,71 @@ int ref_ht_decode(const uint8_t* data, uint32_t missing_msbs, uint32_t num_passe
 }
 
 } // extern "C"
+
+/* ------------------------------------------------------------------------------------- */
+/* Geometry: the code-block list of a tile-component as TileComponent::init builds it
+ * (tile/TileComponent.cpp:69-167), with each block's position in the tile buffer as
+ * toRelativeCoordinates computes it (tile/TileComponentWindowBuffer.h:404-436).           */
+extern "C" {
+struct ref_cblk_geom
+{
+	uint32_t x, y, cx0, cy0, w, h, res, band, orient, precinct, cblkno;
+};
+int ref_layout(uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t numres, uint32_t cblkw,
+			   uint32_t cblkh, const uint32_t* pw, const uint32_t* ph, ref_cblk_geom* out,
+			   uint32_t cap)
+{
+	CodingParams cp;
+	TileCodingParams tcp;
+	TileComponentCodingParams tccp;
+	TileComponent tilec;
+	memset(&cp.m_coding_params, 0, sizeof(cp.m_coding_params));
+	tccp.numresolutions = (uint8_t)numres;
+	tccp.cblkw = (uint8_t)cblkw;
+	tccp.cblkh = (uint8_t)cblkh;
+	tccp.qmfbid = 1;
+	tccp.numgbits = 2;
+	tccp.roishift = 0;
+	for(uint32_t i = 0; i < GRK_J2K_MAXRLVLS; ++i)
+	{
+		tccp.precinctWidthExp[i] = i < numres ? pw[i] : 15;
+		tccp.precinctHeightExp[i] = i < numres ? ph[i] : 15;
+	}
+	for(uint32_t i = 0; i < GRK_J2K_MAXBANDS; ++i)
+	{
+		tccp.stepsizes[i].expn = 10;
+		tccp.stepsizes[i].mant = 0;
+	}
+	grkRectU32 r(x0, y0, x1, y1);
+	if(!tilec.init(true, true, r, 8, &cp, &tcp, &tccp, nullptr))
+		return -1;
+	if(!tilec.allocWindowBuffer(r))
+		return -1;
+	uint32_t n = 0;
+	for(uint8_t resno = 0; resno < numres; ++resno)
+	{
+		auto res = tilec.tileCompResolution + resno;
+		for(uint8_t bi = 0; bi < res->numTileBandWindows; ++bi)
+		{
+			auto band = res->tileBand + bi;
+			for(auto prc : band->precincts)
+			{
+				for(uint64_t cb = 0; cb < prc->getNumCblks(); ++cb)
+				{
+					auto b = prc->getCodeBlockBounds(cb);
+					if(n < cap)
+					{
+						uint32_t bx = b.x0, by = b.y0;
+						tilec.getBuffer()->toRelativeCoordinates(resno, band->orientation, bx, by);
+						out[n] = ref_cblk_geom{bx,	  by,	 b.x0,	b.y0, b.width(), b.height(), resno, bi,
+											   (uint32_t)band->orientation, (uint32_t)prc->precinctIndex,
+											   (uint32_t)cb};
+					}
+					++n;
+				}
+			}
+		}
+	}
+	return (int)n;
+}
+}
