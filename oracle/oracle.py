@@ -221,3 +221,36 @@ def orc_t1_decode(data, segs, numbps, w, h, **kw):
 
 def ref_t1_decode(data, segs, numbps, w, h, **kw):
     return _t1_decode(True, data, segs, numbps, w, h, **kw)
+
+
+# ---------------------------------------------------------------- whole codec (reference C API)
+
+def ref_codec_encode(planes, prec, irreversible, ht=False, numres=6, cblk=(64, 64), tile=(0, 0),
+                     threads=0):
+    """stock CPU encoder on a memory stream -> codestream bytes (uint8 array)"""
+    a = [np.ascontiguousarray(p, dtype=np.int32) for p in planes]
+    h, w = a[0].shape
+    cap = w * h * len(a) * 4 + (1 << 20)
+    out = np.zeros(cap, dtype=np.uint8)
+    ptrs = (C.c_void_p * len(a))(*[p.ctypes.data for p in a])
+    fn = ref().ref_codec_encode
+    fn.restype = C.c_long
+    n = fn(ptrs, C.c_uint32(len(a)), C.c_uint32(w), C.c_uint32(h), C.c_uint32(prec),
+           C.c_int(int(irreversible)), C.c_int(int(ht)), C.c_uint32(numres), C.c_uint32(cblk[0]),
+           C.c_uint32(cblk[1]), C.c_uint32(tile[0]), C.c_uint32(tile[1]), C.c_uint32(threads),
+           _p(out), C.c_size_t(cap))
+    if n < 0:
+        raise RuntimeError("reference encoder failed")
+    return out[:n].copy()
+
+
+def ref_codec_decode(cs, ncomp, w, h, threads=0, want_planes=True):
+    """stock CPU decoder on a memory stream -> list of int32 planes (or None)"""
+    cs = np.ascontiguousarray(cs, dtype=np.uint8)
+    planes = [np.zeros((h, w), dtype=np.int32) for _ in range(ncomp)] if want_planes else None
+    ptrs = (C.c_void_p * ncomp)(*[p.ctypes.data for p in planes]) if want_planes else None
+    rc = ref().ref_codec_decode(_p(cs), C.c_size_t(cs.size), C.c_uint32(threads), ptrs,
+                                C.c_uint32(ncomp), C.c_uint32(w), C.c_uint32(h))
+    if rc != 0:
+        raise RuntimeError("reference decoder failed (%d)" % rc)
+    return planes

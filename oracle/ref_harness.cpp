@@ -429,3 +429,121 @@ int ref_layout(uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, uint32_t numr
 	return (int)n;
 }
 }
+
+/* ------------------------------------------------------------------------------------- */
+/* Whole codec through the reference's PUBLIC C API (grok.h) on memory streams: the stock
+ * CPU encoder and decoder, used as the end-to-end oracle and as bench.py's reference arm. */
+extern "C" {
+
+/* planes: numcomps dense w*h int32 planes. Returns codestream length, or -1.
+ * Mirrors what grk_compress does after argument parsing (src/bin/jp2/grk_compress.cpp:
+ * 820-828 lossless/all-pass default, :1978-1981 MCT default, :1123-1124 HT guard bits). */
+long ref_codec_encode(int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t h, uint32_t prec,
+					  int irreversible, int ht, uint32_t numres, uint32_t cblkw, uint32_t cblkh,
+					  uint32_t tile_w, uint32_t tile_h, uint32_t numthreads, uint8_t* out,
+					  size_t out_cap)
+{
+	grk_initialize(nullptr, numthreads);
+	grk_cparameters p;
+	grk_compress_set_default_params(&p);
+	p.cod_format = GRK_J2K_FMT;
+	p.numresolution = (uint8_t)numres;
+	p.cblockw_init = cblkw;
+	p.cblockh_init = cblkh;
+	p.irreversible = irreversible != 0;
+	p.layer_rate[0] = 0;
+	p.numlayers = 1;
+	p.allocationByRateDistoration = true;
+	p.mct = numcomps >= 3 ? 1 : 0;
+	p.numThreads = numthreads;
+	if(ht)
+	{
+		p.isHT = true;
+		p.numgbits = 1;
+		p.cblk_sty = GRK_CBLKSTY_HT;
+	}
+	if(tile_w && tile_h)
+	{
+		p.tile_size_on = true;
+		p.t_width = tile_w;
+		p.t_height = tile_h;
+	}
+	std::vector<grk_image_cmptparm> cp(numcomps);
+	for(auto& c : cp)
+	{
+		memset(&c, 0, sizeof(c));
+		c.prec = (uint8_t)prec;
+		c.sgnd = false;
+		c.dx = c.dy = 1;
+		c.w = w;
+		c.h = h;
+	}
+	auto image = grk_image_new((uint16_t)numcomps, cp.data(),
+							   numcomps >= 3 ? GRK_CLRSPC_SRGB : GRK_CLRSPC_GRAY, true);
+	if(!image)
+		return -1;
+	image->x0 = image->y0 = 0;
+	image->x1 = w;
+	image->y1 = h;
+	for(uint32_t c = 0; c < numcomps; ++c)
+	{
+		auto comp = image->comps + c;
+		for(uint32_t y = 0; y < h; ++y)
+			memcpy(comp->data + (size_t)y * comp->stride, planes[c] + (size_t)y * w,
+				   sizeof(int32_t) * w);
+	}
+	long rc = -1;
+	auto stream = grk_stream_create_mem_stream(out, out_cap, false, false);
+	auto codec = stream ? grk_compress_create(GRK_CODEC_J2K, stream) : nullptr;
+	if(codec && grk_compress_init(codec, &p, image) && grk_compress_start(codec) &&
+	   grk_compress(codec) && grk_compress_end(codec))
+		rc = (long)grk_stream_get_write_mem_stream_length(stream);
+	if(codec)
+		grk_object_unref(codec);
+	if(stream)
+		grk_object_unref(stream);
+	grk_object_unref(&image->obj);
+	return rc;
+}
+
+/* Full decode of a codestream in memory with the stock multithreaded CPU decoder.
+ * planes may be NULL (timing only). Returns 0 on success. */
+int ref_codec_decode(uint8_t* cs, size_t len, uint32_t numthreads, int32_t** planes,
+					 uint32_t numcomps, uint32_t w, uint32_t h)
+{
+	grk_initialize(nullptr, numthreads);
+	grk_decompress_parameters dp;
+	memset(&dp, 0, sizeof(dp));
+	grk_decompress_set_default_params(&dp.core);
+	auto stream = grk_stream_create_mem_stream(cs, len, false, true);
+	if(!stream)
+		return -1;
+	int rc = -1;
+	auto codec = grk_decompress_create(GRK_CODEC_J2K, stream);
+	grk_header_info hdr;
+	memset(&hdr, 0, sizeof(hdr));
+	if(codec && grk_decompress_init(codec, &dp.core) && grk_decompress_read_header(codec, &hdr) &&
+	   grk_decompress(codec, nullptr))
+	{
+		auto image = grk_decompress_get_composited_image(codec);
+		rc = image ? 0 : -2;
+		if(image && planes)
+		{
+			if(image->numcomps < numcomps || image->comps[0].w != w || image->comps[0].h != h)
+				rc = -3;
+			else
+				for(uint32_t c = 0; c < numcomps; ++c)
+				{
+					auto comp = image->comps + c;
+					for(uint32_t y = 0; y < h; ++y)
+						memcpy(planes[c] + (size_t)y * w, comp->data + (size_t)y * comp->stride,
+							   sizeof(int32_t) * w);
+				}
+		}
+	}
+	if(codec)
+		grk_object_unref(codec);
+	grk_object_unref(stream);
+	return rc;
+}
+}

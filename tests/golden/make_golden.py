@@ -85,3 +85,15 @@ for sty in (0, 0x01, 0x02, 0x04, 0x08, 0x10, 0x20, 0x3F, 0x05):
 t["cases"] = np.array(cases, dtype=np.int32)
 np.savez_compressed(os.path.join(HERE, "t1_mq.npz"), **t)
 print("golden fixtures written:", os.listdir(HERE))
+
+# ---- end to end: the stock codec (public C API) on small synthetic images --------------------
+import codec_helpers as H  # noqa: E402
+e = {}
+e2e_cases = [(96, 80, 8, 0, 4), (120, 67, 12, 1, 5), (64, 90, 16, 1, 3), (150, 40, 12, 0, 6)]
+e["cases"] = np.array(e2e_cases, dtype=np.int32)
+for k, (w, h, prec, irr, nr) in enumerate(e2e_cases):
+    img = H.synth_image(w, h, 3, prec, 100 + k)
+    cs = O.ref_codec_encode(img, prec, irr, numres=nr)
+    e["decoded_%d" % k] = np.stack(O.ref_codec_decode(cs, 3, w, h)).astype(np.int32)
+np.savez_compressed(os.path.join(HERE, "e2e.npz"), **e)
+print("e2e fixture written")

@@ -141,3 +141,18 @@ def test_tile_decode_matches_oracle(gpu, orc, reversible, mct, ncomp, prec, w, h
     for c in range(ncomp):
         assert np.array_equal(again[c], want[c])
     dec.close()
+
+
+def test_tile_decode_matches_reference_codec_golden(gpu, orc):
+    """GPU tile decode == what the stock reference decoder produced for the same image
+    (tests/golden/e2e.npz, generated by the reference's public C API)"""
+    e = np.load(os.path.join(G, "e2e.npz"))
+    for k, (w, h, prec, irr, nr) in enumerate(e["cases"]):
+        w, h, prec, irr, nr = int(w), int(h), int(prec), int(irr), int(nr)
+        img = H.synth_image(w, h, 3, prec, 100 + k)
+        coefs = H.forward_oracle(img, prec, not irr, nr, 1)
+        tile = H.encode_tile(coefs, prec, not irr, nr)
+        dec = T.TileDecoder(T.tile_params(0, 0, w, h, 3, nr, not irr, 1, prec))
+        got = dec.decode(tile["blocks"], tile["segs"], tile["data"])
+        dec.close()
+        assert np.array_equal(np.stack(got), e["decoded_%d" % k]), k
