@@ -11,7 +11,9 @@
 // a, c, ct and the adapted state of its context), so parallelism is across blocks.  A warp
 // owns a block: all lanes clear and later dequantise + store the block (coalesced rows into
 // the Mallat coefficient plane); lane 0 walks the coding passes over a shared-memory state
-// array (one word per stripe column, layout in t1.cuh) and a shared-memory sample array.
+// array (one word per stripe column, layout in t1.cuh); samples are written straight into
+// the block's rectangle of the (L2-resident) plane: a store when a sample becomes significant,
+// a fire-and-forget red.add per refinement bit (the sign is kept in the state word).
 // Warps pull blocks from a global work counter, longest blocks first.  Not HBM-bound: traffic
 // is the compressed bytes in and 4 B/sample out; the bound is the serial decision rate.
 #include "t1.cuh"
@@ -179,7 +181,8 @@ static __device__ __forceinline__ void reset_states(uint8_t* cxs)
 struct Blk
 {
 	uint32_t* fl; // state words, (w+2) x (nstripes+2)
-	int32_t* data; // w x h samples, decoder's x2 fixed point
+	int32_t* data; // the block's rectangle in the coefficient plane (x2 fixed point until dequantised)
+	uint32_t ds; // row pitch of data
 	uint32_t w, h, fs; // fs = w + 2
 	const uint8_t* zc; // zero-coding table of this band orientation
 	const uint8_t* sc;
@@ -232,7 +235,7 @@ static __device__ void cleanup_pass(const Blk& b, Mq& q, uint8_t* cxs, const uin
 	{
 		const uint32_t rows = min(4u, b.h - k);
 		uint32_t* fp = b.fl + (s + 1) * b.fs + 1;
-		int32_t* dp = b.data + k * b.w;
+		int32_t* dp = b.data + (size_t)k * b.ds;
 		for(uint32_t x = 0; x < b.w; ++x, ++fp, ++dp)
 		{
 			uint32_t f = *fp;
@@ -258,7 +261,7 @@ static __device__ void cleanup_pass(const Blk& b, Mq& q, uint8_t* cxs, const uin
 				sign_only = false;
 				const uint32_t e = b.sc[sc_index(f, fp[-1], fp[1], r)];
 				const uint32_t v = mq_decode(q, cxs, mqt, e & 0x7Fu) ^ (e >> 7);
-				dp[r * b.w] = v ? -oph : oph;
+				dp[r * b.ds] = v ? -oph : oph;
 				mark_significant(b, fp, f, r, v);
 			}
 			*fp = f & ~T1_PI_ALL;
@@ -282,7 +285,7 @@ static __device__ void sig_pass(const Blk& b, Mq& q, uint8_t* cxs, const uint32_
 	{
 		const uint32_t rows = min(4u, b.h - k);
 		uint32_t* fp = b.fl + (s + 1) * b.fs + 1;
-		int32_t* dp = b.data + k * b.w;
+		int32_t* dp = b.data + (size_t)k * b.ds;
 		for(uint32_t x = 0; x < b.w; ++x, ++fp, ++dp)
 		{
 			uint32_t f = *fp;
@@ -297,7 +300,7 @@ static __device__ void sig_pass(const Blk& b, Mq& q, uint8_t* cxs, const uint32_
 					if(raw_decode(q))
 					{
 						const uint32_t v = raw_decode(q);
-						dp[r * b.w] = v ? -oph : oph;
+						dp[r * b.ds] = v ? -oph : oph;
 						mark_significant(b, fp, f, r, v);
 					}
 				}
@@ -305,7 +308,7 @@ static __device__ void sig_pass(const Blk& b, Mq& q, uint8_t* cxs, const uint32_
 				{
 					const uint32_t e = b.sc[sc_index(f, fp[-1], fp[1], r)];
 					const uint32_t v = mq_decode(q, cxs, mqt, e & 0x7Fu) ^ (e >> 7);
-					dp[r * b.w] = v ? -oph : oph;
+					dp[r * b.ds] = v ? -oph : oph;
 					mark_significant(b, fp, f, r, v);
 				}
 				f |= T1_PI(r);
@@ -325,7 +328,7 @@ static __device__ void ref_pass(const Blk& b, Mq& q, uint8_t* cxs, const uint32_
 	{
 		const uint32_t rows = min(4u, b.h - k);
 		uint32_t* fp = b.fl + (s + 1) * b.fs + 1;
-		int32_t* dp = b.data + k * b.w;
+		int32_t* dp = b.data + (size_t)k * b.ds;
 		for(uint32_t x = 0; x < b.w; ++x, ++fp, ++dp)
 		{
 			uint32_t f = *fp;
@@ -345,8 +348,9 @@ static __device__ void ref_pass(const Blk& b, Mq& q, uint8_t* cxs, const uint32_
 																	   : T1_CTX_MAG;
 					v = mq_decode(q, cxs, mqt, cx);
 				}
-				const int32_t d = dp[r * b.w];
-				dp[r * b.w] = d + ((v ^ (uint32_t)(d < 0)) ? poshalf : -poshalf);
+				// the sign lives in the state word, so the update is a fire-and-forget reduction
+				const uint32_t neg = (f >> (18 + r + 1)) & 1u;
+				atomicAdd(&dp[r * b.ds], (v ^ neg) ? poshalf : -poshalf);
 				f |= T1_MU(r);
 			}
 			*fp = f;
@@ -374,10 +378,9 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 	__syncthreads();
 
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const size_t per_warp = 32 + ((size_t)l.max_flag_words + l.max_area) * 4;
+	const size_t per_warp = 32 + (size_t)l.max_flag_words * 4;
 	uint8_t* cxs = warp_base + warp * per_warp;
 	uint32_t* fl = reinterpret_cast<uint32_t*>(cxs + 32);
-	int32_t* data = reinterpret_cast<int32_t*>(fl + l.max_flag_words);
 
 	for(;;)
 	{
@@ -391,7 +394,8 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 		const grkb_cblk cb = l.blocks[bi];
 		if(cb.cblk_sty & GRKB_CBLKSTY_HT)
 			continue;
-		const uint32_t w = cb.w, h = cb.h, area = w * h;
+		const uint32_t w = cb.w, h = cb.h;
+		int32_t* blk_data = reinterpret_cast<int32_t*>(l.planes[cb.comp]) + (size_t)cb.y * l.stride + cb.x;
 		const uint32_t fs = w + 2, nstripes = (h + 3) >> 2, nfl = fs * (nstripes + 2);
 		bool bad = (int)cb.numbps >= 31 - 6; // maxBitPlanesGRK, T1.cpp:1373-1377
 		const bool coded = cb.numsegs != 0 && !bad;
@@ -399,15 +403,17 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 		{
 			for(uint32_t i = lane; i < nfl; i += 32)
 				fl[i] = 0;
-			for(uint32_t i = lane; i < area; i += 32)
-				data[i] = 0;
+			for(uint32_t y = 0; y < h; ++y)
+				for(uint32_t x = lane; x < w; x += 32)
+					blk_data[(size_t)y * l.stride + x] = 0;
 		}
 		__syncwarp();
 		if(coded && lane == 0)
 		{
 			Blk b;
 			b.fl = fl;
-			b.data = data;
+			b.data = blk_data;
+			b.ds = l.stride;
 			b.w = w;
 			b.h = h;
 			b.fs = fs;
@@ -462,14 +468,13 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 			atomicAdd(l.status, 1u);
 		// dequantise + store: ShiftFilter (/2, C truncation) or ScaleFilter (x stepsize/2),
 		// Roi* variants when roishift != 0 (PostDecompressFilters.h:7-89)
-		int32_t* plane = reinterpret_cast<int32_t*>(l.planes[cb.comp]);
 		const int32_t thresh = cb.roishift ? (1 << cb.roishift) : 0x7FFFFFFF;
 		for(uint32_t y = 0; y < h; ++y)
 		{
-			int32_t* dst = plane + (size_t)(cb.y + y) * l.stride + cb.x;
+			int32_t* dst = blk_data + (size_t)y * l.stride;
 			for(uint32_t x = lane; x < w; x += 32)
 			{
-				int32_t v = coded ? data[y * w + x] : 0;
+				int32_t v = coded ? dst[x] : 0;
 				int32_t mag = abs(v);
 				if(mag >= thresh)
 				{
@@ -497,7 +502,7 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 		grkb_set_error("t1: cannot upload coding tables");
 		return -1;
 	}
-	const size_t per_warp = 32 + ((size_t)l.max_flag_words + l.max_area) * 4;
+	const size_t per_warp = 32 + (size_t)l.max_flag_words * 4;
 	const size_t fixed = 94 * 4 + 2048 + 256;
 	// warps per CTA: whatever packs most code blocks into the 227 KB of an SM
 	int best_nw = 0, best_total = 0;
