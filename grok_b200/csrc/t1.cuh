@@ -58,6 +58,7 @@ struct T1Launch
 	uint32_t* status; // device: count of rejected blocks
 	uint32_t max_area; // max w*h over MQ blocks
 	uint32_t max_flag_words; // max (w+2)*(ceil(h/4)+2) over MQ blocks
+	uint32_t max_ht_w; // max width over HT blocks
 };
 int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s);
 int grkb_launch_t1_ht_decode(const T1Launch& l, cudaStream_t s);

@@ -1,10 +1,487 @@
-// t1_ht_dec.cu -- HTJ2K (ISO/IEC 15444-15) code-block decoder, sm_100a.  (under construction)
+// t1_ht_dec.cu -- HTJ2K (ISO/IEC 15444-15) cleanup-pass code-block decoder with the HT
+// dequantisers fused into the store, sm_100a.  One code block per warp.
+//
+// Replaces, behind the C-ABI, the reference's
+//   T1HT::decompress               src/lib/jp2/t1/t1_ht/T1HT.cpp:134-187
+//   ojph_decode_codeblock          t1/t1_ht/coding/ojph_block_decoder.cpp:989-1626 (cleanup pass)
+//   ShiftHTFilter / ScaleHTFilter / RoiShiftHT / RoiScaleHT   filters/PostDecompressFilters.h:91-177
+//
+// Shape (first version): all lanes zero the block's rectangle in the coefficient plane; lane 0
+// walks the quad rows, reading the three byte streams of the segment (MEL forward, VLC
+// backward, MagSgn forward) through 64-bit register accumulators, with the CxtVLC decode
+// tables and the per-column "north" state (significance, magnitude exponent) in shared memory,
+// and stores sign-magnitude samples straight into the (L2-resident) plane; then all lanes
+// dequantise the rectangle in place with coalesced rows.  Not HBM-bound: traffic is the coded
+// bytes in and 4 B/sample out.  SigProp / MagRef passes cannot reach this decoder through Grok
+// (T1HT.cpp:171-173 passes lengths2 = 0, which ojph_block_decoder.cpp:1014-1020 rejects for
+// more than one pass); such blocks are rejected here too and counted in the status word.
 #include "t1.cuh"
+#include <mutex>
+
+#include "ht_cxtvlc.inc"
+
+namespace
+{
+// device decode table entry: len | u_off << 3 | rho << 4 | e_k << 8 | e_1 << 12
+struct HtTables
+{
+	uint16_t dec[2][1024];
+};
+
+std::mutex g_mu;
+HtTables* g_dev[64] = {};
+
+const HtTables* ht_tables_device()
+{
+	int dev = 0;
+	if(cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+		return nullptr;
+	std::lock_guard<std::mutex> lk(g_mu);
+	if(g_dev[dev])
+		return g_dev[dev];
+	static HtTables h;
+	for(int t = 0; t < 2; ++t)
+	{
+		const unsigned int* src = t ? HT_CXTVLC_ROWN : HT_CXTVLC_ROW0;
+		const size_t n = t ? sizeof(HT_CXTVLC_ROWN) / 4 : sizeof(HT_CXTVLC_ROW0) / 4;
+		for(uint32_t i = 0; i < 1024; ++i)
+		{
+			uint16_t e = 0;
+			for(size_t j = 0; j < n; ++j)
+			{
+				const uint32_t w = src[j];
+				const uint32_t len = (w >> 23) & 7u;
+				if((w & 7u) == (i >> 7) && ((w >> 16) & 127u) == ((i & 127u) & ((1u << len) - 1)))
+					e = (uint16_t)(len | (((w >> 7) & 1u) << 3) | (((w >> 3) & 15u) << 4) |
+								   (((w >> 8) & 15u) << 8) | (((w >> 12) & 15u) << 12));
+			}
+			h.dec[t][i] = e;
+		}
+	}
+	HtTables* d = nullptr;
+	if(cudaMalloc(&d, sizeof(HtTables)) != cudaSuccess)
+		return nullptr;
+	if(cudaMemcpy(d, &h, sizeof(HtTables), cudaMemcpyHostToDevice) != cudaSuccess)
+	{
+		cudaFree(d);
+		return nullptr;
+	}
+	g_dev[dev] = d;
+	return d;
+}
+
+struct Streams
+{
+	const uint8_t* d;
+	// MEL
+	int mel_pos, mel_left;
+	uint32_t mel_acc;
+	int mel_bits, mel_unstuff, mel_k, mel_run, mel_one;
+	// VLC (backward)
+	int vlc_pos, vlc_real, vlc_unstuff, vlc_bits;
+	uint64_t vlc_acc;
+	// MagSgn (forward)
+	int ms_pos, ms_left, ms_unstuff, ms_bits;
+	uint64_t ms_acc;
+};
+
+static __device__ __forceinline__ int mel_bit(Streams& s)
+{
+	if(s.mel_bits == 0)
+	{
+		uint32_t b = 0xFF;
+		if(s.mel_left > 0)
+		{
+			b = __ldg(s.d + s.mel_pos);
+			if(s.mel_left == 1)
+				b |= 0xF;
+			s.mel_pos++;
+		}
+		s.mel_left--;
+		s.mel_bits = 8 - s.mel_unstuff;
+		s.mel_acc = b;
+		s.mel_unstuff = (b == 0xFF);
+	}
+	s.mel_bits--;
+	return (int)((s.mel_acc >> s.mel_bits) & 1u);
+}
+
+// one MEL symbol (ISO 15444-15 7.3.3; reference: mel_decode / mel_get_run, :170-285)
+static __device__ __forceinline__ int mel_event(Streams& s)
+{
+	if(s.mel_run == 0 && !s.mel_one)
+	{
+		// exponents 0,0,0,1,1,1,2,2,2,3,3,4,5 packed 3 bits each
+		const int e = (int)((05433222111000ull >> (3 * s.mel_k)) & 7ull);
+		if(mel_bit(s))
+		{
+			s.mel_run = 1 << e;
+			s.mel_k = min(s.mel_k + 1, 12);
+		}
+		else
+		{
+			int r = 0;
+			for(int i = 0; i < e; ++i)
+				r = (r << 1) | mel_bit(s);
+			s.mel_run = r;
+			s.mel_k = max(s.mel_k - 1, 0);
+			s.mel_one = 1;
+		}
+	}
+	if(s.mel_run > 0)
+	{
+		s.mel_run--;
+		return 0;
+	}
+	s.mel_one = 0;
+	return 1;
+}
+
+// rev_read, ojph_block_decoder.cpp:327-365 (byte-wise; bytes before the block start read as 0)
+static __device__ __forceinline__ uint32_t vlc_peek(Streams& s)
+{
+	while(s.vlc_bits < 32)
+	{
+		uint32_t b = 0;
+		if(s.vlc_real > 0)
+		{
+			b = s.vlc_pos >= 0 ? (uint32_t)__ldg(s.d + s.vlc_pos) : 0u;
+			s.vlc_real--;
+		}
+		s.vlc_pos--;
+		const int w = 8 - ((s.vlc_unstuff && (b & 0x7F) == 0x7F) ? 1 : 0);
+		s.vlc_acc |= (uint64_t)b << s.vlc_bits;
+		s.vlc_bits += w;
+		s.vlc_unstuff = b > 0x8F;
+	}
+	return (uint32_t)s.vlc_acc;
+}
+static __device__ __forceinline__ void vlc_skip(Streams& s, uint32_t n)
+{
+	s.vlc_acc >>= n;
+	s.vlc_bits -= (int)n;
+}
+
+// frwd_read<0xFF>, ojph_block_decoder.cpp:871-900
+static __device__ __forceinline__ uint32_t ms_peek(Streams& s)
+{
+	while(s.ms_bits < 32)
+	{
+		uint32_t b = 0xFF;
+		if(s.ms_left > 0)
+			b = __ldg(s.d + s.ms_pos);
+		s.ms_pos++;
+		s.ms_left--;
+		s.ms_acc |= (uint64_t)b << s.ms_bits;
+		s.ms_bits += 8 - s.ms_unstuff;
+		s.ms_unstuff = (b == 0xFF);
+	}
+	return (uint32_t)s.ms_acc;
+}
+static __device__ __forceinline__ void ms_skip(Streams& s, uint32_t n)
+{
+	s.ms_acc >>= n;
+	s.ms_bits -= (int)n;
+}
+
+static __device__ __forceinline__ void streams_init(Streams& s, const uint8_t* d, int lcup, int scup)
+{
+	s.d = d;
+	s.mel_pos = lcup - scup;
+	s.mel_left = scup - 1;
+	s.mel_acc = 0;
+	s.mel_bits = s.mel_unstuff = s.mel_k = s.mel_run = s.mel_one = 0;
+	const uint32_t first = __ldg(d + lcup - 2);
+	s.vlc_acc = first >> 4;
+	s.vlc_bits = 4 - (((s.vlc_acc & 7) == 7) ? 1 : 0);
+	s.vlc_unstuff = (first | 0xF) > 0x8F;
+	s.vlc_pos = lcup - 3;
+	// real bytes the reference delivers before zeros: 1 + (address & 3) single bytes, then whole
+	// 32-bit words while any byte of the segment is left (rev_init, :392-421)
+	int size = scup - 2;
+	int tnum = min(1 + (s.vlc_pos & 3), size);
+	tnum = max(tnum, 0);
+	size -= tnum;
+	s.vlc_real = tnum + (size > 0 ? ((size + 3) >> 2) << 2 : 0);
+	s.ms_pos = 0;
+	s.ms_left = lcup - scup;
+	s.ms_unstuff = 0;
+	s.ms_bits = 0;
+	s.ms_acc = 0;
+}
+
+// prefix of one u value: returns prefix length; suffix length and base value by reference
+static __device__ __forceinline__ uint32_t uvlc_prefix(uint32_t bits, uint32_t& suf, uint32_t& base)
+{
+	if(bits & 1)
+	{
+		suf = 0;
+		base = 1;
+		return 1;
+	}
+	if(bits & 2)
+	{
+		suf = 0;
+		base = 2;
+		return 2;
+	}
+	suf = (bits & 4) ? 1 : 5;
+	base = (bits & 4) ? 3 : 5;
+	return 3;
+}
+
+// decode_init_uvlc / decode_noninit_uvlc, ojph_block_decoder.cpp:664-838
+static __device__ __forceinline__ uint32_t uvlc_decode(uint32_t vlc, uint32_t mode, bool initial,
+														uint32_t& u0, uint32_t& u1)
+{
+	uint32_t used, s0, b0, s1, b1, p;
+	u0 = u1 = 1;
+	if(mode == 0)
+		return 0;
+	if(mode <= 2)
+	{
+		p = uvlc_prefix(vlc, s0, b0);
+		vlc >>= p;
+		b0 += vlc & ((1u << s0) - 1);
+		if(mode == 1)
+			u0 = b0 + 1;
+		else
+			u1 = b0 + 1;
+		return p + s0;
+	}
+	p = uvlc_prefix(vlc, s0, b0);
+	vlc >>= p;
+	used = p;
+	if(initial && mode == 3 && p > 2)
+	{
+		u1 = (vlc & 1) + 2;
+		vlc >>= 1;
+		u0 = b0 + (vlc & ((1u << s0) - 1)) + 1;
+		return used + 1 + s0;
+	}
+	p = uvlc_prefix(vlc, s1, b1);
+	vlc >>= p;
+	used += p + s0 + s1;
+	const uint32_t off = (initial && mode == 4) ? 3 : 1;
+	u0 = b0 + (vlc & ((1u << s0) - 1)) + off;
+	vlc >>= s0;
+	u1 = b1 + (vlc & ((1u << s1) - 1)) + off;
+	return used;
+}
+
+constexpr int HT_THREADS = 256; // 8 warps = 8 code blocks in flight per CTA
+
+// Cleanup pass of one block by one lane.  north/cur: per-column significance (bit 7) and
+// magnitude exponent (low 7 bits) of the bottom sample row of the previous / current quad row,
+// index = column + 1.  Returns false if the stream is rejected.
+static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missing_msbs, uint32_t w,
+								   uint32_t h, uint32_t* out, uint32_t ostride,
+								   const uint16_t* dec, uint8_t* north, uint8_t* cur, uint32_t ncol)
+{
+	const uint32_t p = 30 - missing_msbs;
+	const int scup = ((int)__ldg(data + lcup - 1) << 4) + (__ldg(data + lcup - 2) & 0xF);
+	if(scup < 2 || scup > lcup || scup > 4079)
+		return false;
+	Streams s;
+	streams_init(s, data, lcup, scup);
+	for(uint32_t y = 0; y < h; y += 2)
+	{
+		const bool initial = (y == 0);
+		const uint16_t* tbl = dec + (initial ? 0 : 1024);
+		uint32_t carry = 0;
+		for(uint32_t i = 0; i < ncol; ++i)
+			cur[i] = 0;
+		for(uint32_t x = 0; x < w; x += 4)
+		{
+			uint32_t tw[2] = {0, 0};
+			const uint32_t nq = (x + 2 < w) ? 2 : 1;
+			for(uint32_t q = 0; q < nq; ++q)
+			{
+				const uint32_t c0 = x + 2 * q;
+				uint32_t cq = carry;
+				if(!initial)
+				{
+					cq |= (uint32_t)((north[c0] | north[c0 + 1]) >> 7);
+					cq |= (uint32_t)((north[c0 + 2] | north[c0 + 3]) >> 7) << 2;
+				}
+				uint32_t t = tbl[(cq << 7) | (vlc_peek(s) & 0x7F)];
+				if(cq == 0 && !mel_event(s))
+					t = 0;
+				vlc_skip(s, t & 7u);
+				tw[q] = t;
+				const uint32_t rho = (t >> 4) & 15u;
+				carry = initial ? (((rho | (rho >> 1)) & 1u) | ((rho >> 1) & 6u))
+								: ((((rho >> 2) | (rho >> 3)) & 1u) << 1);
+			}
+			uint32_t mode = ((tw[0] >> 3) & 1u) | (((tw[1] >> 3) & 1u) << 1);
+			if(initial && mode == 3 && mel_event(s))
+				mode = 4;
+			uint32_t U[2];
+			vlc_skip(s, uvlc_decode(vlc_peek(s), mode, initial, U[0], U[1]));
+			if(!initial)
+			{
+#pragma unroll
+				for(uint32_t q = 0; q < 2; ++q)
+				{
+					const uint32_t rho = (tw[q] >> 4) & 15u;
+					if(rho & (rho - 1))
+					{
+						const uint32_t c0 = x + 2 * q;
+						uint32_t E = max(max(north[c0] & 0x7Fu, north[c0 + 1] & 0x7Fu),
+										 max(north[c0 + 2] & 0x7Fu, north[c0 + 3] & 0x7Fu));
+						U[q] += E > 2 ? E - 2 : 0;
+					}
+				}
+			}
+			if(U[0] > missing_msbs + 1 || U[1] > missing_msbs + 1)
+				return false;
+#pragma unroll
+			for(uint32_t q = 0; q < 2; ++q)
+			{
+				const uint32_t t = tw[q], rho = (t >> 4) & 15u;
+				if(!rho)
+					continue;
+#pragma unroll
+				for(uint32_t n = 0; n < 4; ++n)
+				{
+					if(!((rho >> n) & 1u))
+						continue;
+					const uint32_t ms = ms_peek(s);
+					const uint32_t m = U[q] - ((t >> (8 + n)) & 1u);
+					ms_skip(s, m);
+					uint32_t v = ms & ((1u << m) - 1);
+					v |= ((t >> (12 + n)) & 1u) << m;
+					v |= 1u;
+					const uint32_t col = x + 2 * q + (n >> 1), row = y + (n & 1);
+					if(col < w && row < h)
+						out[(size_t)row * ostride + col] = (ms << 31) | ((v + 2) << (p - 1));
+					if(n & 1)
+						cur[col + 1] = (uint8_t)(0x80u | (32 - __clz(v)));
+				}
+			}
+		}
+		uint8_t* tmp = north;
+		north = cur;
+		cur = tmp;
+	}
+	return true;
+}
+
+__global__ void __launch_bounds__(HT_THREADS)
+	t1_ht_decode_kernel(const T1Launch l, const HtTables* __restrict__ tab, uint32_t max_w)
+{
+	extern __shared__ __align__(16) uint8_t smem[];
+	uint16_t* dec = reinterpret_cast<uint16_t*>(smem);
+	for(uint32_t i = threadIdx.x; i < 2048; i += blockDim.x)
+		dec[i] = tab->dec[0][i];
+	__syncthreads();
+	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+	const uint32_t ncol = (max_w + 8 + 15) & ~15u;
+	uint8_t* north = smem + 4096 + (size_t)warp * 2 * ncol;
+	uint8_t* cur = north + ncol;
+	for(;;)
+	{
+		uint32_t item = 0;
+		if(lane == 0)
+			item = atomicAdd(l.counter, 1u);
+		item = __shfl_sync(0xffffffffu, item, 0);
+		if(item >= l.nblocks)
+			break;
+		const uint32_t bi = l.order ? l.order[item] : item;
+		const grkb_cblk cb = l.blocks[bi];
+		if(!(cb.cblk_sty & GRKB_CBLKSTY_HT))
+			continue;
+		const uint32_t w = cb.w, h = cb.h;
+		uint32_t* blk = reinterpret_cast<uint32_t*>(l.planes[cb.comp]) + (size_t)cb.y * l.stride + cb.x;
+		for(uint32_t y = 0; y < h; ++y)
+			for(uint32_t x = lane; x < w; x += 32)
+				blk[(size_t)y * l.stride + x] = 0;
+		__syncwarp();
+		// T1HT::decompress (T1HT.cpp:134-187): a block with segments but no passes or no bytes,
+		// more than one pass (lengths2 is always 0 there), or k_msbs > 29 is an error
+		uint32_t ok = 1;
+		if(cb.numsegs != 0 && lane == 0)
+		{
+			uint32_t passes = 0, len = 0;
+			for(uint32_t sgi = 0; sgi < cb.numsegs; ++sgi)
+			{
+				passes += l.segs[cb.seg_first + sgi].numpasses;
+				len += l.segs[cb.seg_first + sgi].len;
+			}
+			uint32_t mm = cb.k_msbs;
+			if(passes != 1 || len < 2 || mm > 29)
+				ok = 0;
+			else
+				ok = ht_cleanup(l.bytes + cb.data_off, (int)len, mm, w, h, blk, l.stride, dec, north,
+								cur, ncol)
+						 ? 1
+						 : 0;
+			if(!ok)
+				atomicAdd(l.status, 1u);
+		}
+		ok = __shfl_sync(0xffffffffu, ok, 0);
+		__syncwarp();
+		// dequantise in place: ShiftHTFilter / ScaleHTFilter and their ROI forms
+		// (PostDecompressFilters.h:91-177; the ROI forms AND the shifted magnitude with the sign
+		// bit exactly as the reference does)
+		const uint32_t shift = 31u - (cb.k_msbs + 1u);
+		const uint32_t thresh = cb.roishift ? (1u << cb.roishift) : 0xFFFFFFFFu;
+		for(uint32_t y = 0; y < h; ++y)
+		{
+			uint32_t* dst = blk + (size_t)y * l.stride;
+			for(uint32_t x = lane; x < w; x += 32)
+			{
+				uint32_t v = ok ? dst[x] : 0u;
+				const uint32_t mag0 = v & 0x7FFFFFFFu;
+				if(cb.roishift && mag0 >= thresh)
+					v = (mag0 >> cb.roishift) & (v & 0x80000000u);
+				const uint32_t mag = v & 0x7FFFFFFFu;
+				if(l.reversible)
+				{
+					const int32_t sv = (int32_t)(mag >> shift);
+					dst[x] = (uint32_t)((v & 0x80000000u) ? -sv : sv);
+				}
+				else
+				{
+					const float f = __fmul_rn((float)(int32_t)mag, cb.scale);
+					dst[x] = __float_as_uint((v & 0x80000000u) ? -f : f);
+				}
+			}
+		}
+		__syncwarp();
+	}
+}
+} // namespace
 
 int grkb_launch_t1_ht_decode(const T1Launch& l, cudaStream_t s)
 {
-	(void)l;
-	(void)s;
-	grkb_set_error("HT block decoder not built yet");
-	return -1;
+	if(l.nblocks == 0)
+		return 0;
+	const HtTables* tab = ht_tables_device();
+	if(!tab)
+	{
+		grkb_set_error("t1-ht: cannot upload decode tables");
+		return -1;
+	}
+	const uint32_t max_w = l.max_ht_w ? l.max_ht_w : 64;
+	const uint32_t ncol = (max_w + 8 + 15) & ~15u;
+	const size_t smem = 4096 + (size_t)(HT_THREADS / 32) * 2 * ncol;
+	static thread_local size_t configured = 0;
+	if(smem > 48 * 1024 && smem > configured)
+	{
+		GRKB_CUDA_CHECK(cudaFuncSetAttribute(t1_ht_decode_kernel,
+											 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		configured = smem;
+	}
+	int dev = 0, sms = 148;
+	cudaGetDevice(&dev);
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+	uint32_t ctas = (uint32_t)sms * 4;
+	const uint32_t need = (l.nblocks + HT_THREADS / 32 - 1) / (HT_THREADS / 32);
+	if(ctas > need)
+		ctas = need;
+	GRKB_CUDA_CHECK(cudaMemsetAsync(l.counter, 0, sizeof(uint32_t), s));
+	t1_ht_decode_kernel<<<ctas, HT_THREADS, smem, s>>>(l, tab, max_w);
+	GRKB_CUDA_CHECK(cudaGetLastError());
+	return 0;
 }

@@ -38,7 +38,7 @@ struct grkb_decoder
 	uint32_t* h_status = nullptr; // pinned
 	// last tile
 	uint32_t nblocks = 0, nsegs = 0;
-	uint32_t max_area = 0, max_flag_words = 0;
+	uint32_t max_area = 0, max_flag_words = 0, max_ht_w = 0;
 	bool any_mq = false, any_ht = false;
 	cudaEvent_t ev[6] = {};
 };
@@ -95,6 +95,7 @@ int scan_blocks(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks, cons
 {
 	d->max_area = 1;
 	d->max_flag_words = 9;
+	d->max_ht_w = 4;
 	d->any_mq = d->any_ht = false;
 	constexpr uint32_t NB = 1024;
 	uint32_t hist[NB + 1];
@@ -125,7 +126,11 @@ int scan_blocks(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks, cons
 			return -1;
 		}
 		if(b.cblk_sty & GRKB_CBLKSTY_HT)
+		{
 			d->any_ht = true;
+			if(b.w > d->max_ht_w)
+				d->max_ht_w = b.w;
+		}
 		else
 		{
 			d->any_mq = true;
@@ -174,6 +179,7 @@ int run_device(grkb_decoder* d, void* const* coeff_planes, uint32_t stride, bool
 	l.status = d->d_counters + 2;
 	l.max_area = d->max_area;
 	l.max_flag_words = d->max_flag_words;
+	l.max_ht_w = d->max_ht_w;
 	if(ev)
 		cudaEventRecord(ev[0], d->stream);
 	if(d->any_mq)

@@ -254,3 +254,48 @@ def ref_codec_decode(cs, ncomp, w, h, threads=0, want_planes=True):
     if rc != 0:
         raise RuntimeError("reference decoder failed (%d)" % rc)
     return planes
+
+
+# ---------------------------------------------------------------- HTJ2K block coder
+
+def ht_samples(values, missing_msbs):
+    """int array -> sign | magnitude << (30 - missing_msbs), as T1HT::preCompress leaves them
+    (t1/t1_ht/T1HT.cpp:71-107, reversible branch)"""
+    v = np.asarray(values, dtype=np.int64)
+    mag = np.abs(v) << (30 - missing_msbs)
+    return (mag | np.where(v < 0, 0x80000000, 0)).astype(np.uint32)
+
+
+def ref_ht_encode(samples, missing_msbs):
+    s = np.ascontiguousarray(samples, dtype=np.uint32)
+    h, w = s.shape
+    out = np.zeros(16384 + 3072 + 64, dtype=np.uint8)
+    n = ref().ref_ht_encode(_p(s), C.c_uint32(missing_msbs), C.c_uint32(w), C.c_uint32(h), _p(out))
+    if n < 0:
+        raise RuntimeError("reference HT encoder failed")
+    return out[:n].tobytes()
+
+
+def _ht_decode(is_ref, data, missing_msbs, w, h, num_passes=1, lengths2=0):
+    raw = bytes(data)
+    l1 = len(raw) - lengths2
+    out = np.zeros((h, w), dtype=np.uint32)
+    if is_ref:
+        buf = np.frombuffer(raw + b"\0" * 8, dtype=np.uint8).copy()
+        rc = ref().ref_ht_decode(_p(buf), C.c_uint32(missing_msbs), C.c_uint32(num_passes),
+                                 C.c_uint32(l1), C.c_uint32(lengths2), C.c_uint32(w), C.c_uint32(h),
+                                 _p(out))
+    else:
+        buf = np.frombuffer(b"\0" * 8 + raw + b"\0" * 8, dtype=np.uint8).copy()
+        rc = oracle().orc_ht_decode(C.c_void_p(buf.ctypes.data + 8), C.c_uint32(missing_msbs),
+                                    C.c_uint32(num_passes), C.c_uint32(l1), C.c_uint32(lengths2),
+                                    C.c_uint32(w), C.c_uint32(h), _p(out))
+    return rc, out
+
+
+def orc_ht_decode(data, missing_msbs, w, h, **kw):
+    return _ht_decode(False, data, missing_msbs, w, h, **kw)
+
+
+def ref_ht_decode(data, missing_msbs, w, h, **kw):
+    return _ht_decode(True, data, missing_msbs, w, h, **kw)

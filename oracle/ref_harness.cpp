@@ -350,8 +350,12 @@ int ref_ht_decode(const uint8_t* data, uint32_t missing_msbs, uint32_t num_passe
 		size_t total = (size_t)lengths1 + lengths2;
 		std::vector<uint8_t> buf(total + 16, 0);
 		memcpy(buf.data() + 8, data, total);
-		bool rc = ojph::local::ojph_decode_codeblock(buf.data() + 8, out, missing_msbs, num_passes,
-													 lengths1, lengths2, w, h, w);
+		/* the decoder also writes the phantom row / columns of a partial last quad row, as it does
+		 * into T1HT's nominal-size buffer (T1HT.cpp:38-45): give it room, then copy w x h out */
+		std::vector<uint32_t> scratch((size_t)w * (h + 2) + 16, 0);
+		bool rc = ojph::local::ojph_decode_codeblock(buf.data() + 8, scratch.data(), missing_msbs,
+													 num_passes, lengths1, lengths2, w, h, w);
+		memcpy(out, scratch.data(), sizeof(uint32_t) * (size_t)w * h);
 		return rc ? 0 : -1;
 	}
 	catch(...)

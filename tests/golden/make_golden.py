@@ -97,3 +97,25 @@ for k, (w, h, prec, irr, nr) in enumerate(e2e_cases):
     e["decoded_%d" % k] = np.stack(O.ref_codec_decode(cs, 3, w, h)).astype(np.int32)
 np.savez_compressed(os.path.join(HERE, "e2e.npz"), **e)
 print("e2e fixture written")
+
+# ---- HTJ2K block coder: reference encoder output and reference decoder output ---------------
+hh = {}
+ht_cases = []
+k = 0
+for (w, h) in [(64, 64), (32, 32), (1, 1), (3, 5), (17, 4), (64, 3), (5, 64), (13, 13), (4, 1), (1, 9),
+               (2, 2), (7, 2), (128, 32), (6, 6)]:
+    for bits, dens in [(1, 0.05), (3, 0.5), (7, 0.3), (11, 0.9), (12, 0.02)]:
+        mm = int(rng.integers(bits + 1, 30 - bits + 1)) if 30 - bits > bits + 1 else bits + 1
+        vals = rng.integers(-(1 << bits) + 1, 1 << bits, size=(h, w))
+        vals = np.where(rng.random((h, w)) < dens, vals, 0)
+        enc = O.ref_ht_encode(O.ht_samples(vals, mm), mm)
+        rc, dec = O.ref_ht_decode(enc, mm - 1, w, h)
+        assert rc == 0
+        hh["vals_%d" % k] = vals.astype(np.int32)
+        hh["bytes_%d" % k] = np.frombuffer(enc, dtype=np.uint8)
+        hh["dec_%d" % k] = dec
+        ht_cases.append((w, h, mm))
+        k += 1
+hh["cases"] = np.array(ht_cases, dtype=np.int32)
+np.savez_compressed(os.path.join(HERE, "t1_ht.npz"), **hh)
+print("HT fixture written", k)

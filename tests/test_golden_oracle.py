@@ -46,3 +46,14 @@ def test_t1_mq_golden(orc):
         rc, dec = O.orc_t1_decode(e["data"], segs, int(numbps), int(w), int(h), orient=int(orient),
                                   cblksty=int(sty))
         assert rc == 0 and np.array_equal(dec, t["dec_%d" % k])
+
+
+def test_t1_ht_golden(orc):
+    t = np.load(os.path.join(G, "t1_ht.npz"))
+    for k, (w, h, mm) in enumerate(t["cases"]):
+        rc, dec = O.orc_ht_decode(t["bytes_%d" % k].tobytes(), int(mm) - 1, int(w), int(h))
+        assert rc == 0 and np.array_equal(dec, t["dec_%d" % k]), k
+        # lossless: magnitude and sign come back (decoder convention: missing_msbs - 1, T1HT.cpp:128)
+        mag = (dec & 0x7FFFFFFF) >> (31 - int(mm))
+        val = np.where(dec >> 31, -mag.astype(np.int64), mag.astype(np.int64))
+        assert np.array_equal(val, t["vals_%d" % k])

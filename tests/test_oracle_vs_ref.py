@@ -155,3 +155,28 @@ def test_tables_match_reference_sources(orc):
             assert int(r[0], 16) == qe and int(r[1]) == mps
             assert int(r[2]) == 2 * nmps + mps
             assert int(r[3]) == 2 * nlps + (mps ^ sw)
+
+
+def test_ht_decode_matches_reference(orc):
+    rng = np.random.default_rng(31)
+    n = 0
+    for (w, h) in [(64, 64), (32, 32), (1, 1), (3, 5), (17, 4), (64, 3), (5, 64), (13, 13), (4, 1), (1, 9),
+                   (2, 2), (7, 2), (128, 32), (6, 6), (1024, 4), (4, 1024)]:
+        for bits in (1, 2, 5, 9, 12):
+            for dens in (0.02, 0.3, 0.9):
+                for mm in (bits + 1, 14, 20):
+                    if 30 - mm < bits:
+                        continue
+                    vals = rng.integers(-(1 << bits) + 1, 1 << bits, size=(h, w))
+                    vals = np.where(rng.random((h, w)) < dens, vals, 0)
+                    enc = O.ref_ht_encode(O.ht_samples(vals, mm), mm)
+                    for mmd in (mm, mm - 1):
+                        rr, r = O.ref_ht_decode(enc, mmd, w, h)
+                        ro, o = O.orc_ht_decode(enc, mmd, w, h)
+                        assert rr == ro and (rr != 0 or np.array_equal(r, o)), (w, h, bits, dens, mm, mmd)
+                        n += 1
+                    # a too-large missing_msbs makes U_q exceed its bound: both reject
+                    rr, _ = O.ref_ht_decode(enc, 29, w, h)
+                    ro, _ = O.orc_ht_decode(enc, 29, w, h)
+                    assert rr == ro
+    assert n > 1000
