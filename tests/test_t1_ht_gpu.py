@@ -65,13 +65,13 @@ def test_ht_decode_golden(gpu, reversible):
 
 def test_ht_decode_rejects_like_reference(gpu):
     """T1HT::decompress / ojph_decode_codeblock reject: more than one pass (lengths2 is always 0
-    in Grok), a missing_msbs that makes U_q overflow, bad Scup, empty streams; uncoded blocks
+    in Grok), a missing_msbs too small for the coded U_q, bad Scup, empty streams; uncoded blocks
     decode to zeros without error"""
     t = np.load(os.path.join(G, "t1_ht.npz"))
     good = t["bytes_7"].tobytes()
     w, h, mm = [int(v) for v in t["cases"][7]]
     bad_scup = good[:-1] + b"\xff"
-    entries = [(good, mm - 1, w, h, 2), (good, 29, w, h, 1), (bad_scup, mm - 1, w, h, 1),
+    entries = [(good, mm - 1, w, h, 2), (good, 0, w, h, 1), (bad_scup, mm - 1, w, h, 1),
                (b"\x00", mm - 1, w, h, 1), (None, mm - 1, w, h, 0), (good, mm - 1, w, h, 1)]
     blocks, got, rej, base = _run(entries, 1)
     assert rej == 4
