@@ -276,6 +276,16 @@ def ref_ht_encode(samples, missing_msbs):
     return out[:n].tobytes()
 
 
+def orc_ht_encode(samples, missing_msbs):
+    s = np.ascontiguousarray(samples, dtype=np.uint32)
+    h, w = s.shape
+    out = np.zeros(16384 + 3072 + 64, dtype=np.uint8)
+    n = oracle().orc_ht_encode(_p(s), C.c_uint32(missing_msbs), C.c_uint32(w), C.c_uint32(h), _p(out))
+    if n < 0:
+        raise RuntimeError("oracle HT encoder failed")
+    return out[:n].tobytes()
+
+
 def _ht_decode(is_ref, data, missing_msbs, w, h, num_passes=1, lengths2=0):
     raw = bytes(data)
     l1 = len(raw) - lengths2

@@ -452,3 +452,365 @@ int orc_ht_decode(const uint8_t* data, uint32_t missing_msbs, uint32_t num_passe
 	free(sigN < sigC ? sigC : sigN);
 	return rc;
 }
+
+/* ---- cleanup pass encoder (ojph_block_encoder.cpp:470-945) ----------------------------------- */
+
+/* encode table: [row0 / other rows][c_q << 8 | rho << 4 | eps] -> packed table word (0: none),
+ * chosen as the reference does (:74-215): without an EMB pattern the first u_off = 0 entry;
+ * with one, among the u_off = 1 entries whose known bits agree ((eps & e_k) == e_1) the LAST one
+ * with the most known bits */
+static uint32_t g_enc[2][2048];
+static int g_enc_ready = 0;
+
+static int popcnt4(uint32_t v)
+{
+	return (int)((v & 1) + ((v >> 1) & 1) + ((v >> 2) & 1) + ((v >> 3) & 1));
+}
+
+static void build_enc_tables(void)
+{
+	if(g_enc_ready)
+		return;
+	for(int t = 0; t < 2; ++t)
+	{
+		const unsigned int* src = t ? HT_CXTVLC_ROWN : HT_CXTVLC_ROW0;
+		const size_t n = t ? sizeof(HT_CXTVLC_ROWN) / 4 : sizeof(HT_CXTVLC_ROW0) / 4;
+		for(uint32_t i = 0; i < 2048; ++i)
+		{
+			const uint32_t cq = i >> 8, rho = (i >> 4) & 15, eps = i & 15;
+			g_enc[t][i] = 0;
+			if((eps & rho) != eps || (rho == 0 && cq == 0))
+				continue;
+			int best = -1;
+			for(size_t j = 0; j < n; ++j)
+			{
+				const uint32_t w = src[j];
+				if(TW_CQ(w) != cq || TW_RHO(w) != rho)
+					continue;
+				if(eps == 0)
+				{
+					if(TW_UOFF(w) == 0)
+					{
+						g_enc[t][i] = w | 0x80000000u;
+						break;
+					}
+				}
+				else if(TW_UOFF(w) == 1 && (eps & TW_EK(w)) == TW_E1(w) && popcnt4(TW_EK(w)) >= best)
+				{
+					best = popcnt4(TW_EK(w));
+					g_enc[t][i] = w | 0x80000000u;
+				}
+			}
+		}
+	}
+	g_enc_ready = 1;
+}
+
+typedef struct
+{
+	uint8_t ms[16384 + 64];
+	uint32_t ms_pos, ms_tmp;
+	int ms_used, ms_max;
+	uint8_t mel[192];
+	uint32_t mel_pos, mel_tmp;
+	int mel_rem, mel_run, mel_k;
+	uint8_t vlc[3072]; /* filled from the end */
+	uint32_t vlc_pos, vlc_tmp; /* vlc_pos bytes written, the first being vlc[sizeof-1] */
+	int vlc_used, vlc_gt8f;
+	int overflow;
+} ht_enc;
+
+/* ms_encode, :397-425: LSB first, a byte after 0xFF holds 7 bits */
+static void enc_ms(ht_enc* e, uint32_t cwd, int len)
+{
+	while(len > 0)
+	{
+		if(e->ms_pos >= 16384)
+		{
+			e->overflow = 1;
+			return;
+		}
+		int t = e->ms_max - e->ms_used;
+		if(t > len)
+			t = len;
+		e->ms_tmp |= (cwd & ((1u << t) - 1)) << e->ms_used;
+		e->ms_used += t;
+		cwd >>= t;
+		len -= t;
+		if(e->ms_used >= e->ms_max)
+		{
+			e->ms[e->ms_pos++] = (uint8_t)e->ms_tmp;
+			e->ms_max = (e->ms_tmp == 0xFF) ? 7 : 8;
+			e->ms_tmp = 0;
+			e->ms_used = 0;
+		}
+	}
+}
+
+/* mel_emit_bit / mel_encode, :247-298 */
+static void enc_mel_bit(ht_enc* e, int v)
+{
+	e->mel_tmp = (e->mel_tmp << 1) + (uint32_t)v;
+	if(--e->mel_rem == 0)
+	{
+		if(e->mel_pos >= 128)
+		{
+			e->overflow = 1;
+			return;
+		}
+		e->mel[e->mel_pos++] = (uint8_t)e->mel_tmp;
+		e->mel_rem = (e->mel_tmp == 0xFF) ? 7 : 8;
+		e->mel_tmp = 0;
+	}
+}
+
+static void enc_mel(ht_enc* e, int bit)
+{
+	const int ex = MEL_EXP[e->mel_k];
+	if(!bit)
+	{
+		if(++e->mel_run >= (1 << ex))
+		{
+			enc_mel_bit(e, 1);
+			e->mel_run = 0;
+			e->mel_k = e->mel_k < 12 ? e->mel_k + 1 : 12;
+		}
+	}
+	else
+	{
+		enc_mel_bit(e, 0);
+		for(int t = ex; t > 0;)
+			enc_mel_bit(e, (e->mel_run >> --t) & 1);
+		e->mel_run = 0;
+		e->mel_k = e->mel_k > 0 ? e->mel_k - 1 : 0;
+	}
+}
+
+/* vlc_encode, :325-358: written backwards, LSB first; after a byte > 0x8F the next byte may
+ * use its 8th bit only if its low seven bits are not all ones */
+static void enc_vlc(ht_enc* e, uint32_t cwd, int len)
+{
+	while(len > 0)
+	{
+		if(e->vlc_pos >= 3072 - 128)
+		{
+			e->overflow = 1;
+			return;
+		}
+		int avail = 8 - e->vlc_gt8f - e->vlc_used;
+		int t = avail < len ? avail : len;
+		e->vlc_tmp |= (cwd & ((1u << t) - 1)) << e->vlc_used;
+		e->vlc_used += t;
+		avail -= t;
+		len -= t;
+		cwd >>= t;
+		if(avail == 0)
+		{
+			if(e->vlc_gt8f && e->vlc_tmp != 0x7F)
+			{
+				e->vlc_gt8f = 0;
+				continue;
+			}
+			e->vlc[sizeof(e->vlc) - 1 - e->vlc_pos] = (uint8_t)e->vlc_tmp;
+			e->vlc_pos++;
+			e->vlc_gt8f = e->vlc_tmp > 0x8F;
+			e->vlc_tmp = 0;
+			e->vlc_used = 0;
+		}
+	}
+}
+
+/* U-VLC codeword of u (uvlc_init_tables, :194-215): prefix value/length, suffix value/length */
+static void uvlc_code(int u, uint32_t* pre, int* pre_len, uint32_t* suf, int* suf_len)
+{
+	if(u <= 0)
+	{
+		*pre = 0, *pre_len = 0, *suf = 0, *suf_len = 0;
+	}
+	else if(u <= 2)
+	{
+		*pre = (uint32_t)u, *pre_len = u, *suf = 0, *suf_len = 0;
+	}
+	else if(u <= 4)
+	{
+		*pre = 4, *pre_len = 3, *suf = (uint32_t)(u - 3), *suf_len = 1;
+	}
+	else
+	{
+		*pre = 0, *pre_len = 3, *suf = (uint32_t)(u - 5), *suf_len = 5;
+	}
+}
+
+/* samples: w*h sign-magnitude words (sign bit 31, magnitude << (30 - missing_msbs)), row pitch w.
+ * out: >= 16384 + 3072 bytes.  Returns the coded length (MagSgn | MEL | VLC, Scup in the last
+ * twelve bits), or -1 if a stream buffer overflowed (the reference throws). */
+int orc_ht_encode(const uint32_t* samples, uint32_t missing_msbs, uint32_t w, uint32_t h,
+				  uint8_t* out)
+{
+	build_enc_tables();
+	if(missing_msbs > 30)
+		return -1;
+	const uint32_t p = 30 - missing_msbs;
+	ht_enc* e = (ht_enc*)calloc(1, sizeof(ht_enc));
+	if(!e)
+		return -1;
+	e->ms_max = 8;
+	e->mel_rem = 8;
+	/* vlc_init, :313-323: the last byte is a placeholder, its neighbour starts with four 1s */
+	e->vlc[sizeof(e->vlc) - 1] = 0xFF;
+	e->vlc_pos = 1;
+	e->vlc_used = 4;
+	e->vlc_tmp = 0xF;
+	e->vlc_gt8f = 1;
+
+	const uint32_t ncol = w + 8;
+	uint8_t* expN = (uint8_t*)calloc(4 * ncol, 1); /* exponent / significance, previous and current */
+	uint8_t *sigN = expN + ncol, *expC = sigN + ncol, *sigC = expC + ncol;
+	for(uint32_t y = 0; y < h; y += 2)
+	{
+		const int initial = (y == 0);
+		uint32_t carry = 0;
+		memset(expC, 0, ncol);
+		memset(sigC, 0, ncol);
+		for(uint32_t x = 0; x < w; x += 4)
+		{
+			int u[2] = {0, 0};
+			const uint32_t nq = (x + 2 < w) ? 2 : 1;
+			for(uint32_t q = 0; q < nq; ++q)
+			{
+				const uint32_t c0 = x + 2 * q;
+				uint32_t rho = 0, v[4] = {0, 0, 0, 0};
+				int eq[4] = {0, 0, 0, 0}, emax = 0;
+				for(uint32_t n = 0; n < 4; ++n)
+				{
+					const uint32_t col = c0 + (n >> 1), row = y + (n & 1);
+					if(col >= w || row >= h)
+						continue;
+					const uint32_t t = samples[(size_t)row * w + col];
+					uint32_t val = ((t + t) >> p) & ~1u; /* 2 * mu_p */
+					if(!val)
+						continue;
+					rho |= 1u << n;
+					eq[n] = (int)bitlen(val - 1); /* exponent of 2 mu_p - 1 */
+					if(eq[n] > emax)
+						emax = eq[n];
+					v[n] = (val - 2) + (t >> 31); /* 2 (mu_p - 1) + sign */
+					if(n & 1)
+					{
+						expC[col + 1] = (uint8_t)eq[n];
+						sigC[col + 1] = 1;
+					}
+				}
+				uint32_t cq = carry;
+				int kappa = 1;
+				if(!initial)
+				{
+					cq |= (uint32_t)(sigN[c0] | sigN[c0 + 1]);
+					cq |= (uint32_t)(sigN[c0 + 2] | sigN[c0 + 3]) << 2;
+					if(rho & (rho - 1))
+					{
+						int me = 0;
+						for(int i = 0; i < 4; ++i)
+							if(expN[c0 + i] > me)
+								me = expN[c0 + i];
+						kappa = me - 1 > 1 ? me - 1 : 1;
+					}
+				}
+				const int U = emax > kappa ? emax : kappa;
+				u[q] = U - kappa;
+				uint32_t eps = 0;
+				if(u[q] > 0)
+					for(uint32_t n = 0; n < 4; ++n)
+						eps |= (uint32_t)(eq[n] == emax) << n;
+				const uint32_t tw = g_enc[initial ? 0 : 1][(cq << 8) | (rho << 4) | eps];
+				enc_vlc(e, TW_CWD(tw), (int)TW_LEN(tw));
+				if(cq == 0)
+					enc_mel(e, rho != 0);
+				for(uint32_t n = 0; n < 4; ++n)
+				{
+					const int m = ((rho >> n) & 1) ? U - (int)((TW_EK(tw) >> n) & 1) : 0;
+					enc_ms(e, v[n] & ((1u << m) - 1), m);
+				}
+				carry = initial ? ((rho >> 1) | (rho & 1)) : ((((rho >> 2) | (rho >> 3)) & 1u) << 1);
+			}
+			/* U-VLC of the pair (:693-716 initial row, :926-929 others) */
+			uint32_t pre[2], suf[2];
+			int prel[2], sufl[2];
+			if(initial && u[0] > 0 && u[1] > 0)
+				enc_mel(e, (u[0] < u[1] ? u[0] : u[1]) > 2);
+			if(initial && u[0] > 2 && u[1] > 2)
+			{
+				uvlc_code(u[0] - 2, &pre[0], &prel[0], &suf[0], &sufl[0]);
+				uvlc_code(u[1] - 2, &pre[1], &prel[1], &suf[1], &sufl[1]);
+			}
+			else if(initial && u[0] > 2 && u[1] > 0)
+			{
+				uvlc_code(u[0], &pre[0], &prel[0], &suf[0], &sufl[0]);
+				pre[1] = (uint32_t)(u[1] - 1);
+				prel[1] = 1;
+				suf[1] = 0;
+				sufl[1] = 0;
+			}
+			else
+			{
+				uvlc_code(u[0], &pre[0], &prel[0], &suf[0], &sufl[0]);
+				uvlc_code(u[1], &pre[1], &prel[1], &suf[1], &sufl[1]);
+			}
+			enc_vlc(e, pre[0], prel[0]);
+			enc_vlc(e, pre[1], prel[1]);
+			enc_vlc(e, suf[0], sufl[0]);
+			enc_vlc(e, suf[1], sufl[1]);
+		}
+		uint8_t* t1 = expN;
+		expN = expC;
+		expC = t1;
+		t1 = sigN;
+		sigN = sigC;
+		sigC = t1;
+	}
+	/* terminate_mel_vlc, :363-392 */
+	if(e->mel_run > 0)
+		enc_mel_bit(e, 1);
+	{
+		e->mel_tmp <<= e->mel_rem;
+		const uint32_t mel_mask = (0xFFu << e->mel_rem) & 0xFF;
+		const uint32_t vlc_mask = 0xFFu >> (8 - e->vlc_used);
+		if((mel_mask | vlc_mask) != 0)
+		{
+			const uint32_t fuse = e->mel_tmp | e->vlc_tmp;
+			if((((fuse ^ e->mel_tmp) & mel_mask) | ((fuse ^ e->vlc_tmp) & vlc_mask)) == 0 &&
+			   fuse != 0xFF && e->vlc_pos > 1)
+				e->mel[e->mel_pos++] = (uint8_t)fuse;
+			else
+			{
+				e->mel[e->mel_pos++] = (uint8_t)e->mel_tmp;
+				e->vlc[sizeof(e->vlc) - 1 - e->vlc_pos] = (uint8_t)e->vlc_tmp;
+				e->vlc_pos++;
+			}
+		}
+	}
+	/* ms_terminate, :427-461 */
+	if(e->ms_used)
+	{
+		const int t = e->ms_max - e->ms_used;
+		e->ms_tmp |= (0xFFu & ((1u << t) - 1)) << e->ms_used;
+		if(e->ms_tmp != 0xFF)
+			e->ms[e->ms_pos++] = (uint8_t)e->ms_tmp;
+	}
+	else if(e->ms_max == 7)
+		e->ms_pos--;
+	int total = -1;
+	if(!e->overflow)
+	{
+		total = (int)(e->ms_pos + e->mel_pos + e->vlc_pos);
+		memcpy(out, e->ms, e->ms_pos);
+		memcpy(out + e->ms_pos, e->mel, e->mel_pos);
+		memcpy(out + e->ms_pos + e->mel_pos, e->vlc + sizeof(e->vlc) - e->vlc_pos, e->vlc_pos);
+		const uint32_t nb = e->mel_pos + e->vlc_pos;
+		out[total - 1] = (uint8_t)(nb >> 4);
+		out[total - 2] = (uint8_t)((out[total - 2] & 0xF0) | (nb & 0xF));
+	}
+	free(expN < expC ? expN : expC);
+	free(e);
+	return total;
+}

@@ -57,3 +57,5 @@ def test_t1_ht_golden(orc):
         mag = (dec & 0x7FFFFFFF) >> (31 - int(mm))
         val = np.where(dec >> 31, -mag.astype(np.int64), mag.astype(np.int64))
         assert np.array_equal(val, t["vals_%d" % k])
+        # and the encoder reproduces the reference's bytes
+        assert O.orc_ht_encode(O.ht_samples(t["vals_%d" % k], int(mm)), int(mm)) == t["bytes_%d" % k].tobytes()

@@ -180,3 +180,21 @@ def test_ht_decode_matches_reference(orc):
                     ro, _ = O.orc_ht_decode(enc, 29, w, h)
                     assert rr == ro
     assert n > 1000
+
+
+def test_ht_encode_matches_reference(orc):
+    rng = np.random.default_rng(32)
+    n = 0
+    for (w, h) in [(64, 64), (32, 32), (1, 1), (3, 5), (17, 4), (64, 3), (5, 64), (13, 13), (4, 1), (1, 9),
+                   (2, 2), (7, 2), (128, 32), (6, 6), (1024, 4), (4, 1024), (2, 1), (1, 2)]:
+        for bits in (1, 2, 5, 9, 12):
+            for dens in (0.0, 0.02, 0.3, 0.9, 1.0):
+                for mm in (bits + 1, 14, 20):
+                    if 30 - mm < bits:
+                        continue
+                    vals = rng.integers(-(1 << bits) + 1, 1 << bits, size=(h, w))
+                    vals = np.where(rng.random((h, w)) < dens, vals, 0)
+                    smp = O.ht_samples(vals, mm)
+                    assert O.ref_ht_encode(smp, mm) == O.orc_ht_encode(smp, mm), (w, h, bits, dens, mm)
+                    n += 1
+    assert n > 1000
