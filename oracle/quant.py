@@ -49,3 +49,38 @@ def band_params(qcd, resno, bandindex, orient, prec, reversible, compress, numgb
     stepsize = np.float32((1.0 + mant / 2048.0) * math.pow(2.0, numbps - expn))
     band_numbps = roishift + max(0, expn + numgbits - 1)
     return stepsize, band_numbps
+
+
+# BIBO gains of the 5/3 analysis filter bank per decomposition depth (OpenJPH tables used by the
+# reference's HT QCD generator, codestream/HTParams.cpp:134-146), first entries
+BIBO_53_L = [1.0000, 1.5000, 1.6250, 1.6875, 1.6963, 1.7067, 1.7116, 1.7129, 1.7141, 1.7145, 1.7151]
+BIBO_53_H = [2.0000, 2.5000, 2.7500, 2.8047, 2.8198, 2.8410, 2.8558, 2.8601, 2.8628, 2.8656, 2.8662]
+
+
+def qcd_ht_rev(numres, prec):
+    """param_qcd::set_rev_quant (HTParams.cpp:253-272); the colour-transform bit is never added
+    because tcp->mct is still 0 when the reference calls it (CodeStreamCompress.cpp:382-396)"""
+    import numpy as np
+    nd = numres - 1
+    f32 = np.float32
+
+    def X(a, b):
+        return int(math.ceil(math.log(float(f32(a) * f32(b) * f32(1.1))) / math.log(2.0)))
+    out = [(prec + X(BIBO_53_L[nd], BIBO_53_L[nd]), 0)]
+    for d in range(nd - 1, -1, -1):
+        lo, hi = BIBO_53_L[d + 1], BIBO_53_H[d]
+        out += [(prec + X(hi, lo), 0)] * 2 + [(prec + X(hi, hi), 0)]
+    return out
+
+
+def parse_qcd(cs):
+    """(Sqcd, [SPqcd words]) from the first QCD marker segment of a codestream (bytes-like)"""
+    b = bytes(cs)
+    i = b.find(b"\xff\x5c")
+    ln = (b[i + 2] << 8) | b[i + 3]
+    sq = b[i + 4]
+    body = b[i + 5:i + 2 + ln]
+    if (sq & 0x1F) == 0:
+        return sq, [(v >> 3, 0) for v in body]
+    return sq, [(((body[k] << 8) | body[k + 1]) >> 11, ((body[k] << 8) | body[k + 1]) & 0x7FF)
+                for k in range(0, len(body), 2)]

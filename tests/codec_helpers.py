@@ -51,10 +51,12 @@ def quantise_block(coef, reversible, stepsize):
 
 
 def encode_tile(coefs, prec, reversible, numres, cblk_exp=(6, 6), cblksty=0, use_ref=False,
-                x0=0, y0=0, threads=None, keep_passes=None):
+                x0=0, y0=0, threads=None, keep_passes=None, ht=False):
     """coefs: list of coefficient planes (Mallat).  Returns dict(blocks, segs, data, geom, qcd)."""
     h, w = coefs[0].shape
     geom = T.layout(x0, y0, x0 + w, y0 + h, numres, cblk_exp[0], cblk_exp[1])
+    if ht:
+        return _encode_tile_ht(coefs, prec, numres, geom, use_ref, threads)
     qcd = Q.qcd_part1(numres, reversible, prec)
     enc = O.ref_t1_encode if use_ref else O.orc_t1_encode
     jobs = []
@@ -103,6 +105,42 @@ def encode_tile(coefs, prec, reversible, numres, cblk_exp=(6, 6), cblksty=0, use
     return dict(blocks=blocks, segs=segarr, data=data, geom=geom, qcd=qcd, shape=(h, w))
 
 
+def _encode_tile_ht(coefs, prec, numres, geom, use_ref, threads):
+    """HT lossless: T1HT::preCompress + ojph_encode_codeblock per block (t1/t1_ht/T1HT.cpp:56-131);
+    the block reports numbps = 1, so the decoder sees k_msbs = band numbps - 1"""
+    h, w = coefs[0].shape
+    qcd = Q.qcd_ht_rev(numres, prec)
+    enc = O.ref_ht_encode if use_ref else O.orc_ht_encode
+    jobs = [(c, g) for c in range(len(coefs)) for g in geom if g["w"] and g["h"]]
+
+    def run(job):
+        c, g = job
+        expn = qcd[(0 if g["res"] == 0 else 3 * int(g["res"]) - 2) + int(g["band"])][0]
+        band_numbps = expn  # expn + numgbits - 1 with numgbits = 1 (grk_compress.cpp:1123-1124)
+        blk = coefs[c][g["y"]:g["y"] + g["h"], g["x"]:g["x"] + g["w"]]
+        return enc(O.ht_samples(blk, band_numbps), band_numbps), band_numbps
+
+    threads = threads or min(32, os.cpu_count() or 1)
+    with cf.ThreadPoolExecutor(threads) as ex:
+        results = list(ex.map(run, jobs, chunksize=16))
+    blocks = np.zeros(len(jobs), dtype=T.CBLK_DTYPE)
+    segs, chunks, off = [], [], 0
+    for i, ((c, g), (data, band_numbps)) in enumerate(zip(jobs, results)):
+        b = blocks[i]
+        b["x"], b["y"], b["w"], b["h"] = g["x"], g["y"], g["w"], g["h"]
+        b["comp"], b["orient"], b["numbps"], b["cblk_sty"] = c, g["orient"], 1, T.CBLKSTY_HT
+        b["numsegs"], b["seg_first"] = 1, len(segs)
+        b["data_off"], b["data_len"] = off, len(data)
+        b["k_msbs"] = band_numbps - 1
+        b["scale"] = 1.0
+        segs.append((len(data), 1))
+        chunks.append(data)
+        off += len(data)
+    data = np.frombuffer(b"".join(chunks) + b"\0" * 16, dtype=np.uint8).copy()
+    return dict(blocks=blocks, segs=np.array(segs, dtype=T.SEG_DTYPE), data=data, geom=geom, qcd=qcd,
+                shape=(h, w))
+
+
 def decode_blocks_oracle(tile, ncomp, reversible, use_ref=False, threads=None):
     """oracle T1 decode + dequantisation of every block -> coefficient planes (int32 / float32)"""
     h, w = tile["shape"]
@@ -116,6 +154,13 @@ def decode_blocks_oracle(tile, ncomp, reversible, use_ref=False, threads=None):
         sg = [(int(s["len"]), int(s["numpasses"])) for s in
               tile["segs"][b["seg_first"]:b["seg_first"] + b["numsegs"]]]
         raw = data[b["data_off"]:b["data_off"] + b["data_len"]].tobytes()
+        if b["cblk_sty"] & T.CBLKSTY_HT:
+            rc, v = (O.ref_ht_decode if use_ref else O.orc_ht_decode)(raw, int(b["k_msbs"]), int(b["w"]),
+                                                                        int(b["h"]))
+            assert rc == 0
+            # ShiftHTFilter (PostDecompressFilters.h:113-129)
+            mag = ((v & 0x7FFFFFFF) >> (31 - (int(b["k_msbs"]) + 1))).astype(np.int64)
+            return ("ht", np.where(v >> 31, -mag, mag).astype(np.int32))
         rc, v = dec(raw, sg, int(b["numbps"]), int(b["w"]), int(b["h"]), orient=int(b["orient"]),
                     cblksty=int(b["cblk_sty"]))
         assert rc == 0
@@ -128,7 +173,9 @@ def decode_blocks_oracle(tile, ncomp, reversible, use_ref=False, threads=None):
         if v is None:
             continue
         dst = planes[b["comp"]][b["y"]:b["y"] + b["h"], b["x"]:b["x"] + b["w"]]
-        if reversible:
+        if isinstance(v, tuple):
+            dst[...] = v[1]
+        elif reversible:
             # ShiftFilter: C division by 2, truncation toward zero (PostDecompressFilters.h:42)
             dst[...] = (np.abs(v) >> 1) * np.sign(v)
         else:

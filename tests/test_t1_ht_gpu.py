@@ -80,3 +80,23 @@ def test_ht_decode_rejects_like_reference(gpu):
         assert not got[b["y"]:b["y"] + b["h"], b["x"]:b["x"] + b["w"]].any()
     b = blocks[5]
     assert np.array_equal(got[b["y"]:b["y"] + b["h"], b["x"]:b["x"] + b["w"]], t["vals_7"])
+
+
+@pytest.mark.parametrize("w,h,ncomp,prec,nr,mct", [(200, 150, 3, 12, 4, 1), (130, 67, 1, 8, 6, 0),
+                                                    (64, 64, 3, 16, 1, 1), (257, 129, 4, 10, 3, 1)])
+def test_ht_tile_decode_lossless(gpu, orc, w, h, ncomp, prec, nr, mct):
+    """whole HT lossless tiles (HT cleanup decode -> /shift -> inverse 5/3 -> inverse RCT + DC shift)
+    on the GPU reproduce the image and equal the oracle chain"""
+    import codec_helpers as H
+    img = H.synth_image(w, h, ncomp, prec, seed=w)
+    coefs = H.forward_oracle(img[:3] if mct else img, prec, True, nr, mct)
+    if mct and ncomp > 3:
+        coefs += H.forward_oracle(img[3:], prec, True, nr, 0)
+    tile = H.encode_tile(coefs, prec, True, nr, ht=True)
+    want, _ = H.decode_tile_oracle(tile, ncomp, prec, True, nr, mct)
+    dec = T.TileDecoder(T.tile_params(0, 0, w, h, ncomp, nr, 1, mct, prec))
+    got = dec.decode(tile["blocks"], tile["segs"], tile["data"])
+    assert dec.rejected == 0
+    dec.close()
+    for c in range(ncomp):
+        assert np.array_equal(got[c], want[c]) and np.array_equal(got[c], img[c])
