@@ -40,7 +40,8 @@
 static uint32_t g_dec[2][1024];
 static int g_dec_ready = 0;
 
-static void build_dec_tables(void)
+/* built once when the library is loaded (tests decode blocks from many threads) */
+__attribute__((constructor)) static void build_dec_tables(void)
 {
 	if(g_dec_ready)
 		return;
@@ -467,7 +468,7 @@ static int popcnt4(uint32_t v)
 	return (int)((v & 1) + ((v >> 1) & 1) + ((v >> 2) & 1) + ((v >> 3) & 1));
 }
 
-static void build_enc_tables(void)
+__attribute__((constructor)) static void build_enc_tables(void)
 {
 	if(g_enc_ready)
 		return;

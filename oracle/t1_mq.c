@@ -742,7 +742,7 @@ int orc_t1_decode(const uint8_t* data, const uint32_t* seg_len, const uint32_t* 
 static int16_t g_nmsedec[4][128];
 static int g_nmsedec_ready = 0;
 
-static void nmsedec_init(void)
+__attribute__((constructor)) static void nmsedec_init(void)
 {
 	if(g_nmsedec_ready)
 		return;
