@@ -33,6 +33,14 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 W, H, NCOMP, PREC, NUMRES, CBLK = 4096, 2160, 3, 16, 6, 6
 WORKLOAD = "j2k_decode_4096x2160_rgb16_97_ict_5lvl_cblk64_1tile"
 SEED = 4096
+HT = False  # --workload ht: BASELINE configs[2], 12-bit HTJ2K lossless (5/3 + RCT) decode
+
+
+def select_workload(name):
+    global PREC, WORKLOAD, HT
+    if name == "ht":
+        PREC, HT = 12, True
+        WORKLOAD = "htj2k_decode_4096x2160_rgb12_53_rct_lossless_5lvl_cblk64_1tile"
 
 
 def log(*a):
@@ -47,7 +55,7 @@ def peaks():
 
 
 def cache_path(tag):
-    key = hashlib.sha1(("%s-%d-%d-%d-%d-%d-v3" % (tag, W, H, PREC, NUMRES, SEED)).encode()).hexdigest()[:12]
+    key = hashlib.sha1(("%s-%d-%d-%d-%d-%d-%d-v4" % (tag, W, H, PREC, NUMRES, SEED, HT)).encode()).hexdigest()[:12]
     d = os.environ.get("GRKB_BENCH_CACHE", "/tmp")
     return os.path.join(d, "grkb_bench_%s_%s.npz" % (tag, key))
 
@@ -77,9 +85,9 @@ def coded_tile(img):
         z = np.load(p)
         return dict(blocks=z["blocks"], segs=z["segs"], data=z["data"])
     t = time.time()
-    coefs = grok_b200.stages.mct_fdwt(img, 0, 0, NUMRES, 0, 1, [1 << (PREC - 1)] * 3)
-    tile = Hh.encode_tile(coefs, PREC, False, NUMRES, (CBLK, CBLK), use_ref=O.have_ref(),
-                          threads=os.cpu_count())
+    coefs = grok_b200.stages.mct_fdwt(img, 0, 0, NUMRES, 1 if HT else 0, 1, [1 << (PREC - 1)] * 3)
+    tile = Hh.encode_tile(coefs, PREC, HT, NUMRES, (CBLK, CBLK), use_ref=O.have_ref(),
+                          threads=os.cpu_count(), ht=HT)
     np.savez(p + ".tmp.npz", blocks=tile["blocks"], segs=tile["segs"], data=tile["data"])
     os.replace(p + ".tmp.npz", p)
     log("[bench] frame coded on the host in %.1f s: %d blocks, %.1f MB" %
@@ -93,8 +101,8 @@ def codestream(img):
     if os.path.exists(p):
         return np.load(p)["cs"]
     t = time.time()
-    cs = O.ref_codec_encode(img, PREC, 1, numres=NUMRES, cblk=(1 << CBLK, 1 << CBLK),
-                            threads=os.cpu_count())
+    cs = O.ref_codec_encode(img, PREC, 0 if HT else 1, ht=HT, numres=NUMRES,
+                            cblk=(1 << CBLK, 1 << CBLK), threads=os.cpu_count())
     np.savez(p + ".tmp.npz", cs=cs)
     os.replace(p + ".tmp.npz", p)
     log("[bench] reference codestream written in %.1f s: %.1f MB" % (time.time() - t, cs.size / 1e6))
@@ -188,11 +196,12 @@ def run_reference(args):
     threads = os.cpu_count() or 1
     base = {"impl": "reference", "metric": "decode_mpixels_per_s", "unit": "Mpixel/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "i32" if HT else "f32",
             "data": "synthetic", "gpu_launches": 0,
             "config": {"workload": WORKLOAD, "width": W, "height": H, "components": NCOMP,
-                       "precision": PREC, "wavelet": "9/7", "mct": "ICT", "levels": NUMRES - 1,
-                       "cblk": "64x64", "frames_per_step": 1}}
+                       "precision": PREC, "wavelet": "5/3" if HT else "9/7",
+                       "mct": "RCT" if HT else "ICT", "levels": NUMRES - 1,
+                       "block_coder": "HT" if HT else "MQ", "cblk": "64x64", "frames_per_step": 1}}
     img = synth_frame()
     if O.have_ref():
         cs = codestream(img)
@@ -243,7 +252,7 @@ def run_ours(args):
         img = synth_frame()
         tile = coded_tile(img)
     blocks, segs, data = tile["blocks"], tile["segs"], tile["data"]
-    params = T.tile_params(0, 0, W, H, NCOMP, NUMRES, 0, 1, PREC)
+    params = T.tile_params(0, 0, W, H, NCOMP, NUMRES, 1 if HT else 0, 1, PREC)
     dec = T.TileDecoder(params, len(blocks), data.size)
     pin_data = T.PinnedArray((data.size,), np.uint8)
     pin_data.array[:] = data
@@ -308,25 +317,27 @@ def run_ours(args):
     line = {
         "metric": "decode_mpixels_per_s", "value": world * mp / (ms * 1e-3), "unit": "Mpixel/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "i32" if HT else "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "width": W, "height": H, "components": NCOMP,
-                   "precision": PREC, "wavelet": "9/7", "mct": "ICT", "levels": NUMRES - 1,
-                   "cblk": "64x64", "code_blocks": int(len(blocks)), "coded_bytes": int(data.size),
+                   "precision": PREC, "wavelet": "5/3" if HT else "9/7",
+                   "mct": "RCT" if HT else "ICT", "levels": NUMRES - 1,
+                   "block_coder": "HT" if HT else "MQ", "cblk": "64x64", "code_blocks": int(len(blocks)), "coded_bytes": int(data.size),
                    "frames_per_step": world, "sharding": "one frame per GPU per step, no collective",
                    "l2": "working set per step (coded bytes + 2 x %d MB planes) exceeds the 126 MB L2"
                          % (NCOMP * W * H * 4 // 1000000)},
         "e2e": {"value": world * mp / (e2e_ms * 1e-3), "unit": "Mpixel/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
         "gpu_launches": int(tm["launches"]) * args.steps,
-        "roofline": {"bound": "hbm", "kernel": "idwt_level_kernel<K97,3 comps,fused ICT> (last level)",
+        "roofline": {"bound": "hbm", "kernel": "idwt_level_kernel<%s,3 comps,fused %s> (last level)"
+                                                % (("K53", "RCT") if HT else ("K97", "ICT")),
                      "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic,
                      "algorithmic_bytes_per_launch": alg_last, "ms_per_launch": tm["dwt_last_ms"]},
-        "stages_ms": {"t1_mq_decode": tm["t1_ms"], "idwt_all_levels_plus_mct": tm["dwt_ms"],
+        "stages_ms": {"t1_ht_decode" if HT else "t1_mq_decode": tm["t1_ms"], "idwt_all_levels_plus_mct": tm["dwt_ms"],
                       "idwt_last_level": tm["dwt_last_ms"]},
         "t1": {"code_blocks_per_s": len(blocks) / (tm["t1_ms"] * 1e-3) if tm["t1_ms"] > 0 else None,
-               "bound": "serial MQ decision rate per warp (not HBM)"},
+               "bound": "serial %s rate per warp (not HBM)" % ("VLC/MEL/MagSgn" if HT else "MQ decision")},
         "clocks": clocks,
     }
     if cpu:
@@ -344,7 +355,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="j2k97", choices=["j2k97", "ht"])
     args = ap.parse_args()
+    select_workload(args.workload)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         return run_reference(args)
