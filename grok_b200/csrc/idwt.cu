@@ -390,8 +390,14 @@ static int launch_idwt(const DwtLevelArgs& a, bool aligned, cudaStream_t stream)
 
 // Host-side dispatch.  fin: 0 raw, 1 dc-shift per component, 2 MCT over 3 components.
 // ncomp planes of a.pl are processed (they must share geometry).
+int grkb_launch_idwt_strip(const DwtLevelArgs& a, int reversible, int ncomp, int fin,
+							cudaStream_t stream);
+
 int grkb_launch_idwt_level(DwtLevelArgs a, int reversible, int ncomp, int fin, cudaStream_t stream)
 {
+	const int fast = grkb_launch_idwt_strip(a, reversible, ncomp, fin, stream);
+	if(fast <= 0)
+		return fast;
 	const int V = (ncomp == 3) ? 4 : 8;
 	const uint32_t H = V / 2;
 	bool al = a.px == 0 && (a.sw % H) == 0;

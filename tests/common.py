@@ -7,6 +7,10 @@ GEOMS = [
     (100, 77, 13, 7, 6), (7, 13, 5, 9, 5), (256, 135, 0, 0, 6), (17, 1, 0, 1, 3), (1, 17, 1, 0, 2),
     (2, 2, 0, 0, 2), (4, 4, 1, 1, 3), (5, 5, 3, 3, 2), (250, 31, 0, 0, 3), (241, 40, 1, 0, 3),
     (481, 66, 2, 3, 4), (512, 270, 0, 0, 6), (37, 300, 0, 1, 5), (8, 8, 0, 0, 4), (9, 300, 1, 1, 6),
+    # widths that are multiples of 8 at even x0: the levels the strip kernel (idwt_strip.cu) takes,
+    # several strips wide, odd/even heights and origins, chunk boundaries inside the plane
+    (1024, 333, 0, 0, 5), (960, 270, 0, 1, 4), (2048, 67, 0, 0, 3), (128, 515, 0, 3, 2),
+    (1920, 130, 0, 0, 3), (64, 2, 0, 0, 2), (72, 1031, 0, 1, 2),
 ]
 # Degenerate geometries on which the REFERENCE itself misbehaves (documented in DESIGN.md):
 #  * inverse 5/3, a level of height exactly 2 at odd y0 writes dest[1] instead of dest[stride]
