@@ -22,6 +22,7 @@
 // HBM traffic per level: every coefficient read once, every sample written once (the
 // algorithmic bytes of SURVEY.md 8d); halo rows/columns are re-read from L2.
 #include "dwt.cuh"
+#include <stdlib.h>
 
 namespace
 {
@@ -318,6 +319,7 @@ __global__ void __launch_bounds__((CW + 1) * GRKB_WARP)
 
 	int s = 0;
 	uint32_t ph = 0;
+#pragma unroll 2
 	for(int m = m0; m <= m1; ++m)
 	{
 		const uint32_t full = smem_u32(bars + 2 * s), empty = smem_u32(bars + 2 * s + 1);
@@ -407,15 +409,32 @@ static int launch_strip(DwtLevelArgs a, int nplanes, cudaStream_t stream)
 	}
 	const uint32_t strip = 30 * V;
 	a.nstrips = (a.rw + strip - 1) / strip;
-	// chunk height: the tallest that still gives every SM ~8 consumer warps
+	// Chunk height: all CTAs are resident at once (<= 4 per SM), so the grid is sized to fill
+	// the 148 SMs evenly -- waves*148 CTAs or just under -- with chunks no shorter than
+	// min_rows (every chunk re-runs NS rows of vertical warm-up).
+	static int waves = 0, min_rows = 0;
+	if(waves == 0)
+	{
+		const char* e = getenv("GRKB_IDWT_WAVES"); // tuning knobs, see DESIGN.md section 4
+		waves = e ? atoi(e) : 2;
+		if(waves < 1 || waves > 4)
+			waves = 2;
+		e = getenv("GRKB_IDWT_MIN_ROWS");
+		min_rows = e ? atoi(e) : 4; // small levels are latency-bound: short chunks, many CTAs
+		if(min_rows < 4)
+			min_rows = 4;
+	}
 	const uint32_t total_rows = a.py + a.rh;
-	uint32_t ch = 128;
-	while(ch > 16 &&
-		  (uint64_t)a.nstrips * ((total_rows + ch - 1) / ch) * (uint32_t)nplanes < 148u * 8u)
-		ch >>= 1;
+	const uint32_t ngroups = (a.nstrips + CW - 1) / CW;
+	const uint32_t per_chunk = ngroups * ((NC == 1) ? (uint32_t)nplanes : 1u);
+	uint32_t nch = (148u * (uint32_t)waves) / per_chunk;
+	if(nch < 1)
+		nch = 1;
+	uint32_t ch = 2 * ((total_rows + 2 * nch - 1) / (2 * nch));
+	if(ch < (uint32_t)min_rows)
+		ch = (uint32_t)min_rows & ~1u;
 	a.chunk_rows = ch;
 	a.nchunks = (total_rows + ch - 1) / ch;
-	const uint32_t ngroups = (a.nstrips + CW - 1) / CW;
 	dim3 grid(ngroups * a.nchunks, (NC == 1) ? nplanes : 1, 1);
 	idwt_strip_kernel<K, V, NC, FIN><<<grid, (CW + 1) * GRKB_WARP, smem, stream>>>(a);
 	GRKB_CUDA_CHECK(cudaGetLastError());
