@@ -81,6 +81,8 @@ lib.grkb_decoder_destroy.argtypes = [_vp]
 lib.grkb_decoder_destroy.restype = None
 lib.grkb_decoder_decode.argtypes = [_vp, _vp, _u32, _vp, _u32, _vp, C.c_size_t, _vp, _u32,
                                     C.POINTER(_u32)]
+lib.grkb_decoder_submit.argtypes = [_vp, _vp, _u32, _vp, _u32, _vp, C.c_size_t, _vp, _u32]
+lib.grkb_decoder_wait.argtypes = [_vp, C.POINTER(_u32)]
 lib.grkb_decoder_time_device.argtypes = [_vp, _u32, _u32, C.POINTER(C.c_float), C.POINTER(_u32)]
 lib.grkb_decoder_download.argtypes = [_vp, _vp, _u32]
 lib.grkb_t1_decode_host.argtypes = [_vp, _u32, _vp, _u32, _vp, C.c_size_t, _vp, _u32, _u32, _u32,

@@ -331,13 +331,13 @@ void grkb_decoder_destroy(grkb_decoder* d)
 	delete d;
 }
 
-int grkb_decoder_decode(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
+int grkb_decoder_submit(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
 						const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
-						int32_t* const* planes, uint32_t stride, uint32_t* status_out)
+						int32_t* const* planes, uint32_t stride)
 {
 	if(!d || (nblocks && !blocks) || (nsegs && !segs) || (nbytes && !bytes))
 	{
-		grkb_set_error("grkb_decoder_decode: null argument");
+		grkb_set_error("grkb_decoder_submit: null argument");
 		return -1;
 	}
 	GRKB_CUDA_CHECK(cudaSetDevice(d->device));
@@ -369,7 +369,7 @@ int grkb_decoder_decode(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nbloc
 	{
 		if(stride < d->W)
 		{
-			grkb_set_error("grkb_decoder_decode: stride smaller than the tile width");
+			grkb_set_error("grkb_decoder_submit: stride smaller than the tile width");
 			return -1;
 		}
 		for(uint32_t c = 0; c < d->p.numcomps; ++c)
@@ -377,10 +377,30 @@ int grkb_decoder_decode(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nbloc
 											  (size_t)d->stride * 4, (size_t)d->W * 4, d->H,
 											  cudaMemcpyDeviceToHost, s));
 	}
-	GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
+	return 0;
+}
+
+int grkb_decoder_wait(grkb_decoder* d, uint32_t* status_out)
+{
+	if(!d)
+	{
+		grkb_set_error("grkb_decoder_wait: null decoder");
+		return -1;
+	}
+	GRKB_CUDA_CHECK(cudaSetDevice(d->device));
+	GRKB_CUDA_CHECK(cudaStreamSynchronize(d->stream));
 	if(status_out)
 		*status_out = *d->h_status;
 	return 0;
+}
+
+int grkb_decoder_decode(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
+						const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
+						int32_t* const* planes, uint32_t stride, uint32_t* status_out)
+{
+	if(grkb_decoder_submit(d, blocks, nblocks, segs, nsegs, bytes, nbytes, planes, stride))
+		return -1;
+	return grkb_decoder_wait(d, status_out);
 }
 
 int grkb_decoder_download(grkb_decoder* d, int32_t* const* planes, uint32_t stride)

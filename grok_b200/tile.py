@@ -113,6 +113,27 @@ class TileDecoder:
         self.rejected = st.value
         return out
 
+    def submit(self, blocks, segs, data, out):
+        """asynchronous half of decode(): enqueue and return; the arrays must stay alive and
+        untouched until wait().  One submit at a time per decoder."""
+        blocks = np.ascontiguousarray(blocks, dtype=CBLK_DTYPE)
+        segs = np.ascontiguousarray(segs, dtype=SEG_DTYPE)
+        nc = self.params.numcomps
+        stride = out[0].strides[0] // 4
+        ptrs = (C.c_void_p * nc)(*[o.ctypes.data for o in out])
+        self._inflight = (blocks, segs, data, out, ptrs)
+        check(lib.grkb_decoder_submit(self.h, blocks.ctypes.data, len(blocks), segs.ctypes.data,
+                                      len(segs), data.ctypes.data, data.size, ptrs, stride),
+              "grkb_decoder_submit")
+
+    def wait(self):
+        st = C.c_uint32()
+        check(lib.grkb_decoder_wait(self.h, C.byref(st)), "grkb_decoder_wait")
+        self.rejected = st.value
+        out = self._inflight[3] if getattr(self, "_inflight", None) else None
+        self._inflight = None
+        return out
+
     def time_device(self, iters, warmup):
         ms = (C.c_float * 4)()
         n = C.c_uint32()

@@ -194,6 +194,16 @@ int grkb_decoder_decode(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nbloc
 						const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
 						int32_t* const* planes, uint32_t stride, uint32_t* status_out);
 
+/* The same in two halves, for keeping several tiles/frames in flight (one decoder each):
+ * grkb_decoder_submit enqueues the copies and kernels on the decoder's stream and returns;
+ * grkb_decoder_wait blocks until they are done.  blocks/segs/bytes/planes must stay valid and
+ * untouched until the wait returns (pinned memory makes the copies truly asynchronous), and a
+ * decoder takes one submit at a time. */
+int grkb_decoder_submit(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
+						const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
+						int32_t* const* planes, uint32_t stride);
+int grkb_decoder_wait(grkb_decoder* d, uint32_t* status_out);
+
 /* Re-runs the device stages (T1, wavelet, MCT) of the last tile given to grkb_decoder_decode,
  * inputs already resident in HBM, no host copies: `iters` passes after `warmup`, timed with CUDA
  * events on the decoder's stream.  ms[0] = mean whole pass, ms[1] = mean T1 kernels,

@@ -100,3 +100,31 @@ def test_ht_tile_decode_lossless(gpu, orc, w, h, ncomp, prec, nr, mct):
     dec.close()
     for c in range(ncomp):
         assert np.array_equal(got[c], want[c]) and np.array_equal(got[c], img[c])
+
+
+def test_two_frames_in_flight(gpu, orc):
+    """grkb_decoder_submit / grkb_decoder_wait: two decoders with different frames in flight give
+    the same planes as the synchronous call"""
+    import codec_helpers as H
+    w, h, nr, prec = 320, 200, 4, 12
+    tiles, imgs = [], []
+    for seed in (1, 2):
+        img = H.synth_image(w, h, 3, prec, seed=seed)
+        tiles.append(H.encode_tile(H.forward_oracle(img, prec, True, nr, 1), prec, True, nr, ht=True))
+        imgs.append(img)
+    params = T.tile_params(0, 0, w, h, 3, nr, 1, 1, prec)
+    decs = [T.TileDecoder(params), T.TileDecoder(params)]
+    outs = [[T.PinnedArray((h, w), np.int32) for _ in range(3)] for _ in range(2)]
+    for rep in range(3):
+        for i in (0, 1):
+            for p in outs[i]:
+                p.array[:] = -1
+            decs[i].submit(tiles[i]["blocks"], tiles[i]["segs"], tiles[i]["data"],
+                           [p.array for p in outs[i]])
+        for i in (0, 1):
+            got = decs[i].wait()
+            assert decs[i].rejected == 0
+            for c in range(3):
+                assert np.array_equal(got[c], imgs[i][c])
+    for d in decs:
+        d.close()
