@@ -87,6 +87,8 @@ lib.grkb_decoder_time_device.argtypes = [_vp, _u32, _u32, C.POINTER(C.c_float), 
 lib.grkb_decoder_download.argtypes = [_vp, _vp, _u32]
 lib.grkb_t1_decode_host.argtypes = [_vp, _u32, _vp, _u32, _vp, C.c_size_t, _vp, _u32, _u32, _u32,
                                     _int, C.POINTER(_u32)]
+lib.grkb_t1_encode_host.argtypes = [_vp, _u32, _vp, _u32, _u32, _u32, _int, _vp, _u32, _int, _vp, _vp,
+                                    _vp, C.c_size_t, C.POINTER(C.c_size_t)]
 lib.grkb_host_alloc.argtypes = [C.c_size_t]
 lib.grkb_host_alloc.restype = _vp
 lib.grkb_host_free.argtypes = [_vp]

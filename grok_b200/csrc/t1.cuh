@@ -60,5 +60,33 @@ struct T1Launch
 	uint32_t max_flag_words; // max (w+2)*(ceil(h/4)+2) over MQ blocks
 	uint32_t max_ht_w; // max width over HT blocks
 };
+// encode side: every block codes into its own slot of `slots`; a second kernel packs the
+// streams back to back (block order) into `packed` and fills coded[].data_off
+struct T1EncLaunch
+{
+	const grkb_enc_cblk* blocks; // device
+	const uint32_t* order; // device: block indices, largest first (may be null)
+	uint32_t nblocks;
+	const void* planes[GRKB_MAX_COMPS]; // device coefficient planes
+	uint32_t stride;
+	int reversible;
+	double mct_norms[GRKB_MAX_COMPS];
+	uint32_t mct_numcomps;
+	int rate_control;
+	grkb_coded* coded; // device, nblocks
+	grkb_pass* passes; // device, nblocks * GRKB_ENC_MAX_PASSES
+	uint8_t* slots; // device, nblocks * slot_bytes (each slot starts with 16 zero bytes)
+	uint32_t slot_bytes;
+	uint8_t* packed; // device
+	uint64_t packed_cap;
+	uint64_t* packed_used; // device: total bytes, or ~0 if the pool was too small
+	uint32_t* counter; // device work counter (zeroed by the launcher)
+	uint32_t max_area; // max w*h over the blocks
+	uint32_t max_flag_words; // max (w+2)*(ceil(h/4)+2) over MQ blocks
+	uint32_t max_w; // widest block
+};
+int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s);
+int grkb_launch_t1_ht_encode(const T1EncLaunch& l, cudaStream_t s);
+int grkb_launch_t1_pack(const T1EncLaunch& l, cudaStream_t s);
 int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s);
 int grkb_launch_t1_ht_decode(const T1Launch& l, cudaStream_t s);

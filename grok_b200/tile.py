@@ -162,3 +162,45 @@ def t1_decode(blocks, segs, data, planes, reversible):
                                   data.ctypes.data, data.size, ptrs, len(a), w, h, int(reversible),
                                   C.byref(st)), "grkb_t1_decode_host")
     return a, st.value
+
+
+# ---------------------------------------------------------------------------------- encode side
+ENC_CBLK_DTYPE = np.dtype([("x", "<u4"), ("y", "<u4"), ("w", "<u2"), ("h", "<u2"), ("comp", "u1"),
+                           ("orient", "u1"), ("level", "u1"), ("cblk_sty", "u1"), ("k_msbs", "u1"),
+                           ("reserved", "u1", (3,)), ("stepsize", "<f4"),
+                           ("reserved2", "<u4", (2,))])
+assert ENC_CBLK_DTYPE.itemsize == 32
+PASS_DTYPE = np.dtype([("distortion", "<f8"), ("rate", "<u4"), ("len", "<u2"), ("term", "u1"),
+                       ("reserved", "u1")])
+assert PASS_DTYPE.itemsize == 16
+CODED_DTYPE = np.dtype([("data_off", "<u8"), ("data_len", "<u4"), ("numbps", "u1"),
+                        ("numpasses", "u1"), ("failed", "<u2"), ("distortion", "<f8")])
+assert CODED_DTYPE.itemsize == 24
+ENC_MAX_PASSES = 100
+
+
+def t1_encode(blocks, planes, reversible, mct_norms=None, rate_control=False, cap=None):
+    """block encoders alone (grkb_t1_encode_host): blocks is an ENC_CBLK_DTYPE array, planes a list
+    of 2-D int32 (reversible) / float32 coefficient arrays of identical shape.
+    Returns (coded CODED_DTYPE array, passes PASS_DTYPE array [nblocks, 100], bytes uint8 array)."""
+    blocks = np.ascontiguousarray(blocks, dtype=ENC_CBLK_DTYPE)
+    a = [np.ascontiguousarray(p) for p in planes]
+    h, stride = a[0].shape
+    for p in a:
+        if p.shape != (h, stride) or p.dtype.itemsize != 4:
+            raise ValueError("planes must be 32-bit and of identical shape")
+    n = len(blocks)
+    coded = np.zeros(n, dtype=CODED_DTYPE)
+    passes = np.zeros((n, ENC_MAX_PASSES), dtype=PASS_DTYPE)
+    if cap is None:
+        cap = int(sum(int(b["w"]) * int(b["h"]) for b in blocks)) * 4 + 20000 * max(n, 1)
+    out = np.zeros(max(cap, 1), dtype=np.uint8)
+    ptrs = (C.c_void_p * len(a))(*[p.ctypes.data for p in a])
+    norms = None if mct_norms is None else np.ascontiguousarray(mct_norms, dtype=np.float64)
+    used = C.c_size_t()
+    check(lib.grkb_t1_encode_host(blocks.ctypes.data, n, ptrs, len(a), stride, h, int(reversible),
+                                  None if norms is None else norms.ctypes.data,
+                                  0 if norms is None else len(norms), int(rate_control),
+                                  coded.ctypes.data, passes.ctypes.data, out.ctypes.data, cap,
+                                  C.byref(used)), "grkb_t1_encode_host")
+    return coded, passes, out[:used.value]

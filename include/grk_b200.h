@@ -225,6 +225,66 @@ int grkb_t1_decode_host(const grkb_cblk* blocks, uint32_t nblocks, const grkb_se
 						uint32_t numcomps, uint32_t stride, uint32_t plane_h, int reversible,
 						uint32_t* status_out);
 
+/* ---- encode side ---------------------------------------------------------------------------- */
+
+/* One code block to encode: what CompressBlockExec carries (src/lib/jp2/t1/BlockExec.h:54-84,
+ * filled by T1CompressScheduler::scheduleCompress, t1/T1CompressScheduler.cpp:31-154). */
+typedef struct grkb_enc_cblk
+{
+	uint32_t x, y; /* top-left sample in the component's coefficient plane (Mallat layout) */
+	uint16_t w, h;
+	uint8_t comp;
+	uint8_t orient; /* 0 LL, 1 HL, 2 LH, 3 HH */
+	uint8_t level; /* numresolutions - 1 - resno: index into the band norms (T1.cpp:264-277) */
+	uint8_t cblk_sty; /* GRKB_CBLKSTY_*; GRKB_CBLKSTY_HT selects the HT cleanup coder */
+	uint8_t k_msbs; /* HT: band numbps (T1CompressScheduler.cpp:84 with cblk->numbps == 0) */
+	uint8_t reserved[3];
+	float stepsize; /* band step size: 9/7 quantiser divisor and distortion weight */
+	uint32_t reserved2[2];
+} grkb_enc_cblk; /* 32 bytes */
+
+#define GRKB_ENC_MAX_PASSES 100 /* passes[] capacity of the reference (t1/Codeblock.h:144) */
+
+/* One coding pass of a coded block: the fields of grk::CodePass the host's rate control and T2
+ * read (rate = cumulative bytes, len = bytes of this pass, term = terminated,
+ * distortion = cumulative weighted MSE decrease; T1.cpp:781-932). */
+typedef struct grkb_pass
+{
+	double distortion;
+	uint32_t rate;
+	uint16_t len;
+	uint8_t term;
+	uint8_t reserved;
+} grkb_pass; /* 16 bytes */
+
+typedef struct grkb_coded
+{
+	uint64_t data_off; /* first byte of the block's stream in the output byte pool */
+	uint32_t data_len;
+	uint8_t numbps; /* MQ: floorlog2(max)+1-6; HT: 1 (T1HT.cpp:121-130) */
+	uint8_t numpasses;
+	uint16_t failed; /* 1: stream buffer overflow (the reference throws / asserts) */
+	double distortion; /* total of the block (CompressBlockExec::distortion) */
+} grkb_coded; /* 24 bytes */
+
+/* Stage-level door for the block encoders (parity tests, and the call a maintainer binds in
+ * place of T1CompressScheduler's worker loop): quantises (T1Part1::preCompress,
+ * t1/t1_part1/T1Part1.cpp:37-88; T1HT::preCompress, t1/t1_ht/T1HT.cpp:56-108) and encodes
+ * (T1::compress_cblk, t1/t1_part1/T1.cpp:781-932; ojph_encode_codeblock,
+ * t1/t1_ht/coding/ojph_block_encoder.cpp:470-945) `nblocks` blocks of host coefficient planes.
+ *   planes[c]     int32 (reversible) or float (irreversible) wavelet coefficients
+ *   mct_norms     per-component weights of the distortion estimate (NULL: 1.0), T1.cpp:418-436
+ *   rate_control  0: distortions are not computed (the reference skips them too)
+ *   coded[i]      result of block i; passes[i * GRKB_ENC_MAX_PASSES + p] its passes
+ *   bytes/cap     output byte pool (streams back to back in block order), *used = bytes written
+ * HT with irreversible data is refused: the reference's own quantiser for that combination
+ * reinterprets float bits as integers (T1HT.cpp:92-104). */
+int grkb_t1_encode_host(const grkb_enc_cblk* blocks, uint32_t nblocks, const void* const* planes,
+						uint32_t numcomps, uint32_t stride, uint32_t plane_h, int reversible,
+						const double* mct_norms, uint32_t mct_numcomps, int rate_control,
+						grkb_coded* coded, grkb_pass* passes, uint8_t* bytes, size_t cap,
+						size_t* used);
+
 /* Page-locked host memory for byte pools and output planes: copies to and from it are true
  * asynchronous DMA (the decoder accepts any host pointer, pageable ones are staged by the
  * driver). */
