@@ -224,4 +224,241 @@ int grkb_t1_encode_host(const grkb_enc_cblk* blocks, uint32_t nblocks, const voi
 	return 0;
 }
 
+// ---- whole-tile encoder ------------------------------------------------------------------------
+
+struct grkb_encoder
+{
+	grkb_tile_params p;
+	grkb_rect tc;
+	uint32_t W, H, stride, sstride;
+	EncState st;
+	void* coeff[GRKB_MAX_COMPS] = {};
+	void* image[GRKB_MAX_COMPS] = {};
+	void* scratch[GRKB_MAX_COMPS][2] = {};
+	cudaEvent_t ev[4] = {};
+	// last tile, for grkb_encoder_time_device
+	T1EncLaunch last{};
+	bool any_mq = false, any_ht = false, have_last = false;
+};
+
+static int encoder_front(grkb_encoder* e, cudaStream_t s)
+{
+	// DC shift + forward MCT + forward wavelet: components 0..2 as one group when the MCT couples
+	// them, every other component on its own (mirror of the decoder's back end)
+	const grkb_tile_params& p = e->p;
+	uint32_t c = 0;
+	while(c < p.numcomps)
+	{
+		DwtGroup g{};
+		const bool grp3 = (c == 0 && p.numcomps >= 3 && p.mct);
+		g.ncomp = grp3 ? 3 : 1;
+		g.coeff_stride = e->stride;
+		g.image_stride = e->stride;
+		g.scratch_stride = e->sstride;
+		int32_t sh[3];
+		for(int i = 0; i < g.ncomp; ++i)
+		{
+			g.coeff[i] = e->coeff[c + i];
+			g.image[i] = e->image[c + i];
+			g.scratch[i][0] = e->scratch[c + i][0];
+			g.scratch[i][1] = e->scratch[c + i][1];
+		}
+		for(int i = 0; i < 3; ++i)
+			sh[i] = p.shift[c + (i < g.ncomp ? i : 0)];
+		if(grkb_fdwt_device(g, e->tc, p.numres, p.reversible, grp3 ? 2 : 1, sh, s))
+			return -1;
+		c += g.ncomp;
+	}
+	return 0;
+}
+
+int grkb_encoder_create(const grkb_tile_params* p, grkb_encoder** out)
+{
+	if(!p || !out || p->numcomps == 0 || p->numcomps > GRKB_MAX_COMPS || p->x1 <= p->x0 ||
+	   p->y1 <= p->y0 || p->numres == 0 || p->numres > 33)
+	{
+		grkb_set_error("grkb_encoder_create: bad parameters");
+		return -1;
+	}
+	grkb_encoder* e = new(std::nothrow) grkb_encoder();
+	if(!e)
+		return -1;
+	e->p = *p;
+	e->tc = grkb_rect{p->x0, p->y0, p->x1, p->y1};
+	e->W = p->x1 - p->x0;
+	e->H = p->y1 - p->y0;
+	e->stride = grkb_stride(e->W);
+	if(cudaGetDevice(&e->st.device) != cudaSuccess)
+	{
+		grkb_set_error("grkb_encoder_create: no CUDA device (there is no CPU fallback)");
+		delete e;
+		return -1;
+	}
+	const size_t plane_bytes = (size_t)e->stride * e->H * 4;
+	const size_t sbytes = grkb_dwt_scratch_bytes(e->tc, p->numres, &e->sstride);
+	bool ok = cudaStreamCreateWithFlags(&e->st.stream, cudaStreamNonBlocking) == cudaSuccess;
+	for(uint32_t c = 0; ok && c < p->numcomps; ++c)
+	{
+		ok = cudaMalloc(&e->coeff[c], plane_bytes) == cudaSuccess &&
+			 cudaMalloc(&e->image[c], plane_bytes) == cudaSuccess &&
+			 cudaMalloc(&e->scratch[c][0], sbytes ? sbytes : 16) == cudaSuccess &&
+			 cudaMalloc(&e->scratch[c][1], sbytes ? sbytes : 16) == cudaSuccess &&
+			 cudaMemsetAsync(e->image[c], 0, plane_bytes, e->st.stream) == cudaSuccess;
+	}
+	for(auto& v : e->ev)
+		ok = ok && cudaEventCreate(&v) == cudaSuccess;
+	if(!ok || cudaStreamSynchronize(e->st.stream) != cudaSuccess)
+	{
+		grkb_set_error("grkb_encoder_create: device allocation failed: %s",
+					   cudaGetErrorString(cudaGetLastError()));
+		grkb_encoder_destroy(e);
+		return -1;
+	}
+	*out = e;
+	return 0;
+}
+
+void grkb_encoder_destroy(grkb_encoder* e)
+{
+	if(!e)
+		return;
+	cudaSetDevice(e->st.device);
+	if(e->st.stream)
+		cudaStreamSynchronize(e->st.stream);
+	for(uint32_t c = 0; c < GRKB_MAX_COMPS; ++c)
+	{
+		cudaFree(e->coeff[c]);
+		cudaFree(e->image[c]);
+		cudaFree(e->scratch[c][0]);
+		cudaFree(e->scratch[c][1]);
+	}
+	for(auto& v : e->ev)
+		if(v)
+			cudaEventDestroy(v);
+	e->st.release();
+	delete e;
+}
+
+int grkb_encoder_encode(grkb_encoder* e, const int32_t* const* image, uint32_t stride,
+						const grkb_enc_cblk* blocks, uint32_t nblocks, const double* mct_norms,
+						uint32_t mct_numcomps, int rate_control, grkb_coded* coded,
+						grkb_pass* passes, uint8_t* bytes, size_t cap, size_t* used)
+{
+	if(!e || !image || stride < (e ? e->W : 0) || (nblocks && (!blocks || !coded || !passes)) ||
+	   (cap && !bytes) || mct_numcomps > GRKB_MAX_COMPS)
+	{
+		grkb_set_error("grkb_encoder_encode: bad arguments");
+		return -1;
+	}
+	if(used)
+		*used = 0;
+	GRKB_CUDA_CHECK(cudaSetDevice(e->st.device));
+	cudaStream_t s = e->st.stream;
+	T1EncLaunch l{};
+	bool any_mq = false, any_ht = false;
+	if(nblocks && scan_enc_blocks(blocks, nblocks, e->p.numcomps, e->stride, e->H, e->p.reversible, l,
+								  any_mq, any_ht))
+		return -1;
+	for(uint32_t c = 0; c < e->p.numcomps; ++c)
+	{
+		if(!image[c])
+		{
+			grkb_set_error("grkb_encoder_encode: plane %u is null", c);
+			return -1;
+		}
+		GRKB_CUDA_CHECK(cudaMemcpy2DAsync(e->image[c], (size_t)e->stride * 4, image[c],
+										  (size_t)stride * 4, (size_t)e->W * 4, e->H,
+										  cudaMemcpyHostToDevice, s));
+	}
+	if(encoder_front(e, s))
+		return -1;
+	e->have_last = false;
+	if(nblocks == 0)
+	{
+		GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
+		return 0;
+	}
+	if(e->st.blocks.reserve((size_t)nblocks * sizeof(grkb_enc_cblk)) ||
+	   e->st.packed.reserve(cap ? cap : 16))
+		return -1;
+	GRKB_CUDA_CHECK(cudaMemcpyAsync(e->st.blocks.p, blocks, (size_t)nblocks * sizeof(grkb_enc_cblk),
+									cudaMemcpyHostToDevice, s));
+	l.blocks = (const grkb_enc_cblk*)e->st.blocks.p;
+	l.nblocks = nblocks;
+	for(uint32_t c = 0; c < e->p.numcomps; ++c)
+		l.planes[c] = e->coeff[c];
+	l.stride = e->stride;
+	l.reversible = e->p.reversible;
+	l.mct_numcomps = mct_norms ? mct_numcomps : 0;
+	for(uint32_t c = 0; c < l.mct_numcomps; ++c)
+		l.mct_norms[c] = mct_norms[c];
+	l.rate_control = rate_control;
+	l.packed = (uint8_t*)e->st.packed.p;
+	l.packed_cap = cap;
+	if(run_encoders(e->st, l, any_mq, any_ht))
+		return -1;
+	e->last = l;
+	e->any_mq = any_mq;
+	e->any_ht = any_ht;
+	e->have_last = true;
+	uint64_t total = 0;
+	GRKB_CUDA_CHECK(cudaMemcpyAsync(coded, l.coded, (size_t)nblocks * sizeof(grkb_coded),
+									cudaMemcpyDeviceToHost, s));
+	GRKB_CUDA_CHECK(cudaMemcpyAsync(passes, l.passes,
+									(size_t)nblocks * GRKB_ENC_MAX_PASSES * sizeof(grkb_pass),
+									cudaMemcpyDeviceToHost, s));
+	GRKB_CUDA_CHECK(cudaMemcpyAsync(&total, l.packed_used, sizeof(total), cudaMemcpyDeviceToHost, s));
+	GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
+	if(total == ~(uint64_t)0)
+	{
+		grkb_set_error("grkb_encoder_encode: output pool of %zu bytes is too small", cap);
+		return -2;
+	}
+	if(total)
+	{
+		GRKB_CUDA_CHECK(cudaMemcpyAsync(bytes, l.packed, (size_t)total, cudaMemcpyDeviceToHost, s));
+		GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
+	}
+	if(used)
+		*used = (size_t)total;
+	return 0;
+}
+
+int grkb_encoder_time_device(grkb_encoder* e, uint32_t iters, uint32_t warmup, float ms[3])
+{
+	if(!e || !e->have_last || iters == 0 || !ms)
+	{
+		grkb_set_error("grkb_encoder_time_device: nothing to time");
+		return -1;
+	}
+	GRKB_CUDA_CHECK(cudaSetDevice(e->st.device));
+	cudaStream_t s = e->st.stream;
+	double acc[3] = {0, 0, 0};
+	for(uint32_t i = 0; i < warmup + iters; ++i)
+	{
+		// the image planes are still resident: the forward stages read them, never write them
+		cudaEventRecord(e->ev[0], s);
+		if(encoder_front(e, s))
+			return -1;
+		cudaEventRecord(e->ev[1], s);
+		T1EncLaunch l = e->last;
+		if(run_encoders(e->st, l, e->any_mq, e->any_ht))
+			return -1;
+		cudaEventRecord(e->ev[2], s);
+		GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
+		if(i >= warmup)
+		{
+			float a = 0, b = 0;
+			cudaEventElapsedTime(&a, e->ev[0], e->ev[1]);
+			cudaEventElapsedTime(&b, e->ev[1], e->ev[2]);
+			acc[0] += a + b;
+			acc[1] += a;
+			acc[2] += b;
+		}
+	}
+	for(int k = 0; k < 3; ++k)
+		ms[k] = (float)(acc[k] / iters);
+	return 0;
+}
+
 } // extern "C"

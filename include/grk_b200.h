@@ -225,6 +225,23 @@ int grkb_t1_decode_host(const grkb_cblk* blocks, uint32_t nblocks, const grkb_se
 						uint32_t numcomps, uint32_t stride, uint32_t plane_h, int reversible,
 						uint32_t* status_out);
 
+/* ---- quantisation parameters (host arithmetic only, no device) ------------------------------ */
+
+/* The step sizes an encoder signals in QCD, one (expn, mant) per band in codestream order (LL,
+ * then HL LH HH per resolution): param_qcd::generate, Part-1 branch
+ * (src/lib/jp2/codestream/HTParams.cpp:194-252) and, for HT + 5/3, param_qcd::set_rev_quant
+ * (:253-272, without the colour-transform bit, as the reference calls it).  expn/mant hold
+ * 3*numres-2 entries. */
+int grkb_qcd_generate(uint32_t numres, uint32_t prec, int reversible, int ht, uint32_t* expn,
+					  uint32_t* mant);
+
+/* Band step size and magnitude bit-plane count from one QCD entry:
+ * Quantizer::setBandStepSizeAndBps (src/lib/jp2/codestream/Quantizer.cpp:26-66), including the
+ * decoder's gain-0 rule for 9/7 and the HT lossy decoder's division by 2^(31-numbps). */
+int grkb_band_quant(uint32_t expn, uint32_t mant, uint32_t orient, uint32_t prec, int reversible,
+					int compress, int ht, uint32_t numgbits, uint32_t roishift, float* stepsize,
+					uint32_t* numbps);
+
 /* ---- encode side ---------------------------------------------------------------------------- */
 
 /* One code block to encode: what CompressBlockExec carries (src/lib/jp2/t1/BlockExec.h:54-84,
@@ -284,6 +301,23 @@ int grkb_t1_encode_host(const grkb_enc_cblk* blocks, uint32_t nblocks, const voi
 						const double* mct_norms, uint32_t mct_numcomps, int rate_control,
 						grkb_coded* coded, grkb_pass* passes, uint8_t* bytes, size_t cap,
 						size_t* used);
+
+/* Whole-tile encoder: the device side of TileProcessor::doCompress up to T2
+ * (src/lib/jp2/tile/TileProcessor.cpp:202-232: dcLevelShiftCompress, mct_encode, dwt_encode,
+ * t1_encode) for all components at once.  H2D of the int32 image planes, DC shift + forward MCT
+ * fused into the first wavelet level, forward wavelet of every component, quantisation fused into
+ * the block encoders, packing, D2H of the block table, the pass table and the coded bytes.
+ * Outputs are as for grkb_t1_encode_host; rate allocation and T2 stay with the host. */
+typedef struct grkb_encoder grkb_encoder;
+int grkb_encoder_create(const grkb_tile_params* p, grkb_encoder** out);
+void grkb_encoder_destroy(grkb_encoder* e);
+int grkb_encoder_encode(grkb_encoder* e, const int32_t* const* image, uint32_t stride,
+						const grkb_enc_cblk* blocks, uint32_t nblocks, const double* mct_norms,
+						uint32_t mct_numcomps, int rate_control, grkb_coded* coded,
+						grkb_pass* passes, uint8_t* bytes, size_t cap, size_t* used);
+/* Re-runs the device stages of the last tile (image still resident), CUDA events on the
+ * encoder's stream: ms[0] whole pass, ms[1] DC/MCT/wavelet, ms[2] block coding + packing. */
+int grkb_encoder_time_device(grkb_encoder* e, uint32_t iters, uint32_t warmup, float ms[3]);
 
 /* Page-locked host memory for byte pools and output planes: copies to and from it are true
  * asynchronous DMA (the decoder accepts any host pointer, pageable ones are staged by the
