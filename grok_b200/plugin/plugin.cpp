@@ -1,0 +1,1035 @@
+// plugin.cpp -- libgrokj2k_plugin.so: Grok's plugin ABI implemented over libgrok_b200.so.
+//
+// Built against the HOST's own headers (grok.h, plugin/plugin_interface.h, plugin/minpf_plugin.h
+// from the Grok source tree the plugin is deployed with: `make -C grok_b200/plugin REF=<tree>`),
+// exactly like any out-of-tree Grok plugin; nothing of those headers is copied here.
+//
+// What the host expects of each symbol is documented in SURVEY.md section 8b; the call sites are
+//   loader        src/lib/jp2/plugin/minpf_plugin_manager.cpp:148-232 (dlsym "minpf_post_load_plugin")
+//   entry points  src/lib/jp2/grok.cpp:606-825 (dlsym of the names in plugin/plugin_interface.h)
+//   encode bridge src/lib/jp2/plugin/plugin_bridge.cpp:146-272 (compress_synch_with_plugin)
+//   decode bridge src/lib/jp2/plugin/plugin_bridge.cpp:24-91  (decompress_synch_plugin_with_host)
+// All compute goes through the C-ABI of include/grk_b200.h; there is no CPU path in here.
+#include "grok.h"
+#include "minpf_plugin.h"
+#include "plugin_interface.h"
+
+#include "../../include/grk_b200.h"
+
+#include <atomic>
+#include <algorithm>
+#include <dirent.h>
+#include <dlfcn.h>
+#include <memory>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <sys/stat.h>
+#include <thread>
+#include <vector>
+
+#define PLUGIN_EXPORT extern "C" __attribute__((visibility("default")))
+
+namespace
+{
+bool g_verbose = false;
+int g_device = 0; // -1: all devices, frames round-robin
+int g_ndev = 0;
+std::atomic<bool> g_stop{false};
+std::atomic<bool> g_batch_done{true};
+std::thread g_batch_thread;
+
+void logf(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
+void logf(const char* fmt, ...)
+{
+	if(!g_verbose)
+		return;
+	va_list ap;
+	va_start(ap, fmt);
+	fprintf(stderr, "[grk_b200 plugin] ");
+	vfprintf(stderr, fmt, ap);
+	fprintf(stderr, "\n");
+	va_end(ap);
+}
+
+// ---- host services the plugin needs (the image object is a host-side C++ object) -------------
+typedef grk_image* (*image_new_fn)(uint16_t, grk_image_cmptparm*, GRK_COLOR_SPACE, bool);
+typedef void (*unref_fn)(grk_object*);
+image_new_fn host_image_new()
+{
+	static image_new_fn f = (image_new_fn)dlsym(RTLD_DEFAULT, "grk_image_new");
+	return f;
+}
+unref_fn host_unref()
+{
+	static unref_fn f = (unref_fn)dlsym(RTLD_DEFAULT, "grk_object_unref");
+	return f;
+}
+
+// ---- the grk_plugin_tile tree (grok.h:995-1077), owned by the plugin --------------------------
+struct TileTree
+{
+	grk_plugin_tile tile{};
+	std::vector<grk_plugin_tile_component> comps;
+	std::vector<grk_plugin_tile_component*> comp_ptrs;
+	std::vector<grk_plugin_resolution> ress;
+	std::vector<grk_plugin_resolution*> res_ptrs;
+	std::vector<grk_plugin_band> bands;
+	std::vector<grk_plugin_band*> band_ptrs;
+	std::vector<grk_plugin_precinct> precs;
+	std::vector<grk_plugin_precinct*> prec_ptrs;
+	std::vector<grk_plugin_code_block> blocks;
+	std::vector<grk_plugin_code_block*> block_ptrs;
+	std::vector<uint8_t> data; // decode: per-block byte buffers the host copies into
+	// flat views, component-major in layout order (the order of the descriptor tables)
+	std::vector<grkb_cblk_geom> geom; // one component's worth
+	std::vector<grk_plugin_code_block*> flat; // numcomps * geom.size()
+	std::vector<grk_plugin_band*> flat_band;
+	uint32_t numcomps = 0, numres = 0;
+};
+
+struct TileGeom
+{
+	uint32_t x0, y0, x1, y1, numcomps, numres, cblkw_exp, cblkh_exp;
+	uint32_t pw[33], ph[33];
+};
+
+uint32_t ceildivpow2(uint32_t a, uint32_t b)
+{
+	return (uint32_t)(((uint64_t)a + ((uint64_t)1 << b) - 1) >> b);
+}
+
+// decode_cap: bytes reserved per block for the host's memcpy (0 on encode)
+bool build_tree(const TileGeom& g, bool decode, TileTree& t)
+{
+	grkb_layout_params lp{};
+	lp.x0 = g.x0;
+	lp.y0 = g.y0;
+	lp.x1 = g.x1;
+	lp.y1 = g.y1;
+	lp.numres = g.numres;
+	lp.cblkw_exp = g.cblkw_exp;
+	lp.cblkh_exp = g.cblkh_exp;
+	for(int r = 0; r < 33; ++r)
+	{
+		lp.prec_w_exp[r] = g.pw[r];
+		lp.prec_h_exp[r] = g.ph[r];
+	}
+	uint32_t n = 0;
+	if(grkb_tile_layout(&lp, nullptr, 0, &n))
+		return false;
+	std::vector<grkb_cblk_geom> all(n);
+	if(n && grkb_tile_layout(&lp, all.data(), n, &n))
+		return false;
+	t.numcomps = g.numcomps;
+	t.numres = g.numres;
+	// count bands / precincts per resolution the way the host does (Resolution::init)
+	uint32_t nbands_total = 0;
+	std::vector<uint64_t> nprec(g.numres);
+	uint64_t nprec_total = 0;
+	for(uint32_t r = 0; r < g.numres; ++r)
+	{
+		const uint32_t nd = g.numres - 1 - r;
+		const uint32_t rx0 = ceildivpow2(g.x0, nd), ry0 = ceildivpow2(g.y0, nd);
+		const uint32_t rx1 = ceildivpow2(g.x1, nd), ry1 = ceildivpow2(g.y1, nd);
+		const uint32_t pwe = g.pw[r], phe = g.ph[r];
+		const uint64_t gw = rx0 == rx1 ? 0 : (((uint64_t)ceildivpow2(rx1, pwe) << pwe) - ((uint64_t)(rx0 >> pwe) << pwe)) >> pwe;
+		const uint64_t gh = ry0 == ry1 ? 0 : (((uint64_t)ceildivpow2(ry1, phe) << phe) - ((uint64_t)(ry0 >> phe) << phe)) >> phe;
+		nprec[r] = gw * gh;
+		const uint32_t nb = r ? 3 : 1;
+		nbands_total += nb;
+		nprec_total += nprec[r] * nb;
+	}
+	size_t nblk = 0;
+	for(auto& b : all)
+		nblk += (b.w && b.h) ? 1 : 0;
+	const uint32_t C = g.numcomps;
+	t.comps.resize(C);
+	t.comp_ptrs.resize(C);
+	t.ress.resize((size_t)C * g.numres);
+	t.res_ptrs.resize(t.ress.size());
+	t.bands.resize((size_t)C * nbands_total);
+	t.band_ptrs.resize(t.bands.size());
+	t.precs.resize((size_t)C * nprec_total);
+	t.prec_ptrs.resize(t.precs.size());
+	t.blocks.resize((size_t)C * all.size());
+	t.block_ptrs.resize(t.blocks.size());
+	size_t cap_total = 0;
+	if(decode)
+	{
+		for(auto& b : all)
+			cap_total += (size_t)b.w * b.h * 4 + 64; // the host's own bound (t1/T1.cpp:256)
+		t.data.assign(cap_total * C, 0);
+	}
+	t.geom.clear();
+	for(auto& b : all)
+		if(b.w && b.h)
+			t.geom.push_back(b);
+	t.flat.clear();
+	t.flat_band.clear();
+	size_t ri = 0, bi = 0, pi = 0, ki = 0, doff = 0;
+	for(uint32_t c = 0; c < C; ++c)
+	{
+		t.comp_ptrs[c] = &t.comps[c];
+		t.comps[c].numResolutions = g.numres;
+		t.comps[c].resolutions = &t.res_ptrs[ri];
+		size_t gi = 0; // cursor in `all` (sorted res, band, precinct, cblkno)
+		for(uint32_t r = 0; r < g.numres; ++r, ++ri)
+		{
+			t.res_ptrs[ri] = &t.ress[ri];
+			t.ress[ri].level = r;
+			t.ress[ri].numBands = r ? 3 : 1;
+			t.ress[ri].band = &t.band_ptrs[bi];
+			for(uint32_t b = 0; b < (r ? 3u : 1u); ++b, ++bi)
+			{
+				t.band_ptrs[bi] = &t.bands[bi];
+				grk_plugin_band& pb = t.bands[bi];
+				pb.orientation = (uint8_t)(r ? b + 1 : 0);
+				pb.numPrecincts = nprec[r];
+				pb.precincts = &t.prec_ptrs[pi];
+				pb.stepsize = 1.0f;
+				for(uint64_t p = 0; p < nprec[r]; ++p, ++pi)
+				{
+					t.prec_ptrs[pi] = &t.precs[pi];
+					grk_plugin_precinct& pp = t.precs[pi];
+					pp.blocks = &t.block_ptrs[ki];
+					uint64_t cnt = 0;
+					while(gi < all.size() && all[gi].res == r && all[gi].band == b && all[gi].precinct == p)
+					{
+						const grkb_cblk_geom& q = all[gi++];
+						grk_plugin_code_block& k = t.blocks[ki];
+						t.block_ptrs[ki] = &k;
+						memset(&k, 0, sizeof(k));
+						k.x0 = q.cx0;
+						k.y0 = q.cy0;
+						k.x1 = q.cx0 + q.w;
+						k.y1 = q.cy0 + q.h;
+						k.numPix = (uint32_t)q.w * q.h;
+						if(decode)
+						{
+							k.compressedData = t.data.data() + doff;
+							doff += (size_t)q.w * q.h * 4 + 64;
+						}
+						if(q.w && q.h)
+						{
+							t.flat.push_back(&k);
+							t.flat_band.push_back(&pb);
+						}
+						++ki;
+						++cnt;
+					}
+					pp.numBlocks = cnt;
+				}
+			}
+		}
+	}
+	t.tile.decompress_flags = 0;
+	t.tile.numComponents = C;
+	t.tile.tileComponents = t.comp_ptrs.data();
+	return t.flat.size() == t.geom.size() * C && nblk == t.geom.size();
+}
+
+// ---- input images for plugin-driven encode: binary PNM (P5/P6, 8/16 bit) and raw ---------------
+struct HostImage
+{
+	uint32_t w = 0, h = 0, numcomps = 0, prec = 0;
+	bool sgnd = false;
+	std::vector<std::vector<int32_t>> planes;
+};
+
+bool read_pnm(FILE* f, HostImage& im)
+{
+	char magic[3] = {0, 0, 0};
+	unsigned w = 0, h = 0, maxv = 0;
+	auto token = [&](unsigned& v) -> bool {
+		int c = fgetc(f);
+		while(c == ' ' || c == '\n' || c == '\r' || c == '\t' || c == '#')
+		{
+			if(c == '#')
+				while(c != '\n' && c != EOF)
+					c = fgetc(f);
+			c = fgetc(f);
+		}
+		if(c < '0' || c > '9')
+			return false;
+		v = 0;
+		while(c >= '0' && c <= '9')
+		{
+			v = v * 10 + (unsigned)(c - '0');
+			c = fgetc(f);
+		}
+		return true; // exactly one whitespace byte has been consumed after the number
+	};
+	if(fread(magic, 1, 2, f) != 2 || magic[0] != 'P' || (magic[1] != '5' && magic[1] != '6'))
+		return false;
+	if(!token(w) || !token(h) || !token(maxv) || !w || !h || !maxv || maxv > 65535)
+		return false;
+	im.w = w;
+	im.h = h;
+	im.numcomps = magic[1] == '6' ? 3 : 1;
+	im.prec = 0;
+	while((1u << im.prec) <= maxv)
+		++im.prec;
+	const size_t bps = maxv > 255 ? 2 : 1, n = (size_t)w * h * im.numcomps;
+	std::vector<uint8_t> raw(n * bps);
+	if(fread(raw.data(), 1, raw.size(), f) != raw.size())
+		return false;
+	im.planes.assign(im.numcomps, std::vector<int32_t>((size_t)w * h));
+	for(size_t i = 0; i < (size_t)w * h; ++i)
+		for(uint32_t c = 0; c < im.numcomps; ++c)
+		{
+			const size_t k = i * im.numcomps + c;
+			im.planes[c][i] = bps == 2 ? (int32_t)((raw[2 * k] << 8) | raw[2 * k + 1]) : raw[k];
+		}
+	return true;
+}
+
+// raw: component-planar, big-endian for > 8 bits (the reference's RAW_FMT; RAWL is little-endian)
+bool read_raw(FILE* f, const grk_raw_cparameters& rc, bool little, HostImage& im)
+{
+	im.w = rc.width;
+	im.h = rc.height;
+	im.numcomps = rc.numcomps;
+	im.prec = rc.prec;
+	im.sgnd = rc.sgnd;
+	if(!im.w || !im.h || !im.numcomps || !im.prec || im.prec > 16)
+		return false;
+	const size_t bps = im.prec > 8 ? 2 : 1, n = (size_t)im.w * im.h;
+	std::vector<uint8_t> raw(n * bps);
+	im.planes.assign(im.numcomps, std::vector<int32_t>(n));
+	for(uint32_t c = 0; c < im.numcomps; ++c)
+	{
+		if(fread(raw.data(), 1, raw.size(), f) != raw.size())
+			return false;
+		for(size_t i = 0; i < n; ++i)
+		{
+			int32_t v;
+			if(bps == 1)
+				v = im.sgnd ? (int8_t)raw[i] : raw[i];
+			else
+			{
+				const uint16_t u = little ? (uint16_t)(raw[2 * i] | (raw[2 * i + 1] << 8))
+										  : (uint16_t)((raw[2 * i] << 8) | raw[2 * i + 1]);
+				v = im.sgnd ? (int16_t)u : u;
+			}
+			im.planes[c][i] = v;
+		}
+	}
+	return true;
+}
+
+bool read_image(const grk_cparameters* p, const char* path, HostImage& im)
+{
+	FILE* f = fopen(path, "rb");
+	if(!f)
+		return false;
+	bool ok;
+	if(p->decod_format == GRK_RAW_FMT || p->decod_format == GRK_RAWL_FMT)
+		ok = read_raw(f, p->raw_cp, p->decod_format == GRK_RAWL_FMT, im);
+	else
+		ok = read_pnm(f, im);
+	fclose(f);
+	return ok;
+}
+
+// ---- one frame through the device encoder, then the host callback ------------------------------
+struct EncodeJob
+{
+	std::string in, out;
+	bool out_relative = false;
+};
+
+int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
+			   grk::PLUGIN_ENCODE_USER_CALLBACK cb)
+{
+	HostImage im;
+	if(!read_image(params, job.in.c_str(), im))
+	{
+		logf("cannot read %s (binary PNM and raw input are supported)", job.in.c_str());
+		return -1;
+	}
+	if(params->tile_size_on && (params->t_width < im.w || params->t_height < im.h))
+	{
+		logf("multi-tile encode is not routed through the plugin tile (one tile per grk_plugin_tile)");
+		return -1;
+	}
+	if(params->subsampling_dx > 1 || params->subsampling_dy > 1 || im.prec > 16)
+		return -1;
+	const bool ht = params->isHT || (params->cblk_sty & GRK_CBLKSTY_HT);
+	const uint8_t sty = (uint8_t)(params->cblk_sty & 0x3F);
+	if(!ht && sty != 0)
+	{
+		logf("mode switches other than HT cannot cross the plugin bridge (pass->term is never set, "
+			 "plugin_bridge.cpp:229-262)");
+		return -1;
+	}
+	const bool reversible = !params->irreversible;
+	const uint32_t numres = params->numresolution;
+	const bool mct = params->mct == 255 ? im.numcomps >= 3 : params->mct == 1;
+	if(grkb_set_device(device))
+		return -1;
+	// geometry
+	TileGeom g{};
+	g.x0 = params->image_offset_x0;
+	g.y0 = params->image_offset_y0;
+	g.x1 = g.x0 + im.w;
+	g.y1 = g.y0 + im.h;
+	g.numcomps = im.numcomps;
+	g.numres = numres;
+	auto log2u = [](uint32_t v) {
+		uint32_t l = 0;
+		while((1u << l) < v)
+			++l;
+		return l;
+	};
+	g.cblkw_exp = log2u(params->cblockw_init ? params->cblockw_init : 64);
+	g.cblkh_exp = log2u(params->cblockh_init ? params->cblockh_init : 64);
+	for(uint32_t r = 0; r < 33; ++r)
+		g.pw[r] = g.ph[r] = 15;
+	if((params->csty & 1) && params->res_spec)
+	{
+		// precinct sizes, highest resolution first; the last pair is halved for every further
+		// resolution (CodeStreamCompress.cpp:542-596)
+		auto flog2 = [](uint32_t v) {
+			uint32_t l = 0;
+			while(v > 1)
+			{
+				v >>= 1;
+				++l;
+			}
+			return l;
+		};
+		for(uint32_t r = 0; r < numres; ++r)
+		{
+			const uint32_t p = numres - 1 - r, last = params->res_spec - 1;
+			uint32_t pw, ph;
+			if(p < params->res_spec)
+			{
+				pw = params->prcw_init[p];
+				ph = params->prch_init[p];
+			}
+			else
+			{
+				pw = (p - last) < 32 ? params->prcw_init[last] >> (p - last) : 0;
+				ph = (p - last) < 32 ? params->prch_init[last] >> (p - last) : 0;
+			}
+			g.pw[r] = pw < 1 ? 1 : flog2(pw);
+			g.ph[r] = ph < 1 ? 1 : flog2(ph);
+		}
+	}
+	auto tree = std::make_unique<TileTree>();
+	if(!build_tree(g, false, *tree))
+		return -1;
+	// block table: quantisation parameters as the host will signal them in QCD
+	const uint32_t nb = 3 * numres - 2;
+	std::vector<uint32_t> expn(nb), mant(nb);
+	if(grkb_qcd_generate(numres, im.prec, reversible, ht, expn.data(), mant.data()))
+	{
+		logf("%s", grkb_last_error());
+		return -1;
+	}
+	const uint32_t numgbits = params->numgbits;
+	const size_t ng = tree->geom.size(), n = ng * im.numcomps;
+	std::vector<grkb_enc_cblk> blocks(n);
+	std::vector<float> band_step(ng);
+	for(size_t i = 0; i < ng; ++i)
+	{
+		const grkb_cblk_geom& q = tree->geom[i];
+		float step = 1.0f;
+		uint32_t bps = 0;
+		const uint32_t qi = (q.res == 0 ? 0 : 3 * q.res - 2) + q.band;
+		if(grkb_band_quant(expn[qi], mant[qi], q.orient, im.prec, reversible, 1, ht, numgbits, 0, &step,
+						   &bps))
+			return -1;
+		band_step[i] = step;
+		for(uint32_t c = 0; c < im.numcomps; ++c)
+		{
+			grkb_enc_cblk& b = blocks[c * ng + i];
+			memset(&b, 0, sizeof(b));
+			b.x = q.x;
+			b.y = q.y;
+			b.w = q.w;
+			b.h = q.h;
+			b.comp = (uint8_t)c;
+			b.orient = q.orient;
+			b.level = q.level;
+			b.cblk_sty = ht ? GRKB_CBLKSTY_HT : 0;
+			b.k_msbs = (uint8_t)bps;
+			b.stepsize = step;
+		}
+	}
+	grkb_tile_params tp{};
+	tp.x0 = g.x0;
+	tp.y0 = g.y0;
+	tp.x1 = g.x1;
+	tp.y1 = g.y1;
+	tp.numcomps = im.numcomps;
+	tp.numres = numres;
+	tp.reversible = reversible;
+	tp.mct = mct;
+	for(uint32_t c = 0; c < im.numcomps; ++c)
+		tp.shift[c] = im.sgnd ? 0 : 1 << (im.prec - 1);
+	grkb_encoder* enc = nullptr;
+	if(grkb_encoder_create(&tp, &enc))
+	{
+		logf("%s", grkb_last_error());
+		return -1;
+	}
+	std::vector<grkb_coded> coded(n);
+	std::vector<grkb_pass> passes(n * GRKB_ENC_MAX_PASSES);
+	std::vector<uint8_t> bytes((size_t)im.w * im.h * im.numcomps * 4 + 65536);
+	std::vector<const int32_t*> planes(im.numcomps);
+	for(uint32_t c = 0; c < im.numcomps; ++c)
+		planes[c] = im.planes[c].data();
+	// the host runs rate control whenever a rate or quality target is set
+	const bool rc = (params->allocationByRateDistoration && params->layer_rate[0] != 0) ||
+					params->allocationByQuality || params->numlayers > 1;
+	static const double norms_rev[3] = {1.732, .8292, .8292}, norms_irrev[3] = {1.732, 1.805, 1.573};
+	size_t used = 0;
+	int err = grkb_encoder_encode(enc, planes.data(), im.w, blocks.data(), (uint32_t)n,
+								  mct ? (reversible ? norms_rev : norms_irrev) : nullptr, mct ? 3 : 0,
+								  rc ? 1 : 0, coded.data(), passes.data(), bytes.data(), bytes.size(),
+								  &used);
+	grkb_encoder_destroy(enc);
+	if(err)
+	{
+		logf("%s", grkb_last_error());
+		return -1;
+	}
+	// fill the tree the way compress_synch_with_plugin reads it (plugin_bridge.cpp:146-272)
+	for(size_t i = 0; i < n; ++i)
+	{
+		grk_plugin_code_block& k = *tree->flat[i];
+		const grkb_coded& c = coded[i];
+		if(c.failed || c.numpasses > 67)
+			return -1;
+		tree->flat_band[i]->stepsize = band_step[i % ng];
+		k.compressedData = bytes.data() + c.data_off;
+		k.compressedDataLength = c.data_len;
+		k.numBitPlanes = c.numbps;
+		k.numPasses = c.numpasses;
+		for(uint32_t p = 0; p < c.numpasses; ++p)
+		{
+			const grkb_pass& ps = passes[i * GRKB_ENC_MAX_PASSES + p];
+			k.passes[p].distortionDecrease = ps.distortion;
+			k.passes[p].rate = (size_t)ps.rate - 1; // the bridge adds the 1 back (:249-257)
+			k.passes[p].length = ps.len;
+		}
+	}
+	// the image object is the host's (a C++ GrkImage behind the C struct)
+	grk_image* image = nullptr;
+	if(host_image_new())
+	{
+		std::vector<grk_image_cmptparm> cp(im.numcomps);
+		for(auto& c : cp)
+		{
+			memset(&c, 0, sizeof(c));
+			c.prec = (uint8_t)im.prec;
+			c.sgnd = im.sgnd;
+			c.dx = c.dy = 1;
+			c.w = im.w;
+			c.h = im.h;
+			c.x0 = g.x0;
+			c.y0 = g.y0;
+		}
+		image = host_image_new()((uint16_t)im.numcomps, cp.data(),
+								 im.numcomps >= 3 ? GRK_CLRSPC_SRGB : GRK_CLRSPC_GRAY, true);
+		if(image)
+		{
+			image->x0 = g.x0;
+			image->y0 = g.y0;
+			image->x1 = g.x1;
+			image->y1 = g.y1;
+			for(uint32_t c = 0; c < im.numcomps; ++c)
+				for(uint32_t y = 0; y < im.h; ++y)
+					memcpy(image->comps[c].data + (size_t)y * image->comps[c].stride,
+						   im.planes[c].data() + (size_t)y * im.w, sizeof(int32_t) * im.w);
+		}
+	}
+	grk::plugin_encode_user_callback_info info;
+	memset(&info, 0, sizeof(info));
+	info.input_file_name = job.in.c_str();
+	info.outputFileNameIsRelative = job.out_relative;
+	info.output_file_name = job.out.c_str();
+	info.compressor_parameters = const_cast<grk_cparameters*>(params);
+	info.image = image;
+	info.tile = &tree->tile;
+	info.error_code = 0;
+	cb(&info); // synchronous: everything it reads stays alive until it returns
+	if(image && host_unref())
+		host_unref()(&image->obj);
+	return info.error_code ? -1 : 0;
+}
+
+int next_device()
+{
+	static std::atomic<uint32_t> rr{0};
+	if(g_device >= 0)
+		return g_device;
+	return g_ndev > 0 ? (int)(rr++ % (uint32_t)g_ndev) : 0;
+}
+
+// ---- decode ------------------------------------------------------------------------------------
+
+// Read-only peek at the main header's QCD: the plugin tile tree carries each block's bit-plane
+// count but not the band's, and the HT dequantiser needs their difference (BlockExec.h:40).
+struct QcdPeek
+{
+	bool ok = false;
+	uint32_t numgbits = 0, style = 0;
+	std::vector<uint32_t> expn, mant;
+};
+
+QcdPeek peek_qcd(const char* path, uint32_t numres)
+{
+	QcdPeek q;
+	FILE* f = path ? fopen(path, "rb") : nullptr;
+	if(!f)
+		return q;
+	std::vector<uint8_t> b(1 << 16);
+	b.resize(fread(b.data(), 1, b.size(), f));
+	fclose(f);
+	size_t i = 0;
+	while(i + 3 < b.size() && !(b[i] == 0xFF && b[i + 1] == 0x4F && b[i + 2] == 0xFF && b[i + 3] == 0x51))
+		++i;
+	i += 2;
+	while(i + 4 <= b.size() && b[i] == 0xFF && b[i + 1] != 0x90)
+	{
+		const uint32_t len = (b[i + 2] << 8) | b[i + 3];
+		if(b[i + 1] == 0x5C && i + 2 + len <= b.size() && len >= 4)
+		{
+			const uint8_t sq = b[i + 4];
+			q.numgbits = sq >> 5;
+			q.style = sq & 0x1F;
+			const uint8_t* p = &b[i + 5];
+			const uint32_t nbody = len - 3, nb = 3 * numres - 2;
+			q.expn.assign(nb, 0);
+			q.mant.assign(nb, 0);
+			for(uint32_t k = 0; k < nb; ++k)
+			{
+				const uint32_t res = k == 0 ? 0 : (k - 1) / 3 + 1;
+				if(q.style == 0 && k < nbody)
+					q.expn[k] = p[k] >> 3;
+				else if(q.style == 2 && 2 * k + 1 < nbody)
+				{
+					const uint32_t v = (p[2 * k] << 8) | p[2 * k + 1];
+					q.expn[k] = v >> 11;
+					q.mant[k] = v & 0x7FF;
+				}
+				else if(q.style == 1 && nbody >= 2)
+				{
+					const uint32_t v = (p[0] << 8) | p[1], e0 = v >> 11;
+					q.expn[k] = res == 0 ? e0 : (e0 > res - 1 ? e0 - (res - 1) : 0);
+					q.mant[k] = v & 0x7FF;
+				}
+			}
+			q.ok = true;
+			return q;
+		}
+		i += 2 + len;
+	}
+	return q;
+}
+
+struct DecodeCtx
+{
+	TileGeom geom{};
+	std::unique_ptr<TileTree> tree;
+	uint32_t prec = 0;
+	bool sgnd = false, reversible = true, mct = false, ht = false;
+	uint8_t cblk_sty = 0;
+	bool ready = false;
+};
+thread_local DecodeCtx* t_ctx = nullptr;
+
+// GROK_INIT_DECOMPRESSORS: called by the host's callback once the main header is read
+int init_decompressors(grk_header_info* h, grk_image* image)
+{
+	DecodeCtx* c = t_ctx;
+	if(!c || !h || !image || image->numcomps == 0 || image->numcomps > GRKB_MAX_COMPS)
+		return -1;
+	if(h->t_grid_width * h->t_grid_height != 1)
+	{
+		logf("multi-tile images are decoded by the host (one tile per grk_plugin_tile)");
+		return -1;
+	}
+	for(uint16_t i = 0; i < image->numcomps; ++i)
+		if(image->comps[i].dx != 1 || image->comps[i].dy != 1 || image->comps[i].prec != image->comps[0].prec)
+			return -1;
+	TileGeom& g = c->geom;
+	g.x0 = image->x0;
+	g.y0 = image->y0;
+	g.x1 = image->x1;
+	g.y1 = image->y1;
+	g.numcomps = image->numcomps;
+	g.numres = h->numresolutions;
+	auto flog2 = [](uint32_t v) {
+		uint32_t l = 0;
+		while(v > 1)
+		{
+			v >>= 1;
+			++l;
+		}
+		return l;
+	};
+	g.cblkw_exp = flog2(h->cblockw_init);
+	g.cblkh_exp = flog2(h->cblockh_init);
+	for(uint32_t r = 0; r < 33; ++r)
+	{
+		g.pw[r] = r < g.numres ? flog2(h->prcw_init[r]) : 15;
+		g.ph[r] = r < g.numres ? flog2(h->prch_init[r]) : 15;
+	}
+	c->prec = image->comps[0].prec;
+	c->sgnd = image->comps[0].sgnd;
+	c->reversible = !h->irreversible;
+	c->mct = h->mct == 1 && image->numcomps >= 3;
+	c->cblk_sty = h->cblk_sty;
+	c->ht = (h->cblk_sty & GRK_CBLKSTY_HT) != 0;
+	c->tree = std::make_unique<TileTree>();
+	c->ready = build_tree(g, true, *c->tree);
+	return c->ready ? 0 : -1;
+}
+
+int decode_one(grk_decompress_parameters* params, const std::string& in, const std::string& out,
+			   int device, grk::PLUGIN_DECODE_USER_CALLBACK cb)
+{
+	DecodeCtx ctx;
+	t_ctx = &ctx;
+	grk::PluginDecodeCallbackInfo info(in, out, params, params ? params->decod_format : GRK_UNK_FMT,
+									   GRK_DECODE_HEADER);
+	if(params)
+		info.cod_format = params->cod_format;
+	info.deviceId = (size_t)device;
+	info.init_decompressors_func = init_decompressors;
+	auto finish = [&](int rc) {
+		info.decompress_flags = GRK_PLUGIN_DECODE_CLEAN;
+		cb(&info);
+		t_ctx = nullptr;
+		return rc;
+	};
+	if(cb(&info) != 0 || !ctx.ready)
+		return finish(-1);
+	TileTree& t = *ctx.tree;
+	// T2 on the host.  GRK_DECODE_POST_T1 has to ride along: without it the host never advances
+	// to the next tile part (CodeStreamDecompress::findNextTile only does so when the post stage
+	// is enabled, codestream/CodeStreamDecompress.cpp:1048-1070) and then fails with "no SOT
+	// marker found".  The host's own post stage then runs over its empty tile buffer; the samples
+	// that count are the ones this plugin hands over below.
+	info.decompress_flags = GRK_DECODE_T2 | GRK_DECODE_POST_T1;
+	info.tile = &t.tile;
+	if(cb(&info) != 0) // host: T2, then decompress_synch_plugin_with_host fills the tree
+		return finish(-1);
+	// descriptor table from the filled tree
+	const TileGeom& g = ctx.geom;
+	const size_t ng = t.geom.size(), n = ng * g.numcomps;
+	QcdPeek qcd;
+	if(ctx.ht)
+	{
+		qcd = peek_qcd(in.c_str(), g.numres);
+		if(!qcd.ok)
+		{
+			logf("cannot read QCD of %s", in.c_str());
+			return finish(-1);
+		}
+	}
+	std::vector<grkb_cblk> blocks(n);
+	std::vector<grkb_seg> segs;
+	std::vector<uint8_t> pool;
+	segs.reserve(n);
+	for(size_t i = 0; i < n; ++i)
+	{
+		const grkb_cblk_geom& q = t.geom[i % ng];
+		const grk_plugin_code_block& k = *t.flat[i];
+		grkb_cblk& b = blocks[i];
+		memset(&b, 0, sizeof(b));
+		b.x = q.x;
+		b.y = q.y;
+		b.w = q.w;
+		b.h = q.h;
+		b.comp = (uint8_t)(i / ng);
+		b.orient = q.orient;
+		b.cblk_sty = ctx.cblk_sty;
+		b.numbps = k.numBitPlanes;
+		const float half_step = t.flat_band[i]->stepsize; // band->stepsize / 2 (bridge :46)
+		if(ctx.ht)
+		{
+			float s;
+			uint32_t band_bps = 0;
+			const uint32_t qi = (q.res == 0 ? 0 : 3 * q.res - 2) + q.band;
+			if(grkb_band_quant(qcd.expn[qi], qcd.mant[qi], q.orient, ctx.prec, ctx.reversible, 0, 0,
+							   qcd.numgbits, 0, &s, &band_bps))
+				return finish(-1);
+			b.k_msbs = (uint8_t)(band_bps > k.numBitPlanes ? band_bps - k.numBitPlanes : 0);
+			b.scale = half_step * 2.0f;
+		}
+		else
+			b.scale = half_step;
+		if(k.compressedDataLength && k.numPasses)
+		{
+			b.numsegs = 1;
+			b.seg_first = (uint32_t)segs.size();
+			b.data_off = (uint32_t)pool.size();
+			b.data_len = k.compressedDataLength;
+			segs.push_back(grkb_seg{k.compressedDataLength, (uint32_t)k.numPasses});
+			pool.insert(pool.end(), k.compressedData, k.compressedData + k.compressedDataLength);
+		}
+	}
+	pool.resize(pool.size() + 16, 0);
+	if(grkb_set_device(device))
+		return finish(-1);
+	grkb_tile_params tp{};
+	tp.x0 = g.x0;
+	tp.y0 = g.y0;
+	tp.x1 = g.x1;
+	tp.y1 = g.y1;
+	tp.numcomps = g.numcomps;
+	tp.numres = g.numres;
+	tp.reversible = ctx.reversible;
+	tp.mct = ctx.mct;
+	for(uint32_t c = 0; c < g.numcomps; ++c)
+	{
+		tp.shift[c] = ctx.sgnd ? 0 : 1 << (ctx.prec - 1);
+		tp.lo[c] = ctx.sgnd ? -(1 << (ctx.prec - 1)) : 0;
+		tp.hi[c] = ctx.sgnd ? (1 << (ctx.prec - 1)) - 1 : (1 << ctx.prec) - 1;
+	}
+	// the output image is a host object; it is handed over with plugin_owns_image = true
+	if(!host_image_new() || !host_unref())
+	{
+		logf("host library symbols grk_image_new / grk_object_unref are not visible");
+		return finish(-1);
+	}
+	const uint32_t W = g.x1 - g.x0, H = g.y1 - g.y0;
+	std::vector<grk_image_cmptparm> cp(g.numcomps);
+	for(auto& c : cp)
+	{
+		memset(&c, 0, sizeof(c));
+		c.prec = (uint8_t)ctx.prec;
+		c.sgnd = ctx.sgnd;
+		c.dx = c.dy = 1;
+		c.w = W;
+		c.h = H;
+		c.x0 = g.x0;
+		c.y0 = g.y0;
+	}
+	grk_image* image = host_image_new()((uint16_t)g.numcomps, cp.data(),
+										g.numcomps >= 3 ? GRK_CLRSPC_SRGB : GRK_CLRSPC_GRAY, true);
+	if(!image)
+		return finish(-1);
+	image->x0 = g.x0;
+	image->y0 = g.y0;
+	image->x1 = g.x1;
+	image->y1 = g.y1;
+	grkb_decoder* dec = nullptr;
+	int rc = grkb_decoder_create(&tp, (uint32_t)n, pool.size(), &dec);
+	uint32_t rejected = 0;
+	if(!rc)
+	{
+		std::vector<int32_t*> planes(g.numcomps);
+		for(uint32_t c = 0; c < g.numcomps; ++c)
+			planes[c] = image->comps[c].data;
+		rc = grkb_decoder_decode(dec, blocks.data(), (uint32_t)n, segs.data(), (uint32_t)segs.size(),
+								 pool.data(), pool.size(), planes.data(), image->comps[0].stride,
+								 &rejected);
+		grkb_decoder_destroy(dec);
+	}
+	if(rc || rejected)
+	{
+		logf("decode failed: %s (%u blocks rejected)", grkb_last_error(), rejected);
+		host_unref()(&image->obj);
+		return finish(-1);
+	}
+	info.image = image;
+	info.plugin_owns_image = true;
+	info.decompress_flags = GRK_DECODE_POST_T1;
+	rc = cb(&info); // host: colour management, file output
+	finish(rc);
+	host_unref()(&image->obj);
+	return rc;
+}
+
+std::vector<std::string> list_dir(const char* dir)
+{
+	std::vector<std::string> v;
+	if(DIR* d = dir ? opendir(dir) : nullptr)
+	{
+		while(dirent* e = readdir(d))
+		{
+			std::string p = std::string(dir) + "/" + e->d_name;
+			struct stat st;
+			if(e->d_name[0] != '.' && stat(p.c_str(), &st) == 0 && S_ISREG(st.st_mode))
+				v.push_back(e->d_name);
+		}
+		closedir(d);
+	}
+	std::sort(v.begin(), v.end());
+	return v;
+}
+
+std::string replace_ext(const std::string& name, const char* ext)
+{
+	const size_t dot = name.rfind('.');
+	return (dot == std::string::npos ? name : name.substr(0, dot)) + "." + ext;
+}
+
+void join_batch()
+{
+	g_stop = true;
+	if(g_batch_thread.joinable())
+		g_batch_thread.join();
+	g_stop = false;
+}
+} // namespace
+
+// ---- minpf registration (plugin/minpf_plugin_manager.cpp:148-232) -------------------------------
+
+PLUGIN_EXPORT void* create(grk::minpf_object_params*)
+{
+	return nullptr;
+}
+PLUGIN_EXPORT int32_t destroy(void*)
+{
+	return 0;
+}
+PLUGIN_EXPORT int32_t exit_func()
+{
+	join_batch();
+	return 0;
+}
+PLUGIN_EXPORT grk::minpf_exit_func minpf_post_load_plugin(const char*,
+														   const grk::minpf_platform_services* params)
+{
+	if(!params || !params->registerObject)
+		return nullptr;
+	grk::minpf_register_params rp;
+	rp.version.major = 1;
+	rp.version.minor = 0;
+	rp.createFunc = create;
+	rp.destroyFunc = destroy;
+	if(params->registerObject("grk_b200", &rp) < 0)
+		return nullptr;
+	return exit_func;
+}
+
+PLUGIN_EXPORT bool plugin_init(grk_plugin_init_info info)
+{
+	g_verbose = info.verbose;
+	g_ndev = grkb_device_count();
+	if(info.deviceId == -2 || g_ndev < 1)
+	{
+		logf("no CUDA device: the plugin stays disabled (there is no CPU path in it)");
+		return false;
+	}
+	g_device = info.deviceId;
+	if(g_device >= g_ndev)
+		return false;
+	return grkb_set_device(g_device < 0 ? 0 : g_device) == 0;
+}
+
+PLUGIN_EXPORT uint32_t plugin_get_debug_state(void)
+{
+	return GRK_PLUGIN_STATE_NO_DEBUG;
+}
+PLUGIN_EXPORT void plugin_debug_mqc_next_cxd(grk::grk_plugin_debug_mqc*, uint32_t) {}
+PLUGIN_EXPORT void plugin_debug_mqc_next_plane(grk::grk_plugin_debug_mqc*) {}
+
+// ---- encode ------------------------------------------------------------------------------------
+
+PLUGIN_EXPORT int32_t plugin_encode(grk_cparameters* params, grk::PLUGIN_ENCODE_USER_CALLBACK cb)
+{
+	if(!params || !cb)
+		return -1;
+	EncodeJob job;
+	job.in = params->infile;
+	job.out = params->outfile;
+	return encode_one(params, job, next_device(), cb);
+}
+
+PLUGIN_EXPORT int32_t plugin_batch_encode(const char* input_dir, const char* output_dir,
+										   grk_cparameters* params,
+										   grk::PLUGIN_ENCODE_USER_CALLBACK cb)
+{
+	if(!input_dir || !output_dir || !params || !cb)
+		return -1;
+	join_batch();
+	const std::string in = input_dir, out = output_dir;
+	const grk_cparameters copy = *params;
+	g_batch_done = false;
+	g_batch_thread = std::thread([in, out, copy, cb]() {
+		const char* ext = copy.cod_format == GRK_JP2_FMT ? "jp2" : "j2k";
+		for(const std::string& name : list_dir(in.c_str()))
+		{
+			if(g_stop)
+				break;
+			EncodeJob job;
+			job.in = in + "/" + name;
+			job.out = out + "/" + replace_ext(name, ext);
+			encode_one(&copy, job, next_device(), cb);
+		}
+		g_batch_done = true;
+	});
+	return 0;
+}
+
+PLUGIN_EXPORT bool plugin_is_batch_complete(void)
+{
+	return g_batch_done;
+}
+PLUGIN_EXPORT void plugin_stop_batch_encode(void)
+{
+	g_stop = true; // async-signal tolerant: a flag only (grk_compress.cpp:79-82)
+}
+
+// ---- decode ------------------------------------------------------------------------------------
+
+PLUGIN_EXPORT int32_t plugin_decompress(grk_decompress_parameters* params,
+										 grk::PLUGIN_DECODE_USER_CALLBACK cb)
+{
+	if(!params || !cb)
+		return -1;
+	return decode_one(params, params->infile, params->outfile, next_device(), cb);
+}
+
+namespace
+{
+std::string g_dec_in, g_dec_out;
+grk_decompress_parameters* g_dec_params = nullptr;
+grk::PLUGIN_DECODE_USER_CALLBACK g_dec_cb = nullptr;
+} // namespace
+
+PLUGIN_EXPORT int32_t plugin_init_batch_decompress(const char* input_dir, const char* output_dir,
+													grk_decompress_parameters* params,
+													grk::PLUGIN_DECODE_USER_CALLBACK cb)
+{
+	if(!input_dir || !output_dir || !params || !cb)
+		return -1;
+	g_dec_in = input_dir;
+	g_dec_out = output_dir;
+	g_dec_params = params;
+	g_dec_cb = cb;
+	return 0;
+}
+
+PLUGIN_EXPORT int32_t plugin_batch_decompress(void)
+{
+	if(!g_dec_cb)
+		return -1;
+	join_batch();
+	g_batch_done = false;
+	g_batch_thread = std::thread([]() {
+		for(const std::string& name : list_dir(g_dec_in.c_str()))
+		{
+			if(g_stop)
+				break;
+			decode_one(g_dec_params, g_dec_in + "/" + name, g_dec_out + "/" + replace_ext(name, "ppm"),
+					   next_device(), g_dec_cb);
+		}
+		g_batch_done = true;
+	});
+	return 0;
+}
+
+PLUGIN_EXPORT void plugin_stop_batch_decompress(void)
+{
+	g_stop = true;
+}

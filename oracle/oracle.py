@@ -59,7 +59,8 @@ def have_ref():
 def ref():
     global _REF
     if _REF is None:
-        _REF = C.CDLL(os.path.join(HERE, "_ref", "libgrok_ref.so"))
+        # RTLD_GLOBAL: a plugin dlopen'ed by the reference resolves grk_image_new etc. from it
+        _REF = C.CDLL(os.path.join(HERE, "_ref", "libgrok_ref.so"), mode=C.RTLD_GLOBAL)
         _REF.ref_t1_encode.restype = C.c_double
         _REF.ref_stride.restype = C.c_uint32
     return _REF
@@ -253,6 +254,63 @@ def ref_codec_decode(cs, ncomp, w, h, threads=0, want_planes=True):
                                 C.c_uint32(ncomp), C.c_uint32(w), C.c_uint32(h))
     if rc != 0:
         raise RuntimeError("reference decoder failed (%d)" % rc)
+    return planes
+
+
+# ---------------------------------------------------------------- reference host + our plugin
+
+PLUGIN_DIR = os.path.join(os.path.dirname(HERE), "grok_b200", "plugin", "_build")
+
+
+def ref_set_rate(ratio):
+    """compression ratio of the single layer for the following reference encodes (0: lossless /
+    all passes, no rate control)"""
+    ref().ref_set_rate(C.c_double(ratio))
+
+
+def have_plugin():
+    return have_ref() and os.path.exists(os.path.join(PLUGIN_DIR, "libgrokj2k_plugin.so"))
+
+
+def ref_plugin_open(device=0, threads=0):
+    """grk_plugin_load + grk_plugin_init of the reference host on grok_b200/plugin/_build"""
+    rc = ref().ref_plugin_open(PLUGIN_DIR.encode(), C.c_int(device), C.c_uint32(threads))
+    if rc != 0:
+        raise RuntimeError("reference host could not load/initialise the plugin (%d)" % rc)
+
+
+def write_pnm(path, planes, prec):
+    """binary PGM/PPM (big-endian 16 bit above 8 bits) of 1 or 3 int planes"""
+    a = np.stack([np.asarray(p) for p in planes], axis=-1)
+    h, w, nc = a.shape
+    assert nc in (1, 3)
+    with open(path, "wb") as f:
+        f.write(b"P%d\n%d %d\n%d\n" % (6 if nc == 3 else 5, w, h, (1 << prec) - 1))
+        f.write(a.astype(">u2" if prec > 8 else "u1").tobytes())
+
+
+def ref_plugin_encode(pnm_path, w, h, ncomp, irreversible, ht=False, numres=6, cblk=(64, 64),
+                      threads=0):
+    """stock host (rate allocation, T2, markers) + our plugin (everything before T2)"""
+    cap = w * h * ncomp * 4 + (1 << 20)
+    out = np.zeros(cap, dtype=np.uint8)
+    fn = ref().ref_plugin_encode
+    fn.restype = C.c_long
+    n = fn(pnm_path.encode(), C.c_int(int(irreversible)), C.c_int(int(ht)), C.c_uint32(numres),
+           C.c_uint32(cblk[0]), C.c_uint32(cblk[1]), C.c_uint32(threads), _p(out), C.c_size_t(cap))
+    if n < 0:
+        raise RuntimeError("plugin-driven encode failed (%d)" % n)
+    return out[:n].copy()
+
+
+def ref_plugin_decode(j2k_path, ncomp, w, h):
+    """stock host (markers, T2) + our plugin (T1, dequantisation, wavelet, MCT)"""
+    planes = [np.zeros((h, w), dtype=np.int32) for _ in range(ncomp)]
+    ptrs = (C.c_void_p * ncomp)(*[p.ctypes.data for p in planes])
+    rc = ref().ref_plugin_decode(j2k_path.encode(), ptrs, C.c_uint32(ncomp), C.c_uint32(w),
+                                 C.c_uint32(h))
+    if rc != 0:
+        raise RuntimeError("plugin-driven decode failed (%d)" % rc)
     return planes
 
 

@@ -442,6 +442,14 @@ extern "C" {
 /* planes: numcomps dense w*h int32 planes. Returns codestream length, or -1.
  * Mirrors what grk_compress does after argument parsing (src/bin/jp2/grk_compress.cpp:
  * 820-828 lossless/all-pass default, :1978-1981 MCT default, :1123-1124 HT guard bits). */
+/* compression ratio of the single quality layer for the next encodes (-r of grk_compress);
+ * 0 = no rate limit: all passes, no rate control */
+static double g_layer_rate = 0;
+void ref_set_rate(double ratio)
+{
+	g_layer_rate = ratio;
+}
+
 long ref_codec_encode(int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t h, uint32_t prec,
 					  int irreversible, int ht, uint32_t numres, uint32_t cblkw, uint32_t cblkh,
 					  uint32_t tile_w, uint32_t tile_h, uint32_t numthreads, uint8_t* out,
@@ -455,7 +463,7 @@ long ref_codec_encode(int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t 
 	p.cblockw_init = cblkw;
 	p.cblockh_init = cblkh;
 	p.irreversible = irreversible != 0;
-	p.layer_rate[0] = 0;
+	p.layer_rate[0] = g_layer_rate;
 	p.numlayers = 1;
 	p.allocationByRateDistoration = true;
 	p.mct = numcomps >= 3 ? 1 : 0;
@@ -549,5 +557,196 @@ int ref_codec_decode(uint8_t* cs, size_t len, uint32_t numthreads, int32_t** pla
 		grk_object_unref(codec);
 	grk_object_unref(stream);
 	return rc;
+}
+
+/* ---- plugin drivers: what grk_compress / grk_decompress do around a loaded plugin -------------
+ * (src/bin/jp2/grk_compress.cpp:1742-2160 pluginCompressCallback, grk_decompress.cpp:996-1300
+ * decompress_callback), reduced to memory streams.  Only the public API of grok.h is used; the
+ * stock grk_decompress binary cannot drive a plugin decode in this snapshot (user_data is not
+ * forwarded, grok.cpp:740-753), hence this driver. */
+static uint8_t* g_enc_out = nullptr;
+static size_t g_enc_cap = 0;
+static long g_enc_len = -1;
+
+static bool plugin_enc_cb(grk_plugin_compress_user_callback_info* info)
+{
+	g_enc_len = -1;
+	if(!info || !info->image || !info->tile)
+		return false;
+	auto stream = grk_stream_create_mem_stream(g_enc_out, g_enc_cap, false, false);
+	auto codec = stream ? grk_compress_create(GRK_CODEC_J2K, stream) : nullptr;
+	if(codec && grk_compress_init(codec, info->compressor_parameters, info->image) &&
+	   grk_compress_start(codec) && grk_compress_with_plugin(codec, info->tile) &&
+	   grk_compress_end(codec))
+		g_enc_len = (long)grk_stream_get_write_mem_stream_length(stream);
+	if(codec)
+		grk_object_unref(codec);
+	if(stream)
+		grk_object_unref(stream);
+	return g_enc_len >= 0;
+}
+
+static bool g_plugin_ready = false;
+int ref_plugin_open(const char* plugin_dir, int device, uint32_t numthreads)
+{
+	if(g_plugin_ready)
+		return 0;
+	grk_initialize(nullptr, numthreads);
+	if(getenv("GRKB_PLUGIN_VERBOSE"))
+	{
+		auto pr = [](const char* msg, void*) { fprintf(stderr, "[ref host] %s\n", msg); };
+		grk_set_warning_handler(pr, nullptr);
+		grk_set_error_handler(pr, nullptr);
+	}
+	grk_plugin_load_info li;
+	li.pluginPath = plugin_dir;
+	if(!grk_plugin_load(li))
+		return -1;
+	grk_plugin_init_info ii;
+	ii.deviceId = device;
+	ii.verbose = getenv("GRKB_PLUGIN_VERBOSE") != nullptr;
+	if(!grk_plugin_init(ii))
+		return -2;
+	g_plugin_ready = true;
+	return 0;
+}
+
+/* infile: binary PNM; parameters as ref_codec_encode.  Returns the codestream length or < 0. */
+long ref_plugin_encode(const char* infile, int irreversible, int ht, uint32_t numres, uint32_t cblkw,
+					   uint32_t cblkh, uint32_t numthreads, uint8_t* out, size_t out_cap)
+{
+	if(!g_plugin_ready)
+		return -10;
+	grk_cparameters p;
+	grk_compress_set_default_params(&p);
+	p.cod_format = GRK_J2K_FMT;
+	p.decod_format = GRK_PXM_FMT;
+	strncpy(p.infile, infile, sizeof(p.infile) - 1);
+	p.numresolution = (uint8_t)numres;
+	p.cblockw_init = cblkw;
+	p.cblockh_init = cblkh;
+	p.irreversible = irreversible != 0;
+	p.layer_rate[0] = g_layer_rate;
+	p.numlayers = 1;
+	p.allocationByRateDistoration = true;
+	p.mct = 255; /* decided from the image, like the CLI does */
+	p.numThreads = numthreads;
+	if(ht)
+	{
+		p.isHT = true;
+		p.numgbits = 1;
+		p.cblk_sty = GRK_CBLKSTY_HT;
+	}
+	g_enc_out = out;
+	g_enc_cap = out_cap;
+	g_enc_len = -1;
+	/* the CLI resolves mct = 255 inside its callback, before grk_compress_init */
+	struct Fix
+	{
+		static bool cb(grk_plugin_compress_user_callback_info* info)
+		{
+			if(info && info->image && info->compressor_parameters->mct == 255)
+				info->compressor_parameters->mct = info->image->numcomps >= 3 ? 1 : 0;
+			return plugin_enc_cb(info);
+		}
+	};
+	if(grk_plugin_compress(&p, Fix::cb) != 0)
+		return g_enc_len >= 0 ? g_enc_len : -11;
+	return g_enc_len;
+}
+
+static int32_t** g_dec_planes = nullptr;
+static uint32_t g_dec_nc = 0, g_dec_w = 0, g_dec_h = 0;
+static int g_dec_rc = -1;
+static grk_decompress_parameters g_dec_params;
+
+static int32_t plugin_dec_cb_impl(grk_plugin_decompress_callback_info* info);
+static int32_t plugin_dec_cb(grk_plugin_decompress_callback_info* info)
+{
+	const int32_t rc = plugin_dec_cb_impl(info);
+	if(getenv("GRKB_PLUGIN_VERBOSE"))
+		fprintf(stderr, "[ref driver] decode callback flags=0x%x rc=%d\n",
+				info ? info->decompress_flags : 0, rc);
+	return rc;
+}
+static int32_t plugin_dec_cb_impl(grk_plugin_decompress_callback_info* info)
+{
+	if(!info)
+		return -1;
+	if(info->decompress_flags & GRK_PLUGIN_DECODE_CLEAN)
+	{
+		if(info->codec)
+			grk_object_unref(info->codec);
+		if(info->stream)
+			grk_object_unref(info->stream);
+		info->codec = nullptr;
+		info->stream = nullptr;
+		return 0;
+	}
+	if(info->decompress_flags & GRK_DECODE_HEADER)
+	{
+		static std::vector<uint8_t> file;
+		file.clear();
+		if(FILE* f = fopen(info->input_file_name, "rb"))
+		{
+			uint8_t buf[65536];
+			size_t n;
+			while((n = fread(buf, 1, sizeof(buf), f)) > 0)
+				file.insert(file.end(), buf, buf + n);
+			fclose(f);
+		}
+		info->stream = file.empty() ? nullptr
+									: grk_stream_create_mem_stream(file.data(), file.size(), false, true);
+		if(!info->stream)
+			return -1;
+		info->codec = grk_decompress_create(GRK_CODEC_J2K, info->stream);
+		if(!info->codec || !grk_decompress_init(info->codec, &g_dec_params.core) ||
+		   !grk_decompress_read_header(info->codec, &info->header_info))
+			return -1;
+		info->image = grk_decompress_get_composited_image(info->codec);
+		if(!info->image || !info->init_decompressors_func)
+			return -1;
+		return info->init_decompressors_func(&info->header_info, info->image);
+	}
+	if(info->decompress_flags & GRK_DECODE_T2)
+	{
+		if(!info->tile || !info->codec)
+			return -1;
+		info->tile->decompress_flags = info->decompress_flags;
+		return grk_decompress(info->codec, info->tile) ? 0 : -1;
+	}
+	if(info->decompress_flags & GRK_DECODE_POST_T1)
+	{
+		auto image = info->image;
+		if(!image || image->numcomps < g_dec_nc || image->comps[0].w != g_dec_w ||
+		   image->comps[0].h != g_dec_h)
+			return -1;
+		for(uint32_t c = 0; c < g_dec_nc; ++c)
+			for(uint32_t y = 0; y < g_dec_h; ++y)
+				memcpy(g_dec_planes[c] + (size_t)y * g_dec_w,
+					   image->comps[c].data + (size_t)y * image->comps[c].stride,
+					   sizeof(int32_t) * g_dec_w);
+		g_dec_rc = 0;
+		return 0;
+	}
+	return -1;
+}
+
+/* Decode of a .j2k file with T2 on the host and everything after it in the plugin. */
+int ref_plugin_decode(const char* infile, int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t h)
+{
+	if(!g_plugin_ready)
+		return -10;
+	memset(&g_dec_params, 0, sizeof(g_dec_params));
+	grk_decompress_set_default_params(&g_dec_params.core);
+	strncpy(g_dec_params.infile, infile, sizeof(g_dec_params.infile) - 1);
+	g_dec_params.decod_format = GRK_J2K_FMT;
+	g_dec_planes = planes;
+	g_dec_nc = numcomps;
+	g_dec_w = w;
+	g_dec_h = h;
+	g_dec_rc = -1;
+	const int rc = grk_plugin_decompress(&g_dec_params, plugin_dec_cb);
+	return rc ? rc : g_dec_rc;
 }
 }
