@@ -20,6 +20,7 @@
 #include <algorithm>
 #include <dirent.h>
 #include <dlfcn.h>
+#include <link.h>
 #include <memory>
 #include <stdarg.h>
 #include <stdio.h>
@@ -56,14 +57,45 @@ void logf(const char* fmt, ...)
 // ---- host services the plugin needs (the image object is a host-side C++ object) -------------
 typedef grk_image* (*image_new_fn)(uint16_t, grk_image_cmptparm*, GRK_COLOR_SPACE, bool);
 typedef void (*unref_fn)(grk_object*);
+// The host library is already in the process (it dlopen'ed this plugin); it may have been loaded
+// RTLD_LOCAL (e.g. through ctypes), so every loaded object is asked, not just the global scope.
+void* find_host_symbol(const char* name)
+{
+	if(void* p = dlsym(RTLD_DEFAULT, name))
+		return p;
+	struct Ctx
+	{
+		const char* name;
+		void* sym;
+	} ctx{name, nullptr};
+	dl_iterate_phdr(
+		[](dl_phdr_info* info, size_t, void* data) -> int {
+			Ctx* c = (Ctx*)data;
+			if(!info->dlpi_name || !*info->dlpi_name)
+				return 0;
+			if(void* h = dlopen(info->dlpi_name, RTLD_LAZY | RTLD_NOLOAD))
+			{
+				void* s = dlsym(h, c->name);
+				dlclose(h);
+				if(s)
+				{
+					c->sym = s;
+					return 1;
+				}
+			}
+			return 0;
+		},
+		&ctx);
+	return ctx.sym;
+}
 image_new_fn host_image_new()
 {
-	static image_new_fn f = (image_new_fn)dlsym(RTLD_DEFAULT, "grk_image_new");
+	static image_new_fn f = (image_new_fn)find_host_symbol("grk_image_new");
 	return f;
 }
 unref_fn host_unref()
 {
-	static unref_fn f = (unref_fn)dlsym(RTLD_DEFAULT, "grk_object_unref");
+	static unref_fn f = (unref_fn)find_host_symbol("grk_object_unref");
 	return f;
 }
 

@@ -59,8 +59,7 @@ def have_ref():
 def ref():
     global _REF
     if _REF is None:
-        # RTLD_GLOBAL: a plugin dlopen'ed by the reference resolves grk_image_new etc. from it
-        _REF = C.CDLL(os.path.join(HERE, "_ref", "libgrok_ref.so"), mode=C.RTLD_GLOBAL)
+        _REF = C.CDLL(os.path.join(HERE, "_ref", "libgrok_ref.so"))
         _REF.ref_t1_encode.restype = C.c_double
         _REF.ref_stride.restype = C.c_uint32
     return _REF
