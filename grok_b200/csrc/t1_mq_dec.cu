@@ -17,6 +17,7 @@
 // Warps pull blocks from a global work counter, longest blocks first.  Not HBM-bound: traffic
 // is the compressed bytes in and 4 B/sample out; the bound is the serial decision rate.
 #include "t1.cuh"
+#include <stdlib.h>
 
 namespace
 {
@@ -492,10 +493,28 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 }
 } // namespace
 
+int grkb_launch_t1_mq_decode_simt(const T1Launch& l, cudaStream_t s);
+
 int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 {
 	if(l.nblocks == 0)
 		return 0;
+	// GRKB_T1_MQ_KERNEL=simt selects the one-block-per-lane kernel of t1_mq_dec_simt.cu (same
+	// results; measured 3.5x slower on 64x64 blocks, where its 2.4 KB of state per lane leave
+	// room for only two warps per SM -- see DESIGN.md section 4); the default is this file's
+	// one-block-per-warp kernel
+	static int simt = -1;
+	if(simt < 0)
+	{
+		const char* e = getenv("GRKB_T1_MQ_KERNEL");
+		simt = (e && e[0] == 's') ? 1 : 0;
+	}
+	if(simt)
+	{
+		const int rc = grkb_launch_t1_mq_decode_simt(l, s);
+		if(rc <= 0)
+			return rc;
+	}
 	const T1Tables* tab = grkb_t1_tables_device();
 	if(!tab)
 	{

@@ -156,3 +156,18 @@ def test_tile_decode_matches_reference_codec_golden(gpu, orc):
         got = dec.decode(tile["blocks"], tile["segs"], tile["data"])
         dec.close()
         assert np.array_equal(np.stack(got), e["decoded_%d" % k]), k
+
+
+def test_simt_kernel_same_results(gpu):
+    """the one-block-per-lane MQ decoder (t1_mq_dec_simt.cu, GRKB_T1_MQ_KERNEL=simt) passes the
+    same parity tests; the kernel choice is read once per process, hence the subprocess"""
+    import subprocess
+    import sys
+    if os.environ.get("GRKB_T1_MQ_KERNEL") == "simt":
+        pytest.skip("already running under the SIMT kernel")
+    env = dict(os.environ, GRKB_T1_MQ_KERNEL="simt")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu",
+                        "-k", "golden or all_modes or arbitrary or tile_decode_matches_oracle"],
+                       env=env, capture_output=True, text=True, timeout=600,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
