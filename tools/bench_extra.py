@@ -1,0 +1,207 @@
+#!/usr/bin/env python3
+"""Measurements beside bench.py's headline line, for the other BASELINE configs (one JSON line each,
+kept under profiles/):
+
+  ht_encode   configs[2], encode half: 4096x2160 12-bit RGB -> HTJ2K lossless code blocks
+              (DC shift + RCT + 5/3 + HT cleanup encode + packing), device-resident and end to end
+              (H2D of the image, D2H of block table + coded bytes), stock CPU encoder beside it.
+  tiled       configs[3]: 8192x8192 16-bit RGB, 1024x1024 tiles, HTJ2K lossless decode; the 64 tiles
+              are independent units: round-robin over the ranks' GPUs (shard.shard_units) and,
+              inside a GPU, over a few decoders kept in flight (grkb_decoder_submit / wait).
+
+usage: python tools/bench_extra.py ht_encode|tiled [--steps K] [--inflight N] [--size S]
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def synth(w, h, prec, seed):
+    """low-pass 'natural-like' field (sum of random 2-D cosines, amplitude ~ 1/f) + noise"""
+    rng = np.random.default_rng(seed)
+    yy = np.arange(h, dtype=np.float32)[:, None]
+    xx = np.arange(w, dtype=np.float32)[None, :]
+    planes = []
+    for c in range(3):
+        f = np.zeros((h, w), np.float32)
+        for k in range(6):
+            fx, fy = rng.uniform(0.5, 24, size=2) / max(w, h)
+            f += np.cos(2 * np.pi * (fx * xx + fy * yy) + rng.uniform(0, 6.28)) / (1 + k)
+        f = (f - f.min()) / (f.max() - f.min())
+        v = f * ((1 << prec) - 1) + rng.standard_normal((h, w)).astype(np.float32) * (1 << max(prec - 10, 0))
+        planes.append(np.clip(np.rint(v), 0, (1 << prec) - 1).astype(np.int32))
+    return planes
+
+
+def ht_encode(args):
+    import grok_b200
+    from grok_b200 import encode as E, tile as T
+    from oracle import oracle as O
+    W, H, prec, nr = 4096, 2160, 12, 6
+    grok_b200._lib.check(grok_b200.lib.grkb_set_device(0), "grkb_set_device")
+    img = synth(W, H, prec, 4096)
+    params = T.tile_params(0, 0, W, H, 3, nr, 1, 1, prec)
+    blocks, geom, qcd = E.enc_block_table(0, 0, W, H, 3, nr, prec, 1, ht=True)
+    enc = E.TileEncoder(params)
+    pin = [T.PinnedArray((H, W), np.int32) for _ in range(3)]
+    for p, a in zip(pin, img):
+        p.array[:] = a
+    src = [p.array for p in pin]
+    n = len(blocks)
+    out = (T.PinnedArray((n,), T.CODED_DTYPE).array, T.PinnedArray((n, T.ENC_MAX_PASSES), T.PASS_DTYPE).array,
+           T.PinnedArray((W * H * 3 * 2,), np.uint8).array)
+    coded, passes, data = enc.encode(src, blocks, out=out)
+    assert not coded["failed"].any()
+    for _ in range(2):
+        enc.encode(src, blocks, out=out)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        coded, passes, data = enc.encode(src, blocks, out=out)
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    tm = enc.time_device(args.steps, 3)
+    # round trip through the GPU decoder: lossless
+    dblocks, dsegs = E.decode_table(blocks, coded, passes, geom, qcd, prec, 1, True)
+    dec = T.TileDecoder(params)
+    back = dec.decode(dblocks, dsegs, np.concatenate([data, np.zeros(16, np.uint8)]))
+    lossless = dec.rejected == 0 and all(np.array_equal(a, b) for a, b in zip(back, img))
+    cpu = None
+    if O.have_ref() and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        O.ref_codec_encode(img, prec, 0, ht=True, numres=nr, threads=threads)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            cs = O.ref_codec_encode(img, prec, 0, ht=True, numres=nr, threads=threads)
+        dt = (time.perf_counter() - t0) / 3
+        cpu = {"value": W * H / 1e6 / dt, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
+               "sample": "whole frame x3: stock grk compress (public C API, memory stream, T2 included), "
+                         "%.0f ms/frame, %d bytes" % (dt * 1e3, len(cs))}
+    mp = W * H / 1e6
+    print(json.dumps({
+        "metric": "encode_mpixels_per_s", "value": mp / (tm["total_ms"] * 1e-3), "unit": "Mpixel/s",
+        "n_gpus": 1, "steps": args.steps, "ms_per_step": tm["total_ms"], "dtype": "i32", "data": "synthetic",
+        "config": {"workload": "htj2k_encode_4096x2160_rgb12_53_rct_lossless_5lvl_cblk64_1tile",
+                   "code_blocks": int(n), "coded_bytes": int(len(data))},
+        "e2e": {"value": mp / (e2e_ms * 1e-3), "unit": "Mpixel/s", "ms_per_step": e2e_ms,
+                "h2d_bytes_per_step": int(W * H * 3 * 4 + blocks.nbytes),
+                "d2h_bytes_per_step": int(len(data) + coded.nbytes + passes.nbytes)},
+        "stages_ms": {"dc_rct_fdwt": tm["dwt_ms"], "t1_ht_encode_pack": tm["t1_ms"]},
+        "round_trip_lossless": bool(lossless), "cpu_baseline": cpu}), flush=True)
+
+
+def tiled(args):
+    import grok_b200
+    from grok_b200 import encode as E, shard, tile as T
+    from oracle import oracle as O
+    rank, local, world = shard.dist_env()
+    S, TS, prec, nr = args.size, 1024, 16, 6
+    grok_b200._lib.check(grok_b200.lib.grkb_set_device(local), "grkb_set_device")
+    img = synth(S, S, prec, 8192)
+    tiles = shard.tile_grid(0, 0, S, S, 0, 0, TS, TS)
+    mine = shard.shard_units(len(tiles), rank, world)
+    params = T.tile_params(0, 0, TS, TS, 3, nr, 1, 1, prec)
+    blocks, geom, qcd = E.enc_block_table(0, 0, TS, TS, 3, nr, prec, 1, ht=True)
+    # set-up (untimed): this rank's tiles are coded with the GPU encoder
+    enc = E.TileEncoder(params)
+    coded_tiles = []
+    for t in mine:
+        x0, y0, x1, y1 = tiles[t]
+        src = [np.ascontiguousarray(p[y0:y1, x0:x1]) for p in img]
+        coded, passes, data = enc.encode(src, blocks)
+        db, ds = E.decode_table(blocks, coded, passes, geom, qcd, prec, 1, True)
+        pool = T.PinnedArray((len(data) + 16,), np.uint8)
+        pool.array[:len(data)] = data
+        pool.array[len(data):] = 0
+        pb = T.PinnedArray((len(db),), T.CBLK_DTYPE)
+        pb.array[:] = db
+        ps = T.PinnedArray((len(ds),), T.SEG_DTYPE)
+        ps.array[:] = ds
+        coded_tiles.append((pb.array, ps.array, pool.array))
+    enc.close()
+    K = args.inflight
+    decs = [T.TileDecoder(params, len(blocks), 1 << 22) for _ in range(K)]
+    outs = [[T.PinnedArray((TS, TS), np.int32) for _ in range(3)] for _ in range(K)]
+    result = [np.zeros((S, S), np.int32) for _ in range(3)] if args.verify else None
+
+    def one_pass(verify):
+        pending = [None] * K
+        for i, t in enumerate(range(len(mine))):
+            k = i % K
+            if pending[k] is not None:
+                decs[k].wait()
+                if verify:
+                    shard.composite(result, [p.array for p in outs[k]], tiles[mine[pending[k]]])
+            b, s, d = coded_tiles[t]
+            decs[k].submit(b, s, d, [p.array for p in outs[k]])
+            pending[k] = t
+        for k in range(K):
+            if pending[k] is not None:
+                decs[k].wait()
+                if verify:
+                    shard.composite(result, [p.array for p in outs[k]], tiles[mine[pending[k]]])
+
+    one_pass(args.verify)
+    ok = True
+    if args.verify:
+        for t in mine:
+            x0, y0, x1, y1 = tiles[t]
+            ok = ok and all(np.array_equal(result[c][y0:y1, x0:x1], img[c][y0:y1, x0:x1]) for c in range(3))
+    one_pass(False)
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    shard.barrier(world)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        one_pass(False)
+    ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    ms = shard.max_over_ranks(ms, world, device="cuda" if world > 1 else None)
+    if rank != 0:
+        return
+    cpu = None
+    if O.have_ref() and not args.no_cpu and world == 1:
+        threads = os.cpu_count() or 1
+        cs = O.ref_codec_encode(img, prec, 0, ht=True, numres=nr, tile=(TS, TS), threads=threads)
+        t0 = time.perf_counter()
+        O.ref_codec_decode(cs, 3, S, S, threads=threads, want_planes=False)
+        dt = time.perf_counter() - t0
+        cpu = {"value": S * S / 1e6 / dt, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
+               "sample": "whole image x1: stock grk decompress of the %d-tile codestream (T2 included), "
+                         "%.0f ms" % (len(tiles), dt * 1e3)}
+    nbytes = sum(int(d.size) for _, _, d in coded_tiles)
+    print(json.dumps({
+        "metric": "decode_mpixels_per_s", "value": S * S / 1e6 / (ms * 1e-3), "unit": "Mpixel/s",
+        "n_gpus": world, "steps": args.steps, "ms_per_step": ms, "scaling": "strong", "dtype": "i32",
+        "data": "synthetic", "timed": "end to end: H2D of descriptors + coded bytes, decode, D2H of int32 planes",
+        "config": {"workload": "htj2k_decode_%dx%d_rgb16_53_rct_lossless_5lvl_cblk64_tiles1024" % (S, S),
+                   "tiles": len(tiles), "tiles_per_rank": len(mine), "decoders_in_flight": K,
+                   "coded_bytes_this_rank": nbytes, "sharding": "tile t -> rank t mod N, no collective"},
+        "lossless": bool(ok) if args.verify else None, "cpu_baseline": cpu}), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("what", choices=["ht_encode", "tiled"])
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--inflight", type=int, default=4)
+    ap.add_argument("--size", type=int, default=8192)
+    ap.add_argument("--verify", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    (ht_encode if args.what == "ht_encode" else tiled)(args)
+
+
+if __name__ == "__main__":
+    main()
