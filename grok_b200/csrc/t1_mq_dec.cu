@@ -1,5 +1,5 @@
 // t1_mq_dec.cu -- EBCOT (JPEG 2000 Part 1) code-block decoder with dequantisation fused into
-// the store, sm_100a.  One code block per warp.
+// the store, sm_100a.  One code block per warp, the MQ decoder replicated in every lane.
 //
 // Replaces, behind the C-ABI, the reference's
 //   T1Part1::decompress            src/lib/jp2/t1/t1_part1/T1Part1.cpp:133-161
@@ -8,22 +8,33 @@
 //   ShiftFilter / ScaleFilter / Roi* src/lib/jp2/filters/PostDecompressFilters.h:7-89
 //
 // Shape: the MQ decoder is one serial dependency chain per block (every decision depends on
-// a, c, ct and the adapted state of its context), so parallelism is across blocks.  A warp
-// owns a block: all lanes clear and later dequantise + store the block (coalesced rows into
-// the Mallat coefficient plane); lane 0 walks the coding passes over a shared-memory state
-// array (one word per stripe column, layout in t1.cuh); samples are written straight into
-// the block's rectangle of the (L2-resident) plane: a store when a sample becomes significant,
-// a fire-and-forget red.add per refinement bit (the sign is kept in the state word).
-// Warps pull blocks from a global work counter, longest blocks first.  Not HBM-bound: traffic
-// is the compressed bytes in and 4 B/sample out; the bound is the serial decision rate.
+// a, c, ct and the adapted state of its context), so parallelism is across blocks and the
+// kernel is bound by warp instructions per decision, not by memory.  A warp owns a block and
+// all 32 lanes run the SAME decision chain on identical register copies of the coder state
+// (an instruction costs one issue slot whether one lane or 32 execute it, and identical
+// values never diverge).  What that buys: a 4-row stripe is walked in segments of 32 columns
+// with lane l holding the state word of column l in a register, so everything that does not
+// depend on the decision just decoded runs 32 columns at a time --
+//   * which columns / rows have anything to code in this pass (one ballot per segment; empty
+//     columns and rows cost nothing in the serial chain),
+//   * the refinement pass's contexts (they are fixed before the pass starts) and its sample
+//     updates (each lane applies the decoded bits to its own column, coalesced, no atomics),
+//   * neighbour updates when a sample becomes significant (the three lanes concerned update
+//     their registers; rows above / below are touched by three lanes at once),
+// and the serial chain is left with: pick the next (column, row), one table look-up for the
+// context, the MQ decision itself.  Samples live in the block's rectangle of the (L2-resident)
+// Mallat coefficient plane.  Warps pull blocks from a global work counter, longest first.
 #include "t1.cuh"
 #include <stdlib.h>
 
 namespace
 {
+constexpr uint32_t FULL = 0xffffffffu;
+
 struct Mq
 {
-	uint32_t a, c, ct;
+	uint32_t a; // the A register in the upper half (A << 16): "A < 0x8000" is a sign test
+	uint32_t c, ct;
 	const uint8_t* p; // segment bytes
 	uint32_t len, pos;
 	uint32_t cur, nxt; // bytes at pos and pos+1 (0xFF past the end: mqc_dec.cpp:78-90)
@@ -69,7 +80,7 @@ static __device__ __forceinline__ void mq_init(Mq& q, const uint8_t* p, uint32_t
 	mq_bytein(q);
 	q.c <<= 7;
 	q.ct -= 7;
-	q.a = 0x8000;
+	q.a = 0x80000000u;
 }
 
 static __device__ __forceinline__ void raw_init(Mq& q, const uint8_t* p, uint32_t len)
@@ -115,7 +126,7 @@ static __device__ __forceinline__ uint32_t raw_decode(Mq& q)
 // renorm_dec_macro (mqc_dec_inl.h:111-121) with the shifts batched between byte fetches
 static __device__ __forceinline__ void mq_renorm(Mq& q)
 {
-	uint32_t n = __clz(q.a) - 16; // shifts until bit 15 of a is set
+	uint32_t n = __clz(q.a); // shifts until the top bit of A is set
 	while(n)
 	{
 		if(q.ct == 0)
@@ -128,55 +139,62 @@ static __device__ __forceinline__ void mq_renorm(Mq& q)
 	}
 }
 
-// decompress_macro, mqc_dec_inl.h:134-158
-static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint8_t* cxs, const uint32_t* mqt,
-													  uint32_t cx)
+// decompress_macro, mqc_dec_inl.h:134-158.  cxs[] holds, per context, the table entry of its
+// current state (Qe | next-if-MPS << 16 | next-if-LPS << 24 | MPS << 31), so the common path is
+// one shared-memory read; cx4 is the context number times four.
+static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t* cxs, const uint32_t* mqt,
+													  uint32_t cx4)
 {
-	uint32_t st = cxs[cx];
-	const uint32_t e = mqt[st];
-	const uint32_t qe = e & 0xFFFFu;
-	uint32_t d = st & 1u;
+	uint32_t* slot = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(cxs) + cx4);
+	const uint32_t e = *slot;
+	const uint32_t qe = e << 16;
+	uint32_t d = e >> 31;
 	q.a -= qe;
-	if(q.c < (qe << 16))
+	if(q.c < qe)
 	{
+		uint32_t st;
 		if(q.a < qe)
-			st = (e >> 16) & 0xFFu;
+			st = (e >> 16) & 0x7Fu;
 		else
 		{
 			d ^= 1u;
-			st = e >> 24;
+			st = (e >> 24) & 0x7Fu;
 		}
 		q.a = qe;
-		cxs[cx] = (uint8_t)st;
+		*slot = mqt[st];
 		mq_renorm(q);
 	}
 	else
 	{
-		q.c -= qe << 16;
-		if(q.a < 0x8000u)
+		q.c -= qe;
+		if((int32_t)q.a >= 0)
 		{
+			uint32_t st;
 			if(q.a < qe)
 			{
 				d ^= 1u;
-				st = e >> 24;
+				st = (e >> 24) & 0x7Fu;
 			}
 			else
-				st = (e >> 16) & 0xFFu;
-			cxs[cx] = (uint8_t)st;
+				st = (e >> 16) & 0x7Fu;
+			*slot = mqt[st];
 			mq_renorm(q);
 		}
 	}
 	return d;
 }
 
-static __device__ __forceinline__ void reset_states(uint8_t* cxs)
+constexpr uint32_t CX4_MAG = T1_CTX_MAG * 4, CX4_AGG = T1_CTX_AGG * 4, CX4_UNI = T1_CTX_UNI * 4;
+
+static __device__ __forceinline__ void reset_states(uint32_t* cxs, const uint32_t* mqt, uint32_t lane)
 {
 	// mqc_resetstates, mqc_dec.cpp:121-130
-	for(int i = 0; i < T1_NCTX; ++i)
-		cxs[i] = 0;
-	cxs[T1_CTX_UNI] = 46 << 1;
-	cxs[T1_CTX_AGG] = 3 << 1;
-	cxs[T1_CTX_ZC] = 4 << 1;
+	if(lane < T1_NCTX)
+	{
+		const uint32_t st = lane == T1_CTX_UNI ? 46u << 1 : lane == T1_CTX_AGG ? 3u << 1 : lane == T1_CTX_ZC ? 4u << 1 : 0u;
+		cxs[lane] = mqt[st];
+	}
+	__syncwarp();
 }
 
 struct Blk
@@ -185,10 +203,25 @@ struct Blk
 	int32_t* data; // the block's rectangle in the coefficient plane (x2 fixed point until dequantised)
 	uint32_t ds; // row pitch of data
 	uint32_t w, h, fs; // fs = w + 2
-	const uint8_t* zc; // zero-coding table of this band orientation
-	const uint8_t* sc;
+	const uint8_t* zc; // zero-coding table of this band orientation (contexts x 4)
+	const uint8_t* sc; // sign-coding table (context x 4 | xor bit << 7)
 	bool vsc;
+	uint32_t lane;
 };
+
+// per-row 4-bit summaries of a state word
+static __device__ __forceinline__ uint32_t sig4(uint32_t f)
+{
+	return ((f >> 4) & 1u) | ((f >> 6) & 2u) | ((f >> 8) & 4u) | ((f >> 10) & 8u);
+}
+static __device__ __forceinline__ uint32_t nz4(uint32_t f)
+{
+	uint32_t m = 0;
+#pragma unroll
+	for(uint32_t r = 0; r < 4; ++r)
+		m |= ((f >> (3 * r)) & T1_NEIGH) ? 1u << r : 0u;
+	return m;
+}
 
 // index into the sign-coding table from the centre word f (row r) and its west/east words
 static __device__ __forceinline__ uint32_t sc_index(uint32_t f, uint32_t fw, uint32_t fe, uint32_t r)
@@ -203,192 +236,314 @@ static __device__ __forceinline__ uint32_t sc_index(uint32_t f, uint32_t fw, uin
 	return i;
 }
 
-// sample (x, stripe row r) became significant with sign sgn: propagate to the neighbours
-// (update_flags_macro, T1.cpp:209-233)
-static __device__ __forceinline__ void mark_significant(const Blk& b, uint32_t* fp, uint32_t& f,
-														 uint32_t r, uint32_t sgn)
+// One 32-column segment of a stripe: lane l holds the state word of column x0 + l in `f`.
+struct Seg
 {
-	f |= T1_SIG_C(r) | (sgn << (18 + r + 1));
-	fp[-1] |= 1u << (3 * (r + 1) + 2); // we are the east neighbour of the west column
-	fp[1] |= 1u << (3 * (r + 1)); // and the west neighbour of the east column
-	if(r == 0 && !b.vsc)
+	uint32_t* fseg; // state word of the segment's first column (this stripe)
+	int32_t* dseg; // sample of the segment's first column, stripe row 0
+};
+
+// state words of the west / east neighbours of segment column `col`, as of now
+static __device__ __forceinline__ void west_east(const Seg& g, uint32_t f, uint32_t col, uint32_t& fw,
+												   uint32_t& fe)
+{
+	fw = __shfl_sync(FULL, f, (col + 31u) & 31u);
+	fe = __shfl_sync(FULL, f, (col + 1u) & 31u);
+	if(col == 0 || col == 31)
 	{
-		uint32_t* n = fp - b.fs; // row 4 of the stripe above
-		n[0] |= (1u << 16) | (sgn << 23);
-		n[-1] |= 1u << 17;
-		n[1] |= 1u << 15;
-	}
-	if(r == 3)
-	{
-		uint32_t* s = fp + b.fs; // row -1 of the stripe below
-		s[0] |= (1u << 1) | (sgn << 18);
-		s[-1] |= 1u << 2;
-		s[1] |= 1u << 0;
+		__syncwarp(); // the word may have been updated by another lane
+		if(col == 0)
+			fw = g.fseg[-1];
+		else
+			fe = g.fseg[32];
 	}
 }
 
+// sample (segment column col, stripe row r) became significant with sign sgn and value val:
+// propagate to the neighbours (update_flags_macro, T1.cpp:209-233).  All lanes call this.
+static __device__ __forceinline__ void mark_significant(const Blk& b, const Seg& g, uint32_t& f,
+														 uint32_t col, uint32_t r, uint32_t sgn,
+														 int32_t val)
+{
+	const uint32_t lane = b.lane;
+	if(lane == col)
+	{
+		f |= T1_SIG_C(r) | (sgn << (18 + r + 1));
+		g.dseg[lane + r * b.ds] = val;
+	}
+	else if(lane + 1 == col)
+		f |= 4u << (3 * (r + 1)); // we are the east neighbour of the west column
+	else if(lane == col + 1)
+		f |= 1u << (3 * (r + 1)); // and the west neighbour of the east column
+	// columns outside the segment are in shared memory
+	if(col == 0)
+	{
+		if(lane == 0)
+			g.fseg[-1] |= 4u << (3 * (r + 1));
+	}
+	else if(col == 31)
+	{
+		if(lane == 31)
+			g.fseg[32] |= 1u << (3 * (r + 1));
+	}
+	// rows of the stripes above / below: lanes 0..2 take columns col-1, col, col+1
+	if(r == 0 && !b.vsc)
+	{
+		__syncwarp(); // successive events update overlapping words from different lanes
+		if(lane < 3)
+		{
+			uint32_t* n = g.fseg - b.fs + col + lane - 1; // row 4 of the stripe above
+			*n |= lane == 1 ? ((1u << 16) | (sgn << 23)) : lane == 0 ? (1u << 17) : (1u << 15);
+		}
+	}
+	else if(r == 3)
+	{
+		__syncwarp();
+		if(lane < 3)
+		{
+			uint32_t* s = g.fseg + b.fs + col + lane - 1; // row -1 of the stripe below
+			*s |= lane == 1 ? ((1u << 1) | (sgn << 18)) : lane == 0 ? (1u << 2) : (1u << 0);
+		}
+	}
+}
+
+// sign of a newly significant sample (T1.cpp dec_*pass "sign" step) + the bookkeeping
+template<bool RAW>
+static __device__ __forceinline__ void code_sign(const Blk& b, const Seg& g, Mq& q, uint32_t* cxs,
+												  const uint32_t* mqt, uint32_t& f, uint32_t& fc,
+												  uint32_t col, uint32_t r, int32_t oph)
+{
+	uint32_t v;
+	if(RAW)
+		v = raw_decode(q);
+	else
+	{
+		uint32_t fw, fe;
+		west_east(g, f, col, fw, fe);
+		const uint32_t e = b.sc[sc_index(fc, fw, fe, r)];
+		v = mq_decode(q, cxs, mqt, e & 0x7Fu) ^ (e >> 7);
+	}
+	mark_significant(b, g, f, col, r, v, v ? -oph : oph);
+	fc |= T1_SIG_C(r) | (v << (18 + r + 1));
+}
+
 // dec_clnpass, T1.cpp:934-1093
-static __device__ void cleanup_pass(const Blk& b, Mq& q, uint8_t* cxs, const uint32_t* mqt,
+static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t* cxs, const uint32_t* mqt,
 									 int bpno_plus_one, bool segsym)
 {
 	const int32_t one = 1 << bpno_plus_one, oph = one | (one >> 1);
 	for(uint32_t k = 0, s = 0; k < b.h; k += 4, ++s)
 	{
-		const uint32_t rows = min(4u, b.h - k);
-		uint32_t* fp = b.fl + (s + 1) * b.fs + 1;
-		int32_t* dp = b.data + (size_t)k * b.ds;
-		for(uint32_t x = 0; x < b.w; ++x, ++fp, ++dp)
+		const uint32_t rows = min(4u, b.h - k), rowmask = (1u << rows) - 1u;
+		for(uint32_t x0 = 0; x0 < b.w; x0 += 32)
 		{
-			uint32_t f = *fp;
-			uint32_t r = 0;
-			bool sign_only = false;
-			if(rows == 4 && f == 0)
+			Seg g;
+			g.fseg = b.fl + (s + 1) * b.fs + 1 + x0;
+			g.dseg = b.data + (size_t)k * b.ds + x0;
+			const bool act = x0 + b.lane < b.w;
+			__syncwarp();
+			uint32_t f = act ? g.fseg[b.lane] : 0u;
+			// rows still to code: not significant, not visited in this bit-plane
+			const uint32_t todo = act ? ~(sig4(f) | (f >> 24)) & rowmask : 0u;
+			uint32_t colmask = __ballot_sync(FULL, todo != 0);
+			while(colmask)
 			{
-				if(!mq_decode(q, cxs, mqt, T1_CTX_AGG))
-					continue;
-				r = mq_decode(q, cxs, mqt, T1_CTX_UNI);
-				r = (r << 1) | mq_decode(q, cxs, mqt, T1_CTX_UNI);
-				sign_only = true;
-			}
-			for(; r < rows; ++r)
-			{
-				if(!sign_only)
+				const uint32_t col = __ffs(colmask) - 1;
+				colmask &= colmask - 1;
+				uint32_t m = __shfl_sync(FULL, todo, col);
+				uint32_t fc = __shfl_sync(FULL, f, col);
+				bool sign_only = false;
+				if(rows == 4 && fc == 0)
 				{
-					if(f & (T1_SIG_C(r) | T1_PI(r)))
+					if(!mq_decode(q, cxs, mqt, CX4_AGG))
 						continue;
-					if(!mq_decode(q, cxs, mqt, b.zc[(f >> (3 * r)) & T1_NEIGH]))
-						continue;
+					uint32_t r = mq_decode(q, cxs, mqt, CX4_UNI);
+					r = (r << 1) | mq_decode(q, cxs, mqt, CX4_UNI);
+					m = (0xFu << r) & 0xFu;
+					sign_only = true;
 				}
-				sign_only = false;
-				const uint32_t e = b.sc[sc_index(f, fp[-1], fp[1], r)];
-				const uint32_t v = mq_decode(q, cxs, mqt, e & 0x7Fu) ^ (e >> 7);
-				dp[r * b.ds] = v ? -oph : oph;
-				mark_significant(b, fp, f, r, v);
+				while(m)
+				{
+					const uint32_t r = __ffs(m) - 1;
+					m &= m - 1;
+					if(!sign_only && !mq_decode(q, cxs, mqt, b.zc[(fc >> (3 * r)) & T1_NEIGH]))
+						continue;
+					sign_only = false;
+					code_sign<false>(b, g, q, cxs, mqt, f, fc, col, r, oph);
+				}
 			}
-			*fp = f & ~T1_PI_ALL;
+			if(act)
+				g.fseg[b.lane] = f & ~T1_PI_ALL;
 		}
 	}
 	if(segsym)
 	{
 		// dec_clnpass_check_segsym, T1.cpp:1053-1073: the four decisions are consumed
 		for(int i = 0; i < 4; ++i)
-			(void)mq_decode(q, cxs, mqt, T1_CTX_UNI);
+			(void)mq_decode(q, cxs, mqt, CX4_UNI);
 	}
 }
 
 // dec_sigpass_mqc / dec_sigpass_raw, T1.cpp:1094-1245
 template<bool RAW>
-static __device__ void sig_pass(const Blk& b, Mq& q, uint8_t* cxs, const uint32_t* mqt,
+static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t* cxs, const uint32_t* mqt,
 								 int bpno_plus_one)
 {
 	const int32_t one = 1 << bpno_plus_one, oph = one | (one >> 1);
 	for(uint32_t k = 0, s = 0; k < b.h; k += 4, ++s)
 	{
-		const uint32_t rows = min(4u, b.h - k);
-		uint32_t* fp = b.fl + (s + 1) * b.fs + 1;
-		int32_t* dp = b.data + (size_t)k * b.ds;
-		for(uint32_t x = 0; x < b.w; ++x, ++fp, ++dp)
+		const uint32_t rows = min(4u, b.h - k), rowmask = (1u << rows) - 1u;
+		for(uint32_t x0 = 0; x0 < b.w; x0 += 32)
 		{
-			uint32_t f = *fp;
-			if(f == 0)
-				continue;
-			for(uint32_t r = 0; r < rows; ++r)
+			Seg g;
+			g.fseg = b.fl + (s + 1) * b.fs + 1 + x0;
+			g.dseg = b.data + (size_t)k * b.ds + x0;
+			const bool act = x0 + b.lane < b.w;
+			__syncwarp();
+			uint32_t f = act ? g.fseg[b.lane] : 0u;
+			// free = not significant and not visited; a free row is coded in this pass as soon
+			// as it has a significant neighbour -- which can happen during the pass
+			const uint32_t fr = act ? ~(sig4(f) | (f >> 24)) & rowmask : 0u;
+			uint32_t cand = fr & nz4(f);
+			uint32_t colmask = __ballot_sync(FULL, cand != 0);
+			while(colmask)
 			{
-				if((f & (T1_SIG_C(r) | T1_PI(r))) || !((f >> (3 * r)) & T1_NEIGH))
-					continue;
-				if(RAW)
+				const uint32_t col = __ffs(colmask) - 1;
+				colmask &= colmask - 1;
+				uint32_t m = __shfl_sync(FULL, cand, col);
+				const uint32_t frc = __shfl_sync(FULL, fr, col);
+				uint32_t fc = __shfl_sync(FULL, f, col);
+				uint32_t pi = 0, grown = 0;
+				while(m)
 				{
-					if(raw_decode(q))
-					{
-						const uint32_t v = raw_decode(q);
-						dp[r * b.ds] = v ? -oph : oph;
-						mark_significant(b, fp, f, r, v);
-					}
+					const uint32_t r = __ffs(m) - 1;
+					m &= m - 1;
+					pi |= 1u << r;
+					const uint32_t bit = RAW ? raw_decode(q)
+											 : mq_decode(q, cxs, mqt, b.zc[(fc >> (3 * r)) & T1_NEIGH]);
+					if(!bit)
+						continue;
+					code_sign<RAW>(b, g, q, cxs, mqt, f, fc, col, r, oph);
+					m |= (2u << r) & frc; // the row below becomes a candidate
+					grown |= (7u << r) >> 1; // and rows r-1..r+1 of the next column
 				}
-				else if(mq_decode(q, cxs, mqt, b.zc[(f >> (3 * r)) & T1_NEIGH]))
+				if(b.lane == col)
+					f |= pi << 24;
+				if(grown)
 				{
-					const uint32_t e = b.sc[sc_index(f, fp[-1], fp[1], r)];
-					const uint32_t v = mq_decode(q, cxs, mqt, e & 0x7Fu) ^ (e >> 7);
-					dp[r * b.ds] = v ? -oph : oph;
-					mark_significant(b, fp, f, r, v);
+					if(b.lane == col + 1)
+						cand |= grown & fr;
+					colmask |= __ballot_sync(FULL, cand != 0) & (2u << col);
 				}
-				f |= T1_PI(r);
 			}
-			*fp = f;
+			if(act)
+				g.fseg[b.lane] = f;
 		}
 	}
 }
 
 // dec_refpass_mqc / dec_refpass_raw, T1.cpp:1246-1364
 template<bool RAW>
-static __device__ void ref_pass(const Blk& b, Mq& q, uint8_t* cxs, const uint32_t* mqt,
+static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t* cxs, const uint32_t* mqt,
 								 int bpno_plus_one)
 {
 	const int32_t poshalf = (1 << bpno_plus_one) >> 1;
 	for(uint32_t k = 0, s = 0; k < b.h; k += 4, ++s)
 	{
-		const uint32_t rows = min(4u, b.h - k);
-		uint32_t* fp = b.fl + (s + 1) * b.fs + 1;
-		int32_t* dp = b.data + (size_t)k * b.ds;
-		for(uint32_t x = 0; x < b.w; ++x, ++fp, ++dp)
+		const uint32_t rows = min(4u, b.h - k), rowmask = (1u << rows) - 1u;
+		for(uint32_t x0 = 0; x0 < b.w; x0 += 32)
 		{
-			uint32_t f = *fp;
-			if(!(f & T1_SIGC_ALL))
-				continue;
-			for(uint32_t r = 0; r < rows; ++r)
+			Seg g;
+			g.fseg = b.fl + (s + 1) * b.fs + 1 + x0;
+			g.dseg = b.data + (size_t)k * b.ds + x0;
+			const bool act = x0 + b.lane < b.w;
+			__syncwarp();
+			const uint32_t f = act ? g.fseg[b.lane] : 0u;
+			// everything about this pass is known before it starts: which samples are refined
+			// (significant before this bit-plane) and with which context
+			const uint32_t todo = sig4(f) & ~(f >> 24) & rowmask;
+			uint32_t cxpk = 0; // four context offsets, one per byte
+			if(!RAW)
 			{
-				if((f & (T1_SIG_C(r) | T1_PI(r))) != T1_SIG_C(r))
-					continue;
-				uint32_t v;
-				if(RAW)
-					v = raw_decode(q);
-				else
+				const uint32_t nz = nz4(f);
+#pragma unroll
+				for(uint32_t r = 0; r < 4; ++r)
 				{
-					const uint32_t cx = (f & T1_MU(r))					   ? T1_CTX_MAG + 2
-										: ((f >> (3 * r)) & T1_NEIGH) ? T1_CTX_MAG + 1
-																	   : T1_CTX_MAG;
-					v = mq_decode(q, cxs, mqt, cx);
+					const uint32_t cx = (f & T1_MU(r)) ? CX4_MAG + 8 : ((nz >> r) & 1u) ? CX4_MAG + 4 : CX4_MAG;
+					cxpk |= cx << (8 * r);
 				}
-				// the sign lives in the state word, so the update is a fire-and-forget reduction
-				const uint32_t neg = (f >> (18 + r + 1)) & 1u;
-				atomicAdd(&dp[r * b.ds], (v ^ neg) ? poshalf : -poshalf);
-				f |= T1_MU(r);
 			}
-			*fp = f;
+			uint32_t colmask = __ballot_sync(FULL, todo != 0);
+			if(colmask == 0)
+				continue;
+			uint32_t bits = 0;
+			while(colmask)
+			{
+				const uint32_t col = __ffs(colmask) - 1;
+				colmask &= colmask - 1;
+				uint32_t m = __shfl_sync(FULL, todo, col);
+				const uint32_t pk = RAW ? 0u : __shfl_sync(FULL, cxpk, col);
+				uint32_t got = 0;
+				while(m)
+				{
+					const uint32_t r = __ffs(m) - 1;
+					m &= m - 1;
+					const uint32_t v = RAW ? raw_decode(q) : mq_decode(q, cxs, mqt, (pk >> (8 * r)) & 0xFFu);
+					got |= v << r;
+				}
+				if(b.lane == col)
+					bits = got;
+			}
+			if(todo)
+			{
+#pragma unroll
+				for(uint32_t r = 0; r < 4; ++r)
+					if((todo >> r) & 1u)
+					{
+						const uint32_t neg = (f >> (18 + r + 1)) & 1u;
+						int32_t* d = g.dseg + b.lane + r * b.ds;
+						*d += (((bits >> r) & 1u) ^ neg) ? poshalf : -poshalf;
+					}
+				g.fseg[b.lane] = f | (todo << 28);
+			}
 		}
 	}
 }
 
 constexpr int MQ_MAX_THREADS = 256; // up to 8 warps = 8 code blocks in flight per CTA
+constexpr uint32_t CXS_BYTES = 128; // 19 context words, padded
 
 __global__ void __launch_bounds__(MQ_MAX_THREADS)
 	t1_mq_decode_kernel(const T1Launch l, const T1Tables* __restrict__ tab)
 {
 	extern __shared__ __align__(16) uint8_t smem[];
-	// CTA-wide tables
+	// CTA-wide tables: MQ states with the MPS in bit 31, context tables scaled by four
 	uint32_t* mqt = reinterpret_cast<uint32_t*>(smem);
-	uint8_t* zc = smem + 94 * 4;
+	uint8_t* zc = smem + 96 * 4;
 	uint8_t* sc = zc + 2048;
 	uint8_t* warp_base = sc + 256;
 	for(uint32_t i = threadIdx.x; i < 94; i += blockDim.x)
-		mqt[i] = tab->mq[i];
+		mqt[i] = tab->mq[i] | ((i & 1u) << 31);
 	for(uint32_t i = threadIdx.x; i < 2048; i += blockDim.x)
-		zc[i] = tab->zc[i];
+		zc[i] = (uint8_t)(tab->zc[i] * 4u);
 	for(uint32_t i = threadIdx.x; i < 256; i += blockDim.x)
-		sc[i] = tab->sc[i];
+	{
+		const uint32_t e = tab->sc[i];
+		sc[i] = (uint8_t)((e & 0x80u) | ((e & 0x7Fu) * 4u));
+	}
 	__syncthreads();
 
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const size_t per_warp = 32 + (size_t)l.max_flag_words * 4;
-	uint8_t* cxs = warp_base + warp * per_warp;
-	uint32_t* fl = reinterpret_cast<uint32_t*>(cxs + 32);
+	const size_t per_warp = CXS_BYTES + (size_t)l.max_flag_words * 4;
+	uint32_t* cxs = reinterpret_cast<uint32_t*>(warp_base + warp * per_warp);
+	uint32_t* fl = cxs + CXS_BYTES / 4;
 
 	for(;;)
 	{
 		uint32_t item = 0;
 		if(lane == 0)
 			item = atomicAdd(l.counter, 1u);
-		item = __shfl_sync(0xffffffffu, item, 0);
+		item = __shfl_sync(FULL, item, 0);
 		if(item >= l.nblocks)
 			break;
 		const uint32_t bi = l.order ? l.order[item] : item;
@@ -398,7 +553,7 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 		const uint32_t w = cb.w, h = cb.h;
 		int32_t* blk_data = reinterpret_cast<int32_t*>(l.planes[cb.comp]) + (size_t)cb.y * l.stride + cb.x;
 		const uint32_t fs = w + 2, nstripes = (h + 3) >> 2, nfl = fs * (nstripes + 2);
-		bool bad = (int)cb.numbps >= 31 - 6; // maxBitPlanesGRK, T1.cpp:1373-1377
+		const bool bad = (int)cb.numbps >= 31 - 6; // maxBitPlanesGRK, T1.cpp:1373-1377
 		const bool coded = cb.numsegs != 0 && !bad;
 		if(coded)
 		{
@@ -407,10 +562,7 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 			for(uint32_t y = 0; y < h; ++y)
 				for(uint32_t x = lane; x < w; x += 32)
 					blk_data[(size_t)y * l.stride + x] = 0;
-		}
-		__syncwarp();
-		if(coded && lane == 0)
-		{
+			__syncwarp();
 			Blk b;
 			b.fl = fl;
 			b.data = blk_data;
@@ -421,8 +573,9 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 			b.zc = zc + 512u * cb.orient;
 			b.sc = sc;
 			b.vsc = (cb.cblk_sty & GRKB_CBLKSTY_VSC) != 0;
+			b.lane = lane;
 			Mq q;
-			reset_states(cxs);
+			reset_states(cxs, mqt, lane);
 			int bp1 = (int)cb.numbps;
 			uint32_t passtype = 2;
 			const uint8_t* p = l.bytes + cb.data_off;
@@ -455,7 +608,10 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 					else
 						cleanup_pass(b, q, cxs, mqt, bp1, (cb.cblk_sty & GRKB_CBLKSTY_SEGSYM) != 0);
 					if((cb.cblk_sty & GRKB_CBLKSTY_RESET) && !raw)
-						reset_states(cxs);
+					{
+						__syncwarp();
+						reset_states(cxs, mqt, lane);
+					}
 					if(++passtype == 3)
 					{
 						passtype = 0;
@@ -521,9 +677,17 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 		grkb_set_error("t1: cannot upload coding tables");
 		return -1;
 	}
-	const size_t per_warp = 32 + (size_t)l.max_flag_words * 4;
-	const size_t fixed = 94 * 4 + 2048 + 256;
+	const size_t per_warp = CXS_BYTES + (size_t)l.max_flag_words * 4;
+	const size_t fixed = 96 * 4 + 2048 + 256;
 	// warps per CTA: whatever packs most code blocks into the 227 KB of an SM
+	static int max_warps_sm = -1;
+	if(max_warps_sm < 0)
+	{
+		const char* e = getenv("GRKB_T1_MQ_WARPS");
+		max_warps_sm = e ? atoi(e) : 32;
+		if(max_warps_sm < 1 || max_warps_sm > 64)
+			max_warps_sm = 32;
+	}
 	int best_nw = 0, best_total = 0;
 	for(int nw = 1; nw <= MQ_MAX_THREADS / 32; ++nw)
 	{
@@ -533,8 +697,8 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 		int per_sm = (int)((227 * 1024) / (need + 1024));
 		if(per_sm > 32)
 			per_sm = 32;
-		if(nw * per_sm > 48)
-			per_sm = 48 / nw;
+		if(nw * per_sm > max_warps_sm)
+			per_sm = max_warps_sm / nw;
 		if(nw * per_sm >= best_total)
 		{
 			best_total = nw * per_sm;
