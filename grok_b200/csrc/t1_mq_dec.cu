@@ -34,7 +34,12 @@ constexpr uint32_t FULL = 0xffffffffu;
 struct Mq
 {
 	uint32_t a; // the A register in the upper half (A << 16): "A < 0x8000" is a sign test
-	uint32_t c, ct;
+	// C is kept 64 bits wide: c is the reference's 32-bit C register, cl holds the bytes that the
+	// reference would add later, already added at the place they will have shifted to.  Every
+	// update of C is an addition or a left shift, so adding a byte early (t shifts early, t bit
+	// positions lower) gives the same register; ct = shifts left until the next byte is due.
+	uint32_t c, cl;
+	int32_t ct;
 	const uint8_t* p; // segment bytes
 	uint32_t len, pos;
 	uint32_t cur, nxt; // bytes at pos and pos+1 (0xFF past the end: mqc_dec.cpp:78-90)
@@ -45,28 +50,39 @@ static __device__ __forceinline__ uint32_t seg_byte(const Mq& q, uint32_t pos)
 	return pos < q.len ? (uint32_t)__ldg(q.p + pos) : 0xFFu;
 }
 
-// bytein_dec_macro, mqc_dec_inl.h:82-108
-static __device__ __forceinline__ void mq_bytein(Mq& q)
+// bytein_dec_macro (mqc_dec_inl.h:82-108), run ahead of time: bytes are added until at least
+// 33 shifts are covered (a renormalisation shifts by at most 15)
+static __device__ __forceinline__ void mq_fill(Mq& q)
 {
-	if(q.cur == 0xFF)
+	do
 	{
-		if(q.nxt > 0x8F)
+		uint32_t add = q.nxt, at = 40, step = 8;
+		bool adv = true;
+		if(q.cur == 0xFF)
 		{
-			q.c += 0xFF00;
-			q.ct = 8;
-			return;
+			if(q.nxt > 0x8F)
+			{
+				add = 0xFF; // c += 0xFF00, the position does not advance
+				adv = false;
+			}
+			else
+			{
+				at = 41; // c += nxt << 9, seven new bits
+				step = 7;
+			}
 		}
-		q.c += q.nxt << 9;
-		q.ct = 7;
-	}
-	else
-	{
-		q.c += q.nxt << 8;
-		q.ct = 8;
-	}
-	q.pos++;
-	q.cur = q.nxt;
-	q.nxt = seg_byte(q, q.pos + 1);
+		const uint64_t w = (uint64_t)add << (at - q.ct);
+		const uint32_t lo = q.cl + (uint32_t)w;
+		q.c += (uint32_t)(w >> 32) + (lo < q.cl ? 1u : 0u);
+		q.cl = lo;
+		q.ct += step;
+		if(adv)
+		{
+			q.pos++;
+			q.cur = q.nxt;
+			q.nxt = seg_byte(q, q.pos + 1);
+		}
+	} while(q.ct <= 32);
 }
 
 static __device__ __forceinline__ void mq_init(Mq& q, const uint8_t* p, uint32_t len)
@@ -77,8 +93,11 @@ static __device__ __forceinline__ void mq_init(Mq& q, const uint8_t* p, uint32_t
 	q.cur = seg_byte(q, 0);
 	q.nxt = seg_byte(q, 1);
 	q.c = q.cur << 16;
-	mq_bytein(q);
-	q.c <<= 7;
+	q.cl = 0;
+	q.ct = 0;
+	mq_fill(q);
+	q.c = __funnelshift_l(q.cl, q.c, 7);
+	q.cl <<= 7;
 	q.ct -= 7;
 	q.a = 0x80000000u;
 }
@@ -123,65 +142,38 @@ static __device__ __forceinline__ uint32_t raw_decode(Mq& q)
 	return (q.c >> q.ct) & 1u;
 }
 
-// renorm_dec_macro (mqc_dec_inl.h:111-121) with the shifts batched between byte fetches
-static __device__ __forceinline__ void mq_renorm(Mq& q)
-{
-	uint32_t n = __clz(q.a); // shifts until the top bit of A is set
-	while(n)
-	{
-		if(q.ct == 0)
-			mq_bytein(q);
-		const uint32_t k = min(n, q.ct);
-		q.a <<= k;
-		q.c <<= k;
-		q.ct -= k;
-		n -= k;
-	}
-}
-
-// decompress_macro, mqc_dec_inl.h:134-158.  cxs[] holds, per context, the table entry of its
-// current state (Qe | next-if-MPS << 16 | next-if-LPS << 24 | MPS << 31), so the common path is
-// one shared-memory read; cx4 is the context number times four.
+// decompress_macro + renorm_dec_macro, mqc_dec_inl.h:111-158.  cxs[] holds, per context, the
+// table entry of its current state (Qe | next-if-MPS << 16 | next-if-LPS << 24 | MPS << 31), so a
+// decision costs one shared-memory read, plus a read and a write when the state moves; cx4 is
+// the context number times four.
 static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t* cxs, const uint32_t* mqt,
 													  uint32_t cx4)
 {
 	uint32_t* slot = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(cxs) + cx4);
 	const uint32_t e = *slot;
 	const uint32_t qe = e << 16;
-	uint32_t d = e >> 31;
 	q.a -= qe;
-	if(q.c < qe)
-	{
-		uint32_t st;
-		if(q.a < qe)
-			st = (e >> 16) & 0x7Fu;
-		else
-		{
-			d ^= 1u;
-			st = (e >> 24) & 0x7Fu;
-		}
-		q.a = qe;
-		*slot = mqt[st];
-		mq_renorm(q);
-	}
-	else
+	const bool lt = q.c < qe;
+	if(!lt)
 	{
 		q.c -= qe;
-		if((int32_t)q.a >= 0)
-		{
-			uint32_t st;
-			if(q.a < qe)
-			{
-				d ^= 1u;
-				st = (e >> 24) & 0x7Fu;
-			}
-			else
-				st = (e >> 16) & 0x7Fu;
-			*slot = mqt[st];
-			mq_renorm(q);
-		}
+		if((int32_t)q.a < 0)
+			return e >> 31; // MPS, no renormalisation
 	}
-	return d;
+	// c < qe: the MPS/LPS sense is exchanged when a < qe; otherwise LPS exactly when a < qe
+	const uint32_t lps = (uint32_t)lt ^ (uint32_t)(q.a < qe);
+	if(lt)
+		q.a = qe;
+	const uint32_t next4 = (lps ? e >> 22 : e >> 14) & 0x1FCu; // next state x 4
+	*slot = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(mqt) + next4);
+	const uint32_t n = __clz(q.a); // shifts until the top bit of A is set
+	q.a <<= n;
+	q.c = __funnelshift_l(q.cl, q.c, n);
+	q.cl <<= n;
+	q.ct -= (int32_t)n;
+	if(q.ct < 16)
+		mq_fill(q);
+	return (e >> 31) ^ lps;
 }
 
 constexpr uint32_t CX4_MAG = T1_CTX_MAG * 4, CX4_AGG = T1_CTX_AGG * 4, CX4_UNI = T1_CTX_UNI * 4;
