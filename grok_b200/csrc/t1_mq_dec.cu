@@ -25,6 +25,7 @@
 // context, the MQ decision itself.  Samples live in the block's rectangle of the (L2-resident)
 // Mallat coefficient plane.  Warps pull blocks from a global work counter, longest first.
 #include "t1.cuh"
+#include <mutex>
 #include <stdlib.h>
 
 namespace
@@ -142,32 +143,40 @@ static __device__ __forceinline__ uint32_t raw_decode(Mq& q)
 	return (q.c >> q.ct) & 1u;
 }
 
+// Coding tables in constant memory (every lane reads the same entry, so a look-up is one LDC):
+// MQ states with the MPS in bit 31, the context tables hold context numbers times four, and the
+// sign-coding table is indexed the way sc_index() below gathers its bits.
+struct DecTables
+{
+	uint32_t mq[96]; // state 2*i+mps: Qe | next-if-MPS << 16 | next-if-LPS << 24 | mps << 31
+	uint8_t zc[4 * 512];
+	uint8_t sc[256]; // context x 4 | xor bit << 7
+};
+__constant__ DecTables c_dec;
+
 // decompress_macro + renorm_dec_macro, mqc_dec_inl.h:111-158.  cxs[] holds, per context, the
-// table entry of its current state (Qe | next-if-MPS << 16 | next-if-LPS << 24 | MPS << 31), so a
-// decision costs one shared-memory read, plus a read and a write when the state moves; cx4 is
-// the context number times four.
-static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t* cxs, const uint32_t* mqt,
-													  uint32_t cx4)
+// table entry of its current state, so a decision costs one shared-memory read, plus a constant
+// read and a shared write when the state moves; cx4 is the context number times four.  Written
+// without branches: a decision that needs no renormalisation shifts by clz(A) = 0.
+static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t* cxs, uint32_t cx4)
 {
 	uint32_t* slot = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(cxs) + cx4);
 	const uint32_t e = *slot;
 	const uint32_t qe = e << 16;
-	q.a -= qe;
+	uint32_t a = q.a - qe;
 	const bool lt = q.c < qe;
-	if(!lt)
-	{
-		q.c -= qe;
-		if((int32_t)q.a < 0)
-			return e >> 31; // MPS, no renormalisation
-	}
 	// c < qe: the MPS/LPS sense is exchanged when a < qe; otherwise LPS exactly when a < qe
-	const uint32_t lps = (uint32_t)lt ^ (uint32_t)(q.a < qe);
-	if(lt)
-		q.a = qe;
-	const uint32_t next4 = (lps ? e >> 22 : e >> 14) & 0x1FCu; // next state x 4
-	*slot = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(mqt) + next4);
-	const uint32_t n = __clz(q.a); // shifts until the top bit of A is set
-	q.a <<= n;
+	// (which cannot happen while a >= 0x8000, Qe being at most 0x5601)
+	const uint32_t lps = (uint32_t)lt ^ (uint32_t)(a < qe);
+	q.c -= lt ? 0u : qe;
+	a = lt ? qe : a;
+	const uint32_t n = __clz(a); // shifts until the top bit of A is set
+	if(n)
+	{
+		const uint32_t next4 = (lps ? e >> 22 : e >> 14) & 0x1FCu; // next state x 4
+		*slot = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(c_dec.mq) + next4);
+	}
+	q.a = a << n;
 	q.c = __funnelshift_l(q.cl, q.c, n);
 	q.cl <<= n;
 	q.ct -= (int32_t)n;
@@ -178,13 +187,13 @@ static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t* cxs, const
 
 constexpr uint32_t CX4_MAG = T1_CTX_MAG * 4, CX4_AGG = T1_CTX_AGG * 4, CX4_UNI = T1_CTX_UNI * 4;
 
-static __device__ __forceinline__ void reset_states(uint32_t* cxs, const uint32_t* mqt, uint32_t lane)
+static __device__ __forceinline__ void reset_states(uint32_t* cxs, uint32_t lane)
 {
 	// mqc_resetstates, mqc_dec.cpp:121-130
 	if(lane < T1_NCTX)
 	{
 		const uint32_t st = lane == T1_CTX_UNI ? 46u << 1 : lane == T1_CTX_AGG ? 3u << 1 : lane == T1_CTX_ZC ? 4u << 1 : 0u;
-		cxs[lane] = mqt[st];
+		cxs[lane] = c_dec.mq[st];
 	}
 	__syncwarp();
 }
@@ -195,8 +204,7 @@ struct Blk
 	int32_t* data; // the block's rectangle in the coefficient plane (x2 fixed point until dequantised)
 	uint32_t ds; // row pitch of data
 	uint32_t w, h, fs; // fs = w + 2
-	const uint8_t* zc; // zero-coding table of this band orientation (contexts x 4)
-	const uint8_t* sc; // sign-coding table (context x 4 | xor bit << 7)
+	uint32_t zc; // offset of this band orientation's zero-coding table in c_dec.zc
 	bool vsc;
 	uint32_t lane;
 };
@@ -218,14 +226,16 @@ static __device__ __forceinline__ uint32_t nz4(uint32_t f)
 // index into the sign-coding table from the centre word f (row r) and its west/east words
 static __device__ __forceinline__ uint32_t sc_index(uint32_t f, uint32_t fw, uint32_t fe, uint32_t r)
 {
-	const uint32_t nb = f >> (3 * r); // 3x3 neighbourhood of row r at bits 0..8
-	uint32_t i = ((nb >> 3) & 1u) | (((nb >> 5) & 1u) << 1) | (((nb >> 1) & 1u) << 2) |
-				 (((nb >> 7) & 1u) << 3);
-	i |= ((fw >> (18 + r + 1)) & 1u) << 4;
-	i |= ((fe >> (18 + r + 1)) & 1u) << 5;
-	i |= ((f >> (18 + r)) & 1u) << 6;
-	i |= ((f >> (18 + r + 2)) & 1u) << 7;
-	return i;
+	// 3x3 neighbourhood of row r at bits 0..8 of f >> 3r: N, W, E, S are its bits 1, 3, 5, 7 and
+	// stay there; the signs of N and S go to bits 0 and 2, those of W and E to bits 4 and 6
+	return ((f >> (3 * r)) & 0xAAu) | ((f >> (18 + r)) & 5u) | ((fw >> (15 + r)) & 0x10u) |
+		   ((fe >> (13 + r)) & 0x40u);
+}
+// the same index for the table as T1Tables::sc orders it (W E N S significance, then signs)
+static inline uint32_t sc_index_tables(uint32_t j)
+{
+	return ((j >> 3) & 1u) | (((j >> 5) & 1u) << 1) | (((j >> 1) & 1u) << 2) | (((j >> 7) & 1u) << 3) |
+		   (((j >> 4) & 1u) << 4) | (((j >> 6) & 1u) << 5) | ((j & 1u) << 6) | (((j >> 2) & 1u) << 7);
 }
 
 // One 32-column segment of a stripe: lane l holds the state word of column x0 + l in `f`.
@@ -302,7 +312,7 @@ static __device__ __forceinline__ void mark_significant(const Blk& b, const Seg&
 // sign of a newly significant sample (T1.cpp dec_*pass "sign" step) + the bookkeeping
 template<bool RAW>
 static __device__ __forceinline__ void code_sign(const Blk& b, const Seg& g, Mq& q, uint32_t* cxs,
-												  const uint32_t* mqt, uint32_t& f, uint32_t& fc,
+												  uint32_t& f, uint32_t& fc,
 												  uint32_t col, uint32_t r, int32_t oph)
 {
 	uint32_t v;
@@ -312,15 +322,15 @@ static __device__ __forceinline__ void code_sign(const Blk& b, const Seg& g, Mq&
 	{
 		uint32_t fw, fe;
 		west_east(g, f, col, fw, fe);
-		const uint32_t e = b.sc[sc_index(fc, fw, fe, r)];
-		v = mq_decode(q, cxs, mqt, e & 0x7Fu) ^ (e >> 7);
+		const uint32_t e = c_dec.sc[sc_index(fc, fw, fe, r)];
+		v = mq_decode(q, cxs, e & 0x7Fu) ^ (e >> 7);
 	}
 	mark_significant(b, g, f, col, r, v, v ? -oph : oph);
 	fc |= T1_SIG_C(r) | (v << (18 + r + 1));
 }
 
 // dec_clnpass, T1.cpp:934-1093
-static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t* cxs, const uint32_t* mqt,
+static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t* cxs,
 									 int bpno_plus_one, bool segsym)
 {
 	const int32_t one = 1 << bpno_plus_one, oph = one | (one >> 1);
@@ -347,10 +357,10 @@ static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t* cxs, const ui
 				bool sign_only = false;
 				if(rows == 4 && fc == 0)
 				{
-					if(!mq_decode(q, cxs, mqt, CX4_AGG))
+					if(!mq_decode(q, cxs, CX4_AGG))
 						continue;
-					uint32_t r = mq_decode(q, cxs, mqt, CX4_UNI);
-					r = (r << 1) | mq_decode(q, cxs, mqt, CX4_UNI);
+					uint32_t r = mq_decode(q, cxs, CX4_UNI);
+					r = (r << 1) | mq_decode(q, cxs, CX4_UNI);
 					m = (0xFu << r) & 0xFu;
 					sign_only = true;
 				}
@@ -358,10 +368,10 @@ static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t* cxs, const ui
 				{
 					const uint32_t r = __ffs(m) - 1;
 					m &= m - 1;
-					if(!sign_only && !mq_decode(q, cxs, mqt, b.zc[(fc >> (3 * r)) & T1_NEIGH]))
+					if(!sign_only && !mq_decode(q, cxs, c_dec.zc[b.zc + ((fc >> (3 * r)) & T1_NEIGH)]))
 						continue;
 					sign_only = false;
-					code_sign<false>(b, g, q, cxs, mqt, f, fc, col, r, oph);
+					code_sign<false>(b, g, q, cxs, f, fc, col, r, oph);
 				}
 			}
 			if(act)
@@ -372,13 +382,13 @@ static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t* cxs, const ui
 	{
 		// dec_clnpass_check_segsym, T1.cpp:1053-1073: the four decisions are consumed
 		for(int i = 0; i < 4; ++i)
-			(void)mq_decode(q, cxs, mqt, CX4_UNI);
+			(void)mq_decode(q, cxs, CX4_UNI);
 	}
 }
 
 // dec_sigpass_mqc / dec_sigpass_raw, T1.cpp:1094-1245
 template<bool RAW>
-static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t* cxs, const uint32_t* mqt,
+static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t* cxs,
 								 int bpno_plus_one)
 {
 	const int32_t one = 1 << bpno_plus_one, oph = one | (one >> 1);
@@ -412,10 +422,10 @@ static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t* cxs, const uint32
 					m &= m - 1;
 					pi |= 1u << r;
 					const uint32_t bit = RAW ? raw_decode(q)
-											 : mq_decode(q, cxs, mqt, b.zc[(fc >> (3 * r)) & T1_NEIGH]);
+											 : mq_decode(q, cxs, c_dec.zc[b.zc + ((fc >> (3 * r)) & T1_NEIGH)]);
 					if(!bit)
 						continue;
-					code_sign<RAW>(b, g, q, cxs, mqt, f, fc, col, r, oph);
+					code_sign<RAW>(b, g, q, cxs, f, fc, col, r, oph);
 					m |= (2u << r) & frc; // the row below becomes a candidate
 					grown |= (7u << r) >> 1; // and rows r-1..r+1 of the next column
 				}
@@ -436,7 +446,7 @@ static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t* cxs, const uint32
 
 // dec_refpass_mqc / dec_refpass_raw, T1.cpp:1246-1364
 template<bool RAW>
-static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t* cxs, const uint32_t* mqt,
+static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t* cxs,
 								 int bpno_plus_one)
 {
 	const int32_t poshalf = (1 << bpno_plus_one) >> 1;
@@ -480,7 +490,7 @@ static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t* cxs, const uint32
 				{
 					const uint32_t r = __ffs(m) - 1;
 					m &= m - 1;
-					const uint32_t v = RAW ? raw_decode(q) : mq_decode(q, cxs, mqt, (pk >> (8 * r)) & 0xFFu);
+					const uint32_t v = RAW ? raw_decode(q) : mq_decode(q, cxs, (pk >> (8 * r)) & 0xFFu);
 					got |= v << r;
 				}
 				if(b.lane == col)
@@ -506,25 +516,10 @@ constexpr int MQ_MAX_THREADS = 256; // up to 8 warps = 8 code blocks in flight p
 constexpr uint32_t CXS_BYTES = 128; // 19 context words, padded
 
 __global__ void __launch_bounds__(MQ_MAX_THREADS)
-	t1_mq_decode_kernel(const T1Launch l, const T1Tables* __restrict__ tab)
+	t1_mq_decode_kernel(const T1Launch l)
 {
 	extern __shared__ __align__(16) uint8_t smem[];
-	// CTA-wide tables: MQ states with the MPS in bit 31, context tables scaled by four
-	uint32_t* mqt = reinterpret_cast<uint32_t*>(smem);
-	uint8_t* zc = smem + 96 * 4;
-	uint8_t* sc = zc + 2048;
-	uint8_t* warp_base = sc + 256;
-	for(uint32_t i = threadIdx.x; i < 94; i += blockDim.x)
-		mqt[i] = tab->mq[i] | ((i & 1u) << 31);
-	for(uint32_t i = threadIdx.x; i < 2048; i += blockDim.x)
-		zc[i] = (uint8_t)(tab->zc[i] * 4u);
-	for(uint32_t i = threadIdx.x; i < 256; i += blockDim.x)
-	{
-		const uint32_t e = tab->sc[i];
-		sc[i] = (uint8_t)((e & 0x80u) | ((e & 0x7Fu) * 4u));
-	}
-	__syncthreads();
-
+	uint8_t* warp_base = smem;
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const size_t per_warp = CXS_BYTES + (size_t)l.max_flag_words * 4;
 	uint32_t* cxs = reinterpret_cast<uint32_t*>(warp_base + warp * per_warp);
@@ -562,12 +557,11 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 			b.w = w;
 			b.h = h;
 			b.fs = fs;
-			b.zc = zc + 512u * cb.orient;
-			b.sc = sc;
+			b.zc = 512u * cb.orient;
 			b.vsc = (cb.cblk_sty & GRKB_CBLKSTY_VSC) != 0;
 			b.lane = lane;
 			Mq q;
-			reset_states(cxs, mqt, lane);
+			reset_states(cxs, lane);
 			int bp1 = (int)cb.numbps;
 			uint32_t passtype = 2;
 			const uint8_t* p = l.bytes + cb.data_off;
@@ -586,23 +580,23 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 					if(passtype == 0)
 					{
 						if(raw)
-							sig_pass<true>(b, q, cxs, mqt, bp1);
+							sig_pass<true>(b, q, cxs, bp1);
 						else
-							sig_pass<false>(b, q, cxs, mqt, bp1);
+							sig_pass<false>(b, q, cxs, bp1);
 					}
 					else if(passtype == 1)
 					{
 						if(raw)
-							ref_pass<true>(b, q, cxs, mqt, bp1);
+							ref_pass<true>(b, q, cxs, bp1);
 						else
-							ref_pass<false>(b, q, cxs, mqt, bp1);
+							ref_pass<false>(b, q, cxs, bp1);
 					}
 					else
-						cleanup_pass(b, q, cxs, mqt, bp1, (cb.cblk_sty & GRKB_CBLKSTY_SEGSYM) != 0);
+						cleanup_pass(b, q, cxs, bp1, (cb.cblk_sty & GRKB_CBLKSTY_SEGSYM) != 0);
 					if((cb.cblk_sty & GRKB_CBLKSTY_RESET) && !raw)
 					{
 						__syncwarp();
-						reset_states(cxs, mqt, lane);
+						reset_states(cxs, lane);
 					}
 					if(++passtype == 3)
 					{
@@ -639,6 +633,34 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS)
 		__syncwarp();
 	}
 }
+
+// c_dec is per device: filled once per device from the host tables
+int upload_tables()
+{
+	static std::mutex mu;
+	static bool done[64] = {};
+	int dev = 0;
+	if(cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+		return -1;
+	std::lock_guard<std::mutex> lk(mu);
+	if(done[dev])
+		return 0;
+	const T1Tables& h = grkb_t1_tables_host();
+	static DecTables t;
+	for(uint32_t i = 0; i < 96; ++i)
+		t.mq[i] = i < 94 ? h.mq[i] | ((i & 1u) << 31) : 0u;
+	for(uint32_t i = 0; i < 4 * 512; ++i)
+		t.zc[i] = (uint8_t)(h.zc[i] * 4u);
+	for(uint32_t j = 0; j < 256; ++j)
+	{
+		const uint32_t e = h.sc[sc_index_tables(j)];
+		t.sc[j] = (uint8_t)((e & 0x80u) | ((e & 0x7Fu) * 4u));
+	}
+	if(cudaMemcpyToSymbol(c_dec, &t, sizeof(t)) != cudaSuccess)
+		return -1;
+	done[dev] = true;
+	return 0;
+}
 } // namespace
 
 int grkb_launch_t1_mq_decode_simt(const T1Launch& l, cudaStream_t s);
@@ -663,14 +685,13 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 		if(rc <= 0)
 			return rc;
 	}
-	const T1Tables* tab = grkb_t1_tables_device();
-	if(!tab)
+	if(upload_tables() != 0)
 	{
 		grkb_set_error("t1: cannot upload coding tables");
 		return -1;
 	}
 	const size_t per_warp = CXS_BYTES + (size_t)l.max_flag_words * 4;
-	const size_t fixed = 96 * 4 + 2048 + 256;
+	const size_t fixed = 0;
 	// warps per CTA: whatever packs most code blocks into the 227 KB of an SM
 	static int max_warps_sm = -1;
 	if(max_warps_sm < 0)
@@ -718,7 +739,7 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 	if(ctas > need)
 		ctas = need;
 	GRKB_CUDA_CHECK(cudaMemsetAsync(l.counter, 0, sizeof(uint32_t), s));
-	t1_mq_decode_kernel<<<ctas, best_nw * 32, smem, s>>>(l, tab);
+	t1_mq_decode_kernel<<<ctas, best_nw * 32, smem, s>>>(l);
 	GRKB_CUDA_CHECK(cudaGetLastError());
 	return 0;
 }
