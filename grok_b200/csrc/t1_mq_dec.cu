@@ -158,10 +158,39 @@ __constant__ DecTables c_dec;
 // table entry of its current state, so a decision costs one shared-memory read, plus a constant
 // read and a shared write when the state moves; cx4 is the context number times four.  Written
 // without branches: a decision that needs no renormalisation shifts by clz(A) = 0.
-static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t* cxs, uint32_t cx4)
+// The per-warp context words are addressed in the shared window (32-bit addresses, no generic
+// address arithmetic in the decision chain).
+static __device__ __forceinline__ uint32_t lds32(uint32_t sa)
 {
-	uint32_t* slot = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(cxs) + cx4);
-	const uint32_t e = *slot;
+	uint32_t v;
+	asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(sa) : "memory");
+	return v;
+}
+static __device__ __forceinline__ void sts32(uint32_t sa, uint32_t v)
+{
+	asm volatile("st.shared.u32 [%0], %1;" ::"r"(sa), "r"(v) : "memory");
+}
+static __device__ __forceinline__ uint32_t lds16(uint32_t sa)
+{
+	uint32_t v;
+	asm volatile("{ .reg .u16 t; ld.shared.u16 t, [%1]; cvt.u32.u16 %0, t; }" : "=r"(v) : "r"(sa) : "memory");
+	return v;
+}
+static __device__ __forceinline__ void sts16(uint32_t sa, uint32_t v)
+{
+	asm volatile("{ .reg .u16 t; cvt.u16.u32 t, %1; st.shared.u16 [%0], t; }" ::"r"(sa), "r"(v) : "memory");
+}
+static __device__ __forceinline__ uint32_t shift_amount(uint32_t a) // clz for a != 0, one FLO
+{
+	uint32_t n;
+	asm("bfind.shiftamt.u32 %0, %1;" : "=r"(n) : "r"(a));
+	return n;
+}
+
+static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t cxs, uint32_t cx4)
+{
+	const uint32_t slot = cxs + cx4;
+	const uint32_t e = lds32(slot);
 	const uint32_t qe = e << 16;
 	uint32_t a = q.a - qe;
 	const bool lt = q.c < qe;
@@ -170,11 +199,11 @@ static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t* cxs, uint3
 	const uint32_t lps = (uint32_t)lt ^ (uint32_t)(a < qe);
 	q.c -= lt ? 0u : qe;
 	a = lt ? qe : a;
-	const uint32_t n = __clz(a); // shifts until the top bit of A is set
+	const uint32_t n = shift_amount(a); // shifts until the top bit of A is set
 	if(n)
 	{
 		const uint32_t next4 = (lps ? e >> 22 : e >> 14) & 0x1FCu; // next state x 4
-		*slot = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(c_dec.mq) + next4);
+		sts32(slot, *reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(c_dec.mq) + next4));
 	}
 	q.a = a << n;
 	q.c = __funnelshift_l(q.cl, q.c, n);
@@ -187,13 +216,13 @@ static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t* cxs, uint3
 
 constexpr uint32_t CX4_MAG = T1_CTX_MAG * 4, CX4_AGG = T1_CTX_AGG * 4, CX4_UNI = T1_CTX_UNI * 4;
 
-static __device__ __forceinline__ void reset_states(uint32_t* cxs, uint32_t lane)
+static __device__ __forceinline__ void reset_states(uint32_t cxs, uint32_t lane)
 {
 	// mqc_resetstates, mqc_dec.cpp:121-130
 	if(lane < T1_NCTX)
 	{
 		const uint32_t st = lane == T1_CTX_UNI ? 46u << 1 : lane == T1_CTX_AGG ? 3u << 1 : lane == T1_CTX_ZC ? 4u << 1 : 0u;
-		cxs[lane] = c_dec.mq[st];
+		sts32(cxs + lane * 4, c_dec.mq[st]);
 	}
 	__syncwarp();
 }
@@ -268,50 +297,40 @@ static __device__ __forceinline__ void mark_significant(const Blk& b, const Seg&
 														 int32_t val)
 {
 	const uint32_t lane = b.lane;
+	const uint32_t sh = 3 * r + 3; // row r of the 3x6 neighbourhood: [west, centre, east] at sh..sh+2
+	// the column itself, and the columns west / east of it (we are their east / west neighbour)
+	uint32_t add = lane == col ? (2u << sh) | (sgn << (18 + r + 1)) : 0u;
+	add = lane + 1 == col ? 4u << sh : add;
+	add = lane == col + 1 ? 1u << sh : add;
+	f |= add;
 	if(lane == col)
-	{
-		f |= T1_SIG_C(r) | (sgn << (18 + r + 1));
 		g.dseg[lane + r * b.ds] = val;
-	}
-	else if(lane + 1 == col)
-		f |= 4u << (3 * (r + 1)); // we are the east neighbour of the west column
-	else if(lane == col + 1)
-		f |= 1u << (3 * (r + 1)); // and the west neighbour of the east column
 	// columns outside the segment are in shared memory
-	if(col == 0)
+	if(col == 0 || col == 31)
 	{
-		if(lane == 0)
-			g.fseg[-1] |= 4u << (3 * (r + 1));
+		if(lane == col)
+		{
+			uint32_t* o = col ? g.fseg + 32 : g.fseg - 1;
+			*o |= (col ? 1u : 4u) << sh;
+		}
 	}
-	else if(col == 31)
-	{
-		if(lane == 31)
-			g.fseg[32] |= 1u << (3 * (r + 1));
-	}
-	// rows of the stripes above / below: lanes 0..2 take columns col-1, col, col+1
-	if(r == 0 && !b.vsc)
+	// row 4 of the stripe above / row -1 of the stripe below: lanes 0..2 take columns col-1..col+1
+	if((r == 0 && !b.vsc) || r == 3)
 	{
 		__syncwarp(); // successive events update overlapping words from different lanes
 		if(lane < 3)
 		{
-			uint32_t* n = g.fseg - b.fs + col + lane - 1; // row 4 of the stripe above
-			*n |= lane == 1 ? ((1u << 16) | (sgn << 23)) : lane == 0 ? (1u << 17) : (1u << 15);
-		}
-	}
-	else if(r == 3)
-	{
-		__syncwarp();
-		if(lane < 3)
-		{
-			uint32_t* s = g.fseg + b.fs + col + lane - 1; // row -1 of the stripe below
-			*s |= lane == 1 ? ((1u << 1) | (sgn << 18)) : lane == 0 ? (1u << 2) : (1u << 0);
+			uint32_t* n = (r ? g.fseg + b.fs : g.fseg - b.fs) + col + lane - 1;
+			// [west, centre, east] of row -1 at bits 0..2 and its sign at bit 18; row 4: 15 higher
+			const uint32_t bits = (4u >> lane) | (lane == 1 ? sgn << (r ? 18 : 8) : 0u);
+			*n |= bits << (r ? 0 : 15);
 		}
 	}
 }
 
 // sign of a newly significant sample (T1.cpp dec_*pass "sign" step) + the bookkeeping
 template<bool RAW>
-static __device__ __forceinline__ void code_sign(const Blk& b, const Seg& g, Mq& q, uint32_t* cxs,
+static __device__ __forceinline__ void code_sign(const Blk& b, const Seg& g, Mq& q, uint32_t cxs,
 												  uint32_t& f, uint32_t& fc,
 												  uint32_t col, uint32_t r, int32_t oph)
 {
@@ -330,7 +349,7 @@ static __device__ __forceinline__ void code_sign(const Blk& b, const Seg& g, Mq&
 }
 
 // dec_clnpass, T1.cpp:934-1093
-static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t* cxs,
+static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t cxs,
 									 int bpno_plus_one, bool segsym)
 {
 	const int32_t one = 1 << bpno_plus_one, oph = one | (one >> 1);
@@ -388,7 +407,7 @@ static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t* cxs,
 
 // dec_sigpass_mqc / dec_sigpass_raw, T1.cpp:1094-1245
 template<bool RAW>
-static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t* cxs,
+static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t cxs,
 								 int bpno_plus_one)
 {
 	const int32_t one = 1 << bpno_plus_one, oph = one | (one >> 1);
@@ -444,12 +463,20 @@ static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t* cxs,
 	}
 }
 
-// dec_refpass_mqc / dec_refpass_raw, T1.cpp:1246-1364
+constexpr uint32_t CXS_LIST = 128; // byte offset of the refinement list behind the context words
+constexpr uint32_t CXS_BYTES = CXS_LIST + 128 * 2; // 19 context words (padded) + 128 list entries
+
+// dec_refpass_mqc / dec_refpass_raw, T1.cpp:1246-1364.  Everything about this pass is known
+// before it starts -- which samples are refined (significant before this bit-plane) and with
+// which context -- so the lanes write the contexts of a segment's decisions, in scan order, to a
+// list; the decision chain walks the list and leaves the decoded bits in it; the lanes then
+// apply them to their own columns.
 template<bool RAW>
-static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t* cxs,
+static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t cxs,
 								 int bpno_plus_one)
 {
 	const int32_t poshalf = (1 << bpno_plus_one) >> 1;
+	const uint32_t list = cxs + CXS_LIST, below = (1u << b.lane) - 1u;
 	for(uint32_t k = 0, s = 0; k < b.h; k += 4, ++s)
 	{
 		const uint32_t rows = min(4u, b.h - k), rowmask = (1u << rows) - 1u;
@@ -461,50 +488,42 @@ static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t* cxs,
 			const bool act = x0 + b.lane < b.w;
 			__syncwarp();
 			const uint32_t f = act ? g.fseg[b.lane] : 0u;
-			// everything about this pass is known before it starts: which samples are refined
-			// (significant before this bit-plane) and with which context
 			const uint32_t todo = sig4(f) & ~(f >> 24) & rowmask;
-			uint32_t cxpk = 0; // four context offsets, one per byte
+			// position of this column's first decision = decisions of the columns before it
+			const uint32_t cnt = __popc(todo);
+			const uint32_t b0 = __ballot_sync(FULL, cnt & 1u), b1 = __ballot_sync(FULL, cnt & 2u),
+						   b2 = __ballot_sync(FULL, cnt & 4u);
+			const uint32_t total = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
+			if(total == 0)
+				continue;
+			const uint32_t mine = list + 2 * (__popc(b0 & below) + 2 * __popc(b1 & below) + 4 * __popc(b2 & below));
 			if(!RAW)
 			{
 				const uint32_t nz = nz4(f);
+				uint32_t at = mine;
 #pragma unroll
 				for(uint32_t r = 0; r < 4; ++r)
-				{
-					const uint32_t cx = (f & T1_MU(r)) ? CX4_MAG + 8 : ((nz >> r) & 1u) ? CX4_MAG + 4 : CX4_MAG;
-					cxpk |= cx << (8 * r);
-				}
+					if((todo >> r) & 1u)
+					{
+						sts16(at, (f & T1_MU(r)) ? CX4_MAG + 8 : ((nz >> r) & 1u) ? CX4_MAG + 4 : CX4_MAG);
+						at += 2;
+					}
+				__syncwarp();
 			}
-			uint32_t colmask = __ballot_sync(FULL, todo != 0);
-			if(colmask == 0)
-				continue;
-			uint32_t bits = 0;
-			while(colmask)
-			{
-				const uint32_t col = __ffs(colmask) - 1;
-				colmask &= colmask - 1;
-				uint32_t m = __shfl_sync(FULL, todo, col);
-				const uint32_t pk = RAW ? 0u : __shfl_sync(FULL, cxpk, col);
-				uint32_t got = 0;
-				while(m)
-				{
-					const uint32_t r = __ffs(m) - 1;
-					m &= m - 1;
-					const uint32_t v = RAW ? raw_decode(q) : mq_decode(q, cxs, (pk >> (8 * r)) & 0xFFu);
-					got |= v << r;
-				}
-				if(b.lane == col)
-					bits = got;
-			}
+			for(uint32_t at = list, end = list + 2 * total; at != end; at += 2)
+				sts16(at, RAW ? raw_decode(q) : mq_decode(q, cxs, lds16(at)));
+			__syncwarp();
 			if(todo)
 			{
+				uint32_t at = mine;
 #pragma unroll
 				for(uint32_t r = 0; r < 4; ++r)
 					if((todo >> r) & 1u)
 					{
 						const uint32_t neg = (f >> (18 + r + 1)) & 1u;
 						int32_t* d = g.dseg + b.lane + r * b.ds;
-						*d += (((bits >> r) & 1u) ^ neg) ? poshalf : -poshalf;
+						*d += (lds16(at) ^ neg) ? poshalf : -poshalf;
+						at += 2;
 					}
 				g.fseg[b.lane] = f | (todo << 28);
 			}
@@ -513,17 +532,17 @@ static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t* cxs,
 }
 
 constexpr int MQ_MAX_THREADS = 256; // up to 8 warps = 8 code blocks in flight per CTA
-constexpr uint32_t CXS_BYTES = 128; // 19 context words, padded
 
-__global__ void __launch_bounds__(MQ_MAX_THREADS)
+__global__ void __launch_bounds__(MQ_MAX_THREADS, 4)
 	t1_mq_decode_kernel(const T1Launch l)
 {
 	extern __shared__ __align__(16) uint8_t smem[];
 	uint8_t* warp_base = smem;
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const size_t per_warp = CXS_BYTES + (size_t)l.max_flag_words * 4;
-	uint32_t* cxs = reinterpret_cast<uint32_t*>(warp_base + warp * per_warp);
-	uint32_t* fl = cxs + CXS_BYTES / 4;
+	uint8_t* mine = warp_base + warp * per_warp;
+	const uint32_t cxs = (uint32_t)__cvta_generic_to_shared(mine); // context words + refinement list
+	uint32_t* fl = reinterpret_cast<uint32_t*>(mine + CXS_BYTES);
 
 	for(;;)
 	{
@@ -734,7 +753,14 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 	int dev = 0, sms = 148;
 	cudaGetDevice(&dev);
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-	uint32_t ctas = (uint32_t)(sms * (best_total / best_nw));
+	int resident = 0; // CTAs per SM once registers are counted too
+	GRKB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, t1_mq_decode_kernel,
+																   best_nw * 32, smem));
+	if(resident < 1)
+		resident = 1;
+	if(resident > best_total / best_nw)
+		resident = best_total / best_nw;
+	uint32_t ctas = (uint32_t)(sms * resident);
 	const uint32_t need = (l.nblocks + best_nw - 1) / best_nw;
 	if(ctas > need)
 		ctas = need;
