@@ -1,6 +1,7 @@
 // common.cuh -- shared device/host helpers for the grok_b200 kernels (sm_100a only).
 #pragma once
 #include <cuda_runtime.h>
+#include <mutex>
 #include <stdint.h>
 #include <stdio.h>
 
@@ -18,6 +19,24 @@ void grkb_set_error(const char* fmt, ...);
 						   __LINE__, cudaGetErrorString(_e));                             \
 			return -1;                                                                    \
 		}                                                                                 \
+	} while(0)
+
+// Opt a kernel in to `bytes` of dynamic shared memory.  The attribute is per device, so what has
+// been set is remembered per device (one process may drive several: plugin deviceId = -1).
+#define GRKB_ENSURE_SMEM(kernel, bytes)                                                           \
+	do                                                                                            \
+	{                                                                                             \
+		static std::mutex _mu;                                                                    \
+		static size_t _set[64] = {};                                                              \
+		int _d = 0;                                                                               \
+		GRKB_CUDA_CHECK(cudaGetDevice(&_d));                                                      \
+		std::lock_guard<std::mutex> _lk(_mu);                                                     \
+		if(_d >= 0 && _d < 64 && (size_t)(bytes) > _set[_d])                                      \
+		{                                                                                         \
+			GRKB_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+												 (int)(bytes)));                                  \
+			_set[_d] = (size_t)(bytes);                                                           \
+		}                                                                                         \
 	} while(0)
 
 struct grkb_rect

@@ -6,15 +6,22 @@
 //   ojph_decode_codeblock          t1/t1_ht/coding/ojph_block_decoder.cpp:989-1626 (cleanup pass)
 //   ShiftHTFilter / ScaleHTFilter / RoiShiftHT / RoiScaleHT   filters/PostDecompressFilters.h:91-177
 //
-// Shape (first version): all lanes zero the block's rectangle in the coefficient plane; lane 0
-// walks the quad rows, reading the three byte streams of the segment (MEL forward, VLC
-// backward, MagSgn forward) through 64-bit register accumulators, with the CxtVLC decode
-// tables and the per-column "north" state (significance, magnitude exponent) in shared memory,
-// and stores sign-magnitude samples straight into the (L2-resident) plane; then all lanes
-// dequantise the rectangle in place with coalesced rows.  Not HBM-bound: traffic is the coded
-// bytes in and 4 B/sample out.  SigProp / MagRef passes cannot reach this decoder through Grok
-// (T1HT.cpp:171-173 passes lengths2 = 0, which ojph_block_decoder.cpp:1014-1020 rejects for
-// more than one pass); such blocks are rejected here too and counted in the status word.
+// Shape: one code block per warp.  The cleanup pass has two halves with different structure and
+// the kernel treats them differently, quad row by quad row (32 quads = 64 columns at a time):
+//   1. MEL + CxtVLC + U-VLC: a serial chain (the context of a quad needs the previous quad's
+//      significance pattern).  All lanes run it on identical register copies (one issue slot
+//      either way) and lane q keeps the result of quad q: the table word and u.  It never needs
+//      the MagSgn stream: the north context is significance only.
+//   2. MagSgn: one quad per lane.  Each lane derives its exponent bound from the north row's
+//      exponents, the bit counts of its four samples and, by a warp prefix sum, where its bits
+//      start.  The MagSgn bytes are un-stuffed 32 at a time (one ballot gives every byte's bit
+//      position) into a per-warp ring of bits in shared memory, from which the lanes pick their
+//      fields; sample reconstruction, the HT dequantiser and the store (coalesced rows of the
+//      L2-resident plane, written once) are fused here.
+// Not HBM-bound: traffic is the coded bytes in and 4 B/sample out.  SigProp / MagRef passes
+// cannot reach this decoder through Grok (T1HT.cpp:171-173 passes lengths2 = 0, which
+// ojph_block_decoder.cpp:1014-1020 rejects for more than one pass); such blocks are rejected
+// here too and counted in the status word.
 #include "t1.cuh"
 #include <mutex>
 
@@ -80,9 +87,6 @@ struct Streams
 	// VLC (backward)
 	int vlc_pos, vlc_real, vlc_unstuff, vlc_bits;
 	uint64_t vlc_acc;
-	// MagSgn (forward)
-	int ms_pos, ms_left, ms_unstuff, ms_bits;
-	uint64_t ms_acc;
 };
 
 static __device__ __forceinline__ int mel_bit(Streams& s)
@@ -162,26 +166,63 @@ static __device__ __forceinline__ void vlc_skip(Streams& s, uint32_t n)
 	s.vlc_bits -= (int)n;
 }
 
-// frwd_read<0xFF>, ojph_block_decoder.cpp:871-900
-static __device__ __forceinline__ uint32_t ms_peek(Streams& s)
+// The MagSgn stream (frwd_read<0xFF>, ojph_block_decoder.cpp:871-900) as a ring of un-stuffed
+// bits, least significant first like the reference's accumulator: a byte that follows 0xFF is
+// 7 bits wide, its eighth bit ORs with the next byte's first (kept that way for bit-exactness on
+// malformed streams); past the end the stream reads as 0xFF.  All fields are warp-uniform.
+constexpr uint32_t MS_RING_WORDS = 256; // 8192 bits: a group of 32 quads needs at most 3840
+struct MagSgn
 {
-	while(s.ms_bits < 32)
-	{
-		uint32_t b = 0xFF;
-		if(s.ms_left > 0)
-			b = __ldg(s.d + s.ms_pos);
-		s.ms_pos++;
-		s.ms_left--;
-		s.ms_acc |= (uint64_t)b << s.ms_bits;
-		s.ms_bits += 8 - s.ms_unstuff;
-		s.ms_unstuff = (b == 0xFF);
-	}
-	return (uint32_t)s.ms_acc;
+	const uint8_t* d;
+	uint32_t len, pos; // stream length, next byte to fetch
+	uint32_t prevff; // the byte before pos was 0xFF
+	uint32_t rp, wp; // read / fill position in bits of the un-stuffed stream
+	uint32_t* ring;
+};
+
+static __device__ __forceinline__ void ms_init(MagSgn& m, const uint8_t* d, uint32_t len, uint32_t* ring,
+												uint32_t lane)
+{
+	m.d = d;
+	m.len = len;
+	m.pos = 0;
+	m.prevff = 0;
+	m.rp = m.wp = 0;
+	m.ring = ring;
+	if(lane == 0)
+		ring[0] = 0;
+	__syncwarp();
 }
-static __device__ __forceinline__ void ms_skip(Streams& s, uint32_t n)
+
+// un-stuff the next 32 bytes into the ring (lane l takes byte pos + l)
+static __device__ __forceinline__ void ms_fill(MagSgn& m, uint32_t lane)
 {
-	s.ms_acc >>= n;
-	s.ms_bits -= (int)n;
+	const uint32_t i = m.pos + lane;
+	const uint32_t b = i < m.len ? (uint32_t)__ldg(m.d + i) : 0xFFu;
+	uint32_t pb = __shfl_up_sync(0xffffffffu, b, 1);
+	if(lane == 0)
+		pb = m.prevff ? 0xFFu : 0u;
+	const uint32_t narrow = __ballot_sync(0xffffffffu, pb == 0xFFu); // bytes that are 7 bits wide
+	const uint32_t at = m.wp + 8 * lane - __popc(narrow & ((1u << lane) - 1u));
+	// the words this step enters (at most 8, plus the one the last byte's eighth bit may touch)
+	if(lane < 9)
+		m.ring[((m.wp >> 5) + 1 + lane) & (MS_RING_WORDS - 1)] = 0;
+	__syncwarp();
+	const uint32_t sh = at & 31u;
+	atomicOr(&m.ring[(at >> 5) & (MS_RING_WORDS - 1)], b << sh);
+	if(sh > 24)
+		atomicOr(&m.ring[((at >> 5) + 1) & (MS_RING_WORDS - 1)], b >> (32 - sh));
+	__syncwarp();
+	m.wp += 256 - __popc(narrow);
+	m.prevff = __shfl_sync(0xffffffffu, b, 31) == 0xFFu;
+	m.pos += 32;
+}
+
+// 32 bits of the un-stuffed stream starting at bit `at`
+static __device__ __forceinline__ uint32_t ms_bits_at(const MagSgn& m, uint32_t at)
+{
+	const uint32_t i = at >> 5;
+	return __funnelshift_r(m.ring[i & (MS_RING_WORDS - 1)], m.ring[(i + 1) & (MS_RING_WORDS - 1)], at & 31u);
 }
 
 static __device__ __forceinline__ void streams_init(Streams& s, const uint8_t* d, int lcup, int scup)
@@ -203,11 +244,6 @@ static __device__ __forceinline__ void streams_init(Streams& s, const uint8_t* d
 	tnum = max(tnum, 0);
 	size -= tnum;
 	s.vlc_real = tnum + (size > 0 ? ((size + 3) >> 2) << 2 : 0);
-	s.ms_pos = 0;
-	s.ms_left = lcup - scup;
-	s.ms_unstuff = 0;
-	s.ms_bits = 0;
-	s.ms_acc = 0;
 }
 
 // prefix of one u value: returns prefix length; suffix length and base value by reference
@@ -269,97 +305,181 @@ static __device__ __forceinline__ uint32_t uvlc_decode(uint32_t vlc, uint32_t mo
 	return used;
 }
 
+// per-warp shared memory: the MagSgn ring, then the north / current exponent rows (index =
+// column + 1, and a lane may look three columns past its quad)
+static __host__ __device__ inline uint32_t ht_ncol(uint32_t max_w)
+{
+	return (((max_w + 63u) & ~63u) + 8u + 15u) & ~15u;
+}
+static __host__ __device__ inline size_t ht_warp_bytes(uint32_t max_w)
+{
+	return MS_RING_WORDS * 4 + 2 * (size_t)ht_ncol(max_w);
+}
+
 constexpr int HT_THREADS = 256; // 8 warps = 8 code blocks in flight per CTA
 
-// Cleanup pass of one block by one lane.  north/cur: per-column significance (bit 7) and
-// magnitude exponent (low 7 bits) of the bottom sample row of the previous / current quad row,
-// index = column + 1.  Returns false if the stream is rejected.
-static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missing_msbs, uint32_t w,
-								   uint32_t h, uint32_t* out, uint32_t ostride,
-								   const uint16_t* dec, uint8_t* north, uint8_t* cur, uint32_t ncol)
+// what the store needs to turn a decoded sample into the plane's value: ShiftHTFilter /
+// ScaleHTFilter and their ROI forms (PostDecompressFilters.h:91-177; the ROI forms AND the
+// shifted magnitude with the sign bit exactly as the reference does)
+struct Dequant
 {
-	const uint32_t p = 30 - missing_msbs;
+	uint32_t p; // 30 - missing_msbs: position of the magnitude's top bit
+	uint32_t shift, roishift, thresh;
+	int reversible;
+	float scale;
+};
+
+static __device__ __forceinline__ uint32_t ht_sample(const Dequant& dq, uint32_t bits, uint32_t m,
+													  uint32_t e1, uint32_t& exponent)
+{
+	uint32_t v = bits & ((1u << m) - 1u);
+	v |= e1 << m;
+	v |= 1u;
+	exponent = 32 - __clz(v);
+	uint32_t s = (bits << 31) | ((v + 2) << (dq.p - 1)); // sign-magnitude, as the block decoder leaves it
+	const uint32_t mag0 = s & 0x7FFFFFFFu;
+	if(dq.roishift && mag0 >= dq.thresh)
+		s = (mag0 >> dq.roishift) & (s & 0x80000000u);
+	const uint32_t mag = s & 0x7FFFFFFFu;
+	if(dq.reversible)
+	{
+		const int32_t sv = (int32_t)(mag >> dq.shift);
+		return (uint32_t)((s & 0x80000000u) ? -sv : sv);
+	}
+	const float f = __fmul_rn((float)(int32_t)mag, dq.scale);
+	return __float_as_uint((s & 0x80000000u) ? -f : f);
+}
+
+// Cleanup pass of one block by one warp (all lanes call this).  north/cur: per-column
+// significance (bit 7) and magnitude exponent (low 7 bits) of the bottom sample row of the
+// previous / current quad row, index = column + 1.  Returns false if the stream is rejected
+// (the caller then zeroes the block).
+static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missing_msbs, uint32_t w,
+								   uint32_t h, uint32_t* out, uint32_t ostride, const Dequant& dq,
+								   const uint16_t* dec, uint8_t* north, uint8_t* cur, uint32_t ncol,
+								   uint32_t* ring, uint32_t lane)
+{
 	const int scup = ((int)__ldg(data + lcup - 1) << 4) + (__ldg(data + lcup - 2) & 0xF);
 	if(scup < 2 || scup > lcup || scup > 4079)
 		return false;
 	Streams s;
 	streams_init(s, data, lcup, scup);
+	MagSgn ms;
+	ms_init(ms, data, (uint32_t)(lcup - scup), ring, lane);
+	for(uint32_t i = lane; i < 2 * ncol; i += 32)
+		north[i] = 0; // north and cur are adjacent
+	__syncwarp();
 	for(uint32_t y = 0; y < h; y += 2)
 	{
 		const bool initial = (y == 0);
 		const uint16_t* tbl = dec + (initial ? 0 : 1024);
 		uint32_t carry = 0;
-		for(uint32_t i = 0; i < ncol; ++i)
-			cur[i] = 0;
-		for(uint32_t x = 0; x < w; x += 4)
+		for(uint32_t xg = 0; xg < w; xg += 64)
 		{
-			uint32_t tw[2] = {0, 0};
-			const uint32_t nq = (x + 2 < w) ? 2 : 1;
-			for(uint32_t q = 0; q < nq; ++q)
+			const uint32_t xend = min(xg + 64, w);
+			// ---- 1. MEL + CxtVLC + U-VLC of up to 32 quads, the same chain in every lane
+			uint32_t myt = 0, myu = 0;
+			for(uint32_t x = xg; x < xend; x += 4)
 			{
-				const uint32_t c0 = x + 2 * q;
-				uint32_t cq = carry;
-				if(!initial)
+				uint32_t tw[2] = {0, 0};
+				const uint32_t nq = (x + 2 < w) ? 2 : 1;
+				for(uint32_t q = 0; q < nq; ++q)
 				{
-					cq |= (uint32_t)((north[c0] | north[c0 + 1]) >> 7);
-					cq |= (uint32_t)((north[c0 + 2] | north[c0 + 3]) >> 7) << 2;
-				}
-				uint32_t t = tbl[(cq << 7) | (vlc_peek(s) & 0x7F)];
-				if(cq == 0 && !mel_event(s))
-					t = 0;
-				vlc_skip(s, t & 7u);
-				tw[q] = t;
-				const uint32_t rho = (t >> 4) & 15u;
-				carry = initial ? (((rho | (rho >> 1)) & 1u) | ((rho >> 1) & 6u))
-								: ((((rho >> 2) | (rho >> 3)) & 1u) << 1);
-			}
-			uint32_t mode = ((tw[0] >> 3) & 1u) | (((tw[1] >> 3) & 1u) << 1);
-			if(initial && mode == 3 && mel_event(s))
-				mode = 4;
-			uint32_t U[2];
-			vlc_skip(s, uvlc_decode(vlc_peek(s), mode, initial, U[0], U[1]));
-			if(!initial)
-			{
-#pragma unroll
-				for(uint32_t q = 0; q < 2; ++q)
-				{
-					const uint32_t rho = (tw[q] >> 4) & 15u;
-					if(rho & (rho - 1))
+					const uint32_t c0 = x + 2 * q;
+					uint32_t cq = carry;
+					if(!initial)
 					{
-						const uint32_t c0 = x + 2 * q;
-						uint32_t E = max(max(north[c0] & 0x7Fu, north[c0 + 1] & 0x7Fu),
-										 max(north[c0 + 2] & 0x7Fu, north[c0 + 3] & 0x7Fu));
-						U[q] += E > 2 ? E - 2 : 0;
+						cq |= (uint32_t)((north[c0] | north[c0 + 1]) >> 7);
+						cq |= (uint32_t)((north[c0 + 2] | north[c0 + 3]) >> 7) << 2;
 					}
+					uint32_t t = tbl[(cq << 7) | (vlc_peek(s) & 0x7F)];
+					if(cq == 0 && !mel_event(s))
+						t = 0;
+					vlc_skip(s, t & 7u);
+					tw[q] = t;
+					const uint32_t rho = (t >> 4) & 15u;
+					carry = initial ? (((rho | (rho >> 1)) & 1u) | ((rho >> 1) & 6u))
+									: ((((rho >> 2) | (rho >> 3)) & 1u) << 1);
+				}
+				uint32_t mode = ((tw[0] >> 3) & 1u) | (((tw[1] >> 3) & 1u) << 1);
+				if(initial && mode == 3 && mel_event(s))
+					mode = 4;
+				uint32_t U[2];
+				vlc_skip(s, uvlc_decode(vlc_peek(s), mode, initial, U[0], U[1]));
+				const uint32_t qi = (x - xg) >> 1;
+				if(lane == qi)
+				{
+					myt = tw[0];
+					myu = U[0];
+				}
+				else if(lane == qi + 1)
+				{
+					myt = tw[1];
+					myu = U[1];
 				}
 			}
-			if(U[0] > missing_msbs + 1 || U[1] > missing_msbs + 1)
-				return false;
-#pragma unroll
-			for(uint32_t q = 0; q < 2; ++q)
+			// ---- 2. MagSgn, one quad per lane
+			const uint32_t c0 = xg + 2 * lane; // first column of this lane's quad
+			const bool live = c0 < xend;
+			const uint32_t rho = live ? (myt >> 4) & 15u : 0u;
+			uint32_t U = myu;
+			if(!initial && (rho & (rho - 1)))
 			{
-				const uint32_t t = tw[q], rho = (t >> 4) & 15u;
-				if(!rho)
-					continue;
+				const uint32_t E = max(max(north[c0] & 0x7Fu, north[c0 + 1] & 0x7Fu),
+									   max(north[c0 + 2] & 0x7Fu, north[c0 + 3] & 0x7Fu));
+				U += E > 2 ? E - 2 : 0;
+			}
+			if(__any_sync(0xffffffffu, live && U > missing_msbs + 1))
+				return false;
+			uint32_t mn[4], total = 0;
 #pragma unroll
-				for(uint32_t n = 0; n < 4; ++n)
+			for(uint32_t n = 0; n < 4; ++n)
+			{
+				mn[n] = ((rho >> n) & 1u) ? U - ((myt >> (8 + n)) & 1u) : 0u;
+				total += mn[n];
+			}
+			uint32_t at = total; // inclusive prefix sum over the lanes
+#pragma unroll
+			for(uint32_t d = 1; d < 32; d <<= 1)
+			{
+				const uint32_t o = __shfl_up_sync(0xffffffffu, at, d);
+				if(lane >= d)
+					at += o;
+			}
+			const uint32_t need = __shfl_sync(0xffffffffu, at, 31);
+			while(ms.wp - ms.rp < need)
+				ms_fill(ms, lane);
+			at = ms.rp + at - total;
+			ms.rp += need;
+			uint32_t val[4], ex[4];
+#pragma unroll
+			for(uint32_t n = 0; n < 4; ++n)
+			{
+				val[n] = 0;
+				ex[n] = 0;
+				if((rho >> n) & 1u)
 				{
-					if(!((rho >> n) & 1u))
-						continue;
-					const uint32_t ms = ms_peek(s);
-					const uint32_t m = U[q] - ((t >> (8 + n)) & 1u);
-					ms_skip(s, m);
-					uint32_t v = ms & ((1u << m) - 1);
-					v |= ((t >> (12 + n)) & 1u) << m;
-					v |= 1u;
-					const uint32_t col = x + 2 * q + (n >> 1), row = y + (n & 1);
-					if(col < w && row < h)
-						out[(size_t)row * ostride + col] = (ms << 31) | ((v + 2) << (p - 1));
-					if(n & 1)
-						cur[col + 1] = (uint8_t)(0x80u | (32 - __clz(v)));
+					val[n] = ht_sample(dq, ms_bits_at(ms, at), mn[n], (myt >> (12 + n)) & 1u, ex[n]);
+					ex[n] |= 0x80u;
+					at += mn[n];
 				}
+			}
+			if(live)
+			{
+				cur[c0 + 1] = (uint8_t)ex[1];
+				cur[c0 + 2] = (uint8_t)ex[3];
+#pragma unroll
+				for(uint32_t r = 0; r < 2; ++r)
+					if(y + r < h)
+					{
+						uint32_t* o = out + (size_t)(y + r) * ostride + c0;
+						o[0] = val[r];
+						if(c0 + 1 < w)
+							o[1] = val[2 + r];
+					}
 			}
 		}
+		__syncwarp();
 		uint8_t* tmp = north;
 		north = cur;
 		cur = tmp;
@@ -376,8 +496,10 @@ __global__ void __launch_bounds__(HT_THREADS)
 		dec[i] = tab->dec[0][i];
 	__syncthreads();
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const uint32_t ncol = (max_w + 8 + 15) & ~15u;
-	uint8_t* north = smem + 4096 + (size_t)warp * 2 * ncol;
+	const uint32_t ncol = ht_ncol(max_w);
+	uint8_t* mine = smem + 4096 + (size_t)warp * ht_warp_bytes(max_w);
+	uint32_t* ring = reinterpret_cast<uint32_t*>(mine);
+	uint8_t* north = mine + MS_RING_WORDS * 4;
 	uint8_t* cur = north + ncol;
 	for(;;)
 	{
@@ -393,14 +515,10 @@ __global__ void __launch_bounds__(HT_THREADS)
 			continue;
 		const uint32_t w = cb.w, h = cb.h;
 		uint32_t* blk = reinterpret_cast<uint32_t*>(l.planes[cb.comp]) + (size_t)cb.y * l.stride + cb.x;
-		for(uint32_t y = 0; y < h; ++y)
-			for(uint32_t x = lane; x < w; x += 32)
-				blk[(size_t)y * l.stride + x] = 0;
-		__syncwarp();
 		// T1HT::decompress (T1HT.cpp:134-187): a block with segments but no passes or no bytes,
 		// more than one pass (lengths2 is always 0 there), or k_msbs > 29 is an error
-		uint32_t ok = 1;
-		if(cb.numsegs != 0 && lane == 0)
+		bool decoded = false;
+		if(cb.numsegs != 0)
 		{
 			uint32_t passes = 0, len = 0;
 			for(uint32_t sgi = 0; sgi < cb.numsegs; ++sgi)
@@ -408,45 +526,29 @@ __global__ void __launch_bounds__(HT_THREADS)
 				passes += l.segs[cb.seg_first + sgi].numpasses;
 				len += l.segs[cb.seg_first + sgi].len;
 			}
-			uint32_t mm = cb.k_msbs;
-			if(passes != 1 || len < 2 || mm > 29)
-				ok = 0;
-			else
-				ok = ht_cleanup(l.bytes + cb.data_off, (int)len, mm, w, h, blk, l.stride, dec, north,
-								cur, ncol)
-						 ? 1
-						 : 0;
-			if(!ok)
+			const uint32_t mm = cb.k_msbs;
+			if(passes == 1 && len >= 2 && mm <= 29)
+			{
+				Dequant dq;
+				dq.p = 30 - mm;
+				dq.shift = 31u - (mm + 1u);
+				dq.roishift = cb.roishift;
+				dq.thresh = cb.roishift ? (1u << cb.roishift) : 0xFFFFFFFFu;
+				dq.reversible = l.reversible;
+				dq.scale = cb.scale;
+				decoded = ht_cleanup(l.bytes + cb.data_off, (int)len, mm, w, h, blk, l.stride, dq, dec, north,
+									 cur, ncol, ring, lane);
+			}
+			if(!decoded && lane == 0)
 				atomicAdd(l.status, 1u);
 		}
-		ok = __shfl_sync(0xffffffffu, ok, 0);
 		__syncwarp();
-		// dequantise in place: ShiftHTFilter / ScaleHTFilter and their ROI forms
-		// (PostDecompressFilters.h:91-177; the ROI forms AND the shifted magnitude with the sign
-		// bit exactly as the reference does)
-		const uint32_t shift = 31u - (cb.k_msbs + 1u);
-		const uint32_t thresh = cb.roishift ? (1u << cb.roishift) : 0xFFFFFFFFu;
-		for(uint32_t y = 0; y < h; ++y)
+		if(!decoded)
 		{
-			uint32_t* dst = blk + (size_t)y * l.stride;
-			for(uint32_t x = lane; x < w; x += 32)
-			{
-				uint32_t v = ok ? dst[x] : 0u;
-				const uint32_t mag0 = v & 0x7FFFFFFFu;
-				if(cb.roishift && mag0 >= thresh)
-					v = (mag0 >> cb.roishift) & (v & 0x80000000u);
-				const uint32_t mag = v & 0x7FFFFFFFu;
-				if(l.reversible)
-				{
-					const int32_t sv = (int32_t)(mag >> shift);
-					dst[x] = (uint32_t)((v & 0x80000000u) ? -sv : sv);
-				}
-				else
-				{
-					const float f = __fmul_rn((float)(int32_t)mag, cb.scale);
-					dst[x] = __float_as_uint((v & 0x80000000u) ? -f : f);
-				}
-			}
+			// empty or rejected block: zeros (0 and +0.0f are the same bits)
+			for(uint32_t y = 0; y < h; ++y)
+				for(uint32_t x = lane; x < w; x += 32)
+					blk[(size_t)y * l.stride + x] = 0;
 		}
 		__syncwarp();
 	}
@@ -464,15 +566,8 @@ int grkb_launch_t1_ht_decode(const T1Launch& l, cudaStream_t s)
 		return -1;
 	}
 	const uint32_t max_w = l.max_ht_w ? l.max_ht_w : 64;
-	const uint32_t ncol = (max_w + 8 + 15) & ~15u;
-	const size_t smem = 4096 + (size_t)(HT_THREADS / 32) * 2 * ncol;
-	static thread_local size_t configured = 0;
-	if(smem > 48 * 1024 && smem > configured)
-	{
-		GRKB_CUDA_CHECK(cudaFuncSetAttribute(t1_ht_decode_kernel,
-											 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		configured = smem;
-	}
+	const size_t smem = 4096 + (size_t)(HT_THREADS / 32) * ht_warp_bytes(max_w);
+	GRKB_ENSURE_SMEM(t1_ht_decode_kernel, smem);
 	int dev = 0, sms = 148;
 	cudaGetDevice(&dev);
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

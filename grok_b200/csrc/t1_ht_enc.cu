@@ -537,13 +537,7 @@ int grkb_launch_t1_ht_encode(const T1EncLaunch& l, cudaStream_t s)
 		grkb_set_error("t1 ht encode: code block too wide for shared memory");
 		return -1;
 	}
-	static thread_local size_t configured = 0;
-	if(smem > configured)
-	{
-		GRKB_CUDA_CHECK(cudaFuncSetAttribute(t1_ht_encode_kernel,
-											 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		configured = smem;
-	}
+	GRKB_ENSURE_SMEM(t1_ht_encode_kernel, smem);
 	int dev = 0, sms = 148;
 	cudaGetDevice(&dev);
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -689,8 +689,8 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 	if(l.nblocks == 0)
 		return 0;
 	// GRKB_T1_MQ_KERNEL=simt selects the one-block-per-lane kernel of t1_mq_dec_simt.cu (same
-	// results; measured 3.5x slower on 64x64 blocks, where its 2.4 KB of state per lane leave
-	// room for only two warps per SM -- see DESIGN.md section 4); the default is this file's
+	// results; measured 8x slower on 64x64 blocks, where its 2.4 KB of state per lane leave room
+	// for only two warps per SM -- see DESIGN.md section 4); the default is this file's
 	// one-block-per-warp kernel
 	static int simt = -1;
 	if(simt < 0)
@@ -711,6 +711,13 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 	}
 	const size_t per_warp = CXS_BYTES + (size_t)l.max_flag_words * 4;
 	const size_t fixed = 0;
+	int dev = 0, sms = 148;
+	if(cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+	{
+		grkb_set_error("t1: no current device");
+		return -1;
+	}
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
 	// warps per CTA: whatever packs most code blocks into the 227 KB of an SM
 	static int max_warps_sm = -1;
 	if(max_warps_sm < 0)
@@ -743,16 +750,7 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 		return -1;
 	}
 	const size_t smem = fixed + per_warp * best_nw;
-	static thread_local size_t configured = 0;
-	if(smem > configured)
-	{
-		GRKB_CUDA_CHECK(cudaFuncSetAttribute(t1_mq_decode_kernel,
-											 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		configured = smem;
-	}
-	int dev = 0, sms = 148;
-	cudaGetDevice(&dev);
-	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+	GRKB_ENSURE_SMEM(t1_mq_decode_kernel, smem);
 	int resident = 0; // CTAs per SM once registers are counted too
 	GRKB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, t1_mq_decode_kernel,
 																   best_nw * 32, smem));

@@ -633,13 +633,7 @@ int grkb_launch_t1_mq_decode_simt(const T1Launch& l, cudaStream_t s)
 	if(nw > SIMT_WARPS_MAX)
 		nw = SIMT_WARPS_MAX;
 	const size_t smem = fixed + per_warp * nw;
-	static thread_local size_t configured = 0;
-	if(smem > configured)
-	{
-		GRKB_CUDA_CHECK(cudaFuncSetAttribute(t1_mq_decode_simt_kernel,
-											 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-		configured = smem;
-	}
+	GRKB_ENSURE_SMEM(t1_mq_decode_simt_kernel, smem);
 	int dev = 0, sms = 148;
 	cudaGetDevice(&dev);
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
