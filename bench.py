@@ -274,31 +274,33 @@ def run_ours(args):
     barrier()
     ms = tm["total_ms"]
     # ---- e2e: through the C-ABI with pinned host buffers, every step's H2D (descriptors +
-    # coded bytes) and D2H (three int32 planes) inside the timed region.  Two decoders keep two
-    # frames in flight (submit frame i, then wait for frame i-1), so one frame's D2H overlaps the
-    # next frame's H2D + kernels; each step still moves and decodes a whole frame.
-    dec2 = T.TileDecoder(params, len(blocks), data.size)
-    pin_out2 = [T.PinnedArray((H, W), np.int32) for _ in range(NCOMP)]
-    decs = [(dec, out), (dec2, [p.array for p in pin_out2])]
+    # coded bytes) and D2H (three int32 planes) inside the timed region.  K decoders keep K
+    # frames in flight (submit frame i, then wait for frame i-K+1), so one frame's D2H overlaps the
+    # next frames' H2D + kernels; each step still moves and decodes a whole frame.
+    K = max(1, args.inflight)
+    decs = [(dec, out)]
+    for _ in range(K - 1):
+        pin_k = [T.PinnedArray((H, W), np.int32) for _ in range(NCOMP)]
+        decs.append((T.TileDecoder(params, len(blocks), data.size), [p.array for p in pin_k]))
 
     def e2e_pass(n):
         for i in range(n):
-            d, o = decs[i & 1]
-            if i >= 2:
+            d, o = decs[i % K]
+            if i >= K:
                 d.wait()
             d.submit(blocks, segs, pin_data.array, o)
-        for i in range(max(n - 2, 0), n):
-            decs[i & 1][0].wait()
+        for i in range(max(n - K, 0), n):
+            decs[i % K][0].wait()
 
-    e2e_pass(max(min(args.warmup, 3), 2))
+    e2e_pass(max(min(args.warmup, 3), K))
     barrier()
     t0 = time.perf_counter()
     e2e_pass(args.steps)
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
     barrier()
-    if dec.rejected or dec2.rejected or not all(
-            np.array_equal(a, b) for a, b in zip(decs[0][1], decs[1][1])):
-        raise SystemExit("bench.py: pipelined decode disagrees between the two decoders")
+    if any(d.rejected for d, _ in decs) or not all(
+            np.array_equal(a, b) for _, o in decs[1:] for a, b in zip(decs[0][1], o)):
+        raise SystemExit("bench.py: pipelined decode disagrees between the decoders in flight")
     clocks = sampler.stop() if sampler else None
     if dist is not None:
         import torch
@@ -346,7 +348,7 @@ def run_ours(args):
                    "frames_per_step": world, "sharding": "one frame per GPU per step, no collective",
                    "l2": "working set per step (coded bytes + 2 x %d MB planes) exceeds the 126 MB L2"
                          % (NCOMP * W * H * 4 // 1000000)},
-        "e2e": {"value": world * mp / (e2e_ms * 1e-3), "unit": "Mpixel/s", "frames_in_flight": 2,
+        "e2e": {"value": world * mp / (e2e_ms * 1e-3), "unit": "Mpixel/s", "frames_in_flight": K,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
         "gpu_launches": int(tm["launches"]) * args.steps,
         "roofline": {"bound": "hbm", "kernel": "idwt_level_kernel<%s,3 comps,fused %s> (last level)"
@@ -376,6 +378,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="j2k97", choices=["j2k97", "ht"])
+    ap.add_argument("--inflight", type=int, default=2, help="decoders (frames) in flight on the e2e leg")
     args = ap.parse_args()
     select_workload(args.workload)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -84,10 +84,15 @@ struct Streams
 	int mel_pos, mel_left;
 	uint32_t mel_acc;
 	int mel_bits, mel_unstuff, mel_k, mel_run, mel_one;
-	// VLC (backward)
-	int vlc_pos, vlc_real, vlc_unstuff, vlc_bits;
-	uint64_t vlc_acc;
+	// VLC (backward), as a ring of un-stuffed bits like the MagSgn stream below
+	int vlc_a0, vlc_real; // offset of the first byte read; bytes delivered before zeros
+	uint32_t vlc_k; // bytes read so far
+	uint32_t vlc_unstuff; // the last byte read was > 0x8F
+	uint32_t vlc_rp, vlc_wp; // read / fill position in bits
+	uint32_t* vlc_ring;
 };
+constexpr uint32_t VLC_RING_WORDS = 128; // 4096 bits: 32 quads use at most 544
+constexpr uint32_t VLC_AHEAD = 768; // bits made available before a group of 32 quads
 
 static __device__ __forceinline__ int mel_bit(Streams& s)
 {
@@ -141,29 +146,40 @@ static __device__ __forceinline__ int mel_event(Streams& s)
 	return 1;
 }
 
-// rev_read, ojph_block_decoder.cpp:327-365 (byte-wise; bytes before the block start read as 0)
-static __device__ __forceinline__ uint32_t vlc_peek(Streams& s)
+// rev_read, ojph_block_decoder.cpp:327-365: the VLC bytes are read backwards; a byte whose low
+// seven bits are all ones is 7 bits wide when the byte read before it was > 0x8F; bytes before
+// the block start, or past what the reference delivers, read as 0.  32 bytes per step, lane l
+// takes the l-th; one ballot gives every byte's bit position.
+static __device__ __forceinline__ void vlc_fill(Streams& s, uint32_t lane)
 {
-	while(s.vlc_bits < 32)
-	{
-		uint32_t b = 0;
-		if(s.vlc_real > 0)
-		{
-			b = s.vlc_pos >= 0 ? (uint32_t)__ldg(s.d + s.vlc_pos) : 0u;
-			s.vlc_real--;
-		}
-		s.vlc_pos--;
-		const int w = 8 - ((s.vlc_unstuff && (b & 0x7F) == 0x7F) ? 1 : 0);
-		s.vlc_acc |= (uint64_t)b << s.vlc_bits;
-		s.vlc_bits += w;
-		s.vlc_unstuff = b > 0x8F;
-	}
-	return (uint32_t)s.vlc_acc;
+	const uint32_t k = s.vlc_k + lane;
+	const int a = s.vlc_a0 - (int)k;
+	const uint32_t b = ((int)k < s.vlc_real && a >= 0) ? (uint32_t)__ldg(s.d + a) : 0u;
+	const uint32_t pb = __shfl_up_sync(0xffffffffu, b, 1);
+	const bool un = lane ? pb > 0x8Fu : s.vlc_unstuff != 0;
+	const uint32_t narrow = __ballot_sync(0xffffffffu, un && (b & 0x7Fu) == 0x7Fu);
+	const uint32_t at = s.vlc_wp + 8 * lane - __popc(narrow & ((1u << lane) - 1u));
+	if(lane < 9)
+		s.vlc_ring[((s.vlc_wp >> 5) + 1 + lane) & (VLC_RING_WORDS - 1)] = 0;
+	__syncwarp();
+	const uint32_t sh = at & 31u;
+	atomicOr(&s.vlc_ring[(at >> 5) & (VLC_RING_WORDS - 1)], b << sh);
+	if(sh > 24)
+		atomicOr(&s.vlc_ring[((at >> 5) + 1) & (VLC_RING_WORDS - 1)], b >> (32 - sh));
+	__syncwarp();
+	s.vlc_wp += 256 - __popc(narrow);
+	s.vlc_unstuff = __shfl_sync(0xffffffffu, b, 31) > 0x8Fu;
+	s.vlc_k += 32;
+}
+static __device__ __forceinline__ uint32_t vlc_peek(const Streams& s)
+{
+	const uint32_t i = s.vlc_rp >> 5;
+	return __funnelshift_r(s.vlc_ring[i & (VLC_RING_WORDS - 1)], s.vlc_ring[(i + 1) & (VLC_RING_WORDS - 1)],
+						   s.vlc_rp & 31u);
 }
 static __device__ __forceinline__ void vlc_skip(Streams& s, uint32_t n)
 {
-	s.vlc_acc >>= n;
-	s.vlc_bits -= (int)n;
+	s.vlc_rp += n;
 }
 
 // The MagSgn stream (frwd_read<0xFF>, ojph_block_decoder.cpp:871-900) as a ring of un-stuffed
@@ -225,25 +241,33 @@ static __device__ __forceinline__ uint32_t ms_bits_at(const MagSgn& m, uint32_t 
 	return __funnelshift_r(m.ring[i & (MS_RING_WORDS - 1)], m.ring[(i + 1) & (MS_RING_WORDS - 1)], at & 31u);
 }
 
-static __device__ __forceinline__ void streams_init(Streams& s, const uint8_t* d, int lcup, int scup)
+static __device__ __forceinline__ void streams_init(Streams& s, const uint8_t* d, int lcup, int scup,
+													 uint32_t* vlc_ring, uint32_t lane)
 {
 	s.d = d;
 	s.mel_pos = lcup - scup;
 	s.mel_left = scup - 1;
 	s.mel_acc = 0;
 	s.mel_bits = s.mel_unstuff = s.mel_k = s.mel_run = s.mel_one = 0;
+	// rev_init, :392-421: the first four bits come from the byte that also holds Scup's low half
 	const uint32_t first = __ldg(d + lcup - 2);
-	s.vlc_acc = first >> 4;
-	s.vlc_bits = 4 - (((s.vlc_acc & 7) == 7) ? 1 : 0);
+	const uint32_t acc = first >> 4;
+	s.vlc_ring = vlc_ring;
+	if(lane == 0)
+		vlc_ring[0] = acc;
+	s.vlc_rp = 0;
+	s.vlc_wp = 4 - (((acc & 7) == 7) ? 1 : 0);
 	s.vlc_unstuff = (first | 0xF) > 0x8F;
-	s.vlc_pos = lcup - 3;
+	s.vlc_a0 = lcup - 3;
+	s.vlc_k = 0;
 	// real bytes the reference delivers before zeros: 1 + (address & 3) single bytes, then whole
-	// 32-bit words while any byte of the segment is left (rev_init, :392-421)
+	// 32-bit words while any byte of the segment is left
 	int size = scup - 2;
-	int tnum = min(1 + (s.vlc_pos & 3), size);
+	int tnum = min(1 + (s.vlc_a0 & 3), size);
 	tnum = max(tnum, 0);
 	size -= tnum;
 	s.vlc_real = tnum + (size > 0 ? ((size + 3) >> 2) << 2 : 0);
+	__syncwarp();
 }
 
 // prefix of one u value: returns prefix length; suffix length and base value by reference
@@ -305,15 +329,18 @@ static __device__ __forceinline__ uint32_t uvlc_decode(uint32_t vlc, uint32_t mo
 	return used;
 }
 
-// per-warp shared memory: the MagSgn ring, then the north / current exponent rows (index =
-// column + 1, and a lane may look three columns past its quad)
+// per-warp shared memory: the MagSgn ring, the VLC ring, the bottom-row significance masks of the
+// previous / current quad row (one even-column and one odd-column word per 64 columns), then
+// the north / current exponent rows (index = column + 1, a lane may look three columns past its
+// quad)
+constexpr uint32_t HT_MAX_GROUPS = 16; // code blocks are at most 1024 wide
 static __host__ __device__ inline uint32_t ht_ncol(uint32_t max_w)
 {
 	return (((max_w + 63u) & ~63u) + 8u + 15u) & ~15u;
 }
 static __host__ __device__ inline size_t ht_warp_bytes(uint32_t max_w)
 {
-	return MS_RING_WORDS * 4 + 2 * (size_t)ht_ncol(max_w);
+	return (MS_RING_WORDS + VLC_RING_WORDS + 4 * HT_MAX_GROUPS) * 4 + 2 * (size_t)ht_ncol(max_w);
 }
 
 constexpr int HT_THREADS = 256; // 8 warps = 8 code blocks in flight per CTA
@@ -357,17 +384,20 @@ static __device__ __forceinline__ uint32_t ht_sample(const Dequant& dq, uint32_t
 static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missing_msbs, uint32_t w,
 								   uint32_t h, uint32_t* out, uint32_t ostride, const Dequant& dq,
 								   const uint16_t* dec, uint8_t* north, uint8_t* cur, uint32_t ncol,
-								   uint32_t* ring, uint32_t lane)
+								   uint32_t* ring, uint32_t* vlc_ring, uint32_t* sig, uint32_t lane)
 {
 	const int scup = ((int)__ldg(data + lcup - 1) << 4) + (__ldg(data + lcup - 2) & 0xF);
 	if(scup < 2 || scup > lcup || scup > 4079)
 		return false;
 	Streams s;
-	streams_init(s, data, lcup, scup);
+	streams_init(s, data, lcup, scup, vlc_ring, lane);
 	MagSgn ms;
 	ms_init(ms, data, (uint32_t)(lcup - scup), ring, lane);
 	for(uint32_t i = lane; i < 2 * ncol; i += 32)
 		north[i] = 0; // north and cur are adjacent
+	// significance of the bottom sample row, per 64 columns: [0] even columns, [1] odd columns
+	uint32_t* psig = sig; // previous quad row
+	uint32_t* csig = sig + 2 * HT_MAX_GROUPS;
 	__syncwarp();
 	for(uint32_t y = 0; y < h; y += 2)
 	{
@@ -376,8 +406,18 @@ static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missin
 		uint32_t carry = 0;
 		for(uint32_t xg = 0; xg < w; xg += 64)
 		{
-			const uint32_t xend = min(xg + 64, w);
+			const uint32_t xend = min(xg + 64, w), g = xg >> 6;
 			// ---- 1. MEL + CxtVLC + U-VLC of up to 32 quads, the same chain in every lane
+			while(s.vlc_wp - s.vlc_rp < VLC_AHEAD)
+				vlc_fill(s, lane);
+			// north context of quad q: bit 0 = columns 2q-1 | 2q, bit 2 = columns 2q+1 | 2q+2
+			uint32_t north0 = 0, north2 = 0;
+			if(!initial)
+			{
+				const uint32_t ev = psig[2 * g], od = psig[2 * g + 1];
+				north0 = (od << 1) | ev | (g ? psig[2 * g - 1] >> 31 : 0u);
+				north2 = od | (ev >> 1) | (xg + 64 < w ? psig[2 * g + 2] << 31 : 0u);
+			}
 			uint32_t myt = 0, myu = 0;
 			for(uint32_t x = xg; x < xend; x += 4)
 			{
@@ -385,13 +425,8 @@ static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missin
 				const uint32_t nq = (x + 2 < w) ? 2 : 1;
 				for(uint32_t q = 0; q < nq; ++q)
 				{
-					const uint32_t c0 = x + 2 * q;
-					uint32_t cq = carry;
-					if(!initial)
-					{
-						cq |= (uint32_t)((north[c0] | north[c0 + 1]) >> 7);
-						cq |= (uint32_t)((north[c0 + 2] | north[c0 + 3]) >> 7) << 2;
-					}
+					const uint32_t qi = ((x - xg) >> 1) + q;
+					const uint32_t cq = carry | ((north0 >> qi) & 1u) | (((north2 >> qi) & 1u) << 2);
 					uint32_t t = tbl[(cq << 7) | (vlc_peek(s) & 0x7F)];
 					if(cq == 0 && !mel_event(s))
 						t = 0;
@@ -464,6 +499,14 @@ static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missin
 					at += mn[n];
 				}
 			}
+			{
+				const uint32_t ev = __ballot_sync(0xffffffffu, ex[1] != 0), od = __ballot_sync(0xffffffffu, ex[3] != 0);
+				if(lane == 0)
+				{
+					csig[2 * g] = ev;
+					csig[2 * g + 1] = od;
+				}
+			}
 			if(live)
 			{
 				cur[c0 + 1] = (uint8_t)ex[1];
@@ -483,6 +526,9 @@ static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missin
 		uint8_t* tmp = north;
 		north = cur;
 		cur = tmp;
+		uint32_t* tsig = psig;
+		psig = csig;
+		csig = tsig;
 	}
 	return true;
 }
@@ -499,7 +545,9 @@ __global__ void __launch_bounds__(HT_THREADS)
 	const uint32_t ncol = ht_ncol(max_w);
 	uint8_t* mine = smem + 4096 + (size_t)warp * ht_warp_bytes(max_w);
 	uint32_t* ring = reinterpret_cast<uint32_t*>(mine);
-	uint8_t* north = mine + MS_RING_WORDS * 4;
+	uint32_t* vlc_ring = ring + MS_RING_WORDS;
+	uint32_t* sig = vlc_ring + VLC_RING_WORDS;
+	uint8_t* north = reinterpret_cast<uint8_t*>(sig + 4 * HT_MAX_GROUPS);
 	uint8_t* cur = north + ncol;
 	for(;;)
 	{
@@ -537,7 +585,7 @@ __global__ void __launch_bounds__(HT_THREADS)
 				dq.reversible = l.reversible;
 				dq.scale = cb.scale;
 				decoded = ht_cleanup(l.bytes + cb.data_off, (int)len, mm, w, h, blk, l.stride, dq, dec, north,
-									 cur, ncol, ring, lane);
+									 cur, ncol, ring, vlc_ring, sig, lane);
 			}
 			if(!decoded && lane == 0)
 				atomicAdd(l.status, 1u);
