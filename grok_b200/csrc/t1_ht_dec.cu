@@ -29,23 +29,87 @@
 
 namespace
 {
-// device decode table entry: len | u_off << 3 | rho << 4 | e_k << 8 | e_1 << 12
+// Decode tables in constant memory (the VLC chain runs replicated, so every lane reads the same
+// entry).  CxtVLC entry: len | u_off << 3 | rho << 4 | e_k << 8 | e_1 << 12 | context carried to
+// the next quad << 16.  U-VLC entry (indexed by row kind, mode, six stream bits):
+// prefix bits | width A << 3 | width B << 6 | base A << 9 | base B << 14 | swap << 19, where A and
+// B are the two fields that follow the prefixes in stream order and swap says that A is u1.
 struct HtTables
 {
-	uint16_t dec[2][1024];
+	uint32_t vlc[2][1024];
+	uint32_t uvlc[2][8][64];
 };
+__constant__ HtTables c_ht;
+
+// prefix of one u value: returns prefix length; suffix length and base value by reference
+// (decode_init_uvlc / decode_noninit_uvlc, ojph_block_decoder.cpp:664-838)
+static uint32_t uvlc_prefix(uint32_t bits, uint32_t& suf, uint32_t& base)
+{
+	if(bits & 1)
+	{
+		suf = 0;
+		base = 1;
+		return 1;
+	}
+	if(bits & 2)
+	{
+		suf = 0;
+		base = 2;
+		return 2;
+	}
+	suf = (bits & 4) ? 1 : 5;
+	base = (bits & 4) ? 3 : 5;
+	return 3;
+}
+
+static uint32_t uvlc_entry(uint32_t bits, uint32_t mode, bool initial)
+{
+	uint32_t plen = 0, wa = 0, wb = 0, ba = 1, bb = 1, swap = 0, s0, b0, s1, b1;
+	if(mode == 1 || mode == 2)
+	{
+		plen = uvlc_prefix(bits, s0, b0);
+		wa = s0;
+		ba = b0 + 1;
+		swap = mode == 2; // the only coded value is u1
+	}
+	else if(mode >= 3)
+	{
+		const uint32_t p0 = uvlc_prefix(bits, s0, b0);
+		if(initial && mode == 3 && p0 > 2)
+		{
+			// one bit of u1 comes before u0's suffix
+			plen = p0;
+			wa = 1;
+			ba = 2;
+			wb = s0;
+			bb = b0 + 1;
+			swap = 1;
+		}
+		else
+		{
+			const uint32_t p1 = uvlc_prefix(bits >> p0, s1, b1);
+			const uint32_t off = (initial && mode == 4) ? 3 : 1;
+			plen = p0 + p1;
+			wa = s0;
+			ba = b0 + off;
+			wb = s1;
+			bb = b1 + off;
+		}
+	}
+	return plen | (wa << 3) | (wb << 6) | (ba << 9) | (bb << 14) | (swap << 19);
+}
 
 std::mutex g_mu;
-HtTables* g_dev[64] = {};
+bool g_done[64] = {};
 
-const HtTables* ht_tables_device()
+int ht_tables_upload()
 {
 	int dev = 0;
 	if(cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
-		return nullptr;
+		return -1;
 	std::lock_guard<std::mutex> lk(g_mu);
-	if(g_dev[dev])
-		return g_dev[dev];
+	if(g_done[dev])
+		return 0;
 	static HtTables h;
 	for(int t = 0; t < 2; ++t)
 	{
@@ -53,28 +117,28 @@ const HtTables* ht_tables_device()
 		const size_t n = t ? sizeof(HT_CXTVLC_ROWN) / 4 : sizeof(HT_CXTVLC_ROW0) / 4;
 		for(uint32_t i = 0; i < 1024; ++i)
 		{
-			uint16_t e = 0;
+			uint32_t e = 0;
 			for(size_t j = 0; j < n; ++j)
 			{
 				const uint32_t w = src[j];
 				const uint32_t len = (w >> 23) & 7u;
 				if((w & 7u) == (i >> 7) && ((w >> 16) & 127u) == ((i & 127u) & ((1u << len) - 1)))
-					e = (uint16_t)(len | (((w >> 7) & 1u) << 3) | (((w >> 3) & 15u) << 4) |
-								   (((w >> 8) & 15u) << 8) | (((w >> 12) & 15u) << 12));
+					e = len | (((w >> 7) & 1u) << 3) | (((w >> 3) & 15u) << 4) | (((w >> 8) & 15u) << 8) |
+						(((w >> 12) & 15u) << 12);
 			}
-			h.dec[t][i] = e;
+			const uint32_t rho = (e >> 4) & 15u;
+			const uint32_t carry = t ? ((((rho >> 2) | (rho >> 3)) & 1u) << 1)
+									 : (((rho | (rho >> 1)) & 1u) | ((rho >> 1) & 6u));
+			h.vlc[t][i] = e | (carry << 16);
 		}
+		for(uint32_t mode = 0; mode < 8; ++mode)
+			for(uint32_t bits = 0; bits < 64; ++bits)
+				h.uvlc[t][mode][bits] = uvlc_entry(bits, mode > 4 ? 0 : mode, t == 0);
 	}
-	HtTables* d = nullptr;
-	if(cudaMalloc(&d, sizeof(HtTables)) != cudaSuccess)
-		return nullptr;
-	if(cudaMemcpy(d, &h, sizeof(HtTables), cudaMemcpyHostToDevice) != cudaSuccess)
-	{
-		cudaFree(d);
-		return nullptr;
-	}
-	g_dev[dev] = d;
-	return d;
+	if(cudaMemcpyToSymbol(c_ht, &h, sizeof(h)) != cudaSuccess)
+		return -1;
+	g_done[dev] = true;
+	return 0;
 }
 
 struct Streams
@@ -171,17 +235,6 @@ static __device__ __forceinline__ void vlc_fill(Streams& s, uint32_t lane)
 	s.vlc_unstuff = __shfl_sync(0xffffffffu, b, 31) > 0x8Fu;
 	s.vlc_k += 32;
 }
-static __device__ __forceinline__ uint32_t vlc_peek(const Streams& s)
-{
-	const uint32_t i = s.vlc_rp >> 5;
-	return __funnelshift_r(s.vlc_ring[i & (VLC_RING_WORDS - 1)], s.vlc_ring[(i + 1) & (VLC_RING_WORDS - 1)],
-						   s.vlc_rp & 31u);
-}
-static __device__ __forceinline__ void vlc_skip(Streams& s, uint32_t n)
-{
-	s.vlc_rp += n;
-}
-
 // The MagSgn stream (frwd_read<0xFF>, ojph_block_decoder.cpp:871-900) as a ring of un-stuffed
 // bits, least significant first like the reference's accumulator: a byte that follows 0xFF is
 // 7 bits wide, its eighth bit ORs with the next byte's first (kept that way for bit-exactness on
@@ -270,67 +323,25 @@ static __device__ __forceinline__ void streams_init(Streams& s, const uint8_t* d
 	__syncwarp();
 }
 
-// prefix of one u value: returns prefix length; suffix length and base value by reference
-static __device__ __forceinline__ uint32_t uvlc_prefix(uint32_t bits, uint32_t& suf, uint32_t& base)
-{
-	if(bits & 1)
-	{
-		suf = 0;
-		base = 1;
-		return 1;
-	}
-	if(bits & 2)
-	{
-		suf = 0;
-		base = 2;
-		return 2;
-	}
-	suf = (bits & 4) ? 1 : 5;
-	base = (bits & 4) ? 3 : 5;
-	return 3;
-}
-
-// decode_init_uvlc / decode_noninit_uvlc, ojph_block_decoder.cpp:664-838
-static __device__ __forceinline__ uint32_t uvlc_decode(uint32_t vlc, uint32_t mode, bool initial,
+// the two u values of a quad pair from the table entry and the stream bits; returns bits used
+static __device__ __forceinline__ uint32_t uvlc_decode(uint32_t vlc, uint32_t mode, uint32_t row,
 														uint32_t& u0, uint32_t& u1)
 {
-	uint32_t used, s0, b0, s1, b1, p;
-	u0 = u1 = 1;
-	if(mode == 0)
-		return 0;
-	if(mode <= 2)
-	{
-		p = uvlc_prefix(vlc, s0, b0);
-		vlc >>= p;
-		b0 += vlc & ((1u << s0) - 1);
-		if(mode == 1)
-			u0 = b0 + 1;
-		else
-			u1 = b0 + 1;
-		return p + s0;
-	}
-	p = uvlc_prefix(vlc, s0, b0);
-	vlc >>= p;
-	used = p;
-	if(initial && mode == 3 && p > 2)
-	{
-		u1 = (vlc & 1) + 2;
-		vlc >>= 1;
-		u0 = b0 + (vlc & ((1u << s0) - 1)) + 1;
-		return used + 1 + s0;
-	}
-	p = uvlc_prefix(vlc, s1, b1);
-	vlc >>= p;
-	used += p + s0 + s1;
-	const uint32_t off = (initial && mode == 4) ? 3 : 1;
-	u0 = b0 + (vlc & ((1u << s0) - 1)) + off;
-	vlc >>= s0;
-	u1 = b1 + (vlc & ((1u << s1) - 1)) + off;
-	return used;
+	const uint32_t e = c_ht.uvlc[row][mode][vlc & 63u];
+	const uint32_t plen = e & 7u, wa = (e >> 3) & 7u, wb = (e >> 6) & 7u;
+	vlc >>= plen;
+	const uint32_t fa = ((e >> 9) & 31u) + (vlc & ((1u << wa) - 1u));
+	vlc >>= wa;
+	const uint32_t fb = ((e >> 14) & 31u) + (vlc & ((1u << wb) - 1u));
+	const bool swap = (e >> 19) & 1u;
+	u0 = swap ? fb : fa;
+	u1 = swap ? fa : fb;
+	return plen + wa + wb;
 }
 
 // per-warp shared memory: the MagSgn ring, the VLC ring, the bottom-row significance masks of the
-// previous / current quad row (one even-column and one odd-column word per 64 columns), then
+// previous / current quad row (one even-column and one odd-column word per 64 columns), the
+// (table word, u) of the 32 quads of a group, then
 // the north / current exponent rows (index = column + 1, a lane may look three columns past its
 // quad)
 constexpr uint32_t HT_MAX_GROUPS = 16; // code blocks are at most 1024 wide
@@ -340,7 +351,7 @@ static __host__ __device__ inline uint32_t ht_ncol(uint32_t max_w)
 }
 static __host__ __device__ inline size_t ht_warp_bytes(uint32_t max_w)
 {
-	return (MS_RING_WORDS + VLC_RING_WORDS + 4 * HT_MAX_GROUPS) * 4 + 2 * (size_t)ht_ncol(max_w);
+	return (MS_RING_WORDS + VLC_RING_WORDS + 4 * HT_MAX_GROUPS + 64) * 4 + 2 * (size_t)ht_ncol(max_w);
 }
 
 constexpr int HT_THREADS = 256; // 8 warps = 8 code blocks in flight per CTA
@@ -383,8 +394,8 @@ static __device__ __forceinline__ uint32_t ht_sample(const Dequant& dq, uint32_t
 // (the caller then zeroes the block).
 static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missing_msbs, uint32_t w,
 								   uint32_t h, uint32_t* out, uint32_t ostride, const Dequant& dq,
-								   const uint16_t* dec, uint8_t* north, uint8_t* cur, uint32_t ncol,
-								   uint32_t* ring, uint32_t* vlc_ring, uint32_t* sig, uint32_t lane)
+								   uint8_t* north, uint8_t* cur, uint32_t ncol, uint32_t* ring,
+								   uint32_t* vlc_ring, uint32_t* sig, uint2* quads, uint32_t lane)
 {
 	const int scup = ((int)__ldg(data + lcup - 1) << 4) + (__ldg(data + lcup - 2) & 0xF);
 	if(scup < 2 || scup > lcup || scup > 4079)
@@ -402,7 +413,7 @@ static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missin
 	for(uint32_t y = 0; y < h; y += 2)
 	{
 		const bool initial = (y == 0);
-		const uint16_t* tbl = dec + (initial ? 0 : 1024);
+		const uint32_t row = initial ? 0u : 1u; // which CxtVLC / U-VLC table
 		uint32_t carry = 0;
 		for(uint32_t xg = 0; xg < w; xg += 64)
 		{
@@ -410,6 +421,18 @@ static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missin
 			// ---- 1. MEL + CxtVLC + U-VLC of up to 32 quads, the same chain in every lane
 			while(s.vlc_wp - s.vlc_rp < VLC_AHEAD)
 				vlc_fill(s, lane);
+			// the two ring words under the VLC read position stay in registers
+			uint32_t vi = s.vlc_rp >> 5;
+			uint32_t vw0 = s.vlc_ring[vi & (VLC_RING_WORDS - 1)], vw1 = s.vlc_ring[(vi + 1) & (VLC_RING_WORDS - 1)];
+			auto vlc_skip = [&](uint32_t n) {
+				s.vlc_rp += n;
+				if((s.vlc_rp >> 5) != vi)
+				{
+					vi = s.vlc_rp >> 5;
+					vw0 = vw1;
+					vw1 = s.vlc_ring[(vi + 1) & (VLC_RING_WORDS - 1)];
+				}
+			};
 			// north context of quad q: bit 0 = columns 2q-1 | 2q, bit 2 = columns 2q+1 | 2q+2
 			uint32_t north0 = 0, north2 = 0;
 			if(!initial)
@@ -418,44 +441,35 @@ static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missin
 				north0 = (od << 1) | ev | (g ? psig[2 * g - 1] >> 31 : 0u);
 				north2 = od | (ev >> 1) | (xg + 64 < w ? psig[2 * g + 2] << 31 : 0u);
 			}
-			uint32_t myt = 0, myu = 0;
-			for(uint32_t x = xg; x < xend; x += 4)
+			for(uint32_t x = xg, qi = 0; x < xend; x += 4, qi += 2)
 			{
 				uint32_t tw[2] = {0, 0};
 				const uint32_t nq = (x + 2 < w) ? 2 : 1;
 				for(uint32_t q = 0; q < nq; ++q)
 				{
-					const uint32_t qi = ((x - xg) >> 1) + q;
-					const uint32_t cq = carry | ((north0 >> qi) & 1u) | (((north2 >> qi) & 1u) << 2);
-					uint32_t t = tbl[(cq << 7) | (vlc_peek(s) & 0x7F)];
+					const uint32_t cq = carry | ((north0 >> (qi + q)) & 1u) | (((north2 >> (qi + q)) & 1u) << 2);
+					uint32_t t = c_ht.vlc[row][(cq << 7) | (__funnelshift_r(vw0, vw1, s.vlc_rp) & 0x7F)];
 					if(cq == 0 && !mel_event(s))
 						t = 0;
-					vlc_skip(s, t & 7u);
+					vlc_skip(t & 7u);
 					tw[q] = t;
-					const uint32_t rho = (t >> 4) & 15u;
-					carry = initial ? (((rho | (rho >> 1)) & 1u) | ((rho >> 1) & 6u))
-									: ((((rho >> 2) | (rho >> 3)) & 1u) << 1);
+					carry = (t >> 16) & 7u;
 				}
 				uint32_t mode = ((tw[0] >> 3) & 1u) | (((tw[1] >> 3) & 1u) << 1);
 				if(initial && mode == 3 && mel_event(s))
 					mode = 4;
 				uint32_t U[2];
-				vlc_skip(s, uvlc_decode(vlc_peek(s), mode, initial, U[0], U[1]));
-				const uint32_t qi = (x - xg) >> 1;
-				if(lane == qi)
-				{
-					myt = tw[0];
-					myu = U[0];
-				}
-				else if(lane == qi + 1)
-				{
-					myt = tw[1];
-					myu = U[1];
-				}
+				vlc_skip(uvlc_decode(__funnelshift_r(vw0, vw1, s.vlc_rp), mode, row, U[0], U[1]));
+				quads[qi] = make_uint2(tw[0], U[0]);
+				quads[qi + 1] = make_uint2(tw[1], U[1]);
 			}
+			__syncwarp();
 			// ---- 2. MagSgn, one quad per lane
 			const uint32_t c0 = xg + 2 * lane; // first column of this lane's quad
 			const bool live = c0 < xend;
+			const uint2 mine = quads[lane];
+			__syncwarp();
+			const uint32_t myt = mine.x, myu = mine.y;
 			const uint32_t rho = live ? (myt >> 4) & 15u : 0u;
 			uint32_t U = myu;
 			if(!initial && (rho & (rho - 1)))
@@ -534,20 +548,17 @@ static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missin
 }
 
 __global__ void __launch_bounds__(HT_THREADS)
-	t1_ht_decode_kernel(const T1Launch l, const HtTables* __restrict__ tab, uint32_t max_w)
+	t1_ht_decode_kernel(const T1Launch l, uint32_t max_w)
 {
 	extern __shared__ __align__(16) uint8_t smem[];
-	uint16_t* dec = reinterpret_cast<uint16_t*>(smem);
-	for(uint32_t i = threadIdx.x; i < 2048; i += blockDim.x)
-		dec[i] = tab->dec[0][i];
-	__syncthreads();
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const uint32_t ncol = ht_ncol(max_w);
-	uint8_t* mine = smem + 4096 + (size_t)warp * ht_warp_bytes(max_w);
+	uint8_t* mine = smem + (size_t)warp * ht_warp_bytes(max_w);
 	uint32_t* ring = reinterpret_cast<uint32_t*>(mine);
 	uint32_t* vlc_ring = ring + MS_RING_WORDS;
 	uint32_t* sig = vlc_ring + VLC_RING_WORDS;
-	uint8_t* north = reinterpret_cast<uint8_t*>(sig + 4 * HT_MAX_GROUPS);
+	uint2* quads = reinterpret_cast<uint2*>(sig + 4 * HT_MAX_GROUPS);
+	uint8_t* north = reinterpret_cast<uint8_t*>(quads + 32);
 	uint8_t* cur = north + ncol;
 	for(;;)
 	{
@@ -584,8 +595,8 @@ __global__ void __launch_bounds__(HT_THREADS)
 				dq.thresh = cb.roishift ? (1u << cb.roishift) : 0xFFFFFFFFu;
 				dq.reversible = l.reversible;
 				dq.scale = cb.scale;
-				decoded = ht_cleanup(l.bytes + cb.data_off, (int)len, mm, w, h, blk, l.stride, dq, dec, north,
-									 cur, ncol, ring, vlc_ring, sig, lane);
+				decoded = ht_cleanup(l.bytes + cb.data_off, (int)len, mm, w, h, blk, l.stride, dq, north, cur,
+									 ncol, ring, vlc_ring, sig, quads, lane);
 			}
 			if(!decoded && lane == 0)
 				atomicAdd(l.status, 1u);
@@ -607,14 +618,13 @@ int grkb_launch_t1_ht_decode(const T1Launch& l, cudaStream_t s)
 {
 	if(l.nblocks == 0)
 		return 0;
-	const HtTables* tab = ht_tables_device();
-	if(!tab)
+	if(ht_tables_upload() != 0)
 	{
 		grkb_set_error("t1-ht: cannot upload decode tables");
 		return -1;
 	}
 	const uint32_t max_w = l.max_ht_w ? l.max_ht_w : 64;
-	const size_t smem = 4096 + (size_t)(HT_THREADS / 32) * ht_warp_bytes(max_w);
+	const size_t smem = (size_t)(HT_THREADS / 32) * ht_warp_bytes(max_w);
 	GRKB_ENSURE_SMEM(t1_ht_decode_kernel, smem);
 	int dev = 0, sms = 148;
 	cudaGetDevice(&dev);
@@ -624,7 +634,7 @@ int grkb_launch_t1_ht_decode(const T1Launch& l, cudaStream_t s)
 	if(ctas > need)
 		ctas = need;
 	GRKB_CUDA_CHECK(cudaMemsetAsync(l.counter, 0, sizeof(uint32_t), s));
-	t1_ht_decode_kernel<<<ctas, HT_THREADS, smem, s>>>(l, tab, max_w);
+	t1_ht_decode_kernel<<<ctas, HT_THREADS, smem, s>>>(l, max_w);
 	GRKB_CUDA_CHECK(cudaGetLastError());
 	return 0;
 }
