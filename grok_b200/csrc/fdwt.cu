@@ -14,6 +14,7 @@
 // 128-bit (V=8) or 64-bit (V=4) stores.  Forward order is vertical then horizontal, as in
 // the reference (WaveletFwd.cpp:496-609).
 #include "dwt.cuh"
+#include <stdlib.h>
 
 namespace
 {
@@ -327,8 +328,21 @@ static int launch_fdwt(const DwtLevelArgs& a, bool aligned, cudaStream_t stream)
 } // namespace
 
 // fin: 0 raw, 1 DC shift of one component, 2 DC shift + forward MCT over three components
+int grkb_launch_fdwt_strip(const DwtLevelArgs& a, int reversible, int ncomp, int fin,
+							cudaStream_t stream);
+
 int grkb_launch_fdwt_level(DwtLevelArgs a, int reversible, int ncomp, int fin, cudaStream_t stream)
 {
+	static const bool use_strip = []() {
+		const char* e = getenv("GRKB_FDWT_STRIP"); // 0: general kernel only (comparison runs)
+		return !(e && e[0] == '0');
+	}();
+	if(use_strip)
+	{
+		const int fast = grkb_launch_fdwt_strip(a, reversible, ncomp, fin, stream);
+		if(fast <= 0)
+			return fast;
+	}
 	const int V = (ncomp == 3) ? 4 : 8;
 	const uint32_t H = V / 2;
 	bool al = a.px == 0 && (a.sw % H) == 0;
