@@ -9,7 +9,12 @@ kept under profiles/):
               are independent units: round-robin over the ranks' GPUs (shard.shard_units) and,
               inside a GPU, over a few decoders kept in flight (grkb_decoder_submit / wait).
 
-usage: python tools/bench_extra.py ht_encode|tiled [--steps K] [--inflight N] [--size S]
+  mq_encode   configs[4]: a batch of DCI-4K frames (4096x2160 12-bit RGB, 9/7 + ICT, 32x32 code
+              blocks, EBCOT/MQ, every pass coded with its rate and distortion for the host's PCRD),
+              frames sharded over the ranks (frame f -> rank f mod N, no collective); stock CPU
+              encoder at the cinema-4K byte budget beside it.
+
+usage: python tools/bench_extra.py ht_encode|tiled|mq_encode [--steps K] [--inflight N] [--size S]
 """
 import argparse
 import json
@@ -191,16 +196,100 @@ def tiled(args):
         dist.destroy_process_group()
 
 
+def mq_encode(args):
+    import grok_b200
+    from grok_b200 import encode as E, shard, tile as T
+    from oracle import oracle as O
+    rank, local, world = shard.dist_env()
+    W, H, prec, nr = 4096, 2160, 12, 6
+    grok_b200._lib.check(grok_b200.lib.grkb_set_device(local), "grkb_set_device")
+    nframes = args.frames
+    mine = shard.shard_units(nframes, rank, world)
+    base = synth(W + 8 * nframes, H, prec, 4096)  # slow pan of one field: frame f starts at column 8f
+    params = T.tile_params(0, 0, W, H, 3, nr, 0, 1, prec)
+    blocks, geom, qcd = E.enc_block_table(0, 0, W, H, 3, nr, prec, 0, ht=False, cblk_exp=(5, 5))
+    enc = E.TileEncoder(params)
+    pins = []
+    for f in mine:
+        pin = [T.PinnedArray((H, W), np.int32) for _ in range(3)]
+        for p, a in zip(pin, base):
+            p.array[:] = a[:, 8 * f:8 * f + W]
+        pins.append([p.array for p in pin])
+    n = len(blocks)
+    out = (T.PinnedArray((n,), T.CODED_DTYPE).array, T.PinnedArray((n, T.ENC_MAX_PASSES), T.PASS_DTYPE).array,
+           T.PinnedArray((W * H * 3 * 2,), np.uint8).array)
+
+    def one_pass():
+        nb = 0
+        for src in pins:
+            coded, passes, data = enc.encode(src, blocks, mct_norms=E.MCT_NORMS_IRREV, rate_control=True, out=out)
+            nb += len(data)
+        return nb
+
+    nb = one_pass()
+    assert not out[0]["failed"].any()
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    shard.barrier(world)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        one_pass()
+    ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    ms = shard.max_over_ranks(ms, world, device="cuda" if world > 1 else None)
+    tm = enc.time_device(max(2, args.steps), 1)
+    if rank != 0:
+        return
+    cpu = None
+    if O.have_ref() and not args.no_cpu and world == 1:
+        threads = os.cpu_count() or 1
+        frame = [a[:, :W] for a in base]
+        O.ref_set_rate(W * H * 3 * 1.5 / 1302083.0)  # cinema4K@24 frame budget, codestream/Profile.cpp:1006-1116
+        try:
+            O.ref_codec_encode(frame, prec, 1, ht=False, numres=nr, cblk=(32, 32), threads=threads)
+            t0 = time.perf_counter()
+            for _ in range(2):
+                cs = O.ref_codec_encode(frame, prec, 1, ht=False, numres=nr, cblk=(32, 32), threads=threads)
+            dt = (time.perf_counter() - t0) / 2
+        finally:
+            O.ref_set_rate(0)
+        cpu = {"value": W * H / 1e6 / dt, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
+               "sample": "one frame x2: stock grk compress (public C API, memory stream, 9/7 + ICT, 32x32 blocks, "
+                         "T1 + PCRD + T2 at the cinema-4K budget), %.0f ms/frame, %d bytes" % (dt * 1e3, len(cs))}
+    mp = W * H / 1e6
+    print(json.dumps({
+        "metric": "encode_mpixels_per_s", "value": mp * world / (tm["total_ms"] * 1e-3), "unit": "Mpixel/s",
+        "n_gpus": world, "steps": args.steps, "ms_per_frame_device": tm["total_ms"], "scaling": "strong",
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "j2k_batch_encode_dci4k_rgb12_97_ict_5lvl_cblk32_mq_all_passes",
+                   "frames": nframes, "frames_per_rank": len(mine), "code_blocks": int(n),
+                   "coded_bytes_per_frame": int(nb // max(1, len(mine))),
+                   "sharding": "frame f -> rank f mod N, no collective",
+                   "scope": "DC shift + ICT + 9/7 + quantise + EBCOT/MQ (all passes, rates, distortions) + packing; "
+                            "PCRD and T2 stay on the host (SURVEY 8f N2)"},
+        "e2e": {"value": mp * nframes / (ms * 1e-3), "unit": "Mpixel/s", "ms_per_batch": ms,
+                "h2d_bytes_per_frame": int(W * H * 3 * 4 + blocks.nbytes),
+                "d2h_bytes_per_frame": int(nb // max(1, len(mine)) + out[0].nbytes + out[1].nbytes)},
+        "stages_ms": {"dc_ict_fdwt": tm["dwt_ms"], "t1_mq_encode_pack": tm["t1_ms"]},
+        "cpu_baseline": cpu}), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["ht_encode", "tiled"])
+    ap.add_argument("what", choices=["ht_encode", "tiled", "mq_encode"])
+    ap.add_argument("--frames", type=int, default=8)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--inflight", type=int, default=4)
     ap.add_argument("--size", type=int, default=8192)
     ap.add_argument("--verify", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
-    (ht_encode if args.what == "ht_encode" else tiled)(args)
+    {"ht_encode": ht_encode, "tiled": tiled, "mq_encode": mq_encode}[args.what](args)
 
 
 if __name__ == "__main__":
