@@ -98,119 +98,59 @@ const HtEncTables* ht_enc_tables_device()
 
 constexpr uint32_t SLOT_LEAD = 16;
 constexpr uint32_t MS_CAP = 16384, MEL_CAP = 192, VLC_CAP = 3072;
+constexpr uint32_t MSW = 128; // words of the MagSgn step buffer (+4 behind it): 32 quads x 4 samples x <= 32 bits + 7
+constexpr uint32_t VLW = 32; // words of the VLC step buffer: 32 quads x <= 15 bits + 7
 
-struct HtE
+// MEL coder state (uniform across the warp: every lane runs the same chain; lane 0 stores)
+struct HtMel
 {
-	uint8_t* ms; // global: the block's slot
-	uint32_t ms_pos, ms_tmp, ms_cap;
-	int ms_used, ms_max;
-	uint8_t* mel; // shared
-	uint32_t mel_pos, mel_tmp;
-	int mel_rem, mel_run, mel_k;
-	uint8_t* vlc; // shared, filled from the end
-	uint32_t vlc_pos, vlc_tmp;
-	int vlc_used, vlc_gt8f;
+	uint8_t* buf; // shared
+	uint32_t pos, tmp;
+	int rem, run, k;
 	bool overflow;
 };
 
-// ms_encode, ojph_block_encoder.cpp:397-425: LSB first, a byte after 0xFF holds 7 bits
-static __device__ __forceinline__ void enc_ms(HtE& e, uint32_t cwd, int len)
-{
-	while(len > 0)
-	{
-		if(e.ms_pos >= e.ms_cap)
-		{
-			e.overflow = true;
-			return;
-		}
-		int t = e.ms_max - e.ms_used;
-		if(t > len)
-			t = len;
-		e.ms_tmp |= (cwd & ((1u << t) - 1)) << e.ms_used;
-		e.ms_used += t;
-		cwd >>= t;
-		len -= t;
-		if(e.ms_used >= e.ms_max)
-		{
-			e.ms[e.ms_pos++] = (uint8_t)e.ms_tmp;
-			e.ms_max = (e.ms_tmp == 0xFF) ? 7 : 8;
-			e.ms_tmp = 0;
-			e.ms_used = 0;
-		}
-	}
-}
-
 // mel_emit_bit / mel_encode, ojph_block_encoder.cpp:247-298
-static __device__ __forceinline__ void enc_mel_bit(HtE& e, int v)
+static __device__ __forceinline__ void enc_mel_bit(HtMel& e, int v, uint32_t lane)
 {
-	e.mel_tmp = (e.mel_tmp << 1) + (uint32_t)v;
-	if(--e.mel_rem == 0)
+	e.tmp = (e.tmp << 1) + (uint32_t)v;
+	if(--e.rem == 0)
 	{
-		if(e.mel_pos >= 128)
+		if(e.pos >= 128)
 		{
 			e.overflow = true;
+			e.rem = 8;
+			e.tmp = 0;
 			return;
 		}
-		e.mel[e.mel_pos++] = (uint8_t)e.mel_tmp;
-		e.mel_rem = (e.mel_tmp == 0xFF) ? 7 : 8;
-		e.mel_tmp = 0;
+		if(lane == 0)
+			e.buf[e.pos] = (uint8_t)e.tmp;
+		e.pos++;
+		e.rem = (e.tmp == 0xFF) ? 7 : 8;
+		e.tmp = 0;
 	}
 }
 
-static __device__ __forceinline__ void enc_mel(HtE& e, int bit)
+static __device__ __forceinline__ void enc_mel(HtMel& e, int bit, uint32_t lane)
 {
 	// MEL exponents of table 2 of 15444-15: 0,0,0,1,1,1,2,2,2,3,3,4,5
-	const int ex = (int)((0x5433222111000ull >> (4 * e.mel_k)) & 15);
+	const int ex = (int)((0x5433222111000ull >> (4 * e.k)) & 15);
 	if(!bit)
 	{
-		if(++e.mel_run >= (1 << ex))
+		if(++e.run >= (1 << ex))
 		{
-			enc_mel_bit(e, 1);
-			e.mel_run = 0;
-			e.mel_k = e.mel_k < 12 ? e.mel_k + 1 : 12;
+			enc_mel_bit(e, 1, lane);
+			e.run = 0;
+			e.k = e.k < 12 ? e.k + 1 : 12;
 		}
 	}
 	else
 	{
-		enc_mel_bit(e, 0);
+		enc_mel_bit(e, 0, lane);
 		for(int t = ex; t > 0;)
-			enc_mel_bit(e, (e.mel_run >> --t) & 1);
-		e.mel_run = 0;
-		e.mel_k = e.mel_k > 0 ? e.mel_k - 1 : 0;
-	}
-}
-
-// vlc_encode, ojph_block_encoder.cpp:325-358: written backwards, LSB first; after a byte > 0x8F
-// the next byte may use its 8th bit only if its low seven bits are not all ones
-static __device__ __forceinline__ void enc_vlc(HtE& e, uint32_t cwd, int len)
-{
-	while(len > 0)
-	{
-		if(e.vlc_pos >= VLC_CAP - 128)
-		{
-			e.overflow = true;
-			return;
-		}
-		int avail = 8 - e.vlc_gt8f - e.vlc_used;
-		const int t = avail < len ? avail : len;
-		e.vlc_tmp |= (cwd & ((1u << t) - 1)) << e.vlc_used;
-		e.vlc_used += t;
-		avail -= t;
-		len -= t;
-		cwd >>= t;
-		if(avail == 0)
-		{
-			if(e.vlc_gt8f && e.vlc_tmp != 0x7F)
-			{
-				e.vlc_gt8f = 0;
-				continue;
-			}
-			e.vlc[VLC_CAP - 1 - e.vlc_pos] = (uint8_t)e.vlc_tmp;
-			e.vlc_pos++;
-			e.vlc_gt8f = e.vlc_tmp > 0x8F;
-			e.vlc_tmp = 0;
-			e.vlc_used = 0;
-		}
+			enc_mel_bit(e, (e.run >> --t) & 1, lane);
+		e.run = 0;
+		e.k = e.k > 0 ? e.k - 1 : 0;
 	}
 }
 
@@ -227,8 +167,45 @@ static __device__ __forceinline__ uint32_t uvlc_code(int u)
 	return 0u | (3u << 8) | ((uint32_t)(u - 5) << 16) | (5u << 24);
 }
 
+// OR `len` (<= 32) bits of `val` into a zeroed bit buffer at bit offset `off`
+static __device__ __forceinline__ void put_bits(uint32_t* buf, uint32_t off, uint32_t val, uint32_t len)
+{
+	if(len == 0)
+		return;
+	const uint64_t x = (uint64_t)val << (off & 31u);
+	const uint32_t lo = (uint32_t)x, hi = (uint32_t)(x >> 32);
+	if(lo)
+		atomicOr(buf + (off >> 5), lo);
+	if(hi)
+		atomicOr(buf + (off >> 5) + 1, hi);
+}
+
+// 8 bits of a bit buffer starting at bit offset `off`
+static __device__ __forceinline__ uint32_t get_byte(const uint32_t* buf, uint32_t off)
+{
+	const uint32_t i = off >> 5;
+	return __funnelshift_r(buf[i], buf[i + 1], off & 31u) & 0xFFu;
+}
+
+static __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane)
+{
+#pragma unroll
+	for(int d = 1; d < 32; d <<= 1)
+	{
+		const uint32_t t = __shfl_up_sync(0xffffffffu, v, d);
+		if((int)lane >= d)
+			v += t;
+	}
+	return v;
+}
+
 constexpr int HTE_THREADS = 256;
-constexpr uint32_t REC_WORDS = 8;
+
+static __host__ __device__ __forceinline__ size_t hte_per_warp(uint32_t ncol)
+{
+	return (size_t)(MSW + 4) * 4 + (size_t)(VLW + 4) * 4 + MEL_CAP + VLC_CAP +
+		   4 * (size_t)((ncol + 3) & ~3u);
+}
 
 __global__ void __launch_bounds__(HTE_THREADS)
 	t1_ht_encode_kernel(const T1EncLaunch l, const HtEncTables* __restrict__ tab)
@@ -236,10 +213,10 @@ __global__ void __launch_bounds__(HTE_THREADS)
 	extern __shared__ __align__(16) uint8_t smem[];
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 	const uint32_t ncol = l.max_w + 8;
-	const size_t per_warp = 32 * REC_WORDS * 4 + MEL_CAP + VLC_CAP + 4 * (size_t)((ncol + 3) & ~3u);
-	uint8_t* base = smem + warp * per_warp;
-	uint32_t* rec = reinterpret_cast<uint32_t*>(base);
-	uint8_t* mel = base + 32 * REC_WORDS * 4;
+	uint8_t* base = smem + warp * hte_per_warp(ncol);
+	uint32_t* msbuf = reinterpret_cast<uint32_t*>(base); // MagSgn bits of one step, un-stuffed
+	uint32_t* vlbuf = msbuf + MSW + 4; // VLC bits of one step, un-stuffed
+	uint8_t* mel = reinterpret_cast<uint8_t*>(vlbuf + VLW + 4);
 	uint8_t* vlc = mel + MEL_CAP;
 	uint8_t* rowbuf = vlc + VLC_CAP; // expN | sigN | expC | sigC, ncol bytes each
 
@@ -261,26 +238,25 @@ __global__ void __launch_bounds__(HTE_THREADS)
 		const uint32_t p = 30 - (bad ? 0 : missing);
 		const int32_t* plane =
 			reinterpret_cast<const int32_t*>(l.planes[cb.comp]) + (size_t)cb.y * l.stride + cb.x;
-		HtE e;
-		e.ms = l.slots + (size_t)bi * l.slot_bytes + SLOT_LEAD;
-		e.ms_cap = min(MS_CAP, l.slot_bytes - SLOT_LEAD - MEL_CAP - VLC_CAP);
-		e.ms_pos = 0;
-		e.ms_tmp = 0;
-		e.ms_used = 0;
-		e.ms_max = 8;
-		e.mel = mel;
-		e.mel_pos = 0;
-		e.mel_tmp = 0;
-		e.mel_rem = 8;
-		e.mel_run = 0;
-		e.mel_k = 0;
-		e.vlc = vlc;
-		// vlc_init, :313-323: the last byte is a placeholder, its neighbour starts with four 1s
-		e.vlc_pos = 1;
-		e.vlc_tmp = 0xF;
-		e.vlc_used = 4;
-		e.vlc_gt8f = 1;
-		e.overflow = bad;
+		uint8_t* const ms = l.slots + (size_t)bi * l.slot_bytes + SLOT_LEAD; // global: the block's slot
+		const uint32_t ms_cap = min(MS_CAP, l.slot_bytes - SLOT_LEAD - MEL_CAP - VLC_CAP);
+		// stream states, identical in all lanes.  MagSgn (ms_encode, :397-425): forward, LSB
+		// first, the byte after 0xFF holds 7 bits.  ms_w0 = width of the next byte, ms_left /
+		// ms_nleft = bits not yet forming a byte.
+		uint32_t ms_pos = 0, ms_w0 = 8, ms_left = 0, ms_nleft = 0;
+		// VLC (vlc_encode, :325-358): backwards, LSB first; after a byte > 0x8F the next byte
+		// is 7 bits wide if those seven bits are all ones.  vlc_init, :313-323: the last byte
+		// is a placeholder, its neighbour starts with four 1s.
+		uint32_t vlc_pos = 1, vl_left = 0xF, vl_nleft = 4, vl_gt = 1;
+		HtMel me;
+		me.buf = mel;
+		me.pos = 0;
+		me.tmp = 0;
+		me.rem = 8;
+		me.run = 0;
+		me.k = 0;
+		me.overflow = false;
+		bool overflow = bad;
 		if(lane == 0)
 			vlc[VLC_CAP - 1] = 0xFF;
 		uint8_t *expN = rowbuf, *sigN = rowbuf + ncol, *expC = rowbuf + 2 * ncol, *sigC = rowbuf + 3 * ncol;
@@ -298,9 +274,16 @@ __global__ void __launch_bounds__(HTE_THREADS)
 			for(uint32_t g0 = 0; g0 < nquads; g0 += 32)
 			{
 				const uint32_t qi = g0 + lane, c0 = 2 * qi;
+				const bool live = qi < nquads;
 				uint32_t rho = 0, v[4] = {0, 0, 0, 0};
 				int eq[4] = {0, 0, 0, 0}, emax = 0;
-				if(qi < nquads)
+				// the step buffers are cleared while the samples load
+				*reinterpret_cast<uint4*>(msbuf + 4 * lane) = make_uint4(0, 0, 0, 0);
+				if(lane < (VLW + 4) / 4)
+					*reinterpret_cast<uint4*>(vlbuf + 4 * lane) = make_uint4(0, 0, 0, 0);
+				if(lane == 0)
+					*reinterpret_cast<uint4*>(msbuf + MSW) = make_uint4(0, 0, 0, 0);
+				if(live)
 				{
 #pragma unroll
 					for(uint32_t n = 0; n < 4; ++n)
@@ -333,19 +316,19 @@ __global__ void __launch_bounds__(HTE_THREADS)
 					cq = carry_in;
 				carry_in = __shfl_sync(0xffffffffu, my_carry, 31);
 				int kappa = 1;
-				if(!initial && qi < nquads)
+				if(!initial && live)
 				{
 					cq |= (uint32_t)(sigN[c0] | sigN[c0 + 1]);
 					cq |= (uint32_t)(sigN[c0 + 2] | sigN[c0 + 3]) << 2;
 					if(rho & (rho - 1))
 					{
-						const int me = max(max((int)expN[c0], (int)expN[c0 + 1]),
-										   max((int)expN[c0 + 2], (int)expN[c0 + 3]));
-						kappa = max(me - 1, 1);
+						const int me2 = max(max((int)expN[c0], (int)expN[c0 + 1]),
+											max((int)expN[c0 + 2], (int)expN[c0 + 3]));
+						kappa = max(me2 - 1, 1);
 					}
 				}
 				const int U = max(emax, kappa);
-				const int u = U - kappa;
+				const int u = live ? U - kappa : 0;
 				uint32_t eps = 0;
 				if(u > 0)
 				{
@@ -353,69 +336,145 @@ __global__ void __launch_bounds__(HTE_THREADS)
 					for(uint32_t n = 0; n < 4; ++n)
 						eps |= (uint32_t)(eq[n] == emax) << n;
 				}
-				if(qi < nquads)
+				const uint32_t tw = live ? tab->enc[initial ? 0 : 1][(cq << 8) | (rho << 4) | eps] : 0u;
+
+				// ---- MagSgn: every sample's field at its prefix-sum bit offset ----------------
+				uint32_t mb[4], mtot = 0;
+#pragma unroll
+				for(uint32_t n = 0; n < 4; ++n)
 				{
-					const uint32_t tw = tab->enc[initial ? 0 : 1][(cq << 8) | (rho << 4) | eps];
-					uint32_t* r = rec + lane * REC_WORDS;
-					r[0] = tw;
-					r[1] = (cq == 0 ? 1u : 0u) | (rho ? 2u : 0u) | ((uint32_t)U << 8) | ((uint32_t)u << 16) |
-						   (rho << 24);
-					r[2] = v[0];
-					r[3] = v[1];
-					r[4] = v[2];
-					r[5] = v[3];
+					const int m = ((rho >> n) & 1) ? U - (int)((TW_EK(tw) >> n) & 1) : 0;
+					mb[n] = (uint32_t)m;
+					mtot += (uint32_t)m;
 				}
-				__syncwarp();
+				const uint32_t mincl = warp_incl_scan(mtot, lane);
+				const uint32_t ms_bits = ms_nleft + __shfl_sync(0xffffffffu, mincl, 31);
+
+				// ---- VLC: CxtVLC codeword of the quad, U-VLC of the pair (prefixes, then suffixes;
+				// :693-716 initial row, :926-929 others) -----------------------------------------
+				const int up = __shfl_xor_sync(0xffffffffu, u, 1);
+				const bool odd = lane & 1u;
+				const int u0 = odd ? up : u, u1 = odd ? u : up;
+				uint32_t uc;
+				if(initial && u0 > 2 && u1 > 2)
+					uc = uvlc_code(u - 2);
+				else if(initial && u0 > 2 && u1 > 0 && odd)
+					uc = (uint32_t)(u - 1) | (1u << 8);
+				else
+					uc = uvlc_code(u);
+				const uint32_t Lc = TW_LEN(tw), Lp = (uc >> 8) & 0xFFu, Ls = uc >> 24;
+				const uint32_t lens = Lc | (Lp << 8) | (Ls << 16);
+				const uint32_t plens = __shfl_xor_sync(0xffffffffu, lens, 1);
+				const uint32_t vtot = Lc + Lp + Ls;
+				const uint32_t vincl = warp_incl_scan(vtot, lane);
+				const uint32_t vl_bits = vl_nleft + __shfl_sync(0xffffffffu, vincl, 31);
+				const uint32_t pLc = plens & 0xFFu, pLp = (plens >> 8) & 0xFFu, pLs = plens >> 16;
+				// pair layout: cwd0 cwd1 pre0 pre1 suf0 suf1
+				const uint32_t pbase = vl_nleft + vincl - vtot - (odd ? pLc + pLp + pLs : 0u);
+				const uint32_t o_cwd = pbase + (odd ? pLc : 0u);
+				const uint32_t o_pre = pbase + Lc + pLc + (odd ? pLp : 0u);
+				const uint32_t o_suf = pbase + Lc + pLc + Lp + pLp + (odd ? pLs : 0u);
+
+				// ---- MEL events, in lane order: the quad's (c_q == 0), then the pair's ------------
+				const uint32_t evA = __ballot_sync(0xffffffffu, live && cq == 0);
+				const uint32_t evAv = __ballot_sync(0xffffffffu, rho != 0);
+				const uint32_t evP = __ballot_sync(0xffffffffu, initial && odd && u0 > 0 && u1 > 0);
+				const uint32_t evPv = __ballot_sync(0xffffffffu, min(u0, u1) > 2);
+
+				__syncwarp(); // buffers cleared
 				if(lane == 0)
 				{
-					const uint32_t ng = min(32u, nquads - g0);
-					for(uint32_t j = 0; j < ng; j += 2)
-					{
-						int uq[2] = {0, 0};
-						const uint32_t nq = (j + 1 < ng) ? 2 : 1;
-						for(uint32_t q = 0; q < nq; ++q)
-						{
-							const uint32_t* r = rec + (j + q) * REC_WORDS;
-							const uint32_t tw = r[0], fl = r[1];
-							const uint32_t qrho = fl >> 24;
-							const int qU = (int)((fl >> 8) & 0xFF);
-							uq[q] = (int)((fl >> 16) & 0xFF);
-							enc_vlc(e, TW_CWD(tw), (int)TW_LEN(tw));
-							if(fl & 1u)
-								enc_mel(e, (fl >> 1) & 1);
+					if(ms_nleft)
+						atomicOr(msbuf, ms_left);
+					if(vl_nleft)
+						atomicOr(vlbuf, vl_left);
+				}
+				{
+					uint32_t off = ms_nleft + mincl - mtot;
 #pragma unroll
-							for(uint32_t n = 0; n < 4; ++n)
-							{
-								const int m = ((qrho >> n) & 1) ? qU - (int)((TW_EK(tw) >> n) & 1) : 0;
-								enc_ms(e, r[2 + n] & ((1u << m) - 1), m);
-							}
-						}
-						// U-VLC of the pair (:693-716 initial row, :926-929 others)
-						uint32_t c0w, c1w;
-						if(initial && uq[0] > 0 && uq[1] > 0)
-							enc_mel(e, min(uq[0], uq[1]) > 2);
-						if(initial && uq[0] > 2 && uq[1] > 2)
-						{
-							c0w = uvlc_code(uq[0] - 2);
-							c1w = uvlc_code(uq[1] - 2);
-						}
-						else if(initial && uq[0] > 2 && uq[1] > 0)
-						{
-							c0w = uvlc_code(uq[0]);
-							c1w = (uint32_t)(uq[1] - 1) | (1u << 8);
-						}
-						else
-						{
-							c0w = uvlc_code(uq[0]);
-							c1w = uvlc_code(uq[1]);
-						}
-						enc_vlc(e, c0w & 0xFF, (int)((c0w >> 8) & 0xFF));
-						enc_vlc(e, c1w & 0xFF, (int)((c1w >> 8) & 0xFF));
-						enc_vlc(e, (c0w >> 16) & 0xFF, (int)(c0w >> 24));
-						enc_vlc(e, (c1w >> 16) & 0xFF, (int)(c1w >> 24));
+					for(uint32_t n = 0; n < 4; ++n)
+					{
+						put_bits(msbuf, off, v[n] & ((mb[n] >= 32u) ? 0xFFFFFFFFu : ((1u << mb[n]) - 1u)),
+								 mb[n]);
+						off += mb[n];
 					}
 				}
-				__syncwarp();
+				put_bits(vlbuf, o_cwd, TW_CWD(tw), Lc);
+				put_bits(vlbuf, o_pre, uc & 0xFFu, Lp);
+				put_bits(vlbuf, o_suf, (uc >> 16) & 0xFFu, Ls);
+
+				// MEL chain while the atomics land
+				for(uint32_t M = evA | evP; M;)
+				{
+					const uint32_t b = (uint32_t)__ffs((int)M) - 1u;
+					M &= M - 1u;
+					if((evA >> b) & 1u)
+						enc_mel(me, (int)((evAv >> b) & 1u), lane);
+					if((evP >> b) & 1u)
+						enc_mel(me, (int)((evPv >> b) & 1u), lane);
+				}
+				__syncwarp(); // bits in place
+
+				// ---- MagSgn flush: whole bytes, up to and including the first 0xFF per round ----
+				{
+					uint32_t rd = 0, avail = ms_bits;
+					while(avail >= ms_w0)
+					{
+						const uint32_t nb = min(32u, 1u + ((avail - ms_w0) >> 3));
+						const uint32_t o = rd + (lane ? ms_w0 + 8u * (lane - 1u) : 0u);
+						uint32_t byte = 0;
+						if(lane < nb)
+							byte = get_byte(msbuf, o) & (lane ? 0xFFu : ((1u << ms_w0) - 1u));
+						const uint32_t ff = __ballot_sync(0xffffffffu, lane < nb && byte == 0xFFu);
+						const uint32_t ne = ff ? (uint32_t)__ffs((int)ff) : nb;
+						if(ms_pos + ne > ms_cap)
+						{
+							overflow = true;
+							avail = 0;
+							break;
+						}
+						if(lane < ne)
+							ms[ms_pos + lane] = (uint8_t)byte;
+						const uint32_t used = ms_w0 + 8u * (ne - 1u);
+						rd += used;
+						avail -= used;
+						ms_pos += ne;
+						ms_w0 = ff ? 7u : 8u;
+					}
+					ms_nleft = avail;
+					ms_left = avail ? (get_byte(msbuf, rd) & ((1u << avail) - 1u)) : 0u;
+				}
+				// ---- VLC flush: whole bytes, up to and including the first 7-bit byte per round --
+				{
+					uint32_t rd = 0, avail = vl_bits;
+					while(avail >= 8u)
+					{
+						const uint32_t nb = min(32u, avail >> 3);
+						const uint32_t byte = (lane < nb) ? get_byte(vlbuf, rd + 8u * lane) : 0u;
+						const uint32_t prev = __shfl_up_sync(0xffffffffu, byte, 1);
+						const bool gt = lane ? (prev > 0x8Fu) : (vl_gt != 0u);
+						const uint32_t sh =
+							__ballot_sync(0xffffffffu, lane < nb && gt && (byte & 0x7Fu) == 0x7Fu);
+						const uint32_t ne = sh ? (uint32_t)__ffs((int)sh) : nb;
+						if(vlc_pos + ne > VLC_CAP - 128)
+						{
+							overflow = true;
+							avail = 0;
+							break;
+						}
+						const uint32_t outb = (sh && lane == ne - 1u) ? 0x7Fu : byte;
+						if(lane < ne)
+							vlc[VLC_CAP - 1 - (vlc_pos + lane)] = (uint8_t)outb;
+						vl_gt = (__shfl_sync(0xffffffffu, outb, (int)(ne - 1u)) > 0x8Fu) ? 1u : 0u;
+						const uint32_t used = 8u * ne - (sh ? 1u : 0u);
+						rd += used;
+						avail -= used;
+						vlc_pos += ne;
+					}
+					vl_nleft = avail;
+					vl_left = avail ? (get_byte(vlbuf, rd) & ((1u << avail) - 1u)) : 0u;
+				}
+				__syncwarp(); // buffers are cleared again at the top
 			}
 			uint8_t* t1 = expN;
 			expN = expC;
@@ -424,59 +483,75 @@ __global__ void __launch_bounds__(HTE_THREADS)
 			sigN = sigC;
 			sigC = t1;
 		}
-		// ---- termination (lane 0), then the warp appends MEL and VLC behind MagSgn -------------
-		uint32_t total = 0, ms_pos = 0, mel_pos = 0, vlc_pos = 0;
+		// ---- termination (every lane computes it, lane 0 stores), then the warp appends MEL
+		// and VLC behind MagSgn ----------------------------------------------------------------
+		uint32_t total = 0, mel_pos = 0;
 		uint32_t failed = bad ? 1u : 0u;
-		if(lane == 0 && !bad)
+		if(!bad)
 		{
+			// a 7-bit byte completed by the last bits (vlc_encode emits it as soon as it is full)
+			if(vl_nleft == 7 && vl_gt && vl_left == 0x7Fu)
+			{
+				if(lane == 0)
+					vlc[VLC_CAP - 1 - vlc_pos] = 0x7F;
+				vlc_pos++;
+				vl_nleft = 0;
+				vl_left = 0;
+			}
 			// terminate_mel_vlc, :363-392
-			if(e.mel_run > 0)
-				enc_mel_bit(e, 1);
-			e.mel_tmp <<= e.mel_rem;
-			const uint32_t mel_mask = (0xFFu << e.mel_rem) & 0xFF;
-			const uint32_t vlc_mask = 0xFFu >> (8 - e.vlc_used);
+			if(me.run > 0)
+				enc_mel_bit(me, 1, lane);
+			me.tmp <<= me.rem;
+			const uint32_t mel_mask = (0xFFu << me.rem) & 0xFF;
+			const uint32_t vlc_mask = 0xFFu >> (8 - vl_nleft);
 			if((mel_mask | vlc_mask) != 0)
 			{
-				const uint32_t fuse = e.mel_tmp | e.vlc_tmp;
-				if((((fuse ^ e.mel_tmp) & mel_mask) | ((fuse ^ e.vlc_tmp) & vlc_mask)) == 0 &&
-				   fuse != 0xFF && e.vlc_pos > 1)
-					e.mel[e.mel_pos++] = (uint8_t)fuse;
+				const uint32_t fuse = me.tmp | vl_left;
+				if((((fuse ^ me.tmp) & mel_mask) | ((fuse ^ vl_left) & vlc_mask)) == 0 && fuse != 0xFF &&
+				   vlc_pos > 1)
+				{
+					if(lane == 0)
+						mel[me.pos] = (uint8_t)fuse;
+					me.pos++;
+				}
 				else
 				{
-					e.mel[e.mel_pos++] = (uint8_t)e.mel_tmp;
-					e.vlc[VLC_CAP - 1 - e.vlc_pos] = (uint8_t)e.vlc_tmp;
-					e.vlc_pos++;
+					if(lane == 0)
+					{
+						mel[me.pos] = (uint8_t)me.tmp;
+						vlc[VLC_CAP - 1 - vlc_pos] = (uint8_t)vl_left;
+					}
+					me.pos++;
+					vlc_pos++;
 				}
 			}
 			// ms_terminate, :427-461
-			if(e.ms_used)
+			if(ms_nleft)
 			{
-				const int t = e.ms_max - e.ms_used;
-				e.ms_tmp |= (0xFFu & ((1u << t) - 1)) << e.ms_used;
-				if(e.ms_tmp != 0xFF)
+				const uint32_t t = ms_w0 - ms_nleft;
+				ms_left |= (0xFFu & ((1u << t) - 1u)) << ms_nleft;
+				if(ms_left != 0xFF)
 				{
-					if(e.ms_pos < e.ms_cap)
-						e.ms[e.ms_pos++] = (uint8_t)e.ms_tmp;
+					if(ms_pos < ms_cap)
+					{
+						if(lane == 0)
+							ms[ms_pos] = (uint8_t)ms_left;
+						ms_pos++;
+					}
 					else
-						e.overflow = true;
+						overflow = true;
 				}
 			}
-			else if(e.ms_max == 7)
-				e.ms_pos--;
-			ms_pos = e.ms_pos;
-			mel_pos = e.mel_pos;
-			vlc_pos = e.vlc_pos;
-			failed = e.overflow ? 1u : 0u;
+			else if(ms_w0 == 7)
+				ms_pos--;
+			mel_pos = me.pos;
+			failed = (overflow || me.overflow) ? 1u : 0u;
 		}
-		ms_pos = __shfl_sync(0xffffffffu, ms_pos, 0);
-		mel_pos = __shfl_sync(0xffffffffu, mel_pos, 0);
-		vlc_pos = __shfl_sync(0xffffffffu, vlc_pos, 0);
-		failed = __shfl_sync(0xffffffffu, failed, 0);
 		__syncwarp();
 		if(!failed)
 		{
 			total = ms_pos + mel_pos + vlc_pos;
-			uint8_t* out = e.ms;
+			uint8_t* out = ms;
 			for(uint32_t i = lane; i < mel_pos; i += 32)
 				out[ms_pos + i] = mel[i];
 			for(uint32_t i = lane; i < vlc_pos; i += 32)
@@ -529,7 +604,7 @@ int grkb_launch_t1_ht_encode(const T1EncLaunch& l, cudaStream_t s)
 		return -1;
 	}
 	const uint32_t ncol = l.max_w + 8;
-	const size_t per_warp = 32 * REC_WORDS * 4 + MEL_CAP + VLC_CAP + 4 * (size_t)((ncol + 3) & ~3u);
+	const size_t per_warp = hte_per_warp(ncol);
 	const int nw = HTE_THREADS / 32;
 	const size_t smem = per_warp * nw;
 	if(smem > 227 * 1024)
