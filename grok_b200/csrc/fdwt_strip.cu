@@ -348,13 +348,13 @@ static int launch_fstrip(DwtLevelArgs a, int nplanes, cudaStream_t stream)
 	// Chunk height: as in idwt_strip.cu -- all CTAs resident at once, grid sized to fill the
 	// 148 SMs evenly, chunks no shorter than min_rows (every chunk re-runs NS row pairs of
 	// vertical warm-up).
-	static int waves = 0, min_rows = 0;
-	if(waves == 0)
+	static int waves = -1, min_rows = 0;
+	if(waves < 0)
 	{
 		const char* e = getenv("GRKB_FDWT_WAVES"); // tuning knobs, see DESIGN.md section 4
-		int w = e ? atoi(e) : 2;
-		if(w < 1 || w > 4)
-			w = 2;
+		int w = e ? atoi(e) : 0; // 0: per kernel (below)
+		if(w < 0 || w > 4)
+			w = 0;
 		e = getenv("GRKB_FDWT_MIN_ROWS");
 		int mr = e ? atoi(e) : 4;
 		min_rows = mr < 4 ? 4 : mr;
@@ -363,7 +363,8 @@ static int launch_fstrip(DwtLevelArgs a, int nplanes, cudaStream_t stream)
 	const uint32_t total_rows = a.py + a.rh;
 	const uint32_t ngroups = (a.nstrips + CW - 1) / CW;
 	const uint32_t per_chunk = ngroups * ((NC == 1) ? (uint32_t)nplanes : 1u);
-	uint32_t nch = (148u * (uint32_t)waves) / per_chunk;
+	const uint32_t nwaves = waves ? (uint32_t)waves : (K::NS == 4 ? 3u : 2u); // see idwt_strip.cu
+	uint32_t nch = (148u * nwaves) / per_chunk;
 	if(nch < 1)
 		nch = 1;
 	uint32_t ch = 2 * ((total_rows + 2 * nch - 1) / (2 * nch));

@@ -366,13 +366,13 @@ static int launch_strip(DwtLevelArgs a, int nplanes, cudaStream_t stream)
 	// Chunk height: all CTAs are resident at once (<= 4 per SM), so the grid is sized to fill
 	// the 148 SMs evenly -- waves*148 CTAs or just under -- with chunks no shorter than
 	// min_rows (every chunk re-runs NS rows of vertical warm-up).
-	static int waves = 0, min_rows = 0;
-	if(waves == 0)
+	static int waves = -1, min_rows = 0;
+	if(waves < 0)
 	{
 		const char* e = getenv("GRKB_IDWT_WAVES"); // tuning knobs, see DESIGN.md section 4
-		waves = e ? atoi(e) : 2;
-		if(waves < 1 || waves > 4)
-			waves = 2;
+		waves = e ? atoi(e) : 0; // 0: per kernel (below)
+		if(waves < 0 || waves > 4)
+			waves = 0;
 		e = getenv("GRKB_IDWT_MIN_ROWS");
 		min_rows = e ? atoi(e) : 4; // small levels are latency-bound: short chunks, many CTAs
 		if(min_rows < 4)
@@ -381,7 +381,13 @@ static int launch_strip(DwtLevelArgs a, int nplanes, cudaStream_t stream)
 	const uint32_t total_rows = a.py + a.rh;
 	const uint32_t ngroups = (a.nstrips + CW - 1) / CW;
 	const uint32_t per_chunk = ngroups * ((NC == 1) ? (uint32_t)nplanes : 1u);
-	uint32_t nch = (148u * (uint32_t)waves) / per_chunk;
+	// CTAs per SM: the 9/7 kernels hide their longer dependency chains with a third CTA per SM
+	// (3 x 160 threads x 125 registers and 3 x 47 KB still fit); 5/3 is fastest with two.
+	// (Tried and dropped: the lifting steps on the packed FP32 pipe, FADD2 + FMUL2 + scalar FADD
+	// -- ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2, so the last add must stay scalar;
+	// bit-exact, but 3 % slower than this kernel: it is not bound by FP32 issue.)
+	const uint32_t nwaves = waves ? (uint32_t)waves : (K::NS == 4 ? 3u : 2u);
+	uint32_t nch = (148u * nwaves) / per_chunk;
 	if(nch < 1)
 		nch = 1;
 	uint32_t ch = 2 * ((total_rows + 2 * nch - 1) / (2 * nch));
