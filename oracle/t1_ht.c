@@ -17,9 +17,11 @@
  * the three bit streams are read lazily one byte at a time, MEL symbols are produced on demand,
  * and quads and samples are plain loops over per-column neighbour arrays.  Results on every
  * stream the reference accepts must be identical (tests/test_oracle_vs_ref.py).  SigProp and
- * MagRef passes are not reachable through Grok (T1HT::decompress always passes lengths2 = 0,
- * T1HT.cpp:171-173; the decoder then rejects num_passes > 1, ojph_block_decoder.cpp:1014-1020)
- * and are rejected here in the same way.
+ * MagRef passes (:1627-2209; readers :466-580, :875-975) are not reachable through Grok's host
+ * (T1HT::decompress always passes lengths2 = 0, T1HT.cpp:171-173; the decoder then rejects
+ * num_passes > 1, ojph_block_decoder.cpp:1014-1020); they are restated here as plain per-sample
+ * loops and pinned by calling the reference's ojph_decode_codeblock directly with a second
+ * segment (oracle/ref_harness.cpp ref_ht_decode).
  */
 #include "oracle.h"
 #include <stdlib.h>
@@ -323,6 +325,124 @@ static uint32_t bitlen(uint32_t v)
 	return n;
 }
 
+/* ---- SigProp / MagRef (ojph_block_decoder.cpp:1627-2209) -------------------------------------
+ * The reference keeps nibble-packed significance / membership words for two stripes and runs the
+ * refinement of a stripe interleaved with the cleanup pass of later rows.  The passes only read
+ * what the cleanup pass left in their own stripe, the row above and the row below, so here they
+ * run after it, stripe by stripe, straight on the sample array:
+ *   MagRef  every sample the cleanup pass made significant takes one bit, stripe-column order;
+ *   SigProp a zero sample with a significant 8-neighbour at the time it is visited (cleanup
+ *           significance for samples not visited yet, plus what this pass has set so far) takes
+ *           one bit; the signs of the samples a group of four columns made significant follow
+ *           that group's significance bits. */
+typedef struct
+{
+	const uint8_t* d;
+	int pos, left, unstuff;
+	uint64_t acc;
+	int bits;
+} ht_bits;
+
+/* frwd_read<0> / frwd_init<0>, :875-945: forward, LSB first, 7 bits after 0xFF, zeros at the end */
+static uint32_t spp_bit(ht_bits* s)
+{
+	while(s->bits <= 56)
+	{
+		uint32_t b = 0;
+		if(s->left > 0)
+			b = s->d[s->pos];
+		s->pos++;
+		s->left--;
+		s->acc |= (uint64_t)b << s->bits; /* a set top bit of a 7-bit byte overlaps, as there */
+		s->bits += 8 - s->unstuff;
+		s->unstuff = (b == 0xFF);
+	}
+	const uint32_t r = (uint32_t)(s->acc & 1);
+	s->acc >>= 1;
+	s->bits--;
+	return r;
+}
+
+/* rev_read_mrp / rev_init_mrp, :466-552: backward from the end of the second segment */
+static uint32_t mrp_bit(ht_bits* s)
+{
+	while(s->bits <= 56)
+	{
+		uint32_t b = 0;
+		if(s->left > 0)
+			b = s->d[s->pos];
+		s->pos--;
+		s->left--;
+		const int wd = 8 - ((s->unstuff && (b & 0x7F) == 0x7F) ? 1 : 0);
+		s->acc |= (uint64_t)b << s->bits;
+		s->bits += wd;
+		s->unstuff = b > 0x8F;
+	}
+	const uint32_t r = (uint32_t)(s->acc & 1);
+	s->acc >>= 1;
+	s->bits--;
+	return r;
+}
+
+static int ht_has_sig_neighbour(const uint32_t* out, uint32_t w, uint32_t h, uint32_t x, uint32_t y)
+{
+	for(int dy = -1; dy <= 1; ++dy)
+		for(int dx = -1; dx <= 1; ++dx)
+		{
+			const int xx = (int)x + dx, yy = (int)y + dy;
+			if((dx || dy) && xx >= 0 && yy >= 0 && xx < (int)w && yy < (int)h &&
+			   out[(size_t)yy * w + xx] != 0)
+				return 1;
+		}
+	return 0;
+}
+
+static void ht_refine(uint32_t* out, uint32_t w, uint32_t h, uint32_t p, uint32_t num_passes,
+					  const uint8_t* seg2, int len2)
+{
+	ht_bits spp = {seg2, 0, len2, 0, 0, 0};
+	ht_bits mrp = {seg2, len2 - 1, len2, 1, 0, 0};
+	for(uint32_t y0 = 0; y0 < h; y0 += 4)
+	{
+		const uint32_t rows = h - y0 < 4 ? h - y0 : 4;
+		if(num_passes > 2)
+		{
+			/* :1630-1701, :1924-1987 */
+			for(uint32_t x = 0; x < w; ++x)
+				for(uint32_t r = 0; r < rows; ++r)
+				{
+					uint32_t* v = out + (size_t)(y0 + r) * w + x;
+					if(*v == 0)
+						continue;
+					const uint32_t sym = mrp_bit(&mrp);
+					*v ^= (1 - sym) << (p - 1);
+					*v |= 1u << (p - 2);
+				}
+		}
+		/* :1731-1916, :1990-2203 */
+		for(uint32_t xg = 0; xg < w; xg += 4)
+		{
+			const uint32_t xe = xg + 4 < w ? xg + 4 : w;
+			uint32_t* fresh[16];
+			uint32_t nfresh = 0;
+			for(uint32_t x = xg; x < xe; ++x)
+				for(uint32_t r = 0; r < rows; ++r)
+				{
+					uint32_t* v = out + (size_t)(y0 + r) * w + x;
+					if(*v != 0 || !ht_has_sig_neighbour(out, w, h, x, y0 + r))
+						continue;
+					if(spp_bit(&spp))
+					{
+						*v = 3u << (p - 2); /* newly significant, bin centre included */
+						fresh[nfresh++] = v;
+					}
+				}
+			for(uint32_t i = 0; i < nfresh; ++i)
+				*fresh[i] |= spp_bit(&spp) << 31;
+		}
+	}
+}
+
 /* ---- cleanup pass decoder ------------------------------------------------------------------- */
 
 int orc_ht_decode(const uint8_t* data, uint32_t missing_msbs, uint32_t num_passes,
@@ -338,8 +458,6 @@ int orc_ht_decode(const uint8_t* data, uint32_t missing_msbs, uint32_t num_passe
 		return -1;
 	if(missing_msbs == 29)
 		num_passes = 1;
-	if(num_passes > 1)
-		return -2; /* SigProp / MagRef: not reachable through Grok, not restated */
 	const uint32_t p = 30 - missing_msbs;
 	const int lcup = (int)lengths1;
 	if(lcup < 2)
@@ -451,6 +569,8 @@ int orc_ht_decode(const uint8_t* data, uint32_t missing_msbs, uint32_t num_passe
 	}
 	free(sigN < sigC ? sigN : sigC);
 	free(sigN < sigC ? sigC : sigN);
+	if(rc == 0 && num_passes > 1)
+		ht_refine(out, w, h, p, num_passes, data + lengths1, (int)lengths2);
 	return rc;
 }
 

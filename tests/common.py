@@ -43,3 +43,27 @@ def plane(rng, w, h, reversible, amp=2000):
 def same_bits(a, b):
     return np.array_equal(np.ascontiguousarray(a).view(np.int32),
                           np.ascontiguousarray(b).view(np.int32))
+
+
+def ht_refine_case(rng, w, h, ht_encode):
+    """One HT block with a refinement segment: (samples, k_msbs, cleanup bytes + second segment,
+    length of the second segment).  The cleanup segment comes from `ht_encode` (oracle or reference
+    encoder, they are byte-identical); the second segment is arbitrary bytes -- random, 0xFF-heavy
+    or drawn from the bytes that trigger the stuffing rules -- sometimes shorter than the passes
+    need, so the zero fill at the end of both readers is exercised too."""
+    from oracle import oracle as O
+    kmsbs = int(rng.integers(3, 20))
+    bits = int(rng.integers(1, kmsbs))
+    v = rng.integers(-(1 << bits) + 1, 1 << bits, size=(h, w)).astype(np.int32)
+    dens = rng.choice([0.02, 0.1, 0.3, 0.7, 1.0])
+    v = np.where(rng.random((h, w)) < dens, v, 0).astype(np.int32)
+    cup = ht_encode(O.ht_samples(v, kmsbs), kmsbs)
+    kind = rng.random()
+    l2 = int(rng.integers(1, 1 + max(2, w * h // 4))) if kind < 0.8 else int(rng.integers(1, 6))
+    if kind < 0.5:
+        seg = rng.integers(0, 256, size=l2, dtype=np.uint8)
+    elif kind < 0.7:
+        seg = np.where(rng.random(l2) < 0.5, 0xFF, rng.integers(0, 256, size=l2)).astype(np.uint8)
+    else:
+        seg = rng.choice(np.array([0x7F, 0xFF, 0x8F, 0x90, 0x00, 0x80], dtype=np.uint8), size=l2)
+    return v, kmsbs, bytes(cup) + bytes(seg), l2

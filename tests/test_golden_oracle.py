@@ -59,3 +59,12 @@ def test_t1_ht_golden(orc):
         assert np.array_equal(val, t["vals_%d" % k])
         # and the encoder reproduces the reference's bytes
         assert O.orc_ht_encode(O.ht_samples(t["vals_%d" % k], int(mm)), int(mm)) == t["bytes_%d" % k].tobytes()
+
+
+def test_t1_ht_refinement_golden(orc):
+    """SigProp / MagRef restatement against what the reference's block decoder returned"""
+    t = np.load(os.path.join(G, "t1_ht_refine.npz"))
+    for k, (w, h, kmsbs, passes, l2) in enumerate(t["cases"]):
+        rc, dec = O.orc_ht_decode(t["bytes_%d" % k].tobytes(), int(kmsbs), int(w), int(h),
+                                  num_passes=int(passes), lengths2=int(l2))
+        assert rc == 0 and np.array_equal(dec, t["dec_%d" % k]), k

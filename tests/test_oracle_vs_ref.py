@@ -182,6 +182,31 @@ def test_ht_decode_matches_reference(orc):
     assert n > 1000
 
 
+def test_ht_refinement_passes_match_reference(orc):
+    """SigProp / MagRef: not reachable through Grok's host, so the pin is the
+    reference's ojph_decode_codeblock called directly with a second segment of arbitrary bytes"""
+    from common import ht_refine_case
+    rng = np.random.default_rng(5)
+    shapes = [(64, 64), (32, 32), (8, 8), (4, 4), (5, 7), (7, 5), (1, 1), (2, 1), (1, 2), (3, 3), (16, 9),
+              (9, 16), (13, 10), (33, 6), (6, 33), (64, 1), (1, 64), (64, 2), (64, 3), (64, 5), (64, 6),
+              (64, 7), (12, 11), (17, 13), (100, 4), (4, 100), (40, 21), (1024, 4), (4, 1024)]
+    changed = 0
+    for it in range(580):
+        w, h = shapes[it % len(shapes)]
+        _, kmsbs, data, l2 = ht_refine_case(rng, w, h, O.orc_ht_encode)
+        for passes in (2, 3):
+            rr, r = O.ref_ht_decode(data, kmsbs, w, h, num_passes=passes, lengths2=l2)
+            ro, o = O.orc_ht_decode(data, kmsbs, w, h, num_passes=passes, lengths2=l2)
+            assert rr == ro == 0 and np.array_equal(r, o), (it, w, h, kmsbs, passes, l2)
+        _, base = O.orc_ht_decode(data[:len(data) - l2], kmsbs, w, h)
+        changed += int(not np.array_equal(base, o))
+    assert changed > 400  # the passes do something
+    # a second pass without a second segment is rejected by both (ojph_block_decoder.cpp:1014-1020)
+    rr, _ = O.ref_ht_decode(data[:len(data) - l2], kmsbs, w, h, num_passes=2, lengths2=0)
+    ro, _ = O.orc_ht_decode(data[:len(data) - l2], kmsbs, w, h, num_passes=2, lengths2=0)
+    assert rr != 0 and ro != 0
+
+
 def test_ht_encode_matches_reference(orc):
     rng = np.random.default_rng(32)
     n = 0
