@@ -18,10 +18,15 @@
 //      position) into a per-warp ring of bits in shared memory, from which the lanes pick their
 //      fields; sample reconstruction, the HT dequantiser and the store (coalesced rows of the
 //      L2-resident plane, written once) are fused here.
-// Not HBM-bound: traffic is the coded bytes in and 4 B/sample out.  SigProp / MagRef passes
-// cannot reach this decoder through Grok (T1HT.cpp:171-173 passes lengths2 = 0, which
-// ojph_block_decoder.cpp:1014-1020 rejects for more than one pass); such blocks are rejected
-// here too and counted in the status word.
+// Not HBM-bound: traffic is the coded bytes in and 4 B/sample out.
+//
+// SigProp / MagRef passes (ojph_block_decoder.cpp:1627-2209): a block whose descriptor carries a
+// second codeword segment (cleanup | SigProp [+ MagRef], 2 or 3 passes) keeps the block decoder's
+// sign-magnitude words in the plane after the cleanup pass, runs the refinement stripe by stripe
+// (ht_refine below) and dequantises in place at the end.  Grok's own host never gets there
+// (T1HT.cpp:171-173 passes lengths2 = 0, which ojph_block_decoder.cpp:1014-1020 rejects for more
+// than one pass), so a block with more than one pass in a single segment is rejected here too
+// and counted in the status word.
 #include "t1.cuh"
 #include <mutex>
 
@@ -367,14 +372,9 @@ struct Dequant
 	float scale;
 };
 
-static __device__ __forceinline__ uint32_t ht_sample(const Dequant& dq, uint32_t bits, uint32_t m,
-													  uint32_t e1, uint32_t& exponent)
+// s: sign-magnitude, as the block decoder leaves it
+static __device__ __forceinline__ uint32_t ht_dequant(const Dequant& dq, uint32_t s)
 {
-	uint32_t v = bits & ((1u << m) - 1u);
-	v |= e1 << m;
-	v |= 1u;
-	exponent = 32 - __clz(v);
-	uint32_t s = (bits << 31) | ((v + 2) << (dq.p - 1)); // sign-magnitude, as the block decoder leaves it
 	const uint32_t mag0 = s & 0x7FFFFFFFu;
 	if(dq.roishift && mag0 >= dq.thresh)
 		s = (mag0 >> dq.roishift) & (s & 0x80000000u);
@@ -388,10 +388,263 @@ static __device__ __forceinline__ uint32_t ht_sample(const Dequant& dq, uint32_t
 	return __float_as_uint((s & 0x80000000u) ? -f : f);
 }
 
+template<bool RAW>
+static __device__ __forceinline__ uint32_t ht_sample(const Dequant& dq, uint32_t bits, uint32_t m,
+													  uint32_t e1, uint32_t& exponent)
+{
+	uint32_t v = bits & ((1u << m) - 1u);
+	v |= e1 << m;
+	v |= 1u;
+	exponent = 32 - __clz(v);
+	const uint32_t s = (bits << 31) | ((v + 2) << (dq.p - 1));
+	return RAW ? s : ht_dequant(dq, s);
+}
+
+// ---- SigProp / MagRef ------------------------------------------------------------------------
+// Raw-bit readers of the second segment, one byte at a time into a 64-bit window (lane 0 only).
+// A 7-bit byte is OR-ed in whole, so a set top bit overlaps the next byte exactly as in the
+// reference's accumulators (frwd_read<0> :875-945, rev_read_mrp :466-552); zeros once the segment
+// is used up.
+struct RawBits
+{
+	const uint8_t* d;
+	int pos, left;
+	uint32_t unstuff;
+	uint64_t acc;
+	int bits;
+};
+static __device__ __forceinline__ void spp_fill(RawBits& s)
+{
+	while(s.bits <= 56)
+	{
+		const uint32_t b = s.left > 0 ? (uint32_t)__ldg(s.d + s.pos) : 0u;
+		s.pos++;
+		s.left--;
+		s.acc |= (uint64_t)b << s.bits;
+		s.bits += 8 - (int)s.unstuff;
+		s.unstuff = (b == 0xFFu);
+	}
+}
+static __device__ __forceinline__ void mrp_fill(RawBits& s)
+{
+	while(s.bits <= 56)
+	{
+		const uint32_t b = s.left > 0 ? (uint32_t)__ldg(s.d + s.pos) : 0u;
+		s.pos--;
+		s.left--;
+		const int wd = 8 - ((s.unstuff && (b & 0x7Fu) == 0x7Fu) ? 1 : 0);
+		s.acc |= (uint64_t)b << s.bits;
+		s.bits += wd;
+		s.unstuff = b > 0x8Fu;
+	}
+}
+static __device__ __forceinline__ uint32_t spp_bit(RawBits& s)
+{
+	if(s.bits < 1)
+		spp_fill(s);
+	const uint32_t r = (uint32_t)s.acc & 1u;
+	s.acc >>= 1;
+	s.bits--;
+	return r;
+}
+
+constexpr uint32_t HT_ROW_WORDS = 32; // a block is at most 1024 columns wide
+
+// Refinement of one block by one warp, after the cleanup pass left sign-magnitude words in
+// `out`.  Stripe by stripe:
+//   * the lanes turn six sample rows (the stripe, the row above, the row below) into bit rows of
+//     "non-zero" in shared memory (one ballot per 32 columns);
+//   * MagRef: every sample the cleanup pass made significant takes one bit, stripe-column order.
+//     Lane 0 un-stuffs as many bits as the stripe has significant samples into shared memory,
+//     then lane l applies them to columns l, l+32, ... (bit index = prefix sum of the per-column
+//     counts): coalesced read-modify-write of the rows;
+//   * SigProp: lane w derives the static membership words of 32 columns (zero samples with a
+//     non-zero 8-neighbour); lane 0 walks the member columns in order, adding the members that
+//     appear when a sample becomes significant (sample below, next column), reads the
+//     significance bits and, after every group of four columns, the signs of that group.
+// S: 6 x HT_ROW_WORDS words, M: 4 x HT_ROW_WORDS words, mbits: 128 words (per warp).
+static __device__ __noinline__ void ht_refine(uint32_t* out, uint32_t ostride, uint32_t w, uint32_t h, uint32_t p,
+								  uint32_t passes, const uint8_t* seg2, int len2, uint32_t* S,
+								  uint32_t* M, uint32_t* mbits, uint32_t lane)
+{
+	RawBits spp{seg2, 0, len2, 0u, 0ull, 0};
+	RawBits mrp{seg2, len2 - 1, len2, 1u, 0ull, 0};
+	const uint32_t nw = (w + 31) >> 5;
+	for(uint32_t y0 = 0; y0 < h; y0 += 4)
+	{
+		const uint32_t rows = min(4u, h - y0);
+		// ---- bit rows: S[rr] = row y0 - 1 + rr
+		for(uint32_t rr = 0; rr < 6; ++rr)
+		{
+			const int y = (int)y0 - 1 + (int)rr;
+			const bool rowok = y >= 0 && y < (int)h;
+			for(uint32_t c = 0; c < nw; ++c)
+			{
+				const uint32_t x = c * 32 + lane;
+				const uint32_t v = (rowok && x < w) ? out[(size_t)y * ostride + x] : 0u;
+				const uint32_t word = __ballot_sync(0xffffffffu, v != 0u);
+				if(lane == 0)
+					S[rr * HT_ROW_WORDS + c] = word;
+			}
+		}
+		__syncwarp();
+		// ---- MagRef (:1630-1701, :1924-1987)
+		if(passes > 2)
+		{
+			// significant samples per 32-column chunk, summed over the stripe's rows
+			uint32_t mine = 0; // lane c: count of chunk c
+			if(lane < nw)
+				for(uint32_t r = 0; r < rows; ++r)
+					mine += (uint32_t)__popc(S[(r + 1) * HT_ROW_WORDS + lane]);
+			uint32_t incl = mine;
+#pragma unroll
+			for(uint32_t d = 1; d < 32; d <<= 1)
+			{
+				const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+				if(lane >= d)
+					incl += o;
+			}
+			const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+			if(lane == 0)
+			{
+				for(uint32_t i = 0; i * 32 < total; ++i)
+				{
+					if(mrp.bits < 32)
+						mrp_fill(mrp);
+					mbits[i] = (uint32_t)mrp.acc;
+					const uint32_t take = min(32u, total - i * 32);
+					mrp.acc >>= take;
+					mrp.bits -= (int)take;
+				}
+			}
+			__syncwarp();
+			for(uint32_t c = 0; c < nw; ++c)
+			{
+				const uint32_t base = __shfl_sync(0xffffffffu, incl - mine, (int)c); // bits before chunk c
+				const uint32_t x = c * 32 + lane;
+				uint32_t nib = 0;
+				for(uint32_t r = 0; r < rows; ++r)
+					nib |= ((S[(r + 1) * HT_ROW_WORDS + c] >> lane) & 1u) << r;
+				const uint32_t k = (uint32_t)__popc(nib);
+				uint32_t at = k;
+#pragma unroll
+				for(uint32_t d = 1; d < 32; d <<= 1)
+				{
+					const uint32_t o = __shfl_up_sync(0xffffffffu, at, d);
+					if(lane >= d)
+						at += o;
+				}
+				at = base + at - k;
+				for(uint32_t r = 0; r < rows; ++r)
+					if((nib >> r) & 1u)
+					{
+						const uint32_t sym = (mbits[at >> 5] >> (at & 31u)) & 1u;
+						++at;
+						uint32_t* v = out + (size_t)(y0 + r) * ostride + x;
+						*v = (*v ^ ((1u - sym) << (p - 1))) | (1u << (p - 2));
+					}
+			}
+			__syncwarp();
+		}
+		// ---- SigProp (:1731-1916, :1990-2203): static membership, 32 columns per lane
+		if(lane < nw)
+		{
+			const uint32_t last = (w & 31u) ? ((1u << (w & 31u)) - 1u) : 0xFFFFFFFFu;
+			const uint32_t colmask = (lane == nw - 1) ? last : 0xFFFFFFFFu;
+			uint32_t dil[6];
+#pragma unroll
+			for(uint32_t rr = 0; rr < 6; ++rr)
+			{
+				const uint32_t c = S[rr * HT_ROW_WORDS + lane];
+				const uint32_t l = lane ? S[rr * HT_ROW_WORDS + lane - 1] : 0u;
+				const uint32_t r = (lane + 1 < nw) ? S[rr * HT_ROW_WORDS + lane + 1] : 0u;
+				dil[rr] = c | (c << 1) | (c >> 1) | (l >> 31) | (r << 31);
+			}
+#pragma unroll
+			for(uint32_t r = 0; r < 4; ++r)
+			{
+				uint32_t m = 0;
+				if(r < rows)
+					m = (dil[r] | dil[r + 1] | dil[r + 2]) & ~S[(r + 1) * HT_ROW_WORDS + lane] & colmask;
+				M[r * HT_ROW_WORDS + lane] = m;
+			}
+		}
+		__syncwarp();
+		if(lane == 0)
+		{
+			const uint32_t rowmask = (1u << rows) - 1u;
+			const uint32_t val = 3u << (p - 2); // newly significant, bin centre included
+			uint32_t dyn = 0; // members of column x added by new significant samples
+			uint32_t nfresh = 0;
+			uint64_t fresh = 0; // (x & 3) | r << 2, four bits per new sample of the group
+			int group = -1;
+			uint32_t x = 0;
+			auto flush = [&]() {
+				for(uint32_t i = 0; i < nfresh; ++i)
+				{
+					const uint32_t e = (uint32_t)(fresh >> (4 * i)) & 15u;
+					const uint32_t fx = (uint32_t)group * 4 + (e & 3u), fr = e >> 2;
+					out[(size_t)(y0 + fr) * ostride + fx] = val | (spp_bit(spp) << 31);
+				}
+				nfresh = 0;
+				fresh = 0;
+			};
+			while(x < w)
+			{
+				if(dyn == 0)
+				{
+					// next column with a static member
+					uint32_t c = x >> 5;
+					uint32_t cm = (M[c] | M[HT_ROW_WORDS + c] | M[2 * HT_ROW_WORDS + c] | M[3 * HT_ROW_WORDS + c]) &
+								  (0xFFFFFFFFu << (x & 31u));
+					while(cm == 0 && ++c < nw)
+						cm = M[c] | M[HT_ROW_WORDS + c] | M[2 * HT_ROW_WORDS + c] | M[3 * HT_ROW_WORDS + c];
+					if(cm == 0)
+						break;
+					x = c * 32 + (uint32_t)__ffs((int)cm) - 1u;
+				}
+				if((int)(x >> 2) != group)
+				{
+					flush();
+					group = (int)(x >> 2);
+				}
+				const uint32_t c = x >> 5, b = x & 31u;
+				uint32_t m = dyn, sg = 0;
+#pragma unroll
+				for(uint32_t r = 0; r < 4; ++r)
+				{
+					m |= ((M[r * HT_ROW_WORDS + c] >> b) & 1u) << r;
+					sg |= ((S[(r + 1) * HT_ROW_WORDS + c] >> b) & 1u) << r;
+				}
+				const uint32_t zero = ~sg & rowmask;
+				m &= zero;
+				uint32_t next = 0;
+#pragma unroll
+				for(uint32_t r = 0; r < 4; ++r)
+					if((m >> r) & 1u)
+					{
+						if(spp_bit(spp))
+						{
+							fresh |= (uint64_t)((x & 3u) | (r << 2)) << (4 * nfresh);
+							++nfresh;
+							m |= (2u << r) & zero; // the sample below joins
+							next |= ((7u << r) >> 1) & 15u; // rows r-1 .. r+1 of the next column
+						}
+					}
+				dyn = next;
+				++x;
+			}
+			flush();
+		}
+		__syncwarp();
+	}
+}
+
 // Cleanup pass of one block by one warp (all lanes call this).  north/cur: per-column
 // significance (bit 7) and magnitude exponent (low 7 bits) of the bottom sample row of the
 // previous / current quad row, index = column + 1.  Returns false if the stream is rejected
 // (the caller then zeroes the block).
+template<bool RAW>
 static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missing_msbs, uint32_t w,
 								   uint32_t h, uint32_t* out, uint32_t ostride, const Dequant& dq,
 								   uint8_t* north, uint8_t* cur, uint32_t ncol, uint32_t* ring,
@@ -508,7 +761,7 @@ static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missin
 				ex[n] = 0;
 				if((rho >> n) & 1u)
 				{
-					val[n] = ht_sample(dq, ms_bits_at(ms, at), mn[n], (myt >> (12 + n)) & 1u, ex[n]);
+					val[n] = ht_sample<RAW>(dq, ms_bits_at(ms, at), mn[n], (myt >> (12 + n)) & 1u, ex[n]);
 					ex[n] |= 0x80u;
 					at += mn[n];
 				}
@@ -547,6 +800,9 @@ static __device__ bool ht_cleanup(const uint8_t* data, int lcup, uint32_t missin
 	return true;
 }
 
+// REFINE: the table holds blocks with a second segment (known on the host); the instantiation
+// without them keeps the one-pass decoder's registers and occupancy
+template<bool REFINE>
 __global__ void __launch_bounds__(HT_THREADS)
 	t1_ht_decode_kernel(const T1Launch l, uint32_t max_w)
 {
@@ -586,8 +842,15 @@ __global__ void __launch_bounds__(HT_THREADS)
 				len += l.segs[cb.seg_first + sgi].len;
 			}
 			const uint32_t mm = cb.k_msbs;
-			if(passes == 1 && len >= 2 && mm <= 29)
+			// the first segment is the cleanup pass, what follows it is SigProp [+ MagRef]
+			// (ojph_decode_codeblock's lengths1 / lengths2, :989-1043)
+			const uint32_t len1 = l.segs[cb.seg_first].len, len2 = len - len1;
+			const bool shape_ok = passes >= 1 && passes <= 3 && (passes == 1 || len2 != 0) &&
+								  l.segs[cb.seg_first].numpasses == 1;
+			if(shape_ok && len1 >= 2 && mm <= 29)
 			{
+				if(mm == 29)
+					passes = 1; // :1031-1032
 				Dequant dq;
 				dq.p = 30 - mm;
 				dq.shift = 31u - (mm + 1u);
@@ -595,8 +858,25 @@ __global__ void __launch_bounds__(HT_THREADS)
 				dq.thresh = cb.roishift ? (1u << cb.roishift) : 0xFFFFFFFFu;
 				dq.reversible = l.reversible;
 				dq.scale = cb.scale;
-				decoded = ht_cleanup(l.bytes + cb.data_off, (int)len, mm, w, h, blk, l.stride, dq, north, cur,
-									 ncol, ring, vlc_ring, sig, quads, lane);
+				if(passes == 1)
+					decoded = ht_cleanup<false>(l.bytes + cb.data_off, (int)len1, mm, w, h, blk, l.stride, dq,
+												north, cur, ncol, ring, vlc_ring, sig, quads, lane);
+				else if(REFINE && ht_cleanup<true>(l.bytes + cb.data_off, (int)len1, mm, w, h, blk, l.stride,
+													dq, north, cur, ncol, ring, vlc_ring, sig, quads, lane))
+				{
+					decoded = true;
+					__syncwarp();
+					// the cleanup pass's rings are free now: bit rows in the MagSgn ring, membership
+					// words in (sig, quads), MagRef bits in the VLC ring
+					ht_refine(blk, l.stride, w, h, dq.p, passes, l.bytes + cb.data_off + len1, (int)len2, ring,
+							  sig, vlc_ring, lane);
+					for(uint32_t y = 0; y < h; ++y)
+						for(uint32_t x = lane; x < w; x += 32)
+						{
+							uint32_t* v = blk + (size_t)y * l.stride + x;
+							*v = ht_dequant(dq, *v);
+						}
+				}
 			}
 			if(!decoded && lane == 0)
 				atomicAdd(l.status, 1u);
@@ -625,7 +905,8 @@ int grkb_launch_t1_ht_decode(const T1Launch& l, cudaStream_t s)
 	}
 	const uint32_t max_w = l.max_ht_w ? l.max_ht_w : 64;
 	const size_t smem = (size_t)(HT_THREADS / 32) * ht_warp_bytes(max_w);
-	GRKB_ENSURE_SMEM(t1_ht_decode_kernel, smem);
+	GRKB_ENSURE_SMEM(t1_ht_decode_kernel<false>, smem);
+	GRKB_ENSURE_SMEM(t1_ht_decode_kernel<true>, smem);
 	int dev = 0, sms = 148;
 	cudaGetDevice(&dev);
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -634,7 +915,10 @@ int grkb_launch_t1_ht_decode(const T1Launch& l, cudaStream_t s)
 	if(ctas > need)
 		ctas = need;
 	GRKB_CUDA_CHECK(cudaMemsetAsync(l.counter, 0, sizeof(uint32_t), s));
-	t1_ht_decode_kernel<<<ctas, HT_THREADS, smem, s>>>(l, max_w);
+	if(l.ht_refine)
+		t1_ht_decode_kernel<true><<<ctas, HT_THREADS, smem, s>>>(l, max_w);
+	else
+		t1_ht_decode_kernel<false><<<ctas, HT_THREADS, smem, s>>>(l, max_w);
 	GRKB_CUDA_CHECK(cudaGetLastError());
 	return 0;
 }

@@ -39,7 +39,7 @@ struct grkb_decoder
 	// last tile
 	uint32_t nblocks = 0, nsegs = 0;
 	uint32_t max_area = 0, max_flag_words = 0, max_ht_w = 0;
-	bool any_mq = false, any_ht = false;
+	bool any_mq = false, any_ht = false, ht_refine = false;
 	cudaEvent_t ev[6] = {};
 };
 
@@ -96,7 +96,7 @@ int scan_blocks(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks, cons
 	d->max_area = 1;
 	d->max_flag_words = 9;
 	d->max_ht_w = 4;
-	d->any_mq = d->any_ht = false;
+	d->any_mq = d->any_ht = d->ht_refine = false;
 	constexpr uint32_t NB = 1024;
 	uint32_t hist[NB + 1];
 	memset(hist, 0, sizeof(hist));
@@ -128,6 +128,8 @@ int scan_blocks(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks, cons
 		if(b.cblk_sty & GRKB_CBLKSTY_HT)
 		{
 			d->any_ht = true;
+			if(b.numsegs > 1)
+				d->ht_refine = true;
 			if(b.w > d->max_ht_w)
 				d->max_ht_w = b.w;
 		}
@@ -180,6 +182,7 @@ int run_device(grkb_decoder* d, void* const* coeff_planes, uint32_t stride, bool
 	l.max_area = d->max_area;
 	l.max_flag_words = d->max_flag_words;
 	l.max_ht_w = d->max_ht_w;
+	l.ht_refine = d->ht_refine ? 1u : 0u;
 	if(ev)
 		cudaEventRecord(ev[0], d->stream);
 	if(d->any_mq)

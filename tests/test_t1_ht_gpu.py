@@ -12,18 +12,25 @@ G = os.path.join(os.path.dirname(__file__), "golden")
 
 
 def _run(entries, reversible, pw=1100):
-    """entries: [(bytes, k_msbs, w, h, numpasses)] stacked vertically in one plane"""
+    """entries: [(bytes, k_msbs, w, h, numpasses[, lengths2])] stacked vertically in one plane; with
+    lengths2 the block has two codeword segments: cleanup | SigProp [+ MagRef]"""
     blocks = np.zeros(len(entries), dtype=T.CBLK_DTYPE)
     segs, chunks, off, y = [], [], 0, 0
-    for i, (data, kmsbs, w, h, npass) in enumerate(entries):
+    for i, ent in enumerate(entries):
+        data, kmsbs, w, h, npass = ent[:5]
+        l2 = ent[5] if len(ent) > 5 else 0
         b = blocks[i]
         b["x"], b["y"], b["w"], b["h"] = (i * 3) % 7, y, w, h
         b["cblk_sty"], b["k_msbs"], b["numbps"] = T.CBLKSTY_HT, kmsbs, 1
-        b["numsegs"], b["seg_first"] = (1 if data is not None else 0), len(segs)
+        b["numsegs"], b["seg_first"] = ((2 if l2 else 1) if data is not None else 0), len(segs)
         b["data_off"], b["data_len"] = off, (len(data) if data is not None else 0)
         b["scale"] = 2.0 ** -20 * 1.25
         if data is not None:
-            segs.append((len(data), npass))
+            if l2:
+                segs.append((len(data) - l2, 1))
+                segs.append((l2, npass - 1))
+            else:
+                segs.append((len(data), npass))
             chunks.append(data)
             off += len(data)
         y += h + 1
@@ -63,9 +70,55 @@ def test_ht_decode_golden(gpu, reversible):
             assert np.array_equal(got[b["y"]:b["y"] + b["h"], b["x"]:b["x"] + b["w"]], t["vals_%d" % k])
 
 
+@pytest.mark.parametrize("reversible", [1, 0])
+def test_ht_refinement_passes_golden(gpu, reversible):
+    """SigProp / MagRef: blocks with a second segment against what the reference's
+    block decoder returned for the same bytes (tests/golden/make_golden_ht_refine.py)"""
+    t = np.load(os.path.join(G, "t1_ht_refine.npz"))
+    entries, want = [], []
+    for k, (w, h, kmsbs, passes, l2) in enumerate(t["cases"]):
+        entries.append((t["bytes_%d" % k].tobytes(), int(kmsbs), int(w), int(h), int(passes), int(l2)))
+        want.append(t["dec_%d" % k])
+    blocks, got, rej, base = _run(entries, reversible)
+    assert rej == 0
+    exp = base.copy()
+    for b, d in zip(blocks, want):
+        exp[b["y"]:b["y"] + b["h"], b["x"]:b["x"] + b["w"]] = _dequant(d, int(b["k_msbs"]), reversible,
+                                                                    b["scale"])
+    assert np.array_equal(got, exp)
+
+
+def test_ht_refinement_passes_match_oracle(gpu, orc):
+    """many more shapes (up to 1024 wide / tall), densities and refinement byte patterns, against
+    the oracle restatement; mixed with cleanup-only blocks in the same launch"""
+    from common import ht_refine_case
+    from oracle import oracle as O
+    rng = np.random.default_rng(11)
+    shapes = [(64, 64), (32, 32), (8, 8), (4, 4), (5, 7), (7, 5), (1, 1), (2, 1), (1, 2), (3, 3), (16, 9),
+              (9, 16), (13, 10), (33, 6), (6, 33), (64, 1), (1, 64), (64, 2), (64, 3), (64, 5), (64, 6),
+              (64, 7), (12, 11), (17, 13), (100, 4), (4, 100), (40, 21), (1024, 4), (4, 1024), (512, 8),
+              (96, 40), (65, 63)]
+    entries, want = [], []
+    for it in range(4 * len(shapes)):
+        w, h = shapes[it % len(shapes)]
+        _, kmsbs, data, l2 = ht_refine_case(rng, w, h, O.orc_ht_encode)
+        passes = 1 + it % 3
+        if passes == 1:
+            data, l2 = data[:len(data) - l2], 0
+        rc, dec = O.orc_ht_decode(data, kmsbs, w, h, num_passes=passes, lengths2=l2)
+        assert rc == 0
+        entries.append((data, kmsbs, w, h, passes, l2))
+        want.append(dec)
+    blocks, got, rej, base = _run(entries, 1)
+    assert rej == 0
+    for i, (b, d) in enumerate(zip(blocks, want)):
+        e = _dequant(d, int(b["k_msbs"]), 1, b["scale"])
+        assert np.array_equal(got[b["y"]:b["y"] + b["h"], b["x"]:b["x"] + b["w"]], e), (i, entries[i][1:])
+
+
 def test_ht_decode_rejects_like_reference(gpu):
-    """T1HT::decompress / ojph_decode_codeblock reject: more than one pass (lengths2 is always 0
-    in Grok), a missing_msbs too small for the coded U_q, bad Scup, empty streams; uncoded blocks
+    """T1HT::decompress / ojph_decode_codeblock reject: more than one pass without a second
+    segment (lengths2 is always 0 in Grok), a missing_msbs too small for the coded U_q, bad Scup, empty streams; uncoded blocks
     decode to zeros without error"""
     t = np.load(os.path.join(G, "t1_ht.npz"))
     good = t["bytes_7"].tobytes()
