@@ -116,6 +116,11 @@ typedef struct grkb_cblk
 				  * encode 9/7: band stepsize (T1Part1.cpp:75-76) */
 } grkb_cblk;
 
+/* HT blocks (GRKB_CBLKSTY_HT): one segment with one pass is a cleanup-only block (all that
+ * Grok's own host produces, T1HT.cpp:171-173).  Two segments are cleanup | SigProp [+ MagRef]:
+ * segment 0 holds the cleanup pass (numpasses 1, ojph_decode_codeblock's lengths1), segment 1 the
+ * refinement passes (numpasses 1 or 2, lengths2), ojph_block_decoder.cpp:989-1057.  More than one
+ * pass without a second segment is rejected like there (:1014-1020). */
 typedef struct grkb_seg
 {
 	uint32_t len; /* bytes of this codeword segment */
