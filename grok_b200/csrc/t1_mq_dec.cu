@@ -43,7 +43,8 @@ struct Mq
 	int32_t ct;
 	const uint8_t* p; // segment bytes
 	uint32_t len, pos;
-	uint32_t cur, nxt; // bytes at pos and pos+1 (0xFF past the end: mqc_dec.cpp:78-90)
+	uint32_t cur; // byte at pos (0xFF past the end: mqc_dec.cpp:78-90)
+	uint32_t w; // bytes pos+1 .. pos+4, the first in the top byte, 0xFF past the end
 };
 
 static __device__ __forceinline__ uint32_t seg_byte(const Mq& q, uint32_t pos)
@@ -51,17 +52,46 @@ static __device__ __forceinline__ uint32_t seg_byte(const Mq& q, uint32_t pos)
 	return pos < q.len ? (uint32_t)__ldg(q.p + pos) : 0xFFu;
 }
 
-// bytein_dec_macro (mqc_dec_inl.h:82-108), run ahead of time: bytes are added until at least
-// 33 shifts are covered (a renormalisation shifts by at most 15)
+// bytes pos .. pos+3 of the segment, the first in the top byte, 0xFF past the end (two aligned
+// words and a funnel shift; the byte pool has 16 bytes of slack behind it)
+static __device__ __forceinline__ uint32_t seg_word(const Mq& q, uint32_t pos)
+{
+	const uintptr_t a = reinterpret_cast<uintptr_t>(q.p) + pos;
+	const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+	const uint32_t le = __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8u * ((uint32_t)a & 3u));
+	const int32_t left = (int32_t)q.len - (int32_t)pos; // real bytes from pos on
+	const uint32_t pad = left >= 4 ? 0u : (left <= 0 ? 0xFFFFFFFFu : 0xFFFFFFFFu >> (8 * left));
+	return __byte_perm(le, 0, 0x0123) | pad;
+}
+
+// bytein_dec_macro (mqc_dec_inl.h:82-108), run ahead of time: called with ct < 16, bytes are
+// added until at least 32 shifts are covered (a renormalisation shifts by at most 15).  Four
+// bytes go in at once when none of the bytes that decide the stuffing rule (the current one and
+// the next three) is 0xFF -- all but ~2 % of the calls.
 static __device__ __forceinline__ void mq_fill(Mq& q)
 {
+	{
+		const uint32_t y = ~((q.cur << 24) | (q.w >> 8));
+		if(((y - 0x01010101u) & ~y & 0x80808080u) == 0) // no zero byte in y
+		{
+			const uint64_t cc = (((uint64_t)q.c << 32) | q.cl) + ((uint64_t)q.w << (16 - q.ct));
+			q.c = (uint32_t)(cc >> 32);
+			q.cl = (uint32_t)cc;
+			q.ct += 32;
+			q.pos += 4;
+			q.cur = q.w & 0xFFu;
+			q.w = seg_word(q, q.pos + 1);
+			return;
+		}
+	}
+	uint32_t nxt = q.w >> 24;
 	do
 	{
-		uint32_t add = q.nxt, at = 40, step = 8;
+		uint32_t add = nxt, at = 40, step = 8;
 		bool adv = true;
 		if(q.cur == 0xFF)
 		{
-			if(q.nxt > 0x8F)
+			if(nxt > 0x8F)
 			{
 				add = 0xFF; // c += 0xFF00, the position does not advance
 				adv = false;
@@ -80,10 +110,11 @@ static __device__ __forceinline__ void mq_fill(Mq& q)
 		if(adv)
 		{
 			q.pos++;
-			q.cur = q.nxt;
-			q.nxt = seg_byte(q, q.pos + 1);
+			q.cur = nxt;
+			nxt = seg_byte(q, q.pos + 1);
 		}
 	} while(q.ct <= 32);
+	q.w = seg_word(q, q.pos + 1);
 }
 
 static __device__ __forceinline__ void mq_init(Mq& q, const uint8_t* p, uint32_t len)
@@ -92,7 +123,7 @@ static __device__ __forceinline__ void mq_init(Mq& q, const uint8_t* p, uint32_t
 	q.len = len;
 	q.pos = 0;
 	q.cur = seg_byte(q, 0);
-	q.nxt = seg_byte(q, 1);
+	q.w = seg_word(q, 1);
 	q.c = q.cur << 16;
 	q.cl = 0;
 	q.ct = 0;
@@ -202,7 +233,7 @@ static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t cxs, uint32
 	const uint32_t n = shift_amount(a); // shifts until the top bit of A is set
 	if(n)
 	{
-		const uint32_t next4 = (lps ? e >> 22 : e >> 14) & 0x1FCu; // next state x 4
+		const uint32_t next4 = (e >> (lps ? 22u : 14u)) & 0x1FCu; // next state x 4
 		sts32(slot, *reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(c_dec.mq) + next4));
 	}
 	q.a = a << n;
