@@ -239,6 +239,14 @@ struct grkb_encoder
 	// last tile, for grkb_encoder_time_device
 	T1EncLaunch last{};
 	bool any_mq = false, any_ht = false, have_last = false;
+	// tile in flight (grkb_encoder_submit .. grkb_encoder_wait)
+	bool pending = false;
+	uint32_t p_nblocks = 0;
+	grkb_coded* p_coded = nullptr;
+	grkb_pass* p_passes = nullptr;
+	uint8_t* p_bytes = nullptr;
+	size_t p_cap = 0;
+	uint64_t* h_total = nullptr; // pinned
 };
 
 static int encoder_front(grkb_encoder* e, cudaStream_t s)
@@ -307,6 +315,7 @@ int grkb_encoder_create(const grkb_tile_params* p, grkb_encoder** out)
 	}
 	for(auto& v : e->ev)
 		ok = ok && cudaEventCreate(&v) == cudaSuccess;
+	ok = ok && cudaMallocHost(&e->h_total, sizeof(uint64_t)) == cudaSuccess;
 	if(!ok || cudaStreamSynchronize(e->st.stream) != cudaSuccess)
 	{
 		grkb_set_error("grkb_encoder_create: device allocation failed: %s",
@@ -335,23 +344,28 @@ void grkb_encoder_destroy(grkb_encoder* e)
 	for(auto& v : e->ev)
 		if(v)
 			cudaEventDestroy(v);
+	if(e->h_total)
+		cudaFreeHost(e->h_total);
 	e->st.release();
 	delete e;
 }
 
-int grkb_encoder_encode(grkb_encoder* e, const int32_t* const* image, uint32_t stride,
+int grkb_encoder_submit(grkb_encoder* e, const int32_t* const* image, uint32_t stride,
 						const grkb_enc_cblk* blocks, uint32_t nblocks, const double* mct_norms,
 						uint32_t mct_numcomps, int rate_control, grkb_coded* coded,
-						grkb_pass* passes, uint8_t* bytes, size_t cap, size_t* used)
+						grkb_pass* passes, uint8_t* bytes, size_t cap)
 {
 	if(!e || !image || stride < (e ? e->W : 0) || (nblocks && (!blocks || !coded || !passes)) ||
 	   (cap && !bytes) || mct_numcomps > GRKB_MAX_COMPS)
 	{
-		grkb_set_error("grkb_encoder_encode: bad arguments");
+		grkb_set_error("grkb_encoder_submit: bad arguments");
 		return -1;
 	}
-	if(used)
-		*used = 0;
+	if(e->pending)
+	{
+		grkb_set_error("grkb_encoder_submit: a tile is already in flight (call grkb_encoder_wait)");
+		return -1;
+	}
 	GRKB_CUDA_CHECK(cudaSetDevice(e->st.device));
 	cudaStream_t s = e->st.stream;
 	T1EncLaunch l{};
@@ -373,14 +387,21 @@ int grkb_encoder_encode(grkb_encoder* e, const int32_t* const* image, uint32_t s
 	if(encoder_front(e, s))
 		return -1;
 	e->have_last = false;
+	e->pending = true;
+	e->p_nblocks = nblocks;
+	e->p_coded = coded;
+	e->p_passes = passes;
+	e->p_bytes = bytes;
+	e->p_cap = cap;
+	*e->h_total = 0;
 	if(nblocks == 0)
-	{
-		GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
 		return 0;
-	}
 	if(e->st.blocks.reserve((size_t)nblocks * sizeof(grkb_enc_cblk)) ||
 	   e->st.packed.reserve(cap ? cap : 16))
+	{
+		e->pending = false;
 		return -1;
+	}
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(e->st.blocks.p, blocks, (size_t)nblocks * sizeof(grkb_enc_cblk),
 									cudaMemcpyHostToDevice, s));
 	l.blocks = (const grkb_enc_cblk*)e->st.blocks.p;
@@ -396,32 +417,72 @@ int grkb_encoder_encode(grkb_encoder* e, const int32_t* const* image, uint32_t s
 	l.packed = (uint8_t*)e->st.packed.p;
 	l.packed_cap = cap;
 	if(run_encoders(e->st, l, any_mq, any_ht))
+	{
+		e->pending = false;
 		return -1;
+	}
 	e->last = l;
 	e->any_mq = any_mq;
 	e->any_ht = any_ht;
 	e->have_last = true;
-	uint64_t total = 0;
+	// the block table and the total come back with the kernels; the pass table and the bytes
+	// are sized from them in grkb_encoder_wait
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(coded, l.coded, (size_t)nblocks * sizeof(grkb_coded),
 									cudaMemcpyDeviceToHost, s));
-	GRKB_CUDA_CHECK(cudaMemcpyAsync(passes, l.passes,
-									(size_t)nblocks * GRKB_ENC_MAX_PASSES * sizeof(grkb_pass),
-									cudaMemcpyDeviceToHost, s));
-	GRKB_CUDA_CHECK(cudaMemcpyAsync(&total, l.packed_used, sizeof(total), cudaMemcpyDeviceToHost, s));
+	GRKB_CUDA_CHECK(cudaMemcpyAsync(e->h_total, l.packed_used, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+	return 0;
+}
+
+int grkb_encoder_wait(grkb_encoder* e, size_t* used)
+{
+	if(used)
+		*used = 0;
+	if(!e || !e->pending)
+	{
+		grkb_set_error("grkb_encoder_wait: no tile in flight");
+		return -1;
+	}
+	e->pending = false;
+	GRKB_CUDA_CHECK(cudaSetDevice(e->st.device));
+	cudaStream_t s = e->st.stream;
 	GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
+	if(e->p_nblocks == 0)
+		return 0;
+	const uint64_t total = *e->h_total;
 	if(total == ~(uint64_t)0)
 	{
-		grkb_set_error("grkb_encoder_encode: output pool of %zu bytes is too small", cap);
+		grkb_set_error("grkb_encoder_encode: output pool of %zu bytes is too small", e->p_cap);
 		return -2;
 	}
+	// only the pass records that exist cross the bus: the first max(numpasses) of every row
+	uint32_t maxp = 1;
+	for(uint32_t i = 0; i < e->p_nblocks; ++i)
+		if(e->p_coded[i].numpasses > maxp)
+			maxp = e->p_coded[i].numpasses;
+	if(maxp > GRKB_ENC_MAX_PASSES)
+		maxp = GRKB_ENC_MAX_PASSES;
+	const size_t pitch = (size_t)GRKB_ENC_MAX_PASSES * sizeof(grkb_pass);
+	GRKB_CUDA_CHECK(cudaMemcpy2DAsync(e->p_passes, pitch, e->last.passes, pitch, (size_t)maxp * sizeof(grkb_pass),
+									  e->p_nblocks, cudaMemcpyDeviceToHost, s));
 	if(total)
-	{
-		GRKB_CUDA_CHECK(cudaMemcpyAsync(bytes, l.packed, (size_t)total, cudaMemcpyDeviceToHost, s));
-		GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
-	}
+		GRKB_CUDA_CHECK(cudaMemcpyAsync(e->p_bytes, e->last.packed, (size_t)total, cudaMemcpyDeviceToHost, s));
+	GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
 	if(used)
 		*used = (size_t)total;
 	return 0;
+}
+
+int grkb_encoder_encode(grkb_encoder* e, const int32_t* const* image, uint32_t stride,
+						const grkb_enc_cblk* blocks, uint32_t nblocks, const double* mct_norms,
+						uint32_t mct_numcomps, int rate_control, grkb_coded* coded,
+						grkb_pass* passes, uint8_t* bytes, size_t cap, size_t* used)
+{
+	if(used)
+		*used = 0;
+	if(grkb_encoder_submit(e, image, stride, blocks, nblocks, mct_norms, mct_numcomps, rate_control, coded,
+						   passes, bytes, cap))
+		return -1;
+	return grkb_encoder_wait(e, used);
 }
 
 int grkb_encoder_time_device(grkb_encoder* e, uint32_t iters, uint32_t warmup, float ms[3])

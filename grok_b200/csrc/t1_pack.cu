@@ -68,8 +68,22 @@ __global__ void __launch_bounds__(256) pack_copy_kernel(const T1EncLaunch l)
 	const grkb_coded c = l.coded[bi];
 	const uint8_t* src = l.slots + (size_t)bi * l.slot_bytes + SLOT_LEAD;
 	uint8_t* dst = l.packed + c.data_off;
-	for(uint32_t i = lane; i < c.data_len; i += 32)
-		dst[i] = src[i];
+	const uint32_t len = c.data_len;
+	// aligned 32-bit stores: the bytes up to the first aligned destination word one by one, then
+	// every destination word from the two source words it straddles (the slot is 16-byte aligned,
+	// so the straddle is the same for all words), then the tail
+	const uint32_t head = min(len, (4u - ((uint32_t)reinterpret_cast<uintptr_t>(dst) & 3u)) & 3u);
+	if(lane < head)
+		dst[lane] = src[lane];
+	const uint32_t nwords = (len - head) >> 2;
+	const uint32_t* sw = reinterpret_cast<const uint32_t*>(src);
+	uint32_t* dw = reinterpret_cast<uint32_t*>(dst + head);
+	const uint32_t sh = 8u * head;
+	for(uint32_t j = lane; j < nwords; j += 32)
+		dw[j] = __funnelshift_r(sw[j], sw[j + 1], sh);
+	const uint32_t done = head + 4u * nwords;
+	if(done + lane < len)
+		dst[done + lane] = src[done + lane];
 }
 } // namespace
 

@@ -16,6 +16,10 @@ lib.grkb_encoder_destroy.restype = None
 lib.grkb_encoder_encode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32,
                                     C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p,
                                     C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]
+lib.grkb_encoder_submit.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32,
+                                    C.c_void_p, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.c_size_t]
+lib.grkb_encoder_wait.argtypes = [C.c_void_p, C.POINTER(C.c_size_t)]
 lib.grkb_encoder_time_device.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_float)]
 
 # weights of the colour components in the distortion estimate (mct::get_norms_rev / _irrev,
@@ -96,6 +100,31 @@ class TileEncoder:
                                       0 if norms is None else len(norms), int(rate_control),
                                       coded.ctypes.data, passes.ctypes.data, buf.ctypes.data, cap,
                                       C.byref(used)), "grkb_encoder_encode")
+        return coded, passes, buf[:used.value]
+
+    def submit(self, image, blocks, out, mct_norms=None, rate_control=False):
+        """grkb_encoder_submit: enqueue one tile without waiting.  image planes, blocks and the
+        (coded, passes, bytes) arrays of `out` should be page-locked (tile.PinnedArray) and are
+        kept referenced here until wait()."""
+        blocks = np.ascontiguousarray(blocks, dtype=T.ENC_CBLK_DTYPE)
+        a = [np.ascontiguousarray(p, dtype=np.int32) for p in image]
+        stride = a[0].strides[0] // 4
+        coded, passes, buf = out
+        ptrs = (C.c_void_p * len(a))(*[p.ctypes.data for p in a])
+        norms = None if mct_norms is None else np.ascontiguousarray(mct_norms, dtype=np.float64)
+        self._inflight = (a, blocks, norms, ptrs, out)
+        check(lib.grkb_encoder_submit(self.h, ptrs, stride, blocks.ctypes.data, len(blocks),
+                                      None if norms is None else norms.ctypes.data,
+                                      0 if norms is None else len(norms), int(rate_control),
+                                      coded.ctypes.data, passes.ctypes.data, buf.ctypes.data, buf.size),
+              "grkb_encoder_submit")
+
+    def wait(self):
+        """grkb_encoder_wait -> (coded, passes, bytes) of the tile submitted last"""
+        used = C.c_size_t()
+        check(lib.grkb_encoder_wait(self.h, C.byref(used)), "grkb_encoder_wait")
+        coded, passes, buf = self._inflight[4]
+        self._inflight = None
         return coded, passes, buf[:used.value]
 
     def time_device(self, iters, warmup):

@@ -320,6 +320,18 @@ int grkb_encoder_encode(grkb_encoder* e, const int32_t* const* image, uint32_t s
 						const grkb_enc_cblk* blocks, uint32_t nblocks, const double* mct_norms,
 						uint32_t mct_numcomps, int rate_control, grkb_coded* coded,
 						grkb_pass* passes, uint8_t* bytes, size_t cap, size_t* used);
+/* The same in two halves, so that several encoders (one per frame or tile, each with its own
+ * stream) can be kept in flight and the copies of one overlap the kernels of another (the batch
+ * path of grk_plugin_batch_compress): submit enqueues H2D, all kernels and the D2H of the block
+ * table without waiting; wait blocks until they are done, then fetches the pass records that
+ * exist (the first max(numpasses) of every row) and the coded bytes.  image, blocks, coded,
+ * passes and bytes must stay valid until wait returns; page-locked memory (grkb_host_alloc)
+ * makes the copies asynchronous. */
+int grkb_encoder_submit(grkb_encoder* e, const int32_t* const* image, uint32_t stride,
+						const grkb_enc_cblk* blocks, uint32_t nblocks, const double* mct_norms,
+						uint32_t mct_numcomps, int rate_control, grkb_coded* coded,
+						grkb_pass* passes, uint8_t* bytes, size_t cap);
+int grkb_encoder_wait(grkb_encoder* e, size_t* used);
 /* Re-runs the device stages of the last tile (image still resident), CUDA events on the
  * encoder's stream: ms[0] whole pass, ms[1] DC/MCT/wavelet, ms[2] block coding + packing. */
 int grkb_encoder_time_device(grkb_encoder* e, uint32_t iters, uint32_t warmup, float ms[3]);

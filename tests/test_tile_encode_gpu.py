@@ -83,3 +83,38 @@ def test_tile_encode_rate_control_distortions(gpu, orc):
             d = passes[i, :n]["distortion"]
             assert np.all(np.diff(d) >= 0) and d[-1] == c["distortion"] and d[-1] > 0
             assert np.all(np.diff(passes[i, :n]["rate"].astype(np.int64)) >= 0)
+
+
+def test_two_encoders_in_flight(gpu, orc):
+    """grkb_encoder_submit / grkb_encoder_wait: two encoders with different frames in flight give
+    the same block tables, pass records and bytes as the synchronous call; a second submit on a
+    busy encoder and a wait on an idle one are errors"""
+    w, h, nr, prec = 200, 136, 4, 10
+    params = T.tile_params(0, 0, w, h, 3, nr, 0, 1, prec)
+    blocks, geom, qcd = E.enc_block_table(0, 0, w, h, 3, nr, prec, 0, cblk_exp=(5, 5))
+    n = len(blocks)
+    imgs = [H.synth_image(w, h, 3, prec, seed=40 + k) for k in range(2)]
+    ref = E.TileEncoder(params)
+    want = []
+    for img in imgs:
+        c, p, d = ref.encode(img, blocks, mct_norms=E.MCT_NORMS_IRREV, rate_control=True)
+        want.append((c.copy(), p.copy(), bytes(d)))
+    ref.close()
+    encs = [E.TileEncoder(params) for _ in range(2)]
+    outs = [(np.zeros(n, T.CODED_DTYPE), np.zeros((n, T.ENC_MAX_PASSES), T.PASS_DTYPE),
+             np.zeros(w * h * 3 * 4, np.uint8)) for _ in range(2)]
+    for k in range(2):
+        encs[k].submit(imgs[k], blocks, outs[k], mct_norms=E.MCT_NORMS_IRREV, rate_control=True)
+    with pytest.raises(Exception):
+        encs[0].submit(imgs[0], blocks, outs[0])
+    for k in range(2):
+        c, p, d = encs[k].wait()
+        wc, wp, wd = want[k]
+        assert np.array_equal(c, wc) and bytes(d) == wd
+        for i in range(n):
+            m = int(c[i]["numpasses"])
+            assert np.array_equal(p[i, :m], wp[i, :m])
+    with pytest.raises(Exception):
+        encs[0].wait()
+    for e in encs:
+        e.close()

@@ -65,12 +65,33 @@ def ht_encode(args):
            T.PinnedArray((W * H * 3 * 2,), np.uint8).array)
     coded, passes, data = enc.encode(src, blocks, out=out)
     assert not coded["failed"].any()
-    for _ in range(2):
-        enc.encode(src, blocks, out=out)
+    # end to end: K encoders in flight (grkb_encoder_submit / wait), one frame each, so the H2D of
+    # one frame overlaps the kernels and the D2H of another
+    K = max(1, args.inflight)
+    pblocks = T.PinnedArray((n,), T.ENC_CBLK_DTYPE)
+    pblocks.array[:] = blocks
+    encs = [enc] + [E.TileEncoder(params) for _ in range(K - 1)]
+    outs = [out] + [(T.PinnedArray((n,), T.CODED_DTYPE).array,
+                     T.PinnedArray((n, T.ENC_MAX_PASSES), T.PASS_DTYPE).array,
+                     T.PinnedArray((W * H * 3 * 2,), np.uint8).array) for _ in range(K - 1)]
+
+    def run(nframes):
+        pend = [False] * K
+        for f in range(nframes):
+            k = f % K
+            if pend[k]:
+                encs[k].wait()
+            encs[k].submit(src, pblocks.array, outs[k])
+            pend[k] = True
+        for k in range(K):
+            if pend[k]:
+                encs[k].wait()
+
+    run(2 * K)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        coded, passes, data = enc.encode(src, blocks, out=out)
-    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    run(args.steps * K)
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / (args.steps * K)
+    coded, passes, data = enc.encode(src, blocks, out=out)
     tm = enc.time_device(args.steps, 3)
     # round trip through the GPU decoder: lossless
     dblocks, dsegs = E.decode_table(blocks, coded, passes, geom, qcd, prec, 1, True)
@@ -95,8 +116,9 @@ def ht_encode(args):
         "config": {"workload": "htj2k_encode_4096x2160_rgb12_53_rct_lossless_5lvl_cblk64_1tile",
                    "code_blocks": int(n), "coded_bytes": int(len(data))},
         "e2e": {"value": mp / (e2e_ms * 1e-3), "unit": "Mpixel/s", "ms_per_step": e2e_ms,
+                "encoders_in_flight": K,
                 "h2d_bytes_per_step": int(W * H * 3 * 4 + blocks.nbytes),
-                "d2h_bytes_per_step": int(len(data) + coded.nbytes + passes.nbytes)},
+                "d2h_bytes_per_step": int(len(data) + coded.nbytes + n * int(coded["numpasses"].max()) * 16)},
         "stages_ms": {"dc_rct_fdwt": tm["dwt_ms"], "t1_ht_encode_pack": tm["t1_ms"]},
         "round_trip_lossless": bool(lossless), "cpu_baseline": cpu}), flush=True)
 
@@ -219,11 +241,26 @@ def mq_encode(args):
     out = (T.PinnedArray((n,), T.CODED_DTYPE).array, T.PinnedArray((n, T.ENC_MAX_PASSES), T.PASS_DTYPE).array,
            T.PinnedArray((W * H * 3 * 2,), np.uint8).array)
 
+    K = max(1, args.inflight)
+    pblocks = T.PinnedArray((n,), T.ENC_CBLK_DTYPE)
+    pblocks.array[:] = blocks
+    encs = [enc] + [E.TileEncoder(params) for _ in range(K - 1)]
+    outs = [out] + [(T.PinnedArray((n,), T.CODED_DTYPE).array,
+                     T.PinnedArray((n, T.ENC_MAX_PASSES), T.PASS_DTYPE).array,
+                     T.PinnedArray((W * H * 3 * 2,), np.uint8).array) for _ in range(K - 1)]
+
     def one_pass():
-        nb = 0
-        for src in pins:
-            coded, passes, data = enc.encode(src, blocks, mct_norms=E.MCT_NORMS_IRREV, rate_control=True, out=out)
-            nb += len(data)
+        # frames of this rank, K encoders in flight (grkb_encoder_submit / wait)
+        nb, pend = 0, [False] * K
+        for i, src in enumerate(pins):
+            k = i % K
+            if pend[k]:
+                nb += len(encs[k].wait()[2])
+            encs[k].submit(src, pblocks.array, outs[k], mct_norms=E.MCT_NORMS_IRREV, rate_control=True)
+            pend[k] = True
+        for k in range(K):
+            if pend[k]:
+                nb += len(encs[k].wait()[2])
         return nb
 
     nb = one_pass()
@@ -271,7 +308,9 @@ def mq_encode(args):
                             "PCRD and T2 stay on the host (SURVEY 8f N2)"},
         "e2e": {"value": mp * nframes / (ms * 1e-3), "unit": "Mpixel/s", "ms_per_batch": ms,
                 "h2d_bytes_per_frame": int(W * H * 3 * 4 + blocks.nbytes),
-                "d2h_bytes_per_frame": int(nb // max(1, len(mine)) + out[0].nbytes + out[1].nbytes)},
+                "encoders_in_flight": K,
+                "d2h_bytes_per_frame": int(nb // max(1, len(mine)) + out[0].nbytes +
+                                           n * int(out[0]["numpasses"].max()) * 16)},
         "stages_ms": {"dc_ict_fdwt": tm["dwt_ms"], "t1_mq_encode_pack": tm["t1_ms"]},
         "cpu_baseline": cpu}), flush=True)
     if world > 1:
@@ -284,11 +323,13 @@ def main():
     ap.add_argument("what", choices=["ht_encode", "tiled", "mq_encode"])
     ap.add_argument("--frames", type=int, default=8)
     ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--inflight", type=int, default=4)
+    ap.add_argument("--inflight", type=int, default=None)
     ap.add_argument("--size", type=int, default=8192)
     ap.add_argument("--verify", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    if args.inflight is None:
+        args.inflight = 4 if args.what == "tiled" else 2
     {"ht_encode": ht_encode, "tiled": tiled, "mq_encode": mq_encode}[args.what](args)
 
 
