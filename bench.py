@@ -230,6 +230,8 @@ def run_ours(args):
     if grok_b200.lib.grkb_device_count() < 1:
         raise SystemExit("bench.py: no CUDA device visible; the product has no CPU fallback")
     grok_b200._lib.check(grok_b200.lib.grkb_set_device(local), "grkb_set_device")
+    from grok_b200 import shard
+    numa_bound = shard.bind_to_device(local) if world > 1 else False
     dist = None
     if world > 1:
         import torch
@@ -346,6 +348,7 @@ def run_ours(args):
                    "mct": "RCT" if HT else "ICT", "levels": NUMRES - 1,
                    "block_coder": "HT" if HT else "MQ", "cblk": "64x64", "code_blocks": int(len(blocks)), "coded_bytes": int(data.size),
                    "frames_per_step": world, "sharding": "one frame per GPU per step, no collective",
+                   "host_threads_bound_to_gpu_numa_node": bool(numa_bound),
                    "l2": "working set per step (coded bytes + 2 x %d MB planes) exceeds the 126 MB L2"
                          % (NCOMP * W * H * 4 // 1000000)},
         "e2e": {"value": world * mp / (e2e_ms * 1e-3), "unit": "Mpixel/s", "frames_in_flight": K,

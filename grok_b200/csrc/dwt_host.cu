@@ -8,6 +8,8 @@
 // ever reads what another CTA of the same launch writes.  The forward transform is the mirror.
 #include "pipeline.h"
 #include "../../include/grk_b200.h"
+#include <ctype.h>
+#include <sched.h>
 #include <stdarg.h>
 #include <vector>
 #include <string.h>
@@ -369,6 +371,53 @@ int grkb_set_device(int device)
 const char* grkb_last_error(void)
 {
 	return g_err;
+}
+
+// Restrict the calling thread to the CPUs next to `device` (its PCI function's local_cpulist), so
+// that the page-locked buffers it allocates afterwards are first touched -- and the copies to and
+// from them stay -- on the GPU's own NUMA node.  With one process (or thread) per GPU on a
+// two-socket box the D2H of the int32 planes otherwise crosses the socket link for half the GPUs.
+// Returns 0 when the affinity was set, 1 when the box gives no topology (nothing changed).
+int grkb_bind_host_to_device(int device)
+{
+	char bus[32] = {};
+	GRKB_CUDA_CHECK(cudaDeviceGetPCIBusId(bus, (int)sizeof(bus), device));
+	for(char* c = bus; *c; ++c)
+		*c = (char)tolower(*c);
+	char path[128];
+	snprintf(path, sizeof(path), "/sys/bus/pci/devices/%s/local_cpulist", bus);
+	FILE* f = fopen(path, "r");
+	if(!f)
+		return 1;
+	char line[4096] = {};
+	const bool got = fgets(line, sizeof(line), f) != nullptr;
+	fclose(f);
+	if(!got)
+		return 1;
+	cpu_set_t allowed, want;
+	CPU_ZERO(&allowed);
+	CPU_ZERO(&want);
+	if(sched_getaffinity(0, sizeof(allowed), &allowed) != 0)
+		return 1;
+	int n = 0;
+	for(char* tok = strtok(line, ",\n"); tok; tok = strtok(nullptr, ",\n"))
+	{
+		int a = 0, b = 0;
+		const int k = sscanf(tok, "%d-%d", &a, &b);
+		if(k < 1)
+			continue;
+		if(k == 1)
+			b = a;
+		for(int c = a; c <= b && c < CPU_SETSIZE; ++c)
+			if(c >= 0 && CPU_ISSET(c, &allowed))
+			{
+				CPU_SET(c, &want);
+				++n;
+			}
+	}
+	if(n == 0 || n == CPU_COUNT(&allowed))
+		return 1; // no local CPUs among the allowed ones, or nothing to narrow
+	return sched_setaffinity(0, sizeof(want), &want) == 0 ? 0 : 1;
 }
 
 int grkb_dwt_host(void* data, uint32_t stride, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1,

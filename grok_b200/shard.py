@@ -18,6 +18,15 @@ def dist_env() -> Tuple[int, int, int]:
     return rank, local, world
 
 
+def bind_to_device(local_rank: int) -> bool:
+    """grkb_bind_host_to_device: keep this rank's threads (and the page-locked buffers it is about
+    to allocate) on the NUMA node of its GPU.  GRKB_NO_NUMA_BIND=1 leaves the affinity alone."""
+    if os.environ.get("GRKB_NO_NUMA_BIND") == "1":
+        return False
+    from ._lib import lib
+    return lib.grkb_bind_host_to_device(int(local_rank)) == 0
+
+
 def shard_units(n_units: int, rank: int, world: int) -> List[int]:
     """Unit u goes to rank u mod world (tile t -> GPU t mod G)."""
     if world < 1 or not (0 <= rank < world):

@@ -42,6 +42,12 @@ int grkb_version(void);
 int grkb_device_count(void);
 /* selects the device used by the calling thread for all later calls */
 int grkb_set_device(int device);
+/* Restricts the calling thread to the CPUs next to `device` (the local_cpulist of its PCI
+ * function), so that page-locked buffers allocated afterwards live on the GPU's own NUMA node.
+ * For hosts that run one thread or process per GPU (plugin deviceId = -1, torchrun ranks).
+ * Returns 0 when the affinity was narrowed, 1 when the box exposes no topology (nothing changed),
+ * negative on a CUDA error. */
+int grkb_bind_host_to_device(int device);
 /* last error text of the calling thread (static storage) */
 const char* grkb_last_error(void);
 
