@@ -8,13 +8,23 @@
 //   getwmsedec                        T1.cpp:418-436 (+ norms :239-277)
 //   MQ / RAW encoder                  t1/t1_part1/mqc_enc.cpp:86-332, mqc_enc_inl.h:38-124
 //
-// Shape: like the decoder (t1_mq_dec.cu) the MQ coder is one serial chain per block.  All lanes
-// of the warp load the block's rows from the coefficient plane (coalesced), quantise to
-// sign-magnitude with 6 fractional bits into shared memory and reduce the block maximum; lane 0
-// then walks the coding passes over the stripe-column state words (layout in t1.cuh), emitting
-// bytes into the block's slot in global memory with the byte under construction held in a
-// register (the coder's carry only ever touches that byte).  Per-pass rate / length /
-// termination and the double-precision distortion estimate are written to the pass table.
+// Shape: one code block per warp.  Unlike the decoder, the encoder knows every decision in
+// advance, so only the arithmetic coder itself is a serial chain:
+//   * all lanes load the block's rows from the coefficient plane (coalesced), quantise to
+//     sign-magnitude with 6 fractional bits into shared memory and reduce the block maximum;
+//   * every coding pass walks the stripes in segments of 32 columns, one column per lane: the
+//     lane finds which of its four samples the pass codes and their contexts as the
+//     neighbourhood stands when the scan reaches them, and leaves its (context, decision)
+//     symbols at its prefix-sum position of a list in shared memory.  The membership of the
+//     significance-propagation pass is recursive (the pass itself makes neighbours significant,
+//     one column to the west or one row up) and is iterated to its fixed point with shuffles;
+//     refinement and cleanup are known outright.  The state words (layout in t1.cuh) are
+//     updated by all lanes at once afterwards;
+//   * lane 0 feeds the list to the MQ (or bypass) coder, emitting bytes into the block's slot
+//     in global memory with the byte under construction held in a register (the coder's carry
+//     only ever touches that byte), and keeps the per-pass rate / length / termination records;
+//     the distortion estimate of a pass is a warp sum of table values (integers, so the order of
+//     the additions does not matter) turned into the reference's double-precision figure.
 #include "t1.cuh"
 
 namespace
@@ -253,41 +263,6 @@ struct EBlk
 	bool vsc;
 };
 
-static __device__ __forceinline__ uint32_t sc_index(uint32_t f, uint32_t fw, uint32_t fe, uint32_t r)
-{
-	const uint32_t nb = f >> (3 * r); // 3x3 neighbourhood of row r at bits 0..8
-	uint32_t i = ((nb >> 3) & 1u) | (((nb >> 5) & 1u) << 1) | (((nb >> 1) & 1u) << 2) |
-				 (((nb >> 7) & 1u) << 3);
-	i |= ((fw >> (18 + r + 1)) & 1u) << 4;
-	i |= ((fe >> (18 + r + 1)) & 1u) << 5;
-	i |= ((f >> (18 + r)) & 1u) << 6;
-	i |= ((f >> (18 + r + 2)) & 1u) << 7;
-	return i;
-}
-
-// update_flags_macro, T1.cpp:209-233, on the stripe-column words
-static __device__ __forceinline__ void mark_significant(const EBlk& b, uint32_t* fp, uint32_t& f,
-														 uint32_t r, uint32_t sgn)
-{
-	f |= T1_SIG_C(r) | (sgn << (18 + r + 1));
-	fp[-1] |= 1u << (3 * (r + 1) + 2);
-	fp[1] |= 1u << (3 * (r + 1));
-	if(r == 0 && !b.vsc)
-	{
-		uint32_t* n = fp - b.fs;
-		n[0] |= (1u << 16) | (sgn << 23);
-		n[-1] |= 1u << 17;
-		n[1] |= 1u << 15;
-	}
-	if(r == 3)
-	{
-		uint32_t* s = fp + b.fs;
-		s[0] |= (1u << 1) | (sgn << 18);
-		s[-1] |= 1u << 2;
-		s[1] |= 1u << 0;
-	}
-}
-
 // getnmsedec_sig / getnmsedec_ref, T1.cpp:194-208
 static __device__ __forceinline__ int32_t nmsedec_sig(const EBlk& b, uint32_t mag, uint32_t bitpos)
 {
@@ -298,143 +273,334 @@ static __device__ __forceinline__ int32_t nmsedec_ref(const EBlk& b, uint32_t ma
 	return bitpos > 0 ? b.nms[256 + ((mag >> bitpos) & 127)] : b.nms[384 + (mag & 127)];
 }
 
+// ---- coding passes: context modelling by the whole warp, MQ coding by lane 0 ------------------
+// The encoder knows every decision in advance, so only the arithmetic coder itself is serial.
+// A stripe is walked in segments of 32 columns, lane l owning column x0 + l: the lane derives
+// which of its four samples the pass codes, their contexts as the neighbourhood stands when the
+// scan reaches them (state before the segment, plus the west column's and its own earlier rows'
+// new significance of this pass), and leaves its (context, decision) symbols at its prefix-sum
+// position of a list in shared memory; lane 0 then feeds the list to the MQ (or bypass) coder.
+// The one recursive part is the membership of the significance-propagation pass (a sample is in
+// the pass if a neighbour is significant, which the pass itself can cause one column to the
+// west or one row up): lanes iterate it to its fixed point, usually in one or two rounds.
+constexpr uint32_t SYM_CAP = 320; // at most 10 symbols per column (run-length column of the cleanup pass)
+
+// bit r of a row nibble -> bit 3(r+1)+c of the state word (c: 0 west, 1 centre, 2 east)
+static __device__ __forceinline__ uint32_t spread4(uint32_t nib, uint32_t c)
+{
+	return (((nib & 1u) << 3) | ((nib & 2u) << 5) | ((nib & 4u) << 7) | ((nib & 8u) << 9)) << c;
+}
+static __device__ __forceinline__ uint32_t sig4(uint32_t f)
+{
+	return ((f >> 4) & 1u) | ((f >> 6) & 2u) | ((f >> 8) & 4u) | ((f >> 10) & 8u);
+}
+static __device__ __forceinline__ uint32_t nz4(uint32_t f)
+{
+	uint32_t m = 0;
+#pragma unroll
+	for(uint32_t r = 0; r < 4; ++r)
+		m |= ((f >> (3 * r)) & T1_NEIGH) ? 1u << r : 0u;
+	return m;
+}
+static __device__ __forceinline__ uint32_t warp_excl_scan(uint32_t v, uint32_t lane, uint32_t& total)
+{
+	uint32_t incl = v;
+#pragma unroll
+	for(int d = 1; d < 32; d <<= 1)
+	{
+		const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+		if((int)lane >= d)
+			incl += t;
+	}
+	total = __shfl_sync(0xffffffffu, incl, 31);
+	return incl - v;
+}
+
+// one stripe segment as a lane sees it
+struct Col
+{
+	uint32_t* fp; // own state word
+	uint32_t f; // its value before the segment is coded
+	uint32_t mag[4], sgn4, bit4; // magnitudes, signs and the bits of this plane, rows 0..3
+	uint32_t sgnL, sgnR; // sign nibbles of the west / east columns
+	uint32_t rowmask;
+	bool act;
+};
+
+static __device__ __forceinline__ Col load_col(const EBlk& b, uint32_t s, uint32_t k, uint32_t x0,
+												uint32_t lane, uint32_t one)
+{
+	Col c;
+	const uint32_t x = x0 + lane;
+	const uint32_t rows = min(4u, b.h - k);
+	c.act = x < b.w;
+	c.rowmask = c.act ? (1u << rows) - 1u : 0u;
+	c.fp = b.fl + (s + 1) * b.fs + 1 + x;
+	c.f = c.act ? *c.fp : 0u;
+	c.sgn4 = c.bit4 = 0;
+#pragma unroll
+	for(uint32_t r = 0; r < 4; ++r)
+	{
+		const uint32_t sm = (c.act && r < rows) ? b.smp[(k + r) * b.w + x] : 0u;
+		c.mag[r] = sm & 0x7FFFFFFFu;
+		c.sgn4 |= (sm >> 31) << r;
+		c.bit4 |= ((sm & one) ? 1u : 0u) << r;
+	}
+	c.sgnL = __shfl_up_sync(0xffffffffu, c.sgn4, 1);
+	c.sgnR = __shfl_down_sync(0xffffffffu, c.sgn4, 1);
+	if(lane == 0 || lane == 31)
+	{
+		// the neighbour column belongs to another segment
+		const bool west = lane == 0;
+		const bool there = west ? x0 > 0 : x + 1 < b.w;
+		uint32_t sg = 0;
+		if(there && c.act)
+			for(uint32_t r = 0; r < rows; ++r)
+				sg |= (b.smp[(k + r) * b.w + (west ? x - 1 : x + 1)] >> 31) << r;
+		if(west)
+			c.sgnL = sg;
+		else
+			c.sgnR = sg;
+	}
+	return c;
+}
+
+// sign-coding symbol of row r with the neighbourhood word fv as it stands at the visit
+static __device__ __forceinline__ uint32_t sign_symbol(const EBlk& b, const Col& c, uint32_t fv, uint32_t r)
+{
+	const uint32_t nb = fv >> (3 * r);
+	const uint32_t sw = (nb >> 3) & 1u, se = (nb >> 5) & 1u;
+	uint32_t i = sw | (se << 1) | (((nb >> 1) & 1u) << 2) | (((nb >> 7) & 1u) << 3);
+	i |= (sw & (c.sgnL >> r)) << 4;
+	i |= (se & (c.sgnR >> r) & 1u) << 5;
+	i |= ((fv >> (18 + r)) & 1u) << 6;
+	i |= ((fv >> (18 + r + 2)) & 1u) << 7;
+	i &= 0xFFu;
+	const uint32_t e = b.sc[i];
+	return (e & 0x7Fu) | ((((c.sgn4 >> r) & 1u) ^ (e >> 7)) << 5);
+}
+
+// the samples of this lane that turned significant (nibble ns): own word, the words of the
+// stripes above and below, and -- for the lanes at the ends of the segment -- the neighbour
+// column of the other segment (update_flags_macro, T1.cpp:209-233, for all of them at once)
+static __device__ __forceinline__ void commit_significance(const EBlk& b, const Col& c, uint32_t f,
+															uint32_t ns, uint32_t lane)
+{
+	uint32_t nsL = __shfl_up_sync(0xffffffffu, ns, 1), nsR = __shfl_down_sync(0xffffffffu, ns, 1);
+	if(lane == 0)
+		nsL = 0;
+	if(lane == 31)
+		nsR = 0;
+	if(c.act)
+	{
+		*c.fp = f | spread4(nsL, 0) | spread4(nsR, 2);
+		if(!b.vsc)
+		{
+			const uint32_t up = ((nsL & 1u) << 15) | ((ns & 1u) << 16) | ((nsR & 1u) << 17) |
+								((ns & c.sgn4 & 1u) << 23);
+			if(up)
+				c.fp[-(int)b.fs] |= up;
+		}
+		const uint32_t dn = ((nsL >> 3) & 1u) | (((ns >> 3) & 1u) << 1) | (((nsR >> 3) & 1u) << 2) |
+							(((ns & c.sgn4) >> 3) << 18);
+		if(dn)
+			c.fp[b.fs] |= dn;
+	}
+	__syncwarp();
+	if((lane == 0 || lane == 31) && c.act && ns)
+	{
+		uint32_t* o = lane ? c.fp + 1 : c.fp - 1;
+		const uint32_t col = lane ? 0u : 2u; // we are their west / east neighbour
+		*o |= spread4(ns, col);
+		if(!b.vsc && (ns & 1u))
+			o[-(int)b.fs] |= 1u << (15 + col);
+		if(ns & 8u)
+			o[b.fs] |= 1u << col;
+	}
+	__syncwarp();
+}
+
+static __device__ __forceinline__ void code_list(MqE& q, uint8_t* cxs, const uint32_t* mqt,
+												  const uint8_t* list, uint32_t total, bool raw)
+{
+	if(raw)
+		for(uint32_t i = 0; i < total; ++i)
+			raw_encode(q, list[i] >> 5);
+	else
+		for(uint32_t i = 0; i < total; ++i)
+		{
+			const uint32_t v = list[i];
+			mq_encode(q, cxs, mqt, v & 31u, v >> 5);
+		}
+}
+
+static __device__ __forceinline__ int32_t warp_sum(int32_t v)
+{
+#pragma unroll
+	for(int o = 16; o; o >>= 1)
+		v += __shfl_xor_sync(0xffffffffu, v, o);
+	return v;
+}
+
 // enc_sigpass, T1.cpp:459-551
-template<bool RAW>
 static __device__ int32_t enc_sig_pass(const EBlk& b, MqE& q, uint8_t* cxs, const uint32_t* mqt,
-										int bpno)
+										uint8_t* list, int bpno, bool raw, uint32_t lane)
 {
 	const uint32_t one = 1u << (bpno + 6);
 	int32_t nmsedec = 0;
 	for(uint32_t k = 0, s = 0; k < b.h; k += 4, ++s)
-	{
-		const uint32_t rows = min(4u, b.h - k);
-		uint32_t* fp = b.fl + (s + 1) * b.fs + 1;
-		const uint32_t* dp = b.smp + k * b.w;
-		for(uint32_t x = 0; x < b.w; ++x, ++fp, ++dp)
+		for(uint32_t x0 = 0; x0 < b.w; x0 += 32)
 		{
-			uint32_t f = *fp;
-			if(f == 0)
-				continue;
-			for(uint32_t r = 0; r < rows; ++r)
+			const Col c = load_col(b, s, k, x0, lane, one);
+			const uint32_t fre = ~(sig4(c.f) | (c.f >> 24)) & c.rowmask; // not significant, not visited
+			const uint32_t stat = nz4(c.f);
+			// membership to its fixed point: a free sample is coded if it has a significant
+			// neighbour when the scan reaches it
+			uint32_t ns = 0, mem = 0;
+			for(;;)
 			{
-				if((f & (T1_SIG_C(r) | T1_PI(r))) || !((f >> (3 * r)) & T1_NEIGH))
-					continue;
-				const uint32_t sm = dp[r * b.w];
-				const uint32_t mag = sm & 0x7FFFFFFFu, sgn = sm >> 31;
-				const uint32_t v = (mag & one) != 0;
-				if(RAW)
-					raw_encode(q, v);
-				else
-					mq_encode(q, cxs, mqt, b.zc[(f >> (3 * r)) & T1_NEIGH], v);
-				if(v)
+				uint32_t nsL = __shfl_up_sync(0xffffffffu, ns, 1);
+				if(lane == 0)
+					nsL = 0;
+				const uint32_t cand = (stat | nsL | (nsL << 1) | (nsL >> 1)) & fre;
+				uint32_t n2 = 0, m2 = 0;
+#pragma unroll
+				for(uint32_t r = 0; r < 4; ++r)
 				{
-					const uint32_t e = b.sc[sc_index(f, fp[-1], fp[1], r)];
-					nmsedec += nmsedec_sig(b, mag, (uint32_t)bpno);
-					if(RAW)
-						raw_encode(q, sgn);
-					else
-						mq_encode(q, cxs, mqt, e & 0x7Fu, sgn ^ (e >> 7));
-					mark_significant(b, fp, f, r, sgn);
+					const uint32_t m = ((cand >> r) | (r ? (n2 >> (r - 1)) & (fre >> r) : 0u)) & 1u;
+					m2 |= m << r;
+					n2 |= (m & (c.bit4 >> r)) << r;
 				}
-				f |= T1_PI(r);
+				const bool changed = n2 != ns;
+				ns = n2;
+				mem = m2;
+				if(!__any_sync(0xffffffffu, changed))
+					break;
 			}
-			*fp = f;
+			uint32_t nsL = __shfl_up_sync(0xffffffffu, ns, 1);
+			if(lane == 0)
+				nsL = 0;
+			uint32_t total;
+			uint32_t at = warp_excl_scan((uint32_t)(__popc(mem) + __popc(ns)), lane, total);
+			const uint32_t fw = c.f | spread4(nsL, 0);
+#pragma unroll
+			for(uint32_t r = 0; r < 4; ++r)
+				if((mem >> r) & 1u)
+				{
+					const uint32_t low = ns & ((1u << r) - 1u);
+					const uint32_t fv = fw | spread4(low, 1) | ((low & c.sgn4) << 19);
+					const uint32_t v = (c.bit4 >> r) & 1u;
+					list[at++] = (uint8_t)(b.zc[(fv >> (3 * r)) & T1_NEIGH] | (v << 5));
+					if(v)
+					{
+						// the bypass coder takes the sign as it is (T1.cpp:505-508)
+						list[at++] = raw ? (uint8_t)(((c.sgn4 >> r) & 1u) << 5) : (uint8_t)sign_symbol(b, c, fv, r);
+						nmsedec += nmsedec_sig(b, c.mag[r], (uint32_t)bpno);
+					}
+				}
+			__syncwarp();
+			if(lane == 0)
+				code_list(q, cxs, mqt, list, total, raw);
+			const uint32_t f = c.f | spread4(ns, 1) | ((ns & c.sgn4) << 19) | (mem << 24);
+			commit_significance(b, c, f, ns, lane);
 		}
-	}
-	return nmsedec;
+	return warp_sum(nmsedec);
 }
 
 // enc_refpass, T1.cpp:552-630
-template<bool RAW>
 static __device__ int32_t enc_ref_pass(const EBlk& b, MqE& q, uint8_t* cxs, const uint32_t* mqt,
-										int bpno)
+										uint8_t* list, int bpno, bool raw, uint32_t lane)
 {
 	const uint32_t one = 1u << (bpno + 6);
 	int32_t nmsedec = 0;
 	for(uint32_t k = 0, s = 0; k < b.h; k += 4, ++s)
-	{
-		const uint32_t rows = min(4u, b.h - k);
-		uint32_t* fp = b.fl + (s + 1) * b.fs + 1;
-		const uint32_t* dp = b.smp + k * b.w;
-		for(uint32_t x = 0; x < b.w; ++x, ++fp, ++dp)
+		for(uint32_t x0 = 0; x0 < b.w; x0 += 32)
 		{
-			uint32_t f = *fp;
-			if(!(f & T1_SIGC_ALL))
+			const Col c = load_col(b, s, k, x0, lane, one);
+			// significant before this bit-plane: significant and not coded by the pass before
+			const uint32_t ref = sig4(c.f) & ~(c.f >> 24) & c.rowmask;
+			uint32_t total;
+			uint32_t at = warp_excl_scan((uint32_t)__popc(ref), lane, total);
+			if(total == 0)
 				continue;
-			for(uint32_t r = 0; r < rows; ++r)
-			{
-				if((f & (T1_SIG_C(r) | T1_PI(r))) != T1_SIG_C(r))
-					continue;
-				const uint32_t mag = dp[r * b.w] & 0x7FFFFFFFu;
-				nmsedec += nmsedec_ref(b, mag, (uint32_t)bpno);
-				const uint32_t v = (mag & one) != 0;
-				if(RAW)
-					raw_encode(q, v);
-				else
+#pragma unroll
+			for(uint32_t r = 0; r < 4; ++r)
+				if((ref >> r) & 1u)
 				{
-					const uint32_t cx = (f & T1_MU(r))					   ? T1_CTX_MAG + 2
-										: ((f >> (3 * r)) & T1_NEIGH) ? T1_CTX_MAG + 1
-																	   : T1_CTX_MAG;
-					mq_encode(q, cxs, mqt, cx, v);
+					nmsedec += nmsedec_ref(b, c.mag[r], (uint32_t)bpno);
+					const uint32_t cx = (c.f & T1_MU(r))					 ? T1_CTX_MAG + 2
+										: ((c.f >> (3 * r)) & T1_NEIGH) ? T1_CTX_MAG + 1
+																		 : T1_CTX_MAG;
+					list[at++] = (uint8_t)(cx | (((c.bit4 >> r) & 1u) << 5));
 				}
-				f |= T1_MU(r);
-			}
-			*fp = f;
+			if(ref)
+				*c.fp = c.f | (ref << 28);
+			__syncwarp();
+			if(lane == 0)
+				code_list(q, cxs, mqt, list, total, raw);
+			__syncwarp();
 		}
-	}
-	return nmsedec;
+	return warp_sum(nmsedec);
 }
 
 // enc_clnpass, T1.cpp:631-780
 static __device__ int32_t enc_cleanup_pass(const EBlk& b, MqE& q, uint8_t* cxs, const uint32_t* mqt,
-											int bpno)
+											uint8_t* list, int bpno, uint32_t lane)
 {
 	const uint32_t one = 1u << (bpno + 6);
 	int32_t nmsedec = 0;
 	for(uint32_t k = 0, s = 0; k < b.h; k += 4, ++s)
-	{
-		const uint32_t rows = min(4u, b.h - k);
-		uint32_t* fp = b.fl + (s + 1) * b.fs + 1;
-		const uint32_t* dp = b.smp + k * b.w;
-		for(uint32_t x = 0; x < b.w; ++x, ++fp, ++dp)
+		for(uint32_t x0 = 0; x0 < b.w; x0 += 32)
 		{
-			uint32_t f = *fp;
-			uint32_t r = 0;
-			bool sign_only = false;
-			if(rows == 4 && f == 0)
+			const Col c = load_col(b, s, k, x0, lane, one);
+			// every sample that is neither significant nor coded by the significance pass
+			const uint32_t todo = ~(sig4(c.f) | (c.f >> 24)) & c.rowmask;
+			const uint32_t ns = todo & c.bit4;
+			uint32_t nsL = __shfl_up_sync(0xffffffffu, ns, 1);
+			if(lane == 0)
+				nsL = 0;
+			const uint32_t fw = c.f | spread4(nsL, 0);
+			// run-length mode: four rows, nothing significant or visited in or around the column
+			const bool rl = c.act && c.rowmask == 0xFu && fw == 0;
+			const uint32_t r0 = ns ? (uint32_t)__ffs((int)ns) - 1u : 4u;
+			uint32_t cnt = (uint32_t)(__popc(todo) + __popc(ns));
+			if(rl)
+				cnt = ns ? 3u + 1u + (uint32_t)(__popc(todo >> (r0 + 1)) + __popc(ns >> (r0 + 1))) : 1u;
+			uint32_t total;
+			uint32_t at = warp_excl_scan(cnt, lane, total);
+			uint32_t first = 0;
+			if(rl)
 			{
-				while(r < 4 && !(dp[r * b.w] & one))
-					++r;
-				mq_encode(q, cxs, mqt, T1_CTX_AGG, r != 4);
-				if(r == 4)
-					continue;
-				mq_encode(q, cxs, mqt, T1_CTX_UNI, r >> 1);
-				mq_encode(q, cxs, mqt, T1_CTX_UNI, r & 1);
-				sign_only = true;
-			}
-			for(; r < rows; ++r)
-			{
-				const uint32_t sm = dp[r * b.w];
-				const uint32_t mag = sm & 0x7FFFFFFFu, sgn = sm >> 31;
-				if(!sign_only)
+				list[at++] = (uint8_t)(T1_CTX_AGG | ((ns ? 1u : 0u) << 5));
+				if(ns)
 				{
-					if(f & (T1_SIG_C(r) | T1_PI(r)))
-						continue;
-					const uint32_t v = (mag & one) != 0;
-					mq_encode(q, cxs, mqt, b.zc[(f >> (3 * r)) & T1_NEIGH], v);
-					if(!v)
-						continue;
+					list[at++] = (uint8_t)(T1_CTX_UNI | ((r0 >> 1) << 5));
+					list[at++] = (uint8_t)(T1_CTX_UNI | ((r0 & 1u) << 5));
 				}
-				sign_only = false;
-				const uint32_t e = b.sc[sc_index(f, fp[-1], fp[1], r)];
-				nmsedec += nmsedec_sig(b, mag, (uint32_t)bpno);
-				mq_encode(q, cxs, mqt, e & 0x7Fu, sgn ^ (e >> 7));
-				mark_significant(b, fp, f, r, sgn);
+				first = r0; // rows above r0 are zero and need no symbol
 			}
-			*fp = f & ~T1_PI_ALL;
+#pragma unroll
+			for(uint32_t r = 0; r < 4; ++r)
+				if(((todo >> r) & 1u) && r >= first)
+				{
+					const uint32_t low = ns & ((1u << r) - 1u);
+					const uint32_t fv = fw | spread4(low, 1) | ((low & c.sgn4) << 19);
+					const uint32_t v = (c.bit4 >> r) & 1u;
+					if(!(rl && r == r0))
+						list[at++] = (uint8_t)(b.zc[(fv >> (3 * r)) & T1_NEIGH] | (v << 5));
+					if(v)
+					{
+						list[at++] = (uint8_t)sign_symbol(b, c, fv, r);
+						nmsedec += nmsedec_sig(b, c.mag[r], (uint32_t)bpno);
+					}
+				}
+			__syncwarp();
+			if(lane == 0)
+				code_list(q, cxs, mqt, list, total, false);
+			const uint32_t f = (c.f | spread4(ns, 1) | ((ns & c.sgn4) << 19)) & ~T1_PI_ALL;
+			commit_significance(b, c, f, ns, lane);
 		}
-	}
-	return nmsedec;
+	return warp_sum(nmsedec);
 }
 
 // T1.cpp:239-248: L2 norms of the synthesis basis functions, [orientation][level]
@@ -490,9 +656,10 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 	__syncthreads();
 
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const size_t per_warp = 32 + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
+	const size_t per_warp = 32 + SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
 	uint8_t* cxs = warp_base + warp * per_warp;
-	uint32_t* fl = reinterpret_cast<uint32_t*>(cxs + 32);
+	uint8_t* list = cxs + 32; // (context, decision) symbols of one stripe segment
+	uint32_t* fl = reinterpret_cast<uint32_t*>(list + SYM_CAP);
 	uint32_t* smp = fl + l.max_flag_words;
 
 	for(;;)
@@ -533,82 +700,82 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 		for(int o = 16; o; o >>= 1)
 			mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
 		__syncwarp();
-		if(lane == 0)
+		grkb_coded res;
+		res.data_off = 0;
+		res.data_len = 0;
+		res.numbps = 0;
+		res.numpasses = 0;
+		res.failed = 0;
+		res.distortion = 0.0;
+		if(mx)
 		{
-			grkb_coded res;
-			res.data_off = 0;
-			res.data_len = 0;
-			res.numbps = 0;
-			res.numpasses = 0;
-			res.failed = 0;
-			res.distortion = 0.0;
-			if(mx)
-			{
-				const uint32_t t = 32 - __clz(mx); // floorlog2(max) + 1
-				res.numbps = (uint8_t)(t <= 6 ? 0 : t - 6);
-			}
-			grkb_pass* passes = l.passes + (size_t)bi * GRKB_ENC_MAX_PASSES;
-			if(res.numbps)
-			{
-				EBlk b;
-				b.fl = fl;
-				b.smp = smp;
-				b.w = w;
-				b.h = h;
-				b.fs = fs;
-				b.zc = zc + 512u * cb.orient;
-				b.sc = sc;
-				b.nms = nms;
-				b.vsc = (cb.cblk_sty & GRKB_CBLKSTY_VSC) != 0;
-				MqE q;
-				q.out = l.slots + (size_t)bi * l.slot_bytes + SLOT_LEAD;
-				q.cap = (int32_t)(l.slot_bytes - SLOT_LEAD);
-				q.a = 0x8000;
-				q.c = 0;
-				q.bp = -1;
-				q.cur = 0;
-				q.ct = 12;
-				q.overflow = false;
+			const uint32_t t = 32 - __clz(mx); // floorlog2(max) + 1
+			res.numbps = (uint8_t)(t <= 6 ? 0 : t - 6);
+		}
+		grkb_pass* passes = l.passes + (size_t)bi * GRKB_ENC_MAX_PASSES;
+		if(res.numbps)
+		{
+			// every lane walks the passes; the coder state q and the pass records are lane 0's
+			EBlk b;
+			b.fl = fl;
+			b.smp = smp;
+			b.w = w;
+			b.h = h;
+			b.fs = fs;
+			b.zc = zc + 512u * cb.orient;
+			b.sc = sc;
+			b.nms = nms;
+			b.vsc = (cb.cblk_sty & GRKB_CBLKSTY_VSC) != 0;
+			MqE q;
+			q.out = l.slots + (size_t)bi * l.slot_bytes + SLOT_LEAD;
+			q.cap = (int32_t)(l.slot_bytes - SLOT_LEAD);
+			q.a = 0x8000;
+			q.c = 0;
+			q.bp = -1;
+			q.cur = 0;
+			q.ct = 12;
+			q.overflow = false;
+			if(lane == 0)
 				reset_states(cxs);
-				const uint32_t sty = cb.cblk_sty, numbps = res.numbps;
-				const bool pterm = (sty & GRKB_CBLKSTY_PTERM) != 0;
-				// getwmsedec weights: w1 * w2 * stepsize, T1.cpp:418-436
-				uint32_t lvl = cb.level;
-				if(cb.orient == 0 && lvl > 9)
-					lvl = 9;
-				else if(cb.orient > 0 && lvl > 8)
-					lvl = 8;
-				const double w1 = cb.comp < l.mct_numcomps ? l.mct_norms[cb.comp] : 1.0;
-				const double w2 = l.reversible ? c_norms53[cb.orient][lvl] : c_norms97[cb.orient][lvl];
-				const double wstep = __dmul_rn(__dmul_rn(w1, w2), (double)cb.stepsize);
-				int bpno = (int)numbps - 1;
-				uint32_t passtype = 2, passno = 0;
-				double cum = 0.0;
-				bool prev_term = false;
-				for(; bpno >= 0 && passno < GRKB_ENC_MAX_PASSES; ++passno)
+			__syncwarp();
+			const uint32_t sty = cb.cblk_sty, numbps = res.numbps;
+			const bool pterm = (sty & GRKB_CBLKSTY_PTERM) != 0;
+			// getwmsedec weights: w1 * w2 * stepsize, T1.cpp:418-436
+			uint32_t lvl = cb.level;
+			if(cb.orient == 0 && lvl > 9)
+				lvl = 9;
+			else if(cb.orient > 0 && lvl > 8)
+				lvl = 8;
+			const double w1 = cb.comp < l.mct_numcomps ? l.mct_norms[cb.comp] : 1.0;
+			const double w2 = l.reversible ? c_norms53[cb.orient][lvl] : c_norms97[cb.orient][lvl];
+			const double wstep = __dmul_rn(__dmul_rn(w1, w2), (double)cb.stepsize);
+			int bpno = (int)numbps - 1;
+			uint32_t passtype = 2, passno = 0;
+			double cum = 0.0;
+			bool prev_term = false;
+			for(; bpno >= 0 && passno < GRKB_ENC_MAX_PASSES; ++passno)
+			{
+				const bool raw = (bpno < (int)numbps - 4) && passtype < 2 && (sty & GRKB_CBLKSTY_LAZY);
+				if(lane == 0 && passno > 0 && prev_term)
 				{
-					const bool raw = (bpno < (int)numbps - 4) && passtype < 2 && (sty & GRKB_CBLKSTY_LAZY);
-					if(passno > 0 && prev_term)
-					{
-						if(raw)
-							raw_init(q);
-						else
-							mq_restart(q);
-					}
-					int32_t nmsedec;
-					if(passtype == 0)
-						nmsedec = raw ? enc_sig_pass<true>(b, q, cxs, mqt, bpno)
-									  : enc_sig_pass<false>(b, q, cxs, mqt, bpno);
-					else if(passtype == 1)
-						nmsedec = raw ? enc_ref_pass<true>(b, q, cxs, mqt, bpno)
-									  : enc_ref_pass<false>(b, q, cxs, mqt, bpno);
+					if(raw)
+						raw_init(q);
 					else
-					{
-						nmsedec = enc_cleanup_pass(b, q, cxs, mqt, bpno);
-						if(sty & GRKB_CBLKSTY_SEGSYM)
-							for(uint32_t i = 1; i < 5; ++i) // mqc_segmark_enc, mqc_enc.cpp:327-332
-								mq_encode(q, cxs, mqt, T1_CTX_UNI, i & 1);
-					}
+						mq_restart(q);
+				}
+				int32_t nmsedec;
+				if(passtype == 0)
+					nmsedec = enc_sig_pass(b, q, cxs, mqt, list, bpno, raw, lane);
+				else if(passtype == 1)
+					nmsedec = enc_ref_pass(b, q, cxs, mqt, list, bpno, raw, lane);
+				else
+					nmsedec = enc_cleanup_pass(b, q, cxs, mqt, list, bpno, lane);
+				const bool term = is_term_pass(numbps, sty, bpno, passtype);
+				if(lane == 0)
+				{
+					if(passtype == 2 && (sty & GRKB_CBLKSTY_SEGSYM))
+						for(uint32_t i = 1; i < 5; ++i) // mqc_segmark_enc, mqc_enc.cpp:327-332
+							mq_encode(q, cxs, mqt, T1_CTX_UNI, i & 1);
 					grkb_pass ps;
 					ps.distortion = 0.0;
 					ps.reserved = 0;
@@ -620,7 +787,7 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 						cum = __dadd_rn(cum, wm);
 						ps.distortion = cum;
 					}
-					if(is_term_pass(numbps, sty, bpno, passtype))
+					if(term)
 					{
 						if(raw)
 							raw_flush(q, pterm);
@@ -641,16 +808,23 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 						ps.term = 0;
 						ps.rate = (uint32_t)q.bp + extra;
 					}
-					prev_term = ps.term != 0;
 					passes[passno] = ps;
-					if(++passtype == 3)
-					{
-						passtype = 0;
-						bpno--;
-					}
-					if(sty & GRKB_CBLKSTY_RESET)
-						reset_states(cxs);
 				}
+				prev_term = term;
+				if(++passtype == 3)
+				{
+					passtype = 0;
+					bpno--;
+				}
+				if(sty & GRKB_CBLKSTY_RESET)
+				{
+					if(lane == 0)
+						reset_states(cxs);
+					__syncwarp();
+				}
+			}
+			if(lane == 0)
+			{
 				eseek(q, q.bp); // write the byte under construction back
 				// T1.cpp:905-931: rates made monotone, a trailing 0xFF is never included
 				uint32_t last = (uint32_t)q.bp;
@@ -677,8 +851,9 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 				res.distortion = cum;
 				res.failed = q.overflow ? 1 : 0;
 			}
-			l.coded[bi] = res;
 		}
+		if(lane == 0)
+			l.coded[bi] = res;
 		__syncwarp();
 	}
 }
@@ -694,7 +869,7 @@ int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s)
 		grkb_set_error("t1: cannot upload coding tables");
 		return -1;
 	}
-	const size_t per_warp = 32 + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
+	const size_t per_warp = 32 + SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
 	const size_t fixed = 94 * 4 + 1024 + 2048 + 256;
 	int nw = ENC_MAX_THREADS / 32;
 	while(nw > 1 && fixed + per_warp * nw > 100 * 1024)
