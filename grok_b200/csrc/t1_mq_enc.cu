@@ -99,14 +99,12 @@ static __device__ __forceinline__ void mq_byteout(MqE& q)
 	}
 }
 
-// renorm of mqc_enc_inl.h:38-60 with the shifts batched between byte outputs
-static __device__ __forceinline__ void mq_renorm(MqE& q)
+// the shifts of a renormalisation that reach a byte boundary (about one decision in ten)
+static __device__ __forceinline__ void mq_renorm_out(MqE& q, uint32_t n)
 {
-	uint32_t n = __clz(q.a) - 16;
 	while(n)
 	{
 		const uint32_t k = min(n, q.ct);
-		q.a <<= k;
 		q.c <<= k;
 		q.ct -= k;
 		n -= k;
@@ -115,37 +113,44 @@ static __device__ __forceinline__ void mq_renorm(MqE& q)
 	}
 }
 
-// mqc_encode_macro, mqc_enc_inl.h:62-102; cxs[cx] = state index << 1 | mps as in the decoder
-static __device__ __forceinline__ void mq_encode(MqE& q, uint8_t* cxs, const uint32_t* mqt,
+// renorm of mqc_enc_inl.h:38-60 with the shifts batched between byte outputs: A is already
+// shifted, C takes its n shifts, a byte leaving whenever ct reaches 0
+static __device__ __forceinline__ void mq_renorm_c(MqE& q, uint32_t n)
+{
+	if(n < q.ct)
+	{
+		q.c <<= n;
+		q.ct -= n;
+		return;
+	}
+	mq_renorm_out(q, n);
+}
+
+// mqc_encode_macro, mqc_enc_inl.h:62-102.  cxs[cx] holds the table entry of the context's current
+// state (qe | next-if-mps << 16 | next-if-lps << 24) with its MPS in bit 31, so a decision is one
+// shared-memory read, plus a table read and a write when the state moves.  One formulation for
+// the three cases of the reference: C takes Qe unless the (conditional) exchange gives A = Qe;
+// the renormalisation shift is clz(A) - 16 = 0 for an MPS that leaves A >= 0x8000.
+static __device__ __forceinline__ void mq_encode(MqE& q, uint32_t* cxs, const uint32_t* mqt,
 												  uint32_t cx, uint32_t d)
 {
-	const uint32_t st = cxs[cx];
-	const uint32_t e = mqt[st];
+	const uint32_t e = cxs[cx];
 	const uint32_t qe = e & 0xFFFFu;
-	q.a -= qe;
-	if(d == (st & 1u))
-	{
-		if((q.a & 0x8000u) == 0)
-		{
-			if(q.a < qe)
-				q.a = qe;
-			else
-				q.c += qe;
-			cxs[cx] = (uint8_t)((e >> 16) & 0xFFu);
-			mq_renorm(q);
-		}
-		else
-			q.c += qe;
-	}
+	uint32_t a = q.a - qe;
+	const bool ismps = d == (e >> 31);
+	const bool lt = a < qe;
+	if(ismps != lt)
+		q.c += qe;
 	else
+		a = qe;
+	const uint32_t n = __clz(a) - 16;
+	if(n)
 	{
-		if(q.a < qe)
-			q.c += qe;
-		else
-			q.a = qe;
-		cxs[cx] = (uint8_t)(e >> 24);
-		mq_renorm(q);
+		const uint32_t nx = (e >> (ismps ? 16u : 24u)) & 0x7Fu;
+		cxs[cx] = mqt[nx];
+		mq_renorm_c(q, n);
 	}
+	q.a = a << n;
 }
 
 // mqc_flush_enc, mqc_enc.cpp:213-227
@@ -242,14 +247,14 @@ static __device__ void mq_erterm(MqE& q)
 		mq_byteout(q);
 }
 
-static __device__ __forceinline__ void reset_states(uint8_t* cxs)
+static __device__ __forceinline__ void reset_states(uint32_t* cxs, const uint32_t* mqt)
 {
-	// mqc_resetstates, mqc_dec.cpp:121-130 (shared by the encoder)
+	// mqc_resetstates, mqc_dec.cpp:121-130 (shared by the encoder); all MPS are 0
 	for(int i = 0; i < T1_NCTX; ++i)
-		cxs[i] = 0;
-	cxs[T1_CTX_UNI] = 46 << 1;
-	cxs[T1_CTX_AGG] = 3 << 1;
-	cxs[T1_CTX_ZC] = 4 << 1;
+		cxs[i] = mqt[0];
+	cxs[T1_CTX_UNI] = mqt[46 << 1];
+	cxs[T1_CTX_AGG] = mqt[3 << 1];
+	cxs[T1_CTX_ZC] = mqt[4 << 1];
 }
 
 struct EBlk
@@ -283,6 +288,7 @@ static __device__ __forceinline__ int32_t nmsedec_ref(const EBlk& b, uint32_t ma
 // The one recursive part is the membership of the significance-propagation pass (a sample is in
 // the pass if a neighbour is significant, which the pass itself can cause one column to the
 // west or one row up): lanes iterate it to its fixed point, usually in one or two rounds.
+constexpr uint32_t CXS_BYTES = 80; // 19 context words, padded
 constexpr uint32_t SYM_CAP = 320; // at most 10 symbols per column (run-length column of the cleanup pass)
 
 // bit r of a row nibble -> bit 3(r+1)+c of the state word (c: 0 west, 1 centre, 2 east)
@@ -420,18 +426,26 @@ static __device__ __forceinline__ void commit_significance(const EBlk& b, const 
 	__syncwarp();
 }
 
-static __device__ __forceinline__ void code_list(MqE& q, uint8_t* cxs, const uint32_t* mqt,
+static __device__ __forceinline__ void code_list(MqE& q, uint32_t* cxs, const uint32_t* mqt,
 												  const uint8_t* list, uint32_t total, bool raw)
 {
+	const uint32_t* lw = reinterpret_cast<const uint32_t*>(list); // four symbols per word
 	if(raw)
+	{
+#pragma unroll 1
 		for(uint32_t i = 0; i < total; ++i)
 			raw_encode(q, list[i] >> 5);
-	else
-		for(uint32_t i = 0; i < total; ++i)
-		{
-			const uint32_t v = list[i];
-			mq_encode(q, cxs, mqt, v & 31u, v >> 5);
-		}
+		return;
+	}
+	uint32_t v = 0;
+#pragma unroll 1 // one copy of the decision (and its byte-out path): the loop has to stay in the instruction cache
+	for(uint32_t i = 0; i < total; ++i)
+	{
+		if((i & 3u) == 0)
+			v = lw[i >> 2];
+		mq_encode(q, cxs, mqt, v & 31u, (v >> 5) & 1u);
+		v >>= 8;
+	}
 }
 
 static __device__ __forceinline__ int32_t warp_sum(int32_t v)
@@ -443,7 +457,7 @@ static __device__ __forceinline__ int32_t warp_sum(int32_t v)
 }
 
 // enc_sigpass, T1.cpp:459-551
-static __device__ int32_t enc_sig_pass(const EBlk& b, MqE& q, uint8_t* cxs, const uint32_t* mqt,
+static __device__ int32_t enc_sig_pass(const EBlk& b, MqE& q, uint32_t* cxs, const uint32_t* mqt,
 										uint8_t* list, int bpno, bool raw, uint32_t lane)
 {
 	const uint32_t one = 1u << (bpno + 6);
@@ -508,7 +522,7 @@ static __device__ int32_t enc_sig_pass(const EBlk& b, MqE& q, uint8_t* cxs, cons
 }
 
 // enc_refpass, T1.cpp:552-630
-static __device__ int32_t enc_ref_pass(const EBlk& b, MqE& q, uint8_t* cxs, const uint32_t* mqt,
+static __device__ int32_t enc_ref_pass(const EBlk& b, MqE& q, uint32_t* cxs, const uint32_t* mqt,
 										uint8_t* list, int bpno, bool raw, uint32_t lane)
 {
 	const uint32_t one = 1u << (bpno + 6);
@@ -544,7 +558,7 @@ static __device__ int32_t enc_ref_pass(const EBlk& b, MqE& q, uint8_t* cxs, cons
 }
 
 // enc_clnpass, T1.cpp:631-780
-static __device__ int32_t enc_cleanup_pass(const EBlk& b, MqE& q, uint8_t* cxs, const uint32_t* mqt,
+static __device__ int32_t enc_cleanup_pass(const EBlk& b, MqE& q, uint32_t* cxs, const uint32_t* mqt,
 											uint8_t* list, int bpno, uint32_t lane)
 {
 	const uint32_t one = 1u << (bpno + 6);
@@ -636,7 +650,7 @@ static __device__ __forceinline__ bool is_term_pass(uint32_t numbps, uint32_t st
 constexpr int ENC_MAX_THREADS = 256;
 constexpr uint32_t SLOT_LEAD = 16; // zero bytes in front of every slot (out[-1] must be 0)
 
-__global__ void __launch_bounds__(ENC_MAX_THREADS)
+__global__ void __launch_bounds__(ENC_MAX_THREADS, 4)
 	t1_mq_encode_kernel(const T1EncLaunch l, const T1Tables* __restrict__ tab)
 {
 	extern __shared__ __align__(16) uint8_t smem[];
@@ -646,7 +660,7 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 	uint8_t* sc = zc + 2048;
 	uint8_t* warp_base = sc + 256;
 	for(uint32_t i = threadIdx.x; i < 94; i += blockDim.x)
-		mqt[i] = tab->mq[i];
+		mqt[i] = tab->mq[i] | (i << 31); // the MPS of state 2i+mps rides in bit 31
 	for(uint32_t i = threadIdx.x; i < 512; i += blockDim.x)
 		nms[i] = tab->nmsedec[i >> 7][i & 127];
 	for(uint32_t i = threadIdx.x; i < 2048; i += blockDim.x)
@@ -656,9 +670,9 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 	__syncthreads();
 
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const size_t per_warp = 32 + SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
-	uint8_t* cxs = warp_base + warp * per_warp;
-	uint8_t* list = cxs + 32; // (context, decision) symbols of one stripe segment
+	const size_t per_warp = CXS_BYTES + SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
+	uint32_t* cxs = reinterpret_cast<uint32_t*>(warp_base + warp * per_warp);
+	uint8_t* list = reinterpret_cast<uint8_t*>(cxs) + CXS_BYTES; // (context, decision) symbols of one stripe segment
 	uint32_t* fl = reinterpret_cast<uint32_t*>(list + SYM_CAP);
 	uint32_t* smp = fl + l.max_flag_words;
 
@@ -736,7 +750,7 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 			q.ct = 12;
 			q.overflow = false;
 			if(lane == 0)
-				reset_states(cxs);
+				reset_states(cxs, mqt);
 			__syncwarp();
 			const uint32_t sty = cb.cblk_sty, numbps = res.numbps;
 			const bool pterm = (sty & GRKB_CBLKSTY_PTERM) != 0;
@@ -819,7 +833,7 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 				if(sty & GRKB_CBLKSTY_RESET)
 				{
 					if(lane == 0)
-						reset_states(cxs);
+						reset_states(cxs, mqt);
 					__syncwarp();
 				}
 			}
@@ -869,7 +883,7 @@ int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s)
 		grkb_set_error("t1: cannot upload coding tables");
 		return -1;
 	}
-	const size_t per_warp = 32 + SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
+	const size_t per_warp = CXS_BYTES + SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
 	const size_t fixed = 94 * 4 + 1024 + 2048 + 256;
 	int nw = ENC_MAX_THREADS / 32;
 	while(nw > 1 && fixed + per_warp * nw > 100 * 1024)
