@@ -44,7 +44,8 @@ struct EncState
 {
 	int device = -1;
 	cudaStream_t stream = nullptr;
-	DevBuf blocks, coded, passes, slots, packed, misc, planes[GRKB_MAX_COMPS];
+	DevBuf blocks, coded, passes, slots, packed, misc, sym, planes[GRKB_MAX_COMPS];
+	uint32_t sym_bytes_per_sample = 8; // symbol pool sizing, doubled when a tile runs out
 	void release()
 	{
 		blocks.release();
@@ -53,6 +54,7 @@ struct EncState
 		slots.release();
 		packed.release();
 		misc.release();
+		sym.release();
 		for(auto& p : planes)
 			p.release();
 		if(stream)
@@ -67,6 +69,7 @@ int scan_enc_blocks(const grkb_enc_cblk* b, uint32_t n, uint32_t ncomp, uint32_t
 					uint32_t plane_h, int reversible, T1EncLaunch& l, bool& any_mq, bool& any_ht)
 {
 	l.max_area = l.max_flag_words = l.max_w = 0;
+	l.total_area = 0;
 	any_mq = any_ht = false;
 	for(uint32_t i = 0; i < n; ++i)
 	{
@@ -96,6 +99,7 @@ int scan_enc_blocks(const grkb_enc_cblk* b, uint32_t n, uint32_t ncomp, uint32_t
 				return -1;
 			}
 			any_mq = true;
+			l.total_area += (uint64_t)c.w * c.h;
 			const uint32_t fw = ((uint32_t)c.w + 2) * ((((uint32_t)c.h + 3) >> 2) + 2);
 			if(fw > l.max_flag_words)
 				l.max_flag_words = fw;
@@ -125,7 +129,18 @@ int run_encoders(EncState& st, T1EncLaunch& l, bool any_mq, bool any_ht)
 	l.slots = (uint8_t*)st.slots.p;
 	l.packed_used = (uint64_t*)st.misc.p;
 	l.counter = (uint32_t*)((uint8_t*)st.misc.p + 16);
+	l.sym_ctrl = (uint32_t*)((uint8_t*)st.misc.p + 8); // read back together with packed_used
 	l.order = nullptr;
+	if(any_mq)
+	{
+		// a symbol is one byte; a block hands its symbols over in 1 KB chunks
+		const size_t want = (size_t)l.total_area * st.sym_bytes_per_sample + (size_t)l.nblocks * 2048 + 4096;
+		if(st.sym.reserve(want))
+			return -1;
+		l.sym_pool = (uint8_t*)st.sym.p;
+		l.sym_cap = st.sym.cap;
+	}
+	GRKB_CUDA_CHECK(cudaMemsetAsync(l.sym_ctrl, 0, 8, s));
 	// every slot starts with zero bytes: the MQ coder reads the byte before the stream
 	GRKB_CUDA_CHECK(cudaMemset2DAsync(l.slots, l.slot_bytes, 0, SLOT_LEAD, l.nblocks, s));
 	if(any_mq && grkb_launch_t1_mq_encode(l, s))
@@ -202,15 +217,28 @@ int grkb_t1_encode_host(const grkb_enc_cblk* blocks, uint32_t nblocks, const voi
 	l.rate_control = rate_control;
 	l.packed = (uint8_t*)st.packed.p;
 	l.packed_cap = cap;
-	if(run_encoders(st, l, any_mq, any_ht))
+	uint64_t ctrl[2] = {0, 0}; // packed bytes | symbol pool: chunks used, overflow flag
+	for(int attempt = 0;; ++attempt)
+	{
+		if(run_encoders(st, l, any_mq, any_ht))
+			return -1;
+		GRKB_CUDA_CHECK(cudaMemcpyAsync(ctrl, l.packed_used, sizeof(ctrl), cudaMemcpyDeviceToHost, s));
+		GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
+		if((ctrl[1] >> 32) == 0 || attempt == 4)
+			break;
+		st.sym_bytes_per_sample *= 2; // the symbol pool ran out: code the tile again with a larger one
+	}
+	if(ctrl[1] >> 32)
+	{
+		grkb_set_error("grkb_t1_encode_host: symbol pool exhausted");
 		return -1;
-	uint64_t total = 0;
+	}
+	const uint64_t total = ctrl[0];
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(coded, l.coded, (size_t)nblocks * sizeof(grkb_coded),
 									cudaMemcpyDeviceToHost, s));
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(passes, l.passes,
 									(size_t)nblocks * GRKB_ENC_MAX_PASSES * sizeof(grkb_pass),
 									cudaMemcpyDeviceToHost, s));
-	GRKB_CUDA_CHECK(cudaMemcpyAsync(&total, l.packed_used, sizeof(total), cudaMemcpyDeviceToHost, s));
 	GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
 	if(total == ~(uint64_t)0)
 	{
@@ -315,7 +343,7 @@ int grkb_encoder_create(const grkb_tile_params* p, grkb_encoder** out)
 	}
 	for(auto& v : e->ev)
 		ok = ok && cudaEventCreate(&v) == cudaSuccess;
-	ok = ok && cudaMallocHost(&e->h_total, sizeof(uint64_t)) == cudaSuccess;
+	ok = ok && cudaMallocHost(&e->h_total, 2 * sizeof(uint64_t)) == cudaSuccess;
 	if(!ok || cudaStreamSynchronize(e->st.stream) != cudaSuccess)
 	{
 		grkb_set_error("grkb_encoder_create: device allocation failed: %s",
@@ -393,7 +421,7 @@ int grkb_encoder_submit(grkb_encoder* e, const int32_t* const* image, uint32_t s
 	e->p_passes = passes;
 	e->p_bytes = bytes;
 	e->p_cap = cap;
-	*e->h_total = 0;
+	e->h_total[0] = e->h_total[1] = 0;
 	if(nblocks == 0)
 		return 0;
 	if(e->st.blocks.reserve((size_t)nblocks * sizeof(grkb_enc_cblk)) ||
@@ -429,7 +457,7 @@ int grkb_encoder_submit(grkb_encoder* e, const int32_t* const* image, uint32_t s
 	// are sized from them in grkb_encoder_wait
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(coded, l.coded, (size_t)nblocks * sizeof(grkb_coded),
 									cudaMemcpyDeviceToHost, s));
-	GRKB_CUDA_CHECK(cudaMemcpyAsync(e->h_total, l.packed_used, sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+	GRKB_CUDA_CHECK(cudaMemcpyAsync(e->h_total, l.packed_used, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
 	return 0;
 }
 
@@ -448,7 +476,25 @@ int grkb_encoder_wait(grkb_encoder* e, size_t* used)
 	GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
 	if(e->p_nblocks == 0)
 		return 0;
-	const uint64_t total = *e->h_total;
+	for(int attempt = 0; (e->h_total[1] >> 32) != 0; ++attempt)
+	{
+		// the symbol pool of the MQ coder ran out: code the tile again with a larger one
+		if(attempt == 4)
+		{
+			grkb_set_error("grkb_encoder_wait: symbol pool exhausted");
+			return -1;
+		}
+		e->st.sym_bytes_per_sample *= 2;
+		T1EncLaunch l = e->last;
+		if(run_encoders(e->st, l, e->any_mq, e->any_ht))
+			return -1;
+		e->last = l;
+		GRKB_CUDA_CHECK(cudaMemcpyAsync(e->p_coded, l.coded, (size_t)e->p_nblocks * sizeof(grkb_coded),
+										cudaMemcpyDeviceToHost, s));
+		GRKB_CUDA_CHECK(cudaMemcpyAsync(e->h_total, l.packed_used, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+		GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
+	}
+	const uint64_t total = e->h_total[0];
 	if(total == ~(uint64_t)0)
 	{
 		grkb_set_error("grkb_encoder_encode: output pool of %zu bytes is too small", e->p_cap);

@@ -85,6 +85,12 @@ struct T1EncLaunch
 	uint32_t max_area; // max w*h over the blocks
 	uint32_t max_flag_words; // max (w+2)*(ceil(h/4)+2) over MQ blocks
 	uint32_t max_w; // widest block
+	// MQ blocks are coded in two kernels: context modelling leaves every block's (context,
+	// decision) symbols in chunks of this pool, the arithmetic coder reads them back
+	uint8_t* sym_pool; // device
+	uint64_t sym_cap; // bytes
+	uint32_t* sym_ctrl; // device: [0] chunks handed out, [1] set when the pool ran out
+	uint64_t total_area; // sum of w*h over the MQ blocks (sizes the pool)
 };
 int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s);
 int grkb_launch_t1_ht_encode(const T1EncLaunch& l, cudaStream_t s);

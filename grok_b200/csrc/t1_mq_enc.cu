@@ -65,38 +65,21 @@ static __device__ __forceinline__ void epush(MqE& q, uint32_t v)
 	q.cur = v & 0xFFu;
 }
 
-// mqc_byteout, mqc_enc.cpp:86-125
+// mqc_byteout, mqc_enc.cpp:86-125, its three cases in one branch-free form (the coders of a warp
+// run in lockstep, one block per thread: a branch taken by any of them costs all of them): a
+// carry out of C goes into the byte under construction unless that byte is 0xFF; the next byte
+// takes 7 bits after a 0xFF, 8 otherwise
 static __device__ __forceinline__ void mq_byteout(MqE& q)
 {
-	if(q.cur == 0xFF)
-	{
-		epush(q, q.c >> 20);
-		q.c &= 0xFFFFF;
-		q.ct = 7;
-	}
-	else if((q.c & 0x8000000) == 0)
-	{
-		epush(q, q.c >> 19);
-		q.c &= 0x7FFFF;
-		q.ct = 8;
-	}
-	else
-	{
-		q.cur++;
-		if(q.cur == 0xFF)
-		{
-			q.c &= 0x7FFFFFF;
-			epush(q, q.c >> 20);
-			q.c &= 0xFFFFF;
-			q.ct = 7;
-		}
-		else
-		{
-			epush(q, q.c >> 19);
-			q.c &= 0x7FFFF;
-			q.ct = 8;
-		}
-	}
+	const uint32_t carry = q.cur != 0xFF ? (q.c >> 27) & 1u : 0u;
+	q.cur += carry;
+	q.c &= ~(carry << 27);
+	const bool ff = q.cur == 0xFF;
+	const uint32_t sh = ff ? 20u : 19u;
+	const uint32_t nb = q.c >> sh;
+	q.c &= (1u << sh) - 1u;
+	q.ct = ff ? 7u : 8u;
+	epush(q, nb);
 }
 
 // the shifts of a renormalisation that reach a byte boundary (about one decision in ten)
@@ -131,9 +114,12 @@ static __device__ __forceinline__ void mq_renorm_c(MqE& q, uint32_t n)
 // shared-memory read, plus a table read and a write when the state moves.  One formulation for
 // the three cases of the reference: C takes Qe unless the (conditional) exchange gives A = Qe;
 // the renormalisation shift is clz(A) - 16 = 0 for an MPS that leaves A >= 0x8000.
+template<uint32_t STRIDE>
 static __device__ __forceinline__ void mq_encode(MqE& q, uint32_t* cxs, const uint32_t* mqt,
 												  uint32_t cx, uint32_t d)
 {
+	cxs += cx * STRIDE; // context words of one block are STRIDE words apart (one thread per block)
+	cx = 0;
 	const uint32_t e = cxs[cx];
 	const uint32_t qe = e & 0xFFFFu;
 	uint32_t a = q.a - qe;
@@ -247,14 +233,15 @@ static __device__ void mq_erterm(MqE& q)
 		mq_byteout(q);
 }
 
+template<uint32_t STRIDE>
 static __device__ __forceinline__ void reset_states(uint32_t* cxs, const uint32_t* mqt)
 {
 	// mqc_resetstates, mqc_dec.cpp:121-130 (shared by the encoder); all MPS are 0
 	for(int i = 0; i < T1_NCTX; ++i)
-		cxs[i] = mqt[0];
-	cxs[T1_CTX_UNI] = mqt[46 << 1];
-	cxs[T1_CTX_AGG] = mqt[3 << 1];
-	cxs[T1_CTX_ZC] = mqt[4 << 1];
+		cxs[i * STRIDE] = mqt[0];
+	cxs[T1_CTX_UNI * STRIDE] = mqt[46 << 1];
+	cxs[T1_CTX_AGG * STRIDE] = mqt[3 << 1];
+	cxs[T1_CTX_ZC * STRIDE] = mqt[4 << 1];
 }
 
 struct EBlk
@@ -426,26 +413,63 @@ static __device__ __forceinline__ void commit_significance(const EBlk& b, const 
 	__syncwarp();
 }
 
-static __device__ __forceinline__ void code_list(MqE& q, uint32_t* cxs, const uint32_t* mqt,
-												  const uint8_t* list, uint32_t total, bool raw)
+// ---- symbol stream of a block in the pool -------------------------------------------------------
+// Chunks of SYM_CHUNK bytes: payload, then the number of payload bytes and the index of the next
+// chunk.  A segment's symbols never straddle chunks.  All members are uniform across the warp.
+constexpr uint32_t SYM_CHUNK = 1024, SYM_PAYLOAD = SYM_CHUNK - 8, SYM_NONE = 0xFFFFFFFFu;
+struct SymWriter
 {
-	const uint32_t* lw = reinterpret_cast<const uint32_t*>(list); // four symbols per word
-	if(raw)
+	uint8_t* pool;
+	uint64_t cap;
+	uint32_t* ctrl;
+	uint32_t chunk, fill;
+	uint32_t count; // symbols of the current pass
+	bool dead; // the pool ran out
+};
+static __device__ __forceinline__ uint32_t sym_alloc(SymWriter& w, uint32_t lane)
+{
+	uint32_t c = 0;
+	if(lane == 0)
+		c = atomicAdd(w.ctrl, 1u);
+	c = __shfl_sync(0xffffffffu, c, 0);
+	if(((uint64_t)c + 1) * SYM_CHUNK > w.cap)
 	{
-#pragma unroll 1
-		for(uint32_t i = 0; i < total; ++i)
-			raw_encode(q, list[i] >> 5);
+		if(lane == 0)
+			w.ctrl[1] = 1;
+		w.dead = true;
+		return SYM_NONE;
+	}
+	return c;
+}
+static __device__ __forceinline__ void sym_close(const SymWriter& w, uint32_t next, uint32_t lane)
+{
+	if(lane == 0 && !w.dead && w.chunk != SYM_NONE)
+	{
+		uint32_t* t = reinterpret_cast<uint32_t*>(w.pool + (size_t)w.chunk * SYM_CHUNK + SYM_PAYLOAD);
+		t[0] = w.fill;
+		t[1] = next;
+	}
+}
+// the `total` symbols the lanes left in `list` go to the block's stream
+static __device__ __forceinline__ void sym_emit(SymWriter& w, const uint8_t* list, uint32_t total,
+												 uint32_t lane)
+{
+	w.count += total;
+	if(w.dead || total == 0)
 		return;
-	}
-	uint32_t v = 0;
-#pragma unroll 1 // one copy of the decision (and its byte-out path): the loop has to stay in the instruction cache
-	for(uint32_t i = 0; i < total; ++i)
+	if(w.fill + total > SYM_PAYLOAD)
 	{
-		if((i & 3u) == 0)
-			v = lw[i >> 2];
-		mq_encode(q, cxs, mqt, v & 31u, (v >> 5) & 1u);
-		v >>= 8;
+		const uint32_t nxt = sym_alloc(w, lane);
+		if(nxt == SYM_NONE)
+			return;
+		sym_close(w, nxt, lane);
+		w.chunk = nxt;
+		w.fill = 0;
 	}
+	uint8_t* dst = w.pool + (size_t)w.chunk * SYM_CHUNK + w.fill;
+	for(uint32_t i = lane; i < total; i += 32)
+		dst[i] = list[i];
+	w.fill += total;
 }
 
 static __device__ __forceinline__ int32_t warp_sum(int32_t v)
@@ -457,8 +481,8 @@ static __device__ __forceinline__ int32_t warp_sum(int32_t v)
 }
 
 // enc_sigpass, T1.cpp:459-551
-static __device__ int32_t enc_sig_pass(const EBlk& b, MqE& q, uint32_t* cxs, const uint32_t* mqt,
-										uint8_t* list, int bpno, bool raw, uint32_t lane)
+static __device__ int32_t enc_sig_pass(const EBlk& b, SymWriter& sw, uint8_t* list, int bpno, bool raw,
+										uint32_t lane)
 {
 	const uint32_t one = 1u << (bpno + 6);
 	int32_t nmsedec = 0;
@@ -513,8 +537,7 @@ static __device__ int32_t enc_sig_pass(const EBlk& b, MqE& q, uint32_t* cxs, con
 					}
 				}
 			__syncwarp();
-			if(lane == 0)
-				code_list(q, cxs, mqt, list, total, raw);
+			sym_emit(sw, list, total, lane);
 			const uint32_t f = c.f | spread4(ns, 1) | ((ns & c.sgn4) << 19) | (mem << 24);
 			commit_significance(b, c, f, ns, lane);
 		}
@@ -522,8 +545,7 @@ static __device__ int32_t enc_sig_pass(const EBlk& b, MqE& q, uint32_t* cxs, con
 }
 
 // enc_refpass, T1.cpp:552-630
-static __device__ int32_t enc_ref_pass(const EBlk& b, MqE& q, uint32_t* cxs, const uint32_t* mqt,
-										uint8_t* list, int bpno, bool raw, uint32_t lane)
+static __device__ int32_t enc_ref_pass(const EBlk& b, SymWriter& sw, uint8_t* list, int bpno, uint32_t lane)
 {
 	const uint32_t one = 1u << (bpno + 6);
 	int32_t nmsedec = 0;
@@ -550,16 +572,15 @@ static __device__ int32_t enc_ref_pass(const EBlk& b, MqE& q, uint32_t* cxs, con
 			if(ref)
 				*c.fp = c.f | (ref << 28);
 			__syncwarp();
-			if(lane == 0)
-				code_list(q, cxs, mqt, list, total, raw);
+			sym_emit(sw, list, total, lane);
 			__syncwarp();
 		}
 	return warp_sum(nmsedec);
 }
 
 // enc_clnpass, T1.cpp:631-780
-static __device__ int32_t enc_cleanup_pass(const EBlk& b, MqE& q, uint32_t* cxs, const uint32_t* mqt,
-											uint8_t* list, int bpno, uint32_t lane)
+static __device__ int32_t enc_cleanup_pass(const EBlk& b, SymWriter& sw, uint8_t* list, int bpno,
+											uint32_t lane)
 {
 	const uint32_t one = 1u << (bpno + 6);
 	int32_t nmsedec = 0;
@@ -609,8 +630,7 @@ static __device__ int32_t enc_cleanup_pass(const EBlk& b, MqE& q, uint32_t* cxs,
 					}
 				}
 			__syncwarp();
-			if(lane == 0)
-				code_list(q, cxs, mqt, list, total, false);
+			sym_emit(sw, list, total, lane);
 			const uint32_t f = (c.f | spread4(ns, 1) | ((ns & c.sgn4) << 19)) & ~T1_PI_ALL;
 			commit_significance(b, c, f, ns, lane);
 		}
@@ -650,17 +670,23 @@ static __device__ __forceinline__ bool is_term_pass(uint32_t numbps, uint32_t st
 constexpr int ENC_MAX_THREADS = 256;
 constexpr uint32_t SLOT_LEAD = 16; // zero bytes in front of every slot (out[-1] must be 0)
 
-__global__ void __launch_bounds__(ENC_MAX_THREADS, 4)
-	t1_mq_encode_kernel(const T1EncLaunch l, const T1Tables* __restrict__ tab)
+// what the modelling kernel leaves for the coding kernel: in coded[bi] the number of bit-planes,
+// the number of passes and (in data_off) the block's first chunk; in passes[bi][p] the number of
+// symbols of pass p (rate) and its distortion sum (the int32 in the bits of `distortion`)
+static __device__ __forceinline__ bool pass_is_raw(uint32_t numbps, uint32_t sty, int bpno, uint32_t passtype)
+{
+	return (bpno < (int)numbps - 4) && passtype < 2 && (sty & GRKB_CBLKSTY_LAZY);
+}
+
+// ---- kernel 1: context modelling, one code block per warp ---------------------------------------
+__global__ void __launch_bounds__(ENC_MAX_THREADS)
+	t1_mq_model_kernel(const T1EncLaunch l, const T1Tables* __restrict__ tab)
 {
 	extern __shared__ __align__(16) uint8_t smem[];
-	uint32_t* mqt = reinterpret_cast<uint32_t*>(smem);
-	int16_t* nms = reinterpret_cast<int16_t*>(smem + 94 * 4);
-	uint8_t* zc = smem + 94 * 4 + 1024;
+	int16_t* nms = reinterpret_cast<int16_t*>(smem);
+	uint8_t* zc = smem + 1024;
 	uint8_t* sc = zc + 2048;
 	uint8_t* warp_base = sc + 256;
-	for(uint32_t i = threadIdx.x; i < 94; i += blockDim.x)
-		mqt[i] = tab->mq[i] | (i << 31); // the MPS of state 2i+mps rides in bit 31
 	for(uint32_t i = threadIdx.x; i < 512; i += blockDim.x)
 		nms[i] = tab->nmsedec[i >> 7][i & 127];
 	for(uint32_t i = threadIdx.x; i < 2048; i += blockDim.x)
@@ -670,9 +696,8 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS, 4)
 	__syncthreads();
 
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const size_t per_warp = CXS_BYTES + SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
-	uint32_t* cxs = reinterpret_cast<uint32_t*>(warp_base + warp * per_warp);
-	uint8_t* list = reinterpret_cast<uint8_t*>(cxs) + CXS_BYTES; // (context, decision) symbols of one stripe segment
+	const size_t per_warp = SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
+	uint8_t* list = warp_base + warp * per_warp; // (context, decision) symbols of one stripe segment
 	uint32_t* fl = reinterpret_cast<uint32_t*>(list + SYM_CAP);
 	uint32_t* smp = fl + l.max_flag_words;
 
@@ -729,7 +754,6 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS, 4)
 		grkb_pass* passes = l.passes + (size_t)bi * GRKB_ENC_MAX_PASSES;
 		if(res.numbps)
 		{
-			// every lane walks the passes; the coder state q and the pass records are lane 0's
 			EBlk b;
 			b.fl = fl;
 			b.smp = smp;
@@ -740,136 +764,263 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS, 4)
 			b.sc = sc;
 			b.nms = nms;
 			b.vsc = (cb.cblk_sty & GRKB_CBLKSTY_VSC) != 0;
-			MqE q;
-			q.out = l.slots + (size_t)bi * l.slot_bytes + SLOT_LEAD;
-			q.cap = (int32_t)(l.slot_bytes - SLOT_LEAD);
-			q.a = 0x8000;
-			q.c = 0;
-			q.bp = -1;
-			q.cur = 0;
-			q.ct = 12;
-			q.overflow = false;
-			if(lane == 0)
-				reset_states(cxs, mqt);
-			__syncwarp();
+			SymWriter sw;
+			sw.pool = l.sym_pool;
+			sw.cap = l.sym_cap;
+			sw.ctrl = l.sym_ctrl;
+			sw.dead = false;
+			sw.fill = 0;
+			sw.count = 0;
+			sw.chunk = SYM_NONE;
+			sw.chunk = sym_alloc(sw, lane);
+			res.data_off = sw.chunk;
 			const uint32_t sty = cb.cblk_sty, numbps = res.numbps;
-			const bool pterm = (sty & GRKB_CBLKSTY_PTERM) != 0;
-			// getwmsedec weights: w1 * w2 * stepsize, T1.cpp:418-436
-			uint32_t lvl = cb.level;
-			if(cb.orient == 0 && lvl > 9)
-				lvl = 9;
-			else if(cb.orient > 0 && lvl > 8)
-				lvl = 8;
-			const double w1 = cb.comp < l.mct_numcomps ? l.mct_norms[cb.comp] : 1.0;
-			const double w2 = l.reversible ? c_norms53[cb.orient][lvl] : c_norms97[cb.orient][lvl];
-			const double wstep = __dmul_rn(__dmul_rn(w1, w2), (double)cb.stepsize);
 			int bpno = (int)numbps - 1;
 			uint32_t passtype = 2, passno = 0;
-			double cum = 0.0;
-			bool prev_term = false;
 			for(; bpno >= 0 && passno < GRKB_ENC_MAX_PASSES; ++passno)
 			{
-				const bool raw = (bpno < (int)numbps - 4) && passtype < 2 && (sty & GRKB_CBLKSTY_LAZY);
-				if(lane == 0 && passno > 0 && prev_term)
-				{
-					if(raw)
-						raw_init(q);
-					else
-						mq_restart(q);
-				}
+				const bool raw = pass_is_raw(numbps, sty, bpno, passtype);
+				sw.count = 0;
 				int32_t nmsedec;
 				if(passtype == 0)
-					nmsedec = enc_sig_pass(b, q, cxs, mqt, list, bpno, raw, lane);
+					nmsedec = enc_sig_pass(b, sw, list, bpno, raw, lane);
 				else if(passtype == 1)
-					nmsedec = enc_ref_pass(b, q, cxs, mqt, list, bpno, raw, lane);
+					nmsedec = enc_ref_pass(b, sw, list, bpno, lane);
 				else
-					nmsedec = enc_cleanup_pass(b, q, cxs, mqt, list, bpno, lane);
-				const bool term = is_term_pass(numbps, sty, bpno, passtype);
+				{
+					nmsedec = enc_cleanup_pass(b, sw, list, bpno, lane);
+					if(sty & GRKB_CBLKSTY_SEGSYM)
+					{
+						// mqc_segmark_enc, mqc_enc.cpp:327-332: 1 0 1 0 in the uniform context
+						if(lane < 4)
+							list[lane] = (uint8_t)(T1_CTX_UNI | (((lane + 1) & 1u) << 5));
+						__syncwarp();
+						sym_emit(sw, list, 4, lane);
+						__syncwarp();
+					}
+				}
 				if(lane == 0)
 				{
-					if(passtype == 2 && (sty & GRKB_CBLKSTY_SEGSYM))
-						for(uint32_t i = 1; i < 5; ++i) // mqc_segmark_enc, mqc_enc.cpp:327-332
-							mq_encode(q, cxs, mqt, T1_CTX_UNI, i & 1);
 					grkb_pass ps;
-					ps.distortion = 0.0;
-					ps.reserved = 0;
+					ps.distortion = __longlong_as_double((long long)nmsedec);
+					ps.rate = sw.count;
 					ps.len = 0;
-					if(l.rate_control)
-					{
-						double wm = __dmul_rn(wstep, (double)(1 << bpno));
-						wm = __dmul_rn(wm, __ddiv_rn(__dmul_rn(wm, (double)nmsedec), 8192.0));
-						cum = __dadd_rn(cum, wm);
-						ps.distortion = cum;
-					}
-					if(term)
-					{
-						if(raw)
-							raw_flush(q, pterm);
-						else if(pterm)
-							mq_erterm(q);
-						else
-							mq_flush(q);
-						ps.term = 1;
-						ps.rate = (uint32_t)q.bp;
-					}
-					else
-					{
-						uint32_t extra;
-						if(raw)
-							extra = raw_needs_two(q, pterm) ? 2 : 1;
-						else
-							extra = q.ct < 5 ? 6 : 5;
-						ps.term = 0;
-						ps.rate = (uint32_t)q.bp + extra;
-					}
+					ps.term = 0;
+					ps.reserved = 0;
 					passes[passno] = ps;
 				}
-				prev_term = term;
 				if(++passtype == 3)
 				{
 					passtype = 0;
 					bpno--;
 				}
-				if(sty & GRKB_CBLKSTY_RESET)
-				{
-					if(lane == 0)
-						reset_states(cxs, mqt);
-					__syncwarp();
-				}
 			}
-			if(lane == 0)
-			{
-				eseek(q, q.bp); // write the byte under construction back
-				// T1.cpp:905-931: rates made monotone, a trailing 0xFF is never included
-				uint32_t last = (uint32_t)q.bp;
-				for(uint32_t p = passno; p > 0;)
-				{
-					--p;
-					if(passes[p].rate > last)
-						passes[p].rate = last;
-					else
-						last = passes[p].rate;
-				}
-				uint32_t prev = 0;
-				for(uint32_t p = 0; p < passno; ++p)
-				{
-					uint32_t r = passes[p].rate;
-					if(r > 0 && q.out[r - 1] == 0xFF)
-						r--;
-					passes[p].rate = r;
-					passes[p].len = (uint16_t)(r - prev);
-					prev = r;
-				}
-				res.numpasses = (uint8_t)passno;
-				res.data_len = passno ? prev : 0;
-				res.distortion = cum;
-				res.failed = q.overflow ? 1 : 0;
-			}
+			sym_close(sw, SYM_NONE, lane);
+			res.numpasses = (uint8_t)passno;
+			res.failed = sw.dead ? 2 : 0;
 		}
 		if(lane == 0)
 			l.coded[bi] = res;
 		__syncwarp();
 	}
+}
+
+// ---- kernel 2: the arithmetic coder, one code block per THREAD ------------------------------------
+// With the decisions on a list the MQ coder is a flat loop: 32 blocks per warp run it in lockstep,
+// each lane on its own stream, coder registers and context words (shared memory, one column per
+// thread).  Per pass the reference's bookkeeping follows: restart / bypass initialisation,
+// termination (flush, predictable termination, bypass flush), the rate and the distortion record.
+constexpr int CODE_THREADS = 64;
+
+struct SymReader
+{
+	const uint8_t* pool;
+	const uint8_t* base; // current chunk
+	uint32_t pos, fill;
+	uint32_t word, ahead; // the four symbols being handed out, and the next four (loaded early:
+						  // the load would otherwise sit in the middle of the decision chain)
+};
+static __device__ __forceinline__ void sym_open(SymReader& r, uint32_t chunk)
+{
+	r.base = r.pool + (size_t)chunk * SYM_CHUNK;
+	r.pos = 0;
+	r.fill = *reinterpret_cast<const uint32_t*>(r.base + SYM_PAYLOAD);
+	r.ahead = *reinterpret_cast<const uint32_t*>(r.base);
+	r.word = 0;
+	asm volatile("prefetch.global.L1 [%0];" ::"l"(r.base + 128));
+	asm volatile("prefetch.global.L1 [%0];" ::"l"(r.base + 256));
+	// and the start of the chunk after this one (its index is final: the chunks were closed in order)
+	const uint32_t nxt = *reinterpret_cast<const uint32_t*>(r.base + SYM_PAYLOAD + 4);
+	if(nxt != SYM_NONE)
+		asm volatile("prefetch.global.L1 [%0];" ::"l"(r.pool + (size_t)nxt * SYM_CHUNK));
+}
+static __device__ __forceinline__ uint32_t sym_next(SymReader& r)
+{
+	if(r.pos == r.fill)
+		sym_open(r, *reinterpret_cast<const uint32_t*>(r.base + SYM_PAYLOAD + 4));
+	if((r.pos & 3u) == 0)
+	{
+		r.word = r.ahead;
+		r.ahead = *reinterpret_cast<const uint32_t*>(r.base + r.pos + 4); // at worst the chunk's trailer
+		// the pool is larger than L2 holds between the two kernels: pull the lines in well ahead
+		if((r.pos & 127u) == 0 && r.pos + 384u < SYM_CHUNK)
+			asm volatile("prefetch.global.L1 [%0];" ::"l"(r.base + r.pos + 384u));
+	}
+	const uint32_t v = r.word & 0xFFu;
+	r.word >>= 8;
+	r.pos++;
+	return v;
+}
+
+__global__ void __launch_bounds__(CODE_THREADS)
+	t1_mq_code_kernel(const T1EncLaunch l, const T1Tables* __restrict__ tab)
+{
+	__shared__ uint32_t mqt[96];
+	__shared__ uint32_t cxs_all[T1_NCTX * CODE_THREADS];
+	for(uint32_t i = threadIdx.x; i < 94; i += blockDim.x)
+		mqt[i] = tab->mq[i] | (i << 31); // the MPS of state 2i+mps rides in bit 31
+	__syncthreads();
+	const uint32_t bi = blockIdx.x * CODE_THREADS + threadIdx.x;
+	if(bi >= l.nblocks)
+		return;
+	const grkb_enc_cblk cb = l.blocks[bi];
+	if(cb.cblk_sty & GRKB_CBLKSTY_HT)
+		return;
+	grkb_coded res = l.coded[bi];
+	if(res.numbps == 0)
+		return; // nothing to code: the record is final
+	const uint32_t npasses = res.numpasses, first_chunk = (uint32_t)res.data_off;
+	res.data_off = 0;
+	if(res.failed)
+	{
+		res.numpasses = 0;
+		l.coded[bi] = res;
+		return; // the symbol pool ran out: the host codes the tile again with a larger one
+	}
+	uint32_t* cxs = cxs_all + threadIdx.x;
+	grkb_pass* passes = l.passes + (size_t)bi * GRKB_ENC_MAX_PASSES;
+	SymReader rd;
+	rd.pool = l.sym_pool;
+	sym_open(rd, first_chunk);
+	MqE q;
+	q.out = l.slots + (size_t)bi * l.slot_bytes + SLOT_LEAD;
+	q.cap = (int32_t)(l.slot_bytes - SLOT_LEAD);
+	q.a = 0x8000;
+	q.c = 0;
+	q.bp = -1;
+	q.cur = 0;
+	q.ct = 12;
+	q.overflow = false;
+	reset_states<CODE_THREADS>(cxs, mqt);
+	const uint32_t sty = cb.cblk_sty, numbps = res.numbps;
+	const bool pterm = (sty & GRKB_CBLKSTY_PTERM) != 0;
+	// getwmsedec weights: w1 * w2 * stepsize, T1.cpp:418-436
+	uint32_t lvl = cb.level;
+	if(cb.orient == 0 && lvl > 9)
+		lvl = 9;
+	else if(cb.orient > 0 && lvl > 8)
+		lvl = 8;
+	const double w1 = cb.comp < l.mct_numcomps ? l.mct_norms[cb.comp] : 1.0;
+	const double w2 = l.reversible ? c_norms53[cb.orient][lvl] : c_norms97[cb.orient][lvl];
+	const double wstep = __dmul_rn(__dmul_rn(w1, w2), (double)cb.stepsize);
+	int bpno = (int)numbps - 1;
+	uint32_t passtype = 2;
+	double cum = 0.0;
+	bool prev_term = false;
+	for(uint32_t passno = 0; passno < npasses; ++passno)
+	{
+		const bool raw = pass_is_raw(numbps, sty, bpno, passtype);
+		if(passno > 0 && prev_term)
+		{
+			if(raw)
+				raw_init(q);
+			else
+				mq_restart(q);
+		}
+		const uint32_t count = passes[passno].rate;
+		const int32_t nmsedec = (int32_t)__double_as_longlong(passes[passno].distortion);
+		if(raw)
+		{
+#pragma unroll 1
+			for(uint32_t i = 0; i < count; ++i)
+				raw_encode(q, sym_next(rd) >> 5);
+		}
+		else
+		{
+#pragma unroll 1
+			for(uint32_t i = 0; i < count; ++i)
+			{
+				const uint32_t v = sym_next(rd);
+				mq_encode<CODE_THREADS>(q, cxs, mqt, v & 31u, v >> 5);
+			}
+		}
+		grkb_pass ps;
+		ps.distortion = 0.0;
+		ps.reserved = 0;
+		ps.len = 0;
+		if(l.rate_control)
+		{
+			double wm = __dmul_rn(wstep, (double)(1 << bpno));
+			wm = __dmul_rn(wm, __ddiv_rn(__dmul_rn(wm, (double)nmsedec), 8192.0));
+			cum = __dadd_rn(cum, wm);
+			ps.distortion = cum;
+		}
+		if(is_term_pass(numbps, sty, bpno, passtype))
+		{
+			if(raw)
+				raw_flush(q, pterm);
+			else if(pterm)
+				mq_erterm(q);
+			else
+				mq_flush(q);
+			ps.term = 1;
+			ps.rate = (uint32_t)q.bp;
+		}
+		else
+		{
+			uint32_t extra;
+			if(raw)
+				extra = raw_needs_two(q, pterm) ? 2 : 1;
+			else
+				extra = q.ct < 5 ? 6 : 5;
+			ps.term = 0;
+			ps.rate = (uint32_t)q.bp + extra;
+		}
+		prev_term = ps.term != 0;
+		passes[passno] = ps;
+		if(++passtype == 3)
+		{
+			passtype = 0;
+			bpno--;
+		}
+		if(sty & GRKB_CBLKSTY_RESET)
+			reset_states<CODE_THREADS>(cxs, mqt);
+	}
+	eseek(q, q.bp); // write the byte under construction back
+	// T1.cpp:905-931: rates made monotone, a trailing 0xFF is never included
+	uint32_t last = (uint32_t)q.bp;
+	for(uint32_t p = npasses; p > 0;)
+	{
+		--p;
+		if(passes[p].rate > last)
+			passes[p].rate = last;
+		else
+			last = passes[p].rate;
+	}
+	uint32_t prev = 0;
+	for(uint32_t p = 0; p < npasses; ++p)
+	{
+		uint32_t r = passes[p].rate;
+		if(r > 0 && q.out[r - 1] == 0xFF)
+			r--;
+		passes[p].rate = r;
+		passes[p].len = (uint16_t)(r - prev);
+		prev = r;
+	}
+	res.data_len = npasses ? prev : 0;
+	res.distortion = cum;
+	res.failed = q.overflow ? 1 : 0;
+	l.coded[bi] = res;
 }
 } // namespace
 
@@ -883,8 +1034,13 @@ int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s)
 		grkb_set_error("t1: cannot upload coding tables");
 		return -1;
 	}
-	const size_t per_warp = CXS_BYTES + SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
-	const size_t fixed = 94 * 4 + 1024 + 2048 + 256;
+	if(!l.sym_pool || l.sym_cap < (uint64_t)SYM_CHUNK)
+	{
+		grkb_set_error("t1 encode: no symbol pool");
+		return -1;
+	}
+	const size_t per_warp = SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
+	const size_t fixed = 1024 + 2048 + 256;
 	int nw = ENC_MAX_THREADS / 32;
 	while(nw > 1 && fixed + per_warp * nw > 100 * 1024)
 		--nw;
@@ -894,17 +1050,23 @@ int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s)
 		grkb_set_error("t1 encode: code block too large for shared memory (%zu bytes)", smem);
 		return -1;
 	}
-	GRKB_ENSURE_SMEM(t1_mq_encode_kernel, smem);
+	GRKB_ENSURE_SMEM(t1_mq_model_kernel, smem);
 	int dev = 0, sms = 148;
 	cudaGetDevice(&dev);
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-	const int per_sm = (int)((227 * 1024) / (smem + 1024)) > 0 ? (int)((227 * 1024) / (smem + 1024)) : 1;
+	int per_sm = (int)((227 * 1024) / (smem + 1024));
+	if(per_sm < 1)
+		per_sm = 1;
+	if(per_sm * nw > 64)
+		per_sm = 64 / nw;
 	uint32_t ctas = (uint32_t)(sms * per_sm);
 	const uint32_t need = (l.nblocks + nw - 1) / nw;
 	if(ctas > need)
 		ctas = need;
 	GRKB_CUDA_CHECK(cudaMemsetAsync(l.counter, 0, sizeof(uint32_t), s));
-	t1_mq_encode_kernel<<<ctas, nw * 32, smem, s>>>(l, tab);
+	t1_mq_model_kernel<<<ctas, nw * 32, smem, s>>>(l, tab);
+	GRKB_CUDA_CHECK(cudaGetLastError());
+	t1_mq_code_kernel<<<(l.nblocks + CODE_THREADS - 1) / CODE_THREADS, CODE_THREADS, 0, s>>>(l, tab);
 	GRKB_CUDA_CHECK(cudaGetLastError());
 	return 0;
 }
