@@ -83,6 +83,11 @@ lib.grkb_decoder_decode.argtypes = [_vp, _vp, _u32, _vp, _u32, _vp, C.c_size_t, 
                                     C.POINTER(_u32)]
 lib.grkb_decoder_submit.argtypes = [_vp, _vp, _u32, _vp, _u32, _vp, C.c_size_t, _vp, _u32]
 lib.grkb_decoder_wait.argtypes = [_vp, C.POINTER(_u32)]
+lib.grkb_decoder_submit_packed.argtypes = [_vp, _vp, _u32, _vp, _u32, _vp, C.c_size_t, _vp, _u32, C.c_size_t]
+lib.grkb_samples_size.argtypes = [_u32, _u32, _u32, C.c_size_t]
+lib.grkb_samples_size.restype = C.c_size_t
+lib.grkb_encoder_submit_packed.argtypes = [_vp, _vp, _u32, _int, C.c_size_t, _vp, _u32, _vp, _u32, _int, _vp, _vp,
+                                           _vp, C.c_size_t]
 lib.grkb_decoder_time_device.argtypes = [_vp, _u32, _u32, C.POINTER(C.c_float), C.POINTER(_u32)]
 lib.grkb_decoder_download.argtypes = [_vp, _vp, _u32]
 lib.grkb_t1_decode_host.argtypes = [_vp, _u32, _vp, _u32, _vp, C.c_size_t, _vp, _u32, _u32, _u32,

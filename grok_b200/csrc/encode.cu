@@ -122,7 +122,7 @@ int run_encoders(EncState& st, T1EncLaunch& l, bool any_mq, bool any_ht)
 	cudaStream_t s = st.stream;
 	if(st.coded.reserve((size_t)l.nblocks * sizeof(grkb_coded)) ||
 	   st.passes.reserve((size_t)l.nblocks * GRKB_ENC_MAX_PASSES * sizeof(grkb_pass)) ||
-	   st.slots.reserve((size_t)l.nblocks * l.slot_bytes) || st.misc.reserve(64))
+	   st.slots.reserve((size_t)l.nblocks * l.slot_bytes) || st.misc.reserve(64 + (size_t)l.nblocks * 8))
 		return -1;
 	l.coded = (grkb_coded*)st.coded.p;
 	l.passes = (grkb_pass*)st.passes.p;
@@ -130,7 +130,9 @@ int run_encoders(EncState& st, T1EncLaunch& l, bool any_mq, bool any_ht)
 	l.packed_used = (uint64_t*)st.misc.p;
 	l.counter = (uint32_t*)((uint8_t*)st.misc.p + 16);
 	l.sym_ctrl = (uint32_t*)((uint8_t*)st.misc.p + 8); // read back together with packed_used
-	l.order = nullptr;
+	l.code_ctrl = (uint32_t*)((uint8_t*)st.misc.p + 24);
+	l.sym_total = (uint32_t*)((uint8_t*)st.misc.p + 64);
+	l.code_order = l.sym_total + l.nblocks;
 	if(any_mq)
 	{
 		// a symbol is one byte; a block hands its symbols over in 1 KB chunks
@@ -275,6 +277,8 @@ struct grkb_encoder
 	uint8_t* p_bytes = nullptr;
 	size_t p_cap = 0;
 	uint64_t* h_total = nullptr; // pinned
+	void* packed_in = nullptr; // narrow input (row N3), allocated on first use
+	size_t packed_in_cap = 0;
 };
 
 static int encoder_front(grkb_encoder* e, cudaStream_t s)
@@ -374,16 +378,19 @@ void grkb_encoder_destroy(grkb_encoder* e)
 			cudaEventDestroy(v);
 	if(e->h_total)
 		cudaFreeHost(e->h_total);
+	if(e->packed_in)
+		cudaFree(e->packed_in);
 	e->st.release();
 	delete e;
 }
 
-int grkb_encoder_submit(grkb_encoder* e, const int32_t* const* image, uint32_t stride,
-						const grkb_enc_cblk* blocks, uint32_t nblocks, const double* mct_norms,
-						uint32_t mct_numcomps, int rate_control, grkb_coded* coded,
-						grkb_pass* passes, uint8_t* bytes, size_t cap)
+// the image arrives as int32 planes (image, stride) or in a narrow format (packed, format, ...)
+static int submit_any(grkb_encoder* e, const int32_t* const* image, uint32_t stride, const void* packed,
+					  uint32_t format, int sgnd, size_t row_bytes, const grkb_enc_cblk* blocks, uint32_t nblocks,
+					  const double* mct_norms, uint32_t mct_numcomps, int rate_control, grkb_coded* coded,
+					  grkb_pass* passes, uint8_t* bytes, size_t cap)
 {
-	if(!e || !image || stride < (e ? e->W : 0) || (nblocks && (!blocks || !coded || !passes)) ||
+	if(!e || (!image && !packed) || (image && stride < e->W) || (nblocks && (!blocks || !coded || !passes)) ||
 	   (cap && !bytes) || mct_numcomps > GRKB_MAX_COMPS)
 	{
 		grkb_set_error("grkb_encoder_submit: bad arguments");
@@ -401,16 +408,42 @@ int grkb_encoder_submit(grkb_encoder* e, const int32_t* const* image, uint32_t s
 	if(nblocks && scan_enc_blocks(blocks, nblocks, e->p.numcomps, e->stride, e->H, e->p.reversible, l,
 								  any_mq, any_ht))
 		return -1;
-	for(uint32_t c = 0; c < e->p.numcomps; ++c)
+	if(image)
 	{
-		if(!image[c])
+		for(uint32_t c = 0; c < e->p.numcomps; ++c)
 		{
-			grkb_set_error("grkb_encoder_encode: plane %u is null", c);
+			if(!image[c])
+			{
+				grkb_set_error("grkb_encoder_encode: plane %u is null", c);
+				return -1;
+			}
+			GRKB_CUDA_CHECK(cudaMemcpy2DAsync(e->image[c], (size_t)e->stride * 4, image[c],
+											  (size_t)stride * 4, (size_t)e->W * 4, e->H,
+											  cudaMemcpyHostToDevice, s));
+		}
+	}
+	else
+	{
+		if(format == GRKB_SAMPLES_32 || row_bytes < grkb_samples_min_row_bytes(format, e->W, e->p.numcomps) ||
+		   grkb_samples_min_row_bytes(format, e->W, e->p.numcomps) == 0)
+		{
+			grkb_set_error("grkb_encoder_submit_packed: bad format %u or rows of %zu bytes", format, row_bytes);
 			return -1;
 		}
-		GRKB_CUDA_CHECK(cudaMemcpy2DAsync(e->image[c], (size_t)e->stride * 4, image[c],
-										  (size_t)stride * 4, (size_t)e->W * 4, e->H,
-										  cudaMemcpyHostToDevice, s));
+		const size_t total = grkb_samples_bytes(format, e->H, e->p.numcomps, row_bytes);
+		if(total > e->packed_in_cap)
+		{
+			if(e->packed_in)
+				cudaFree(e->packed_in);
+			e->packed_in = nullptr;
+			e->packed_in_cap = 0;
+			GRKB_CUDA_CHECK(cudaMalloc(&e->packed_in, total));
+			e->packed_in_cap = total;
+		}
+		GRKB_CUDA_CHECK(cudaMemcpyAsync(e->packed_in, packed, total, cudaMemcpyHostToDevice, s));
+		if(grkb_launch_unpack_samples(e->packed_in, row_bytes, format, sgnd, e->image, e->p.numcomps, e->stride,
+									  e->W, e->H, s))
+			return -1;
 	}
 	if(encoder_front(e, s))
 		return -1;
@@ -459,6 +492,34 @@ int grkb_encoder_submit(grkb_encoder* e, const int32_t* const* image, uint32_t s
 									cudaMemcpyDeviceToHost, s));
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(e->h_total, l.packed_used, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
 	return 0;
+}
+
+int grkb_encoder_submit(grkb_encoder* e, const int32_t* const* image, uint32_t stride,
+						const grkb_enc_cblk* blocks, uint32_t nblocks, const double* mct_norms,
+						uint32_t mct_numcomps, int rate_control, grkb_coded* coded,
+						grkb_pass* passes, uint8_t* bytes, size_t cap)
+{
+	if(!image)
+	{
+		grkb_set_error("grkb_encoder_submit: bad arguments");
+		return -1;
+	}
+	return submit_any(e, image, stride, nullptr, 0, 0, 0, blocks, nblocks, mct_norms, mct_numcomps, rate_control,
+					  coded, passes, bytes, cap);
+}
+
+int grkb_encoder_submit_packed(grkb_encoder* e, const void* image, uint32_t format, int sgnd,
+							   size_t row_bytes, const grkb_enc_cblk* blocks, uint32_t nblocks,
+							   const double* mct_norms, uint32_t mct_numcomps, int rate_control,
+							   grkb_coded* coded, grkb_pass* passes, uint8_t* bytes, size_t cap)
+{
+	if(!image)
+	{
+		grkb_set_error("grkb_encoder_submit_packed: bad arguments");
+		return -1;
+	}
+	return submit_any(e, nullptr, 0, image, format, sgnd, row_bytes, blocks, nblocks, mct_norms, mct_numcomps,
+					  rate_control, coded, passes, bytes, cap);
 }
 
 int grkb_encoder_wait(grkb_encoder* e, size_t* used)

@@ -31,4 +31,12 @@ int grkb_idwt_device(const DwtGroup& g, grkb_rect tc, uint32_t numres, int rever
 int grkb_fdwt_device(const DwtGroup& g, grkb_rect tc, uint32_t numres, int reversible, int fin,
 					 const int32_t* shift, cudaStream_t s);
 
+// narrow sample formats (samples.cu, row N3): int32 planes <-> 8/16-bit packed buffer, both on the device
+int grkb_launch_pack_samples(void* const* planes, uint32_t numcomps, uint32_t stride, uint32_t W, uint32_t H,
+							 uint32_t format, void* packed, size_t row_bytes, cudaStream_t s);
+int grkb_launch_unpack_samples(const void* packed, size_t row_bytes, uint32_t format, int sgnd, void* const* planes,
+							   uint32_t numcomps, uint32_t stride, uint32_t W, uint32_t H, cudaStream_t s);
+size_t grkb_samples_min_row_bytes(uint32_t format, uint32_t W, uint32_t numcomps);
+size_t grkb_samples_bytes(uint32_t format, uint32_t H, uint32_t numcomps, size_t row_bytes);
+
 void grkb_set_error(const char* fmt, ...);

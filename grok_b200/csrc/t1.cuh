@@ -66,7 +66,6 @@ struct T1Launch
 struct T1EncLaunch
 {
 	const grkb_enc_cblk* blocks; // device
-	const uint32_t* order; // device: block indices, largest first (may be null)
 	uint32_t nblocks;
 	const void* planes[GRKB_MAX_COMPS]; // device coefficient planes
 	uint32_t stride;
@@ -91,6 +90,12 @@ struct T1EncLaunch
 	uint64_t sym_cap; // bytes
 	uint32_t* sym_ctrl; // device: [0] chunks handed out, [1] set when the pool ran out
 	uint64_t total_area; // sum of w*h over the MQ blocks (sizes the pool)
+	// the arithmetic coder takes the blocks longest first: symbols per block (left by the context
+	// modelling), the block indices in that order, and [0] how many of the longest blocks get a
+	// warp of their own
+	uint32_t* sym_total; // device, nblocks
+	uint32_t* code_order; // device, nblocks
+	uint32_t* code_ctrl; // device
 };
 int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s);
 int grkb_launch_t1_ht_encode(const T1EncLaunch& l, cudaStream_t s);

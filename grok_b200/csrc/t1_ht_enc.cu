@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(HTE_THREADS)
 		item = __shfl_sync(0xffffffffu, item, 0);
 		if(item >= l.nblocks)
 			break;
-		const uint32_t bi = l.order ? l.order[item] : item;
+		const uint32_t bi = item;
 		const grkb_enc_cblk cb = l.blocks[bi];
 		if(!(cb.cblk_sty & GRKB_CBLKSTY_HT))
 			continue;

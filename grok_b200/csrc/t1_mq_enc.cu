@@ -1,5 +1,6 @@
 // t1_mq_enc.cu -- EBCOT (JPEG 2000 Part 1) code-block encoder with the quantiser fused into
-// the load, sm_100a.  One code block per warp.
+// the load, sm_100a.  Two kernels: context modelling (one code block per warp) and the
+// arithmetic coder (one code block per THREAD).
 //
 // Replaces, behind the C-ABI, the reference's
 //   T1Part1::preCompress / compress   src/lib/jp2/t1/t1_part1/T1Part1.cpp:37-132
@@ -8,8 +9,11 @@
 //   getwmsedec                        T1.cpp:418-436 (+ norms :239-277)
 //   MQ / RAW encoder                  t1/t1_part1/mqc_enc.cpp:86-332, mqc_enc_inl.h:38-124
 //
-// Shape: one code block per warp.  Unlike the decoder, the encoder knows every decision in
-// advance, so only the arithmetic coder itself is a serial chain:
+// Shape.  Unlike the decoder, the encoder knows every decision in advance, so only the
+// arithmetic coder itself is a serial chain; the two halves have opposite shapes and are
+// separate kernels with a symbol stream in global memory between them.
+//
+// t1_mq_model_kernel, one code block per warp:
 //   * all lanes load the block's rows from the coefficient plane (coalesced), quantise to
 //     sign-magnitude with 6 fractional bits into shared memory and reduce the block maximum;
 //   * every coding pass walks the stripes in segments of 32 columns, one column per lane: the
@@ -20,12 +24,23 @@
 //     one column to the west or one row up) and is iterated to its fixed point with shuffles;
 //     refinement and cleanup are known outright.  The state words (layout in t1.cuh) are
 //     updated by all lanes at once afterwards;
-//   * lane 0 feeds the list to the MQ (or bypass) coder, emitting bytes into the block's slot
-//     in global memory with the byte under construction held in a register (the coder's carry
-//     only ever touches that byte), and keeps the per-pass rate / length / termination records;
-//     the distortion estimate of a pass is a warp sum of table values (integers, so the order of
-//     the additions does not matter) turned into the reference's double-precision figure.
+//   * the list goes out, one byte per symbol, to a chain of SYM_CHUNK-byte chunks taken from a
+//     device pool with an atomic counter (the host sizes the pool per sample and retries with a
+//     larger one if a frame runs it dry); the number of symbols of each pass is left in the
+//     pass record, and the distortion estimate of a pass is a warp sum of table values
+//     (integers, so the order of the additions does not matter) kept for the second kernel to
+//     turn into the reference's double-precision figure.
+//
+// t1_mq_code_kernel, one code block per thread (32 coders per warp, in lockstep):
+//   * reads its block's chain a word at a time with the next word prefetched, and runs the MQ
+//     (or bypass) coder as one flat loop over symbols with the pass bookkeeping (termination,
+//     rate, length, RESET / TERMALL / PTERM / SEGSYM) at the pass boundaries.  A branch taken
+//     by any coder of the warp costs all of them, so the decision and byte-out are written
+//     with selects; the context states of a thread are one column of a shared-memory array;
+//   * bytes go into the block's slot in global memory with the byte under construction held
+//     in a register (the coder's carry only ever touches that byte).
 #include "t1.cuh"
+#include <stdlib.h>
 
 namespace
 {
@@ -709,10 +724,14 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 		item = __shfl_sync(0xffffffffu, item, 0);
 		if(item >= l.nblocks)
 			break;
-		const uint32_t bi = l.order ? l.order[item] : item;
+		const uint32_t bi = item;
 		const grkb_enc_cblk cb = l.blocks[bi];
 		if(cb.cblk_sty & GRKB_CBLKSTY_HT)
+		{
+			if(lane == 0)
+				l.sym_total[bi] = 0;
 			continue;
+		}
 		const uint32_t w = cb.w, h = cb.h;
 		const uint32_t fs = w + 2, nstripes = (h + 3) >> 2, nfl = fs * (nstripes + 2);
 		// ---- quantise to sign-magnitude, 6 fractional bits (T1Part1.cpp:37-88) -----------------
@@ -752,6 +771,7 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 			res.numbps = (uint8_t)(t <= 6 ? 0 : t - 6);
 		}
 		grkb_pass* passes = l.passes + (size_t)bi * GRKB_ENC_MAX_PASSES;
+		uint32_t nsym = 0;
 		if(res.numbps)
 		{
 			EBlk b;
@@ -804,6 +824,7 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 					grkb_pass ps;
 					ps.distortion = __longlong_as_double((long long)nmsedec);
 					ps.rate = sw.count;
+					nsym += sw.count;
 					ps.len = 0;
 					ps.term = 0;
 					ps.reserved = 0;
@@ -820,8 +841,85 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 			res.failed = sw.dead ? 2 : 0;
 		}
 		if(lane == 0)
+		{
 			l.coded[bi] = res;
+			l.sym_total[bi] = nsym;
+		}
 		__syncwarp();
+	}
+}
+
+// ---- between the two: the order the coder takes the blocks in ------------------------------------
+// The coder's running time is the length of its longest chain, and the 32 chains of a warp cost
+// as much as the longest of them.  So the blocks are handed out longest first (bucket sort on the
+// symbol count, 1024 buckets), which puts blocks of like length into the same warp, and the
+// blocks at the very top -- longer than `frac`/256 of the longest one, at most `cap` of them --
+// each get a warp to themselves, where the chain runs several times faster than in lockstep with
+// 31 others on different branches.
+constexpr int ORDER_THREADS = 1024;
+__global__ void __launch_bounds__(ORDER_THREADS)
+	t1_mq_order_kernel(const T1EncLaunch l, uint32_t frac, uint32_t cap, uint32_t min_long)
+{
+	__shared__ uint32_t cnt[ORDER_THREADS], start[ORDER_THREADS], red[32];
+	const uint32_t t = threadIdx.x, lane = t & 31, warp = t >> 5;
+	uint32_t mx = 0;
+	for(uint32_t i = t; i < l.nblocks; i += ORDER_THREADS)
+		mx = max(mx, l.sym_total[i]);
+	for(int o = 16; o; o >>= 1)
+		mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+	if(lane == 0)
+		red[warp] = mx;
+	cnt[t] = 0;
+	__syncthreads();
+	mx = red[lane];
+	for(int o = 16; o; o >>= 1)
+		mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+	const uint64_t scale = (uint64_t)mx + 1;
+	// bucket 0 holds the longest blocks
+	for(uint32_t i = t; i < l.nblocks; i += ORDER_THREADS)
+		atomicAdd(&cnt[ORDER_THREADS - 1 - (uint32_t)(((uint64_t)l.sym_total[i] * ORDER_THREADS) / scale)], 1u);
+	__syncthreads();
+	// exclusive scan of the 1024 counts
+	const uint32_t own = cnt[t];
+	uint32_t inc = own;
+	for(int o = 1; o < 32; o <<= 1)
+	{
+		const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+		if((int)lane >= o)
+			inc += v;
+	}
+	__syncthreads();
+	if(lane == 31)
+		red[warp] = inc;
+	__syncthreads();
+	uint32_t wsum = red[lane];
+	for(int o = 1; o < 32; o <<= 1)
+	{
+		const uint32_t v = __shfl_up_sync(0xffffffffu, wsum, o);
+		if((int)lane >= o)
+			wsum += v;
+	}
+	const uint32_t before = __shfl_sync(0xffffffffu, wsum, warp ? warp - 1 : 0);
+	start[t] = inc - own + (warp ? before : 0);
+	__syncthreads();
+	if(t == 0)
+	{
+		// blocks in the buckets above the threshold, whole buckets only
+		uint32_t nlong = 0;
+		if(mx >= min_long)
+		{
+			const uint32_t nb = ORDER_THREADS - (ORDER_THREADS * frac >> 8); // buckets that qualify
+			nlong = nb < ORDER_THREADS ? start[nb] : l.nblocks;
+			if(nlong > cap)
+				nlong = cap;
+		}
+		l.code_ctrl[0] = nlong;
+	}
+	__syncthreads();
+	for(uint32_t i = t; i < l.nblocks; i += ORDER_THREADS)
+	{
+		const uint32_t b = ORDER_THREADS - 1 - (uint32_t)(((uint64_t)l.sym_total[i] * ORDER_THREADS) / scale);
+		l.code_order[atomicAdd(&start[b], 1u)] = i;
 	}
 }
 
@@ -880,9 +978,21 @@ __global__ void __launch_bounds__(CODE_THREADS)
 	for(uint32_t i = threadIdx.x; i < 94; i += blockDim.x)
 		mqt[i] = tab->mq[i] | (i << 31); // the MPS of state 2i+mps rides in bit 31
 	__syncthreads();
-	const uint32_t bi = blockIdx.x * CODE_THREADS + threadIdx.x;
-	if(bi >= l.nblocks)
+	// the first nlong warps take one block each (lane 0 only), the others 32 blocks each
+	const uint32_t nlong = l.code_ctrl[0];
+	const uint32_t gw = blockIdx.x * (CODE_THREADS / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+	uint32_t idx;
+	if(gw < nlong)
+	{
+		if(lane)
+			return;
+		idx = gw;
+	}
+	else
+		idx = nlong + (gw - nlong) * 32 + lane;
+	if(idx >= l.nblocks)
 		return;
+	const uint32_t bi = l.code_order[idx];
 	const grkb_enc_cblk cb = l.blocks[bi];
 	if(cb.cblk_sty & GRKB_CBLKSTY_HT)
 		return;
@@ -1024,6 +1134,12 @@ __global__ void __launch_bounds__(CODE_THREADS)
 }
 } // namespace
 
+static uint32_t env_u32(const char* name, uint32_t dflt)
+{
+	const char* v = getenv(name);
+	return v && *v ? (uint32_t)strtoul(v, nullptr, 10) : dflt;
+}
+
 int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s)
 {
 	if(l.nblocks == 0)
@@ -1066,7 +1182,14 @@ int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s)
 	GRKB_CUDA_CHECK(cudaMemsetAsync(l.counter, 0, sizeof(uint32_t), s));
 	t1_mq_model_kernel<<<ctas, nw * 32, smem, s>>>(l, tab);
 	GRKB_CUDA_CHECK(cudaGetLastError());
-	t1_mq_code_kernel<<<(l.nblocks + CODE_THREADS - 1) / CODE_THREADS, CODE_THREADS, 0, s>>>(l, tab);
+	static const uint32_t frac = env_u32("GRKB_MQ_LONG_FRAC", 50); // of 256: 0.2 of the longest block
+	static const uint32_t cap = env_u32("GRKB_MQ_LONG_CAP", 2048);
+	static const uint32_t min_long = env_u32("GRKB_MQ_LONG_MIN", 1024);
+	t1_mq_order_kernel<<<1, ORDER_THREADS, 0, s>>>(l, frac > 256 ? 256 : frac, cap, min_long);
+	GRKB_CUDA_CHECK(cudaGetLastError());
+	const uint32_t solo = cap < l.nblocks ? cap : l.nblocks;
+	const uint32_t warps = solo + (l.nblocks + 31) / 32;
+	t1_mq_code_kernel<<<(warps + CODE_THREADS / 32 - 1) / (CODE_THREADS / 32), CODE_THREADS, 0, s>>>(l, tab);
 	GRKB_CUDA_CHECK(cudaGetLastError());
 	return 0;
 }

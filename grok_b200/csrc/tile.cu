@@ -41,6 +41,8 @@ struct grkb_decoder
 	uint32_t max_area = 0, max_flag_words = 0, max_ht_w = 0;
 	bool any_mq = false, any_ht = false, ht_refine = false;
 	cudaEvent_t ev[6] = {};
+	void* packed = nullptr; // narrow output (row N3), allocated on first use
+	size_t packed_cap = 0;
 };
 
 namespace
@@ -334,9 +336,9 @@ void grkb_decoder_destroy(grkb_decoder* d)
 	delete d;
 }
 
-int grkb_decoder_submit(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
-						const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
-						int32_t* const* planes, uint32_t stride)
+// copies in, all kernels, status out: everything of a submit but the results
+static int submit_front(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks, const grkb_seg* segs,
+						uint32_t nsegs, const uint8_t* bytes, size_t nbytes)
 {
 	if(!d || (nblocks && !blocks) || (nsegs && !segs) || (nbytes && !bytes))
 	{
@@ -368,6 +370,16 @@ int grkb_decoder_submit(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nbloc
 		return -1;
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(d->h_status, d->d_counters + 2, sizeof(uint32_t),
 									cudaMemcpyDeviceToHost, s));
+	return 0;
+}
+
+int grkb_decoder_submit(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
+						const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
+						int32_t* const* planes, uint32_t stride)
+{
+	if(submit_front(d, blocks, nblocks, segs, nsegs, bytes, nbytes))
+		return -1;
+	cudaStream_t s = d->stream;
 	if(planes)
 	{
 		if(stride < d->W)
@@ -380,6 +392,69 @@ int grkb_decoder_submit(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nbloc
 											  (size_t)d->stride * 4, (size_t)d->W * 4, d->H,
 											  cudaMemcpyDeviceToHost, s));
 	}
+	return 0;
+}
+
+size_t grkb_samples_size(uint32_t format, uint32_t H, uint32_t numcomps, size_t row_bytes)
+{
+	if(format == GRKB_SAMPLES_32)
+		return row_bytes * H * numcomps;
+	return grkb_samples_bytes(format, H, numcomps, row_bytes);
+}
+
+int grkb_decoder_submit_packed(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
+							   const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
+							   void* out, uint32_t format, size_t row_bytes)
+{
+	if(!d || !out)
+	{
+		grkb_set_error("grkb_decoder_submit_packed: null argument");
+		return -1;
+	}
+	const uint32_t width = (format == GRKB_SAMPLES_16 || format == GRKB_SAMPLES_16_INTERLEAVED) ? 16
+						   : (format == GRKB_SAMPLES_8 || format == GRKB_SAMPLES_8_INTERLEAVED) ? 8
+																								  : 0;
+	if(width == 0 || row_bytes < grkb_samples_min_row_bytes(format, d->W, d->p.numcomps))
+	{
+		grkb_set_error("grkb_decoder_submit_packed: bad format %u or rows of %zu bytes", format, row_bytes);
+		return -1;
+	}
+	// the clamp of the last stage must already fit the format: [lo, hi] inside its range
+	for(uint32_t c = 0; c < d->p.numcomps; ++c)
+	{
+		const int64_t lo = d->p.lo[c], hi = d->p.hi[c];
+		const bool fits = lo >= 0 ? hi < ((int64_t)1 << width)
+								  : (lo >= -((int64_t)1 << (width - 1)) && hi < ((int64_t)1 << (width - 1)));
+		if(!fits)
+		{
+			grkb_set_error("grkb_decoder_submit_packed: component %u ranges over [%lld, %lld], wider than %u bits", c,
+						   (long long)lo, (long long)hi, width);
+			return -1;
+		}
+	}
+	GRKB_CUDA_CHECK(cudaSetDevice(d->device));
+	const size_t total = grkb_samples_bytes(format, d->H, d->p.numcomps, row_bytes);
+	if(total > d->packed_cap)
+	{
+		if(d->packed)
+			cudaFree(d->packed);
+		d->packed = nullptr;
+		d->packed_cap = 0;
+		GRKB_CUDA_CHECK(cudaMalloc(&d->packed, total));
+		d->packed_cap = total;
+	}
+	if(submit_front(d, blocks, nblocks, segs, nsegs, bytes, nbytes))
+		return -1;
+	cudaStream_t s = d->stream;
+	if(grkb_launch_pack_samples(d->image, d->p.numcomps, d->stride, d->W, d->H, format, d->packed, row_bytes, s))
+		return -1;
+	// padding between the caller's rows stays untouched
+	const size_t need = grkb_samples_min_row_bytes(format, d->W, d->p.numcomps);
+	if(need == row_bytes)
+		GRKB_CUDA_CHECK(cudaMemcpyAsync(out, d->packed, total, cudaMemcpyDeviceToHost, s));
+	else
+		GRKB_CUDA_CHECK(cudaMemcpy2DAsync(out, row_bytes, d->packed, row_bytes, need, total / row_bytes,
+										  cudaMemcpyDeviceToHost, s));
 	return 0;
 }
 

@@ -119,6 +119,23 @@ class TileEncoder:
                                       coded.ctypes.data, passes.ctypes.data, buf.ctypes.data, buf.size),
               "grkb_encoder_submit")
 
+    def submit_packed(self, image, blocks, out, mct_norms=None, rate_control=False, interleaved=False):
+        """grkb_encoder_submit_packed (row N3): the image as one 8- or 16-bit array, widened on the
+        device (signed dtypes sign-extend): (numcomps, H, >=W) planar, or (H, >=W, numcomps) with
+        interleaved=True."""
+        blocks = np.ascontiguousarray(blocks, dtype=T.ENC_CBLK_DTYPE)
+        fmt, row_bytes = T.sample_format(image, interleaved, self.params.numcomps,
+                                         self.params.y1 - self.params.y0)
+        coded, passes, buf = out
+        norms = None if mct_norms is None else np.ascontiguousarray(mct_norms, dtype=np.float64)
+        self._inflight = (image, blocks, norms, None, out)
+        check(lib.grkb_encoder_submit_packed(self.h, image.ctypes.data, fmt, int(image.dtype.kind == "i"),
+                                             row_bytes, blocks.ctypes.data, len(blocks),
+                                             None if norms is None else norms.ctypes.data,
+                                             0 if norms is None else len(norms), int(rate_control),
+                                             coded.ctypes.data, passes.ctypes.data, buf.ctypes.data, buf.size),
+              "grkb_encoder_submit_packed")
+
     def wait(self):
         """grkb_encoder_wait -> (coded, passes, bytes) of the tile submitted last"""
         used = C.c_size_t()

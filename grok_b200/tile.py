@@ -72,6 +72,29 @@ class PinnedArray:
             self.ptr = None
 
 
+SAMPLES_32, SAMPLES_16, SAMPLES_16_INTERLEAVED, SAMPLES_8, SAMPLES_8_INTERLEAVED = range(5)
+
+
+def sample_format(a, interleaved, numcomps, H):
+    """(format, row_bytes) of a packed sample array for the grkb_*_submit_packed calls."""
+    if a.ndim != 3 or a.dtype.itemsize not in (1, 2) or a.dtype.kind not in "iu":
+        raise ValueError("packed samples: 3-D array of 8- or 16-bit integers expected")
+    if interleaved:
+        ok = a.shape[0] == H and a.shape[2] == numcomps and a.strides[2] == a.dtype.itemsize and \
+            a.strides[1] == numcomps * a.dtype.itemsize
+        row = a.strides[0]
+    else:
+        ok = a.shape[0] == numcomps and a.shape[1] == H and a.strides[2] == a.dtype.itemsize and \
+            a.strides[0] == a.strides[1] * H
+        row = a.strides[1]
+    if not ok:
+        raise ValueError("packed samples: unexpected shape/strides %r %r" % (a.shape, a.strides))
+    wide = a.dtype.itemsize == 2
+    fmt = (SAMPLES_16_INTERLEAVED if interleaved else SAMPLES_16) if wide else \
+        (SAMPLES_8_INTERLEAVED if interleaved else SAMPLES_8)
+    return fmt, row
+
+
 class TileDecoder:
     """grkb_decoder: device-resident state for one tile geometry"""
 
@@ -125,6 +148,18 @@ class TileDecoder:
         check(lib.grkb_decoder_submit(self.h, blocks.ctypes.data, len(blocks), segs.ctypes.data,
                                       len(segs), data.ctypes.data, data.size, ptrs, stride),
               "grkb_decoder_submit")
+
+    def submit_packed(self, blocks, segs, data, out, interleaved=False):
+        """grkb_decoder_submit_packed (row N3): like submit(), the result narrowed on the device to
+        out's dtype (uint16 / int16 / uint8 / int8).  out: (numcomps, H, >=W) planar, or
+        (H, >=W, numcomps) with interleaved=True; rows contiguous."""
+        blocks = np.ascontiguousarray(blocks, dtype=CBLK_DTYPE)
+        segs = np.ascontiguousarray(segs, dtype=SEG_DTYPE)
+        fmt, row_bytes = sample_format(out, interleaved, self.params.numcomps, self.H)
+        self._inflight = (blocks, segs, data, out, None)
+        check(lib.grkb_decoder_submit_packed(self.h, blocks.ctypes.data, len(blocks), segs.ctypes.data,
+                                             len(segs), data.ctypes.data, data.size, out.ctypes.data,
+                                             fmt, row_bytes), "grkb_decoder_submit_packed")
 
     def wait(self):
         st = C.c_uint32()

@@ -215,6 +215,31 @@ int grkb_decoder_submit(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nbloc
 						int32_t* const* planes, uint32_t stride);
 int grkb_decoder_wait(grkb_decoder* d, uint32_t* status_out);
 
+/* Narrow sample formats at the bus (opt-in, beyond the int32 grk_image
+ * contract).  The reference narrows int32 planes on the host whenever samples leave the library
+ * (planarToInterleaved, src/bin/common/convert.cpp:397-405; the 8/16-bit file writers) and widens
+ * file samples on the way in (convert_16u32s_C1R, convert.cpp:547-556); here that runs on the
+ * device and the bus carries 1 or 2 bytes per sample.  Samples are in host byte order: the low
+ * 16 / 8 bits of the int32 (two's complement for signed components).  Planar buffers hold
+ * numcomps planes of H rows back to back; interleaved ones H rows of W pixels of numcomps
+ * samples; rows are row_bytes apart (>= the samples of a row; a multiple of 8 with an 8-byte
+ * aligned base keeps the device side on vector accesses). */
+enum
+{
+	GRKB_SAMPLES_32 = 0, /* int32 planes: the grk_image form */
+	GRKB_SAMPLES_16 = 1,
+	GRKB_SAMPLES_16_INTERLEAVED = 2,
+	GRKB_SAMPLES_8 = 3,
+	GRKB_SAMPLES_8_INTERLEAVED = 4
+};
+/* grkb_decoder_submit with the result narrowed on the device: `out` receives
+ * grkb_samples_size(format, ...) bytes.  Precision above the format's width is refused. */
+int grkb_decoder_submit_packed(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
+							   const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
+							   void* out, uint32_t format, size_t row_bytes);
+/* bytes of a packed buffer: H rows (x numcomps planes when planar) of row_bytes */
+size_t grkb_samples_size(uint32_t format, uint32_t H, uint32_t numcomps, size_t row_bytes);
+
 /* Re-runs the device stages (T1, wavelet, MCT) of the last tile given to grkb_decoder_decode,
  * inputs already resident in HBM, no host copies: `iters` passes after `warmup`, timed with CUDA
  * events on the decoder's stream.  ms[0] = mean whole pass, ms[1] = mean T1 kernels,
@@ -338,6 +363,12 @@ int grkb_encoder_submit(grkb_encoder* e, const int32_t* const* image, uint32_t s
 						uint32_t mct_numcomps, int rate_control, grkb_coded* coded,
 						grkb_pass* passes, uint8_t* bytes, size_t cap);
 int grkb_encoder_wait(grkb_encoder* e, size_t* used);
+/* grkb_encoder_submit with the image in a narrow format (GRKB_SAMPLES_16 ..., see the decoder):
+ * `image` holds grkb_samples_size(format, ...) bytes, widened on the device (sgnd: sign-extend). */
+int grkb_encoder_submit_packed(grkb_encoder* e, const void* image, uint32_t format, int sgnd,
+							   size_t row_bytes, const grkb_enc_cblk* blocks, uint32_t nblocks,
+							   const double* mct_norms, uint32_t mct_numcomps, int rate_control,
+							   grkb_coded* coded, grkb_pass* passes, uint8_t* bytes, size_t cap);
 /* Re-runs the device stages of the last tile (image still resident), CUDA events on the
  * encoder's stream: ms[0] whole pass, ms[1] DC/MCT/wavelet, ms[2] block coding + packing. */
 int grkb_encoder_time_device(grkb_encoder* e, uint32_t iters, uint32_t warmup, float ms[3]);

@@ -146,6 +146,38 @@ def ref_mct_inv(planes, irrev, mct_on, prec, sgnd, shift):
 
 # ---------------------------------------------------------------- EBCOT / MQ block coder
 
+# ---------------------------------------------------------------- narrow samples (row N3)
+
+def orc_pack_samples(planes, dtype, interleaved=False, row_pad=0):
+    """int32 planes -> one array of `dtype` (8 or 16 bits): (nc, H, W+row_pad) or (H, W+row_pad, nc)"""
+    a = [np.ascontiguousarray(p, dtype=np.int32) for p in planes]
+    nc, (H, W) = len(a), a[0].shape
+    dt = np.dtype(dtype)
+    out = np.zeros((H, W + row_pad, nc) if interleaved else (nc, H, W + row_pad), dtype=dt)
+    row = out.strides[0] if interleaved else out.strides[1]
+    ptrs = (C.c_void_p * nc)(*[p.ctypes.data for p in a])
+    oracle().orc_pack_samples(ptrs, C.c_uint32(nc), C.c_uint32(W), C.c_uint32(W), C.c_uint32(H),
+                              C.c_uint32(dt.itemsize), C.c_int(int(interleaved)), _p(out), C.c_uint64(row))
+    return out
+
+
+def orc_unpack_samples(packed, W, interleaved=False):
+    """inverse of orc_pack_samples (signed dtypes sign-extend) -> list of int32 planes"""
+    packed = np.ascontiguousarray(packed)
+    if interleaved:
+        H, nc = packed.shape[0], packed.shape[2]
+        row = packed.strides[0]
+    else:
+        nc, H = packed.shape[0], packed.shape[1]
+        row = packed.strides[1]
+    out = [np.zeros((H, W), dtype=np.int32) for _ in range(nc)]
+    ptrs = (C.c_void_p * nc)(*[p.ctypes.data for p in out])
+    oracle().orc_unpack_samples(_p(packed), C.c_uint64(row), C.c_uint32(packed.dtype.itemsize),
+                                C.c_int(int(interleaved)), C.c_int(int(packed.dtype.kind == "i")), ptrs,
+                                C.c_uint32(nc), C.c_uint32(W), C.c_uint32(W), C.c_uint32(H))
+    return out
+
+
 def to_smr(x):
     """two's complement int32 array -> sign-magnitude (t1_common.h:84)"""
     x = np.asarray(x, dtype=np.int64)

@@ -81,12 +81,23 @@ def ht_encode(args):
             k = f % K
             if pend[k]:
                 encs[k].wait()
-            encs[k].submit(src, pblocks.array, outs[k])
+            if args.samples16:
+                encs[k].submit_packed(src16.array, pblocks.array, outs[k])
+            else:
+                encs[k].submit(src, pblocks.array, outs[k])
             pend[k] = True
         for k in range(K):
             if pend[k]:
                 encs[k].wait()
 
+    if args.samples16:
+        # row N3: the frame crosses the bus as uint16 planes, widened on the device
+        src16 = T.PinnedArray((3, H, W), np.uint16)
+        for c in range(3):
+            src16.array[c] = img[c]
+        encs[0].submit_packed(src16.array, pblocks.array, outs[0])
+        c16, p16, d16 = encs[0].wait()
+        assert np.array_equal(c16, coded) and bytes(d16) == bytes(data)
     run(2 * K)
     t0 = time.perf_counter()
     run(args.steps * K)
@@ -116,8 +127,8 @@ def ht_encode(args):
         "config": {"workload": "htj2k_encode_4096x2160_rgb12_53_rct_lossless_5lvl_cblk64_1tile",
                    "code_blocks": int(n), "coded_bytes": int(len(data))},
         "e2e": {"value": mp / (e2e_ms * 1e-3), "unit": "Mpixel/s", "ms_per_step": e2e_ms,
-                "encoders_in_flight": K,
-                "h2d_bytes_per_step": int(W * H * 3 * 4 + blocks.nbytes),
+                "encoders_in_flight": K, "input_samples": "uint16 planes (N3)" if args.samples16 else "int32 planes",
+                "h2d_bytes_per_step": int(W * H * 3 * (2 if args.samples16 else 4) + blocks.nbytes),
                 "d2h_bytes_per_step": int(len(data) + coded.nbytes + n * int(coded["numpasses"].max()) * 16)},
         "stages_ms": {"dc_rct_fdwt": tm["dwt_ms"], "t1_ht_encode_pack": tm["t1_ms"]},
         "round_trip_lossless": bool(lossless), "cpu_baseline": cpu}), flush=True)
@@ -233,6 +244,12 @@ def mq_encode(args):
     enc = E.TileEncoder(params)
     pins = []
     for f in mine:
+        if args.samples16:
+            pin = T.PinnedArray((3, H, W), np.uint16)
+            for c in range(3):
+                pin.array[c] = base[c][:, 8 * f:8 * f + W]
+            pins.append(pin.array)
+            continue
         pin = [T.PinnedArray((H, W), np.int32) for _ in range(3)]
         for p, a in zip(pin, base):
             p.array[:] = a[:, 8 * f:8 * f + W]
@@ -249,18 +266,27 @@ def mq_encode(args):
                      T.PinnedArray((n, T.ENC_MAX_PASSES), T.PASS_DTYPE).array,
                      T.PinnedArray((W * H * 3 * 2,), np.uint8).array) for _ in range(K - 1)]
 
+    host = {"submit": 0.0, "wait": 0.0}
+
     def one_pass():
         # frames of this rank, K encoders in flight (grkb_encoder_submit / wait)
         nb, pend = 0, [False] * K
         for i, src in enumerate(pins):
             k = i % K
+            ta = time.perf_counter()
             if pend[k]:
                 nb += len(encs[k].wait()[2])
-            encs[k].submit(src, pblocks.array, outs[k], mct_norms=E.MCT_NORMS_IRREV, rate_control=True)
+            tb = time.perf_counter()
+            (encs[k].submit_packed if args.samples16 else encs[k].submit)(
+                src, pblocks.array, outs[k], mct_norms=E.MCT_NORMS_IRREV, rate_control=True)
             pend[k] = True
+            host["wait"] += tb - ta
+            host["submit"] += time.perf_counter() - tb
+        ta = time.perf_counter()
         for k in range(K):
             if pend[k]:
                 nb += len(encs[k].wait()[2])
+        host["wait"] += time.perf_counter() - ta
         return nb
 
     nb = one_pass()
@@ -272,9 +298,11 @@ def mq_encode(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     shard.barrier(world)
     t0 = time.perf_counter()
+    host["submit"] = host["wait"] = 0.0
     for _ in range(args.steps):
         one_pass()
     ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    host_ms = {k: v * 1e3 / args.steps / max(1, len(mine)) for k, v in host.items()}
     ms = shard.max_over_ranks(ms, world, device="cuda" if world > 1 else None)
     tm = enc.time_device(max(2, args.steps), 1)
     if rank != 0:
@@ -307,8 +335,10 @@ def mq_encode(args):
                    "scope": "DC shift + ICT + 9/7 + quantise + EBCOT/MQ (all passes, rates, distortions) + packing; "
                             "PCRD and T2 stay on the host (SURVEY 8f N2)"},
         "e2e": {"value": mp * nframes / (ms * 1e-3), "unit": "Mpixel/s", "ms_per_batch": ms,
-                "h2d_bytes_per_frame": int(W * H * 3 * 4 + blocks.nbytes),
+                "input_samples": "uint16 planes (N3)" if args.samples16 else "int32 planes",
+                "h2d_bytes_per_frame": int(W * H * 3 * (2 if args.samples16 else 4) + blocks.nbytes),
                 "encoders_in_flight": K,
+                "host_ms_per_frame_in_submit": host_ms["submit"], "host_ms_per_frame_in_wait": host_ms["wait"],
                 "d2h_bytes_per_frame": int(nb // max(1, len(mine)) + out[0].nbytes +
                                            n * int(out[0]["numpasses"].max()) * 16)},
         "stages_ms": {"dc_ict_fdwt": tm["dwt_ms"], "t1_mq_encode_pack": tm["t1_ms"]},
@@ -327,6 +357,8 @@ def main():
     ap.add_argument("--size", type=int, default=8192)
     ap.add_argument("--verify", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--samples16", action="store_true",
+                    help="encode benches: send the frames as uint16 planes (grkb_encoder_submit_packed)")
     args = ap.parse_args()
     if args.inflight is None:
         args.inflight = 4 if args.what == "tiled" else 2
