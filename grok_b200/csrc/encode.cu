@@ -570,12 +570,6 @@ int grkb_encoder_wait(grkb_encoder* e, size_t* used)
 	if(maxp > GRKB_ENC_MAX_PASSES)
 		maxp = GRKB_ENC_MAX_PASSES;
 	const size_t pitch = (size_t)GRKB_ENC_MAX_PASSES * sizeof(grkb_pass);
-	static const int exp_mode = getenv("GRKB_EXP_PASSES") ? atoi(getenv("GRKB_EXP_PASSES")) : 0;
-	if(exp_mode == 1)
-		; // experiment: no pass table at all
-	else if(exp_mode == 2)
-		GRKB_CUDA_CHECK(cudaMemcpyAsync(e->p_passes, e->last.passes, pitch * e->p_nblocks, cudaMemcpyDeviceToHost, s));
-	else
 	GRKB_CUDA_CHECK(cudaMemcpy2DAsync(e->p_passes, pitch, e->last.passes, pitch, (size_t)maxp * sizeof(grkb_pass),
 									  e->p_nblocks, cudaMemcpyDeviceToHost, s));
 	if(total)

@@ -30,6 +30,7 @@ struct SampleArgs
 	size_t plane_bytes; // planar formats: H * row_bytes
 	int sgnd;
 	int vec_ok; // packed rows and base aligned for the vector accesses
+	int be; // 16-bit samples are big-endian on the packed side (PNM files)
 };
 
 template<typename T> struct Vec4;
@@ -66,6 +67,21 @@ template<> struct Vec4<uint8_t>
 	}
 };
 
+// byte order of the packed side: 16-bit samples swapped when the buffer is big-endian
+template<typename V> static __device__ __forceinline__ V swap16(V p, int be);
+template<> __device__ __forceinline__ uint2 swap16<uint2>(uint2 p, int be)
+{
+	return be ? make_uint2(__byte_perm(p.x, 0, 0x2301), __byte_perm(p.y, 0, 0x2301)) : p;
+}
+template<> __device__ __forceinline__ uint32_t swap16<uint32_t>(uint32_t p, int) // 8-bit samples
+{
+	return p;
+}
+template<typename T> static __device__ __forceinline__ T swap1(T s, int be)
+{
+	return sizeof(T) == 2 && be ? (T)(((uint32_t)s >> 8) | ((uint32_t)s << 8)) : s;
+}
+
 static __device__ __forceinline__ int elem(const int4& v, int i)
 {
 	return i == 0 ? v.x : i == 1 ? v.y : i == 2 ? v.z : v.w;
@@ -97,21 +113,24 @@ __global__ void __launch_bounds__(256) samples_kernel(const SampleArgs a)
 			{
 				const int4 v = *p;
 				if(whole)
-					*reinterpret_cast<V*>(q) = Vec4<T>::pack(v);
+					*reinterpret_cast<V*>(q) = swap16<V>(Vec4<T>::pack(v), a.be);
 				else
 					for(uint32_t i = 0; i < 4 && x + i < a.W; ++i)
-						q[i] = (T)elem(v, (int)i);
+						q[i] = swap1<T>((T)elem(v, (int)i), a.be);
 			}
 			else
 			{
 				int4 v = make_int4(0, 0, 0, 0);
 				if(whole)
-					v = Vec4<T>::unpack(*reinterpret_cast<const V*>(q), a.sgnd);
+					v = Vec4<T>::unpack(swap16<V>(*reinterpret_cast<const V*>(q), a.be), a.sgnd);
 				else
 				{
 					int t[4] = {0, 0, 0, 0};
 					for(uint32_t i = 0; i < 4 && x + i < a.W; ++i)
-						t[i] = a.sgnd ? (int)(typename std::make_signed<T>::type)q[i] : (int)q[i];
+					{
+						const T sv = swap1<T>(q[i], a.be);
+						t[i] = a.sgnd ? (int)(typename std::make_signed<T>::type)sv : (int)sv;
+					}
 					v = make_int4(t[0], t[1], t[2], t[3]);
 				}
 				*p = v;
@@ -129,7 +148,7 @@ __global__ void __launch_bounds__(256) samples_kernel(const SampleArgs a)
 				const int4 v =
 					*reinterpret_cast<const int4*>(reinterpret_cast<const int32_t*>(a.planes[c]) + (size_t)y * a.stride + x);
 				for(uint32_t i = 0; i < n; ++i)
-					q[i * a.numcomps + c] = (T)elem(v, (int)i);
+					q[i * a.numcomps + c] = swap1<T>((T)elem(v, (int)i), a.be);
 			}
 		}
 		else
@@ -139,7 +158,7 @@ __global__ void __launch_bounds__(256) samples_kernel(const SampleArgs a)
 				int t[4] = {0, 0, 0, 0};
 				for(uint32_t i = 0; i < n; ++i)
 				{
-					const T s = q[i * a.numcomps + c];
+					const T s = swap1<T>(q[i * a.numcomps + c], a.be);
 					t[i] = a.sgnd ? (int)(typename std::make_signed<T>::type)s : (int)s;
 				}
 				*reinterpret_cast<int4*>(reinterpret_cast<int32_t*>(a.planes[c]) + (size_t)y * a.stride + x) =
@@ -153,7 +172,7 @@ template<bool PACK>
 int launch(const SampleArgs& a, uint32_t format, cudaStream_t s)
 {
 	const dim3 grid(((a.W + 3) / 4 + 255) / 256, a.H);
-	switch(format)
+	switch(format & ~(uint32_t)GRKB_SAMPLES_BIG_ENDIAN)
 	{
 		case GRKB_SAMPLES_16:
 			samples_kernel<uint16_t, false, PACK><<<grid, 256, 0, s>>>(a);
@@ -178,7 +197,10 @@ int launch(const SampleArgs& a, uint32_t format, cudaStream_t s)
 
 size_t grkb_samples_min_row_bytes(uint32_t format, uint32_t W, uint32_t numcomps)
 {
-	switch(format)
+	if((format & GRKB_SAMPLES_BIG_ENDIAN) && (format & ~(uint32_t)GRKB_SAMPLES_BIG_ENDIAN) != GRKB_SAMPLES_16 &&
+	   (format & ~(uint32_t)GRKB_SAMPLES_BIG_ENDIAN) != GRKB_SAMPLES_16_INTERLEAVED)
+		return 0; // byte order only means something for 16-bit samples
+	switch(format & ~(uint32_t)GRKB_SAMPLES_BIG_ENDIAN)
 	{
 		case GRKB_SAMPLES_16:
 			return (size_t)W * 2;
@@ -195,6 +217,7 @@ size_t grkb_samples_min_row_bytes(uint32_t format, uint32_t W, uint32_t numcomps
 
 size_t grkb_samples_bytes(uint32_t format, uint32_t H, uint32_t numcomps, size_t row_bytes)
 {
+	format &= ~(uint32_t)GRKB_SAMPLES_BIG_ENDIAN;
 	const bool planar = format == GRKB_SAMPLES_16 || format == GRKB_SAMPLES_8;
 	return row_bytes * H * (planar ? numcomps : 1);
 }
@@ -233,6 +256,7 @@ int grkb_launch_pack_samples(void* const* planes, uint32_t numcomps, uint32_t st
 	a.row_bytes = row_bytes;
 	a.plane_bytes = row_bytes * H;
 	a.vec_ok = !((row_bytes | a.plane_bytes | (uintptr_t)packed) & 7);
+	a.be = (format & GRKB_SAMPLES_BIG_ENDIAN) != 0;
 	return launch<true>(a, format, s);
 }
 
@@ -255,5 +279,6 @@ int grkb_launch_unpack_samples(const void* packed, size_t row_bytes, uint32_t fo
 	a.plane_bytes = row_bytes * H;
 	a.sgnd = sgnd;
 	a.vec_ok = !((row_bytes | a.plane_bytes | (uintptr_t)packed) & 7);
+	a.be = (format & GRKB_SAMPLES_BIG_ENDIAN) != 0;
 	return launch<false>(a, format, s);
 }

@@ -411,9 +411,10 @@ int grkb_decoder_submit_packed(grkb_decoder* d, const grkb_cblk* blocks, uint32_
 		grkb_set_error("grkb_decoder_submit_packed: null argument");
 		return -1;
 	}
-	const uint32_t width = (format == GRKB_SAMPLES_16 || format == GRKB_SAMPLES_16_INTERLEAVED) ? 16
-						   : (format == GRKB_SAMPLES_8 || format == GRKB_SAMPLES_8_INTERLEAVED) ? 8
-																								  : 0;
+	const uint32_t base = format & ~(uint32_t)GRKB_SAMPLES_BIG_ENDIAN;
+	const uint32_t width = (base == GRKB_SAMPLES_16 || base == GRKB_SAMPLES_16_INTERLEAVED) ? 16
+						   : (base == GRKB_SAMPLES_8 || base == GRKB_SAMPLES_8_INTERLEAVED)   ? 8
+																							   : 0;
 	if(width == 0 || row_bytes < grkb_samples_min_row_bytes(format, d->W, d->p.numcomps))
 	{
 		grkb_set_error("grkb_decoder_submit_packed: bad format %u or rows of %zu bytes", format, row_bytes);

@@ -17,11 +17,13 @@
 #include "../../include/grk_b200.h"
 
 #include <atomic>
+#include <chrono>
 #include <algorithm>
 #include <dirent.h>
 #include <dlfcn.h>
 #include <link.h>
 #include <memory>
+#include <mutex>
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
@@ -39,7 +41,19 @@ int g_device = 0; // -1: all devices, frames round-robin
 int g_ndev = 0;
 std::atomic<bool> g_stop{false};
 std::atomic<bool> g_batch_done{true};
-std::thread g_batch_thread;
+// joined when the library goes away (a host that never calls the plugin's exit function would
+// otherwise end in std::terminate on a finished but unjoined thread)
+struct BatchThread : std::thread
+{
+	using std::thread::operator=;
+	~BatchThread()
+	{
+		g_stop = true;
+		if(joinable())
+			join();
+	}
+};
+BatchThread g_batch_thread;
 
 void logf(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
 void logf(const char* fmt, ...)
@@ -263,14 +277,40 @@ bool build_tree(const TileGeom& g, bool decode, TileTree& t)
 }
 
 // ---- input images for plugin-driven encode: binary PNM (P5/P6, 8/16 bit) and raw ---------------
+// page-locked host memory that only grows (kept by a batch worker from frame to frame)
+struct PinnedBuf
+{
+	uint8_t* p = nullptr;
+	size_t cap = 0;
+	bool reserve(size_t n)
+	{
+		if(n <= cap)
+			return true;
+		if(p)
+			grkb_host_free(p);
+		p = (uint8_t*)grkb_host_alloc(n);
+		cap = p ? n : 0;
+		return p != nullptr;
+	}
+	~PinnedBuf()
+	{
+		if(p)
+			grkb_host_free(p);
+	}
+};
+
 struct HostImage
 {
 	uint32_t w = 0, h = 0, numcomps = 0, prec = 0;
 	bool sgnd = false;
-	std::vector<std::vector<int32_t>> planes;
+	std::vector<std::vector<int32_t>> planes; // raw input: one int32 plane per component
+	// PNM input: the file's samples as they are (pixel-interleaved, 1 or 2 bytes, big-endian),
+	// widened on the device (grkb_encoder_submit_packed) instead of here
+	const uint8_t* packed = nullptr;
+	uint32_t packed_bps = 0;
 };
 
-bool read_pnm(FILE* f, HostImage& im)
+bool read_pnm(FILE* f, HostImage& im, PinnedBuf& keep)
 {
 	char magic[3] = {0, 0, 0};
 	unsigned w = 0, h = 0, maxv = 0;
@@ -304,16 +344,10 @@ bool read_pnm(FILE* f, HostImage& im)
 	while((1u << im.prec) <= maxv)
 		++im.prec;
 	const size_t bps = maxv > 255 ? 2 : 1, n = (size_t)w * h * im.numcomps;
-	std::vector<uint8_t> raw(n * bps);
-	if(fread(raw.data(), 1, raw.size(), f) != raw.size())
+	if(!keep.reserve(n * bps + 16) || fread(keep.p, 1, n * bps, f) != n * bps)
 		return false;
-	im.planes.assign(im.numcomps, std::vector<int32_t>((size_t)w * h));
-	for(size_t i = 0; i < (size_t)w * h; ++i)
-		for(uint32_t c = 0; c < im.numcomps; ++c)
-		{
-			const size_t k = i * im.numcomps + c;
-			im.planes[c][i] = bps == 2 ? (int32_t)((raw[2 * k] << 8) | raw[2 * k + 1]) : raw[k];
-		}
+	im.packed = keep.p;
+	im.packed_bps = (uint32_t)bps;
 	return true;
 }
 
@@ -351,7 +385,7 @@ bool read_raw(FILE* f, const grk_raw_cparameters& rc, bool little, HostImage& im
 	return true;
 }
 
-bool read_image(const grk_cparameters* p, const char* path, HostImage& im)
+bool read_image(const grk_cparameters* p, const char* path, HostImage& im, PinnedBuf& keep)
 {
 	FILE* f = fopen(path, "rb");
 	if(!f)
@@ -360,7 +394,7 @@ bool read_image(const grk_cparameters* p, const char* path, HostImage& im)
 	if(p->decod_format == GRK_RAW_FMT || p->decod_format == GRK_RAWL_FMT)
 		ok = read_raw(f, p->raw_cp, p->decod_format == GRK_RAWL_FMT, im);
 	else
-		ok = read_pnm(f, im);
+		ok = read_pnm(f, im, keep);
 	fclose(f);
 	return ok;
 }
@@ -372,11 +406,78 @@ struct EncodeJob
 	bool out_relative = false;
 };
 
-int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
-			   grk::PLUGIN_ENCODE_USER_CALLBACK cb)
+// What a batch worker keeps from frame to frame: the device encoder (planes, pools and a stream
+// of its own, so the copies of one worker's frame overlap the kernels of another's) and the
+// page-locked buffers its results land in.
+struct EncodeCtx
 {
+	grkb_encoder* enc = nullptr;
+	grkb_tile_params tp{};
+	int device = -1;
+	uint8_t* bytes = nullptr; // grkb_host_alloc
+	size_t bytes_cap = 0;
+	grkb_coded* coded = nullptr; // grkb_host_alloc
+	grkb_pass* passes = nullptr;
+	size_t blocks_cap = 0;
+	PinnedBuf raw; // the frame's file samples
+	// tile tree and block table of the last frame, reused while the geometry stays the same
+	std::unique_ptr<TileTree> tree;
+	std::vector<grkb_enc_cblk> blocks;
+	std::vector<float> band_step;
+	TileGeom tg{};
+	uint32_t t_prec = 0, t_numgbits = 0;
+	bool t_reversible = false, t_ht = false;
+	~EncodeCtx()
+	{
+		if(enc)
+			grkb_encoder_destroy(enc);
+		if(bytes)
+			grkb_host_free(bytes);
+		if(coded)
+			grkb_host_free(coded);
+		if(passes)
+			grkb_host_free(passes);
+	}
+	bool reserve(size_t nblocks, size_t nbytes)
+	{
+		if(nbytes > bytes_cap)
+		{
+			if(bytes)
+				grkb_host_free(bytes);
+			bytes = (uint8_t*)grkb_host_alloc(nbytes);
+			bytes_cap = bytes ? nbytes : 0;
+		}
+		if(nblocks > blocks_cap)
+		{
+			if(coded)
+				grkb_host_free(coded);
+			if(passes)
+				grkb_host_free(passes);
+			coded = (grkb_coded*)grkb_host_alloc(nblocks * sizeof(grkb_coded));
+			passes = (grkb_pass*)grkb_host_alloc(nblocks * GRKB_ENC_MAX_PASSES * sizeof(grkb_pass));
+			blocks_cap = coded && passes ? nblocks : 0;
+		}
+		return bytes_cap >= nbytes && blocks_cap >= nblocks;
+	}
+};
+
+std::mutex g_cb_mutex; // GRKB_BATCH_SERIAL_CALLBACK=1: one host callback at a time
+// The batch workers' contexts outlive a batch (creating a device encoder and page-locking its
+// buffers costs as much as several frames).  Heap-allocated and released in exit_func only: no
+// CUDA call is left to the static destructors.
+std::vector<std::unique_ptr<EncodeCtx>>* g_ctx_pool = new std::vector<std::unique_ptr<EncodeCtx>>();
+
+int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
+			   grk::PLUGIN_ENCODE_USER_CALLBACK cb, EncodeCtx* ctx = nullptr, bool serial_cb = false)
+{
+	EncodeCtx local;
+	if(!ctx)
+		ctx = &local;
+	using clk = std::chrono::steady_clock;
+	const auto t_start = clk::now();
+	auto ms_since = [](clk::time_point a) { return std::chrono::duration<double, std::milli>(clk::now() - a).count(); };
 	HostImage im;
-	if(!read_image(params, job.in.c_str(), im))
+	if(!read_image(params, job.in.c_str(), im, ctx->raw))
 	{
 		logf("cannot read %s (binary PNM and raw input are supported)", job.in.c_str());
 		return -1;
@@ -450,47 +551,69 @@ int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
 			g.ph[r] = ph < 1 ? 1 : flog2(ph);
 		}
 	}
-	auto tree = std::make_unique<TileTree>();
-	if(!build_tree(g, false, *tree))
-		return -1;
-	// block table: quantisation parameters as the host will signal them in QCD
-	const uint32_t nb = 3 * numres - 2;
-	std::vector<uint32_t> expn(nb), mant(nb);
-	if(grkb_qcd_generate(numres, im.prec, reversible, ht, expn.data(), mant.data()))
-	{
-		logf("%s", grkb_last_error());
-		return -1;
-	}
+	const double ms_read = ms_since(t_start);
 	const uint32_t numgbits = params->numgbits;
-	const size_t ng = tree->geom.size(), n = ng * im.numcomps;
-	std::vector<grkb_enc_cblk> blocks(n);
-	std::vector<float> band_step(ng);
-	for(size_t i = 0; i < ng; ++i)
+	const bool cached = ctx->tree && memcmp(&ctx->tg, &g, sizeof(g)) == 0 && ctx->t_prec == im.prec &&
+						ctx->t_numgbits == numgbits && ctx->t_reversible == reversible && ctx->t_ht == ht;
+	if(!cached)
 	{
-		const grkb_cblk_geom& q = tree->geom[i];
-		float step = 1.0f;
-		uint32_t bps = 0;
-		const uint32_t qi = (q.res == 0 ? 0 : 3 * q.res - 2) + q.band;
-		if(grkb_band_quant(expn[qi], mant[qi], q.orient, im.prec, reversible, 1, ht, numgbits, 0, &step,
-						   &bps))
-			return -1;
-		band_step[i] = step;
-		for(uint32_t c = 0; c < im.numcomps; ++c)
+		ctx->tree = std::make_unique<TileTree>();
+		if(!build_tree(g, false, *ctx->tree))
 		{
-			grkb_enc_cblk& b = blocks[c * ng + i];
-			memset(&b, 0, sizeof(b));
-			b.x = q.x;
-			b.y = q.y;
-			b.w = q.w;
-			b.h = q.h;
-			b.comp = (uint8_t)c;
-			b.orient = q.orient;
-			b.level = q.level;
-			b.cblk_sty = ht ? GRKB_CBLKSTY_HT : 0;
-			b.k_msbs = (uint8_t)bps;
-			b.stepsize = step;
+			ctx->tree.reset();
+			return -1;
 		}
+		// block table: quantisation parameters as the host will signal them in QCD
+		const uint32_t nb = 3 * numres - 2;
+		std::vector<uint32_t> expn(nb), mant(nb);
+		if(grkb_qcd_generate(numres, im.prec, reversible, ht, expn.data(), mant.data()))
+		{
+			logf("%s", grkb_last_error());
+			ctx->tree.reset();
+			return -1;
+		}
+		const size_t ng0 = ctx->tree->geom.size();
+		ctx->blocks.assign(ng0 * im.numcomps, grkb_enc_cblk{});
+		ctx->band_step.assign(ng0, 1.0f);
+		for(size_t i = 0; i < ng0; ++i)
+		{
+			const grkb_cblk_geom& q = ctx->tree->geom[i];
+			float step = 1.0f;
+			uint32_t bps = 0;
+			const uint32_t qi = (q.res == 0 ? 0 : 3 * q.res - 2) + q.band;
+			if(grkb_band_quant(expn[qi], mant[qi], q.orient, im.prec, reversible, 1, ht, numgbits, 0, &step,
+							   &bps))
+			{
+				ctx->tree.reset();
+				return -1;
+			}
+			ctx->band_step[i] = step;
+			for(uint32_t c = 0; c < im.numcomps; ++c)
+			{
+				grkb_enc_cblk& b = ctx->blocks[c * ng0 + i];
+				memset(&b, 0, sizeof(b));
+				b.x = q.x;
+				b.y = q.y;
+				b.w = q.w;
+				b.h = q.h;
+				b.comp = (uint8_t)c;
+				b.orient = q.orient;
+				b.level = q.level;
+				b.cblk_sty = ht ? GRKB_CBLKSTY_HT : 0;
+				b.k_msbs = (uint8_t)bps;
+				b.stepsize = step;
+			}
+		}
+		ctx->tg = g;
+		ctx->t_prec = im.prec;
+		ctx->t_numgbits = numgbits;
+		ctx->t_reversible = reversible;
+		ctx->t_ht = ht;
 	}
+	TileTree* tree = ctx->tree.get();
+	const std::vector<grkb_enc_cblk>& blocks = ctx->blocks;
+	const std::vector<float>& band_step = ctx->band_step;
+	const size_t ng = tree->geom.size(), n = ng * im.numcomps;
 	grkb_tile_params tp{};
 	tp.x0 = g.x0;
 	tp.y0 = g.y0;
@@ -502,33 +625,65 @@ int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
 	tp.mct = mct;
 	for(uint32_t c = 0; c < im.numcomps; ++c)
 		tp.shift[c] = im.sgnd ? 0 : 1 << (im.prec - 1);
-	grkb_encoder* enc = nullptr;
-	if(grkb_encoder_create(&tp, &enc))
+	if(ctx->enc && (ctx->device != device || memcmp(&ctx->tp, &tp, sizeof(tp)) != 0))
 	{
-		logf("%s", grkb_last_error());
+		grkb_encoder_destroy(ctx->enc);
+		ctx->enc = nullptr;
+	}
+	if(!ctx->enc)
+	{
+		if(grkb_encoder_create(&tp, &ctx->enc))
+		{
+			ctx->enc = nullptr;
+			logf("%s", grkb_last_error());
+			return -1;
+		}
+		ctx->tp = tp;
+		ctx->device = device;
+	}
+	grkb_encoder* enc = ctx->enc;
+	const size_t bytes_cap = (size_t)im.w * im.h * im.numcomps * 4 + 65536;
+	if(!ctx->reserve(n, bytes_cap))
+	{
+		logf("cannot allocate page-locked result buffers");
 		return -1;
 	}
-	std::vector<grkb_coded> coded(n);
-	std::vector<grkb_pass> passes(n * GRKB_ENC_MAX_PASSES);
-	std::vector<uint8_t> bytes((size_t)im.w * im.h * im.numcomps * 4 + 65536);
-	std::vector<const int32_t*> planes(im.numcomps);
-	for(uint32_t c = 0; c < im.numcomps; ++c)
-		planes[c] = im.planes[c].data();
+	grkb_coded* coded = ctx->coded;
+	grkb_pass* passes = ctx->passes;
+	uint8_t* bytes = ctx->bytes;
 	// the host runs rate control whenever a rate or quality target is set
 	const bool rc = (params->allocationByRateDistoration && params->layer_rate[0] != 0) ||
 					params->allocationByQuality || params->numlayers > 1;
 	static const double norms_rev[3] = {1.732, .8292, .8292}, norms_irrev[3] = {1.732, 1.805, 1.573};
+	const double* norms = mct ? (reversible ? norms_rev : norms_irrev) : nullptr;
 	size_t used = 0;
-	int err = grkb_encoder_encode(enc, planes.data(), im.w, blocks.data(), (uint32_t)n,
-								  mct ? (reversible ? norms_rev : norms_irrev) : nullptr, mct ? 3 : 0,
-								  rc ? 1 : 0, coded.data(), passes.data(), bytes.data(), bytes.size(),
-								  &used);
-	grkb_encoder_destroy(enc);
+	const double ms_prep = ms_since(t_start);
+	int err;
+	if(im.packed)
+	{
+		// PNM samples go to the device as the file holds them
+		const uint32_t fmt = im.packed_bps == 2 ? (GRKB_SAMPLES_16_INTERLEAVED | GRKB_SAMPLES_BIG_ENDIAN)
+												: GRKB_SAMPLES_8_INTERLEAVED;
+		err = grkb_encoder_submit_packed(enc, im.packed, fmt, 0, (size_t)im.w * im.numcomps * im.packed_bps,
+										 blocks.data(), (uint32_t)n, norms, mct ? 3 : 0, rc ? 1 : 0, coded, passes,
+										 bytes, bytes_cap);
+		if(!err)
+			err = grkb_encoder_wait(enc, &used);
+	}
+	else
+	{
+		std::vector<const int32_t*> planes(im.numcomps);
+		for(uint32_t c = 0; c < im.numcomps; ++c)
+			planes[c] = im.planes[c].data();
+		err = grkb_encoder_encode(enc, planes.data(), im.w, blocks.data(), (uint32_t)n, norms, mct ? 3 : 0,
+								  rc ? 1 : 0, coded, passes, bytes, bytes_cap, &used);
+	}
 	if(err)
 	{
 		logf("%s", grkb_last_error());
 		return -1;
 	}
+	const double ms_gpu = ms_since(t_start);
 	// fill the tree the way compress_synch_with_plugin reads it (plugin_bridge.cpp:146-272)
 	for(size_t i = 0; i < n; ++i)
 	{
@@ -537,7 +692,7 @@ int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
 		if(c.failed || c.numpasses > 67)
 			return -1;
 		tree->flat_band[i]->stepsize = band_step[i % ng];
-		k.compressedData = bytes.data() + c.data_off;
+		k.compressedData = bytes + c.data_off;
 		k.compressedDataLength = c.data_len;
 		k.numBitPlanes = c.numbps;
 		k.numPasses = c.numpasses;
@@ -573,12 +728,37 @@ int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
 			image->y0 = g.y0;
 			image->x1 = g.x1;
 			image->y1 = g.y1;
-			for(uint32_t c = 0; c < im.numcomps; ++c)
+			if(im.packed)
+			{
+				// de-interleave the file's samples into the host's int32 planes (what the host's own
+				// PNM reader does, src/bin/image_format/PNMFormat.cpp)
+				const uint32_t nc = im.numcomps;
 				for(uint32_t y = 0; y < im.h; ++y)
-					memcpy(image->comps[c].data + (size_t)y * image->comps[c].stride,
-						   im.planes[c].data() + (size_t)y * im.w, sizeof(int32_t) * im.w);
+				{
+					const uint8_t* src = im.packed + (size_t)y * im.w * nc * im.packed_bps;
+					for(uint32_t c = 0; c < nc; ++c)
+					{
+						int32_t* dst = image->comps[c].data + (size_t)y * image->comps[c].stride;
+						if(im.packed_bps == 2)
+							for(uint32_t x = 0; x < im.w; ++x)
+							{
+								const uint8_t* q = src + ((size_t)x * nc + c) * 2;
+								dst[x] = (int32_t)((q[0] << 8) | q[1]);
+							}
+						else
+							for(uint32_t x = 0; x < im.w; ++x)
+								dst[x] = src[(size_t)x * nc + c];
+					}
+				}
+			}
+			else
+				for(uint32_t c = 0; c < im.numcomps; ++c)
+					for(uint32_t y = 0; y < im.h; ++y)
+						memcpy(image->comps[c].data + (size_t)y * image->comps[c].stride,
+							   im.planes[c].data() + (size_t)y * im.w, sizeof(int32_t) * im.w);
 		}
 	}
+	const double ms_fill = ms_since(t_start);
 	grk::plugin_encode_user_callback_info info;
 	memset(&info, 0, sizeof(info));
 	info.input_file_name = job.in.c_str();
@@ -588,7 +768,16 @@ int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
 	info.image = image;
 	info.tile = &tree->tile;
 	info.error_code = 0;
-	cb(&info); // synchronous: everything it reads stays alive until it returns
+	// synchronous: everything it reads stays alive until it returns
+	if(serial_cb)
+	{
+		std::lock_guard<std::mutex> lk(g_cb_mutex);
+		cb(&info);
+	}
+	else
+		cb(&info);
+	logf("%s: read %.1f ms, tables %.1f, device encode %.1f, tree + host image %.1f, host callback %.1f",
+		 job.in.c_str(), ms_read, ms_prep - ms_read, ms_gpu - ms_prep, ms_fill - ms_gpu, ms_since(t_start) - ms_fill);
 	if(image && host_unref())
 		host_unref()(&image->obj);
 	return info.error_code ? -1 : 0;
@@ -926,6 +1115,7 @@ PLUGIN_EXPORT int32_t destroy(void*)
 PLUGIN_EXPORT int32_t exit_func()
 {
 	join_batch();
+	g_ctx_pool->clear();
 	return 0;
 }
 PLUGIN_EXPORT grk::minpf_exit_func minpf_post_load_plugin(const char*,
@@ -987,17 +1177,50 @@ PLUGIN_EXPORT int32_t plugin_batch_encode(const char* input_dir, const char* out
 	const std::string in = input_dir, out = output_dir;
 	const grk_cparameters copy = *params;
 	g_batch_done = false;
+	// Frames are independent: a pool of workers takes them in directory order, each with a device
+	// encoder of its own, so the H2D of one frame, the kernels of another and the host's rate
+	// allocation + T2 + file write (the callback) of a third run at the same time.  The host's
+	// callback works on its own codec and stream per call (grk_compress.cpp:1742-2160).
 	g_batch_thread = std::thread([in, out, copy, cb]() {
 		const char* ext = copy.cod_format == GRK_JP2_FMT ? "jp2" : "j2k";
-		for(const std::string& name : list_dir(in.c_str()))
-		{
-			if(g_stop)
-				break;
-			EncodeJob job;
-			job.in = in + "/" + name;
-			job.out = out + "/" + replace_ext(name, ext);
-			encode_one(&copy, job, next_device(), cb);
-		}
+		const std::vector<std::string> names = list_dir(in.c_str());
+		// the host's callback (rate allocation + T2 + file write, ~150 ms per DCI-4K frame on one
+		// core) bounds the batch: one worker per core, 16 at most (each holds a device encoder)
+		unsigned nthreads = std::max(2u, std::min(16u, std::thread::hardware_concurrency()));
+		if(const char* v = getenv("GRKB_BATCH_THREADS"))
+			nthreads = std::max(1, atoi(v));
+		nthreads = (unsigned)std::min<size_t>(nthreads, std::max<size_t>(names.size(), 1));
+		const char* sv = getenv("GRKB_BATCH_SERIAL_CALLBACK");
+		const bool serial_cb = sv && *sv && *sv != '0';
+		std::atomic<size_t> next{0};
+		std::atomic<uint32_t> failed{0};
+		while(g_ctx_pool->size() < nthreads)
+			g_ctx_pool->emplace_back(new EncodeCtx());
+		auto worker = [&](unsigned slot) {
+			EncodeCtx& ctx = *(*g_ctx_pool)[slot];
+			for(;;)
+			{
+				const size_t i = next++;
+				if(i >= names.size() || g_stop)
+					break;
+				grk_cparameters p = copy; // the callback may write to its parameters
+				EncodeJob job;
+				job.in = in + "/" + names[i];
+				job.out = out + "/" + replace_ext(names[i], ext);
+				strncpy(p.infile, job.in.c_str(), sizeof(p.infile) - 1);
+				strncpy(p.outfile, job.out.c_str(), sizeof(p.outfile) - 1);
+				if(encode_one(&p, job, next_device(), cb, &ctx, serial_cb))
+					failed++;
+			}
+		};
+		std::vector<std::thread> pool;
+		for(unsigned t = 1; t < nthreads; ++t)
+			pool.emplace_back(worker, t);
+		worker(0);
+		for(auto& t : pool)
+			t.join();
+		if(failed)
+			logf("batch encode: %u of %zu frames failed", failed.load(), names.size());
 		g_batch_done = true;
 	});
 	return 0;

@@ -73,6 +73,7 @@ class PinnedArray:
 
 
 SAMPLES_32, SAMPLES_16, SAMPLES_16_INTERLEAVED, SAMPLES_8, SAMPLES_8_INTERLEAVED = range(5)
+SAMPLES_BIG_ENDIAN = 0x10
 
 
 def sample_format(a, interleaved, numcomps, H):
@@ -92,6 +93,8 @@ def sample_format(a, interleaved, numcomps, H):
     wide = a.dtype.itemsize == 2
     fmt = (SAMPLES_16_INTERLEAVED if interleaved else SAMPLES_16) if wide else \
         (SAMPLES_8_INTERLEAVED if interleaved else SAMPLES_8)
+    if wide and a.dtype.byteorder == ">":
+        fmt |= SAMPLES_BIG_ENDIAN  # as PNM files store them
     return fmt, row
 
 

@@ -230,7 +230,8 @@ enum
 	GRKB_SAMPLES_16 = 1,
 	GRKB_SAMPLES_16_INTERLEAVED = 2,
 	GRKB_SAMPLES_8 = 3,
-	GRKB_SAMPLES_8_INTERLEAVED = 4
+	GRKB_SAMPLES_8_INTERLEAVED = 4,
+	GRKB_SAMPLES_BIG_ENDIAN = 0x10 /* OR-ed to a 16-bit format: samples as PNM files store them */
 };
 /* grkb_decoder_submit with the result narrowed on the device: `out` receives
  * grkb_samples_size(format, ...) bytes.  Precision above the format's width is refused. */

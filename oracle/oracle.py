@@ -334,6 +334,17 @@ def ref_plugin_encode(pnm_path, w, h, ncomp, irreversible, ht=False, numres=6, c
     return out[:n].copy()
 
 
+def ref_plugin_batch_encode(in_dir, out_dir, irreversible, ht=False, numres=6, cblk=(64, 64), threads=0):
+    """grk_plugin_batch_compress over a directory of binary PNM frames: stock host callback (rate
+    allocation, T2, file write) + our plugin; returns the number of frames written"""
+    fn = ref().ref_plugin_batch_encode
+    n = fn(in_dir.encode(), out_dir.encode(), C.c_int(int(irreversible)), C.c_int(int(ht)),
+           C.c_uint32(numres), C.c_uint32(cblk[0]), C.c_uint32(cblk[1]), C.c_uint32(threads))
+    if n < 0:
+        raise RuntimeError("plugin-driven batch encode failed (%d)" % n)
+    return n
+
+
 def ref_plugin_decode(j2k_path, ncomp, w, h):
     """stock host (markers, T2) + our plugin (T1, dequantisation, wavelet, MCT)"""
     planes = [np.zeros((h, w), dtype=np.int32) for _ in range(ncomp)]

@@ -15,6 +15,9 @@
 #include "T1.h"
 #include "WaveletFwd.h"
 #include "mct.h"
+#include <atomic>
+#include <chrono>
+#include <thread>
 
 /* zeroed raw storage (the reference poisons malloc/calloc/free) */
 template<typename T>
@@ -653,6 +656,66 @@ long ref_plugin_encode(const char* infile, int irreversible, int ht, uint32_t nu
 	if(grk_plugin_compress(&p, Fix::cb) != 0)
 		return g_enc_len >= 0 ? g_enc_len : -11;
 	return g_enc_len;
+}
+
+/* The batch door, as grk_compress drives it (src/bin/jp2/grk_compress.cpp:2216-2240): every
+ * binary PNM of input_dir goes through the plugin and comes back to this callback, possibly on
+ * several threads at once, which runs the stock rate allocation + T2 into output_file_name.
+ * Returns the number of frames the callback completed, or < 0. */
+static std::atomic<int> g_batch_ok{0}, g_batch_bad{0};
+static bool plugin_batch_cb(grk_plugin_compress_user_callback_info* info)
+{
+	bool ok = false;
+	if(info && info->image && info->tile && info->output_file_name)
+	{
+		if(info->compressor_parameters->mct == 255)
+			info->compressor_parameters->mct = info->image->numcomps >= 3 ? 1 : 0;
+		auto stream = grk_stream_create_file_stream(info->output_file_name, 1 << 20, false);
+		auto codec = stream ? grk_compress_create(GRK_CODEC_J2K, stream) : nullptr;
+		ok = codec && grk_compress_init(codec, info->compressor_parameters, info->image) &&
+			 grk_compress_start(codec) && grk_compress_with_plugin(codec, info->tile) &&
+			 grk_compress_end(codec);
+		if(codec)
+			grk_object_unref(codec);
+		if(stream)
+			grk_object_unref(stream);
+	}
+	(ok ? g_batch_ok : g_batch_bad)++;
+	return ok;
+}
+
+int ref_plugin_batch_encode(const char* input_dir, const char* output_dir, int irreversible, int ht,
+							uint32_t numres, uint32_t cblkw, uint32_t cblkh, uint32_t numthreads)
+{
+	if(!g_plugin_ready)
+		return -10;
+	grk_cparameters p;
+	grk_compress_set_default_params(&p);
+	p.cod_format = GRK_J2K_FMT;
+	p.decod_format = GRK_PXM_FMT;
+	p.numresolution = (uint8_t)numres;
+	p.cblockw_init = cblkw;
+	p.cblockh_init = cblkh;
+	p.irreversible = irreversible != 0;
+	p.layer_rate[0] = g_layer_rate;
+	p.numlayers = 1;
+	p.allocationByRateDistoration = true;
+	p.mct = 255;
+	p.numThreads = numthreads;
+	if(ht)
+	{
+		p.isHT = true;
+		p.numgbits = 1;
+		p.cblk_sty = GRK_CBLKSTY_HT;
+	}
+	g_batch_ok = 0;
+	g_batch_bad = 0;
+	if(grk_plugin_batch_compress(input_dir, output_dir, &p, plugin_batch_cb) != 0)
+		return -11;
+	while(!grk_plugin_is_batch_complete())
+		std::this_thread::sleep_for(std::chrono::milliseconds(2));
+	grk_plugin_stop_batch_compress();
+	return g_batch_bad ? -100 - g_batch_bad.load() : g_batch_ok.load();
 }
 
 static int32_t** g_dec_planes = nullptr;

@@ -81,3 +81,31 @@ def test_plugin_decode_identical_samples(host, tmp_path, w, h, ncomp, prec, nr, 
         assert np.array_equal(got[c], want[c])
         if not irr:
             assert np.array_equal(got[c], img[c])
+
+
+@pytest.mark.parametrize("w,h,ncomp,prec,nr,irr,ht,ratio", [
+    (320, 200, 3, 12, 6, 0, 1, 1.0),    # HTJ2K lossless
+    (320, 200, 3, 12, 6, 1, 0, 8.0),    # 9/7 + ICT, rate controlled (BASELINE configs[5] in small)
+])
+def test_plugin_batch_encode_byte_identical(host, tmp_path, w, h, ncomp, prec, nr, irr, ht, ratio):
+    """grk_plugin_batch_compress: a directory of frames through the plugin's worker pool (several
+    device encoders in flight, host callbacks on several threads) -> every output file equals the
+    stock CPU encoder's codestream for that frame."""
+    indir, outdir = tmp_path / "in", tmp_path / "out"
+    indir.mkdir()
+    outdir.mkdir()
+    frames = []
+    for f in range(9):
+        img = H.synth_image(w, h, ncomp, prec, seed=100 + f)
+        frames.append(img)
+        O.write_pnm(str(indir / ("f%03d.ppm" % f)), img, prec)
+    try:
+        O.ref_set_rate(ratio)
+        n = O.ref_plugin_batch_encode(str(indir), str(outdir), irr, ht=bool(ht), numres=nr)
+        stock = [O.ref_codec_encode(img, prec, irr, ht=bool(ht), numres=nr) for img in frames]
+    finally:
+        O.ref_set_rate(0)
+    assert n == len(frames)
+    for f in range(len(frames)):
+        got = np.fromfile(str(outdir / ("f%03d.j2k" % f)), dtype=np.uint8)
+        assert len(got) == len(stock[f]) and np.array_equal(got, stock[f]), "frame %d" % f

@@ -62,6 +62,8 @@ def _coded_tile(w, h, ncomp, prec, nr, sgnd=False):
     (128, 64, 3, 8, np.uint8, False, 0),
     (200, 64, 3, 10, np.int16, True, 0),      # signed components
     (96, 40, 4, 16, np.uint16, False, 0),     # full 16 bits, extra component
+    (256, 96, 3, 12, ">u2", False, 0),        # big-endian samples (PNM byte order), vector path
+    (250, 67, 3, 12, ">u2", False, 0),        # and the scalar path
 ])
 @pytest.mark.parametrize("interleaved", [False, True])
 def test_decode_packed_matches_oracle(gpu, orc, w, h, ncomp, prec, dtype, sgnd, pad, interleaved):
@@ -75,7 +77,8 @@ def test_decode_packed_matches_oracle(gpu, orc, w, h, ncomp, prec, dtype, sgnd, 
     dec.wait()
     dec.close()
     assert dec.rejected == 0
-    want = orc.orc_pack_samples(planes, dtype, interleaved, row_pad=pad)
+    # (a big-endian dtype only changes the byte order in memory: values compare the same)
+    want = orc.orc_pack_samples(planes, np.dtype(dtype).newbyteorder("="), interleaved, row_pad=pad)
     if interleaved:
         assert np.array_equal(out[:, :w, :], want[:, :w, :])
         assert (out[:, w:, :] == 0x55).all()  # padding untouched
@@ -90,16 +93,19 @@ def test_decode_packed_matches_oracle(gpu, orc, w, h, ncomp, prec, dtype, sgnd, 
     (250, 67, 3, 12, np.uint16, False, 2),
     (131, 50, 1, 8, np.uint8, False, 0),
     (200, 64, 3, 10, np.int16, True, 0),
+    (256, 96, 3, 12, ">u2", False, 0),
+    (250, 67, 3, 12, ">u2", False, 2),
 ])
 @pytest.mark.parametrize("interleaved", [False, True])
 def test_encode_packed_equals_encode_of_int32(gpu, orc, w, h, ncomp, prec, dtype, sgnd, pad, interleaved):
     img, params, blocks, _ = _coded_tile(w, h, ncomp, prec, 4, sgnd)
     enc = E.TileEncoder(params)
     coded, passes, data = enc.encode(img, blocks)
-    packed = orc.orc_pack_samples(img, dtype, interleaved, row_pad=pad)
+    packed = orc.orc_pack_samples(img, np.dtype(dtype).newbyteorder("="), interleaved, row_pad=pad)
     # widening is the oracle's too
     for a, b in zip(orc.orc_unpack_samples(packed, w, interleaved), img):
         assert np.array_equal(a, b)
+    packed = packed.astype(dtype)  # same values, the byte order under test
     n = len(blocks)
     out = (np.zeros(n, T.CODED_DTYPE), np.zeros((n, T.ENC_MAX_PASSES), T.PASS_DTYPE),
            np.zeros(w * h * ncomp * 4 + 4096, np.uint8))

@@ -348,21 +348,85 @@ def mq_encode(args):
         dist.destroy_process_group()
 
 
+def plugin_batch(args):
+    """BASELINE configs[5] as the reference drives it: grk_plugin_batch_compress over a directory
+    of DCI-4K PPM frames.  Our plugin reads the files and does everything before T2 on the GPU
+    (worker pool, one device encoder per worker); the UNMODIFIED host callback does rate
+    allocation + T2 + the file write on the host threads.  Timed wall clock, files included."""
+    import shutil
+    import tempfile
+    from oracle import oracle as O
+    W, H, prec, nr = 4096, 2160, 12, 6
+    nframes = args.frames
+    if not O.have_plugin():
+        raise SystemExit("reference host / plugin not built")
+    if args.inflight:
+        os.environ["GRKB_BATCH_THREADS"] = str(args.inflight)
+    base = synth(W + 8 * nframes, H, prec, 4096)
+    root = tempfile.mkdtemp(prefix="grkb_batch_")
+    try:
+        indir, outdir = os.path.join(root, "in"), os.path.join(root, "out")
+        os.makedirs(indir)
+        os.makedirs(outdir)
+        for f in range(nframes):
+            O.write_pnm(os.path.join(indir, "f%04d.ppm" % f), [a[:, 8 * f:8 * f + W] for a in base], prec)
+        O.ref_plugin_open(device=0, threads=args.host_threads)
+        ratio = W * H * 3 * 1.5 / 1302083.0  # cinema4K@24 frame budget
+        O.ref_set_rate(ratio)
+        try:
+            O.ref_plugin_batch_encode(indir, outdir, 1, numres=nr, cblk=(32, 32))  # warm-up
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                n = O.ref_plugin_batch_encode(indir, outdir, 1, numres=nr, cblk=(32, 32))
+                assert n == nframes
+            dt = (time.perf_counter() - t0) / args.steps
+            sizes = [os.path.getsize(os.path.join(outdir, x)) for x in sorted(os.listdir(outdir))]
+            cpu = None
+            if not args.no_cpu:
+                threads = os.cpu_count() or 1
+                frame = [a[:, :W] for a in base]
+                O.ref_codec_encode(frame, prec, 1, ht=False, numres=nr, cblk=(32, 32), threads=threads)
+                t1 = time.perf_counter()
+                cs = O.ref_codec_encode(frame, prec, 1, ht=False, numres=nr, cblk=(32, 32), threads=threads)
+                ct = time.perf_counter() - t1
+                same = np.array_equal(np.fromfile(os.path.join(outdir, "f0000.j2k"), dtype=np.uint8), cs)
+                cpu = {"value": W * H / 1e6 / ct, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
+                       "sample": "one frame: stock grk compress, memory stream, %.0f ms; plugin output of that "
+                                 "frame byte-identical: %s" % (ct * 1e3, same)}
+        finally:
+            O.ref_set_rate(0)
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
+    mp = W * H / 1e6
+    print(json.dumps({
+        "metric": "encode_mpixels_per_s", "value": mp * nframes / dt, "unit": "Mpixel/s", "n_gpus": 1,
+        "steps": args.steps, "ms_per_frame": dt * 1e3 / nframes, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "grk_plugin_batch_compress_dci4k_rgb12_97_ict_5lvl_cblk32_cinema4k_rate",
+                   "frames": nframes, "workers": os.environ.get("GRKB_BATCH_THREADS", "default"),
+                   "host_library_threads": args.host_threads or "all",
+                   "scope": "PPM read + GPU (DC shift, ICT, 9/7, quantise, EBCOT, packing) in the plugin; PCRD + T2 + "
+                            "file write in the unmodified host callback; wall clock",
+                   "bytes_per_frame": int(sum(sizes) // max(1, len(sizes)))},
+        "cpu_baseline": cpu}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["ht_encode", "tiled", "mq_encode"])
+    ap.add_argument("what", choices=["ht_encode", "tiled", "mq_encode", "plugin_batch"])
     ap.add_argument("--frames", type=int, default=8)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--inflight", type=int, default=None)
     ap.add_argument("--size", type=int, default=8192)
     ap.add_argument("--verify", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--host-threads", type=int, default=0,
+                    help="plugin_batch: threads of the reference host's own pool (0 = all cores)")
     ap.add_argument("--samples16", action="store_true",
                     help="encode benches: send the frames as uint16 planes (grkb_encoder_submit_packed)")
     args = ap.parse_args()
-    if args.inflight is None:
+    if args.inflight is None and args.what != "plugin_batch":
         args.inflight = 4 if args.what == "tiled" else 2
-    {"ht_encode": ht_encode, "tiled": tiled, "mq_encode": mq_encode}[args.what](args)
+    {"ht_encode": ht_encode, "tiled": tiled, "mq_encode": mq_encode, "plugin_batch": plugin_batch}[args.what](args)
 
 
 if __name__ == "__main__":
