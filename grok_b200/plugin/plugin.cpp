@@ -406,6 +406,69 @@ struct EncodeJob
 	bool out_relative = false;
 };
 
+// A host image kept from frame to frame by a batch worker: a fresh 100 MB image costs more in
+// page faults than everything the device does for the frame.  Reused only while the host left its
+// shape alone; every sample is overwritten each frame.
+struct CachedImage
+{
+	grk_image* image = nullptr;
+	uint32_t w = 0, h = 0, nc = 0, prec = 0, x0 = 0, y0 = 0;
+	bool sgnd = false;
+	~CachedImage()
+	{
+		drop();
+	}
+	void drop()
+	{
+		if(image && host_unref())
+			host_unref()(&image->obj);
+		image = nullptr;
+	}
+	grk_image* get(uint32_t W, uint32_t H, uint32_t numcomps, uint32_t precision, bool is_signed, uint32_t ox,
+				   uint32_t oy)
+	{
+		bool ok = image && w == W && h == H && nc == numcomps && prec == precision && sgnd == is_signed &&
+				  x0 == ox && y0 == oy && image->numcomps == numcomps && image->comps;
+		for(uint32_t c = 0; ok && c < numcomps; ++c)
+			ok = image->comps[c].data && image->comps[c].w == W && image->comps[c].h == H &&
+				 image->comps[c].stride >= W && image->comps[c].prec == precision;
+		if(ok)
+			return image;
+		drop();
+		if(!host_image_new())
+			return nullptr;
+		std::vector<grk_image_cmptparm> cp(numcomps);
+		for(auto& c : cp)
+		{
+			memset(&c, 0, sizeof(c));
+			c.prec = (uint8_t)precision;
+			c.sgnd = is_signed;
+			c.dx = c.dy = 1;
+			c.w = W;
+			c.h = H;
+			c.x0 = ox;
+			c.y0 = oy;
+		}
+		image = host_image_new()((uint16_t)numcomps, cp.data(), numcomps >= 3 ? GRK_CLRSPC_SRGB : GRK_CLRSPC_GRAY,
+								 true);
+		if(image)
+		{
+			image->x0 = ox;
+			image->y0 = oy;
+			image->x1 = ox + W;
+			image->y1 = oy + H;
+			w = W;
+			h = H;
+			nc = numcomps;
+			prec = precision;
+			sgnd = is_signed;
+			x0 = ox;
+			y0 = oy;
+		}
+		return image;
+	}
+};
+
 // What a batch worker keeps from frame to frame: the device encoder (planes, pools and a stream
 // of its own, so the copies of one worker's frame overlap the kernels of another's) and the
 // page-locked buffers its results land in.
@@ -420,6 +483,7 @@ struct EncodeCtx
 	grkb_pass* passes = nullptr;
 	size_t blocks_cap = 0;
 	PinnedBuf raw; // the frame's file samples
+	CachedImage himage; // the host-side image handed to the callback
 	// tile tree and block table of the last frame, reused while the geometry stays the same
 	std::unique_ptr<TileTree> tree;
 	std::vector<grkb_enc_cblk> blocks;
@@ -705,29 +769,10 @@ int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
 		}
 	}
 	// the image object is the host's (a C++ GrkImage behind the C struct)
-	grk_image* image = nullptr;
-	if(host_image_new())
+	grk_image* image = ctx->himage.get(im.w, im.h, im.numcomps, im.prec, im.sgnd, g.x0, g.y0);
 	{
-		std::vector<grk_image_cmptparm> cp(im.numcomps);
-		for(auto& c : cp)
-		{
-			memset(&c, 0, sizeof(c));
-			c.prec = (uint8_t)im.prec;
-			c.sgnd = im.sgnd;
-			c.dx = c.dy = 1;
-			c.w = im.w;
-			c.h = im.h;
-			c.x0 = g.x0;
-			c.y0 = g.y0;
-		}
-		image = host_image_new()((uint16_t)im.numcomps, cp.data(),
-								 im.numcomps >= 3 ? GRK_CLRSPC_SRGB : GRK_CLRSPC_GRAY, true);
 		if(image)
 		{
-			image->x0 = g.x0;
-			image->y0 = g.y0;
-			image->x1 = g.x1;
-			image->y1 = g.y1;
 			if(im.packed)
 			{
 				// de-interleave the file's samples into the host's int32 planes (what the host's own
@@ -778,9 +823,7 @@ int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
 		cb(&info);
 	logf("%s: read %.1f ms, tables %.1f, device encode %.1f, tree + host image %.1f, host callback %.1f",
 		 job.in.c_str(), ms_read, ms_prep - ms_read, ms_gpu - ms_prep, ms_fill - ms_gpu, ms_since(t_start) - ms_fill);
-	if(image && host_unref())
-		host_unref()(&image->obj);
-	return info.error_code ? -1 : 0;
+	return info.error_code ? -1 : 0; // the image stays with the worker's context
 }
 
 int next_device()
@@ -853,10 +896,30 @@ QcdPeek peek_qcd(const char* path, uint32_t numres)
 	return q;
 }
 
+// What a batch worker keeps from frame to frame on the decode side: the device decoder, the tile
+// tree of its geometry (with the per-block byte buffers the host copies into), and page-locked
+// staging for the coded bytes on the way in and the samples on the way out.
+struct DecoderSlot
+{
+	grkb_decoder* dec = nullptr;
+	grkb_tile_params tp{};
+	int device = -1;
+	std::unique_ptr<TileTree> tree;
+	TileGeom tg{};
+	PinnedBuf pool, out;
+	CachedImage himage; // handed to the host's output callback with plugin_owns_image = true
+	~DecoderSlot()
+	{
+		if(dec)
+			grkb_decoder_destroy(dec);
+	}
+};
+
 struct DecodeCtx
 {
 	TileGeom geom{};
-	std::unique_ptr<TileTree> tree;
+	DecoderSlot* slot = nullptr;
+	TileTree* tree = nullptr; // owned by the slot
 	uint32_t prec = 0;
 	bool sgnd = false, reversible = true, mct = false, ht = false;
 	uint8_t cblk_sty = 0;
@@ -907,15 +970,67 @@ int init_decompressors(grk_header_info* h, grk_image* image)
 	c->mct = h->mct == 1 && image->numcomps >= 3;
 	c->cblk_sty = h->cblk_sty;
 	c->ht = (h->cblk_sty & GRK_CBLKSTY_HT) != 0;
-	c->tree = std::make_unique<TileTree>();
-	c->ready = build_tree(g, true, *c->tree);
+	DecoderSlot* sl = c->slot;
+	if(!sl)
+		return -1;
+	if(sl->tree && memcmp(&sl->tg, &g, sizeof(g)) == 0)
+	{
+		// same geometry as the last frame: the tree stands, only what the host fills in is reset
+		for(auto& k : sl->tree->blocks)
+		{
+			k.compressedDataLength = 0;
+			k.numPasses = 0;
+			k.numBitPlanes = 0;
+		}
+		c->ready = true;
+	}
+	else
+	{
+		sl->tree = std::make_unique<TileTree>();
+		c->ready = build_tree(g, true, *sl->tree);
+		if(c->ready)
+			sl->tg = g;
+		else
+			sl->tree.reset();
+	}
+	c->tree = sl->tree.get();
 	return c->ready ? 0 : -1;
 }
 
-int decode_one(grk_decompress_parameters* params, const std::string& in, const std::string& out,
-			   int device, grk::PLUGIN_DECODE_USER_CALLBACK cb)
+std::vector<std::unique_ptr<DecoderSlot>>* g_dec_pool = new std::vector<std::unique_ptr<DecoderSlot>>();
+
+// The host's callback runs library code that throws for streams it will not hand to a plugin
+// (PluginDecodeUnsupportedException, plugin/plugin_bridge.cpp:55-72: several segments in a block, or
+// more passes than its BIBO bound) and nothing above catches it: an exception must not unwind
+// through this library or end a batch worker's thread.
+int32_t call_host(grk::PLUGIN_DECODE_USER_CALLBACK cb, grk::PluginDecodeCallbackInfo* info)
 {
+	try
+	{
+		return cb(info);
+	}
+	catch(const std::exception& e)
+	{
+		logf("host callback threw (%s): the frame is left to the host's CPU path", e.what());
+	}
+	catch(...)
+	{
+		logf("host callback threw: the frame is left to the host's CPU path");
+	}
+	return -1;
+}
+
+int decode_one(grk_decompress_parameters* params, const std::string& in, const std::string& out,
+			   int device, grk::PLUGIN_DECODE_USER_CALLBACK cb, DecoderSlot* slot = nullptr)
+{
+	DecoderSlot local;
+	if(!slot)
+		slot = &local;
+	using clk = std::chrono::steady_clock;
+	const auto t_start = clk::now();
+	auto ms_since = [](clk::time_point a) { return std::chrono::duration<double, std::milli>(clk::now() - a).count(); };
 	DecodeCtx ctx;
+	ctx.slot = slot;
 	t_ctx = &ctx;
 	grk::PluginDecodeCallbackInfo info(in, out, params, params ? params->decod_format : GRK_UNK_FMT,
 									   GRK_DECODE_HEADER);
@@ -925,12 +1040,13 @@ int decode_one(grk_decompress_parameters* params, const std::string& in, const s
 	info.init_decompressors_func = init_decompressors;
 	auto finish = [&](int rc) {
 		info.decompress_flags = GRK_PLUGIN_DECODE_CLEAN;
-		cb(&info);
+		call_host(cb, &info);
 		t_ctx = nullptr;
 		return rc;
 	};
-	if(cb(&info) != 0 || !ctx.ready)
+	if(call_host(cb, &info) != 0 || !ctx.ready)
 		return finish(-1);
+	const double ms_header = ms_since(t_start);
 	TileTree& t = *ctx.tree;
 	// T2 on the host.  GRK_DECODE_POST_T1 has to ride along: without it the host never advances
 	// to the next tile part (CodeStreamDecompress::findNextTile only does so when the post stage
@@ -939,8 +1055,9 @@ int decode_one(grk_decompress_parameters* params, const std::string& in, const s
 	// that count are the ones this plugin hands over below.
 	info.decompress_flags = GRK_DECODE_T2 | GRK_DECODE_POST_T1;
 	info.tile = &t.tile;
-	if(cb(&info) != 0) // host: T2, then decompress_synch_plugin_with_host fills the tree
+	if(call_host(cb, &info) != 0) // host: T2, then decompress_synch_plugin_with_host fills the tree
 		return finish(-1);
+	const double ms_t2 = ms_since(t_start);
 	// descriptor table from the filled tree
 	const TileGeom& g = ctx.geom;
 	const size_t ng = t.geom.size(), n = ng * g.numcomps;
@@ -956,8 +1073,14 @@ int decode_one(grk_decompress_parameters* params, const std::string& in, const s
 	}
 	std::vector<grkb_cblk> blocks(n);
 	std::vector<grkb_seg> segs;
-	std::vector<uint8_t> pool;
 	segs.reserve(n);
+	size_t pool_bytes = 16;
+	for(size_t i = 0; i < n; ++i)
+		pool_bytes += t.flat[i]->numPasses ? t.flat[i]->compressedDataLength : 0;
+	if(!slot->pool.reserve(pool_bytes))
+		return finish(-1);
+	uint8_t* pool = slot->pool.p;
+	size_t pool_size = 0;
 	for(size_t i = 0; i < n; ++i)
 	{
 		const grkb_cblk_geom& q = t.geom[i % ng];
@@ -990,13 +1113,15 @@ int decode_one(grk_decompress_parameters* params, const std::string& in, const s
 		{
 			b.numsegs = 1;
 			b.seg_first = (uint32_t)segs.size();
-			b.data_off = (uint32_t)pool.size();
+			b.data_off = (uint32_t)pool_size;
 			b.data_len = k.compressedDataLength;
 			segs.push_back(grkb_seg{k.compressedDataLength, (uint32_t)k.numPasses});
-			pool.insert(pool.end(), k.compressedData, k.compressedData + k.compressedDataLength);
+			memcpy(pool + pool_size, k.compressedData, k.compressedDataLength);
+			pool_size += k.compressedDataLength;
 		}
 	}
-	pool.resize(pool.size() + 16, 0);
+	memset(pool + pool_size, 0, 16);
+	pool_size += 16;
 	if(grkb_set_device(device))
 		return finish(-1);
 	grkb_tile_params tp{};
@@ -1021,52 +1146,76 @@ int decode_one(grk_decompress_parameters* params, const std::string& in, const s
 		return finish(-1);
 	}
 	const uint32_t W = g.x1 - g.x0, H = g.y1 - g.y0;
-	std::vector<grk_image_cmptparm> cp(g.numcomps);
-	for(auto& c : cp)
-	{
-		memset(&c, 0, sizeof(c));
-		c.prec = (uint8_t)ctx.prec;
-		c.sgnd = ctx.sgnd;
-		c.dx = c.dy = 1;
-		c.w = W;
-		c.h = H;
-		c.x0 = g.x0;
-		c.y0 = g.y0;
-	}
-	grk_image* image = host_image_new()((uint16_t)g.numcomps, cp.data(),
-										g.numcomps >= 3 ? GRK_CLRSPC_SRGB : GRK_CLRSPC_GRAY, true);
+	grk_image* image = slot->himage.get(W, H, g.numcomps, ctx.prec, ctx.sgnd, g.x0, g.y0);
 	if(!image)
 		return finish(-1);
-	image->x0 = g.x0;
-	image->y0 = g.y0;
-	image->x1 = g.x1;
-	image->y1 = g.y1;
-	grkb_decoder* dec = nullptr;
-	int rc = grkb_decoder_create(&tp, (uint32_t)n, pool.size(), &dec);
+	const double ms_table = ms_since(t_start);
+	if(slot->dec && (slot->device != device || memcmp(&slot->tp, &tp, sizeof(tp)) != 0))
+	{
+		grkb_decoder_destroy(slot->dec);
+		slot->dec = nullptr;
+	}
+	int rc = 0;
+	if(!slot->dec)
+	{
+		rc = grkb_decoder_create(&tp, (uint32_t)n, pool_size, &slot->dec);
+		if(rc)
+			slot->dec = nullptr;
+		slot->tp = tp;
+		slot->device = device;
+	}
+	grkb_decoder* dec = slot->dec;
 	uint32_t rejected = 0;
 	if(!rc)
 	{
-		std::vector<int32_t*> planes(g.numcomps);
-		for(uint32_t c = 0; c < g.numcomps; ++c)
-			planes[c] = image->comps[c].data;
-		rc = grkb_decoder_decode(dec, blocks.data(), (uint32_t)n, segs.data(), (uint32_t)segs.size(),
-								 pool.data(), pool.size(), planes.data(), image->comps[0].stride,
-								 &rejected);
-		grkb_decoder_destroy(dec);
+		const size_t row16 = (size_t)W * 2;
+		if(ctx.prec <= 16 && slot->out.reserve(row16 * H * g.numcomps + 16))
+		{
+			// the samples cross the bus as 16-bit planes into page-locked memory and are
+			// widened into the host's int32 image here
+			rc = grkb_decoder_submit_packed(dec, blocks.data(), (uint32_t)n, segs.data(), (uint32_t)segs.size(),
+											pool, pool_size, slot->out.p, GRKB_SAMPLES_16, row16);
+			if(!rc)
+				rc = grkb_decoder_wait(dec, &rejected);
+			if(!rc)
+				for(uint32_t c = 0; c < g.numcomps; ++c)
+					for(uint32_t y = 0; y < H; ++y)
+					{
+						const uint16_t* src = (const uint16_t*)(slot->out.p + ((size_t)c * H + y) * row16);
+						int32_t* dst = image->comps[c].data + (size_t)y * image->comps[c].stride;
+						if(ctx.sgnd)
+							for(uint32_t x = 0; x < W; ++x)
+								dst[x] = (int16_t)src[x];
+						else
+							for(uint32_t x = 0; x < W; ++x)
+								dst[x] = src[x];
+					}
+		}
+		else
+		{
+			std::vector<int32_t*> planes(g.numcomps);
+			for(uint32_t c = 0; c < g.numcomps; ++c)
+				planes[c] = image->comps[c].data;
+			rc = grkb_decoder_decode(dec, blocks.data(), (uint32_t)n, segs.data(), (uint32_t)segs.size(), pool,
+									 pool_size, planes.data(), image->comps[0].stride, &rejected);
+		}
 	}
 	if(rc || rejected)
 	{
 		logf("decode failed: %s (%u blocks rejected)", grkb_last_error(), rejected);
-		host_unref()(&image->obj);
 		return finish(-1);
 	}
+	const double ms_dev = ms_since(t_start);
 	info.image = image;
 	info.plugin_owns_image = true;
 	info.decompress_flags = GRK_DECODE_POST_T1;
-	rc = cb(&info); // host: colour management, file output
+	rc = call_host(cb, &info); // host: colour management, file output
+	const double ms_out = ms_since(t_start);
 	finish(rc);
-	host_unref()(&image->obj);
-	return rc;
+	logf("%s: host header %.1f ms, host T2 %.1f, table + host image %.1f, device decode %.1f, host output %.1f, "
+		 "clean %.1f", in.c_str(), ms_header, ms_t2 - ms_header, ms_table - ms_t2, ms_dev - ms_table,
+		 ms_out - ms_dev, ms_since(t_start) - ms_out);
+	return rc; // the image stays with the slot
 }
 
 std::vector<std::string> list_dir(const char* dir)
@@ -1116,6 +1265,7 @@ PLUGIN_EXPORT int32_t exit_func()
 {
 	join_batch();
 	g_ctx_pool->clear();
+	g_dec_pool->clear();
 	return 0;
 }
 PLUGIN_EXPORT grk::minpf_exit_func minpf_post_load_plugin(const char*,
@@ -1271,14 +1421,34 @@ PLUGIN_EXPORT int32_t plugin_batch_decompress(void)
 		return -1;
 	join_batch();
 	g_batch_done = false;
+	// frames are independent: workers take them in directory order, each with a device decoder of
+	// its own; the host's T2 (first callback) and output stage (last callback) of different frames
+	// run side by side, as do the copies and kernels on the device
 	g_batch_thread = std::thread([]() {
-		for(const std::string& name : list_dir(g_dec_in.c_str()))
-		{
-			if(g_stop)
-				break;
-			decode_one(g_dec_params, g_dec_in + "/" + name, g_dec_out + "/" + replace_ext(name, "ppm"),
-					   next_device(), g_dec_cb);
-		}
+		const std::vector<std::string> names = list_dir(g_dec_in.c_str());
+		unsigned nthreads = std::max(2u, std::min(8u, std::thread::hardware_concurrency()));
+		if(const char* v = getenv("GRKB_BATCH_THREADS"))
+			nthreads = std::max(1, atoi(v));
+		nthreads = (unsigned)std::min<size_t>(nthreads, std::max<size_t>(names.size(), 1));
+		while(g_dec_pool->size() < nthreads)
+			g_dec_pool->emplace_back(new DecoderSlot());
+		std::atomic<size_t> next{0};
+		auto worker = [&](unsigned slot) {
+			for(;;)
+			{
+				const size_t i = next++;
+				if(i >= names.size() || g_stop)
+					break;
+				decode_one(g_dec_params, g_dec_in + "/" + names[i], g_dec_out + "/" + replace_ext(names[i], "ppm"),
+						   next_device(), g_dec_cb, (*g_dec_pool)[slot].get());
+			}
+		};
+		std::vector<std::thread> pool;
+		for(unsigned t = 1; t < nthreads; ++t)
+			pool.emplace_back(worker, t);
+		worker(0);
+		for(auto& t : pool)
+			t.join();
 		g_batch_done = true;
 	});
 	return 0;

@@ -345,6 +345,21 @@ def ref_plugin_batch_encode(in_dir, out_dir, irreversible, ht=False, numres=6, c
     return n
 
 
+def ref_plugin_batch_decode(in_dir, out_dir):
+    """grk_plugin_init_batch_decompress + grk_plugin_batch_decompress over a directory of
+    codestreams; returns the number of frames the host callback wrote (read_plane_dump)"""
+    n = ref().ref_plugin_batch_decode(in_dir.encode(), out_dir.encode())
+    if n < 0:
+        raise RuntimeError("plugin-driven batch decode failed (%d)" % n)
+    return n
+
+
+def read_plane_dump(path):
+    raw = np.fromfile(path, dtype=np.int32)
+    nc, w, h = int(raw[0]), int(raw[1]), int(raw[2])
+    return [raw[3 + c * w * h:3 + (c + 1) * w * h].reshape(h, w) for c in range(nc)]
+
+
 def ref_plugin_decode(j2k_path, ncomp, w, h):
     """stock host (markers, T2) + our plugin (T1, dequantisation, wavelet, MCT)"""
     planes = [np.zeros((h, w), dtype=np.int32) for _ in range(ncomp)]

@@ -795,6 +795,87 @@ static int32_t plugin_dec_cb_impl(grk_plugin_decompress_callback_info* info)
 	return -1;
 }
 
+/* The batch door of the decoder (grk_decompress.cpp:996-1300 reduced to file streams): every
+ * codestream of input_dir goes through host T2 + plugin, possibly on several threads at once;
+ * the samples the plugin hands back are written to output_file_name as a flat dump
+ * (uint32 numcomps, w, h, then the int32 planes).  All per-frame state rides in `info`. */
+static std::atomic<int> g_bdec_ok{0}, g_bdec_bad{0};
+static int32_t plugin_batch_dec_cb(grk_plugin_decompress_callback_info* info)
+{
+	if(!info)
+		return -1;
+	if(info->decompress_flags & GRK_PLUGIN_DECODE_CLEAN)
+	{
+		if(info->codec)
+			grk_object_unref(info->codec);
+		if(info->stream)
+			grk_object_unref(info->stream);
+		info->codec = nullptr;
+		info->stream = nullptr;
+		return 0;
+	}
+	if(info->decompress_flags & GRK_DECODE_HEADER)
+	{
+		info->stream = grk_stream_create_file_stream(info->input_file_name, 1 << 20, true);
+		if(!info->stream)
+			return -1;
+		info->codec = grk_decompress_create(GRK_CODEC_J2K, info->stream);
+		if(!info->codec || !grk_decompress_init(info->codec, &g_dec_params.core) ||
+		   !grk_decompress_read_header(info->codec, &info->header_info))
+			return -1;
+		info->image = grk_decompress_get_composited_image(info->codec);
+		if(!info->image || !info->init_decompressors_func)
+			return -1;
+		return info->init_decompressors_func(&info->header_info, info->image);
+	}
+	if(info->decompress_flags & GRK_DECODE_T2)
+	{
+		if(!info->tile || !info->codec)
+			return -1;
+		info->tile->decompress_flags = info->decompress_flags;
+		return grk_decompress(info->codec, info->tile) ? 0 : -1;
+	}
+	if(info->decompress_flags & GRK_DECODE_POST_T1)
+	{
+		auto image = info->image;
+		FILE* f = image && info->output_file_name ? fopen(info->output_file_name, "wb") : nullptr;
+		if(!f)
+		{
+			g_bdec_bad++;
+			return -1;
+		}
+		const uint32_t hdr[3] = {image->numcomps, image->comps[0].w, image->comps[0].h};
+		fwrite(hdr, sizeof(uint32_t), 3, f);
+		for(uint32_t c = 0; c < image->numcomps; ++c)
+			for(uint32_t y = 0; y < image->comps[c].h; ++y)
+				fwrite(image->comps[c].data + (size_t)y * image->comps[c].stride, sizeof(int32_t),
+					   image->comps[c].w, f);
+		fclose(f);
+		g_bdec_ok++;
+		return 0;
+	}
+	return -1;
+}
+
+int ref_plugin_batch_decode(const char* input_dir, const char* output_dir)
+{
+	if(!g_plugin_ready)
+		return -10;
+	memset(&g_dec_params, 0, sizeof(g_dec_params));
+	grk_decompress_set_default_params(&g_dec_params.core);
+	g_dec_params.decod_format = GRK_J2K_FMT;
+	g_bdec_ok = 0;
+	g_bdec_bad = 0;
+	if(grk_plugin_init_batch_decompress(input_dir, output_dir, &g_dec_params, plugin_batch_dec_cb) != 0)
+		return -11;
+	if(grk_plugin_batch_decompress() != 0)
+		return -12;
+	while(!grk_plugin_is_batch_complete())
+		std::this_thread::sleep_for(std::chrono::milliseconds(2));
+	grk_plugin_stop_batch_decompress();
+	return g_bdec_bad ? -100 - g_bdec_bad.load() : g_bdec_ok.load();
+}
+
 /* Decode of a .j2k file with T2 on the host and everything after it in the plugin. */
 int ref_plugin_decode(const char* infile, int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t h)
 {

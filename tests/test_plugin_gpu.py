@@ -109,3 +109,28 @@ def test_plugin_batch_encode_byte_identical(host, tmp_path, w, h, ncomp, prec, n
     for f in range(len(frames)):
         got = np.fromfile(str(outdir / ("f%03d.j2k" % f)), dtype=np.uint8)
         assert len(got) == len(stock[f]) and np.array_equal(got, stock[f]), "frame %d" % f
+
+
+@pytest.mark.parametrize("w,h,ncomp,prec,nr,irr,ht", [
+    (320, 200, 3, 12, 6, 0, 1),    # HTJ2K lossless
+    (320, 200, 3, 12, 6, 1, 0),    # 9/7 + ICT, MQ (BASELINE configs[1] in small)
+])
+def test_plugin_batch_decode_identical_samples(host, tmp_path, w, h, ncomp, prec, nr, irr, ht):
+    """grk_plugin_batch_decompress: a directory of codestreams through the plugin's worker pool
+    (host T2 and output callbacks on several threads, one device decoder per worker) -> every
+    frame's samples equal the stock CPU decoder's."""
+    indir, outdir = tmp_path / "in", tmp_path / "out"
+    indir.mkdir()
+    outdir.mkdir()
+    want = []
+    for f in range(9):
+        img = H.synth_image(w, h, ncomp, prec, seed=200 + f)
+        cs = O.ref_codec_encode(img, prec, irr, ht=bool(ht), numres=nr)
+        cs.tofile(str(indir / ("f%03d.j2k" % f)))
+        want.append(O.ref_codec_decode(cs, ncomp, w, h))
+    assert O.ref_plugin_batch_decode(str(indir), str(outdir)) == 9
+    for f in range(9):
+        got = O.read_plane_dump(str(outdir / ("f%03d.ppm" % f)))
+        assert len(got) == ncomp
+        for c in range(ncomp):
+            assert np.array_equal(got[c], want[f][c]), "frame %d component %d" % (f, c)

@@ -410,23 +410,82 @@ def plugin_batch(args):
         "cpu_baseline": cpu}), flush=True)
 
 
+def plugin_batch_decode(args):
+    """grk_plugin_init_batch_decompress + grk_plugin_batch_decompress over a directory of 4K HTJ2K
+    (or, with --mq, 9/7 MQ) codestreams: host T2 + output callback of the UNMODIFIED library on the
+    host threads, everything between in our plugin.  Wall clock, files included; the output
+    callback dumps the int32 planes to files."""
+    import shutil
+    import tempfile
+    from oracle import oracle as O
+    W, H, prec, nr = 4096, 2160, 12, 6
+    nframes = args.frames
+    if not O.have_plugin():
+        raise SystemExit("reference host / plugin not built")
+    if args.inflight:
+        os.environ["GRKB_BATCH_THREADS"] = str(args.inflight)
+    base = synth(W + 8 * 4, H, prec, 4096)
+    root = tempfile.mkdtemp(prefix="grkb_bdec_")
+    try:
+        indir, outdir = os.path.join(root, "in"), os.path.join(root, "out")
+        os.makedirs(indir)
+        os.makedirs(outdir)
+        threads = os.cpu_count() or 1
+        streams = [O.ref_codec_encode([a[:, 8 * f:8 * f + W] for a in base], prec, 1 if args.mq else 0,
+                                      ht=not args.mq, numres=nr, threads=threads) for f in range(4)]
+        for f in range(nframes):
+            streams[f % 4].tofile(os.path.join(indir, "f%04d.j2k" % f))
+        O.ref_plugin_open(device=0, threads=args.host_threads)
+        O.ref_plugin_batch_decode(indir, outdir)  # warm-up
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            assert O.ref_plugin_batch_decode(indir, outdir) == nframes
+        dt = (time.perf_counter() - t0) / args.steps
+        want = O.ref_codec_decode(streams[1], 3, W, H, threads=threads)
+        t1 = time.perf_counter()
+        O.ref_codec_decode(streams[1], 3, W, H, threads=threads)
+        ct = time.perf_counter() - t1
+        got = O.read_plane_dump(os.path.join(outdir, "f0001.ppm"))
+        same = all(np.array_equal(a, b) for a, b in zip(got, want))
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
+    mp = W * H / 1e6
+    print(json.dumps({
+        "metric": "decode_mpixels_per_s", "value": mp * nframes / dt, "unit": "Mpixel/s", "n_gpus": 1,
+        "steps": args.steps, "ms_per_frame": dt * 1e3 / nframes, "dtype": "f32" if args.mq else "i32",
+        "data": "synthetic",
+        "config": {"workload": "grk_plugin_batch_decompress_4096x2160_rgb12_" +
+                               ("97_ict_mq" if args.mq else "53_rct_ht_lossless") + "_5lvl_cblk64",
+                   "frames": nframes, "workers": os.environ.get("GRKB_BATCH_THREADS", "default"),
+                   "host_library_threads": args.host_threads or "all",
+                   "coded_bytes_per_frame": int(len(streams[0])),
+                   "scope": "file read + T2 in the unmodified host callback; T1, dequantisation, inverse wavelet, "
+                            "inverse MCT in the plugin; int32 planes handed to the host's output callback, which "
+                            "writes them to a file; wall clock"},
+        "cpu_baseline": {"value": mp / ct, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
+                         "sample": "one frame: stock grk decompress, memory stream, %.0f ms; plugin samples of that "
+                                   "frame identical: %s" % (ct * 1e3, same)}}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["ht_encode", "tiled", "mq_encode", "plugin_batch"])
+    ap.add_argument("what", choices=["ht_encode", "tiled", "mq_encode", "plugin_batch", "plugin_batch_decode"])
     ap.add_argument("--frames", type=int, default=8)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--inflight", type=int, default=None)
     ap.add_argument("--size", type=int, default=8192)
     ap.add_argument("--verify", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--mq", action="store_true", help="plugin_batch_decode: 9/7 MQ frames instead of HT lossless")
     ap.add_argument("--host-threads", type=int, default=0,
                     help="plugin_batch: threads of the reference host's own pool (0 = all cores)")
     ap.add_argument("--samples16", action="store_true",
                     help="encode benches: send the frames as uint16 planes (grkb_encoder_submit_packed)")
     args = ap.parse_args()
-    if args.inflight is None and args.what != "plugin_batch":
+    if args.inflight is None and not args.what.startswith("plugin_batch"):
         args.inflight = 4 if args.what == "tiled" else 2
-    {"ht_encode": ht_encode, "tiled": tiled, "mq_encode": mq_encode, "plugin_batch": plugin_batch}[args.what](args)
+    {"ht_encode": ht_encode, "tiled": tiled, "mq_encode": mq_encode, "plugin_batch": plugin_batch,
+     "plugin_batch_decode": plugin_batch_decode}[args.what](args)
 
 
 if __name__ == "__main__":
