@@ -166,7 +166,13 @@ def tiled(args):
     K = args.inflight
     decs = [T.TileDecoder(params, len(blocks), 1 << 22) for _ in range(K)]
     outs = [[T.PinnedArray((TS, TS), np.int32) for _ in range(3)] for _ in range(K)]
+    outs16 = [T.PinnedArray((3, TS, TS), np.uint16) for _ in range(K)] if args.samples16 else None
     result = [np.zeros((S, S), np.int32) for _ in range(3)] if args.verify else None
+
+    def planes_of(k):
+        if outs16 is not None:  # row N3: the tile came back as uint16 planes
+            return [outs16[k].array[c].astype(np.int32) for c in range(3)]
+        return [p.array for p in outs[k]]
 
     def one_pass(verify):
         pending = [None] * K
@@ -175,15 +181,18 @@ def tiled(args):
             if pending[k] is not None:
                 decs[k].wait()
                 if verify:
-                    shard.composite(result, [p.array for p in outs[k]], tiles[mine[pending[k]]])
+                    shard.composite(result, planes_of(k), tiles[mine[pending[k]]])
             b, s, d = coded_tiles[t]
-            decs[k].submit(b, s, d, [p.array for p in outs[k]])
+            if outs16 is not None:
+                decs[k].submit_packed(b, s, d, outs16[k].array)
+            else:
+                decs[k].submit(b, s, d, [p.array for p in outs[k]])
             pending[k] = t
         for k in range(K):
             if pending[k] is not None:
                 decs[k].wait()
                 if verify:
-                    shard.composite(result, [p.array for p in outs[k]], tiles[mine[pending[k]]])
+                    shard.composite(result, planes_of(k), tiles[mine[pending[k]]])
 
     one_pass(args.verify)
     ok = True
@@ -219,7 +228,8 @@ def tiled(args):
     print(json.dumps({
         "metric": "decode_mpixels_per_s", "value": S * S / 1e6 / (ms * 1e-3), "unit": "Mpixel/s",
         "n_gpus": world, "steps": args.steps, "ms_per_step": ms, "scaling": "strong", "dtype": "i32",
-        "data": "synthetic", "timed": "end to end: H2D of descriptors + coded bytes, decode, D2H of int32 planes",
+        "data": "synthetic", "timed": "end to end: H2D of descriptors + coded bytes, decode, D2H of %s planes"
+                                     % ("uint16 (N3)" if args.samples16 else "int32"),
         "config": {"workload": "htj2k_decode_%dx%d_rgb16_53_rct_lossless_5lvl_cblk64_tiles1024" % (S, S),
                    "tiles": len(tiles), "tiles_per_rank": len(mine), "decoders_in_flight": K,
                    "coded_bytes_this_rank": nbytes, "sharding": "tile t -> rank t mod N, no collective"},
@@ -480,7 +490,8 @@ def main():
     ap.add_argument("--host-threads", type=int, default=0,
                     help="plugin_batch: threads of the reference host's own pool (0 = all cores)")
     ap.add_argument("--samples16", action="store_true",
-                    help="encode benches: send the frames as uint16 planes (grkb_encoder_submit_packed)")
+                    help="encode benches: send the frames as uint16 planes (grkb_encoder_submit_packed); tiled: receive "
+                         "the tiles as uint16 planes (grkb_decoder_submit_packed)")
     args = ap.parse_args()
     if args.inflight is None and not args.what.startswith("plugin_batch"):
         args.inflight = 4 if args.what == "tiled" else 2
