@@ -262,7 +262,7 @@ static __device__ __forceinline__ void reset_states(uint32_t* cxs, const uint32_
 struct EBlk
 {
 	uint32_t* fl; // state words, (w+2) x (nstripes+2)
-	const uint32_t* smp; // sign-magnitude samples, 6 fractional bits, row pitch w
+	const uint32_t* smp; // sign-magnitude samples, 6 fractional bits: [stripe][column][row of the stripe]
 	uint32_t w, h, fs;
 	const uint8_t* zc; // zero-coding table of this band orientation
 	const uint8_t* sc;
@@ -296,11 +296,16 @@ constexpr uint32_t SYM_CAP = 320; // at most 10 symbols per column (run-length c
 // bit r of a row nibble -> bit 3(r+1)+c of the state word (c: 0 west, 1 centre, 2 east)
 static __device__ __forceinline__ uint32_t spread4(uint32_t nib, uint32_t c)
 {
-	return (((nib & 1u) << 3) | ((nib & 2u) << 5) | ((nib & 4u) << 7) | ((nib & 8u) << 9)) << c;
+	// b0 b1 . . . . b2 b3, then every bit to three times its index (two multiply-and-mask steps
+	// instead of four shift-and-mask pairs: this runs several times per stripe column and pass)
+	const uint32_t t = (nib * 17u) & 0xC3u;
+	return ((t * 5u) & 0x249u) << (3u + c);
 }
 static __device__ __forceinline__ uint32_t sig4(uint32_t f)
 {
-	return ((f >> 4) & 1u) | ((f >> 6) & 2u) | ((f >> 8) & 4u) | ((f >> 10) & 8u);
+	uint32_t g = (f >> 4) & 0x249u; // bits 0, 3, 6, 9
+	g = (g | (g >> 2)) & 0xC3u;
+	return (g | (g >> 4)) & 0xFu;
 }
 static __device__ __forceinline__ uint32_t nz4(uint32_t f)
 {
@@ -346,10 +351,12 @@ static __device__ __forceinline__ Col load_col(const EBlk& b, uint32_t s, uint32
 	c.fp = b.fl + (s + 1) * b.fs + 1 + x;
 	c.f = c.act ? *c.fp : 0u;
 	c.sgn4 = c.bit4 = 0;
+	const uint4 q4 = c.act ? reinterpret_cast<const uint4*>(b.smp)[s * b.w + x] : make_uint4(0, 0, 0, 0);
+	const uint32_t sm4[4] = {q4.x, q4.y, q4.z, q4.w};
 #pragma unroll
 	for(uint32_t r = 0; r < 4; ++r)
 	{
-		const uint32_t sm = (c.act && r < rows) ? b.smp[(k + r) * b.w + x] : 0u;
+		const uint32_t sm = sm4[r];
 		c.mag[r] = sm & 0x7FFFFFFFu;
 		c.sgn4 |= (sm >> 31) << r;
 		c.bit4 |= ((sm & one) ? 1u : 0u) << r;
@@ -363,8 +370,10 @@ static __device__ __forceinline__ Col load_col(const EBlk& b, uint32_t s, uint32
 		const bool there = west ? x0 > 0 : x + 1 < b.w;
 		uint32_t sg = 0;
 		if(there && c.act)
-			for(uint32_t r = 0; r < rows; ++r)
-				sg |= (b.smp[(k + r) * b.w + (west ? x - 1 : x + 1)] >> 31) << r;
+		{
+			const uint4 n4 = reinterpret_cast<const uint4*>(b.smp)[s * b.w + (west ? x - 1 : x + 1)];
+			sg = (n4.x >> 31) | ((n4.y >> 31) << 1) | ((n4.z >> 31) << 2) | ((n4.w >> 31) << 3);
+		}
 		if(west)
 			c.sgnL = sg;
 		else
@@ -536,12 +545,13 @@ static __device__ int32_t enc_sig_pass(const EBlk& b, SymWriter& sw, uint8_t* li
 			uint32_t total;
 			uint32_t at = warp_excl_scan((uint32_t)(__popc(mem) + __popc(ns)), lane, total);
 			const uint32_t fw = c.f | spread4(nsL, 0);
+			const uint32_t sp1 = spread4(ns, 1); // own column; a visit sees the rows above it only
 #pragma unroll
 			for(uint32_t r = 0; r < 4; ++r)
 				if((mem >> r) & 1u)
 				{
 					const uint32_t low = ns & ((1u << r) - 1u);
-					const uint32_t fv = fw | spread4(low, 1) | ((low & c.sgn4) << 19);
+					const uint32_t fv = fw | (sp1 & ((1u << (3u * r + 4u)) - 1u)) | ((low & c.sgn4) << 19);
 					const uint32_t v = (c.bit4 >> r) & 1u;
 					list[at++] = (uint8_t)(b.zc[(fv >> (3 * r)) & T1_NEIGH] | (v << 5));
 					if(v)
@@ -610,6 +620,7 @@ static __device__ int32_t enc_cleanup_pass(const EBlk& b, SymWriter& sw, uint8_t
 			if(lane == 0)
 				nsL = 0;
 			const uint32_t fw = c.f | spread4(nsL, 0);
+			const uint32_t sp1 = spread4(ns, 1); // own column; a visit sees the rows above it only
 			// run-length mode: four rows, nothing significant or visited in or around the column
 			const bool rl = c.act && c.rowmask == 0xFu && fw == 0;
 			const uint32_t r0 = ns ? (uint32_t)__ffs((int)ns) - 1u : 4u;
@@ -634,7 +645,7 @@ static __device__ int32_t enc_cleanup_pass(const EBlk& b, SymWriter& sw, uint8_t
 				if(((todo >> r) & 1u) && r >= first)
 				{
 					const uint32_t low = ns & ((1u << r) - 1u);
-					const uint32_t fv = fw | spread4(low, 1) | ((low & c.sgn4) << 19);
+					const uint32_t fv = fw | (sp1 & ((1u << (3u * r + 4u)) - 1u)) | ((low & c.sgn4) << 19);
 					const uint32_t v = (c.bit4 >> r) & 1u;
 					if(!(rl && r == r0))
 						list[at++] = (uint8_t)(b.zc[(fv >> (3 * r)) & T1_NEIGH] | (v << 5));
@@ -693,6 +704,15 @@ static __device__ __forceinline__ bool pass_is_raw(uint32_t numbps, uint32_t sty
 	return (bpno < (int)numbps - 4) && passtype < 2 && (sty & GRKB_CBLKSTY_LAZY);
 }
 
+// shared memory of one warp of the modelling kernel: symbol list, state words, samples (stripe
+// by stripe, four rows per column: a block of height h takes 4 * ceil(h / 4) <= h + 3 rows)
+static __host__ __device__ __forceinline__ size_t model_per_warp(const T1EncLaunch& l)
+{
+	const size_t flag_words = ((size_t)l.max_flag_words + 3) & ~(size_t)3;
+	const size_t smp_words = ((size_t)l.max_area + 3 * (size_t)l.max_w + 3) & ~(size_t)3;
+	return SYM_CAP + flag_words * 4 + smp_words * 4;
+}
+
 // ---- kernel 1: context modelling, one code block per warp ---------------------------------------
 __global__ void __launch_bounds__(ENC_MAX_THREADS)
 	t1_mq_model_kernel(const T1EncLaunch l, const T1Tables* __restrict__ tab)
@@ -711,10 +731,10 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 	__syncthreads();
 
 	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const size_t per_warp = SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
+	const size_t per_warp = model_per_warp(l);
 	uint8_t* list = warp_base + warp * per_warp; // (context, decision) symbols of one stripe segment
 	uint32_t* fl = reinterpret_cast<uint32_t*>(list + SYM_CAP);
-	uint32_t* smp = fl + l.max_flag_words;
+	uint32_t* smp = fl + ((l.max_flag_words + 3u) & ~3u); // 16-byte aligned: read as uint4
 
 	for(;;)
 	{
@@ -736,21 +756,31 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 		const uint32_t fs = w + 2, nstripes = (h + 3) >> 2, nfl = fs * (nstripes + 2);
 		// ---- quantise to sign-magnitude, 6 fractional bits (T1Part1.cpp:37-88) -----------------
 		uint32_t mx = 0;
-		for(uint32_t y = 0; y < h; ++y)
+		// stored stripe by stripe with the four rows of a column side by side (one 128-bit load per
+		// column and pass in load_col); rows past the block's height are zeros
+		for(uint32_t s4 = 0; s4 < nstripes; ++s4)
 		{
 			const int32_t* src =
-				reinterpret_cast<const int32_t*>(l.planes[cb.comp]) + (size_t)(cb.y + y) * l.stride + cb.x;
+				reinterpret_cast<const int32_t*>(l.planes[cb.comp]) + (size_t)(cb.y + 4 * s4) * l.stride + cb.x;
+			const uint32_t rows = min(4u, h - 4 * s4);
 			for(uint32_t x = lane; x < w; x += 32)
 			{
-				int32_t t;
-				if(l.reversible)
-					t = (int32_t)((uint32_t)src[x] << 6);
-				else
-					t = __float2int_rn(
-						__fmul_rn(__fdiv_rn(__int_as_float(src[x]), cb.stepsize), 64.0f));
-				const uint32_t mag = (uint32_t)(t < 0 ? -t : t);
-				smp[y * w + x] = mag | (t < 0 ? 0x80000000u : 0u);
-				mx = max(mx, mag);
+				uint32_t q[4] = {0, 0, 0, 0};
+#pragma unroll
+				for(uint32_t r = 0; r < 4; ++r)
+					if(r < rows)
+					{
+						const int32_t v = src[(size_t)r * l.stride + x];
+						int32_t t;
+						if(l.reversible)
+							t = (int32_t)((uint32_t)v << 6);
+						else
+							t = __float2int_rn(__fmul_rn(__fdiv_rn(__int_as_float(v), cb.stepsize), 64.0f));
+						const uint32_t mag = (uint32_t)(t < 0 ? -t : t);
+						q[r] = mag | (t < 0 ? 0x80000000u : 0u);
+						mx = max(mx, mag);
+					}
+				reinterpret_cast<uint4*>(smp)[s4 * w + x] = make_uint4(q[0], q[1], q[2], q[3]);
 			}
 		}
 		for(uint32_t i = lane; i < nfl; i += 32)
@@ -1155,7 +1185,7 @@ int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s)
 		grkb_set_error("t1 encode: no symbol pool");
 		return -1;
 	}
-	const size_t per_warp = SYM_CAP + (size_t)l.max_flag_words * 4 + (size_t)l.max_area * 4;
+	const size_t per_warp = model_per_warp(l);
 	const size_t fixed = 1024 + 2048 + 256;
 	int nw = ENC_MAX_THREADS / 32;
 	while(nw > 1 && fixed + per_warp * nw > 100 * 1024)

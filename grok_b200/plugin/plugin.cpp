@@ -1359,7 +1359,9 @@ PLUGIN_EXPORT int32_t plugin_batch_encode(const char* input_dir, const char* out
 				job.out = out + "/" + replace_ext(names[i], ext);
 				strncpy(p.infile, job.in.c_str(), sizeof(p.infile) - 1);
 				strncpy(p.outfile, job.out.c_str(), sizeof(p.outfile) - 1);
-				if(encode_one(&p, job, next_device(), cb, &ctx, serial_cb))
+				// a worker stays on one device (deviceId = -1: workers spread over all of them)
+				const int dev = g_device >= 0 ? g_device : (g_ndev > 0 ? (int)(slot % (unsigned)g_ndev) : 0);
+				if(encode_one(&p, job, dev, cb, &ctx, serial_cb))
 					failed++;
 			}
 		};
@@ -1440,7 +1442,8 @@ PLUGIN_EXPORT int32_t plugin_batch_decompress(void)
 				if(i >= names.size() || g_stop)
 					break;
 				decode_one(g_dec_params, g_dec_in + "/" + names[i], g_dec_out + "/" + replace_ext(names[i], "ppm"),
-						   next_device(), g_dec_cb, (*g_dec_pool)[slot].get());
+						   g_device >= 0 ? g_device : (g_ndev > 0 ? (int)(slot % (unsigned)g_ndev) : 0), g_dec_cb,
+						   (*g_dec_pool)[slot].get());
 			}
 		};
 		std::vector<std::thread> pool;
