@@ -279,7 +279,7 @@ def run_ours(args):
     # coded bytes) and D2H (three int32 planes) inside the timed region.  K decoders keep K
     # frames in flight (submit frame i, then wait for frame i-K+1), so one frame's D2H overlaps the
     # next frames' H2D + kernels; each step still moves and decodes a whole frame.
-    K = max(1, args.inflight)
+    K = max(1, args.inflight if args.inflight else (2 if HT else 4))
     decs = [(dec, out)]
     for _ in range(K - 1):
         pin_k = [T.PinnedArray((H, W), np.int32) for _ in range(NCOMP)]
@@ -407,7 +407,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="j2k97", choices=["j2k97", "ht"])
-    ap.add_argument("--inflight", type=int, default=2, help="decoders (frames) in flight on the e2e leg")
+    ap.add_argument("--inflight", type=int, default=None,
+                    help="decoders (frames) in flight on the e2e leg (default: 4 for the MQ workload, whose kernel "
+                         "tails overlap; 2 for HT, which is bound by the bus)")
     args = ap.parse_args()
     select_workload(args.workload)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
