@@ -62,12 +62,14 @@ def _coded_tile(w, h, ncomp, prec, nr, sgnd=False):
     (128, 64, 3, 8, np.uint8, False, 0),
     (200, 64, 3, 10, np.int16, True, 0),      # signed components
     (96, 40, 4, 16, np.uint16, False, 0),     # full 16 bits, extra component
+    (3, 1, 1, 8, np.uint8, False, 0),         # narrower than one group of four
+    (5, 2, 3, 12, np.uint16, False, 0),
     (256, 96, 3, 12, ">u2", False, 0),        # big-endian samples (PNM byte order), vector path
     (250, 67, 3, 12, ">u2", False, 0),        # and the scalar path
 ])
 @pytest.mark.parametrize("interleaved", [False, True])
 def test_decode_packed_matches_oracle(gpu, orc, w, h, ncomp, prec, dtype, sgnd, pad, interleaved):
-    img, params, _, (dblocks, dsegs, pool) = _coded_tile(w, h, ncomp, prec, 4, sgnd)
+    img, params, _, (dblocks, dsegs, pool) = _coded_tile(w, h, ncomp, prec, 4 if min(w, h) >= 16 else 1, sgnd)
     dec = T.TileDecoder(params)
     planes = dec.decode(dblocks, dsegs, pool)
     for a, b in zip(planes, img):
@@ -98,7 +100,7 @@ def test_decode_packed_matches_oracle(gpu, orc, w, h, ncomp, prec, dtype, sgnd, 
 ])
 @pytest.mark.parametrize("interleaved", [False, True])
 def test_encode_packed_equals_encode_of_int32(gpu, orc, w, h, ncomp, prec, dtype, sgnd, pad, interleaved):
-    img, params, blocks, _ = _coded_tile(w, h, ncomp, prec, 4, sgnd)
+    img, params, blocks, _ = _coded_tile(w, h, ncomp, prec, 4 if min(w, h) >= 16 else 1, sgnd)
     enc = E.TileEncoder(params)
     coded, passes, data = enc.encode(img, blocks)
     packed = orc.orc_pack_samples(img, np.dtype(dtype).newbyteorder("="), interleaved, row_pad=pad)
