@@ -1001,25 +1001,27 @@ static __device__ __forceinline__ uint32_t sym_next(SymReader& r)
 }
 
 __global__ void __launch_bounds__(CODE_THREADS)
-	t1_mq_code_kernel(const T1EncLaunch l, const T1Tables* __restrict__ tab)
+	t1_mq_code_kernel(const T1EncLaunch l, const T1Tables* __restrict__ tab, const uint32_t group)
 {
 	__shared__ uint32_t mqt[96];
 	__shared__ uint32_t cxs_all[T1_NCTX * CODE_THREADS];
 	for(uint32_t i = threadIdx.x; i < 94; i += blockDim.x)
 		mqt[i] = tab->mq[i] | (i << 31); // the MPS of state 2i+mps rides in bit 31
 	__syncthreads();
-	// the first nlong warps take one block each (lane 0 only), the others 32 blocks each
+	// the first warps take `group` of the nlong longest blocks each (one by default, on lane 0), the
+	// others 32 blocks each
 	const uint32_t nlong = l.code_ctrl[0];
 	const uint32_t gw = blockIdx.x * (CODE_THREADS / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
 	uint32_t idx;
-	if(gw < nlong)
+	const uint32_t nlw = (nlong + group - 1) / group; // warps that hold `group` long blocks each
+	if(gw < nlw)
 	{
-		if(lane)
+		idx = gw * group + lane;
+		if(lane >= group || idx >= nlong)
 			return;
-		idx = gw;
 	}
 	else
-		idx = nlong + (gw - nlong) * 32 + lane;
+		idx = nlong + (gw - nlw) * 32 + lane;
 	if(idx >= l.nblocks)
 		return;
 	const uint32_t bi = l.code_order[idx];
@@ -1217,9 +1219,11 @@ int grkb_launch_t1_mq_encode(const T1EncLaunch& l, cudaStream_t s)
 	static const uint32_t min_long = env_u32("GRKB_MQ_LONG_MIN", 1024);
 	t1_mq_order_kernel<<<1, ORDER_THREADS, 0, s>>>(l, frac > 256 ? 256 : frac, cap, min_long);
 	GRKB_CUDA_CHECK(cudaGetLastError());
+	static const uint32_t group_env = env_u32("GRKB_MQ_LONG_GROUP", 1); // long blocks per warp
+	const uint32_t group = group_env < 1 ? 1 : (group_env > 32 ? 32 : group_env);
 	const uint32_t solo = cap < l.nblocks ? cap : l.nblocks;
-	const uint32_t warps = solo + (l.nblocks + 31) / 32;
-	t1_mq_code_kernel<<<(warps + CODE_THREADS / 32 - 1) / (CODE_THREADS / 32), CODE_THREADS, 0, s>>>(l, tab);
+	const uint32_t warps = (solo + group - 1) / group + (l.nblocks + 31) / 32;
+	t1_mq_code_kernel<<<(warps + CODE_THREADS / 32 - 1) / (CODE_THREADS / 32), CODE_THREADS, 0, s>>>(l, tab, group);
 	GRKB_CUDA_CHECK(cudaGetLastError());
 	return 0;
 }
