@@ -278,7 +278,28 @@ def mq_encode(args):
 
     host = {"submit": 0.0, "wait": 0.0}
 
+    def one_pass_threads():
+        # one host thread per encoder, frames k, k+K, ... each: an encoder takes its next frame
+        # the moment its last one is back, whatever the others are doing (the calls release the GIL)
+        import threading
+        nbs = [0] * K
+
+        def work(k):
+            for src in pins[k::K]:
+                encs[k].submit_packed(src, pblocks.array, outs[k], mct_norms=E.MCT_NORMS_IRREV, rate_control=True) \
+                    if args.samples16 else \
+                    encs[k].submit(src, pblocks.array, outs[k], mct_norms=E.MCT_NORMS_IRREV, rate_control=True)
+                nbs[k] += len(encs[k].wait()[2])
+        th = [threading.Thread(target=work, args=(k,)) for k in range(K)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        return sum(nbs)
+
     def one_pass():
+        if K > 1 and not args.single_thread:
+            return one_pass_threads()
         # frames of this rank, K encoders in flight (grkb_encoder_submit / wait)
         nb, pend = 0, [False] * K
         for i, src in enumerate(pins):
@@ -348,6 +369,7 @@ def mq_encode(args):
                 "input_samples": "uint16 planes (N3)" if args.samples16 else "int32 planes",
                 "h2d_bytes_per_frame": int(W * H * 3 * (2 if args.samples16 else 4) + blocks.nbytes),
                 "encoders_in_flight": K,
+                "host_threads": 1 if (K == 1 or args.single_thread) else K,
                 "host_ms_per_frame_in_submit": host_ms["submit"], "host_ms_per_frame_in_wait": host_ms["wait"],
                 "d2h_bytes_per_frame": int(nb // max(1, len(mine)) + out[0].nbytes +
                                            n * int(out[0]["numpasses"].max()) * 16)},
@@ -486,6 +508,8 @@ def main():
     ap.add_argument("--size", type=int, default=8192)
     ap.add_argument("--verify", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--single-thread", action="store_true",
+                    help="mq_encode: drive all encoders round-robin from one host thread instead of one thread each")
     ap.add_argument("--mq", action="store_true", help="plugin_batch_decode: 9/7 MQ frames instead of HT lossless")
     ap.add_argument("--host-threads", type=int, default=0,
                     help="plugin_batch: threads of the reference host's own pool (0 = all cores)")
