@@ -19,12 +19,12 @@
 //   * every coding pass walks the stripes in segments of 32 columns, one column per lane: the
 //     lane finds which of its four samples the pass codes and their contexts as the
 //     neighbourhood stands when the scan reaches them, and leaves its (context, decision)
-//     symbols at its prefix-sum position of a list in shared memory.  The membership of the
+//     symbols at its prefix-sum position of the block's symbol stream.  The membership of the
 //     significance-propagation pass is recursive (the pass itself makes neighbours significant,
 //     one column to the west or one row up) and is iterated to its fixed point with shuffles;
 //     refinement and cleanup are known outright.  The state words (layout in t1.cuh) are
 //     updated by all lanes at once afterwards;
-//   * the list goes out, one byte per symbol, to a chain of SYM_CHUNK-byte chunks taken from a
+//   * the stream is one byte per symbol in a chain of SYM_CHUNK-byte chunks taken from a
 //     device pool with an atomic counter (the host sizes the pool per sample and retries with a
 //     larger one if a frame runs it dry); the number of symbols of each pass is left in the
 //     pass record, and the distortion estimate of a pass is a warp sum of table values
@@ -474,26 +474,26 @@ static __device__ __forceinline__ void sym_close(const SymWriter& w, uint32_t ne
 		t[1] = next;
 	}
 }
-// the `total` symbols the lanes left in `list` go to the block's stream
-static __device__ __forceinline__ void sym_emit(SymWriter& w, const uint8_t* list, uint32_t total,
-												 uint32_t lane)
+// room for the `total` symbols of a stripe segment in the block's stream: the lanes write them
+// straight to their prefix-sum positions there (`sink`: where they go once the pool has run out)
+static __device__ __forceinline__ uint8_t* sym_reserve(SymWriter& w, uint32_t total, uint32_t lane,
+														uint8_t* sink)
 {
 	w.count += total;
 	if(w.dead || total == 0)
-		return;
+		return sink;
 	if(w.fill + total > SYM_PAYLOAD)
 	{
 		const uint32_t nxt = sym_alloc(w, lane);
 		if(nxt == SYM_NONE)
-			return;
+			return sink;
 		sym_close(w, nxt, lane);
 		w.chunk = nxt;
 		w.fill = 0;
 	}
 	uint8_t* dst = w.pool + (size_t)w.chunk * SYM_CHUNK + w.fill;
-	for(uint32_t i = lane; i < total; i += 32)
-		dst[i] = list[i];
 	w.fill += total;
+	return dst;
 }
 
 static __device__ __forceinline__ int32_t warp_sum(int32_t v)
@@ -544,6 +544,7 @@ static __device__ int32_t enc_sig_pass(const EBlk& b, SymWriter& sw, uint8_t* li
 				nsL = 0;
 			uint32_t total;
 			uint32_t at = warp_excl_scan((uint32_t)(__popc(mem) + __popc(ns)), lane, total);
+			uint8_t* out = sym_reserve(sw, total, lane, list);
 			const uint32_t fw = c.f | spread4(nsL, 0);
 			const uint32_t sp1 = spread4(ns, 1); // own column; a visit sees the rows above it only
 #pragma unroll
@@ -553,16 +554,14 @@ static __device__ int32_t enc_sig_pass(const EBlk& b, SymWriter& sw, uint8_t* li
 					const uint32_t low = ns & ((1u << r) - 1u);
 					const uint32_t fv = fw | (sp1 & ((1u << (3u * r + 4u)) - 1u)) | ((low & c.sgn4) << 19);
 					const uint32_t v = (c.bit4 >> r) & 1u;
-					list[at++] = (uint8_t)(b.zc[(fv >> (3 * r)) & T1_NEIGH] | (v << 5));
+					out[at++] = (uint8_t)(b.zc[(fv >> (3 * r)) & T1_NEIGH] | (v << 5));
 					if(v)
 					{
 						// the bypass coder takes the sign as it is (T1.cpp:505-508)
-						list[at++] = raw ? (uint8_t)(((c.sgn4 >> r) & 1u) << 5) : (uint8_t)sign_symbol(b, c, fv, r);
+						out[at++] = raw ? (uint8_t)(((c.sgn4 >> r) & 1u) << 5) : (uint8_t)sign_symbol(b, c, fv, r);
 						nmsedec += nmsedec_sig(b, c.mag[r], (uint32_t)bpno);
 					}
 				}
-			__syncwarp();
-			sym_emit(sw, list, total, lane);
 			const uint32_t f = c.f | spread4(ns, 1) | ((ns & c.sgn4) << 19) | (mem << 24);
 			commit_significance(b, c, f, ns, lane);
 		}
@@ -584,6 +583,7 @@ static __device__ int32_t enc_ref_pass(const EBlk& b, SymWriter& sw, uint8_t* li
 			uint32_t at = warp_excl_scan((uint32_t)__popc(ref), lane, total);
 			if(total == 0)
 				continue;
+			uint8_t* out = sym_reserve(sw, total, lane, list);
 #pragma unroll
 			for(uint32_t r = 0; r < 4; ++r)
 				if((ref >> r) & 1u)
@@ -592,12 +592,10 @@ static __device__ int32_t enc_ref_pass(const EBlk& b, SymWriter& sw, uint8_t* li
 					const uint32_t cx = (c.f & T1_MU(r))					 ? T1_CTX_MAG + 2
 										: ((c.f >> (3 * r)) & T1_NEIGH) ? T1_CTX_MAG + 1
 																		 : T1_CTX_MAG;
-					list[at++] = (uint8_t)(cx | (((c.bit4 >> r) & 1u) << 5));
+					out[at++] = (uint8_t)(cx | (((c.bit4 >> r) & 1u) << 5));
 				}
 			if(ref)
 				*c.fp = c.f | (ref << 28);
-			__syncwarp();
-			sym_emit(sw, list, total, lane);
 			__syncwarp();
 		}
 	return warp_sum(nmsedec);
@@ -629,14 +627,15 @@ static __device__ int32_t enc_cleanup_pass(const EBlk& b, SymWriter& sw, uint8_t
 				cnt = ns ? 3u + 1u + (uint32_t)(__popc(todo >> (r0 + 1)) + __popc(ns >> (r0 + 1))) : 1u;
 			uint32_t total;
 			uint32_t at = warp_excl_scan(cnt, lane, total);
+			uint8_t* out = sym_reserve(sw, total, lane, list);
 			uint32_t first = 0;
 			if(rl)
 			{
-				list[at++] = (uint8_t)(T1_CTX_AGG | ((ns ? 1u : 0u) << 5));
+				out[at++] = (uint8_t)(T1_CTX_AGG | ((ns ? 1u : 0u) << 5));
 				if(ns)
 				{
-					list[at++] = (uint8_t)(T1_CTX_UNI | ((r0 >> 1) << 5));
-					list[at++] = (uint8_t)(T1_CTX_UNI | ((r0 & 1u) << 5));
+					out[at++] = (uint8_t)(T1_CTX_UNI | ((r0 >> 1) << 5));
+					out[at++] = (uint8_t)(T1_CTX_UNI | ((r0 & 1u) << 5));
 				}
 				first = r0; // rows above r0 are zero and need no symbol
 			}
@@ -648,15 +647,13 @@ static __device__ int32_t enc_cleanup_pass(const EBlk& b, SymWriter& sw, uint8_t
 					const uint32_t fv = fw | (sp1 & ((1u << (3u * r + 4u)) - 1u)) | ((low & c.sgn4) << 19);
 					const uint32_t v = (c.bit4 >> r) & 1u;
 					if(!(rl && r == r0))
-						list[at++] = (uint8_t)(b.zc[(fv >> (3 * r)) & T1_NEIGH] | (v << 5));
+						out[at++] = (uint8_t)(b.zc[(fv >> (3 * r)) & T1_NEIGH] | (v << 5));
 					if(v)
 					{
-						list[at++] = (uint8_t)sign_symbol(b, c, fv, r);
+						out[at++] = (uint8_t)sign_symbol(b, c, fv, r);
 						nmsedec += nmsedec_sig(b, c.mag[r], (uint32_t)bpno);
 					}
 				}
-			__syncwarp();
-			sym_emit(sw, list, total, lane);
 			const uint32_t f = (c.f | spread4(ns, 1) | ((ns & c.sgn4) << 19)) & ~T1_PI_ALL;
 			commit_significance(b, c, f, ns, lane);
 		}
@@ -842,10 +839,9 @@ __global__ void __launch_bounds__(ENC_MAX_THREADS)
 					if(sty & GRKB_CBLKSTY_SEGSYM)
 					{
 						// mqc_segmark_enc, mqc_enc.cpp:327-332: 1 0 1 0 in the uniform context
+						uint8_t* out = sym_reserve(sw, 4, lane, list);
 						if(lane < 4)
-							list[lane] = (uint8_t)(T1_CTX_UNI | (((lane + 1) & 1u) << 5));
-						__syncwarp();
-						sym_emit(sw, list, 4, lane);
+							out[lane] = (uint8_t)(T1_CTX_UNI | (((lane + 1) & 1u) << 5));
 						__syncwarp();
 					}
 				}
