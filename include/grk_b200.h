@@ -389,6 +389,30 @@ void grkb_host_free(void* p);
 int grkb_bench_dwt(uint32_t w, uint32_t h, uint32_t numres, int reversible, int forward,
 				   uint32_t ncomp, int mct, uint32_t iters, uint32_t warmup, float* ms_per_iter);
 
+/* D. allocation-free door --------------------------------------------------------------------- */
+
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * allocation).  Multi-level inverse wavelet of ONE tile-component on DEVICE buffers, the same
+ * kernels and results as grkb_dwt_host(forward = 0) / grkb_decoder_*, with the two ping-pong planes
+ * of the intermediate resolutions taken from a file-scope __device__ array of
+ * GRKB_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.  The call
+ * performs no cudaMalloc / cudaFree / allocating library routine; it enqueues on `stream`
+ * (a cudaStream_t; NULL = the default stream) and returns without synchronising.
+ *   coeff   device: dequantised coefficients, tile buffer layout, coeff_stride samples per row
+ *           (read only)
+ *   image   device: receives the (x1-x0) x (y1-y0) samples, image_stride samples per row; must not
+ *           alias coeff
+ * Limit: 2 x stride32(ceil(w/2)) x ceil(h/2) x 4 bytes <= GRKB_NOALLOC_SCRATCH_BYTES, i.e.
+ * tile-components up to 2048 x 2048; larger ones return -2 with a message in grkb_last_error().
+ * All calls on one GPU share the array: calls that overlap on the GPU (different streams, or
+ * different threads without ordering) race -- serialise them.  Nothing in the array has to start
+ * at zero (every level overwrites what the next one reads), so nothing is cleared between calls. */
+#define GRKB_NOALLOC_SCRATCH_BYTES (8u << 20)
+int grkb_idwt_device_noalloc(const void* coeff, uint32_t coeff_stride, void* image,
+							 uint32_t image_stride, uint32_t x0, uint32_t y0, uint32_t x1,
+							 uint32_t y1, uint32_t numres, int reversible, void* stream);
+
 #pragma GCC visibility pop
 #ifdef __cplusplus
 }
