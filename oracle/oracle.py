@@ -424,3 +424,82 @@ def orc_ht_decode(data, missing_msbs, w, h, **kw):
 
 def ref_ht_decode(data, missing_msbs, w, h, **kw):
     return _ht_decode(True, data, missing_msbs, w, h, **kw)
+
+
+# ---------------------------------------------------------------- dequantising copy (row Q4)
+
+def _dequant(is_ref, kind, src, roishift=0, k_msbs=0, stepsize=1.0):
+    """kind 0 MQ 5/3, 1 MQ 9/7, 2 HT 5/3, 3 HT 9/7 (filters/PostDecompressFilters.h); src: int32 /
+    uint32 array as the block decoder leaves it.  Returns int32 (kinds 0, 2) or float32."""
+    s = np.ascontiguousarray(src).view(np.int32).copy()
+    d = np.zeros_like(s)
+    fn = ref().ref_dequant if is_ref else oracle().orc_dequant
+    fn(C.c_int(kind), _p(s), _p(d), C.c_uint32(s.size), C.c_uint32(roishift), C.c_uint32(k_msbs),
+       C.c_float(stepsize))
+    return d if kind in (0, 2) else d.view(np.float32)
+
+
+def orc_dequant(kind, src, **kw):
+    return _dequant(False, kind, src, **kw)
+
+
+def ref_dequant(kind, src, **kw):
+    return _dequant(True, kind, src, **kw)
+
+
+# ---------------------------------------------------------------- application-side sample loops
+
+_APPS = None
+
+
+def have_ref_apps():
+    return os.path.exists(os.path.join(HERE, "_ref", "libgrok_ref_apps.so"))
+
+
+def ref_apps():
+    """src/bin/common/convert.cpp of the reference, compiled in place (oracle/Makefile)"""
+    global _APPS
+    if _APPS is None:
+        ref()  # libgrok_ref.so first: it provides grk_image_new
+        _APPS = C.CDLL(os.path.join(HERE, "_ref", "libgrok_ref_apps.so"))
+    return _APPS
+
+
+def ref_planar_to_interleaved(planes, adjust=0):
+    a = [np.ascontiguousarray(p, dtype=np.int32).ravel() for p in planes]
+    n = a[0].size
+    out = np.zeros(n * len(a), dtype=np.int32)
+    ptrs = (C.c_void_p * len(a))(*[p.ctypes.data for p in a])
+    rc = ref_apps().ref_planar_to_interleaved(ptrs, C.c_uint32(len(a)), _p(out), C.c_size_t(n),
+                                              C.c_int32(adjust))
+    assert rc == 0
+    return out.reshape(n, len(a))
+
+
+def ref_interleaved_to_planar(inter, numcomps):
+    src = np.ascontiguousarray(inter, dtype=np.int32).ravel()
+    n = src.size // numcomps
+    out = [np.zeros(n, dtype=np.int32) for _ in range(numcomps)]
+    ptrs = (C.c_void_p * numcomps)(*[p.ctypes.data for p in out])
+    rc = ref_apps().ref_interleaved_to_planar(_p(src), ptrs, C.c_uint32(numcomps), C.c_size_t(n))
+    assert rc == 0
+    return out
+
+
+def ref_narrow(samples, bytes_per_sample):
+    """convert_tif_32sto16u / cvtFrom32_LUT[8]: int32 -> uint16 (host order) / uint8"""
+    s = np.ascontiguousarray(samples, dtype=np.int32).ravel()
+    out = np.zeros(s.size, dtype=np.uint16 if bytes_per_sample == 2 else np.uint8)
+    fn = ref_apps().ref_32s_to_16u if bytes_per_sample == 2 else ref_apps().ref_32s_to_8u
+    fn(_p(s), _p(out), C.c_size_t(s.size))
+    return out
+
+
+def ref_widen(raw, bytes_per_sample):
+    """convert_16u32s_C1R (big-endian file bytes) / cvtTo32_LUT[8]: -> int32"""
+    b = np.ascontiguousarray(raw, dtype=np.uint8).ravel()
+    n = b.size // bytes_per_sample
+    out = np.zeros(n, dtype=np.int32)
+    fn = ref_apps().ref_16u_to_32s if bytes_per_sample == 2 else ref_apps().ref_8u_to_32s
+    fn(_p(b), _p(out), C.c_size_t(n))
+    return out

@@ -15,6 +15,7 @@
 #include "T1.h"
 #include "WaveletFwd.h"
 #include "mct.h"
+#include "PostDecompressFilters.h"
 #include <atomic>
 #include <chrono>
 #include <thread>
@@ -893,4 +894,30 @@ int ref_plugin_decode(const char* infile, int32_t** planes, uint32_t numcomps, u
 	const int rc = grk_plugin_decompress(&g_dec_params, plugin_dec_cb);
 	return rc ? rc : g_dec_rc;
 }
+}
+
+/* ------------------------------------------------------------------------------------- */
+/* The dequantising copy: the reference's own filter classes (filters/PostDecompressFilters.h)
+ * instantiated on a DecompressBlockExec that carries roishift / k_msbs / stepsize, chosen as
+ * TileComponent::postProcess / postProcessHT choose them (tile/TileComponent.cpp:333-386).    */
+extern "C" int ref_dequant(int kind, int32_t* src, int32_t* dst, uint32_t n, uint32_t roishift,
+						   uint32_t k_msbs, float stepsize)
+{
+	DecompressBlockExec block;
+	block.roishift = (uint8_t)roishift;
+	block.k_msbs = (uint8_t)k_msbs;
+	block.stepsize = stepsize;
+	switch(kind * 2 + (roishift ? 1 : 0))
+	{
+		case 0: { ShiftFilter<int32_t> f(&block); f.copy(dst, src, n); break; }
+		case 1: { RoiShiftFilter<int32_t> f(&block); f.copy(dst, src, n); break; }
+		case 2: { ScaleFilter<int32_t> f(&block); f.copy(dst, src, n); break; }
+		case 3: { RoiScaleFilter<int32_t> f(&block); f.copy(dst, src, n); break; }
+		case 4: { ShiftHTFilter<int32_t> f(&block); f.copy(dst, src, n); break; }
+		case 5: { RoiShiftHTFilter<int32_t> f(&block); f.copy(dst, src, n); break; }
+		case 6: { ScaleHTFilter<int32_t> f(&block); f.copy(dst, src, n); break; }
+		case 7: { RoiScaleHTFilter<int32_t> f(&block); f.copy(dst, src, n); break; }
+		default: return -1;
+	}
+	return 0;
 }

@@ -8,9 +8,11 @@
  *                                       dest[i] = (uint16_t)pSrc[i]); 8 bits: :564-end, cvtFrom32_LUT[8]
  *   16-bit sample -> int32              common/convert.cpp:547-556  (convert_16u32s_C1R; the
  *                                       reference reads big-endian file bytes, the value is the same)
- * PARITY UNPINNED BY EXECUTION: convert.cpp belongs to the applications, not to the library
- * compiled under oracle/_ref, and needs the cmake-generated grk_apps_config.h; the loops below
- * are a restatement only.
+ * Pinned by execution: oracle/Makefile compiles the reference's convert.cpp where it lies (with a
+ * hand-written grk_apps_config.h stand-in, ref_config/) into oracle/_ref/libgrok_ref_apps.so, and
+ * tests/test_oracle_vs_ref.py compares these loops with planarToInterleaved<N>,
+ * convert_tif_32sto16u, cvtFrom32_LUT[8] and convert_16u32s_C1R called through
+ * ref_apps_harness.cpp.
  */
 #include "oracle.h"
 

@@ -77,25 +77,28 @@ def test_fused_mct_fdwt(gpu, orc, reversible, mct_on):
 
 
 @pytest.mark.parametrize("reversible", [1, 0])
-def test_full_size_roundtrip(gpu, reversible):
-    """BASELINE shape B (4096x2160, 5 levels): forward then inverse on the GPU.
-    5/3 must reproduce the input exactly.  9/7: the reference's synthesis scales high-pass
-    samples by 2/K, not 1/K (WaveletReverse.cpp:365-371; the decoder's step sizes carry the
-    other half, Quantizer.cpp:31-37), so HL and LH are halved and HH quartered in between;
-    then the round trip holds to 1e-3 relative (float lifting)."""
-    rng = np.random.default_rng(4096)
+@pytest.mark.parametrize("forward", [0, 1])
+def test_full_size_vs_oracle(gpu, orc, reversible, forward):
+    """BASELINE shape B (4096x2160, 5 levels), one component: both directions against the oracle
+    (423-CTA strip grids, every level on the bulk-copy path), bit-exact, 9/7 included."""
+    rng = np.random.default_rng(4096 + reversible * 2 + forward)
     w, h, nr = 4096, 2160, 6
     p = plane(rng, w, h, reversible, amp=30000)
-    c = gpu.stages.dwt(p, 0, 0, nr, reversible, 1)
-    if not reversible:
-        for lvl in range(nr - 1):
-            rw, rh = -((-w) >> lvl), -((-h) >> lvl)
-            lw, lh = -((-w) >> (lvl + 1)), -((-h) >> (lvl + 1))
-            c[:lh, lw:rw] *= 0.5
-            c[lh:rh, :lw] *= 0.5
-            c[lh:rh, lw:rw] *= 0.25
-    r = gpu.stages.dwt(c, 0, 0, nr, reversible, 0)
-    if reversible:
-        assert np.array_equal(p, r)
-    else:
-        assert np.max(np.abs(p - r)) <= 1e-3 * np.max(np.abs(p))
+    want = orc.orc_dwt(p, 0, 0, nr, reversible, forward)
+    got = gpu.stages.dwt(p, 0, 0, nr, reversible, forward)
+    assert same_bits(want, got)
+
+
+@pytest.mark.parametrize("reversible", [1, 0])
+def test_full_size_fused_idwt_mct_vs_oracle(gpu, orc, reversible):
+    """the decoder back end of shape B as the frame runs it: three components per launch, inverse
+    RCT / ICT + DC shift + clamp fused into the last level"""
+    rng = np.random.default_rng(2160 + reversible)
+    w, h, nr, prec = 4096, 2160, 6, 12
+    pl = [plane(rng, w, h, reversible, amp=3000) for _ in range(3)]
+    sh, lo, hi = [1 << (prec - 1)] * 3, [0] * 3, [(1 << prec) - 1] * 3
+    stage = [orc.orc_dwt(p, 0, 0, nr, reversible, 0) for p in pl]
+    want = orc.orc_mct_inv([s.view(np.int32) for s in stage], 0 if reversible else 1, 1, [prec] * 3,
+                           [0] * 3, sh)
+    got = gpu.stages.idwt_mct(pl, 0, 0, nr, reversible, 1, sh, lo, hi)
+    assert all(np.array_equal(a, b) for a, b in zip(want, got))

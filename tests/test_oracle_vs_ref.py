@@ -223,3 +223,75 @@ def test_ht_encode_matches_reference(orc):
                     assert O.ref_ht_encode(smp, mm) == O.orc_ht_encode(smp, mm), (w, h, bits, dens, mm)
                     n += 1
     assert n > 1000
+
+
+# ---------------------------------------------------------------- dequantising copy (row Q4, ROI)
+
+@pytest.mark.parametrize("kind", [0, 1, 2, 3])
+@pytest.mark.parametrize("roishift", [0, 1, 5, 9, 14])
+def test_dequant_filters(orc, kind, roishift):
+    """oracle/dequant.c == the reference's own filter classes (PostDecompressFilters.h:7-177),
+    ROI forms included; magnitudes on both sides of 2^roishift, both signs, zero"""
+    rng = np.random.default_rng(900 + kind * 31 + roishift)
+    n = 4096
+    if kind < 2:
+        bits = rng.integers(1, 26, size=n)
+        v = (rng.integers(0, 1 << 26, size=n) >> (26 - bits)).astype(np.int64)
+        v = np.where(rng.random(n) < 0.5, -v, v).astype(np.int32)
+        edge = np.array([0, 1, -1, (1 << roishift) - 1, 1 << roishift, -(1 << roishift),
+                         -(1 << roishift) + 1, (1 << roishift) + 1], dtype=np.int32)
+        v[:edge.size] = edge
+        k_msbs = 0
+    else:
+        k_msbs = int(rng.integers(0, 28))
+        mag = rng.integers(0, 1 << 31, size=n, dtype=np.int64)
+        mag >>= rng.integers(0, 31, size=n)
+        sign = np.where(rng.random(n) < 0.5, 0x80000000, 0)
+        v = (mag | sign).astype(np.uint32).view(np.int32)
+    for step in (1.0, 0.0009765625, 3.1415927):
+        r = O.ref_dequant(kind, v, roishift=roishift, k_msbs=k_msbs, stepsize=step)
+        o = O.orc_dequant(kind, v, roishift=roishift, k_msbs=k_msbs, stepsize=step)
+        assert same_bits(r, o), (kind, roishift, step)
+
+
+# ---------------------------------------------------------------- narrow samples (row N3)
+
+needs_apps = pytest.mark.skipif(not O.have_ref_apps(), reason="reference convert.cpp not compiled")
+
+
+@needs_apps
+@pytest.mark.parametrize("numcomps", [1, 3, 4])
+@pytest.mark.parametrize("bytes_per_sample", [2, 1])
+def test_samples_pack_vs_reference_convert(orc, numcomps, bytes_per_sample):
+    """oracle/samples.c == planarToInterleaved<N> (convert.cpp:397-405) followed by
+    convert_tif_32sto16u (:1158-1163) / cvtFrom32_LUT[8], including values beyond the narrow range
+    (the reference's loops are C casts: they wrap)"""
+    rng = np.random.default_rng(41 + numcomps)
+    H, W = 19, 37
+    dt = np.uint16 if bytes_per_sample == 2 else np.uint8
+    lim = 1 << (8 * bytes_per_sample)
+    planes = [rng.integers(-lim, 2 * lim, size=(H, W)).astype(np.int32) for _ in range(numcomps)]
+    inter = O.ref_planar_to_interleaved(planes)                       # (H*W, numcomps) int32
+    want_inter = O.ref_narrow(inter, bytes_per_sample).reshape(H, W, numcomps)
+    got_inter = O.orc_pack_samples(planes, dt, interleaved=True)
+    assert np.array_equal(got_inter, want_inter)
+    want_planar = np.stack([O.ref_narrow(p, bytes_per_sample).reshape(H, W) for p in planes])
+    assert np.array_equal(O.orc_pack_samples(planes, dt, interleaved=False), want_planar)
+
+
+@needs_apps
+@pytest.mark.parametrize("numcomps", [1, 3])
+@pytest.mark.parametrize("bytes_per_sample", [2, 1])
+def test_samples_unpack_vs_reference_convert(orc, numcomps, bytes_per_sample):
+    """oracle/samples.c == convert_16u32s_C1R (convert.cpp:547-556, big-endian file bytes) /
+    cvtTo32_LUT[8] followed by interleavedToPlanar<N> (:360-384)"""
+    rng = np.random.default_rng(43 + numcomps)
+    H, W = 11, 29
+    dt = np.uint16 if bytes_per_sample == 2 else np.uint8
+    packed = rng.integers(0, 1 << (8 * bytes_per_sample), size=(H, W, numcomps)).astype(dt)
+    file_bytes = packed.astype(">u2").tobytes() if bytes_per_sample == 2 else packed.tobytes()
+    wide = O.ref_widen(np.frombuffer(file_bytes, dtype=np.uint8), bytes_per_sample)
+    want = [p.reshape(H, W) for p in O.ref_interleaved_to_planar(wide, numcomps)]
+    got = O.orc_unpack_samples(packed, W, interleaved=True)
+    for a, b in zip(want, got):
+        assert np.array_equal(a, b)
