@@ -1,0 +1,158 @@
+"""numpy-facing wrappers of the codestream-level C-ABI (include/grk_b200.h, section E): the
+codestream index, per-tile T2 (descriptor tables from packet headers) and the whole-image
+decompressor.  No codec arithmetic here."""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import lib, check, TileParams, GrokB200Error
+from . import tile as T
+
+_u32, _vp = C.c_uint32, C.c_void_p
+
+
+class CodestreamInfo(C.Structure):
+    """grkb_codestream_info"""
+    _fields_ = [("x0", _u32), ("y0", _u32), ("x1", _u32), ("y1", _u32), ("tile_x0", _u32),
+                ("tile_y0", _u32), ("tile_w", _u32), ("tile_h", _u32), ("tiles_x", _u32),
+                ("tiles_y", _u32), ("numcomps", _u32), ("prec", C.c_uint8 * 4), ("sgnd", C.c_uint8 * 4),
+                ("numres", _u32), ("numlayers", _u32), ("prog_order", _u32), ("reversible", _u32),
+                ("mct", _u32), ("cblkw_exp", _u32), ("cblkh_exp", _u32), ("cblk_sty", _u32),
+                ("csty", _u32), ("ht", _u32), ("truncated", _u32), ("rsiz", _u32), ("tile_parts", _u32)]
+
+
+class TileTables(C.Structure):
+    """grkb_tile_tables"""
+    _fields_ = [("params", TileParams), ("blocks", _vp), ("nblocks", _u32), ("segs", _vp),
+                ("nsegs", _u32), ("bytes", _vp), ("nbytes", C.c_size_t), ("zero_copy", _u32),
+                ("packets", _u32), ("truncated", _u32)]
+
+
+lib.grkb_codestream_open.argtypes = [_vp, C.c_size_t, C.POINTER(_vp)]
+lib.grkb_codestream_close.argtypes = [_vp]
+lib.grkb_codestream_close.restype = None
+lib.grkb_codestream_get_info.argtypes = [_vp, C.POINTER(CodestreamInfo)]
+lib.grkb_codestream_parse_tile.argtypes = [_vp, _u32, _u32, _u32, C.POINTER(TileTables)]
+lib.grkb_decompressor_create.argtypes = [C.c_int, _u32, C.POINTER(_vp)]
+lib.grkb_decompressor_destroy.argtypes = [_vp]
+lib.grkb_decompressor_destroy.restype = None
+lib.grkb_decompress_submit.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _vp, _u32]
+lib.grkb_decompress_submit_packed.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _vp, _u32, C.c_size_t]
+lib.grkb_decompress_wait.argtypes = [_vp, C.POINTER(_u32)]
+lib.grkb_decompress.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _vp, _u32, C.POINTER(_u32)]
+lib.grkb_decompress_stats.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(_u32)]
+
+
+def _ceildivpow2(a, b):
+    return (a + (1 << b) - 1) >> b
+
+
+class Codestream:
+    """grkb_codestream over a uint8 array (kept alive here)"""
+
+    def __init__(self, data):
+        self.data = np.ascontiguousarray(data, dtype=np.uint8)
+        self.h = _vp()
+        check(lib.grkb_codestream_open(self.data.ctypes.data, self.data.size, C.byref(self.h)),
+              "grkb_codestream_open")
+        self.info = CodestreamInfo()
+        check(lib.grkb_codestream_get_info(self.h, C.byref(self.info)), "grkb_codestream_get_info")
+
+    def close(self):
+        if self.h:
+            lib.grkb_codestream_close(self.h)
+            self.h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def num_tiles(self):
+        return self.info.tiles_x * self.info.tiles_y
+
+    def image_size(self, reduce=0):
+        """(width, height) of the image the decompressor delivers, sized as the reference sizes its
+        grk_image: ceil(width / 2^reduce) (codestream/markers/SIZMarker.cpp:54-57)"""
+        i = self.info
+        return _ceildivpow2(i.x1 - i.x0, reduce), _ceildivpow2(i.y1 - i.y0, reduce)
+
+    def parse_tile(self, tileno, reduce=0, max_layers=0):
+        """T2 of one tile -> dict(params, blocks, segs, data, zero_copy, packets, truncated); the
+        arrays are copies (the C tables live until the next parse of that tile)"""
+        t = TileTables()
+        check(lib.grkb_codestream_parse_tile(self.h, tileno, reduce, max_layers, C.byref(t)),
+              "grkb_codestream_parse_tile")
+
+        def arr(ptr, n, dt):
+            if not n:
+                return np.zeros(0, dtype=dt)
+            buf = (C.c_uint8 * (n * dt.itemsize)).from_address(ptr)
+            return np.frombuffer(buf, dtype=dt, count=n).copy()
+
+        p = TileParams()
+        C.memmove(C.byref(p), C.byref(t.params), C.sizeof(TileParams))
+        data = arr(t.bytes, t.nbytes, np.dtype(np.uint8))
+        return dict(params=p, blocks=arr(t.blocks, t.nblocks, T.CBLK_DTYPE), segs=arr(t.segs, t.nsegs, T.SEG_DTYPE),
+                    data=np.concatenate([data, np.zeros(16, np.uint8)]), zero_copy=bool(t.zero_copy),
+                    packets=t.packets, truncated=bool(t.truncated),
+                    shape=(p.y1 - p.y0, p.x1 - p.x0))
+
+
+class Decompressor:
+    """grkb_decompressor: whole codestreams -> host planes on one device"""
+
+    def __init__(self, device=0, slots=2):
+        self.h = _vp()
+        check(lib.grkb_decompressor_create(device, slots, C.byref(self.h)), "grkb_decompressor_create")
+
+    def close(self):
+        if self.h:
+            lib.grkb_decompressor_destroy(self.h)
+            self.h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def submit(self, data, out, reduce=0, max_layers=0):
+        """data: uint8 array (whole codestream or JP2 file); out: list of int32 (H, stride) planes"""
+        nc = len(out)
+        ptrs = (_vp * nc)(*[o.ctypes.data for o in out])
+        self._keep = (data, out, ptrs)
+        check(lib.grkb_decompress_submit(self.h, data.ctypes.data, data.size, reduce, max_layers, ptrs,
+                                         out[0].strides[0] // 4), "grkb_decompress_submit")
+
+    def submit_packed(self, data, out, numcomps, interleaved=False, reduce=0, max_layers=0):
+        H = out.shape[0] if interleaved else out.shape[1]
+        fmt, row_bytes = T.sample_format(out, interleaved, numcomps, H)
+        self._keep = (data, out, None)
+        check(lib.grkb_decompress_submit_packed(self.h, data.ctypes.data, data.size, reduce, max_layers,
+                                                out.ctypes.data, fmt, row_bytes), "grkb_decompress_submit_packed")
+
+    def wait(self):
+        rej = _u32()
+        check(lib.grkb_decompress_wait(self.h, C.byref(rej)), "grkb_decompress_wait")
+        self.rejected = rej.value
+        keep, self._keep = self._keep, None
+        return keep[1]
+
+    def decode(self, data, reduce=0, max_layers=0):
+        """synchronous: returns a list of int32 planes of the (reduced) image"""
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        cs = Codestream(data)
+        w, h = cs.image_size(reduce)
+        nc = cs.info.numcomps
+        cs.close()
+        out = [np.zeros((h, w), dtype=np.int32) for _ in range(nc)]
+        self.submit(data, out, reduce, max_layers)
+        return self.wait()
+
+    def stats(self):
+        ms, n = C.c_double(), _u32()
+        check(lib.grkb_decompress_stats(self.h, C.byref(ms), C.byref(n)), "grkb_decompress_stats")
+        return dict(t2_ms=ms.value, tiles=n.value)

@@ -10,7 +10,7 @@
 //   band window placement           src/lib/jp2/tile/TileComponentWindowBuffer.h:188-221
 // (ISO/IEC 15444-1 B.5-B.7) so that descriptor tables built here address the same samples as
 // the reference's DecompressBlockExec / CompressBlockExec lists.
-#include "../../include/grk_b200.h"
+#include "geometry.h"
 #include <algorithm>
 
 namespace
@@ -54,6 +54,12 @@ R isect(R a, R b)
 extern "C" int grkb_tile_layout(const grkb_layout_params* p, grkb_cblk_geom* out, uint32_t cap,
 								 uint32_t* count)
 {
+	return grkb_layout_walk(p, out, cap, count, nullptr);
+}
+
+int grkb_layout_walk(const grkb_layout_params* p, grkb_cblk_geom* out, uint32_t cap, uint32_t* count,
+					 grkb_layout_index* idx)
+{
 	if(!p || !count || p->numres == 0 || p->numres > 33 || p->x1 < p->x0 || p->y1 < p->y0)
 		return -1;
 	const R tc{p->x0, p->y0, p->x1, p->y1};
@@ -68,6 +74,21 @@ extern "C" int grkb_tile_layout(const grkb_layout_params* p, grkb_cblk_geom* out
 		const uint64_t px1 = (uint64_t)cdp2(res.x1, pwe) << pwe, py1 = (uint64_t)cdp2(res.y1, phe) << phe;
 		const uint32_t gw = res.x0 == res.x1 ? 0 : (uint32_t)((px1 - px0) >> pwe);
 		const uint32_t gh = res.y0 == res.y1 ? 0 : (uint32_t)((py1 - py0) >> phe);
+		if(idx)
+		{
+			grkb_layout_res lr{};
+			lr.gw = gw;
+			lr.gh = gh;
+			lr.pwe = pwe;
+			lr.phe = phe;
+			lr.x0 = res.x0;
+			lr.y0 = res.y0;
+			lr.x1 = res.x1;
+			lr.y1 = res.y1;
+			lr.first_pb = (uint32_t)idx->pb.size();
+			lr.nbands = resno ? 3 : 1;
+			idx->res.push_back(lr);
+		}
 		// in band coordinates the partition is halved for resno > 0
 		uint32_t sx = px0, sy = py0;
 		if(resno)
@@ -90,6 +111,8 @@ extern "C" int grkb_tile_layout(const grkb_layout_params* p, grkb_cblk_geom* out
 				const uint32_t gx0 = fdp2(prec.x0, cwe), gy0 = fdp2(prec.y0, che);
 				const uint32_t gx1 = cdp2(prec.x1, cwe), gy1 = cdp2(prec.y1, che);
 				const uint32_t cgw = gx1 - gx0, cgh = gy1 - gy0;
+				if(idx)
+					idx->pb.push_back(grkb_layout_pb{n, cgw, cgh, band.empty() ? 1u : 0u});
 				for(uint64_t cb = 0; cb < (uint64_t)cgw * cgh; ++cb)
 				{
 					const uint32_t bx = (gx0 + (uint32_t)(cb % cgw)) << cwe, by = (gy0 + (uint32_t)(cb / cgw)) << che;

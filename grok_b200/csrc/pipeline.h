@@ -39,4 +39,12 @@ int grkb_launch_unpack_samples(const void* packed, size_t row_bytes, uint32_t fo
 size_t grkb_samples_min_row_bytes(uint32_t format, uint32_t W, uint32_t numcomps);
 size_t grkb_samples_bytes(uint32_t format, uint32_t H, uint32_t numcomps, size_t row_bytes);
 
+// grkb_decoder_submit_packed into a rectangle of a larger packed image (tile.cu)
+struct grkb_decoder;
+struct grkb_cblk;
+struct grkb_seg;
+int grkb_decoder_submit_packed_region(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
+									  const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
+									  void* out, uint32_t format, size_t row_bytes, size_t plane_bytes);
+
 void grkb_set_error(const char* fmt, ...);

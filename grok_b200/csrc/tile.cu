@@ -40,7 +40,7 @@ struct grkb_decoder
 	uint32_t nblocks = 0, nsegs = 0;
 	uint32_t max_area = 0, max_flag_words = 0, max_ht_w = 0;
 	bool any_mq = false, any_ht = false, ht_refine = false;
-	cudaEvent_t ev[6] = {};
+	cudaEvent_t ev[7] = {};
 	void* packed = nullptr; // narrow output (row N3), allocated on first use
 	size_t packed_cap = 0;
 };
@@ -324,6 +324,7 @@ void grkb_decoder_destroy(grkb_decoder* d)
 	cudaFree(d->d_bytes);
 	cudaFree(d->d_order);
 	cudaFree(d->d_counters);
+	cudaFree(d->packed);
 	if(d->h_order)
 		cudaFreeHost(d->h_order);
 	if(d->h_status)
@@ -406,6 +407,18 @@ int grkb_decoder_submit_packed(grkb_decoder* d, const grkb_cblk* blocks, uint32_
 							   const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
 							   void* out, uint32_t format, size_t row_bytes)
 {
+	return grkb_decoder_submit_packed_region(d, blocks, nblocks, segs, nsegs, bytes, nbytes, out, format, row_bytes,
+											 0);
+}
+
+} // extern "C"
+
+// plane_bytes: distance between the component planes of a planar `out` (0: H rows, the tile is the
+// whole buffer).  With it a tile lands in its rectangle of a larger image buffer.
+int grkb_decoder_submit_packed_region(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks,
+									  const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
+									  void* out, uint32_t format, size_t row_bytes, size_t plane_bytes)
+{
 	if(!d || !out)
 	{
 		grkb_set_error("grkb_decoder_submit_packed: null argument");
@@ -415,6 +428,7 @@ int grkb_decoder_submit_packed(grkb_decoder* d, const grkb_cblk* blocks, uint32_
 	const uint32_t width = (base == GRKB_SAMPLES_16 || base == GRKB_SAMPLES_16_INTERLEAVED) ? 16
 						   : (base == GRKB_SAMPLES_8 || base == GRKB_SAMPLES_8_INTERLEAVED)   ? 8
 																							   : 0;
+	const bool interleaved = base == GRKB_SAMPLES_16_INTERLEAVED || base == GRKB_SAMPLES_8_INTERLEAVED;
 	if(width == 0 || row_bytes < grkb_samples_min_row_bytes(format, d->W, d->p.numcomps))
 	{
 		grkb_set_error("grkb_decoder_submit_packed: bad format %u or rows of %zu bytes", format, row_bytes);
@@ -434,7 +448,10 @@ int grkb_decoder_submit_packed(grkb_decoder* d, const grkb_cblk* blocks, uint32_
 		}
 	}
 	GRKB_CUDA_CHECK(cudaSetDevice(d->device));
-	const size_t total = grkb_samples_bytes(format, d->H, d->p.numcomps, row_bytes);
+	// on the device the tile is packed densely (rows of `need` bytes rounded up to 16)
+	const size_t need = grkb_samples_min_row_bytes(format, d->W, d->p.numcomps);
+	const size_t drow = plane_bytes ? ((need + 15) & ~(size_t)15) : row_bytes;
+	const size_t total = grkb_samples_bytes(format, d->H, d->p.numcomps, drow);
 	if(total > d->packed_cap)
 	{
 		if(d->packed)
@@ -447,10 +464,18 @@ int grkb_decoder_submit_packed(grkb_decoder* d, const grkb_cblk* blocks, uint32_
 	if(submit_front(d, blocks, nblocks, segs, nsegs, bytes, nbytes))
 		return -1;
 	cudaStream_t s = d->stream;
-	if(grkb_launch_pack_samples(d->image, d->p.numcomps, d->stride, d->W, d->H, format, d->packed, row_bytes, s))
+	if(grkb_launch_pack_samples(d->image, d->p.numcomps, d->stride, d->W, d->H, format, d->packed, drow, s))
 		return -1;
+	if(plane_bytes)
+	{
+		const uint32_t nplanes = interleaved ? 1 : d->p.numcomps;
+		for(uint32_t c = 0; c < nplanes; ++c)
+			GRKB_CUDA_CHECK(cudaMemcpy2DAsync((uint8_t*)out + (size_t)c * plane_bytes, row_bytes,
+											  (const uint8_t*)d->packed + (size_t)c * d->H * drow, drow, need, d->H,
+											  cudaMemcpyDeviceToHost, s));
+		return 0;
+	}
 	// padding between the caller's rows stays untouched
-	const size_t need = grkb_samples_min_row_bytes(format, d->W, d->p.numcomps);
 	if(need == row_bytes)
 		GRKB_CUDA_CHECK(cudaMemcpyAsync(out, d->packed, total, cudaMemcpyDeviceToHost, s));
 	else
@@ -458,6 +483,8 @@ int grkb_decoder_submit_packed(grkb_decoder* d, const grkb_cblk* blocks, uint32_
 										  cudaMemcpyDeviceToHost, s));
 	return 0;
 }
+
+extern "C" {
 
 int grkb_decoder_wait(grkb_decoder* d, uint32_t* status_out)
 {
@@ -513,8 +540,7 @@ int grkb_decoder_time_device(grkb_decoder* d, uint32_t iters, uint32_t warmup, f
 		if(run_device(d, d->coeff, d->stride, true, nullptr, nullptr))
 			return -1;
 	// whole passes back to back between two events
-	cudaEvent_t t0 = d->ev[5], t1;
-	GRKB_CUDA_CHECK(cudaEventCreate(&t1));
+	cudaEvent_t t0 = d->ev[5], t1 = d->ev[6];
 	GRKB_CUDA_CHECK(cudaEventRecord(t0, s));
 	for(uint32_t i = 0; i < iters; ++i)
 	{
@@ -526,7 +552,6 @@ int grkb_decoder_time_device(grkb_decoder* d, uint32_t iters, uint32_t warmup, f
 	GRKB_CUDA_CHECK(cudaEventSynchronize(t1));
 	float total = 0;
 	GRKB_CUDA_CHECK(cudaEventElapsedTime(&total, t0, t1));
-	cudaEventDestroy(t1);
 	ms[0] = total / (float)iters;
 	// stage shares: the same passes again, each bracketed by its own events
 	double t_t1 = 0, t_dwt = 0, t_last = 0;

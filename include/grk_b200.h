@@ -389,6 +389,96 @@ void grkb_host_free(void* p);
 int grkb_bench_dwt(uint32_t w, uint32_t h, uint32_t numres, int reversible, int forward,
 				   uint32_t ncomp, int mct, uint32_t iters, uint32_t warmup, float* ms_per_iter);
 
+/* E. codestream level: T2 on our side ------------------------------------ */
+
+/* Everything below parses JPEG 2000 codestreams itself (markers, tile parts, packet headers), so
+ * that a whole image -- any number of tiles, layers, precincts, any progression order, POC, SOP /
+ * EPH, several tile parts per tile -- goes from coded bytes to samples without the reference's T2.
+ * It replaces, on the decode side, grk_decompress_read_header + grk_decompress
+ * (src/lib/jp2/grok.h:1305-1345) up to the int32 planes of grk_image:
+ * CodeStreamDecompress::readHeader / the marker readers (codestream/CodeStreamDecompress.cpp:
+ * 1148-1860, codestream/markers/SIZMarker.cpp, SOTMarker.cpp), T2Decompress (t2/T2Decompress.cpp:
+ * 28-566), PacketIter (t2/PacketIter.cpp:55-355), TagTree (t2/TagTree.h), BitIO (t2/BitIO.cpp) and the
+ * tile compositing of CodeStreamDecompress::decompressTiles (:412-640).  Refused (error, nothing
+ * decoded): sub-sampled components, more than GRKB_MAX_COMPS components, component-specific COC
+ * geometry, PPM / PPT packed headers. */
+typedef struct grkb_codestream grkb_codestream;
+
+typedef struct grkb_codestream_info
+{
+	uint32_t x0, y0, x1, y1; /* image area on the reference grid (SIZ) */
+	uint32_t tile_x0, tile_y0, tile_w, tile_h; /* tile grid origin and nominal tile size */
+	uint32_t tiles_x, tiles_y;
+	uint32_t numcomps;
+	uint8_t prec[GRKB_MAX_COMPS], sgnd[GRKB_MAX_COMPS];
+	/* main-header COD */
+	uint32_t numres, numlayers, prog_order, reversible, mct, cblkw_exp, cblkh_exp, cblk_sty, csty;
+	uint32_t ht; /* 1: HT block coder */
+	uint32_t truncated; /* 1: the buffer ends inside a tile part */
+	uint32_t rsiz;
+	uint32_t tile_parts; /* tile-part bodies indexed */
+} grkb_codestream_info;
+
+/* Reads the main header and indexes all tile parts of a raw codestream or a JP2 file (the jp2c box
+ * is located).  `data` must stay valid and unchanged until grkb_codestream_close. */
+int grkb_codestream_open(const uint8_t* data, size_t len, grkb_codestream** out);
+void grkb_codestream_close(grkb_codestream* cs);
+int grkb_codestream_get_info(const grkb_codestream* cs, grkb_codestream_info* info);
+
+/* The descriptor tables of one tile after T2: what grkb_decoder_submit takes.  With zero_copy the
+ * byte pool is a range of the caller's own buffer (every block's bytes are one run of the
+ * codestream: any single-layer stream); otherwise the bytes were gathered into memory the
+ * codestream object owns.  The tables stay valid until the tile is parsed again or the object is
+ * closed. */
+typedef struct grkb_tile_tables
+{
+	grkb_tile_params params; /* the tile the decoder sees: reduced rectangle, kept resolutions */
+	const grkb_cblk* blocks;
+	uint32_t nblocks;
+	const grkb_seg* segs;
+	uint32_t nsegs;
+	const uint8_t* bytes;
+	size_t nbytes;
+	uint32_t zero_copy, packets, truncated;
+} grkb_tile_tables;
+
+/* T2 of one tile.  reduce: highest resolutions to leave out (cp_reduce of the reference,
+ * tile/TileProcessor.cpp:288-317: the tile shrinks to ceil(rect / 2^reduce)); max_layers: quality
+ * layers to keep, 0 = all.  Tiles may be parsed from different threads at once. */
+int grkb_codestream_parse_tile(grkb_codestream* cs, uint32_t tileno, uint32_t reduce, uint32_t max_layers,
+							   grkb_tile_tables* out);
+
+/* Whole image: the device side of grk_decompress.  A decompressor owns `slots` tile decoders on
+ * one device (decoders are cached per tile geometry), so the tiles of an image -- or, with one
+ * slot per frame and several decompressors, several frames -- are in flight together. */
+typedef struct grkb_decompressor grkb_decompressor;
+int grkb_decompressor_create(int device, uint32_t slots, grkb_decompressor** out);
+void grkb_decompressor_destroy(grkb_decompressor* d);
+
+/* Parses `data` and enqueues every tile: H2D of its tables and bytes, T1, wavelet, MCT, D2H of its
+ * rectangle into the output.  Returns once the last tile is enqueued; grkb_decompress_wait blocks
+ * until all are done.  data, planes / out must stay valid until then (page-locked memory from
+ * grkb_host_alloc makes the copies asynchronous).
+ *   planes[c], stride   int32 planes of the (reduced) image, sized as the reference sizes its
+ *                       grk_image: ceil((x1-x0)/2^r) x ceil((y1-y0)/2^r) (codestream/markers/
+ *                       SIZMarker.cpp:54-57).  The tiles cover ceil(x1/2^r)-ceil(x0/2^r) of it; a
+ *                       last row / column beyond that is left as the caller gave it (the reference
+ *                       leaves zeros)
+ * rejected_out: code blocks the block decoders refused (they decode as zeros). */
+int grkb_decompress_submit(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,
+						   uint32_t max_layers, int32_t* const* planes, uint32_t stride);
+/* The same with the samples narrowed on the device (GRKB_SAMPLES_16 / _8, planar or interleaved;
+ * opt-in): `out` holds grkb_samples_size(format, H, numcomps, row_bytes) bytes of the
+ * whole (reduced) image. */
+int grkb_decompress_submit_packed(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,
+								  uint32_t max_layers, void* out, uint32_t format, size_t row_bytes);
+int grkb_decompress_wait(grkb_decompressor* d, uint32_t* rejected_out);
+/* submit + wait */
+int grkb_decompress(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,
+					uint32_t max_layers, int32_t* const* planes, uint32_t stride, uint32_t* rejected_out);
+/* host milliseconds the last submit spent in marker + packet parsing (T2), and tiles enqueued */
+int grkb_decompress_stats(const grkb_decompressor* d, double* t2_ms, uint32_t* tiles);
+
 /* D. allocation-free door --------------------------------------------------------------------- */
 
 /* No counterpart in the reference: added for callers that

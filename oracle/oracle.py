@@ -503,3 +503,16 @@ def ref_widen(raw, bytes_per_sample):
     fn = ref_apps().ref_16u_to_32s if bytes_per_sample == 2 else ref_apps().ref_8u_to_32s
     fn(_p(b), _p(out), C.c_size_t(n))
     return out
+
+
+# ---------------------------------------------------------------- encoder / decoder switches
+
+def ref_set_encode_options(opts=""):
+    """further grk_compress switches for the next reference encodes ('prog=RPCL;rates=20:10:1;
+    prc=128x128;sop;eph;tp=R;poc=...;cinema=4k24;roi=0:5;off=3:5' ...; see ref_harness.cpp)"""
+    ref().ref_set_encode_options(opts.encode())
+
+
+def ref_set_decode_options(reduce=0, layers=0):
+    """cp_reduce / cp_layer of the next ref_codec_decode calls"""
+    ref().ref_set_decode_options(C.c_uint32(reduce), C.c_uint32(layers))

@@ -454,6 +454,152 @@ void ref_set_rate(double ratio)
 	g_layer_rate = ratio;
 }
 
+/* Further encoder parameters for the next encodes, as a comma-free list of key=value pairs separated
+ * by ';' -- the switches of grk_compress that the tests need, set on grk_cparameters the way the
+ * CLI sets them (src/bin/jp2/grk_compress.cpp:820-1400):
+ *   prog=LRCP|RLCP|RPCL|PCRL|CPRL     -p          rates=20:10:1         -r (layers)
+ *   prc=256x256:128x128               -c          sop / eph             -S / -E
+ *   tp=R|L|C                          -u          plt / tlm             -L / -X
+ *   poc=0,0,1,3,3,CPRL/3,0,1,6,3,CPRL -P (resS,compS,layE,resE,compE,order per record)
+ *   cinema=4k24|4k48|2k24|2k48        -x / -w     roi=c:s               -R
+ *   sty=N   (code-block style bits)   -M          gbits=N               -N
+ *   off=x0:y0 (image offset)          -d          torg=x0:y0 (tile origin) -T
+ *   mct=0|1                           -Y                                                       */
+static std::string g_enc_opts;
+void ref_set_encode_options(const char* opts)
+{
+	g_enc_opts = opts ? opts : "";
+}
+static GRK_PROG_ORDER prog_by_name(const std::string& v)
+{
+	if(v == "RLCP")
+		return GRK_RLCP;
+	if(v == "RPCL")
+		return GRK_RPCL;
+	if(v == "PCRL")
+		return GRK_PCRL;
+	if(v == "CPRL")
+		return GRK_CPRL;
+	return GRK_LRCP;
+}
+static void apply_encode_options(grk_cparameters& p)
+{
+	size_t i = 0;
+	while(i < g_enc_opts.size())
+	{
+		size_t j = g_enc_opts.find(';', i);
+		if(j == std::string::npos)
+			j = g_enc_opts.size();
+		std::string kv = g_enc_opts.substr(i, j - i);
+		i = j + 1;
+		const size_t eq = kv.find('=');
+		const std::string k = kv.substr(0, eq), v = eq == std::string::npos ? "" : kv.substr(eq + 1);
+		if(k == "prog")
+			p.prog_order = prog_by_name(v);
+		else if(k == "rates")
+		{
+			p.numlayers = 0;
+			size_t a = 0;
+			while(a <= v.size() && p.numlayers < 100)
+			{
+				size_t b = v.find(':', a);
+				if(b == std::string::npos)
+					b = v.size();
+				p.layer_rate[p.numlayers++] = atof(v.substr(a, b - a).c_str());
+				a = b + 1;
+			}
+			p.allocationByRateDistoration = true;
+		}
+		else if(k == "prc")
+		{
+			p.res_spec = 0;
+			size_t a = 0;
+			while(a <= v.size() && p.res_spec < GRK_J2K_MAXRLVLS)
+			{
+				size_t b = v.find(':', a);
+				if(b == std::string::npos)
+					b = v.size();
+				unsigned w = 0, h = 0;
+				if(sscanf(v.substr(a, b - a).c_str(), "%ux%u", &w, &h) == 2)
+				{
+					p.prcw_init[p.res_spec] = w;
+					p.prch_init[p.res_spec] = h;
+					p.res_spec++;
+				}
+				a = b + 1;
+			}
+			p.csty |= 0x01;
+		}
+		else if(k == "sop")
+			p.csty |= 0x02;
+		else if(k == "eph")
+			p.csty |= 0x04;
+		else if(k == "tp")
+		{
+			p.newTilePartProgressionDivider = (uint8_t)v[0];
+			p.enableTilePartGeneration = true;
+		}
+		else if(k == "plt")
+			p.writePLT = true;
+		else if(k == "tlm")
+			p.writeTLM = true;
+		else if(k == "poc")
+		{
+			uint32_t n = 0;
+			size_t a = 0;
+			while(a <= v.size() && n < GRK_J2K_MAXRLVLS)
+			{
+				size_t b = v.find('/', a);
+				if(b == std::string::npos)
+					b = v.size();
+				unsigned rs, cs_, le, re, ce;
+				char name[8] = {};
+				if(sscanf(v.substr(a, b - a).c_str(), "%u,%u,%u,%u,%u,%4s", &rs, &cs_, &le, &re, &ce, name) == 6)
+				{
+					auto& g = p.progression[n++];
+					g.tileno = 0;
+					g.resS = (uint8_t)rs;
+					g.compS = (uint16_t)cs_;
+					g.layE = (uint16_t)le;
+					g.resE = (uint8_t)re;
+					g.compE = (uint16_t)ce;
+					g.specifiedCompressionPocProg = prog_by_name(name);
+				}
+				a = b + 1;
+			}
+			p.numpocs = n ? n - 1 : 0;
+		}
+		else if(k == "cinema")
+		{
+			const bool k4 = v.substr(0, 2) == "4k", f48 = v.size() >= 4 && v.substr(2) == "48";
+			p.rsiz = k4 ? GRK_PROFILE_CINEMA_4K : GRK_PROFILE_CINEMA_2K;
+			p.max_comp_size = f48 ? GRK_CINEMA_48_COMP : GRK_CINEMA_24_COMP;
+			p.max_cs_size = f48 ? GRK_CINEMA_48_CS : GRK_CINEMA_24_CS;
+			p.framerate = f48 ? 48 : 24;
+		}
+		else if(k == "roi")
+		{
+			int c = 0;
+			unsigned sh = 0;
+			if(sscanf(v.c_str(), "%d:%u", &c, &sh) == 2)
+			{
+				p.roi_compno = c;
+				p.roi_shift = sh;
+			}
+		}
+		else if(k == "sty")
+			p.cblk_sty = (uint8_t)atoi(v.c_str());
+		else if(k == "gbits")
+			p.numgbits = (uint8_t)atoi(v.c_str());
+		else if(k == "off")
+			sscanf(v.c_str(), "%u:%u", &p.image_offset_x0, &p.image_offset_y0);
+		else if(k == "torg")
+			sscanf(v.c_str(), "%u:%u", &p.tx0, &p.ty0);
+		else if(k == "mct")
+			p.mct = (uint8_t)atoi(v.c_str());
+	}
+}
+
 long ref_codec_encode(int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t h, uint32_t prec,
 					  int irreversible, int ht, uint32_t numres, uint32_t cblkw, uint32_t cblkh,
 					  uint32_t tile_w, uint32_t tile_h, uint32_t numthreads, uint8_t* out,
@@ -484,6 +630,7 @@ long ref_codec_encode(int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t 
 		p.t_width = tile_w;
 		p.t_height = tile_h;
 	}
+	apply_encode_options(p);
 	std::vector<grk_image_cmptparm> cp(numcomps);
 	for(auto& c : cp)
 	{
@@ -498,12 +645,15 @@ long ref_codec_encode(int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t 
 							   numcomps >= 3 ? GRK_CLRSPC_SRGB : GRK_CLRSPC_GRAY, true);
 	if(!image)
 		return -1;
-	image->x0 = image->y0 = 0;
-	image->x1 = w;
-	image->y1 = h;
+	image->x0 = p.image_offset_x0;
+	image->y0 = p.image_offset_y0;
+	image->x1 = image->x0 + w;
+	image->y1 = image->y0 + h;
 	for(uint32_t c = 0; c < numcomps; ++c)
 	{
 		auto comp = image->comps + c;
+		comp->x0 = image->x0;
+		comp->y0 = image->y0;
 		for(uint32_t y = 0; y < h; ++y)
 			memcpy(comp->data + (size_t)y * comp->stride, planes[c] + (size_t)y * w,
 				   sizeof(int32_t) * w);
@@ -524,6 +674,15 @@ long ref_codec_encode(int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t 
 
 /* Full decode of a codestream in memory with the stock multithreaded CPU decoder.
  * planes may be NULL (timing only). Returns 0 on success. */
+/* resolutions to drop (-r of grk_decompress) and quality layers to keep (-l; 0 = all) for the next
+ * ref_codec_decode calls; w and h are then those of the reduced image */
+static uint32_t g_dec_reduce = 0, g_dec_layers = 0;
+void ref_set_decode_options(uint32_t reduce, uint32_t layers)
+{
+	g_dec_reduce = reduce;
+	g_dec_layers = layers;
+}
+
 int ref_codec_decode(uint8_t* cs, size_t len, uint32_t numthreads, int32_t** planes,
 					 uint32_t numcomps, uint32_t w, uint32_t h)
 {
@@ -531,6 +690,8 @@ int ref_codec_decode(uint8_t* cs, size_t len, uint32_t numthreads, int32_t** pla
 	grk_decompress_parameters dp;
 	memset(&dp, 0, sizeof(dp));
 	grk_decompress_set_default_params(&dp.core);
+	dp.core.cp_reduce = (uint8_t)g_dec_reduce;
+	dp.core.cp_layer = (uint16_t)g_dec_layers;
 	auto stream = grk_stream_create_mem_stream(cs, len, false, true);
 	if(!stream)
 		return -1;
@@ -555,6 +716,39 @@ int ref_codec_decode(uint8_t* cs, size_t len, uint32_t numthreads, int32_t** pla
 						memcpy(planes[c] + (size_t)y * w, comp->data + (size_t)y * comp->stride,
 							   sizeof(int32_t) * w);
 				}
+		}
+	}
+	if(codec)
+		grk_object_unref(codec);
+	grk_object_unref(stream);
+	return rc;
+}
+
+/* dimensions and origin of component 0 of the image the stock decoder would deliver (after
+ * cp_reduce): dims = {w, h, x0, y0} */
+int ref_codec_decode_dims(uint8_t* cs, size_t len, uint32_t* dims)
+{
+	grk_decompress_parameters dp;
+	memset(&dp, 0, sizeof(dp));
+	grk_decompress_set_default_params(&dp.core);
+	dp.core.cp_reduce = (uint8_t)g_dec_reduce;
+	auto stream = grk_stream_create_mem_stream(cs, len, false, true);
+	if(!stream)
+		return -1;
+	int rc = -1;
+	auto codec = grk_decompress_create(GRK_CODEC_J2K, stream);
+	grk_header_info hdr;
+	memset(&hdr, 0, sizeof(hdr));
+	if(codec && grk_decompress_init(codec, &dp.core) && grk_decompress_read_header(codec, &hdr))
+	{
+		auto image = grk_decompress_get_composited_image(codec);
+		if(image)
+		{
+			dims[0] = image->comps[0].w;
+			dims[1] = image->comps[0].h;
+			dims[2] = image->comps[0].x0;
+			dims[3] = image->comps[0].y0;
+			rc = 0;
 		}
 	}
 	if(codec)
@@ -641,6 +835,7 @@ long ref_plugin_encode(const char* infile, int irreversible, int ht, uint32_t nu
 		p.numgbits = 1;
 		p.cblk_sty = GRK_CBLKSTY_HT;
 	}
+	apply_encode_options(p);
 	g_enc_out = out;
 	g_enc_cap = out_cap;
 	g_enc_len = -1;
@@ -709,6 +904,7 @@ int ref_plugin_batch_encode(const char* input_dir, const char* output_dir, int i
 		p.numgbits = 1;
 		p.cblk_sty = GRK_CBLKSTY_HT;
 	}
+	apply_encode_options(p);
 	g_batch_ok = 0;
 	g_batch_bad = 0;
 	if(grk_plugin_batch_compress(input_dir, output_dir, &p, plugin_batch_cb) != 0)

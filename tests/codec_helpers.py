@@ -158,9 +158,10 @@ def decode_blocks_oracle(tile, ncomp, reversible, use_ref=False, threads=None):
             rc, v = (O.ref_ht_decode if use_ref else O.orc_ht_decode)(raw, int(b["k_msbs"]), int(b["w"]),
                                                                         int(b["h"]))
             assert rc == 0
-            # ShiftHTFilter (PostDecompressFilters.h:113-129)
-            mag = ((v & 0x7FFFFFFF) >> (31 - (int(b["k_msbs"]) + 1))).astype(np.int64)
-            return ("ht", np.where(v >> 31, -mag, mag).astype(np.int32))
+            # ShiftHTFilter / ScaleHTFilter and their ROI forms (PostDecompressFilters.h:91-177)
+            d = O.orc_dequant(2 if reversible else 3, v, roishift=int(b["roishift"]), k_msbs=int(b["k_msbs"]),
+                              stepsize=float(b["scale"]))
+            return ("ht", d.reshape(v.shape))
         rc, v = dec(raw, sg, int(b["numbps"]), int(b["w"]), int(b["h"]), orient=int(b["orient"]),
                     cblksty=int(b["cblk_sty"]))
         assert rc == 0
@@ -175,6 +176,10 @@ def decode_blocks_oracle(tile, ncomp, reversible, use_ref=False, threads=None):
         dst = planes[b["comp"]][b["y"]:b["y"] + b["h"], b["x"]:b["x"] + b["w"]]
         if isinstance(v, tuple):
             dst[...] = v[1]
+        elif int(b["roishift"]):
+            # RoiShiftFilter / RoiScaleFilter (PostDecompressFilters.h:7-66); b.scale is stepsize / 2
+            dst[...] = O.orc_dequant(0 if reversible else 1, v, roishift=int(b["roishift"]),
+                                     stepsize=float(np.float32(b["scale"]) * np.float32(2))).reshape(v.shape)
         elif reversible:
             # ShiftFilter: C division by 2, truncation toward zero (PostDecompressFilters.h:42)
             dst[...] = (np.abs(v) >> 1) * np.sign(v)
@@ -184,17 +189,43 @@ def decode_blocks_oracle(tile, ncomp, reversible, use_ref=False, threads=None):
     return planes
 
 
-def decode_tile_oracle(tile, ncomp, prec, reversible, numres, mct, x0=0, y0=0, use_ref=False):
+def decode_tile_oracle(tile, ncomp, prec, reversible, numres, mct, x0=0, y0=0, use_ref=False, sgnd=0):
     coefs = decode_blocks_oracle(tile, ncomp, reversible, use_ref)
     stage = [O.orc_dwt(p, x0, y0, numres, 1 if reversible else 0, 0) for p in coefs]
-    sh = 1 << (prec - 1)
+    sh = 0 if sgnd else 1 << (prec - 1)
     st = [s.view(np.int32) for s in stage]
     irrev = 0 if reversible else 1
     if mct:
-        out = O.orc_mct_inv(st[:3], irrev, 1, [prec] * 3, [0] * 3, [sh] * 3)
+        out = O.orc_mct_inv(st[:3], irrev, 1, [prec] * 3, [sgnd] * 3, [sh] * 3)
         if ncomp > 3:
-            out += O.orc_mct_inv(st[3:], irrev, 0, [prec] * (ncomp - 3), [0] * (ncomp - 3),
+            out += O.orc_mct_inv(st[3:], irrev, 0, [prec] * (ncomp - 3), [sgnd] * (ncomp - 3),
                                  [sh] * (ncomp - 3))
     else:
-        out = O.orc_mct_inv(st, irrev, 0, [prec] * ncomp, [0] * ncomp, [sh] * ncomp)
+        out = O.orc_mct_inv(st, irrev, 0, [prec] * ncomp, [sgnd] * ncomp, [sh] * ncomp)
     return out, coefs
+
+
+def decode_codestream_oracle(cs, reduce=0, max_layers=0):
+    """Whole codestream through the product's own T2 (grok_b200.codestream: host C++, no GPU) and
+    the ORACLE's block decoders, wavelet and component transform, tile by tile -> int32 planes of
+    the (reduced) image.  What comes out equals the stock decoder's planes only if every table T2
+    produced (bytes, segments, passes, bit planes, step sizes, geometry) is right."""
+    from grok_b200 import codestream as CS
+    c = CS.Codestream(cs)
+    i = c.info
+    W, Hh = c.image_size(reduce)
+    ix0, iy0 = (i.x0 + (1 << reduce) - 1) >> reduce, (i.y0 + (1 << reduce) - 1) >> reduce
+    out = [np.zeros((Hh, W), dtype=np.int32) for _ in range(i.numcomps)]
+    info = []
+    for t in range(c.num_tiles):
+        tab = c.parse_tile(t, reduce, max_layers)
+        p = tab["params"]
+        info.append(tab)
+        if p.x1 <= p.x0 or p.y1 <= p.y0:
+            continue
+        planes, _ = decode_tile_oracle(tab, i.numcomps, int(i.prec[0]), bool(p.reversible), p.numres, p.mct,
+                                       x0=p.x0, y0=p.y0, sgnd=int(i.sgnd[0]))
+        for k in range(i.numcomps):
+            out[k][p.y0 - iy0:p.y1 - iy0, p.x0 - ix0:p.x1 - ix0] = planes[k]
+    c.close()
+    return out, info
