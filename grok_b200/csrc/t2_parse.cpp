@@ -360,23 +360,6 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 			}
 			bandq[(size_t)c * (3 * numres - 2) + b] = q;
 		}
-	out.blocks.assign((size_t)ng_keep * nc, grkb_cblk{});
-	for(uint32_t c = 0; c < nc; ++c)
-		for(uint32_t i = 0; i < ng_keep; ++i)
-		{
-			const grkb_cblk_geom& g = geom[i];
-			grkb_cblk& b = out.blocks[(size_t)c * ng_keep + i];
-			b.x = g.x;
-			b.y = g.y;
-			b.w = g.w;
-			b.h = g.h;
-			b.comp = (uint8_t)c;
-			b.orient = g.orient;
-			b.cblk_sty = cod.cblk_sty;
-			b.roishift = h.roishift[c];
-			const BandQ& q = bandq[(size_t)c * (3 * numres - 2) + (g.res == 0 ? 0 : 3 * g.res - 2) + g.band];
-			b.scale = ht ? q.step : q.step / 2; // PostDecompressFilters.h:51, :139
-		}
 	// ---- T2 state
 	std::vector<BlockState> st((size_t)ng * nc);
 	std::vector<std::vector<SegState>> bsegs; // per block that was ever included (index in seg_of)
@@ -764,18 +747,33 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 	}
 	else
 		out.pool.reserve(total + 16);
+	out.blocks.reserve((size_t)ng_keep * nc);
 	for(uint32_t c = 0; c < nc; ++c)
 		for(uint32_t i = 0; i < ng_keep; ++i)
 		{
 			const uint32_t bi = c * ng + i;
-			grkb_cblk& b = out.blocks[(size_t)c * ng_keep + i];
+			const grkb_cblk_geom& g = geom[i];
+			if(g.w == 0 || g.h == 0)
+				continue; // degenerate blocks exist for T2 only: they hold no samples
+			out.blocks.emplace_back();
+			grkb_cblk& b = out.blocks.back();
+			memset(&b, 0, sizeof(b));
+			b.x = g.x;
+			b.y = g.y;
+			b.w = g.w;
+			b.h = g.h;
+			b.comp = (uint8_t)c;
+			b.orient = g.orient;
+			b.cblk_sty = cod.cblk_sty;
+			b.roishift = h.roishift[c];
+			const uint32_t qb = (g.res == 0 ? 0 : 3 * g.res - 2) + g.band;
+			const BandQ& q = bandq[(size_t)c * (3 * numres - 2) + qb];
+			b.scale = ht ? q.step : q.step / 2; // PostDecompressFilters.h:51, :139
 			b.seg_first = (uint32_t)out.segs.size();
 			if(slot[bi] == UINT32_MAX || st[bi].dropped)
 				continue;
 			b.numbps = numbps[bi];
-			const grkb_cblk_geom& g = geom[i];
-			const uint32_t qb = (g.res == 0 ? 0 : 3 * g.res - 2) + g.band;
-			const uint32_t band_numbps = bandq[(size_t)c * (3 * numres - 2) + qb].numbps;
+			const uint32_t band_numbps = q.numbps;
 			b.k_msbs = (uint8_t)(band_numbps > b.numbps ? band_numbps - b.numbps : 0);
 			const std::vector<Chunk>& C = bchunks[slot[bi]];
 			uint32_t nbytes = 0;
