@@ -98,6 +98,8 @@ lib.grkb_host_alloc.argtypes = [C.c_size_t]
 lib.grkb_host_alloc.restype = _vp
 lib.grkb_host_free.argtypes = [_vp]
 lib.grkb_host_free.restype = None
+lib.grkb_host_register.argtypes = [_vp, C.c_size_t]
+lib.grkb_host_unregister.argtypes = [_vp]
 # section D: the allocation-free door (device pointers in and out, built-in scratch)
 lib.grkb_idwt_device_noalloc.argtypes = [_vp, _u32, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _int, _vp]
 NOALLOC_SCRATCH_BYTES = 8 << 20

@@ -18,7 +18,8 @@ class CodestreamInfo(C.Structure):
                 ("tiles_y", _u32), ("numcomps", _u32), ("prec", C.c_uint8 * 4), ("sgnd", C.c_uint8 * 4),
                 ("numres", _u32), ("numlayers", _u32), ("prog_order", _u32), ("reversible", _u32),
                 ("mct", _u32), ("cblkw_exp", _u32), ("cblkh_exp", _u32), ("cblk_sty", _u32),
-                ("csty", _u32), ("ht", _u32), ("truncated", _u32), ("rsiz", _u32), ("tile_parts", _u32)]
+                ("csty", _u32), ("ht", _u32), ("truncated", _u32), ("rsiz", _u32), ("tile_parts", _u32),
+                ("features", _u32)]
 
 
 class TileTables(C.Structure):

@@ -82,6 +82,27 @@ int grkb_codestream_get_info(const grkb_codestream* c, grkb_codestream_info* inf
 	info->rsiz = cs.rsiz;
 	for(const auto& t : cs.tiles)
 		info->tile_parts += (uint32_t)t.parts.size();
+	auto scan = [&](const grkb_cs::TileHeader& h, bool tile) {
+		for(uint32_t i = 0; i < cs.numcomps; ++i)
+		{
+			if(h.roishift[i])
+				info->features |= GRKB_CS_RGN;
+			if(h.q[i].level == 2 || h.q[i].level == 4)
+				info->features |= GRKB_CS_QCC;
+			if(h.cod[i].level == 2 || h.cod[i].level == 4)
+				info->features |= GRKB_CS_COC;
+			if(tile && (h.q[i].level >= 3 || h.cod[i].level >= 3))
+				info->features |= GRKB_CS_TILE_OVERRIDES;
+			if(cs.comps[i].prec != cs.comps[0].prec || cs.comps[i].sgnd != cs.comps[0].sgnd)
+				info->features |= GRKB_CS_MIXED_PRECISION;
+		}
+		if(!h.pocs.empty())
+			info->features |= GRKB_CS_POC;
+	};
+	scan(cs.main, false);
+	for(const auto& t : cs.tiles)
+		if(t.seen)
+			scan(t.hdr, true);
 	return 0;
 }
 

@@ -665,4 +665,20 @@ void grkb_host_free(void* p)
 		cudaFreeHost(p);
 }
 
+int grkb_host_register(void* p, size_t bytes)
+{
+	if(!p || !bytes)
+		return -1;
+	GRKB_CUDA_CHECK(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+	return 0;
+}
+
+int grkb_host_unregister(void* p)
+{
+	if(!p)
+		return -1;
+	GRKB_CUDA_CHECK(cudaHostUnregister(p));
+	return 0;
+}
+
 } // extern "C"

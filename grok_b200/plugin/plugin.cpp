@@ -26,6 +26,7 @@
 #include <mutex>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <sys/stat.h>
@@ -146,6 +147,34 @@ uint32_t ceildivpow2(uint32_t a, uint32_t b)
 	return (uint32_t)(((uint64_t)a + ((uint64_t)1 << b) - 1) >> b);
 }
 
+constexpr size_t TREE_GUARD_BYTES = 16u << 20;
+
+// After the host's T2 filled the tree: no block may hold more than its buffer.  Returns false when
+// one does (the frame is failed: the neighbouring buffers were overwritten); a block that ran past
+// the guard region has corrupted memory that is not ours, and the process is stopped.
+bool check_tree_capacity(const TileTree& t)
+{
+	bool ok = true;
+	const uint8_t* end = t.data.data() + t.data.size();
+	for(const grk_plugin_code_block& k : t.blocks)
+	{
+		if(!k.compressedData)
+			continue;
+		const size_t cap = (size_t)k.numPix * 4 + 64;
+		if(k.compressedDataLength > cap)
+		{
+			ok = false;
+			if(k.compressedData + k.compressedDataLength > end)
+			{
+				fprintf(stderr, "[grk_b200 plugin] fatal: the host wrote %u bytes for one code block, past the "
+								"plugin's buffers; memory is corrupt\n", k.compressedDataLength);
+				abort();
+			}
+		}
+	}
+	return ok;
+}
+
 // decode_cap: bytes reserved per block for the host's memcpy (0 on encode)
 bool build_tree(const TileGeom& g, bool decode, TileTree& t)
 {
@@ -206,7 +235,11 @@ bool build_tree(const TileGeom& g, bool decode, TileTree& t)
 	{
 		for(auto& b : all)
 			cap_total += (size_t)b.w * b.h * 4 + 64; // the host's own bound (t1/T1.cpp:256)
-		t.data.assign(cap_total * C, 0);
+		// The host copies every block's bytes into its buffer with no bound of its own
+		// (plugin_bridge.cpp:84, Codeblock.h:245-259).  A block longer than the reference's own
+		// T1 bound spills into the buffers that follow -- all inside this vector, whose tail is a
+		// guard region -- and is caught by check_tree_capacity() before anything reads the data.
+		t.data.assign(cap_total * C + TREE_GUARD_BYTES, 0);
 	}
 	t.geom.clear();
 	for(auto& b : all)
@@ -418,8 +451,12 @@ struct CachedImage
 	{
 		drop();
 	}
+	std::vector<void*> registered;
 	void drop()
 	{
+		for(void* p : registered)
+			grkb_host_unregister(p);
+		registered.clear();
 		if(image && host_unref())
 			host_unref()(&image->obj);
 		image = nullptr;
@@ -453,6 +490,17 @@ struct CachedImage
 								 true);
 		if(image)
 		{
+			// the device writes straight into the host's planes: page-lock them once (they live as long
+			// as the slot), and start from zeros (a reduced image may have a last row / column no tile
+			// covers, which the reference leaves at zero)
+			for(uint32_t c = 0; c < numcomps; ++c)
+				if(image->comps[c].data)
+				{
+					const size_t bytes = (size_t)image->comps[c].stride * H * sizeof(int32_t);
+					memset(image->comps[c].data, 0, bytes);
+					if(grkb_host_register(image->comps[c].data, bytes) == 0)
+						registered.push_back(image->comps[c].data);
+				}
 			image->x0 = ox;
 			image->y0 = oy;
 			image->x1 = ox + W;
@@ -901,6 +949,9 @@ QcdPeek peek_qcd(const char* path, uint32_t numres)
 // staging for the coded bytes on the way in and the samples on the way out.
 struct DecoderSlot
 {
+	grkb_decompressor* dz = nullptr; // own T2 (the default): whole codestreams, any number of tiles
+	int dz_device = -1;
+	PinnedBuf file; // the codestream as read from disk, page-locked: its bytes are the byte pool
 	grkb_decoder* dec = nullptr;
 	grkb_tile_params tp{};
 	int device = -1;
@@ -910,6 +961,8 @@ struct DecoderSlot
 	CachedImage himage; // handed to the host's output callback with plugin_owns_image = true
 	~DecoderSlot()
 	{
+		if(dz)
+			grkb_decompressor_destroy(dz);
 		if(dec)
 			grkb_decoder_destroy(dec);
 	}
@@ -1020,12 +1073,219 @@ int32_t call_host(grk::PLUGIN_DECODE_USER_CALLBACK cb, grk::PluginDecodeCallback
 	return -1;
 }
 
+
+// GROK_INIT_DECOMPRESSORS for the own-T2 path: the header the host read is not needed (the plugin
+// parses the codestream itself); returning 0 tells the host to go on
+int init_decompressors_own(grk_header_info*, grk_image*)
+{
+	return 0;
+}
+
+// uint16 / int16 rows -> the host's int32 planes, on a few threads (the 16-bit bus format, used
+// when several GPUs share one host bridge)
+void widen16(const uint8_t* src, size_t row16, grk_image* image, uint32_t numcomps, uint32_t W, uint32_t H, bool sgnd)
+{
+	const unsigned nt = std::max(1u, std::min(4u, std::thread::hardware_concurrency()));
+	auto work = [&](unsigned t) {
+		for(uint32_t c = 0; c < numcomps; ++c)
+			for(uint32_t y = t; y < H; y += nt)
+			{
+				const uint16_t* s = (const uint16_t*)(src + ((size_t)c * H + y) * row16);
+				int32_t* d = image->comps[c].data + (size_t)y * image->comps[c].stride;
+				if(sgnd)
+					for(uint32_t x = 0; x < W; ++x)
+						d[x] = (int16_t)s[x];
+				else
+					for(uint32_t x = 0; x < W; ++x)
+						d[x] = s[x];
+			}
+	};
+	std::vector<std::thread> th;
+	for(unsigned t = 1; t < nt; ++t)
+		th.emplace_back(work, t);
+	work(0);
+	for(auto& t : th)
+		t.join();
+}
+
+// Decode with T2 on our side: the plugin reads the file, parses markers and packets
+// itself (grkb_decompress_*), decodes every tile on the device and hands the host a finished
+// grk_image for its POST_T1 stage (colour management, file output).  The host's callback is asked
+// for GRK_DECODE_HEADER (it opens its codec; the stock callback needs that for the later stages)
+// and GRK_DECODE_POST_T1 only: its T2 and the grk_plugin_tile bridge -- one tile, one segment per
+// block, 3*(prec+3) passes at most, one memcpy per block -- are not on the path.
+int decode_one_own_t2(grk_decompress_parameters* params, const std::string& in, const std::string& out,
+					  int device, grk::PLUGIN_DECODE_USER_CALLBACK cb, DecoderSlot* slot)
+{
+	using clk = std::chrono::steady_clock;
+	const auto t_start = clk::now();
+	auto ms_since = [](clk::time_point a) { return std::chrono::duration<double, std::milli>(clk::now() - a).count(); };
+	// ---- the file, into page-locked memory
+	FILE* f = fopen(in.c_str(), "rb");
+	if(!f)
+	{
+		logf("cannot open %s", in.c_str());
+		return -1;
+	}
+	struct stat sb;
+	if(fstat(fileno(f), &sb) != 0 || sb.st_size <= 0 || !slot->file.reserve((size_t)sb.st_size + 16))
+	{
+		fclose(f);
+		return -1;
+	}
+	const size_t len = fread(slot->file.p, 1, (size_t)sb.st_size, f);
+	fclose(f);
+	if(len != (size_t)sb.st_size)
+		return -1;
+	const double ms_read = ms_since(t_start);
+	grk::PluginDecodeCallbackInfo info(in, out, params, params ? params->decod_format : GRK_UNK_FMT,
+									   GRK_DECODE_HEADER);
+	if(params)
+		info.cod_format = params->cod_format;
+	info.deviceId = (size_t)device;
+	info.init_decompressors_func = init_decompressors_own;
+	auto finish = [&](int rc) {
+		info.decompress_flags = GRK_PLUGIN_DECODE_CLEAN;
+		call_host(cb, &info);
+		return rc;
+	};
+	if(call_host(cb, &info) != 0)
+		return finish(-1);
+	const double ms_header = ms_since(t_start);
+	grkb_codestream* cs = nullptr;
+	grkb_codestream_info ci;
+	if(grkb_codestream_open(slot->file.p, len, &cs) || grkb_codestream_get_info(cs, &ci))
+	{
+		logf("%s: %s", in.c_str(), grkb_last_error());
+		if(cs)
+			grkb_codestream_close(cs);
+		return finish(-1);
+	}
+	grkb_codestream_close(cs);
+	const uint32_t reduce = params ? params->core.cp_reduce : 0, layers = params ? params->core.cp_layer : 0;
+	if(reduce >= ci.numres)
+	{
+		logf("%s: cannot drop %u of %u resolutions", in.c_str(), reduce, ci.numres);
+		return finish(-1);
+	}
+	if(ci.features & GRKB_CS_MIXED_PRECISION)
+	{
+		logf("%s: components of different precision or signedness are left to the host", in.c_str());
+		return finish(-1);
+	}
+	const uint32_t W = ceildivpow2(ci.x1 - ci.x0, reduce), H = ceildivpow2(ci.y1 - ci.y0, reduce);
+	const uint32_t prec = ci.prec[0];
+	const bool sgnd = ci.sgnd[0] != 0;
+	if(!host_image_new() || !host_unref())
+	{
+		logf("host library symbols grk_image_new / grk_object_unref are not visible");
+		return finish(-1);
+	}
+	if(grkb_set_device(device))
+		return finish(-1);
+	grk_image* image = slot->himage.get(W, H, ci.numcomps, prec, sgnd, ceildivpow2(ci.x0, reduce),
+										ceildivpow2(ci.y0, reduce));
+	if(!image)
+		return finish(-1);
+	if(slot->dz && slot->dz_device != device)
+	{
+		grkb_decompressor_destroy(slot->dz);
+		slot->dz = nullptr;
+	}
+	if(!slot->dz)
+	{
+		if(grkb_decompressor_create(device, 3, &slot->dz))
+		{
+			slot->dz = nullptr;
+			logf("%s", grkb_last_error());
+			return finish(-1);
+		}
+		slot->dz_device = device;
+	}
+	const double ms_setup = ms_since(t_start);
+	uint32_t rejected = 0;
+	int rc;
+	// one GPU: int32 planes by DMA straight into the host's (page-locked) image.  Several GPUs behind
+	// one host bridge (deviceId = -1): 16-bit samples across the bus, widened here.
+	const bool bus16 = prec <= 16 && (getenv("GRKB_PLUGIN_BUS16") ? atoi(getenv("GRKB_PLUGIN_BUS16")) != 0
+																  : (g_device < 0 && g_ndev > 1));
+	const size_t row16 = (size_t)W * 2;
+	if(bus16 && slot->out.reserve(row16 * H * ci.numcomps + 16))
+	{
+		memset(slot->out.p, 0, row16 * H * ci.numcomps);
+		rc = grkb_decompress_submit_packed(slot->dz, slot->file.p, len, reduce, layers, slot->out.p, GRKB_SAMPLES_16,
+										   row16);
+		if(!rc)
+			rc = grkb_decompress_wait(slot->dz, &rejected);
+		if(!rc)
+			widen16(slot->out.p, row16, image, ci.numcomps, W, H, sgnd);
+	}
+	else
+	{
+		int32_t* planes[GRKB_MAX_COMPS] = {};
+		for(uint32_t c = 0; c < ci.numcomps; ++c)
+			planes[c] = image->comps[c].data;
+		rc = grkb_decompress(slot->dz, slot->file.p, len, reduce, layers, planes, image->comps[0].stride, &rejected);
+	}
+	if(rc || rejected)
+	{
+		logf("%s: decode failed: %s (%u blocks rejected)", in.c_str(), grkb_last_error(), rejected);
+		return finish(-1);
+	}
+	const double ms_dev = ms_since(t_start);
+	double t2_ms = 0;
+	uint32_t tiles = 0;
+	grkb_decompress_stats(slot->dz, &t2_ms, &tiles);
+	info.image = image;
+	info.plugin_owns_image = true;
+	info.decompress_flags = GRK_DECODE_POST_T1;
+	rc = call_host(cb, &info); // host: colour management, file output
+	const double ms_out = ms_since(t_start);
+	finish(rc);
+	logf("%s: read %.1f ms, host header %.1f, setup %.1f, decode %.1f (own T2 %.1f, %u tiles), host output %.1f, "
+		 "clean %.1f", in.c_str(), ms_read, ms_header - ms_read, ms_setup - ms_header, ms_dev - ms_setup, t2_ms, tiles,
+		 ms_out - ms_dev, ms_since(t_start) - ms_out);
+	return rc;
+}
+
 int decode_one(grk_decompress_parameters* params, const std::string& in, const std::string& out,
 			   int device, grk::PLUGIN_DECODE_USER_CALLBACK cb, DecoderSlot* slot = nullptr)
 {
 	DecoderSlot local;
 	if(!slot)
 		slot = &local;
+	// GRKB_PLUGIN_HOST_T2=1 selects the bridge path: the host's T2 fills a grk_plugin_tile
+	const bool host_t2 = getenv("GRKB_PLUGIN_HOST_T2") && atoi(getenv("GRKB_PLUGIN_HOST_T2")) != 0;
+	if(!host_t2)
+		return decode_one_own_t2(params, in, out, device, cb, slot);
+	// The bridge carries one tile, one QCD, no ROI shift and neither cp_reduce nor cp_layer: what it
+	// cannot express is refused here instead of being decoded wrongly.
+	{
+		if(params && (params->core.cp_reduce || params->core.cp_layer))
+		{
+			fprintf(stderr, "[grk_b200 plugin] %s: bridge path: cp_reduce / cp_layer are not supported\n", in.c_str());
+			return -1;
+		}
+		std::vector<uint8_t> head(1 << 20);
+		FILE* f = fopen(in.c_str(), "rb");
+		if(!f)
+			return -1;
+		head.resize(fread(head.data(), 1, head.size(), f));
+		fclose(f);
+		grkb_codestream* cs = nullptr;
+		grkb_codestream_info ci;
+		memset(&ci, 0, sizeof(ci));
+		const bool ok = grkb_codestream_open(head.data(), head.size(), &cs) == 0 && grkb_codestream_get_info(cs, &ci) == 0;
+		if(cs)
+			grkb_codestream_close(cs);
+		if(ok && (ci.features & (GRKB_CS_RGN | GRKB_CS_QCC | GRKB_CS_COC | GRKB_CS_TILE_OVERRIDES |
+								 GRKB_CS_MIXED_PRECISION)))
+		{
+			fprintf(stderr, "[grk_b200 plugin] %s: bridge path: RGN / QCC / COC / tile-header overrides / mixed "
+							"precision cannot cross grk_plugin_tile\n", in.c_str());
+			return -1;
+		}
+	}
 	using clk = std::chrono::steady_clock;
 	const auto t_start = clk::now();
 	auto ms_since = [](clk::time_point a) { return std::chrono::duration<double, std::milli>(clk::now() - a).count(); };
@@ -1057,6 +1317,12 @@ int decode_one(grk_decompress_parameters* params, const std::string& in, const s
 	info.tile = &t.tile;
 	if(call_host(cb, &info) != 0) // host: T2, then decompress_synch_plugin_with_host fills the tree
 		return finish(-1);
+	if(!check_tree_capacity(t))
+	{
+		fprintf(stderr, "[grk_b200 plugin] %s: a code block is longer than the buffer the plugin ABI lets us "
+						"offer; frame refused\n", in.c_str());
+		return finish(-1);
+	}
 	const double ms_t2 = ms_since(t_start);
 	// descriptor table from the filled tree
 	const TileGeom& g = ctx.geom;
@@ -1402,6 +1668,31 @@ namespace
 std::string g_dec_in, g_dec_out;
 grk_decompress_parameters* g_dec_params = nullptr;
 grk::PLUGIN_DECODE_USER_CALLBACK g_dec_cb = nullptr;
+std::atomic<int> g_dec_failed{0}, g_dec_ok{0};
+
+// extension of the output files, from the format the host asked for (params->cod_format)
+const char* output_ext(const grk_decompress_parameters* p)
+{
+	switch(p ? p->cod_format : GRK_PXM_FMT)
+	{
+		case GRK_PGX_FMT:
+			return "pgx";
+		case GRK_BMP_FMT:
+			return "bmp";
+		case GRK_TIF_FMT:
+			return "tif";
+		case GRK_RAW_FMT:
+			return "raw";
+		case GRK_RAWL_FMT:
+			return "rawl";
+		case GRK_PNG_FMT:
+			return "png";
+		case GRK_JPG_FMT:
+			return "jpg";
+		default:
+			return "ppm";
+	}
+}
 } // namespace
 
 PLUGIN_EXPORT int32_t plugin_init_batch_decompress(const char* input_dir, const char* output_dir,
@@ -1414,6 +1705,8 @@ PLUGIN_EXPORT int32_t plugin_init_batch_decompress(const char* input_dir, const 
 	g_dec_out = output_dir;
 	g_dec_params = params;
 	g_dec_cb = cb;
+	g_dec_failed = 0;
+	g_dec_ok = 0;
 	return 0;
 }
 
@@ -1441,9 +1734,19 @@ PLUGIN_EXPORT int32_t plugin_batch_decompress(void)
 				const size_t i = next++;
 				if(i >= names.size() || g_stop)
 					break;
-				decode_one(g_dec_params, g_dec_in + "/" + names[i], g_dec_out + "/" + replace_ext(names[i], "ppm"),
-						   g_device >= 0 ? g_device : (g_ndev > 0 ? (int)(slot % (unsigned)g_ndev) : 0), g_dec_cb,
-						   (*g_dec_pool)[slot].get());
+				const int rc = decode_one(g_dec_params, g_dec_in + "/" + names[i],
+										  g_dec_out + "/" + replace_ext(names[i], output_ext(g_dec_params)),
+										  g_device >= 0 ? g_device : (g_ndev > 0 ? (int)(slot % (unsigned)g_ndev) : 0),
+										  g_dec_cb, (*g_dec_pool)[slot].get());
+				if(rc)
+				{
+					// never silent: the frame has no output file
+					++g_dec_failed;
+					fprintf(stderr, "[grk_b200 plugin] batch decompress: %s was NOT decoded (%s)\n", names[i].c_str(),
+							grkb_last_error());
+				}
+				else
+					++g_dec_ok;
 			}
 		};
 		std::vector<std::thread> pool;
@@ -1452,6 +1755,9 @@ PLUGIN_EXPORT int32_t plugin_batch_decompress(void)
 		worker(0);
 		for(auto& t : pool)
 			t.join();
+		if(g_dec_failed)
+			fprintf(stderr, "[grk_b200 plugin] batch decompress: %d of %d frames failed\n", g_dec_failed.load(),
+					g_dec_failed.load() + g_dec_ok.load());
 		g_batch_done = true;
 	});
 	return 0;

@@ -379,6 +379,10 @@ int grkb_encoder_time_device(grkb_encoder* e, uint32_t iters, uint32_t warmup, f
  * driver). */
 void* grkb_host_alloc(size_t bytes);
 void grkb_host_free(void* p);
+/* Page-locks memory the caller already owns (a grk_image's planes), so that results are written
+ * into it by DMA instead of through the driver's staging buffer. */
+int grkb_host_register(void* p, size_t bytes);
+int grkb_host_unregister(void* p);
 
 /* C. diagnostics ------------------------------------------------------------------------------ */
 
@@ -417,7 +421,14 @@ typedef struct grkb_codestream_info
 	uint32_t truncated; /* 1: the buffer ends inside a tile part */
 	uint32_t rsiz;
 	uint32_t tile_parts; /* tile-part bodies indexed */
+	uint32_t features; /* GRKB_CS_* */
 } grkb_codestream_info;
+#define GRKB_CS_RGN 0x01 /* region of interest shift on some component */
+#define GRKB_CS_QCC 0x02 /* component-specific quantisation */
+#define GRKB_CS_COC 0x04 /* component-specific coding style (identical geometry: accepted) */
+#define GRKB_CS_TILE_OVERRIDES 0x08 /* COD / QCD / ... in tile-part headers */
+#define GRKB_CS_POC 0x10
+#define GRKB_CS_MIXED_PRECISION 0x20 /* components differ in precision or signedness */
 
 /* Reads the main header and indexes all tile parts of a raw codestream or a JP2 file (the jp2c box
  * is located).  `data` must stay valid and unchanged until grkb_codestream_close. */

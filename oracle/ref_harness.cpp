@@ -1082,6 +1082,8 @@ int ref_plugin_decode(const char* infile, int32_t** planes, uint32_t numcomps, u
 	grk_decompress_set_default_params(&g_dec_params.core);
 	strncpy(g_dec_params.infile, infile, sizeof(g_dec_params.infile) - 1);
 	g_dec_params.decod_format = GRK_J2K_FMT;
+	g_dec_params.core.cp_reduce = (uint8_t)g_dec_reduce;
+	g_dec_params.core.cp_layer = (uint16_t)g_dec_layers;
 	g_dec_planes = planes;
 	g_dec_nc = numcomps;
 	g_dec_w = w;

@@ -7,10 +7,13 @@ grk_plugin_load / grk_plugin_init, and
   * grk_plugin_decompress: the host parses markers and packets (T2), our plugin does T1,
     dequantisation, inverse wavelet and inverse MCT on the GPU -> the samples must be identical
     to the stock CPU decoder's (bit-exact, 9/7 included)."""
+import os
+
 import numpy as np
 import pytest
 
 import codec_helpers as H
+from grok_b200 import codestream as CS
 from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -134,3 +137,135 @@ def test_plugin_batch_decode_identical_samples(host, tmp_path, w, h, ncomp, prec
         assert len(got) == ncomp
         for c in range(ncomp):
             assert np.array_equal(got[c], want[f][c]), "frame %d component %d" % (f, c)
+
+
+# ---------------------------------------------------------------------------- own T2 (row N1)
+
+def _plugin_decode(tmp_path, cs, ncomp, reduce=0, layers=0):
+    path = str(tmp_path / "in.j2k")
+    cs.tofile(path)
+    c = CS.Codestream(cs)
+    w, h = c.image_size(reduce)
+    c.close()
+    try:
+        O.ref_set_decode_options(reduce, layers)
+        want = O.ref_codec_decode(cs, ncomp, w, h)
+        got = O.ref_plugin_decode(path, ncomp, w, h)
+    finally:
+        O.ref_set_decode_options(0, 0)
+    return want, got
+
+
+def _encode(img, prec, irr, opts="", rate=0.0, **kw):
+    try:
+        O.ref_set_rate(rate)
+        O.ref_set_encode_options(opts)
+        return O.ref_codec_encode(img, prec, irr, threads=os.cpu_count(), **kw)
+    finally:
+        O.ref_set_rate(0)
+        O.ref_set_encode_options("")
+
+
+@pytest.mark.parametrize("w,h,ncomp,prec,irr,ht,nr,cblk,tile,opts,rate", [
+    (250, 190, 3, 8, 0, 0, 5, (32, 32), (96, 80), "off=13:7;torg=5:3;prog=PCRL;prc=64x64", 0.0),   # multi-tile
+    (200, 150, 3, 8, 0, 0, 5, (32, 32), (0, 0), "prog=RPCL;prc=64x64:32x32;rates=40:15:1", 0.0),   # layers
+    (130, 100, 1, 10, 0, 0, 5, (64, 64), (0, 0), "sty=5;rates=30:8:1", 0.0),                       # several segments
+    (300, 260, 3, 12, 0, 1, 4, (64, 64), (128, 128), "prog=RPCL;prc=128x128", 0.0),                # HT, tiled
+    (512, 270, 3, 12, 1, 0, 6, (32, 32), (0, 0), "cinema=4k24", 0.0),                              # CPRL + POC
+    (160, 120, 3, 8, 0, 0, 5, (32, 32), (0, 0), "roi=0:5", 0.0),                                   # RGN
+])
+def test_plugin_decode_beyond_the_bridge(host, tmp_path, w, h, ncomp, prec, irr, ht, nr, cblk, tile, opts, rate):
+    """grk_plugin_decompress with T2 on the plugin's side: streams a grk_plugin_tile cannot carry
+    (several tiles, several segments per block, ROI) decode to the stock decoder's samples"""
+    img = H.synth_image(w, h, ncomp, prec, seed=w + h)
+    cs = _encode(img, prec, irr, opts, rate, ht=bool(ht), numres=nr, cblk=cblk, tile=tile)
+    want, got = _plugin_decode(tmp_path, cs, ncomp)
+    for c in range(ncomp):
+        assert np.array_equal(got[c], want[c])
+
+
+@pytest.mark.parametrize("reduce,layers", [(1, 0), (3, 0), (0, 2)])
+def test_plugin_decode_reduce_and_layers(host, tmp_path, reduce, layers):
+    img = H.synth_image(250, 190, 3, 8, seed=12)
+    cs = _encode(img, 8, 0, "rates=30:10:1;off=3:5", tile=(128, 96), numres=5, cblk=(32, 32))
+    want, got = _plugin_decode(tmp_path, cs, 3, reduce, layers)
+    for c in range(3):
+        assert np.array_equal(got[c], want[c])
+
+
+def test_plugin_decode_bridge_path_still_works(host, tmp_path):
+    """GRKB_PLUGIN_HOST_T2=1: the host's T2 fills the grk_plugin_tile (rows P1, P2) -- and what that
+    tree cannot express is refused, not decoded wrongly"""
+    os.environ["GRKB_PLUGIN_HOST_T2"] = "1"
+    try:
+        img = H.synth_image(320, 200, 3, 12, seed=3)
+        cs = _encode(img, 12, 0, ht=True, numres=6, cblk=(64, 64))
+        want, got = _plugin_decode(tmp_path, cs, 3)
+        assert all(np.array_equal(a, b) for a, b in zip(want, got))
+        cs = _encode(img, 12, 0, "roi=0:4", numres=5, cblk=(64, 64))
+        with pytest.raises(RuntimeError):
+            _plugin_decode(tmp_path, cs, 3)
+        cs = _encode(img, 12, 0, numres=5, cblk=(64, 64), tile=(128, 128))
+        with pytest.raises(RuntimeError):
+            _plugin_decode(tmp_path, cs, 3)
+    finally:
+        del os.environ["GRKB_PLUGIN_HOST_T2"]
+
+
+# ---------------------------------------------------------------------------- BASELINE shapes
+
+@pytest.fixture(scope="module")
+def frame16():
+    return H.synth_image(4096, 2160, 3, 16, seed=4096)
+
+
+def test_configs1_frame_through_the_plugin_door(host, tmp_path, frame16):
+    """BASELINE configs[1] (the frame bench.py times) through grk_plugin_decompress.  Its LL blocks
+    carry 67 coding passes against the bridge's bound of 3 * (16 + 3) = 57
+    (plugin/plugin_bridge.cpp:57-72): through the host's T2 the frame cannot be handed to any plugin
+    (checked below: the bridge path fails it); with T2 on our side it decodes, bit-exact."""
+    cs = _encode(frame16, 16, 1, numres=6, cblk=(64, 64))
+    c = CS.Codestream(cs)
+    t = c.parse_tile(0)
+    c.close()
+    assert int(t["segs"]["numpasses"].max()) > 3 * (16 + 3)
+    want, got = _plugin_decode(tmp_path, cs, 3)
+    for k in range(3):
+        assert np.array_equal(got[k], want[k])
+    os.environ["GRKB_PLUGIN_HOST_T2"] = "1"
+    try:
+        with pytest.raises(RuntimeError):
+            _plugin_decode(tmp_path, cs, 3)
+    finally:
+        del os.environ["GRKB_PLUGIN_HOST_T2"]
+
+
+def test_configs2_ht_4k_through_the_plugin_doors(host, tmp_path, frame16):
+    """BASELINE configs[2]: 4096x2160 12-bit HTJ2K lossless.  Encode through grk_plugin_compress is
+    byte-identical to the stock encoder's codestream; decode through grk_plugin_decompress gives
+    the stock decoder's samples (= the image)."""
+    img = [p >> 4 for p in frame16]
+    pnm = str(tmp_path / "in.ppm")
+    O.write_pnm(pnm, img, 12)
+    lossless = _encode(img, 12, 0, ht=True, numres=6, cblk=(64, 64))
+    try:
+        O.ref_set_rate(1.0)
+        ours = O.ref_plugin_encode(pnm, 4096, 2160, 3, 0, ht=True, numres=6)
+    finally:
+        O.ref_set_rate(0)
+    assert len(ours) == len(lossless) and np.array_equal(ours, lossless)
+    want, got = _plugin_decode(tmp_path, ours, 3)
+    for k in range(3):
+        assert np.array_equal(got[k], want[k]) and np.array_equal(got[k], img[k])
+
+
+def test_configs3_8k_tiled_through_the_plugin_door(host, tmp_path):
+    """BASELINE configs[3]: 8192x8192 16-bit HTJ2K in 1024x1024 tiles -- 64 tiles through one
+    grk_plugin_decompress call (impossible across grk_plugin_tile, which holds one tile)"""
+    img = H.synth_image(8192, 8192, 3, 16, seed=8192)
+    cs = _encode(img, 16, 0, ht=True, numres=6, cblk=(64, 64), tile=(1024, 1024))
+    path = str(tmp_path / "in.j2k")
+    cs.tofile(path)
+    got = O.ref_plugin_decode(path, 3, 8192, 8192)
+    for k in range(3):
+        assert np.array_equal(got[k], img[k])
