@@ -579,12 +579,58 @@ std::mutex g_cb_mutex; // GRKB_BATCH_SERIAL_CALLBACK=1: one host callback at a t
 // CUDA call is left to the static destructors.
 std::vector<std::unique_ptr<EncodeCtx>>* g_ctx_pool = new std::vector<std::unique_ptr<EncodeCtx>>();
 
-int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
+// What the host's grk_compress_init will do to the parameters of a digital-cinema profile before its
+// rate allocation and T2 run (codestream/CodeStreamCompress.cpp:219-235 -> Profile::is_cinema_compliant
+// and Profile::set_cinema_parameters, codestream/Profile.cpp:1006-1215; `-x 24` / `-w 24` of
+// grk_compress: BASELINE configs[4]).  The plugin codes its blocks before that call, so it has to
+// partition the tile the way the host is going to: 32x32 blocks, 256x256 precincts (128 at the lowest
+// resolution), 9/7, no mode switches, one or two guard bits.
+void apply_profile(grk_cparameters& p, const HostImage& im)
+{
+	if(!GRK_IS_CINEMA(p.rsiz))
+		return;
+	const bool k4 = p.rsiz == GRK_PROFILE_CINEMA_4K;
+	const bool compliant = (p.rsiz == GRK_PROFILE_CINEMA_2K || k4) && im.numcomps == 3 && im.prec == 12 && !im.sgnd &&
+						   im.w <= (k4 ? 4096u : 2048u) && im.h <= (k4 ? 2160u : 1080u);
+	if(!compliant)
+	{
+		p.rsiz = GRK_PROFILE_NONE; // the host falls back to the plain parameters
+		return;
+	}
+	p.tile_size_on = false;
+	p.tx0 = p.ty0 = 0;
+	p.image_offset_x0 = p.image_offset_y0 = 0;
+	p.cblockw_init = p.cblockh_init = 32;
+	p.cblk_sty = 0;
+	p.subsampling_dx = p.subsampling_dy = 1;
+	p.irreversible = true;
+	p.numlayers = 1;
+	if(!k4 && p.numresolution > 6)
+		p.numresolution = 6;
+	if(k4 && p.numresolution < 2)
+		p.numresolution = 1;
+	if(k4 && p.numresolution > 7)
+		p.numresolution = 7;
+	p.csty |= 1;
+	p.res_spec = (uint32_t)(p.numresolution - 1);
+	for(uint32_t i = 0; i < p.res_spec; ++i)
+		p.prcw_init[i] = p.prch_init[i] = 256;
+	p.numgbits = k4 ? 2 : 1;
+	// the byte budget of the profile makes the single layer rate controlled (Profile.cpp:1108-1150):
+	// the host needs the passes' distortions
+	p.allocationByRateDistoration = true;
+	if(p.max_cs_size == 0 || p.max_cs_size > GRK_CINEMA_24_CS)
+		p.max_cs_size = GRK_CINEMA_24_CS;
+	p.layer_rate[0] = ((double)im.numcomps * im.w * im.h * im.prec) / ((double)p.max_cs_size * 8);
+}
+
+int encode_one(const grk_cparameters* params_in, const EncodeJob& job, int device,
 			   grk::PLUGIN_ENCODE_USER_CALLBACK cb, EncodeCtx* ctx = nullptr, bool serial_cb = false)
 {
 	EncodeCtx local;
 	if(!ctx)
 		ctx = &local;
+	const grk_cparameters* params = params_in; // for reading the input; replaced below
 	using clk = std::chrono::steady_clock;
 	const auto t_start = clk::now();
 	auto ms_since = [](clk::time_point a) { return std::chrono::duration<double, std::milli>(clk::now() - a).count(); };
@@ -594,6 +640,9 @@ int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
 		logf("cannot read %s (binary PNM and raw input are supported)", job.in.c_str());
 		return -1;
 	}
+	grk_cparameters eff = *params_in; // the parameters as the host's grk_compress_init will leave them
+	apply_profile(eff, im);
+	params = &eff;
 	if(params->tile_size_on && (params->t_width < im.w || params->t_height < im.h))
 	{
 		logf("multi-tile encode is not routed through the plugin tile (one tile per grk_plugin_tile)");
@@ -857,7 +906,7 @@ int encode_one(const grk_cparameters* params, const EncodeJob& job, int device,
 	info.input_file_name = job.in.c_str();
 	info.outputFileNameIsRelative = job.out_relative;
 	info.output_file_name = job.out.c_str();
-	info.compressor_parameters = const_cast<grk_cparameters*>(params);
+	info.compressor_parameters = const_cast<grk_cparameters*>(params_in);
 	info.image = image;
 	info.tile = &tree->tile;
 	info.error_code = 0;

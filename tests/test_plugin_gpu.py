@@ -269,3 +269,43 @@ def test_configs3_8k_tiled_through_the_plugin_door(host, tmp_path):
     got = O.ref_plugin_decode(path, 3, 8192, 8192)
     for k in range(3):
         assert np.array_equal(got[k], img[k])
+
+
+def test_plugin_encode_cinema_profile_small(host, tmp_path):
+    """-x 24 / -w 24: the plugin partitions the tile as the host's grk_compress_init is going to
+    (32x32 blocks, 256x256 precincts, 9/7, CPRL + POC on the host side) -> byte-identical"""
+    for prof, (w, h) in (("cinema=4k24", (640, 360)), ("cinema=2k24", (512, 270))):
+        img = H.synth_image(w, h, 3, 12, seed=w)
+        pnm = str(tmp_path / "in.ppm")
+        O.write_pnm(pnm, img, 12)
+        try:
+            O.ref_set_encode_options(prof)
+            stock = O.ref_codec_encode(img, 12, 0, numres=6)
+            ours = O.ref_plugin_encode(pnm, w, h, 3, 0, numres=6)
+        finally:
+            O.ref_set_encode_options("")
+        assert len(ours) == len(stock) and np.array_equal(ours, stock), prof
+
+
+def test_configs4_dci4k_frames_through_the_batch_door(host, tmp_path, frame16):
+    """BASELINE configs[4]: DCI-4K 12-bit frames through grk_plugin_batch_compress with the
+    cinema-4K profile (9/7, 32x32 blocks, 256x256 precincts, CPRL + POC, 1 302 083 bytes per frame):
+    every file byte-identical to the stock encoder's"""
+    indir, outdir = tmp_path / "in", tmp_path / "out"
+    indir.mkdir()
+    outdir.mkdir()
+    base = [p >> 4 for p in frame16]
+    frames = [base, [np.roll(p, 37, axis=1) for p in base]]
+    for f, img in enumerate(frames):
+        O.write_pnm(str(indir / ("f%03d.ppm" % f)), img, 12)
+    try:
+        O.ref_set_encode_options("cinema=4k24")
+        n = O.ref_plugin_batch_encode(str(indir), str(outdir), 0, numres=6)
+        stock = [O.ref_codec_encode(img, 12, 0, numres=6, threads=os.cpu_count()) for img in frames]
+    finally:
+        O.ref_set_encode_options("")
+    assert n == len(frames)
+    for f in range(len(frames)):
+        got = np.fromfile(str(outdir / ("f%03d.j2k" % f)), dtype=np.uint8)
+        assert len(stock[f]) <= 1302083
+        assert len(got) == len(stock[f]) and np.array_equal(got, stock[f]), "frame %d" % f
