@@ -1,18 +1,27 @@
 #!/usr/bin/env python
 """bench.py -- whole-frame JPEG 2000 decode throughput of the B200 tile decoder.
 
-Workload (BASELINE.json configs[1]): 4096x2160 16-bit RGB, irreversible 9/7 + ICT, 5
-decomposition levels, 64x64 code blocks, one tile, one layer, every coding pass kept.
-A step = one decode of one frame: EBCOT/MQ block decoding with fused dequantisation, inverse
-9/7 wavelet of the three components, inverse ICT + DC shift + clamp fused into the last level.
-T2 (packet parsing) stays on the host in the reference's design and is outside the step.
+Workload (BASELINE.json configs[1]): 4096x2160 16-bit RGB, irreversible 9/7 + ICT, 5 decomposition
+levels, 64x64 code blocks, one tile, one layer, every coding pass kept -- the codestream the STOCK
+reference encoder writes for the synthetic frame.  A step = one decode of that codestream:
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    ours       value = device-resident: T1 (EBCOT/MQ + fused dequantisation) + inverse 9/7 of three
+                       components + fused inverse ICT / DC shift / clamp, tables already in HBM,
+                       CUDA events on the decoder's stream;
+               e2e   = the C-ABI codestream door (grkb_decompress_submit / _wait): coded bytes in
+                       page-locked host memory in, our own marker + packet parsing (T2) on the host,
+                       H2D, all kernels, D2H of the int32 planes -- the same work the reference arm
+                       does on its memory stream; K frames in flight;
+               e2e_plugin / e2e_plugin_batch (N = 1) = the same frame through the reference's own
+                       plugin doors, grk_plugin_decompress and grk_plugin_batch_decompress, driven by
+                       the UNMODIFIED reference host (oracle/_ref) that loads libgrokj2k_plugin.so;
+               ht    = the same three figures for BASELINE configs[2] (12-bit HTJ2K lossless);
+               parity = GPU planes compared with the stock decoder's planes of the same codestream.
+    reference  the unmodified reference's own multithreaded CPU decoder (public C API, memory
+               stream, oracle/_ref/libgrok_ref.so) on the same codestream, all host threads.
 
-ours:       value = device-resident throughput (inputs already in HBM), e2e = through the
-            C-ABI with pinned host buffers (H2D of descriptors + bytes, D2H of int32 planes).
-reference:  the unmodified reference's own multithreaded CPU decoder (public C API, memory
-            stream, oracle/_ref/libgrok_ref.so) on the same frame, all host threads.
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload j2k97|ht]
+
 Synthetic data; frames are sharded over ranks with no collective (weak scaling).
 """
 import argparse
@@ -30,21 +39,34 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-W, H, NCOMP, PREC, NUMRES, CBLK = 4096, 2160, 3, 16, 6, 6
-WORKLOAD = "j2k_decode_4096x2160_rgb16_97_ict_5lvl_cblk64_1tile"
+W, H, NCOMP, NUMRES, CBLK = 4096, 2160, 3, 6, 6
 SEED = 4096
-HT = False  # --workload ht: BASELINE configs[2], 12-bit HTJ2K lossless (5/3 + RCT) decode
-
-
-def select_workload(name):
-    global PREC, WORKLOAD, HT
-    if name == "ht":
-        PREC, HT = 12, True
-        WORKLOAD = "htj2k_decode_4096x2160_rgb12_53_rct_lossless_5lvl_cblk64_1tile"
+WORKLOADS = {
+    "j2k97": dict(name="j2k_decode_4096x2160_rgb16_97_ict_5lvl_cblk64_1tile", prec=16, ht=False, irr=1,
+                  dtype="f32"),
+    "ht": dict(name="htj2k_decode_4096x2160_rgb12_53_rct_lossless_5lvl_cblk64_1tile", prec=12, ht=True, irr=0,
+               dtype="i32"),
+}
+# MQ decisions of the configs[1] frame and the kernel's instruction counts: from the committed ncu
+# capture, not measured in this run
+T1_PROFILE = os.path.join(ROOT, "profiles", "t1_mq_decode_profile.json")
 
 
 def log(*a):
     print(*a, file=sys.stderr, flush=True)
+
+
+def dist_env():
+    """(rank, local_rank, world_size) from the torchrun environment"""
+    rank = int(os.environ.get("RANK", "0"))
+    return rank, int(os.environ.get("LOCAL_RANK", str(rank))), int(os.environ.get("WORLD_SIZE", "1"))
+
+
+def config_dict(wl, world):
+    """identical for both arms (anything else goes under "detail")"""
+    return {"workload": wl["name"], "width": W, "height": H, "components": NCOMP, "precision": wl["prec"],
+            "wavelet": "5/3" if wl["ht"] else "9/7", "mct": "RCT" if wl["ht"] else "ICT", "levels": NUMRES - 1,
+            "block_coder": "HT" if wl["ht"] else "MQ", "cblk": "64x64", "frames_per_step": world}
 
 
 def peaks():
@@ -54,55 +76,41 @@ def peaks():
     return 6650.0, "fallback"
 
 
-def cache_path(tag):
-    key = hashlib.sha1(("%s-%d-%d-%d-%d-%d-%d-v4" % (tag, W, H, PREC, NUMRES, SEED, HT)).encode()).hexdigest()[:12]
-    d = os.environ.get("GRKB_BENCH_CACHE", "/tmp")
-    return os.path.join(d, "grkb_bench_%s_%s.npz" % (tag, key))
+def cache_path(tag, wl):
+    key = hashlib.sha1(("%s-%d-%d-%d-%d-%d-%d-v5" % (tag, W, H, wl["prec"], NUMRES, SEED, wl["ht"])).encode()).hexdigest()[:12]
+    return os.path.join(os.environ.get("GRKB_BENCH_CACHE", "/tmp"), "grkb_bench_%s_%s.npz" % (tag, key))
 
 
-def synth_frame():
-    import codec_helpers as Hh
-    p = cache_path("img")
+def synth_frame(wl):
+    """the 16-bit frame of configs[1]; configs[2] is the same field >> 4"""
+    import synth as Hh
+    base = dict(WORKLOADS["j2k97"])
+    p = cache_path("img", base)
     if os.path.exists(p):
-        return list(np.load(p)["img"])
-    t = time.time()
-    img = Hh.synth_image(W, H, NCOMP, PREC, SEED)
-    np.savez(p + ".tmp.npz", img=np.stack(img))
-    os.replace(p + ".tmp.npz", p)
-    log("[bench] synthetic frame generated in %.1f s" % (time.time() - t))
-    return img
+        img = list(np.load(p)["img"])
+    else:
+        t = time.time()
+        img = Hh.synth_image(W, H, NCOMP, 16, SEED)
+        np.savez(p + ".tmp.npz", img=np.stack(img))
+        os.replace(p + ".tmp.npz", p)
+        log("[bench] synthetic frame generated in %.1f s" % (time.time() - t))
+    return [a >> (16 - wl["prec"]) for a in img] if wl["prec"] != 16 else img
 
 
-def coded_tile(img):
-    """descriptor table + byte pool of the frame (setup, untimed): forward path on the GPU
-    stages (parity-tested), block coding on the host cores with the reference's T1 encoder
-    when oracle/_ref is present, else the oracle port."""
-    import codec_helpers as Hh
-    import grok_b200
+def codestream(wl, img=None):
+    """the stock reference encoder's codestream of the frame (set-up, untimed)"""
     from oracle import oracle as O
-    p = cache_path("tile")
-    if os.path.exists(p):
-        z = np.load(p)
-        return dict(blocks=z["blocks"], segs=z["segs"], data=z["data"])
-    t = time.time()
-    coefs = grok_b200.stages.mct_fdwt(img, 0, 0, NUMRES, 1 if HT else 0, 1, [1 << (PREC - 1)] * 3)
-    tile = Hh.encode_tile(coefs, PREC, HT, NUMRES, (CBLK, CBLK), use_ref=O.have_ref(),
-                          threads=os.cpu_count(), ht=HT)
-    np.savez(p + ".tmp.npz", blocks=tile["blocks"], segs=tile["segs"], data=tile["data"])
-    os.replace(p + ".tmp.npz", p)
-    log("[bench] frame coded on the host in %.1f s: %d blocks, %.1f MB" %
-        (time.time() - t, len(tile["blocks"]), tile["data"].size / 1e6))
-    return tile
-
-
-def codestream(img):
-    from oracle import oracle as O
-    p = cache_path("cs")
+    p = cache_path("cs", wl)
     if os.path.exists(p):
         return np.load(p)["cs"]
+    if not O.have_ref():
+        raise SystemExit("bench.py: oracle/_ref/libgrok_ref.so (the compiled reference) is needed to write the "
+                         "workload's codestream; build it with __graft_entry__.build() where /root/reference exists")
+    if img is None:
+        img = synth_frame(wl)
     t = time.time()
-    cs = O.ref_codec_encode(img, PREC, 0 if HT else 1, ht=HT, numres=NUMRES,
-                            cblk=(1 << CBLK, 1 << CBLK), threads=os.cpu_count())
+    cs = O.ref_codec_encode(img, wl["prec"], wl["irr"], ht=wl["ht"], numres=NUMRES, cblk=(1 << CBLK, 1 << CBLK),
+                            threads=os.cpu_count())
     np.savez(p + ".tmp.npz", cs=cs)
     os.replace(p + ".tmp.npz", p)
     log("[bench] reference codestream written in %.1f s: %.1f MB" % (time.time() - t, cs.size / 1e6))
@@ -149,10 +157,7 @@ class ClockSampler:
                 "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
 
 
-def dist_env():
-    from grok_b200 import shard
-    return shard.dist_env()
-
+# ------------------------------------------------------------------------------------ reference arm
 
 def cpu_reference_decode(cs, steps, warmup, threads):
     """the stock reference decoder on the whole frame; returns (MP/s, seconds per frame)"""
@@ -166,71 +171,175 @@ def cpu_reference_decode(cs, steps, warmup, threads):
     return W * H / 1e6 / dt, dt
 
 
-def cpu_port_decode(tile):
-    """no compiled reference on this box: the single-threaded oracle port on a bounded sample
-    of the frame's code blocks (T1 + dequantisation only), scaled to the frame"""
-    from oracle import oracle as O
-    idx = np.arange(0, len(tile["blocks"]), max(1, len(tile["blocks"]) // 200))
-    t = time.perf_counter()
-    px = 0
-    for i in idx:
-        b = tile["blocks"][i]
-        if b["numsegs"] == 0:
-            continue
-        sg = [(int(s["len"]), int(s["numpasses"])) for s in
-              tile["segs"][b["seg_first"]:b["seg_first"] + b["numsegs"]]]
-        raw = tile["data"][b["data_off"]:b["data_off"] + b["data_len"]].tobytes()
-        O.orc_t1_decode(raw, sg, int(b["numbps"]), int(b["w"]), int(b["h"]), orient=int(b["orient"]))
-        px += int(b["w"]) * int(b["h"])
-    dt = time.perf_counter() - t
-    return px / NCOMP / 1e6 / dt, len(idx)
-
-
-def run_reference(args):
+def run_reference(args, wl):
     rank, local, world = dist_env()
     if rank != 0:
         return 0
-    from oracle import oracle as O
     threads = os.cpu_count() or 1
-    base = {"impl": "reference", "metric": "decode_mpixels_per_s", "unit": "Mpixel/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "i32" if HT else "f32",
-            "data": "synthetic", "gpu_launches": 0,
-            "config": {"workload": WORKLOAD, "width": W, "height": H, "components": NCOMP,
-                       "precision": PREC, "wavelet": "5/3" if HT else "9/7",
-                       "mct": "RCT" if HT else "ICT", "levels": NUMRES - 1,
-                       "block_coder": "HT" if HT else "MQ", "cblk": "64x64", "frames_per_step": 1}}
-    img = synth_frame()
-    if O.have_ref():
-        cs = codestream(img)
-        val, dt = cpu_reference_decode(cs, args.steps, args.warmup, threads)
-        kind = "reference"
-        sample = ("whole frame: stock grk decompress (public C API, memory stream, T2 included), "
-                  "%d steps" % args.steps)
-    else:
-        tile = coded_tile(img)
-        val, n = cpu_port_decode(tile)
-        dt = W * H / 1e6 / val
-        kind, threads = "port", 1
-        sample = "oracle port, T1 decode of %d of %d code blocks, scaled" % (n, len(tile["blocks"]))
-    base.update({"value": val, "ms_per_step": dt * 1e3,
-                 "cpu_baseline": {"value": val, "unit": "Mpixel/s", "cores": threads, "kind": kind,
-                                  "sample": sample},
-                 "e2e": {"value": val, "unit": "Mpixel/s", "h2d_bytes_per_step": 0,
-                         "d2h_bytes_per_step": 0}})
-    print(json.dumps(base), flush=True)
+    cs = codestream(wl)
+    val, dt = cpu_reference_decode(cs, args.steps, args.warmup, threads)
+    line = {"impl": "reference", "metric": "decode_mpixels_per_s", "value": val, "unit": "Mpixel/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": wl["dtype"],
+            "data": "synthetic", "gpu_launches": 0, "config": config_dict(wl, world),
+            "cpu_baseline": {"value": val, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
+                             "sample": "whole frame: stock grk decompress (public C API, memory stream, markers + T2 "
+                                       "+ T1 + wavelet + MCT), %d steps" % args.steps},
+            "e2e": {"value": val, "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
     return 0
 
 
-def run_ours(args):
+# ------------------------------------------------------------------------------------ our arm
+
+def measure(wl, args, local, barrier, with_parity=True):
+    """all legs of one workload on this rank's GPU; returns a dict of raw figures (ms per frame)"""
+    from grok_b200 import codestream as CS
+    from grok_b200 import tile as T
+    from oracle import oracle as O
+    cs_arr = codestream(wl)
+    pin_cs = T.PinnedArray((cs_arr.size + 16,), np.uint8)
+    pin_cs.array[:cs_arr.size] = cs_arr
+    cs = pin_cs.array[:cs_arr.size]
+    # ---- our own T2 once, for the device-resident leg
+    c = CS.Codestream(cs)
+    t0 = time.perf_counter()
+    tab = c.parse_tile(0)
+    t2_ms = (time.perf_counter() - t0) * 1e3
+    c.close()
+    blocks, segs, data = tab["blocks"], tab["segs"], tab["data"]
+    params = tab["params"]
+    dec = T.TileDecoder(params, len(blocks), data.size)
+    pin_out = [T.PinnedArray((H, W), np.int32) for _ in range(NCOMP)]
+    out = [p.array for p in pin_out]
+    dec.decode(blocks, segs, data, out=out)
+    if dec.rejected:
+        raise SystemExit("bench.py: %d code blocks rejected" % dec.rejected)
+    res = {"blocks": int(len(blocks)), "coded_bytes": int(cs_arr.size), "t2_ms_single": t2_ms,
+           "passes_max": int(segs["numpasses"].max()) if len(segs) else 0}
+    # ---- parity: the stock decoder's planes of the very same codestream (untimed)
+    if with_parity:
+        if O.have_ref():
+            want = O.ref_codec_decode(cs_arr, NCOMP, W, H, threads=os.cpu_count())
+            diff = max(int(np.abs(a.astype(np.int64) - b).max()) for a, b in zip(out, want))
+            res["parity"] = {"checked": True, "max_abs_diff": diff, "vs": "oracle/_ref stock grk_decompress of the same "
+                             "codestream", "tolerance": 0 if wl["ht"] else 1}
+            if diff > (0 if wl["ht"] else 1):
+                raise SystemExit("bench.py: PARITY FAILURE on %s: max |diff| = %d" % (wl["name"], diff))
+        else:
+            res["parity"] = {"checked": False, "why": "oracle/_ref not present on this box"}
+    # ---- value: device-resident decode, CUDA events on the decoder's stream
+    barrier()
+    res["tm"] = dec.time_device(args.steps, args.warmup)
+    barrier()
+    # ---- e2e: the codestream door, K frames in flight (one decompressor each, one slot each)
+    K = max(1, args.inflight if args.inflight else (2 if wl["ht"] else 4))
+    dzs = [CS.Decompressor(local, slots=1) for _ in range(K)]
+    outs = [out] + [[T.PinnedArray((H, W), np.int32).array for _ in range(NCOMP)] for _ in range(K - 1)]
+
+    def e2e_pass(n, packed=None):
+        for i in range(n):
+            d = dzs[i % K]
+            if i >= K:
+                d.wait()
+            if packed is None:
+                d.submit(cs, outs[i % K])
+            else:
+                d.submit_packed(cs, packed[i % K], NCOMP)
+        for i in range(max(n - K, 0), n):
+            dzs[i % K].wait()
+
+    for o in outs:
+        for p in o:
+            p[:] = 0
+    e2e_pass(max(min(args.warmup, 3), K))
+    barrier()
+    t0 = time.perf_counter()
+    e2e_pass(args.steps)
+    res["e2e_ms"] = (time.perf_counter() - t0) * 1e3 / args.steps
+    barrier()
+    res["t2_ms"] = dzs[0].stats()["t2_ms"]
+    if any(d.rejected for d in dzs) or not all(np.array_equal(a, b) for o in outs[1:] for a, b in zip(outs[0], o)):
+        raise SystemExit("bench.py: the frames in flight disagree")
+    # ---- the same with 16-bit samples across the bus (row N3, opt-in)
+    outs16 = [T.PinnedArray((NCOMP, H, W), np.uint16).array for _ in range(K)]
+    e2e_pass(max(min(args.warmup, 3), K), outs16)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_pass(args.steps, outs16)
+    res["e2e16_ms"] = (time.perf_counter() - t0) * 1e3 / args.steps
+    barrier()
+    if not all(np.array_equal(o[k], outs[0][k].astype(np.uint16)) for o in outs16 for k in range(NCOMP)):
+        raise SystemExit("bench.py: 16-bit output differs from the int32 planes")
+    res["K"] = K
+    res["h2d"] = int(cs_arr.size + blocks.nbytes + segs.nbytes + 4 * len(blocks))
+    for d in dzs:
+        d.close()
+    dec.close()
+    return res
+
+
+_PLUGIN_OPEN = False
+
+
+def plugin_legs(wl, args):
+    """N = 1: the frame through the reference's own plugin doors with the unmodified host"""
+    from oracle import oracle as O
+    import tempfile
+    if not O.have_plugin():
+        return None
+    try:
+        import ctypes as C
+        global _PLUGIN_OPEN
+        if not _PLUGIN_OPEN:
+            O.ref_plugin_open(device=0)
+            _PLUGIN_OPEN = True
+        cs_arr = codestream(wl)
+        d = tempfile.mkdtemp(prefix="grkb_bench_")
+        path = os.path.join(d, "frame.j2k")
+        cs_arr.tofile(path)
+        ms = C.c_double()
+        steps = max(3, min(args.steps, 10))
+        rc = O.ref().ref_plugin_decode_bench(path.encode(), C.c_uint32(NCOMP), C.c_uint32(W), C.c_uint32(H),
+                                            C.c_uint32(steps), C.c_uint32(2), C.byref(ms))
+        out = {}
+        if rc == 0:
+            out["e2e_plugin"] = {"value": W * H / 1e6 / (ms.value * 1e-3), "unit": "Mpixel/s", "ms_per_step": ms.value,
+                                 "door": "grk_plugin_decompress, one synchronous call per frame: file read + host "
+                                         "header + own T2 + H2D + kernels + D2H into the host's grk_image",
+                                 "host": "unmodified reference (oracle/_ref) with libgrokj2k_plugin.so loaded"}
+        else:
+            out["e2e_plugin"] = {"value": None, "error": "ref_plugin_decode_bench rc %d" % rc}
+        nb = 16
+        ind, outd = os.path.join(d, "in"), os.path.join(d, "out")
+        os.makedirs(ind)
+        os.makedirs(outd)
+        for i in range(nb):
+            os.link(path, os.path.join(ind, "f%03d.j2k" % i))
+        O.ref().ref_plugin_batch_decode_bench(ind.encode(), outd.encode(), C.byref(ms))  # warm-up
+        n = O.ref().ref_plugin_batch_decode_bench(ind.encode(), outd.encode(), C.byref(ms))
+        if n == nb:
+            out["e2e_plugin_batch"] = {"value": nb * W * H / 1e6 / (ms.value * 1e-3), "unit": "Mpixel/s",
+                                       "ms_per_step": ms.value / nb, "frames": nb,
+                                       "door": "grk_plugin_batch_decompress over a directory of %d files, the plugin's "
+                                               "worker pool (one decoder per worker)" % nb}
+        else:
+            out["e2e_plugin_batch"] = {"value": None, "error": "batch returned %d" % n}
+        import shutil
+        shutil.rmtree(d, ignore_errors=True)
+        return out
+    except Exception as e:  # the plugin legs are extra keys; the line stands without them
+        return {"e2e_plugin": {"value": None, "error": str(e)[:200]}}
+
+
+def run_ours(args, wl):
     rank, local, world = dist_env()
     import grok_b200
-    from grok_b200 import tile as T
+    from grok_b200 import shard
     from oracle import oracle as O
     if grok_b200.lib.grkb_device_count() < 1:
         raise SystemExit("bench.py: no CUDA device visible; the product has no CPU fallback")
     grok_b200._lib.check(grok_b200.lib.grkb_set_device(local), "grkb_set_device")
-    from grok_b200 import shard
     numa_bound = shard.bind_to_device(local) if world > 1 else False
     dist = None
     if world > 1:
@@ -243,156 +352,160 @@ def run_ours(args):
         if dist is not None:
             dist.barrier()
 
-    # ---- setup (untimed): rank 0 builds the coded frame, the others read the cache
+    # ---- set-up (untimed): rank 0 writes the caches, the others read them
+    wl_ht = WORKLOADS["ht"]
+    second = None if (wl["ht"] or args.no_ht) else wl_ht
     if rank == 0:
-        img = synth_frame()
-        tile = coded_tile(img)
+        codestream(wl)
+        if second:
+            codestream(second)
     barrier()
-    if rank != 0:
-        img = synth_frame()
-        tile = coded_tile(img)
-    blocks, segs, data = tile["blocks"], tile["segs"], tile["data"]
-    params = T.tile_params(0, 0, W, H, NCOMP, NUMRES, 1 if HT else 0, 1, PREC)
-    dec = T.TileDecoder(params, len(blocks), data.size)
-    pin_data = T.PinnedArray((data.size,), np.uint8)
-    pin_data.array[:] = data
-    pin_blocks = T.PinnedArray((len(blocks),), T.CBLK_DTYPE)
-    pin_blocks.array[:] = blocks
-    pin_segs = T.PinnedArray((len(segs),), T.SEG_DTYPE)
-    pin_segs.array[:] = segs
-    blocks, segs = pin_blocks.array, pin_segs.array
-    pin_out = [T.PinnedArray((H, W), np.int32) for _ in range(NCOMP)]
-    out = [p.array for p in pin_out]
-
-    # first pass also makes the frame resident for the device-timed loop
-    dec.decode(blocks, segs, pin_data.array, out=out)
-    if dec.rejected:
-        raise SystemExit("bench.py: %d code blocks rejected" % dec.rejected)
-
-    sampler = ClockSampler(local) if rank == 0 else None
-    # ---- value: device-resident decode, CUDA events on the decoder's stream
+    sampler = ClockSampler(local)
+    main = measure(wl, args, local, barrier)
+    sub = None
+    if second:
+        a2 = argparse.Namespace(**vars(args))
+        a2.steps = max(5, args.steps // 2)
+        sub = measure(second, a2, local, barrier)
+    # ---- the link, all ranks at once
+    import ctypes as C
     barrier()
-    tm = dec.time_device(args.steps, args.warmup)
+    h2d, d2h, dup = C.c_double(), C.c_double(), (C.c_double * 2)()
+    grok_b200._lib.check(grok_b200.lib.grkb_bench_link(256 << 20, 4, C.byref(h2d), C.byref(d2h), dup), "grkb_bench_link")
     barrier()
-    ms = tm["total_ms"]
-    # ---- e2e: through the C-ABI with pinned host buffers, every step's H2D (descriptors +
-    # coded bytes) and D2H (three int32 planes) inside the timed region.  K decoders keep K
-    # frames in flight (submit frame i, then wait for frame i-K+1), so one frame's D2H overlaps the
-    # next frames' H2D + kernels; each step still moves and decodes a whole frame.
-    K = max(1, args.inflight if args.inflight else (2 if HT else 4))
-    decs = [(dec, out)]
-    for _ in range(K - 1):
-        pin_k = [T.PinnedArray((H, W), np.int32) for _ in range(NCOMP)]
-        decs.append((T.TileDecoder(params, len(blocks), data.size), [p.array for p in pin_k]))
-
-    def e2e_pass(n):
-        for i in range(n):
-            d, o = decs[i % K]
-            if i >= K:
-                d.wait()
-            d.submit(blocks, segs, pin_data.array, o)
-        for i in range(max(n - K, 0), n):
-            decs[i % K][0].wait()
-
-    e2e_pass(max(min(args.warmup, 3), K))
-    barrier()
-    t0 = time.perf_counter()
-    e2e_pass(args.steps)
-    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
-    barrier()
-    if any(d.rejected for d, _ in decs) or not all(
-            np.array_equal(a, b) for _, o in decs[1:] for a, b in zip(decs[0][1], o)):
-        raise SystemExit("bench.py: pipelined decode disagrees between the decoders in flight")
-    # ---- the same leg with the planes narrowed on the device (row N3, opt-in beyond the int32
-    # grk_image contract): D2H of 16-bit samples instead of int32
-    outs16 = [T.PinnedArray((NCOMP, H, W), np.uint16) for _ in range(K)]
-
-    def e2e16_pass(n):
-        for i in range(n):
-            d = decs[i % K][0]
-            if i >= K:
-                d.wait()
-            d.submit_packed(blocks, segs, pin_data.array, outs16[i % K].array)
-        for i in range(max(n - K, 0), n):
-            decs[i % K][0].wait()
-
-    e2e16_pass(max(min(args.warmup, 3), K))
-    barrier()
-    t0 = time.perf_counter()
-    e2e16_pass(args.steps)
-    e2e16_ms = (time.perf_counter() - t0) * 1e3 / args.steps
-    barrier()
-    if not all(np.array_equal(o.array[c], decs[0][1][c].astype(np.uint16)) for o in outs16 for c in range(NCOMP)):
-        raise SystemExit("bench.py: 16-bit output differs from the int32 planes")
-    clocks = sampler.stop() if sampler else None
+    clocks = sampler.stop()
+    # ---- max over ranks
+    keys = ["e2e_ms", "e2e16_ms"]
+    vals = [main["tm"]["total_ms"]] + [main[k] for k in keys]
+    if sub:
+        vals += [sub["tm"]["total_ms"]] + [sub[k] for k in keys]
+    link = [h2d.value, d2h.value, dup[0], dup[1]]
+    all_clocks = [clocks]
     if dist is not None:
         import torch
-        t = torch.tensor([ms, e2e_ms, e2e16_ms], dtype=torch.float64, device="cuda")
+        t = torch.tensor(vals, dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_ms, e2e16_ms = float(t[0]), float(t[1]), float(t[2])
+        vals = [float(x) for x in t]
+        t = torch.tensor(link, dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        link = [float(x) for x in t]
+        all_clocks = [None] * world
+        dist.all_gather_object(all_clocks, clocks)
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
         return 0
+    sm = [c["sm_mhz"] for c in all_clocks if c and c.get("sm_mhz")]
+    clocks = {"sm_mhz": min(sm) if sm else None,
+              "sm_max_mhz": max([c["sm_max_mhz"] for c in all_clocks if c and c.get("sm_max_mhz")] or [0]) or None,
+              "reasons": sorted({r for c in all_clocks if c for r in c.get("reasons", [])}),
+              "samples": sum(c.get("samples", 0) for c in all_clocks if c), "gpus_sampled": len(all_clocks),
+              "note": "sm_mhz = lowest per-GPU median under load"}
 
     mp = W * H / 1e6
     peak, peak_kind = peaks()
-    alg_last = 2 * 4 * W * H * NCOMP  # one read + one write of every sample of the last level
-    traffic = None
-    rp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
-    if os.path.exists(rp):
-        traffic = json.load(open(rp)).get("idwt_last_level_dram_bytes")
-    achieved = alg_last / (tm["dwt_last_ms"] * 1e-3) / 1e9 if tm["dwt_last_ms"] > 0 else 0.0
-    h2d = int(blocks.nbytes + segs.nbytes + 4 * len(blocks) + data.size)
-    d2h = int(NCOMP * W * H * 4 + 4)
-    # ---- cpu baseline beside it (rank 0, N = 1 only): bounded, ~10-30 s of host work
-    cpu = None
-    if world == 1 and not args.no_cpu_baseline:
+
+    def figures(wl_, r, ms, e2e_ms, e2e16_ms):
+        tm = r["tm"]
+        d2h_b = int(NCOMP * W * H * 4 + 4)
+        alg_last = 2 * 4 * W * H * NCOMP
+        alg_all = sum(2 * 4 * (-(-W >> l)) * (-(-H >> l)) for l in range(NUMRES - 1)) * NCOMP
+        ach = alg_last / (tm["dwt_last_ms"] * 1e-3) / 1e9 if tm["dwt_last_ms"] > 0 else 0.0
+        ach_all = alg_all / (tm["dwt_ms"] * 1e-3) / 1e9 if tm["dwt_ms"] > 0 else 0.0
+        traffic = None
+        rp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        if os.path.exists(rp) and not wl_["ht"]:
+            traffic = json.load(open(rp)).get("idwt_last_level_dram_bytes")
+        # what the link allows: the H2D and D2H of consecutive frames overlap (full duplex)
+        t_link = max(r["h2d"] / (link[2] * 1e9), d2h_b / (link[3] * 1e9)) if link[2] > 0 and link[3] > 0 else None
+        pcie_bound = world * mp / t_link if t_link else None
+        e2e_v = world * mp / (e2e_ms * 1e-3)
+        t1 = {"code_blocks_per_s": r["blocks"] / (tm["t1_ms"] * 1e-3) if tm["t1_ms"] > 0 else None,
+              "bound": "warp-instruction issue: serial %s chain per code block (not HBM)"
+                       % ("VLC/MEL/MagSgn" if wl_["ht"] else "MQ decision")}
+        if not wl_["ht"] and os.path.exists(T1_PROFILE):
+            prof = json.load(open(T1_PROFILE))
+            t1.update({"decisions_per_frame": prof["decisions_per_frame"],
+                       "decisions_per_s": prof["decisions_per_frame"] / (tm["t1_ms"] * 1e-3),
+                       "warp_inst_per_decision": prof["warp_inst_per_decision"],
+                       "issue_active_pct": prof["issue_active_pct"],
+                       "from": prof["source"] + " (committed ncu capture, not measured in this run)"})
+        return {
+            "value": world * mp / (ms * 1e-3), "ms_per_step": ms,
+            "e2e": {"value": e2e_v, "unit": "Mpixel/s", "frames_in_flight": r["K"], "h2d_bytes_per_step": r["h2d"],
+                    "d2h_bytes_per_step": d2h_b, "ms_per_step": e2e_ms,
+                    "boundary": "grkb_decompress_submit/_wait (C-ABI): codestream bytes in page-locked host memory in, "
+                                "int32 planes out; own marker + packet parsing (T2) inside the timed region, like "
+                                "the reference arm's",
+                    "host_t2_ms_per_frame": r["t2_ms"]},
+            "e2e_samples16": {"value": world * mp / (e2e16_ms * 1e-3), "unit": "Mpixel/s", "frames_in_flight": r["K"],
+                              "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": int(NCOMP * W * H * 2 + 4),
+                              "ms_per_step": e2e16_ms,
+                              "note": "grkb_decompress_submit_packed: planes narrowed to uint16 on the device "
+                                      "(SURVEY 8f N3, opt-in); `e2e` is the int32 grk_image contract"},
+            "pcie_bound": {"value": pcie_bound, "unit": "Mpixel/s",
+                           "what": "frames/s the link alone allows for this frame's H2D and D2H bytes, both "
+                                   "directions busy at once, at the rates measured below"},
+            "e2e_over_pcie_bound": (e2e_v / pcie_bound) if pcie_bound else None,
+            "roofline": {"bound": "hbm", "kernel": "idwt_strip_kernel<%s,3 comps,fused %s> (last level)"
+                                                    % (("K53", "RCT") if wl_["ht"] else ("K97", "ICT")),
+                         "achieved": ach, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s", "frac": ach / peak,
+                         "traffic": traffic,
+                         "traffic_note": "dram bytes of one ncu --set full capture under profiles/, not measured in "
+                                         "this run" if traffic else None,
+                         "algorithmic_bytes_per_launch": alg_last, "ms_per_launch": tm["dwt_last_ms"],
+                         "whole_dwt": {"bytes": alg_all, "ms": tm["dwt_ms"], "achieved": ach_all, "frac": ach_all / peak,
+                                       "what": "all %d levels of three components (SURVEY 8d: sum of 2*4*w_r*h_r), "
+                                               "MCT fused" % (NUMRES - 1)}},
+            "stages_ms": {("t1_ht_decode" if wl_["ht"] else "t1_mq_decode"): tm["t1_ms"],
+                          "idwt_all_levels_plus_mct": tm["dwt_ms"], "idwt_last_level": tm["dwt_last_ms"]},
+            "t1": t1,
+            "parity": r.get("parity"),
+            "detail": {"code_blocks": r["blocks"], "coded_bytes": r["coded_bytes"],
+                       "max_passes_in_a_block": r["passes_max"], "kernel_launches_per_step": int(tm["launches"])},
+        }
+
+    f = figures(wl, main, vals[0], vals[1], vals[2])
+    line = {"metric": "decode_mpixels_per_s", "value": f["value"], "unit": "Mpixel/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": f["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
+            "config": config_dict(wl, world)}
+    for k in ("e2e", "e2e_samples16", "pcie_bound", "e2e_over_pcie_bound", "roofline", "stages_ms", "t1", "parity",
+              "detail"):
+        line[k] = f[k]
+    line["gpu_launches"] = int(main["tm"]["launches"]) * args.steps
+    line["link"] = {"h2d_gbs": link[0], "d2h_gbs": link[1], "duplex_h2d_gbs": link[2], "duplex_d2h_gbs": link[3],
+                    "what": "page-locked cudaMemcpyAsync, 256 MiB x 4, all %d ranks at once (lowest rank)" % world}
+    line["detail"].update({"sharding": "one frame per GPU per step, no collective",
+                           "host_threads_bound_to_gpu_numa_node": bool(numa_bound),
+                           "l2": "working set per step (coded bytes + 2 x %d MB planes) exceeds the 126 MB L2"
+                                 % (NCOMP * W * H * 4 // 1000000)})
+    if sub:
+        g = figures(second, sub, vals[3], vals[4], vals[5])
+        line["ht"] = {"config": config_dict(second, world), "dtype": second["dtype"], "steps": max(5, args.steps // 2)}
+        for k in ("value", "ms_per_step", "e2e", "e2e_samples16", "pcie_bound", "e2e_over_pcie_bound", "roofline",
+                  "stages_ms", "t1", "parity", "detail"):
+            line["ht"][k] = g[k]
+    line["clocks"] = clocks
+    # ---- N = 1 only: the reference's own plugin doors, and the CPU baseline beside it
+    if world == 1 and not args.no_plugin:
+        pl = plugin_legs(wl, args)
+        if pl:
+            line.update(pl)
+        if second:
+            pl = plugin_legs(second, args)
+            if pl:
+                line["ht"].update(pl)
+    if world == 1 and not args.no_cpu_baseline and O.have_ref():
         threads = os.cpu_count() or 1
-        if O.have_ref():
-            cs = codestream(img)
-            v, dt = cpu_reference_decode(cs, 3, 1, threads)
-            cpu = {"value": v, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
-                   "sample": "whole frame x3: stock grk decompress (public C API, memory stream, "
-                             "T2 included), %.0f ms/frame" % (dt * 1e3)}
-        else:
-            v, n = cpu_port_decode(tile)
-            cpu = {"value": v, "unit": "Mpixel/s", "cores": 1, "kind": "port",
-                   "sample": "oracle port, T1 decode of %d of %d code blocks, scaled" % (n, len(blocks))}
-    line = {
-        "metric": "decode_mpixels_per_s", "value": world * mp / (ms * 1e-3), "unit": "Mpixel/s",
-        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "i32" if HT else "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "width": W, "height": H, "components": NCOMP,
-                   "precision": PREC, "wavelet": "5/3" if HT else "9/7",
-                   "mct": "RCT" if HT else "ICT", "levels": NUMRES - 1,
-                   "block_coder": "HT" if HT else "MQ", "cblk": "64x64", "code_blocks": int(len(blocks)), "coded_bytes": int(data.size),
-                   "frames_per_step": world, "sharding": "one frame per GPU per step, no collective",
-                   "host_threads_bound_to_gpu_numa_node": bool(numa_bound),
-                   "l2": "working set per step (coded bytes + 2 x %d MB planes) exceeds the 126 MB L2"
-                         % (NCOMP * W * H * 4 // 1000000)},
-        "e2e": {"value": world * mp / (e2e_ms * 1e-3), "unit": "Mpixel/s", "frames_in_flight": K,
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms},
-        "e2e_samples16": {"value": world * mp / (e2e16_ms * 1e-3), "unit": "Mpixel/s", "frames_in_flight": K,
-                          "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": int(NCOMP * W * H * 2 + 4),
-                          "ms_per_step": e2e16_ms,
-                          "note": "grkb_decoder_submit_packed: planes narrowed to uint16 on the device "
-                                  "(SURVEY 8f N3, opt-in); `e2e` above is the int32 grk_image contract"},
-        "gpu_launches": int(tm["launches"]) * args.steps,
-        "roofline": {"bound": "hbm", "kernel": "idwt_level_kernel<%s,3 comps,fused %s> (last level)"
-                                                % (("K53", "RCT") if HT else ("K97", "ICT")),
-                     "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": traffic,
-                     "algorithmic_bytes_per_launch": alg_last, "ms_per_launch": tm["dwt_last_ms"]},
-        "stages_ms": {"t1_ht_decode" if HT else "t1_mq_decode": tm["t1_ms"], "idwt_all_levels_plus_mct": tm["dwt_ms"],
-                      "idwt_last_level": tm["dwt_last_ms"]},
-        "t1": {"code_blocks_per_s": len(blocks) / (tm["t1_ms"] * 1e-3) if tm["t1_ms"] > 0 else None,
-               "bound": "serial %s rate per warp (not HBM)" % ("VLC/MEL/MagSgn" if HT else "MQ decision")},
-        "clocks": clocks,
-    }
-    if cpu:
-        line["cpu_baseline"] = cpu
+        v, dt = cpu_reference_decode(codestream(wl), 3, 1, threads)
+        line["cpu_baseline"] = {"value": v, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
+                                "sample": "whole frame x3: stock grk decompress (public C API, memory stream, markers "
+                                          "+ T2 + T1 + wavelet + MCT), %.0f ms/frame" % (dt * 1e3)}
+        if second:
+            v, dt = cpu_reference_decode(codestream(second), 3, 1, threads)
+            line["ht"]["cpu_baseline"] = {"value": v, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
+                                          "sample": "whole frame x3, %.0f ms/frame" % (dt * 1e3)}
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
@@ -406,16 +519,18 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-plugin", action="store_true", help="skip the grk_plugin_* legs (N = 1 extras)")
+    ap.add_argument("--no-ht", action="store_true", help="skip the configs[2] sub-line")
     ap.add_argument("--workload", default="j2k97", choices=["j2k97", "ht"])
     ap.add_argument("--inflight", type=int, default=None,
-                    help="decoders (frames) in flight on the e2e leg (default: 4 for the MQ workload, whose kernel "
-                         "tails overlap; 2 for HT, which is bound by the bus)")
+                    help="frames in flight on the e2e leg (default: 4 for the MQ workload, whose kernel tails "
+                         "overlap; 2 for HT, which is bound by the bus)")
     args = ap.parse_args()
-    select_workload(args.workload)
+    wl = WORKLOADS[args.workload]
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
-        return run_reference(args)
-    return run_ours(args)
+        return run_reference(args, wl)
+    return run_ours(args, wl)
 
 
 if __name__ == "__main__":

@@ -100,6 +100,8 @@ lib.grkb_host_free.argtypes = [_vp]
 lib.grkb_host_free.restype = None
 lib.grkb_host_register.argtypes = [_vp, C.c_size_t]
 lib.grkb_host_unregister.argtypes = [_vp]
+lib.grkb_bench_link.argtypes = [C.c_size_t, _u32, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                C.POINTER(C.c_double)]
 # section D: the allocation-free door (device pointers in and out, built-in scratch)
 lib.grkb_idwt_device_noalloc.argtypes = [_vp, _u32, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _int, _vp]
 NOALLOC_SCRATCH_BYTES = 8 << 20

@@ -597,3 +597,85 @@ extern "C" int grkb_bench_dwt(uint32_t w, uint32_t h, uint32_t numres, int rever
 	cudaEventDestroy(e1);
 	return 0;
 }
+
+
+// Host <-> device link bandwidth with page-locked memory, measured the way the decoders use the
+// link: one cudaMemcpyAsync per direction on a stream of its own.  h2d / d2h: each direction alone;
+// duplex[0..1]: both at once (what a pipelined decode sees).  GB/s (1e9 bytes).
+extern "C" int grkb_bench_link(size_t bytes, uint32_t iters, double* h2d_gbs, double* d2h_gbs, double duplex_gbs[2])
+{
+	if(bytes < 4096 || iters == 0)
+	{
+		grkb_set_error("grkb_bench_link: bad arguments");
+		return -1;
+	}
+	void *hin = nullptr, *hout = nullptr;
+	DevBuf din, dout;
+	if(cudaMallocHost(&hin, bytes) != cudaSuccess || cudaMallocHost(&hout, bytes) != cudaSuccess || din.alloc(bytes) ||
+	   dout.alloc(bytes))
+	{
+		if(hin)
+			cudaFreeHost(hin);
+		if(hout)
+			cudaFreeHost(hout);
+		grkb_set_error("grkb_bench_link: allocation failed");
+		return -1;
+	}
+	memset(hin, 1, bytes);
+	memset(hout, 0, bytes);
+	cudaStream_t s0, s1;
+	cudaEvent_t e[4];
+	int rc = -1;
+	if(cudaStreamCreateWithFlags(&s0, cudaStreamNonBlocking) == cudaSuccess &&
+	   cudaStreamCreateWithFlags(&s1, cudaStreamNonBlocking) == cudaSuccess)
+	{
+		for(auto& x : e)
+			cudaEventCreate(&x);
+		auto run = [&](bool up, bool down, float& ms_up, float& ms_down) {
+			// warm-up
+			if(up)
+				cudaMemcpyAsync(din.p, hin, bytes, cudaMemcpyHostToDevice, s0);
+			if(down)
+				cudaMemcpyAsync(hout, dout.p, bytes, cudaMemcpyDeviceToHost, s1);
+			cudaStreamSynchronize(s0);
+			cudaStreamSynchronize(s1);
+			cudaEventRecord(e[0], s0);
+			cudaEventRecord(e[2], s1);
+			for(uint32_t i = 0; i < iters; ++i)
+			{
+				if(up)
+					cudaMemcpyAsync(din.p, hin, bytes, cudaMemcpyHostToDevice, s0);
+				if(down)
+					cudaMemcpyAsync(hout, dout.p, bytes, cudaMemcpyDeviceToHost, s1);
+			}
+			cudaEventRecord(e[1], s0);
+			cudaEventRecord(e[3], s1);
+			cudaStreamSynchronize(s0);
+			cudaStreamSynchronize(s1);
+			cudaEventElapsedTime(&ms_up, e[0], e[1]);
+			cudaEventElapsedTime(&ms_down, e[2], e[3]);
+		};
+		float a = 0, b = 0, c = 0, d = 0, x = 0;
+		run(true, false, a, x);
+		run(false, true, x, b);
+		run(true, true, c, d);
+		const double gb = (double)bytes * iters / 1e9;
+		if(h2d_gbs)
+			*h2d_gbs = a > 0 ? gb / (a * 1e-3) : 0;
+		if(d2h_gbs)
+			*d2h_gbs = b > 0 ? gb / (b * 1e-3) : 0;
+		if(duplex_gbs)
+		{
+			duplex_gbs[0] = c > 0 ? gb / (c * 1e-3) : 0;
+			duplex_gbs[1] = d > 0 ? gb / (d * 1e-3) : 0;
+		}
+		rc = cudaGetLastError() == cudaSuccess ? 0 : -1;
+		for(auto& x2 : e)
+			cudaEventDestroy(x2);
+		cudaStreamDestroy(s0);
+		cudaStreamDestroy(s1);
+	}
+	cudaFreeHost(hin);
+	cudaFreeHost(hout);
+	return rc;
+}

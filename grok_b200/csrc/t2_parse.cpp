@@ -70,8 +70,15 @@ struct BitReader
 	inline uint32_t bits(uint32_t n)
 	{
 		uint32_t v = 0;
-		while(n--)
-			v = (v << 1) | bit();
+		while(n)
+		{
+			if(ct == 0)
+				bytein();
+			const uint32_t take = n < ct ? n : ct;
+			ct -= take;
+			v = (v << take) | ((buf >> ct) & ((1u << take) - 1u));
+			n -= take;
+		}
 		return v;
 	}
 	// end of the header: the stuffing byte after a final 0xFF belongs to it
@@ -174,6 +181,66 @@ struct TagArena
 		}
 		return nodes[path[0]].value < threshold;
 	}
+	// The leaf's value outright: what `i = 1; while(!decode(leaf, i)) ++i;` reads (the reference's
+	// zero-bit-plane loop, T2Decompress.cpp:333-349), in one walk from the root.  limit: give up
+	// (corrupt stream) beyond this value.
+	uint32_t decode_value(BitReader& br, const TagTree& t, uint32_t leaf, uint32_t limit)
+	{
+		uint32_t path[34];
+		int depth = 0;
+		uint32_t x = leaf % t.w, y = leaf / t.w, lw = t.w, lh = t.h, base = t.first;
+		while(true)
+		{
+			path[depth++] = base + y * lw + x;
+			if(lw <= 1 && lh <= 1)
+				break;
+			base += lw * lh;
+			x >>= 1;
+			y >>= 1;
+			lw = (lw + 1) >> 1;
+			lh = (lh + 1) >> 1;
+		}
+		uint32_t low = 0;
+		for(int i = depth - 1; i >= 0; --i)
+		{
+			TagNode& nd = nodes[path[i]];
+			if(low < nd.low)
+				low = nd.low;
+			while(nd.value == 0xFFFF)
+			{
+				if(br.bit())
+					nd.value = (uint16_t)low;
+				else if(++low > limit)
+					throw Corrupt{"zero bit-plane count out of range"};
+			}
+			low = nd.value;
+			nd.low = (uint16_t)low;
+		}
+		return low;
+	}
+};
+
+// a few elements inline, more on the heap: almost every block has one segment and one chunk
+template<typename T, unsigned N>
+struct SmallVec
+{
+	T inl[N];
+	uint32_t n = 0;
+	std::vector<T> more;
+	bool empty() const { return n == 0; }
+	size_t size() const { return n; }
+	T& operator[](size_t i) { return i < N ? inl[i] : more[i - N]; }
+	const T& operator[](size_t i) const { return i < N ? inl[i] : more[i - N]; }
+	T& back() { return (*this)[n - 1]; }
+	T& emplace_back()
+	{
+		if(n < N)
+			inl[n] = T();
+		else
+			more.emplace_back();
+		return (*this)[n++];
+	}
+	void push_back(const T& v) { emplace_back() = v; }
 };
 
 // what T2 keeps per code block between packets
@@ -362,8 +429,12 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 		}
 	// ---- T2 state
 	std::vector<BlockState> st((size_t)ng * nc);
-	std::vector<std::vector<SegState>> bsegs; // per block that was ever included (index in seg_of)
-	std::vector<std::vector<Chunk>> bchunks;
+	typedef SmallVec<SegState, 2> Segs;
+	typedef SmallVec<Chunk, 1> Chunks;
+	std::vector<Segs> bsegs; // per block that was ever included (slot[])
+	std::vector<Chunks> bchunks;
+	bsegs.reserve((size_t)ng * nc);
+	bchunks.reserve((size_t)ng * nc);
 	std::vector<uint32_t> slot((size_t)ng * nc, UINT32_MAX);
 	std::vector<uint8_t> numbps((size_t)ng * nc, 0);
 	TagArena arena;
@@ -474,13 +545,7 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 						}
 						if(!B.numlenbits)
 						{
-							uint32_t i = 1;
-							while(!arena.decode(br, imsb[ti], cb, i))
-							{
-								if(++i > MAX_BITPLANES + 50)
-									throw Corrupt{"zero bit-plane count out of range"};
-							}
-							const uint32_t kmsbs = i - 1;
+							const uint32_t kmsbs = arena.decode_value(br, imsb[ti], cb, MAX_BITPLANES + 50);
 							uint32_t nb = kmsbs > band_numbps ? MAX_BITPLANES : band_numbps - kmsbs;
 							if(nb > MAX_BITPLANES)
 								nb = MAX_BITPLANES;
@@ -492,7 +557,7 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 						}
 						B.passes_in_packet = br.numpasses();
 						B.numlenbits += br.comma();
-						std::vector<SegState>& S = bsegs[slot[bi]];
+						Segs& S = bsegs[slot[bi]];
 						if(S.empty())
 						{
 							S.emplace_back();
@@ -547,7 +612,7 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 			for(uint32_t bi : touched)
 			{
 				BlockState& B = st[bi];
-				std::vector<SegState>& S = bsegs[slot[bi]];
+				Segs& S = bsegs[slot[bi]];
 				for(size_t k = B.first_seg_in_packet; k < S.size(); ++k)
 				{
 					SegState& sg = S[k];
@@ -565,7 +630,7 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 					}
 					if(sg.bytes_in_packet && keep && !B.dropped)
 					{
-						std::vector<Chunk>& C = bchunks[slot[bi]];
+						Chunks& C = bchunks[slot[bi]];
 						if(!C.empty() && C.back().off + C.back().len == at)
 							C.back().len += sg.bytes_in_packet;
 						else
@@ -719,11 +784,12 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 			const uint32_t bi = c * ng + i;
 			if(slot[bi] == UINT32_MAX || st[bi].dropped)
 				continue;
-			const std::vector<Chunk>& C = bchunks[slot[bi]];
+			const Chunks& C = bchunks[slot[bi]];
 			if(C.size() > 1)
 				single = false;
-			for(const Chunk& k : C)
+			for(size_t ki = 0; ki < C.size(); ++ki)
 			{
+				const Chunk& k = C[ki];
 				lo = std::min(lo, k.off);
 				hi = std::max(hi, k.off + k.len);
 				total += k.len;
@@ -775,7 +841,7 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 			b.numbps = numbps[bi];
 			const uint32_t band_numbps = q.numbps;
 			b.k_msbs = (uint8_t)(band_numbps > b.numbps ? band_numbps - b.numbps : 0);
-			const std::vector<Chunk>& C = bchunks[slot[bi]];
+			const Chunks& C = bchunks[slot[bi]];
 			uint32_t nbytes = 0;
 			if(single)
 			{
@@ -788,16 +854,19 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 			else
 			{
 				b.data_off = (uint32_t)out.pool.size();
-				for(const Chunk& k : C)
+				for(size_t ki = 0; ki < C.size(); ++ki)
 				{
+					const Chunk& k = C[ki];
 					out.pool.insert(out.pool.end(), cs.data + k.off, cs.data + k.off + k.len);
 					nbytes += k.len;
 				}
 			}
 			b.data_len = nbytes;
 			uint32_t ns = 0;
-			for(const SegState& sg : bsegs[slot[bi]])
+			const Segs& SS = bsegs[slot[bi]];
+			for(size_t si2 = 0; si2 < SS.size(); ++si2)
 			{
+				const SegState& sg = SS[si2];
 				if(sg.kpasses == 0)
 					continue;
 				out.segs.push_back(grkb_seg{sg.klen, sg.kpasses});

@@ -669,7 +669,15 @@ int grkb_host_register(void* p, size_t bytes)
 {
 	if(!p || !bytes)
 		return -1;
-	GRKB_CUDA_CHECK(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
+	// may fail harmlessly (small buffers sharing a page with registered memory): the copies then go
+	// through the driver's staging buffer; the error must not linger for the next launch check
+	const cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+	if(e != cudaSuccess)
+	{
+		cudaGetLastError();
+		grkb_set_error("grkb_host_register: %s", cudaGetErrorString(e));
+		return -1;
+	}
 	return 0;
 }
 
@@ -677,7 +685,11 @@ int grkb_host_unregister(void* p)
 {
 	if(!p)
 		return -1;
-	GRKB_CUDA_CHECK(cudaHostUnregister(p));
+	if(cudaHostUnregister(p) != cudaSuccess)
+	{
+		cudaGetLastError();
+		return -1;
+	}
 	return 0;
 }
 

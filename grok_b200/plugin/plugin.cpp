@@ -451,18 +451,28 @@ struct CachedImage
 	{
 		drop();
 	}
-	std::vector<void*> registered;
+	// The planes are page-locked memory of ours (the device writes them by DMA), lent to a host image
+	// created without data; they are taken back before the host object is released, so the host's
+	// allocator never sees them.  (Registering the host's own allocation instead is not safe: small
+	// planes share pages with unrelated heap memory, and a copy that straddles registered and
+	// unregistered pages is refused by the driver.)
+	std::vector<void*> pinned;
 	void drop()
 	{
-		for(void* p : registered)
-			grkb_host_unregister(p);
-		registered.clear();
+		if(image && !pinned.empty())
+			for(uint32_t c = 0; c < image->numcomps && image->comps; ++c)
+				image->comps[c].data = nullptr;
+		for(void* p : pinned)
+			grkb_host_free(p);
+		pinned.clear();
 		if(image && host_unref())
 			host_unref()(&image->obj);
 		image = nullptr;
 	}
+	// lend_planes: decode side (see above).  On the encode side the host takes the planes over
+	// (its compressor moves the data pointers into its own image), so they are the host's allocation.
 	grk_image* get(uint32_t W, uint32_t H, uint32_t numcomps, uint32_t precision, bool is_signed, uint32_t ox,
-				   uint32_t oy)
+				   uint32_t oy, bool lend_planes = false)
 	{
 		bool ok = image && w == W && h == H && nc == numcomps && prec == precision && sgnd == is_signed &&
 				  x0 == ox && y0 == oy && image->numcomps == numcomps && image->comps;
@@ -487,20 +497,29 @@ struct CachedImage
 			c.y0 = oy;
 		}
 		image = host_image_new()((uint16_t)numcomps, cp.data(), numcomps >= 3 ? GRK_CLRSPC_SRGB : GRK_CLRSPC_GRAY,
-								 true);
+								 !lend_planes);
+		if(image && lend_planes)
+		{
+			// planes start from zeros: a reduced image may have a last row / column no tile covers,
+			// which the reference leaves at zero
+			const uint32_t stride = (W + 31u) & ~31u;
+			for(uint32_t c = 0; c < numcomps; ++c)
+			{
+				const size_t bytes = (size_t)stride * H * sizeof(int32_t);
+				void* p = grkb_host_alloc(bytes);
+				if(!p)
+				{
+					drop();
+					return nullptr;
+				}
+				memset(p, 0, bytes);
+				pinned.push_back(p);
+				image->comps[c].data = (int32_t*)p;
+				image->comps[c].stride = stride;
+			}
+		}
 		if(image)
 		{
-			// the device writes straight into the host's planes: page-lock them once (they live as long
-			// as the slot), and start from zeros (a reduced image may have a last row / column no tile
-			// covers, which the reference leaves at zero)
-			for(uint32_t c = 0; c < numcomps; ++c)
-				if(image->comps[c].data)
-				{
-					const size_t bytes = (size_t)image->comps[c].stride * H * sizeof(int32_t);
-					memset(image->comps[c].data, 0, bytes);
-					if(grkb_host_register(image->comps[c].data, bytes) == 0)
-						registered.push_back(image->comps[c].data);
-				}
 			image->x0 = ox;
 			image->y0 = oy;
 			image->x1 = ox + W;
@@ -578,6 +597,7 @@ std::mutex g_cb_mutex; // GRKB_BATCH_SERIAL_CALLBACK=1: one host callback at a t
 // buffers costs as much as several frames).  Heap-allocated and released in exit_func only: no
 // CUDA call is left to the static destructors.
 std::vector<std::unique_ptr<EncodeCtx>>* g_ctx_pool = new std::vector<std::unique_ptr<EncodeCtx>>();
+EncodeCtx* g_single_ctx = nullptr; // grk_plugin_compress (one frame per call)
 
 // What the host's grk_compress_init will do to the parameters of a digital-cinema profile before its
 // rate allocation and T2 run (codestream/CodeStreamCompress.cpp:219-235 -> Profile::is_cinema_compliant
@@ -1100,6 +1120,7 @@ int init_decompressors(grk_header_info* h, grk_image* image)
 }
 
 std::vector<std::unique_ptr<DecoderSlot>>* g_dec_pool = new std::vector<std::unique_ptr<DecoderSlot>>();
+DecoderSlot* g_single_slot = nullptr; // grk_plugin_decompress (one frame per call)
 
 // The host's callback runs library code that throws for streams it will not hand to a plugin
 // (PluginDecodeUnsupportedException, plugin/plugin_bridge.cpp:55-72: several segments in a block, or
@@ -1233,7 +1254,7 @@ int decode_one_own_t2(grk_decompress_parameters* params, const std::string& in, 
 	if(grkb_set_device(device))
 		return finish(-1);
 	grk_image* image = slot->himage.get(W, H, ci.numcomps, prec, sgnd, ceildivpow2(ci.x0, reduce),
-										ceildivpow2(ci.y0, reduce));
+										ceildivpow2(ci.y0, reduce), true);
 	if(!image)
 		return finish(-1);
 	if(slot->dz && slot->dz_device != device)
@@ -1581,6 +1602,10 @@ PLUGIN_EXPORT int32_t exit_func()
 	join_batch();
 	g_ctx_pool->clear();
 	g_dec_pool->clear();
+	delete g_single_slot;
+	g_single_slot = nullptr;
+	delete g_single_ctx;
+	g_single_ctx = nullptr;
 	return 0;
 }
 PLUGIN_EXPORT grk::minpf_exit_func minpf_post_load_plugin(const char*,
@@ -1629,7 +1654,13 @@ PLUGIN_EXPORT int32_t plugin_encode(grk_cparameters* params, grk::PLUGIN_ENCODE_
 	EncodeJob job;
 	job.in = params->infile;
 	job.out = params->outfile;
-	return encode_one(params, job, next_device(), cb);
+	// the context (device encoder, page-locked buffers, host image) is kept from call to call;
+	// concurrent callers take turns
+	static std::mutex mu;
+	std::lock_guard<std::mutex> lk(mu);
+	if(!g_single_ctx)
+		g_single_ctx = new EncodeCtx();
+	return encode_one(params, job, next_device(), cb, g_single_ctx);
 }
 
 PLUGIN_EXPORT int32_t plugin_batch_encode(const char* input_dir, const char* output_dir,
@@ -1709,7 +1740,13 @@ PLUGIN_EXPORT int32_t plugin_decompress(grk_decompress_parameters* params,
 {
 	if(!params || !cb)
 		return -1;
-	return decode_one(params, params->infile, params->outfile, next_device(), cb);
+	// one slot kept for this door too: the decoders, the page-locked file buffer and the host image
+	// (whose planes are page-locked once) survive from call to call; concurrent callers take turns
+	static std::mutex mu;
+	std::lock_guard<std::mutex> lk(mu);
+	if(!g_single_slot)
+		g_single_slot = new DecoderSlot();
+	return decode_one(params, params->infile, params->outfile, next_device(), cb, g_single_slot);
 }
 
 namespace

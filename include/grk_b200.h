@@ -379,8 +379,10 @@ int grkb_encoder_time_device(grkb_encoder* e, uint32_t iters, uint32_t warmup, f
  * driver). */
 void* grkb_host_alloc(size_t bytes);
 void grkb_host_free(void* p);
-/* Page-locks memory the caller already owns (a grk_image's planes), so that results are written
- * into it by DMA instead of through the driver's staging buffer. */
+/* Page-locks memory the caller already owns, so that results are written into it by DMA instead of
+ * through the driver's staging buffer.  Only for page-aligned buffers that share no page with other
+ * memory used in copies: the driver refuses a copy that straddles registered and unregistered
+ * pages.  Failure is harmless (returns -1, the memory stays pageable). */
 int grkb_host_register(void* p, size_t bytes);
 int grkb_host_unregister(void* p);
 
@@ -392,6 +394,10 @@ int grkb_host_unregister(void* p);
  * Used by bench.py for the DWT roofline figure. */
 int grkb_bench_dwt(uint32_t w, uint32_t h, uint32_t numres, int reversible, int forward,
 				   uint32_t ncomp, int mct, uint32_t iters, uint32_t warmup, float* ms_per_iter);
+
+/* Host <-> device link bandwidth with page-locked memory (what bounds every end-to-end figure,
+ * SURVEY 8d): each direction alone and both at once, GB/s = 1e9 bytes/s. */
+int grkb_bench_link(size_t bytes, uint32_t iters, double* h2d_gbs, double* d2h_gbs, double duplex_gbs[2]);
 
 /* E. codestream level: T2 on our side ------------------------------------ */
 

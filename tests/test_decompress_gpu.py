@@ -141,10 +141,10 @@ def test_configs2_ht_4k_codestream(dec, frame16):
         assert np.array_equal(got[c], want[c])
 
 
-def test_configs3_8k_tiled_ht_codestream(dec):
+def test_configs3_8k_tiled_ht_codestream(dec, frame8k):
     """BASELINE configs[3]: 8192x8192 16-bit RGB HTJ2K in 64 tiles of 1024x1024, all tiles through
     one decompressor (three tile decoders in flight, one geometry), == stock decoder == image"""
-    img = H.synth_image(8192, 8192, 3, 16, seed=8192)
+    img = frame8k
     cs = _encode(img, 16, 0, ht=True, numres=6, cblk=(64, 64), tile=(1024, 1024))
     got = dec.decode(cs)
     assert dec.rejected == 0 and dec.stats()["tiles"] == 64

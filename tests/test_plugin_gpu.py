@@ -259,10 +259,10 @@ def test_configs2_ht_4k_through_the_plugin_doors(host, tmp_path, frame16):
         assert np.array_equal(got[k], want[k]) and np.array_equal(got[k], img[k])
 
 
-def test_configs3_8k_tiled_through_the_plugin_door(host, tmp_path):
+def test_configs3_8k_tiled_through_the_plugin_door(host, tmp_path, frame8k):
     """BASELINE configs[3]: 8192x8192 16-bit HTJ2K in 1024x1024 tiles -- 64 tiles through one
     grk_plugin_decompress call (impossible across grk_plugin_tile, which holds one tile)"""
-    img = H.synth_image(8192, 8192, 3, 16, seed=8192)
+    img = frame8k
     cs = _encode(img, 16, 0, ht=True, numres=6, cblk=(64, 64), tile=(1024, 1024))
     path = str(tmp_path / "in.j2k")
     cs.tofile(path)
