@@ -27,10 +27,12 @@
 
 namespace
 {
-constexpr int CW = 4; // consumer warps per CTA
 constexpr int STAGES = 4; // row pairs in flight per consumer warp
 
-template<int V>
+// CW: consumer warps per CTA.  A CTA takes CW adjacent strips, so CW is chosen per level to leave
+// as few consumer warps without columns as possible (2048 columns are 8.5 strips of 240: three CTAs
+// of three warps are 95 % busy, three of four 71 %).
+template<int V, int CW>
 struct StripGeom
 {
 	static constexpr int H = V / 2; // coefficient pairs per lane
@@ -166,12 +168,12 @@ static __device__ __forceinline__ void finish_store(const DwtLevelArgs& a, int c
 	}
 }
 
-template<class K, int V, int NC, int FIN>
+template<class K, int V, int NC, int FIN, int CW>
 __global__ void __launch_bounds__((CW + 1) * GRKB_WARP)
 	idwt_strip_kernel(const __grid_constant__ DwtLevelArgs a)
 {
 	typedef typename K::T T;
-	typedef StripGeom<V> G;
+	typedef StripGeom<V, CW> G;
 	constexpr int H = G::H, NS = K::NS, LEN = G::LEN;
 	constexpr int ROW = 2 * LEN; // one staged row: low part then high part
 	constexpr int STAGE = NC * 2 * ROW; // one stage: a row pair of NC components
@@ -354,13 +356,13 @@ __global__ void __launch_bounds__((CW + 1) * GRKB_WARP)
 	}
 }
 
-template<class K, int V, int NC, int FIN>
-static int launch_strip(DwtLevelArgs a, int nplanes, cudaStream_t stream)
+template<class K, int V, int NC, int FIN, int CW>
+static int launch_strip_cw(DwtLevelArgs a, int nplanes, cudaStream_t stream)
 {
-	typedef StripGeom<V> G;
+	typedef StripGeom<V, CW> G;
 	constexpr size_t smem =
 		(size_t)STAGES * NC * 2 * 2 * G::LEN * 4 + (size_t)STAGES * 2 * sizeof(uint64_t);
-	GRKB_ENSURE_SMEM((idwt_strip_kernel<K, V, NC, FIN>), smem);
+	GRKB_ENSURE_SMEM((idwt_strip_kernel<K, V, NC, FIN, CW>), smem);
 	const uint32_t strip = 30 * V;
 	a.nstrips = (a.rw + strip - 1) / strip;
 	// Chunk height: all CTAs are resident at once (<= 4 per SM), so the grid is sized to fill
@@ -396,9 +398,32 @@ static int launch_strip(DwtLevelArgs a, int nplanes, cudaStream_t stream)
 	a.chunk_rows = ch;
 	a.nchunks = (total_rows + ch - 1) / ch;
 	dim3 grid(ngroups * a.nchunks, (NC == 1) ? nplanes : 1, 1);
-	idwt_strip_kernel<K, V, NC, FIN><<<grid, (CW + 1) * GRKB_WARP, smem, stream>>>(a);
+	idwt_strip_kernel<K, V, NC, FIN, CW><<<grid, (CW + 1) * GRKB_WARP, smem, stream>>>(a);
 	GRKB_CUDA_CHECK(cudaGetLastError());
 	return 0;
+}
+
+// picks the CTA width that wastes the fewest consumer warps on this level's strips
+template<class K, int V, int NC, int FIN>
+static int launch_strip(DwtLevelArgs a, int nplanes, cudaStream_t stream)
+{
+	const uint32_t nstrips = (a.rw + 30 * V - 1) / (30 * V);
+	static int forced = -1;
+	if(forced < 0)
+	{
+		const char* e = getenv("GRKB_IDWT_CW");
+		forced = e ? atoi(e) : 0;
+	}
+	// measured on B200 (4096x2160x3, 9/7): the 2048-wide level 18.5 -> 16.4 us with three warps;
+	// the three-component kernel is fastest with four whatever the strip count (five: 45 -> 56 us)
+	uint32_t best = 4;
+	if(NC == 1 && ((nstrips + 2) / 3) * 3 < ((nstrips + 3) / 4) * 4)
+		best = 3;
+	if(forced == 3 || forced == 4)
+		best = (uint32_t)forced;
+	if(best == 3)
+		return launch_strip_cw<K, V, NC, FIN, 3>(a, nplanes, stream);
+	return launch_strip_cw<K, V, NC, FIN, 4>(a, nplanes, stream);
 }
 } // namespace
 
