@@ -102,6 +102,7 @@ lib.grkb_host_register.argtypes = [_vp, C.c_size_t]
 lib.grkb_host_unregister.argtypes = [_vp]
 lib.grkb_bench_link.argtypes = [C.c_size_t, _u32, C.POINTER(C.c_double), C.POINTER(C.c_double),
                                 C.POINTER(C.c_double)]
+lib.grkb_mct_custom_host.argtypes = [_vp, _u32, _u64, _vp, _int]
 # section D: the allocation-free door (device pointers in and out, built-in scratch)
 lib.grkb_idwt_device_noalloc.argtypes = [_vp, _u32, _vp, _u32, _u32, _u32, _u32, _u32, _u32, _int, _vp]
 NOALLOC_SCRATCH_BYTES = 8 << 20

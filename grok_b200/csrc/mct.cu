@@ -9,6 +9,8 @@
 // Pure streaming kernels: 128-bit loads and stores, grid-stride, one read + one write per
 // sample (HBM-bound; 8 B/sample/component algorithmic).
 #include "dwt.cuh"
+#include "../../include/grk_b200.h"
+#include <algorithm>
 
 namespace
 {
@@ -178,4 +180,129 @@ int grkb_launch_dc(const MctArgs& p, int mode, cudaStream_t stream)
 	}
 	GRKB_CUDA_CHECK(cudaGetLastError());
 	return 0;
+}
+
+
+// ---- array-based ("custom matrix") multi-component transform, Part 2 (row M7) ------------------
+//   mct::decompress_custom  src/lib/jp2/point_transform/mct.cpp:660-686: planes are read as float,
+//     out[j] = sum_k M[j][k] * in[k], products and sums rounded separately, accumulated in k order
+//     from 0 (the DC shift follows per component, TileProcessor.cpp:490-504 with mct == 2)
+//   mct::compress_custom    mct.cpp:622-658: integer planes, the matrix in 13-bit fixed point
+//     ((int32_t)(m * 8192.f)), out[j] = sum_k fix_mul(M[j][k], in[k]) with fix_mul rounding
+//     (util/grk_intmath.h:66-79) -- except that the reference resets its matrix pointer to the first
+//     row for every output component (:642), so every component comes out as row 0 applied to the
+//     pixel.  Kept as the reference computes it (parity); the defect is listed in DESIGN.md.
+namespace
+{
+struct CustomMctArgs
+{
+	void* c[GRKB_MAX_COMPS];
+	uint64_t n;
+	uint32_t nc;
+	float m[GRKB_MAX_COMPS * GRKB_MAX_COMPS];
+	int32_t mi[GRKB_MAX_COMPS * GRKB_MAX_COMPS];
+};
+
+template<int FORWARD>
+__global__ void __launch_bounds__(256) mct_custom_kernel(const __grid_constant__ CustomMctArgs p)
+{
+	for(uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < p.n; i += (uint64_t)gridDim.x * blockDim.x)
+	{
+		int32_t in[GRKB_MAX_COMPS], out[GRKB_MAX_COMPS];
+#pragma unroll
+		for(uint32_t j = 0; j < GRKB_MAX_COMPS; ++j)
+			in[j] = j < p.nc ? ((const int32_t*)p.c[j])[i] : 0;
+#pragma unroll
+		for(uint32_t j = 0; j < GRKB_MAX_COMPS; ++j)
+		{
+			if(j >= p.nc)
+				break;
+			if(FORWARD)
+			{
+				int32_t acc = 0;
+				for(uint32_t k = 0; k < p.nc; ++k)
+					acc += (int32_t)(((int64_t)p.mi[k] * (int64_t)in[k] + 4096) >> 13); // row 0 for every j: see below
+				out[j] = acc;
+			}
+			else
+			{
+				float acc = 0.0f;
+				for(uint32_t k = 0; k < p.nc; ++k)
+					acc = __fadd_rn(acc, __fmul_rn(p.m[j * p.nc + k], __int_as_float(in[k])));
+				out[j] = __float_as_int(acc);
+			}
+		}
+#pragma unroll
+		for(uint32_t j = 0; j < GRKB_MAX_COMPS; ++j)
+			if(j < p.nc)
+				((int32_t*)p.c[j])[i] = out[j];
+	}
+}
+} // namespace
+
+int grkb_launch_mct_custom(void* const* planes, uint32_t nc, uint64_t n, const float* matrix, int forward,
+						   cudaStream_t s)
+{
+	if(nc == 0 || nc > GRKB_MAX_COMPS || !matrix)
+	{
+		grkb_set_error("custom MCT: 1..%d components and a matrix are needed", GRKB_MAX_COMPS);
+		return -1;
+	}
+	CustomMctArgs a{};
+	a.n = n;
+	a.nc = nc;
+	for(uint32_t c = 0; c < nc; ++c)
+		a.c[c] = planes[c];
+	for(uint32_t i = 0; i < nc * nc; ++i)
+	{
+		a.m[i] = matrix[i];
+		a.mi[i] = (int32_t)(matrix[i] * (float)(1 << 13));
+	}
+	const unsigned grid = (unsigned)std::min<uint64_t>((n + 255) / 256, 148u * 8u);
+	if(forward)
+		mct_custom_kernel<1><<<grid ? grid : 1, 256, 0, s>>>(a);
+	else
+		mct_custom_kernel<0><<<grid ? grid : 1, 256, 0, s>>>(a);
+	GRKB_CUDA_CHECK(cudaGetLastError());
+	return 0;
+}
+
+extern "C" int grkb_mct_custom_host(void* const* planes, uint32_t numcomps, uint64_t n, const float* matrix,
+									int forward)
+{
+	if(n == 0)
+		return 0;
+	if(!planes || numcomps == 0 || numcomps > GRKB_MAX_COMPS || !matrix)
+	{
+		grkb_set_error("grkb_mct_custom_host: bad arguments");
+		return -1;
+	}
+	void* d[GRKB_MAX_COMPS] = {};
+	int rc = -1;
+	do
+	{
+		bool ok = true;
+		for(uint32_t c = 0; c < numcomps && ok; ++c)
+			ok = cudaMalloc(&d[c], n * 4) == cudaSuccess &&
+				 cudaMemcpy(d[c], planes[c], n * 4, cudaMemcpyHostToDevice) == cudaSuccess;
+		if(!ok)
+		{
+			grkb_set_error("grkb_mct_custom_host: no CUDA device or allocation failed (there is no CPU fallback)");
+			cudaGetLastError();
+			break;
+		}
+		if(grkb_launch_mct_custom(d, numcomps, n, matrix, forward, 0))
+			break;
+		for(uint32_t c = 0; c < numcomps && ok; ++c)
+			ok = cudaMemcpy(planes[c], d[c], n * 4, cudaMemcpyDeviceToHost) == cudaSuccess;
+		if(!ok)
+		{
+			grkb_set_error("grkb_mct_custom_host: copy back failed");
+			break;
+		}
+		rc = 0;
+	} while(0);
+	for(uint32_t c = 0; c < numcomps; ++c)
+		cudaFree(d[c]);
+	return rc;
 }

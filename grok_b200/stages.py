@@ -67,3 +67,12 @@ def mct_fdwt(planes, x0, y0, numres, reversible, mct_on, shift):
     check(lib.grkb_mct_fdwt_host(ptrs, len(a), w, x0, y0, x0 + w, y0 + h, numres, int(reversible),
                                  int(mct_on), _p(s)), "grkb_mct_fdwt_host")
     return a if reversible else [p.view(np.float32) for p in a]
+
+
+def mct_custom(planes, matrix, forward):
+    """array-based MCT (row M7): planes float32 (inverse) or int32 (forward), matrix (nc, nc) float32"""
+    a = [np.ascontiguousarray(p).copy() for p in planes]
+    m = np.ascontiguousarray(matrix, dtype=np.float32)
+    ptrs = (C.c_void_p * len(a))(*[p.ctypes.data for p in a])
+    check(lib.grkb_mct_custom_host(ptrs, len(a), a[0].size, _p(m), int(forward)), "grkb_mct_custom_host")
+    return a

@@ -74,6 +74,18 @@ int grkb_dwt_host(void* data, uint32_t stride, uint32_t x0, uint32_t y0, uint32_
 int grkb_mct_host(void* c0, void* c1, void* c2, uint64_t n, int mode, const int32_t* shift,
 				  const int32_t* lo, const int32_t* hi);
 
+/* Array-based ("custom matrix") multi-component transform of Part 2, in place on `numcomps` planes
+ * of n samples (row M7).  matrix: numcomps x numcomps, row-major (output component j = row j).
+ * forward 0: mct::decompress_custom (point_transform/mct.cpp:660-686): planes hold IEEE single
+ *            precision samples, out[j] = sum_k M[j][k] * in[k] with separately rounded products and
+ *            sums in k order; the per-component DC shift follows as a separate stage
+ *            (grkb_dc_shift_host), as in TileProcessor::dcLevelShiftDecompress (:490-504)
+ * forward 1: mct::compress_custom (:622-658): int32 planes, the matrix truncated to 13-bit fixed
+ *            point, products rounded by fix_mul (util/grk_intmath.h:66-79); like the reference,
+ *            every output component uses the matrix's FIRST row (its pointer is reset per
+ *            component, :642 -- a reference defect reproduced for parity) */
+int grkb_mct_custom_host(void* const* planes, uint32_t numcomps, uint64_t n, const float* matrix, int forward);
+
 /* DC level shift of one plane, in place.
  * mode 0: x+shift, clamp            (mct::decompress_dc_shift_rev,   mct.cpp:515-539)
  * mode 1: rne(float x)+shift, clamp (mct::decompress_dc_shift_irrev, mct.cpp:450-475)

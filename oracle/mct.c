@@ -101,3 +101,51 @@ void orc_dc_shift_inv_irrev(int32_t* c, uint64_t n, int32_t shift, int32_t lo, i
 	for(uint64_t i = 0; i < n; ++i)
 		c[i] = clampi((int32_t)lrintf(f[i]) + shift, lo, hi);
 }
+
+
+/* ---- array-based multi-component transform (Part 2 "custom MCT", row M7) ---------------------- */
+
+/* mct::decompress_custom (point_transform/mct.cpp:660-686): planes read as float, out[j] =
+ * sum_k M[j][k] * in[k], accumulated from 0 in k order (no contraction: -ffp-contract=off) */
+void orc_mct_custom_inv(float* const* planes, uint32_t nc, uint64_t n, const float* matrix)
+{
+	float in[16], out[16];
+	for(uint64_t i = 0; i < n; ++i)
+	{
+		for(uint32_t j = 0; j < nc; ++j)
+			in[j] = planes[j][i];
+		for(uint32_t j = 0; j < nc; ++j)
+		{
+			out[j] = 0;
+			for(uint32_t k = 0; k < nc; ++k)
+			{
+				const float p = matrix[j * nc + k] * in[k];
+				out[j] = out[j] + p;
+			}
+		}
+		for(uint32_t j = 0; j < nc; ++j)
+			planes[j][i] = out[j];
+	}
+}
+
+/* mct::compress_custom (mct.cpp:622-658) with fix_mul (util/grk_intmath.h:66-79).  As the reference
+ * computes it: the matrix pointer is reset to the FIRST row for every output component (:642), so
+ * every output component is row 0 applied to the pixel (a reference defect, kept for parity). */
+void orc_mct_custom_fwd(int32_t* const* planes, uint32_t nc, uint64_t n, const float* matrix)
+{
+	int32_t m[256], in[16];
+	for(uint32_t i = 0; i < nc * nc; ++i)
+		m[i] = (int32_t)(matrix[i] * (float)(1 << 13));
+	for(uint64_t i = 0; i < n; ++i)
+	{
+		for(uint32_t j = 0; j < nc; ++j)
+			in[j] = planes[j][i];
+		for(uint32_t j = 0; j < nc; ++j)
+		{
+			int32_t acc = 0;
+			for(uint32_t k = 0; k < nc; ++k)
+				acc += (int32_t)(((int64_t)m[k] * (int64_t)in[k] + 4096) >> 13);
+			planes[j][i] = acc;
+		}
+	}
+}

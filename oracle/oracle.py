@@ -516,3 +516,26 @@ def ref_set_encode_options(opts=""):
 def ref_set_decode_options(reduce=0, layers=0):
     """cp_reduce / cp_layer of the next ref_codec_decode calls"""
     ref().ref_set_decode_options(C.c_uint32(reduce), C.c_uint32(layers))
+
+
+# ---------------------------------------------------------------- array-based MCT (row M7)
+
+def _mct_custom(is_ref, planes, matrix, forward):
+    a = [np.ascontiguousarray(p).copy() for p in planes]
+    m = np.ascontiguousarray(matrix, dtype=np.float32).copy()
+    ptrs = (C.c_void_p * len(a))(*[p.ctypes.data for p in a])
+    if is_ref:
+        rc = ref().ref_mct_custom(ptrs, C.c_uint32(len(a)), C.c_uint64(a[0].size), _p(m), C.c_int(int(forward)))
+        assert rc == 0
+    else:
+        fn = oracle().orc_mct_custom_fwd if forward else oracle().orc_mct_custom_inv
+        fn(ptrs, C.c_uint32(len(a)), C.c_uint64(a[0].size), _p(m))
+    return a
+
+
+def orc_mct_custom(planes, matrix, forward):
+    return _mct_custom(False, planes, matrix, forward)
+
+
+def ref_mct_custom(planes, matrix, forward):
+    return _mct_custom(True, planes, matrix, forward)

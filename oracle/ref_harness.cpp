@@ -1173,3 +1173,16 @@ extern "C" int ref_dequant(int kind, int32_t* src, int32_t* dst, uint32_t n, uin
 	}
 	return 0;
 }
+
+
+/* array-based MCT: mct::compress_custom / decompress_custom (point_transform/mct.cpp:622-686) on the
+ * caller's planes */
+extern "C" int ref_mct_custom(void** planes, uint32_t nc, uint64_t n, float* matrix, int forward)
+{
+	std::vector<uint8_t*> p(nc);
+	for(uint32_t c = 0; c < nc; ++c)
+		p[c] = (uint8_t*)planes[c];
+	const bool ok = forward ? mct::compress_custom((uint8_t*)matrix, n, p.data(), nc, 0)
+							: mct::decompress_custom((uint8_t*)matrix, n, p.data(), nc, 0);
+	return ok ? 0 : -1;
+}

@@ -102,3 +102,17 @@ def test_full_size_fused_idwt_mct_vs_oracle(gpu, orc, reversible):
                            [0] * 3, sh)
     got = gpu.stages.idwt_mct(pl, 0, 0, nr, reversible, 1, sh, lo, hi)
     assert all(np.array_equal(a, b) for a, b in zip(want, got))
+
+
+@pytest.mark.parametrize("nc", [1, 3, 4])
+def test_custom_mct_matches_oracle(gpu, orc, nc):
+    """row M7: the array-based MCT of Part 2, both directions, bit-exact"""
+    rng = np.random.default_rng(170 + nc)
+    m = (rng.standard_normal((nc, nc)) * 0.7).astype(np.float32)
+    for n in (1, 5, 4099):
+        ints = [rng.integers(-40000, 40000, size=n).astype(np.int32) for _ in range(nc)]
+        for a, b in zip(orc.orc_mct_custom(ints, m, 1), gpu.stages.mct_custom(ints, m, 1)):
+            assert np.array_equal(a, b)
+        flts = [(rng.standard_normal(n) * 3000).astype(np.float32) for _ in range(nc)]
+        for a, b in zip(orc.orc_mct_custom(flts, m, 0), gpu.stages.mct_custom(flts, m, 0)):
+            assert same_bits(a, b)

@@ -295,3 +295,18 @@ def test_samples_unpack_vs_reference_convert(orc, numcomps, bytes_per_sample):
     got = O.orc_unpack_samples(packed, W, interleaved=True)
     for a, b in zip(want, got):
         assert np.array_equal(a, b)
+
+
+# ---------------------------------------------------------------- array-based MCT (row M7)
+
+@pytest.mark.parametrize("nc", [1, 2, 3, 4])
+def test_custom_mct(orc, nc):
+    """oracle/mct.c == mct::compress_custom / decompress_custom (point_transform/mct.cpp:622-686)"""
+    rng = np.random.default_rng(70 + nc)
+    m = (rng.standard_normal((nc, nc)) * 0.7).astype(np.float32)
+    ints = [rng.integers(-40000, 40000, size=777).astype(np.int32) for _ in range(nc)]
+    for a, b in zip(O.ref_mct_custom(ints, m, 1), O.orc_mct_custom(ints, m, 1)):
+        assert np.array_equal(a, b)
+    flts = [(rng.standard_normal(777) * 3000).astype(np.float32) for _ in range(nc)]
+    for a, b in zip(O.ref_mct_custom(flts, m, 0), O.orc_mct_custom(flts, m, 0)):
+        assert same_bits(a, b)
