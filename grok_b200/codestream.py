@@ -38,6 +38,7 @@ lib.grkb_decompressor_create.argtypes = [C.c_int, _u32, C.POINTER(_vp)]
 lib.grkb_decompressor_destroy.argtypes = [_vp]
 lib.grkb_decompressor_destroy.restype = None
 lib.grkb_decompress_submit.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _vp, _u32]
+lib.grkb_decompress_submit_window.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _u32]
 lib.grkb_decompress_submit_packed.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _vp, _u32, C.c_size_t]
 lib.grkb_decompress_wait.argtypes = [_vp, C.POINTER(_u32)]
 lib.grkb_decompress.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _vp, _u32, C.POINTER(_u32)]
@@ -127,6 +128,26 @@ class Decompressor:
         self._keep = (data, out, ptrs)
         check(lib.grkb_decompress_submit(self.h, data.ctypes.data, data.size, reduce, max_layers, ptrs,
                                          out[0].strides[0] // 4), "grkb_decompress_submit")
+
+    def decode_window(self, data, window, reduce=0, max_layers=0):
+        """windowed decode: window = (x0, y0, x1, y1) relative to the image origin; returns int32 planes
+        of the window at the (reduced) resolution"""
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        cs = Codestream(data)
+        i = cs.info
+        nc = i.numcomps
+        x0, y0 = min(i.x0 + window[0], i.x1), min(i.y0 + window[1], i.y1)
+        x1, y1 = min(i.x0 + window[2], i.x1), min(i.y0 + window[3], i.y1)
+        cs.close()
+        w = _ceildivpow2(x1, reduce) - _ceildivpow2(x0, reduce)
+        h = _ceildivpow2(y1, reduce) - _ceildivpow2(y0, reduce)
+        out = [np.zeros((h, w), dtype=np.int32) for _ in range(nc)]
+        ptrs = (_vp * nc)(*[o.ctypes.data for o in out])
+        self._keep = (data, out, ptrs)
+        check(lib.grkb_decompress_submit_window(self.h, data.ctypes.data, data.size, reduce, max_layers,
+                                                window[0], window[1], window[2], window[3], ptrs, w),
+              "grkb_decompress_submit_window")
+        return self.wait()
 
     def submit_packed(self, data, out, numcomps, interleaved=False, reduce=0, max_layers=0):
         H = out.shape[0] if interleaved else out.shape[1]

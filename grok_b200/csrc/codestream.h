@@ -94,6 +94,8 @@ struct TileTables
 
 // T2 of one tile: walks its packets in progression order and decodes the packet headers into the
 // decoder's descriptor tables.  reduce: highest resolutions to drop (cp_reduce); max_layers: 0 = all.
+// window: x0, y0, x1, y1 in the coordinates of the REDUCED tile (canvas coordinates / 2^reduce), or
+// null.  With a window only the code blocks its samples depend on are put in the tables.
 bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t max_layers, TileTables& out,
-				std::string& err);
+				std::string& err, const uint32_t* window = nullptr);
 } // namespace grkb_cs

@@ -5,6 +5,7 @@
 // CodeStreamDecompress::decompressTiles, codestream/CodeStreamDecompress.cpp:412-640).
 #include "pipeline.h"
 #include "codestream.h"
+#include <algorithm>
 #include <chrono>
 #include <memory>
 #include <mutex>
@@ -204,8 +205,11 @@ int drain(grkb_decompressor* d, Slot& s)
 	return rc;
 }
 
+// win: x0, y0, x1, y1 relative to the image origin on the reference grid (grk_decompress_set_window),
+// or null for the whole image
 int submit_any(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce, uint32_t max_layers,
-			   int32_t* const* planes, uint32_t stride, void* out, uint32_t format, size_t row_bytes)
+			   int32_t* const* planes, uint32_t stride, void* out, uint32_t format, size_t row_bytes,
+			   const uint32_t* win = nullptr)
 {
 	if(!d || !data || (!planes && !out))
 	{
@@ -233,8 +237,42 @@ int submit_any(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t r
 	// the reference sizes the reduced image as ceil(width / 2^reduce) (codestream/markers/
 	// SIZMarker.cpp:54-57), which can be one sample more than the ceil(x1 / 2^r) - ceil(x0 / 2^r) the
 	// tiles cover; that last row / column is not written (the reference leaves zeros there)
-	const uint32_t IW = cdp2(cs.x1 - cs.x0, reduce), IH = cdp2(cs.y1 - cs.y0, reduce);
+	uint32_t IW = cdp2(cs.x1 - cs.x0, reduce), IH = cdp2(cs.y1 - cs.y0, reduce);
 	const uint32_t nc = cs.numcomps;
+	// the window on the reference grid, clipped to the image (CodeStreamDecompress::setDecompressWindow,
+	// codestream/CodeStreamDecompress.cpp:295-398), and in reduced coordinates: the output image is
+	// then [ceil(x0 / 2^r), ceil(x1 / 2^r)) as subsampleAndReduce sizes it (util/GrkImage.cpp:74-115)
+	uint32_t wx0 = cs.x0, wy0 = cs.y0, wx1 = cs.x1, wy1 = cs.y1;
+	uint32_t ox0 = ix0, oy0 = iy0; // origin of the output in reduced coordinates
+	if(win && !(win[0] == 0 && win[1] == 0 && win[2] == 0 && win[3] == 0))
+	{
+		if(out)
+		{
+			grkb_set_error("grkb_decompress: a window is served as int32 planes only");
+			return -1;
+		}
+		wx0 = (uint32_t)std::min<uint64_t>((uint64_t)cs.x0 + win[0], cs.x1);
+		wy0 = (uint32_t)std::min<uint64_t>((uint64_t)cs.y0 + win[1], cs.y1);
+		wx1 = (uint32_t)std::min<uint64_t>((uint64_t)cs.x0 + win[2], cs.x1);
+		wy1 = (uint32_t)std::min<uint64_t>((uint64_t)cs.y0 + win[3], cs.y1);
+		if(wx1 <= wx0 || wy1 <= wy0)
+		{
+			grkb_set_error("grkb_decompress: empty window");
+			return -1;
+		}
+		ox0 = cdp2(wx0, reduce);
+		oy0 = cdp2(wy0, reduce);
+		IW = cdp2(wx1, reduce) - ox0;
+		IH = cdp2(wy1, reduce) - oy0;
+		if(IW == 0 || IH == 0)
+		{
+			grkb_set_error("grkb_decompress: the window holds no sample at this resolution");
+			return -1;
+		}
+	}
+	else
+		win = nullptr;
+	const uint32_t rwx1 = cdp2(wx1, reduce), rwy1 = cdp2(wy1, reduce); // window end, reduced coordinates
 	size_t bps = 0, plane_bytes = 0;
 	bool interleaved = false;
 	if(out)
@@ -263,8 +301,20 @@ int submit_any(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t r
 		next = (next + 1) % (uint32_t)d->slots.size();
 		if(drain(d, s))
 			return -1;
+		uint32_t tw[4] = {ox0, oy0, rwx1, rwy1};
+		if(win)
+		{
+			// tiles the window does not touch are not parsed at all
+			const uint32_t tp = t % cs.ntx, tq = t / cs.ntx;
+			const uint64_t tx0 = std::max<uint64_t>((uint64_t)cs.tx0 + (uint64_t)tp * cs.tw, cs.x0);
+			const uint64_t ty0 = std::max<uint64_t>((uint64_t)cs.ty0 + (uint64_t)tq * cs.th, cs.y0);
+			const uint64_t tx1 = std::min<uint64_t>((uint64_t)cs.tx0 + (uint64_t)(tp + 1) * cs.tw, cs.x1);
+			const uint64_t ty1 = std::min<uint64_t>((uint64_t)cs.ty0 + (uint64_t)(tq + 1) * cs.th, cs.y1);
+			if(tx1 <= wx0 || tx0 >= wx1 || ty1 <= wy0 || ty0 >= wy1)
+				continue;
+		}
 		const auto t1 = std::chrono::steady_clock::now();
-		if(!grkb_cs::parse_tile(cs, t, reduce, max_layers, s.tables, err))
+		if(!grkb_cs::parse_tile(cs, t, reduce, max_layers, s.tables, err, win ? tw : nullptr))
 		{
 			grkb_set_error("grkb_decompress: tile %u: %s", t, err.c_str());
 			return -1;
@@ -292,7 +342,12 @@ int submit_any(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t r
 		}
 		const uint8_t* bytes = s.tables.zero_copy ? data + s.tables.src_off : s.tables.pool.data();
 		const size_t nbytes = s.tables.zero_copy ? s.tables.src_len : s.tables.pool.size();
-		const size_t ox = P.x0 - ix0, oy = P.y0 - iy0;
+		// the part of the tile that lands in the output
+		const uint32_t cx0 = std::max(P.x0, ox0), cy0 = std::max(P.y0, oy0);
+		const uint32_t cx1 = std::min(P.x1, win ? rwx1 : P.x1), cy1 = std::min(P.y1, win ? rwy1 : P.y1);
+		if(cx1 <= cx0 || cy1 <= cy0)
+			continue;
+		const size_t ox = cx0 - ox0, oy = cy0 - oy0;
 		int rc;
 		if(out)
 		{
@@ -306,8 +361,9 @@ int submit_any(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t r
 			int32_t* dst[GRKB_MAX_COMPS] = {};
 			for(uint32_t c = 0; c < nc; ++c)
 				dst[c] = planes[c] + oy * stride + ox;
-			rc = grkb_decoder_submit(dec, s.tables.blocks.data(), (uint32_t)s.tables.blocks.size(),
-									 s.tables.segs.data(), (uint32_t)s.tables.segs.size(), bytes, nbytes, dst, stride);
+			rc = grkb_decoder_submit_region(dec, s.tables.blocks.data(), (uint32_t)s.tables.blocks.size(),
+											s.tables.segs.data(), (uint32_t)s.tables.segs.size(), bytes, nbytes, dst,
+											stride, cx0 - P.x0, cy0 - P.y0, cx1 - cx0, cy1 - cy0);
 		}
 		if(rc)
 			return -1;
@@ -350,6 +406,14 @@ int grkb_decompress_submit(grkb_decompressor* d, const uint8_t* data, size_t len
 						   uint32_t max_layers, int32_t* const* planes, uint32_t stride)
 {
 	return submit_any(d, data, len, reduce, max_layers, planes, stride, nullptr, 0, 0);
+}
+
+int grkb_decompress_submit_window(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,
+								  uint32_t max_layers, uint32_t wx0, uint32_t wy0, uint32_t wx1, uint32_t wy1,
+								  int32_t* const* planes, uint32_t stride)
+{
+	const uint32_t win[4] = {wx0, wy0, wx1, wy1};
+	return submit_any(d, data, len, reduce, max_layers, planes, stride, nullptr, 0, 0, win);
 }
 
 int grkb_decompress_submit_packed(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,

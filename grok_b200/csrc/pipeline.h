@@ -47,4 +47,8 @@ int grkb_decoder_submit_packed_region(grkb_decoder* d, const grkb_cblk* blocks, 
 									  const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
 									  void* out, uint32_t format, size_t row_bytes, size_t plane_bytes);
 
+int grkb_decoder_submit_region(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks, const grkb_seg* segs,
+							   uint32_t nsegs, const uint8_t* bytes, size_t nbytes, int32_t* const* planes,
+							   uint32_t stride, uint32_t rx, uint32_t ry, uint32_t rw, uint32_t rh);
+
 void grkb_set_error(const char* fmt, ...);

@@ -314,7 +314,7 @@ struct BodyReader
 } // namespace
 
 bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t max_layers, TileTables& out,
-				std::string& err)
+				std::string& err, const uint32_t* window)
 {
 	out = TileTables();
 	if(tileno >= cs.tiles.size())
@@ -775,6 +775,28 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 	if(!err.empty() && out.packets == 0)
 		return false;
 	err.clear();
+	// Windowed decode (tile/TileProcessor.cpp:288-317, transform/WaveletReverse.cpp:1374-2230 in the
+	// reference): a block is needed when its band samples reach the window through the synthesis
+	// filters.  At resolution r (nd levels below the decoded one) the window covers
+	// [w0 >> nd, ceil(w1 / 2^nd)); every level above adds four samples of filter reach at its own
+	// scale (less than eight in total at this one); band coordinates are half of that.
+	auto in_window = [&](const grkb_cblk_geom& g) -> bool {
+		if(!window)
+			return true;
+		const uint32_t nd = keep_res - 1 - g.res;
+		const int64_t M = 10;
+		int64_t rx0 = (int64_t)(window[0] >> nd) - M, rx1 = (int64_t)cdp2(window[2], nd) + M;
+		int64_t ry0 = (int64_t)(window[1] >> nd) - M, ry1 = (int64_t)cdp2(window[3], nd) + M;
+		if(g.res > 0)
+		{
+			rx0 = (rx0 - 1) >> 1;
+			ry0 = (ry0 - 1) >> 1;
+			rx1 = (rx1 + 2) >> 1;
+			ry1 = (ry1 + 2) >> 1;
+		}
+		return !((int64_t)g.cx0 + g.w <= rx0 || (int64_t)g.cx0 >= rx1 || (int64_t)g.cy0 + g.h <= ry0 ||
+				 (int64_t)g.cy0 >= ry1);
+	};
 	// ---- tables
 	size_t lo = SIZE_MAX, hi = 0, total = 0;
 	bool single = true;
@@ -782,7 +804,7 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 		for(uint32_t i = 0; i < ng_keep; ++i)
 		{
 			const uint32_t bi = c * ng + i;
-			if(slot[bi] == UINT32_MAX || st[bi].dropped)
+			if(slot[bi] == UINT32_MAX || st[bi].dropped || !in_window(geom[i]))
 				continue;
 			const Chunks& C = bchunks[slot[bi]];
 			if(C.size() > 1)
@@ -821,6 +843,8 @@ bool parse_tile(const Codestream& cs, uint32_t tileno, uint32_t reduce, uint32_t
 			const grkb_cblk_geom& g = geom[i];
 			if(g.w == 0 || g.h == 0)
 				continue; // degenerate blocks exist for T2 only: they hold no samples
+			if(!in_window(g))
+				continue;
 			out.blocks.emplace_back();
 			grkb_cblk& b = out.blocks.back();
 			memset(&b, 0, sizeof(b));

@@ -378,23 +378,41 @@ int grkb_decoder_submit(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nbloc
 						const grkb_seg* segs, uint32_t nsegs, const uint8_t* bytes, size_t nbytes,
 						int32_t* const* planes, uint32_t stride)
 {
+	if(!d)
+	{
+		grkb_set_error("grkb_decoder_submit: null decoder");
+		return -1;
+	}
+	return grkb_decoder_submit_region(d, blocks, nblocks, segs, nsegs, bytes, nbytes, planes, stride, 0, 0, d->W, d->H);
+}
+
+} // extern "C"
+
+// grkb_decoder_submit that copies back only the rectangle (rx, ry, rw, rh) of the tile: planes[c]
+// points at where that rectangle's first sample goes (windowed decode)
+int grkb_decoder_submit_region(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks, const grkb_seg* segs,
+							   uint32_t nsegs, const uint8_t* bytes, size_t nbytes, int32_t* const* planes,
+							   uint32_t stride, uint32_t rx, uint32_t ry, uint32_t rw, uint32_t rh)
+{
 	if(submit_front(d, blocks, nblocks, segs, nsegs, bytes, nbytes))
 		return -1;
 	cudaStream_t s = d->stream;
-	if(planes)
+	if(planes && rw && rh)
 	{
-		if(stride < d->W)
+		if(stride < rw || (uint64_t)rx + rw > d->W || (uint64_t)ry + rh > d->H)
 		{
-			grkb_set_error("grkb_decoder_submit: stride smaller than the tile width");
+			grkb_set_error("grkb_decoder_submit: stride smaller than the rectangle, or rectangle outside the tile");
 			return -1;
 		}
 		for(uint32_t c = 0; c < d->p.numcomps; ++c)
-			GRKB_CUDA_CHECK(cudaMemcpy2DAsync(planes[c], (size_t)stride * 4, d->image[c],
-											  (size_t)d->stride * 4, (size_t)d->W * 4, d->H,
-											  cudaMemcpyDeviceToHost, s));
+			GRKB_CUDA_CHECK(cudaMemcpy2DAsync(planes[c], (size_t)stride * 4,
+											  (const int32_t*)d->image[c] + (size_t)ry * d->stride + rx,
+											  (size_t)d->stride * 4, (size_t)rw * 4, rh, cudaMemcpyDeviceToHost, s));
 	}
 	return 0;
 }
+
+extern "C" {
 
 size_t grkb_samples_size(uint32_t format, uint32_t H, uint32_t numcomps, size_t row_bytes)
 {

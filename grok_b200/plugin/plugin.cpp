@@ -1243,7 +1243,31 @@ int decode_one_own_t2(grk_decompress_parameters* params, const std::string& in, 
 		logf("%s: components of different precision or signedness are left to the host", in.c_str());
 		return finish(-1);
 	}
-	const uint32_t W = ceildivpow2(ci.x1 - ci.x0, reduce), H = ceildivpow2(ci.y1 - ci.y0, reduce);
+	uint32_t W = ceildivpow2(ci.x1 - ci.x0, reduce), H = ceildivpow2(ci.y1 - ci.y0, reduce);
+	// decode window (-d of grk_decompress, relative to the image origin): the host image is the window
+	uint32_t win[4] = {0, 0, 0, 0};
+	uint32_t img_x0 = ceildivpow2(ci.x0, reduce), img_y0 = ceildivpow2(ci.y0, reduce);
+	const bool windowed = params && (params->DA_x1 > params->DA_x0) && (params->DA_y1 > params->DA_y0);
+	if(windowed)
+	{
+		win[0] = params->DA_x0;
+		win[1] = params->DA_y0;
+		win[2] = params->DA_x1;
+		win[3] = params->DA_y1;
+		const uint32_t ax0 = (uint32_t)std::min<uint64_t>((uint64_t)ci.x0 + win[0], ci.x1);
+		const uint32_t ay0 = (uint32_t)std::min<uint64_t>((uint64_t)ci.y0 + win[1], ci.y1);
+		const uint32_t ax1 = (uint32_t)std::min<uint64_t>((uint64_t)ci.x0 + win[2], ci.x1);
+		const uint32_t ay1 = (uint32_t)std::min<uint64_t>((uint64_t)ci.y0 + win[3], ci.y1);
+		img_x0 = ceildivpow2(ax0, reduce);
+		img_y0 = ceildivpow2(ay0, reduce);
+		W = ceildivpow2(ax1, reduce) - img_x0;
+		H = ceildivpow2(ay1, reduce) - img_y0;
+		if(ax1 <= ax0 || ay1 <= ay0 || W == 0 || H == 0)
+		{
+			logf("%s: empty decode window", in.c_str());
+			return finish(-1);
+		}
+	}
 	const uint32_t prec = ci.prec[0];
 	const bool sgnd = ci.sgnd[0] != 0;
 	if(!host_image_new() || !host_unref())
@@ -1253,8 +1277,7 @@ int decode_one_own_t2(grk_decompress_parameters* params, const std::string& in, 
 	}
 	if(grkb_set_device(device))
 		return finish(-1);
-	grk_image* image = slot->himage.get(W, H, ci.numcomps, prec, sgnd, ceildivpow2(ci.x0, reduce),
-										ceildivpow2(ci.y0, reduce), true);
+	grk_image* image = slot->himage.get(W, H, ci.numcomps, prec, sgnd, img_x0, img_y0, true);
 	if(!image)
 		return finish(-1);
 	if(slot->dz && slot->dz_device != device)
@@ -1277,7 +1300,7 @@ int decode_one_own_t2(grk_decompress_parameters* params, const std::string& in, 
 	int rc;
 	// one GPU: int32 planes by DMA straight into the host's (page-locked) image.  Several GPUs behind
 	// one host bridge (deviceId = -1): 16-bit samples across the bus, widened here.
-	const bool bus16 = prec <= 16 && (getenv("GRKB_PLUGIN_BUS16") ? atoi(getenv("GRKB_PLUGIN_BUS16")) != 0
+	const bool bus16 = !windowed && prec <= 16 && (getenv("GRKB_PLUGIN_BUS16") ? atoi(getenv("GRKB_PLUGIN_BUS16")) != 0
 																  : (g_device < 0 && g_ndev > 1));
 	const size_t row16 = (size_t)W * 2;
 	if(bus16 && slot->out.reserve(row16 * H * ci.numcomps + 16))
@@ -1295,7 +1318,10 @@ int decode_one_own_t2(grk_decompress_parameters* params, const std::string& in, 
 		int32_t* planes[GRKB_MAX_COMPS] = {};
 		for(uint32_t c = 0; c < ci.numcomps; ++c)
 			planes[c] = image->comps[c].data;
-		rc = grkb_decompress(slot->dz, slot->file.p, len, reduce, layers, planes, image->comps[0].stride, &rejected);
+		rc = grkb_decompress_submit_window(slot->dz, slot->file.p, len, reduce, layers, win[0], win[1], win[2], win[3],
+										   planes, image->comps[0].stride);
+		if(!rc)
+			rc = grkb_decompress_wait(slot->dz, &rejected);
 	}
 	if(rc || rejected)
 	{

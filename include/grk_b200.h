@@ -496,6 +496,16 @@ void grkb_decompressor_destroy(grkb_decompressor* d);
  * rejected_out: code blocks the block decoders refused (they decode as zeros). */
 int grkb_decompress_submit(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,
 						   uint32_t max_layers, int32_t* const* planes, uint32_t stride);
+/* Windowed decode (grk_decompress_set_window, src/lib/jp2/grok.h:1321-1331 ->
+ * CodeStreamDecompress::setDecompressWindow, codestream/CodeStreamDecompress.cpp:295-398, and the
+ * partial wavelet of transform/WaveletReverse.cpp:1374-2230).  wx0..wy1: the window relative to the
+ * image origin on the reference grid (0, 0, 0, 0: the whole image), clipped to the image.  Only the
+ * tiles it touches are parsed and, inside them, only the code blocks whose samples reach the window
+ * through the synthesis filters are decoded; planes receive the (ceil(x1/2^r) - ceil(x0/2^r)) x ...
+ * samples of the window, identical to the same region of a full decode. */
+int grkb_decompress_submit_window(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,
+								  uint32_t max_layers, uint32_t wx0, uint32_t wy0, uint32_t wx1, uint32_t wy1,
+								  int32_t* const* planes, uint32_t stride);
 /* The same with the samples narrowed on the device (GRKB_SAMPLES_16 / _8, planar or interleaved;
  * opt-in): `out` holds grkb_samples_size(format, H, numcomps, row_bytes) bytes of the
  * whole (reduced) image. */

@@ -539,3 +539,8 @@ def orc_mct_custom(planes, matrix, forward):
 
 def ref_mct_custom(planes, matrix, forward):
     return _mct_custom(True, planes, matrix, forward)
+
+
+def ref_set_decode_window(x0=0, y0=0, x1=0, y1=0):
+    """decode window of the next ref_codec_decode calls, relative to the image origin (0,0,0,0: all)"""
+    ref().ref_set_decode_window(C.c_uint32(x0), C.c_uint32(y0), C.c_uint32(x1), C.c_uint32(y1))

@@ -677,10 +677,20 @@ long ref_codec_encode(int32_t** planes, uint32_t numcomps, uint32_t w, uint32_t 
 /* resolutions to drop (-r of grk_decompress) and quality layers to keep (-l; 0 = all) for the next
  * ref_codec_decode calls; w and h are then those of the reduced image */
 static uint32_t g_dec_reduce = 0, g_dec_layers = 0;
+static uint32_t g_dec_win[4] = {0, 0, 0, 0};
 void ref_set_decode_options(uint32_t reduce, uint32_t layers)
 {
 	g_dec_reduce = reduce;
 	g_dec_layers = layers;
+}
+/* decode window of the next ref_codec_decode calls (-d of grk_decompress: grk_decompress_set_window),
+ * relative to the image origin; 0,0,0,0 = whole image.  w and h are then those of the window. */
+void ref_set_decode_window(uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1)
+{
+	g_dec_win[0] = x0;
+	g_dec_win[1] = y0;
+	g_dec_win[2] = x1;
+	g_dec_win[3] = y1;
 }
 
 int ref_codec_decode(uint8_t* cs, size_t len, uint32_t numthreads, int32_t** planes,
@@ -700,6 +710,7 @@ int ref_codec_decode(uint8_t* cs, size_t len, uint32_t numthreads, int32_t** pla
 	grk_header_info hdr;
 	memset(&hdr, 0, sizeof(hdr));
 	if(codec && grk_decompress_init(codec, &dp.core) && grk_decompress_read_header(codec, &hdr) &&
+	   grk_decompress_set_window(codec, g_dec_win[0], g_dec_win[1], g_dec_win[2], g_dec_win[3]) &&
 	   grk_decompress(codec, nullptr))
 	{
 		auto image = grk_decompress_get_composited_image(codec);

@@ -102,6 +102,63 @@ def test_packed_output_multi_tile(dec, orc, interleaved, dtype):
     assert np.array_equal(out, want)
 
 
+@pytest.mark.parametrize("irr,ht", [(0, 0), (1, 0), (0, 1)])
+@pytest.mark.parametrize("tile", [(0, 0), (128, 96)])
+@pytest.mark.parametrize("win,reduce", [((40, 30, 170, 140), 0), ((0, 0, 64, 64), 0), ((129, 97, 250, 190), 0),
+                                        ((100, 50, 101, 51), 0), ((37, 21, 203, 177), 1), ((60, 60, 200, 150), 2)])
+def test_windowed_decode_matches_stock_decoder(dec, irr, ht, tile, win, reduce):
+    """row N4, the windowed half: only the tiles and code blocks the window depends on are decoded;
+    the samples equal the stock decoder's own windowed decode (grk_decompress_set_window)"""
+    prec = 12 if ht else 8
+    img = H.synth_image(250, 190, 3, prec, seed=31)
+    cs = _encode(img, prec, irr, "" if ht else "rates=30:10:%d" % (2 if irr else 1), tile=tile, numres=5,
+                 cblk=(32, 32), ht=bool(ht))
+    w = ((win[2] + (1 << reduce) - 1) >> reduce) - ((win[0] + (1 << reduce) - 1) >> reduce)
+    h = ((win[3] + (1 << reduce) - 1) >> reduce) - ((win[1] + (1 << reduce) - 1) >> reduce)
+    try:
+        O.ref_set_decode_window(*win)
+        O.ref_set_decode_options(reduce, 0)
+        want = O.ref_codec_decode(cs, 3, w, h)
+    finally:
+        O.ref_set_decode_window()
+        O.ref_set_decode_options(0, 0)
+    got = dec.decode_window(cs, win, reduce=reduce)
+    for k in range(3):
+        assert got[k].shape == want[k].shape and np.array_equal(got[k], want[k])
+
+
+@pytest.mark.parametrize("irr", [0, 1])
+@pytest.mark.parametrize("win,reduce", [((40, 30, 170, 140), 0), ((129, 97, 250, 190), 0), ((37, 21, 203, 177), 1)])
+def test_windowed_decode_with_image_offset_is_the_crop_of_the_full_decode(dec, irr, win, reduce):
+    """With an image origin other than (0, 0) the REFERENCE's windowed decode disagrees with its own
+    full decode (and, for lossless streams, with the image): a reference defect.  Ours is, as the
+    window of a decode must be, the same region of the full decode -- the stock decoder's."""
+    img = H.synth_image(250, 190, 3, 8, seed=31)
+    cs = _encode(img, 8, irr, "off=3:5;rates=30:10:%d" % (2 if irr else 1), tile=(128, 96), numres=5, cblk=(32, 32))
+    full = _ref_decode(cs, 3, reduce)
+    x0, y0 = 3 + win[0], 5 + win[1]
+    x1, y1 = 3 + win[2], 5 + win[3]
+    up = lambda v: (v + (1 << reduce) - 1) >> reduce
+    ox, oy = up(3), up(5)
+    got = dec.decode_window(cs, win, reduce=reduce)
+    for k in range(3):
+        assert np.array_equal(got[k], full[k][up(y0) - oy:up(y1) - oy, up(x0) - ox:up(x1) - ox])
+
+
+def test_windowed_decode_skips_work(dec, frame16):
+    """a 512x512 window of the 4K HT frame: same samples as the full decode's region, a fraction of
+    the blocks"""
+    img = [p >> 4 for p in frame16]
+    cs = _encode(img, 12, 0, ht=True, numres=6, cblk=(64, 64))
+    got = dec.decode_window(cs, (1800, 900, 2312, 1412))
+    for k in range(3):
+        assert np.array_equal(got[k], img[k][900:1412, 1800:2312])
+    c = CS.Codestream(cs)
+    full = c.parse_tile(0)
+    c.close()
+    assert dec.stats()["tiles"] == 1 and len(full["blocks"]) == 6708
+
+
 def test_refused_streams_fail_loudly(dec):
     with pytest.raises(Exception):
         dec.decode(np.frombuffer(b"garbage" * 10, dtype=np.uint8))
