@@ -178,3 +178,87 @@ class Decompressor:
         ms, n = C.c_double(), _u32()
         check(lib.grkb_decompress_stats(self.h, C.byref(ms), C.byref(n)), "grkb_decompress_stats")
         return dict(t2_ms=ms.value, tiles=n.value)
+
+
+# ---------------------------------------------------------------------------------- encode side
+
+class CompressParams(C.Structure):
+    """grkb_compress_params"""
+    _fields_ = [("width", _u32), ("height", _u32), ("numcomps", _u32), ("prec", _u32), ("sgnd", _u32),
+                ("x0", _u32), ("y0", _u32), ("tile_w", _u32), ("tile_h", _u32), ("tile_x0", _u32),
+                ("tile_y0", _u32), ("numres", _u32), ("cblkw_exp", _u32), ("cblkh_exp", _u32),
+                ("cblk_sty", _u32), ("reversible", _u32), ("mct", _u32), ("prog_order", _u32), ("csty", _u32),
+                ("numgbits", _u32), ("prec_w_exp", C.c_uint8 * 33), ("prec_h_exp", C.c_uint8 * 33),
+                ("comment", C.c_char * 64)]
+
+
+lib.grkb_compressor_create.argtypes = [C.c_int, C.POINTER(CompressParams), C.POINTER(_vp)]
+lib.grkb_compressor_destroy.argtypes = [_vp]
+lib.grkb_compressor_destroy.restype = None
+lib.grkb_compress.argtypes = [_vp, _vp, _u32, _vp, C.c_size_t, C.POINTER(C.c_size_t)]
+lib.grkb_compress_stats.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+
+PROGS = {"LRCP": 0, "RLCP": 1, "RPCL": 2, "PCRL": 3, "CPRL": 4}
+
+
+class Compressor:
+    """grkb_compressor: images -> codestreams (one layer, every pass kept) on one device"""
+
+    def __init__(self, width, height, numcomps, prec, reversible=True, ht=False, numres=6, cblk=(64, 64),
+                 tile=(0, 0), origin=(0, 0), tile_origin=None, prog="LRCP", precincts=None, sop=False, eph=False,
+                 cblk_sty=0, mct=None, sgnd=False, comment="", device=0):
+        p = CompressParams()
+        p.width, p.height, p.numcomps, p.prec, p.sgnd = width, height, numcomps, prec, int(sgnd)
+        p.x0, p.y0 = origin
+        p.tile_w, p.tile_h = tile
+        p.tile_x0, p.tile_y0 = tile_origin if tile_origin is not None else (0, 0)
+        p.numres = numres
+        p.cblkw_exp, p.cblkh_exp = cblk[0].bit_length() - 1, cblk[1].bit_length() - 1
+        p.cblk_sty = T.CBLKSTY_HT if ht else cblk_sty
+        p.reversible = int(reversible)
+        p.mct = int(numcomps >= 3 if mct is None else mct)
+        p.prog_order = PROGS[prog]
+        p.csty = (2 if sop else 0) | (4 if eph else 0)
+        for r in range(33):
+            p.prec_w_exp[r] = p.prec_h_exp[r] = 15
+        if precincts:
+            # as grk_compress -c: sizes from the HIGHEST resolution down, the last one halved for
+            # every resolution below (CodeStreamCompress.cpp:542-596)
+            for r in range(numres):
+                k = numres - 1 - r
+                if k < len(precincts):
+                    w, h = precincts[k]
+                else:
+                    w, h = precincts[-1][0] >> (k - len(precincts) + 1), precincts[-1][1] >> (k - len(precincts) + 1)
+                p.prec_w_exp[r] = max(w, 1).bit_length() - 1
+                p.prec_h_exp[r] = max(h, 1).bit_length() - 1
+        p.comment = comment.encode()
+        self.params = p
+        self.h = _vp()
+        check(lib.grkb_compressor_create(device, C.byref(p), C.byref(self.h)), "grkb_compressor_create")
+
+    def close(self):
+        if self.h:
+            lib.grkb_compressor_destroy(self.h)
+            self.h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def encode(self, planes):
+        a = [np.ascontiguousarray(x, dtype=np.int32) for x in planes]
+        ptrs = (_vp * len(a))(*[x.ctypes.data for x in a])
+        cap = a[0].size * len(a) * 4 + (1 << 20)
+        out = np.zeros(cap, dtype=np.uint8)
+        used = C.c_size_t()
+        check(lib.grkb_compress(self.h, ptrs, a[0].strides[0] // 4, out.ctypes.data, cap, C.byref(used)),
+              "grkb_compress")
+        return out[:used.value].copy()
+
+    def stats(self):
+        a, b = C.c_double(), C.c_double()
+        check(lib.grkb_compress_stats(self.h, C.byref(a), C.byref(b)), "grkb_compress_stats")
+        return dict(device_ms=a.value, t2_ms=b.value)

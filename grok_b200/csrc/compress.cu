@@ -1,0 +1,668 @@
+// compress.cu -- the encode side of the codestream-level C-ABI (include/grk_b200.h, section E):
+// image planes in, a complete JPEG 2000 / HTJ2K codestream out, with T2 on our side.
+// The device part of every tile is grkb_encoder_* (DC shift, MCT, forward wavelet, quantiser, block
+// coders, packing); this file adds what the reference host does around it for a single quality
+// layer that keeps every coding pass:
+//   main header         CodeStreamCompress::start / write_siz / write_cap / write_cod / write_qcd /
+//                       write_com   src/lib/jp2/codestream/CodeStreamCompress.cpp:640-1130
+//   packets             T2Compress::compressPacket / compressHeader   t2/T2Compress.cpp:112-330,
+//                       TagTree::compress t2/TagTree.h:160-200, BitIO::putbit / flush t2/BitIO.cpp:36-150
+//   packet order        packet_order.h (t2/PacketIter.cpp)
+//   tile parts          one tile part per tile: SOT, SOD, packets (SOTMarker.cpp:30-58)
+// Without a rate target the reference keeps all passes too (makeSingleLosslessLayer,
+// tile/TileProcessor.cpp:969-977), so for these parameters the codestream is byte-identical to the
+// stock encoder's (tests/test_compress_gpu.py).  Rate-controlled layers (PCRD) are not written here.
+#include "pipeline.h"
+#include "codestream.h"
+#include "geometry.h"
+#include "packet_order.h"
+#include <chrono>
+#include <memory>
+#include <string.h>
+#include <string>
+
+namespace
+{
+// packet-header bit writer: MSB first, seven bits in the byte after 0xFF (BitIO::putbit / writeByte)
+struct BitWriter
+{
+	std::vector<uint8_t>& out;
+	uint32_t buf = 0, ct = 8;
+	explicit BitWriter(std::vector<uint8_t>& o) : out(o) {}
+	inline void byteout()
+	{
+		out.push_back((uint8_t)buf);
+		ct = buf == 0xFF ? 7 : 8;
+		buf = 0;
+	}
+	inline void bit(uint32_t b)
+	{
+		if(ct == 0)
+			byteout();
+		--ct;
+		buf |= (b & 1u) << ct;
+	}
+	inline void bits(uint32_t v, uint32_t n)
+	{
+		for(int i = (int)n - 1; i >= 0; --i)
+			bit((v >> i) & 1u);
+	}
+	inline void comma(uint32_t n)
+	{
+		while(n--)
+			bit(1);
+		bit(0);
+	}
+	inline void numpasses(uint32_t n)
+	{
+		if(n == 1)
+			bits(0, 1);
+		else if(n == 2)
+			bits(2, 2);
+		else if(n <= 5)
+			bits(0xC | (n - 3), 4);
+		else if(n <= 36)
+			bits(0x1E0 | (n - 6), 9);
+		else
+			bits(0xFF80 | (n - 37), 16);
+	}
+	inline void flush()
+	{
+		byteout();
+		if(ct == 7)
+			byteout();
+	}
+};
+
+struct TNode
+{
+	uint32_t value, low;
+	bool known;
+};
+// tag tree over a w x h grid, levels halving (rounding up) to 1 x 1; compress() as TagTree::compress
+struct TagTreeEnc
+{
+	std::vector<TNode> nodes;
+	std::vector<uint32_t> lvl_off, lvl_w;
+	uint32_t w = 0, h = 0;
+	void init(uint32_t W, uint32_t H)
+	{
+		w = W;
+		h = H;
+		lvl_off.clear();
+		lvl_w.clear();
+		uint32_t n = 0, lw = W, lh = H;
+		while(true)
+		{
+			lvl_off.push_back(n);
+			lvl_w.push_back(lw);
+			n += lw * lh;
+			if(lw <= 1 && lh <= 1)
+				break;
+			lw = (lw + 1) >> 1;
+			lh = (lh + 1) >> 1;
+		}
+		nodes.assign(n, TNode{0xFFFFFFFFu, 0, false});
+	}
+	void setvalue(uint32_t leaf, uint32_t value)
+	{
+		uint32_t x = leaf % w, y = leaf / w;
+		for(size_t l = 0; l < lvl_off.size(); ++l)
+		{
+			TNode& nd = nodes[lvl_off[l] + y * lvl_w[l] + x];
+			if(nd.value <= value)
+				break;
+			nd.value = value;
+			x >>= 1;
+			y >>= 1;
+		}
+	}
+	void compress(BitWriter& bw, uint32_t leaf, uint32_t threshold)
+	{
+		uint32_t path[34];
+		int depth = 0;
+		uint32_t x = leaf % w, y = leaf / w;
+		for(size_t l = 0; l < lvl_off.size(); ++l)
+		{
+			path[depth++] = lvl_off[l] + y * lvl_w[l] + x;
+			x >>= 1;
+			y >>= 1;
+		}
+		uint32_t low = 0;
+		for(int i = depth - 1; i >= 0; --i)
+		{
+			TNode& nd = nodes[path[i]];
+			if(nd.low < low)
+				nd.low = low;
+			else
+				low = nd.low;
+			while(low < threshold)
+			{
+				if(low >= nd.value)
+				{
+					if(!nd.known)
+					{
+						bw.bit(1);
+						nd.known = true;
+					}
+					break;
+				}
+				bw.bit(0);
+				++low;
+			}
+			nd.low = low;
+		}
+	}
+};
+
+uint32_t floorlog2u(uint32_t v)
+{
+	uint32_t l = 0;
+	while(v > 1)
+	{
+		v >>= 1;
+		++l;
+	}
+	return l;
+}
+
+void put16(std::vector<uint8_t>& o, uint32_t v)
+{
+	o.push_back((uint8_t)(v >> 8));
+	o.push_back((uint8_t)v);
+}
+void put32(std::vector<uint8_t>& o, uint32_t v)
+{
+	put16(o, v >> 16);
+	put16(o, v & 0xFFFF);
+}
+
+// everything about one tile geometry that does not change from image to image
+struct TileKit
+{
+	grkb_tile_params tp{};
+	grkb_encoder* enc = nullptr;
+	std::vector<grkb_cblk_geom> geom; // all blocks of one component, degenerate ones included
+	grkb_layout_index idx;
+	std::vector<int32_t> table_of; // geom index -> index in the encoder's block table of component 0, or -1
+	std::vector<grkb_enc_cblk> blocks; // component-major, non-degenerate blocks only
+	std::vector<uint32_t> band_numbps; // per (component, band in codestream order)
+	uint32_t per_comp = 0; // blocks per component in `blocks`
+	// results of the last encode (page-locked)
+	grkb_coded* coded = nullptr;
+	grkb_pass* passes = nullptr;
+	uint8_t* bytes = nullptr;
+	size_t bytes_cap = 0;
+	~TileKit()
+	{
+		if(enc)
+			grkb_encoder_destroy(enc);
+		grkb_host_free(coded);
+		grkb_host_free(passes);
+		grkb_host_free(bytes);
+	}
+};
+} // namespace
+
+struct grkb_compressor
+{
+	int device = 0;
+	grkb_compress_params p{};
+	std::string comment;
+	std::vector<uint32_t> expn[GRKB_MAX_COMPS], mant[GRKB_MAX_COMPS];
+	std::vector<std::unique_ptr<TileKit>> kits;
+	std::vector<uint8_t> hdr; // packet headers of the packet being written
+	double t2_ms = 0, device_ms = 0;
+};
+
+namespace
+{
+bool same_geometry(const grkb_tile_params& a, const grkb_tile_params& b)
+{
+	return memcmp(&a, &b, sizeof(a)) == 0;
+}
+
+TileKit* kit_for(grkb_compressor* z, const grkb_tile_params& tp)
+{
+	for(auto& k : z->kits)
+		if(same_geometry(k->tp, tp))
+			return k.get();
+	const grkb_compress_params& p = z->p;
+	auto k = std::make_unique<TileKit>();
+	k->tp = tp;
+	grkb_layout_params lp{};
+	lp.x0 = tp.x0;
+	lp.y0 = tp.y0;
+	lp.x1 = tp.x1;
+	lp.y1 = tp.y1;
+	lp.numres = p.numres;
+	lp.cblkw_exp = p.cblkw_exp;
+	lp.cblkh_exp = p.cblkh_exp;
+	for(uint32_t r = 0; r < 33; ++r)
+	{
+		lp.prec_w_exp[r] = r < p.numres ? p.prec_w_exp[r] : 15;
+		lp.prec_h_exp[r] = r < p.numres ? p.prec_h_exp[r] : 15;
+	}
+	uint32_t ng = 0;
+	if(grkb_layout_walk(&lp, nullptr, 0, &ng, nullptr))
+		return nullptr;
+	k->geom.resize(ng);
+	if(grkb_layout_walk(&lp, k->geom.data(), ng, &ng, &k->idx) && ng)
+		return nullptr;
+	const bool ht = (p.cblk_sty & GRKB_CBLKSTY_HT) != 0;
+	const uint32_t nb = 3 * p.numres - 2;
+	k->table_of.assign(ng, -1);
+	uint32_t n0 = 0;
+	for(uint32_t i = 0; i < ng; ++i)
+		if(k->geom[i].w && k->geom[i].h)
+			k->table_of[i] = (int32_t)n0++;
+	k->per_comp = n0;
+	k->blocks.assign((size_t)n0 * p.numcomps, grkb_enc_cblk{});
+	k->band_numbps.assign((size_t)nb * p.numcomps, 0);
+	for(uint32_t c = 0; c < p.numcomps; ++c)
+	{
+		for(uint32_t b = 0; b < nb; ++b)
+		{
+			float step;
+			uint32_t bps;
+			const uint32_t orient = b == 0 ? 0 : (b - 1) % 3 + 1;
+			if(grkb_band_quant(z->expn[c][b], z->mant[c][b], orient, p.prec, p.reversible, 1, ht, p.numgbits, 0, &step,
+							   &bps))
+				return nullptr;
+			k->band_numbps[(size_t)c * nb + b] = bps;
+		}
+		for(uint32_t i = 0; i < ng; ++i)
+		{
+			if(k->table_of[i] < 0)
+				continue;
+			const grkb_cblk_geom& g = k->geom[i];
+			grkb_enc_cblk& e = k->blocks[(size_t)c * n0 + (uint32_t)k->table_of[i]];
+			memset(&e, 0, sizeof(e));
+			e.x = g.x;
+			e.y = g.y;
+			e.w = g.w;
+			e.h = g.h;
+			e.comp = (uint8_t)c;
+			e.orient = g.orient;
+			e.level = g.level;
+			e.cblk_sty = (uint8_t)p.cblk_sty;
+			const uint32_t qb = (g.res == 0 ? 0 : 3 * g.res - 2) + g.band;
+			float step;
+			uint32_t bps;
+			grkb_band_quant(z->expn[c][qb], z->mant[c][qb], g.orient, p.prec, p.reversible, 1, ht, p.numgbits, 0, &step,
+							&bps);
+			e.stepsize = step;
+			e.k_msbs = (uint8_t)bps;
+		}
+	}
+	if(grkb_encoder_create(&tp, &k->enc))
+		return nullptr;
+	const size_t n = k->blocks.size();
+	k->bytes_cap = (size_t)(tp.x1 - tp.x0) * (tp.y1 - tp.y0) * p.numcomps * 4 + 65536;
+	k->coded = (grkb_coded*)grkb_host_alloc(std::max<size_t>(n, 1) * sizeof(grkb_coded));
+	k->passes = (grkb_pass*)grkb_host_alloc(std::max<size_t>(n, 1) * GRKB_ENC_MAX_PASSES * sizeof(grkb_pass));
+	k->bytes = (uint8_t*)grkb_host_alloc(k->bytes_cap);
+	if(!k->coded || !k->passes || !k->bytes)
+		return nullptr;
+	z->kits.push_back(std::move(k));
+	return z->kits.back().get();
+}
+
+// main header (CodeStreamCompress.cpp:640-1130 in the order the reference writes it)
+void write_main_header(const grkb_compressor* z, std::vector<uint8_t>& o)
+{
+	const grkb_compress_params& p = z->p;
+	const bool ht = (p.cblk_sty & GRKB_CBLKSTY_HT) != 0;
+	put16(o, 0xFF4F);
+	// SIZ
+	put16(o, 0xFF51);
+	put16(o, 38 + 3 * p.numcomps);
+	put16(o, ht ? 0x4000 : 0); // Rsiz: GRK_JPH_RSIZ_FLAG for Part 15
+	put32(o, p.x0 + p.width);
+	put32(o, p.y0 + p.height);
+	put32(o, p.x0);
+	put32(o, p.y0);
+	put32(o, p.tile_w ? p.tile_w : p.x0 + p.width - p.tile_x0);
+	put32(o, p.tile_h ? p.tile_h : p.y0 + p.height - p.tile_y0);
+	put32(o, p.tile_x0);
+	put32(o, p.tile_y0);
+	put16(o, p.numcomps);
+	for(uint32_t c = 0; c < p.numcomps; ++c)
+	{
+		o.push_back((uint8_t)((p.prec - 1) | (p.sgnd ? 0x80 : 0)));
+		o.push_back(1);
+		o.push_back(1);
+	}
+	// CAP (Part 15): Pcap bit 15, Ccap15 = reversibility | magnitude bound (write_cap, :1064-1112)
+	if(ht)
+	{
+		uint32_t B = 0;
+		for(uint32_t b = 0; b < 3 * p.numres - 2; ++b)
+			B = std::max<uint32_t>(B, p.reversible ? z->expn[0][b] + p.numgbits - 1
+												   : z->expn[0][b] + p.numgbits - (p.numres - 1 - (b ? (b - 1) / 3 : 0)));
+		const uint32_t Bp = B <= 8 ? 0 : B < 28 ? B - 8 : B < 48 ? 13 + (B >> 2) : 31;
+		put16(o, 0xFF50);
+		put16(o, 8);
+		put32(o, 0x00020000);
+		put16(o, (p.reversible ? 0 : 0x20) | Bp);
+	}
+	// COD
+	bool prt = false;
+	for(uint32_t r = 0; r < p.numres; ++r)
+		prt = prt || p.prec_w_exp[r] != 15 || p.prec_h_exp[r] != 15;
+	put16(o, 0xFF52);
+	put16(o, 12 + (prt ? p.numres : 0));
+	o.push_back((uint8_t)((prt ? 1 : 0) | (p.csty & 6)));
+	o.push_back((uint8_t)p.prog_order);
+	put16(o, 1);
+	o.push_back((uint8_t)(p.mct ? 1 : 0));
+	o.push_back((uint8_t)(p.numres - 1));
+	o.push_back((uint8_t)(p.cblkw_exp - 2));
+	o.push_back((uint8_t)(p.cblkh_exp - 2));
+	o.push_back((uint8_t)p.cblk_sty);
+	o.push_back((uint8_t)(p.reversible ? 1 : 0));
+	if(prt)
+		for(uint32_t r = 0; r < p.numres; ++r)
+			o.push_back((uint8_t)(p.prec_w_exp[r] | (p.prec_h_exp[r] << 4)));
+	// QCD
+	const uint32_t nb = 3 * p.numres - 2;
+	put16(o, 0xFF5C);
+	put16(o, 3 + (p.reversible ? nb : 2 * nb));
+	o.push_back((uint8_t)((p.reversible ? 0 : 2) | (p.numgbits << 5)));
+	for(uint32_t b = 0; b < nb; ++b)
+	{
+		if(p.reversible)
+			o.push_back((uint8_t)(z->expn[0][b] << 3));
+		else
+			put16(o, (z->expn[0][b] << 11) | z->mant[0][b]);
+	}
+	// COM
+	if(!z->comment.empty())
+	{
+		put16(o, 0xFF64);
+		put16(o, 4 + (uint32_t)z->comment.size());
+		put16(o, 1); // Latin text
+		o.insert(o.end(), z->comment.begin(), z->comment.end());
+	}
+}
+
+// T2 of one tile: SOT, SOD and every packet of the single layer, appended to o
+bool write_tile(grkb_compressor* z, TileKit* k, uint32_t tileno, std::vector<uint8_t>& o, std::string& err)
+{
+	const grkb_compress_params& p = z->p;
+	const uint32_t nc = p.numcomps, numres = p.numres, nb = 3 * numres - 2;
+	const size_t sot = o.size();
+	put16(o, 0xFF90);
+	put16(o, 10);
+	put16(o, tileno);
+	put32(o, 0); // Psot, patched below
+	o.push_back(0);
+	o.push_back(1);
+	put16(o, 0xFF93);
+	std::vector<grkb_cs::Poc> progs;
+	progs.push_back(grkb_cs::Poc{0, (uint8_t)numres, (uint8_t)p.prog_order, 0, (uint16_t)nc, 1});
+	TagTreeEnc incl, imsb;
+	uint32_t packet_no = 0;
+	bool ok = true;
+	grkb_cs::for_each_packet(progs, numres, nc, 1, k->idx, k->tp.x0, k->tp.y0, k->tp.x1, k->tp.y1,
+							 [&](uint32_t, uint32_t resno, uint32_t compno, uint64_t precinct) {
+		const grkb_layout_res& R = k->idx.res[resno];
+		if(p.csty & 2) // SOP
+		{
+			put16(o, 0xFF91);
+			put16(o, 4);
+			put16(o, packet_no & 0xFFFF);
+		}
+		z->hdr.clear();
+		BitWriter bw(z->hdr);
+		bw.bit(1); // the reference never writes the empty-packet form (T2Compress.cpp:150-153)
+		for(uint32_t band = 0; band < R.nbands; ++band)
+		{
+			const grkb_layout_pb& pb = k->idx.pb[(size_t)R.first_pb + (size_t)band * R.gw * R.gh + (size_t)precinct];
+			const uint32_t ncb = pb.cgw * pb.cgh;
+			if(ncb == 0 || pb.band_empty)
+				continue;
+			const uint32_t band_bps = k->band_numbps[(size_t)compno * nb + (resno == 0 ? 0 : 3 * resno - 2) + band];
+			incl.init(pb.cgw, pb.cgh);
+			imsb.init(pb.cgw, pb.cgh);
+			for(uint32_t cb = 0; cb < ncb; ++cb)
+			{
+				const int32_t ti = k->table_of[pb.first + cb];
+				const grkb_coded* c = ti >= 0 ? &k->coded[(size_t)compno * k->per_comp + (uint32_t)ti] : nullptr;
+				const uint32_t bps = c ? c->numbps : 0;
+				if(bps > band_bps)
+				{
+					err = "a code block has more bit planes than its band";
+					ok = false;
+					return false;
+				}
+				imsb.setvalue(cb, band_bps - bps);
+				if(c && c->numpasses)
+					incl.setvalue(cb, 0);
+			}
+			for(uint32_t cb = 0; cb < ncb; ++cb)
+			{
+				const int32_t ti = k->table_of[pb.first + cb];
+				const size_t bi = ti >= 0 ? (size_t)compno * k->per_comp + (uint32_t)ti : 0;
+				const grkb_coded* c = ti >= 0 ? &k->coded[bi] : nullptr;
+				incl.compress(bw, cb, 1);
+				if(!c || !c->numpasses)
+					continue;
+				imsb.compress(bw, cb, 0xFF);
+				bw.numpasses(c->numpasses);
+				const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES;
+				// Lblock increment, then one length per codeword segment (T2Compress.cpp:213-256)
+				uint32_t numlenbits = 3, inc = 0, nump = 0, len = 0;
+				for(uint32_t q = 0; q < c->numpasses; ++q)
+				{
+					++nump;
+					len += ps[q].len;
+					if(ps[q].term || q == (uint32_t)c->numpasses - 1)
+					{
+						const int need = (int)floorlog2u(len) + 1 - (int)(numlenbits + floorlog2u(nump));
+						if(need > (int)inc)
+							inc = (uint32_t)need;
+						len = 0;
+						nump = 0;
+					}
+				}
+				bw.comma(inc);
+				numlenbits += inc;
+				for(uint32_t q = 0; q < c->numpasses; ++q)
+				{
+					++nump;
+					len += ps[q].len;
+					if(ps[q].term || q == (uint32_t)c->numpasses - 1)
+					{
+						bw.bits(len, numlenbits + floorlog2u(nump));
+						len = 0;
+						nump = 0;
+					}
+				}
+			}
+		}
+		bw.flush();
+		o.insert(o.end(), z->hdr.begin(), z->hdr.end());
+		if(p.csty & 4) // EPH
+			put16(o, 0xFF92);
+		for(uint32_t band = 0; band < R.nbands; ++band)
+		{
+			const grkb_layout_pb& pb = k->idx.pb[(size_t)R.first_pb + (size_t)band * R.gw * R.gh + (size_t)precinct];
+			const uint32_t ncb = pb.cgw * pb.cgh;
+			if(ncb == 0 || pb.band_empty)
+				continue;
+			for(uint32_t cb = 0; cb < ncb; ++cb)
+			{
+				const int32_t ti = k->table_of[pb.first + cb];
+				if(ti < 0)
+					continue;
+				const grkb_coded& c = k->coded[(size_t)compno * k->per_comp + (uint32_t)ti];
+				if(!c.numpasses || !c.data_len)
+					continue;
+				// what the packet carries is the rate of the last pass, not the coder's byte count
+				const grkb_pass* ps = k->passes + ((size_t)compno * k->per_comp + (uint32_t)ti) * GRKB_ENC_MAX_PASSES;
+				const uint32_t rate = ps[c.numpasses - 1].rate;
+				o.insert(o.end(), k->bytes + c.data_off, k->bytes + c.data_off + std::min<uint32_t>(rate, c.data_len));
+			}
+		}
+		++packet_no;
+		return true;
+	});
+	if(!ok)
+		return false;
+	const uint64_t psot = o.size() - sot;
+	if(psot > 0xFFFFFFFFull)
+	{
+		err = "tile part longer than 4 GB";
+		return false;
+	}
+	o[sot + 6] = (uint8_t)(psot >> 24);
+	o[sot + 7] = (uint8_t)(psot >> 16);
+	o[sot + 8] = (uint8_t)(psot >> 8);
+	o[sot + 9] = (uint8_t)psot;
+	return true;
+}
+} // namespace
+
+extern "C" {
+
+int grkb_compressor_create(int device, const grkb_compress_params* p, grkb_compressor** out)
+{
+	if(!p || !out || p->width == 0 || p->height == 0 || p->numcomps == 0 || p->numcomps > GRKB_MAX_COMPS ||
+	   p->prec == 0 || p->prec > 16 || p->numres == 0 || p->numres > 33 || p->cblkw_exp < 2 || p->cblkh_exp < 2 ||
+	   p->cblkw_exp > 10 || p->cblkh_exp > 10 || p->cblkw_exp + p->cblkh_exp > 12 || p->prog_order > 4 ||
+	   p->tile_x0 > p->x0 || p->tile_y0 > p->y0)
+	{
+		grkb_set_error("grkb_compressor_create: bad parameters");
+		return -1;
+	}
+	const bool ht = (p->cblk_sty & GRKB_CBLKSTY_HT) != 0;
+	if(ht && (p->cblk_sty != GRKB_CBLKSTY_HT || !p->reversible))
+	{
+		grkb_set_error("grkb_compressor_create: HT is written with the reversible transform and no other mode switch");
+		return -1;
+	}
+	if(p->mct && p->numcomps < 3)
+	{
+		grkb_set_error("grkb_compressor_create: the component transform needs three components");
+		return -1;
+	}
+	GRKB_CUDA_CHECK(cudaSetDevice(device));
+	auto z = std::make_unique<grkb_compressor>();
+	z->device = device;
+	z->p = *p;
+	if(z->p.numgbits == 0)
+		z->p.numgbits = ht ? 1 : 2; // grk_compress defaults (src/bin/jp2/grk_compress.cpp:1123-1124)
+	z->comment = p->comment[0] ? std::string(p->comment) : std::string("Created by grok_b200");
+	const uint32_t nb = 3 * p->numres - 2;
+	for(uint32_t c = 0; c < p->numcomps; ++c)
+	{
+		z->expn[c].resize(nb);
+		z->mant[c].resize(nb);
+		if(grkb_qcd_generate(p->numres, p->prec, p->reversible, ht, z->expn[c].data(), z->mant[c].data()))
+			return -1;
+	}
+	*out = z.release();
+	return 0;
+}
+
+void grkb_compressor_destroy(grkb_compressor* z)
+{
+	if(!z)
+		return;
+	cudaSetDevice(z->device);
+	delete z;
+}
+
+int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t stride, uint8_t* out, size_t cap,
+				  size_t* used)
+{
+	if(!z || !planes || !out || !used || stride < z->p.width)
+	{
+		grkb_set_error("grkb_compress: bad arguments");
+		return -1;
+	}
+	GRKB_CUDA_CHECK(cudaSetDevice(z->device));
+	const grkb_compress_params& p = z->p;
+	const uint32_t ix0 = p.x0, iy0 = p.y0, ix1 = p.x0 + p.width, iy1 = p.y0 + p.height;
+	const uint32_t tw = p.tile_w ? p.tile_w : ix1 - p.tile_x0, th = p.tile_h ? p.tile_h : iy1 - p.tile_y0;
+	const uint32_t ntx = (uint32_t)(((uint64_t)ix1 - p.tile_x0 + tw - 1) / tw);
+	const uint32_t nty = (uint32_t)(((uint64_t)iy1 - p.tile_y0 + th - 1) / th);
+	if((uint64_t)ntx * nty > 65535)
+	{
+		grkb_set_error("grkb_compress: more than 65535 tiles");
+		return -1;
+	}
+	std::vector<uint8_t> o;
+	o.reserve((size_t)p.width * p.height * p.numcomps + 65536);
+	write_main_header(z, o);
+	z->t2_ms = z->device_ms = 0;
+	for(uint32_t t = 0; t < ntx * nty; ++t)
+	{
+		const uint32_t tp = t % ntx, tq = t / ntx;
+		grkb_tile_params g{};
+		g.x0 = (uint32_t)std::max<uint64_t>((uint64_t)p.tile_x0 + (uint64_t)tp * tw, ix0);
+		g.y0 = (uint32_t)std::max<uint64_t>((uint64_t)p.tile_y0 + (uint64_t)tq * th, iy0);
+		g.x1 = (uint32_t)std::min<uint64_t>((uint64_t)p.tile_x0 + (uint64_t)(tp + 1) * tw, ix1);
+		g.y1 = (uint32_t)std::min<uint64_t>((uint64_t)p.tile_y0 + (uint64_t)(tq + 1) * th, iy1);
+		g.numcomps = p.numcomps;
+		g.numres = p.numres;
+		g.reversible = p.reversible ? 1 : 0;
+		g.mct = p.mct ? 1 : 0;
+		for(uint32_t c = 0; c < p.numcomps; ++c)
+			g.shift[c] = p.sgnd ? 0 : 1 << (p.prec - 1);
+		TileKit* k = kit_for(z, g);
+		if(!k)
+		{
+			if(!grkb_last_error()[0])
+				grkb_set_error("grkb_compress: tile %u: cannot set up the encoder", t);
+			return -1;
+		}
+		const int32_t* src[GRKB_MAX_COMPS] = {};
+		for(uint32_t c = 0; c < p.numcomps; ++c)
+			src[c] = planes[c] + (size_t)(g.y0 - iy0) * stride + (g.x0 - ix0);
+		const auto t0 = std::chrono::steady_clock::now();
+		size_t nbytes = 0;
+		if(grkb_encoder_encode(k->enc, src, stride, k->blocks.data(), (uint32_t)k->blocks.size(), nullptr, 0, 0, k->coded,
+							   k->passes, k->bytes, k->bytes_cap, &nbytes))
+			return -1;
+		for(size_t i = 0; i < k->blocks.size(); ++i)
+			if(k->coded[i].failed)
+			{
+				grkb_set_error("grkb_compress: tile %u: block %zu overflowed its stream buffer", t, i);
+				return -1;
+			}
+		const auto t1 = std::chrono::steady_clock::now();
+		std::string err;
+		if(!write_tile(z, k, t, o, err))
+		{
+			grkb_set_error("grkb_compress: tile %u: %s", t, err.c_str());
+			return -1;
+		}
+		const auto t2 = std::chrono::steady_clock::now();
+		z->device_ms += std::chrono::duration<double, std::milli>(t1 - t0).count();
+		z->t2_ms += std::chrono::duration<double, std::milli>(t2 - t1).count();
+	}
+	put16(o, 0xFFD9);
+	*used = o.size();
+	if(o.size() > cap)
+	{
+		grkb_set_error("grkb_compress: the codestream needs %zu bytes, the buffer holds %zu", o.size(), cap);
+		return -2;
+	}
+	memcpy(out, o.data(), o.size());
+	return 0;
+}
+
+int grkb_compress_stats(const grkb_compressor* z, double* device_ms, double* t2_ms)
+{
+	if(!z)
+		return -1;
+	if(device_ms)
+		*device_ms = z->device_ms;
+	if(t2_ms)
+		*t2_ms = z->t2_ms;
+	return 0;
+}
+
+} // extern "C"

@@ -518,6 +518,42 @@ int grkb_decompress(grkb_decompressor* d, const uint8_t* data, size_t len, uint3
 /* host milliseconds the last submit spent in marker + packet parsing (T2), and tiles enqueued */
 int grkb_decompress_stats(const grkb_decompressor* d, double* t2_ms, uint32_t* tiles);
 
+/* ---- the encode side of the codestream level ---------------------------------------------------
+ * Image planes in, a complete JPEG 2000 / HTJ2K codestream out: the device tile encoder
+ * (grkb_encoder_*) plus, on the host, what the reference does around it for ONE quality layer that
+ * keeps every coding pass -- main header (CodeStreamCompress::start and the marker writers,
+ * src/lib/jp2/codestream/CodeStreamCompress.cpp:640-1130), packet headers and bodies
+ * (T2Compress::compressPacket / compressHeader, t2/T2Compress.cpp:112-330; TagTree::compress,
+ * t2/TagTree.h:160-200), one tile part per tile.  It replaces grk_compress_init + grk_compress_start
+ * + grk_compress + grk_compress_end (grok.h:1380-1420) for lossless J2K, HTJ2K lossless and
+ * all-passes 9/7 streams, byte-identical to the stock encoder's output for the same parameters.
+ * Rate-controlled layers (PCRD) are NOT written here: they stay with the host. */
+typedef struct grkb_compress_params
+{
+	uint32_t width, height, numcomps, prec, sgnd;
+	uint32_t x0, y0; /* image origin on the reference grid */
+	uint32_t tile_w, tile_h; /* 0: one tile */
+	uint32_t tile_x0, tile_y0; /* tile grid origin (<= image origin) */
+	uint32_t numres, cblkw_exp, cblkh_exp;
+	uint32_t cblk_sty; /* GRKB_CBLKSTY_* (GRKB_CBLKSTY_HT alone for HTJ2K) */
+	uint32_t reversible, mct;
+	uint32_t prog_order; /* 0 LRCP, 1 RLCP, 2 RPCL, 3 PCRL, 4 CPRL */
+	uint32_t csty; /* bit 1: SOP markers, bit 2: EPH markers */
+	uint32_t numgbits; /* guard bits; 0: the reference's default (2, HT: 1) */
+	uint8_t prec_w_exp[33], prec_h_exp[33]; /* log2 precinct size per resolution, lowest first (15: none) */
+	char comment[64]; /* COM marker text; empty: "Created by grok_b200" */
+} grkb_compress_params;
+
+typedef struct grkb_compressor grkb_compressor;
+int grkb_compressor_create(int device, const grkb_compress_params* p, grkb_compressor** out);
+void grkb_compressor_destroy(grkb_compressor* z);
+/* planes[c]: int32 samples, `stride` per row.  out / cap: the codestream buffer; *used = bytes
+ * written (or needed, with -2, when cap is too small). */
+int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t stride, uint8_t* out, size_t cap,
+				  size_t* used);
+/* milliseconds of the last call: device tile encodes (copies included), host T2 + markers */
+int grkb_compress_stats(const grkb_compressor* z, double* device_ms, double* t2_ms);
+
 /* D. allocation-free door --------------------------------------------------------------------- */
 
 /* No counterpart in the reference: added for callers that

@@ -1,0 +1,88 @@
+"""GPU parity of the ENCODE side of the codestream door (grkb_compress, include/grk_b200.h section E):
+image in, codestream out with T2 and the markers on our side.  For one layer that keeps every pass --
+lossless J2K, HTJ2K lossless (BASELINE configs[2]: "byte-identical codestream"), all-passes 9/7 -- the
+bytes must equal the STOCK reference encoder's for the same parameters, whole files compared."""
+import os
+
+import numpy as np
+import pytest
+
+import codec_helpers as H
+from grok_b200 import codestream as CS
+from oracle import oracle as O
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(not O.have_ref(), reason="compiled reference (oracle/_ref) not present")]
+GROK_COMMENT = "Created by Grok     version 9.2.0"
+
+
+def _stock(img, prec, irr, opts="", **kw):
+    try:
+        O.ref_set_rate(0)
+        O.ref_set_encode_options(opts)
+        return O.ref_codec_encode(img, prec, irr, threads=os.cpu_count(), **kw)
+    finally:
+        O.ref_set_encode_options("")
+
+
+CASES = [
+    # w, h, ncomp, prec, irr, ht, numres, cblk, tile, stock opts, ours kwargs
+    (200, 150, 3, 8, 0, 0, 5, (32, 32), (0, 0), "", {}),
+    (257, 131, 1, 8, 0, 0, 4, (64, 64), (0, 0), "", {}),
+    (320, 200, 3, 12, 0, 1, 6, (64, 64), (0, 0), "", {}),
+    (200, 333, 1, 16, 0, 1, 5, (64, 64), (0, 0), "", {}),
+    (256, 200, 3, 12, 1, 0, 6, (64, 64), (0, 0), "", {}),
+    (250, 190, 3, 8, 0, 0, 5, (32, 32), (96, 80), "", {}),
+    (250, 190, 3, 8, 0, 0, 5, (32, 32), (96, 80), "off=13:7;torg=5:3", dict(origin=(13, 7), tile_origin=(5, 3))),
+    (200, 150, 3, 8, 0, 0, 5, (32, 32), (0, 0), "off=3:5", dict(origin=(3, 5))),
+    (200, 150, 3, 8, 0, 0, 5, (32, 32), (0, 0), "prog=RPCL;prc=64x64;sop;eph",
+     dict(prog="RPCL", precincts=[(64, 64)], sop=True, eph=True)),
+    (200, 150, 3, 8, 0, 0, 5, (32, 32), (0, 0), "prog=CPRL;prc=128x128:64x64", dict(prog="CPRL", precincts=[(128, 128), (64, 64)])),
+    (200, 150, 3, 8, 0, 0, 5, (32, 32), (0, 0), "prog=PCRL;prc=64x64", dict(prog="PCRL", precincts=[(64, 64)])),
+    (200, 150, 3, 8, 0, 0, 5, (32, 32), (0, 0), "prog=RLCP", dict(prog="RLCP")),
+    (300, 260, 3, 12, 0, 1, 4, (64, 64), (128, 128), "prog=RPCL;prc=128x128", dict(prog="RPCL", precincts=[(128, 128)])),
+    (130, 100, 1, 10, 0, 0, 5, (64, 64), (0, 0), "sty=63", dict(cblk_sty=63)),
+    (130, 100, 1, 10, 0, 0, 5, (64, 64), (0, 0), "sty=5", dict(cblk_sty=5)),
+]
+
+
+@pytest.mark.parametrize("w,h,ncomp,prec,irr,ht,nr,cblk,tile,opts,kw", CASES)
+def test_compress_is_byte_identical_to_the_stock_encoder(gpu, w, h, ncomp, prec, irr, ht, nr, cblk, tile, opts, kw):
+    img = H.synth_image(w, h, ncomp, prec, seed=w + 7 * h)
+    want = _stock(img, prec, irr, opts, ht=bool(ht), numres=nr, cblk=cblk, tile=tile)
+    z = CS.Compressor(w, h, ncomp, prec, reversible=not irr, ht=bool(ht), numres=nr, cblk=cblk, tile=tile,
+                      comment=GROK_COMMENT, **kw)
+    got = z.encode(img)
+    z.close()
+    assert got.size == want.size and np.array_equal(got, want), \
+        "first difference at byte %d of %d / %d" % (int(np.argmax(got[:min(got.size, want.size)] != want[:min(got.size, want.size)])), got.size, want.size)
+
+
+def test_compress_then_decompress_round_trip(gpu):
+    """our encoder's stream through our decoder and through the stock decoder: the image back"""
+    img = H.synth_image(300, 260, 3, 12, seed=5)
+    z = CS.Compressor(300, 260, 3, 12, ht=True, numres=5, tile=(128, 128))
+    cs = z.encode(img)
+    z.close()
+    d = CS.Decompressor(0, slots=2)
+    got = d.decode(cs)
+    d.close()
+    ref = O.ref_codec_decode(cs, 3, 300, 260)
+    for c in range(3):
+        assert np.array_equal(got[c], img[c]) and np.array_equal(ref[c], img[c])
+
+
+W4K, H4K = 4096, 2160
+
+
+def test_configs2_ht_4k_encode_codestream_byte_identical(gpu):
+    """BASELINE configs[2], encode: 4096x2160 12-bit RGB HTJ2K lossless -- the whole codestream equal
+    to the stock encoder's, byte for byte"""
+    img = [p >> 4 for p in H.synth_image(W4K, H4K, 3, 16, seed=4096)]
+    want = _stock(img, 12, 0, ht=True, numres=6, cblk=(64, 64))
+    z = CS.Compressor(W4K, H4K, 3, 12, ht=True, numres=6, comment=GROK_COMMENT)
+    got = z.encode(img)
+    st = z.stats()
+    z.close()
+    assert got.size == want.size and np.array_equal(got, want)
+    assert st["t2_ms"] < 200
