@@ -189,7 +189,7 @@ class CompressParams(C.Structure):
                 ("tile_y0", _u32), ("numres", _u32), ("cblkw_exp", _u32), ("cblkh_exp", _u32),
                 ("cblk_sty", _u32), ("reversible", _u32), ("mct", _u32), ("prog_order", _u32), ("csty", _u32),
                 ("numgbits", _u32), ("prec_w_exp", C.c_uint8 * 33), ("prec_h_exp", C.c_uint8 * 33),
-                ("comment", C.c_char * 64)]
+                ("comment", C.c_char * 64), ("rate", C.c_double)]
 
 
 lib.grkb_compressor_create.argtypes = [C.c_int, C.POINTER(CompressParams), C.POINTER(_vp)]
@@ -206,7 +206,7 @@ class Compressor:
 
     def __init__(self, width, height, numcomps, prec, reversible=True, ht=False, numres=6, cblk=(64, 64),
                  tile=(0, 0), origin=(0, 0), tile_origin=None, prog="LRCP", precincts=None, sop=False, eph=False,
-                 cblk_sty=0, mct=None, sgnd=False, comment="", device=0):
+                 cblk_sty=0, mct=None, sgnd=False, comment="", rate=0.0, device=0):
         p = CompressParams()
         p.width, p.height, p.numcomps, p.prec, p.sgnd = width, height, numcomps, prec, int(sgnd)
         p.x0, p.y0 = origin
@@ -233,6 +233,7 @@ class Compressor:
                 p.prec_w_exp[r] = max(w, 1).bit_length() - 1
                 p.prec_h_exp[r] = max(h, 1).bit_length() - 1
         p.comment = comment.encode()
+        p.rate = float(rate)
         self.params = p
         self.h = _vp()
         check(lib.grkb_compressor_create(device, C.byref(p), C.byref(self.h)), "grkb_compressor_create")

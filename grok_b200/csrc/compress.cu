@@ -11,12 +11,14 @@
 //   tile parts          one tile part per tile: SOT, SOD, packets (SOTMarker.cpp:30-58)
 // Without a rate target the reference keeps all passes too (makeSingleLosslessLayer,
 // tile/TileProcessor.cpp:969-977), so for these parameters the codestream is byte-identical to the
-// stock encoder's (tests/test_compress_gpu.py).  Rate-controlled layers (PCRD) are not written here.
+// stock encoder's (tests/test_compress_gpu.py).  A single layer with a rate target is allocated as
+// TileProcessor::pcrdBisectSimple does it (rate_allocate below).
 #include "pipeline.h"
 #include "codestream.h"
 #include "geometry.h"
 #include "packet_order.h"
 #include <chrono>
+#include <math.h>
 #include <memory>
 #include <string.h>
 #include <string>
@@ -188,6 +190,7 @@ struct TileKit
 	std::vector<grkb_enc_cblk> blocks; // component-major, non-degenerate blocks only
 	std::vector<uint32_t> band_numbps; // per (component, band in codestream order)
 	uint32_t per_comp = 0; // blocks per component in `blocks`
+	std::vector<uint32_t> npass; // coding passes of every block that go into the layer (rate allocation)
 	// results of the last encode (page-locked)
 	grkb_coded* coded = nullptr;
 	grkb_pass* passes = nullptr;
@@ -386,11 +389,250 @@ void write_main_header(const grkb_compressor* z, std::vector<uint8_t>& o)
 	}
 }
 
+// One packet: header bits into z->hdr (returns false on an inconsistent table).  The passes of a block
+// that go into the layer are k->npass[block].
+bool packet_header(grkb_compressor* z, TileKit* k, uint32_t resno, uint32_t compno, uint64_t precinct,
+				   TagTreeEnc& incl, TagTreeEnc& imsb, std::string& err)
+{
+	const grkb_compress_params& p = z->p;
+	const uint32_t nb = 3 * p.numres - 2;
+	const grkb_layout_res& R = k->idx.res[resno];
+	z->hdr.clear();
+	BitWriter bw(z->hdr);
+	bw.bit(1); // the reference never writes the empty-packet form (T2Compress.cpp:150-153)
+	for(uint32_t band = 0; band < R.nbands; ++band)
+	{
+		const grkb_layout_pb& pb = k->idx.pb[(size_t)R.first_pb + (size_t)band * R.gw * R.gh + (size_t)precinct];
+		const uint32_t ncb = pb.cgw * pb.cgh;
+		if(ncb == 0 || pb.band_empty)
+			continue;
+		const uint32_t band_bps = k->band_numbps[(size_t)compno * nb + (resno == 0 ? 0 : 3 * resno - 2) + band];
+		incl.init(pb.cgw, pb.cgh);
+		imsb.init(pb.cgw, pb.cgh);
+		for(uint32_t cb = 0; cb < ncb; ++cb)
+		{
+			const int32_t ti = k->table_of[pb.first + cb];
+			const size_t bi = ti >= 0 ? (size_t)compno * k->per_comp + (uint32_t)ti : 0;
+			const uint32_t bps = ti >= 0 ? k->coded[bi].numbps : 0;
+			if(bps > band_bps)
+			{
+				err = "a code block has more bit planes than its band";
+				return false;
+			}
+			imsb.setvalue(cb, band_bps - bps);
+			if(ti >= 0 && k->npass[bi])
+				incl.setvalue(cb, 0);
+		}
+		for(uint32_t cb = 0; cb < ncb; ++cb)
+		{
+			const int32_t ti = k->table_of[pb.first + cb];
+			const size_t bi = ti >= 0 ? (size_t)compno * k->per_comp + (uint32_t)ti : 0;
+			const uint32_t np = ti >= 0 ? k->npass[bi] : 0;
+			incl.compress(bw, cb, 1);
+			if(!np)
+				continue;
+			imsb.compress(bw, cb, 0xFF);
+			bw.numpasses(np);
+			const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES;
+			// Lblock increment, then one length per codeword segment (T2Compress.cpp:213-256)
+			uint32_t numlenbits = 3, inc = 0, nump = 0, len = 0;
+			for(uint32_t q = 0; q < np; ++q)
+			{
+				++nump;
+				len += ps[q].len;
+				if(ps[q].term || q == np - 1)
+				{
+					const int need = (int)floorlog2u(len) + 1 - (int)(numlenbits + floorlog2u(nump));
+					if(need > (int)inc)
+						inc = (uint32_t)need;
+					len = 0;
+					nump = 0;
+				}
+			}
+			bw.comma(inc);
+			numlenbits += inc;
+			for(uint32_t q = 0; q < np; ++q)
+			{
+				++nump;
+				len += ps[q].len;
+				if(ps[q].term || q == np - 1)
+				{
+					bw.bits(len, numlenbits + floorlog2u(nump));
+					len = 0;
+					nump = 0;
+				}
+			}
+		}
+	}
+	bw.flush();
+	return true;
+}
+
+// bytes of block bi that go into the layer: the rate of its last included pass
+inline uint32_t layer_len(const TileKit* k, size_t bi)
+{
+	const uint32_t np = k->npass[bi];
+	if(!np)
+		return 0;
+	return std::min<uint32_t>(k->passes[bi * GRKB_ENC_MAX_PASSES + np - 1].rate, k->coded[bi].data_len);
+}
+
+// T2Compress::compressPacketsSimulate (t2/T2Compress.cpp:58-110, :331-420): would the packets of the
+// layer fit in max_bytes?  The reference's own accounting, packet by packet: a header must stay
+// strictly below what is left (BitIO::writeByte fails when it fills its buffer), a body may use it up.
+bool simulate(grkb_compressor* z, TileKit* k, uint64_t max_bytes, uint64_t* total)
+{
+	const grkb_compress_params& p = z->p;
+	std::vector<grkb_cs::Poc> progs;
+	progs.push_back(grkb_cs::Poc{0, (uint8_t)p.numres, (uint8_t)p.prog_order, 0, (uint16_t)p.numcomps, 1});
+	TagTreeEnc incl, imsb;
+	bool fits = true;
+	const bool limited = max_bytes != UINT32_MAX;
+	uint64_t all = 0, left = max_bytes;
+	std::string err;
+	grkb_cs::for_each_packet(progs, p.numres, p.numcomps, 1, k->idx, k->tp.x0, k->tp.y0, k->tp.x1, k->tp.y1,
+							 [&](uint32_t, uint32_t resno, uint32_t compno, uint64_t precinct) {
+		uint64_t avail = left, bytes = 0;
+		if(p.csty & 2)
+		{
+			if(limited)
+				avail -= 6;
+			bytes += 6;
+		}
+		if(!packet_header(z, k, resno, compno, precinct, incl, imsb, err) || (limited && z->hdr.size() >= avail))
+		{
+			fits = false;
+			return false;
+		}
+		bytes += z->hdr.size();
+		if(limited)
+			avail -= z->hdr.size();
+		if(p.csty & 4)
+		{
+			if(limited)
+				avail -= 2;
+			bytes += 2;
+		}
+		const grkb_layout_res& R = k->idx.res[resno];
+		for(uint32_t band = 0; band < R.nbands && fits; ++band)
+		{
+			const grkb_layout_pb& pb = k->idx.pb[(size_t)R.first_pb + (size_t)band * R.gw * R.gh + (size_t)precinct];
+			// (the reference's simulation walks the bodies of empty bands too: they hold no passes)
+			for(uint32_t cb = 0; cb < pb.cgw * pb.cgh; ++cb)
+			{
+				const int32_t ti = k->table_of[pb.first + cb];
+				if(ti < 0)
+					continue;
+				const size_t bi = (size_t)compno * k->per_comp + (uint32_t)ti;
+				const uint32_t len = layer_len(k, bi);
+				if(!k->npass[bi])
+					continue;
+				if(limited && len > avail)
+				{
+					fits = false;
+					break;
+				}
+				bytes += len;
+				if(limited)
+					avail -= len;
+			}
+		}
+		if(!fits)
+			return false;
+		all += bytes;
+		if(limited)
+			left -= bytes;
+		return true;
+	});
+	if(total)
+		*total = all;
+	return fits;
+}
+
+// TileProcessor::makeLayerSimple (tile/TileProcessor.cpp:1366-1440) for the single layer
+void make_layer(TileKit* k, double thresh)
+{
+	for(size_t bi = 0; bi < k->blocks.size(); ++bi)
+	{
+		const uint32_t total = k->coded[bi].numpasses;
+		const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES;
+		uint32_t inc = 0;
+		if(thresh == 0)
+			inc = total;
+		else
+			for(uint32_t q = 0; q < total; ++q)
+			{
+				uint32_t dr;
+				double dd;
+				if(inc == 0)
+				{
+					dr = ps[q].rate;
+					dd = ps[q].distortion;
+				}
+				else
+				{
+					dr = ps[q].rate - ps[inc - 1].rate;
+					dd = ps[q].distortion - ps[inc - 1].distortion;
+				}
+				if(!dr)
+				{
+					if(dd != 0)
+						inc = q + 1;
+					continue;
+				}
+				const double slope = dd / dr;
+				if(thresh - slope < 2.2204460492503131e-16) // DBL_EPSILON
+					inc = q + 1;
+			}
+		k->npass[bi] = inc;
+	}
+}
+
+// TileProcessor::pcrdBisectSimple (tile/TileProcessor.cpp:1195-1357), one layer, rate target in bytes:
+// the slope threshold is bisected on the reference's own packet accounting until the layer fits.
+void rate_allocate(grkb_compressor* z, TileKit* k, double rate_bytes)
+{
+	double min_slope = 1.7976931348623157e308, max_slope = -1;
+	for(size_t bi = 0; bi < k->blocks.size(); ++bi)
+	{
+		const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES;
+		for(uint32_t q = 0; q < k->coded[bi].numpasses; ++q)
+		{
+			const int32_t dr = q ? (int32_t)(ps[q].rate - ps[q - 1].rate) : (int32_t)ps[q].rate;
+			const double dd = q ? ps[q].distortion - ps[q - 1].distortion : ps[q].distortion;
+			if(dr == 0)
+				continue;
+			const double s = dd / dr;
+			if(s < min_slope)
+				min_slope = s;
+			if(s > max_slope)
+				max_slope = s;
+		}
+	}
+	const uint64_t max_len = rate_bytes > 0 ? (uint64_t)(uint32_t)ceil(rate_bytes) : UINT32_MAX;
+	double lower = min_slope, upper = max_slope, prev = -1, thresh = 0;
+	for(uint32_t i = 0; i < 128; ++i)
+	{
+		thresh = (upper == -1) ? lower : (lower + upper) / 2;
+		make_layer(k, thresh);
+		if(prev != -1 && fabs(prev - thresh) < 0.001)
+			break;
+		prev = thresh;
+		if(!simulate(z, k, max_len, nullptr))
+		{
+			lower = thresh;
+			continue;
+		}
+		upper = thresh;
+	}
+	make_layer(k, (upper == -1) ? thresh : upper);
+}
+
 // T2 of one tile: SOT, SOD and every packet of the single layer, appended to o
 bool write_tile(grkb_compressor* z, TileKit* k, uint32_t tileno, std::vector<uint8_t>& o, std::string& err)
 {
 	const grkb_compress_params& p = z->p;
-	const uint32_t nc = p.numcomps, numres = p.numres, nb = 3 * numres - 2;
+	const uint32_t nc = p.numcomps, numres = p.numres;
 	const size_t sot = o.size();
 	put16(o, 0xFF90);
 	put16(o, 10);
@@ -413,75 +655,11 @@ bool write_tile(grkb_compressor* z, TileKit* k, uint32_t tileno, std::vector<uin
 			put16(o, 4);
 			put16(o, packet_no & 0xFFFF);
 		}
-		z->hdr.clear();
-		BitWriter bw(z->hdr);
-		bw.bit(1); // the reference never writes the empty-packet form (T2Compress.cpp:150-153)
-		for(uint32_t band = 0; band < R.nbands; ++band)
+		if(!packet_header(z, k, resno, compno, precinct, incl, imsb, err))
 		{
-			const grkb_layout_pb& pb = k->idx.pb[(size_t)R.first_pb + (size_t)band * R.gw * R.gh + (size_t)precinct];
-			const uint32_t ncb = pb.cgw * pb.cgh;
-			if(ncb == 0 || pb.band_empty)
-				continue;
-			const uint32_t band_bps = k->band_numbps[(size_t)compno * nb + (resno == 0 ? 0 : 3 * resno - 2) + band];
-			incl.init(pb.cgw, pb.cgh);
-			imsb.init(pb.cgw, pb.cgh);
-			for(uint32_t cb = 0; cb < ncb; ++cb)
-			{
-				const int32_t ti = k->table_of[pb.first + cb];
-				const grkb_coded* c = ti >= 0 ? &k->coded[(size_t)compno * k->per_comp + (uint32_t)ti] : nullptr;
-				const uint32_t bps = c ? c->numbps : 0;
-				if(bps > band_bps)
-				{
-					err = "a code block has more bit planes than its band";
-					ok = false;
-					return false;
-				}
-				imsb.setvalue(cb, band_bps - bps);
-				if(c && c->numpasses)
-					incl.setvalue(cb, 0);
-			}
-			for(uint32_t cb = 0; cb < ncb; ++cb)
-			{
-				const int32_t ti = k->table_of[pb.first + cb];
-				const size_t bi = ti >= 0 ? (size_t)compno * k->per_comp + (uint32_t)ti : 0;
-				const grkb_coded* c = ti >= 0 ? &k->coded[bi] : nullptr;
-				incl.compress(bw, cb, 1);
-				if(!c || !c->numpasses)
-					continue;
-				imsb.compress(bw, cb, 0xFF);
-				bw.numpasses(c->numpasses);
-				const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES;
-				// Lblock increment, then one length per codeword segment (T2Compress.cpp:213-256)
-				uint32_t numlenbits = 3, inc = 0, nump = 0, len = 0;
-				for(uint32_t q = 0; q < c->numpasses; ++q)
-				{
-					++nump;
-					len += ps[q].len;
-					if(ps[q].term || q == (uint32_t)c->numpasses - 1)
-					{
-						const int need = (int)floorlog2u(len) + 1 - (int)(numlenbits + floorlog2u(nump));
-						if(need > (int)inc)
-							inc = (uint32_t)need;
-						len = 0;
-						nump = 0;
-					}
-				}
-				bw.comma(inc);
-				numlenbits += inc;
-				for(uint32_t q = 0; q < c->numpasses; ++q)
-				{
-					++nump;
-					len += ps[q].len;
-					if(ps[q].term || q == (uint32_t)c->numpasses - 1)
-					{
-						bw.bits(len, numlenbits + floorlog2u(nump));
-						len = 0;
-						nump = 0;
-					}
-				}
-			}
+			ok = false;
+			return false;
 		}
-		bw.flush();
 		o.insert(o.end(), z->hdr.begin(), z->hdr.end());
 		if(p.csty & 4) // EPH
 			put16(o, 0xFF92);
@@ -496,13 +674,10 @@ bool write_tile(grkb_compressor* z, TileKit* k, uint32_t tileno, std::vector<uin
 				const int32_t ti = k->table_of[pb.first + cb];
 				if(ti < 0)
 					continue;
-				const grkb_coded& c = k->coded[(size_t)compno * k->per_comp + (uint32_t)ti];
-				if(!c.numpasses || !c.data_len)
-					continue;
-				// what the packet carries is the rate of the last pass, not the coder's byte count
-				const grkb_pass* ps = k->passes + ((size_t)compno * k->per_comp + (uint32_t)ti) * GRKB_ENC_MAX_PASSES;
-				const uint32_t rate = ps[c.numpasses - 1].rate;
-				o.insert(o.end(), k->bytes + c.data_off, k->bytes + c.data_off + std::min<uint32_t>(rate, c.data_len));
+				const size_t bi = (size_t)compno * k->per_comp + (uint32_t)ti;
+				const uint32_t len = layer_len(k, bi);
+				if(len)
+					o.insert(o.end(), k->bytes + k->coded[bi].data_off, k->bytes + k->coded[bi].data_off + len);
 			}
 		}
 		++packet_no;
@@ -596,6 +771,7 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 	std::vector<uint8_t> o;
 	o.reserve((size_t)p.width * p.height * p.numcomps + 65536);
 	write_main_header(z, o);
+	const size_t header_size = o.size();
 	z->t2_ms = z->device_ms = 0;
 	for(uint32_t t = 0; t < ntx * nty; ++t)
 	{
@@ -623,8 +799,11 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 			src[c] = planes[c] + (size_t)(g.y0 - iy0) * stride + (g.x0 - ix0);
 		const auto t0 = std::chrono::steady_clock::now();
 		size_t nbytes = 0;
-		if(grkb_encoder_encode(k->enc, src, stride, k->blocks.data(), (uint32_t)k->blocks.size(), nullptr, 0, 0, k->coded,
-							   k->passes, k->bytes, k->bytes_cap, &nbytes))
+		static const double norms_rev[3] = {1.732, .8292, .8292}, norms_irrev[3] = {1.732, 1.805, 1.573};
+		const bool rc = p.rate > 0;
+		const double* norms = (rc && p.mct) ? (p.reversible ? norms_rev : norms_irrev) : nullptr;
+		if(grkb_encoder_encode(k->enc, src, stride, k->blocks.data(), (uint32_t)k->blocks.size(), norms, norms ? 3 : 0,
+							   rc ? 1 : 0, k->coded, k->passes, k->bytes, k->bytes_cap, &nbytes))
 			return -1;
 		for(size_t i = 0; i < k->blocks.size(); ++i)
 			if(k->coded[i].failed)
@@ -633,6 +812,20 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 				return -1;
 			}
 		const auto t1 = std::chrono::steady_clock::now();
+		k->npass.resize(k->blocks.size());
+		for(size_t i = 0; i < k->blocks.size(); ++i)
+			k->npass[i] = k->coded[i].numpasses;
+		if(rc)
+		{
+			// the tile's byte budget as CodeStreamCompress::updateRates leaves it (:950-1018): its share of
+			// the target size minus its share of the main header, at least 30 bytes
+			const double pixels = (double)(g.x1 - g.x0) * (double)(g.y1 - g.y0);
+			double bytes = ((double)(p.numcomps * p.prec) * pixels) / (p.rate * 8.0);
+			bytes -= (pixels * (double)header_size) / ((double)p.width * (double)p.height);
+			if(bytes < 30.0)
+				bytes = 30.0;
+			rate_allocate(z, k, bytes);
+		}
 		std::string err;
 		if(!write_tile(z, k, t, o, err))
 		{

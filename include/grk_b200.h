@@ -525,9 +525,10 @@ int grkb_decompress_stats(const grkb_decompressor* d, double* t2_ms, uint32_t* t
  * src/lib/jp2/codestream/CodeStreamCompress.cpp:640-1130), packet headers and bodies
  * (T2Compress::compressPacket / compressHeader, t2/T2Compress.cpp:112-330; TagTree::compress,
  * t2/TagTree.h:160-200), one tile part per tile.  It replaces grk_compress_init + grk_compress_start
- * + grk_compress + grk_compress_end (grok.h:1380-1420) for lossless J2K, HTJ2K lossless and
- * all-passes 9/7 streams, byte-identical to the stock encoder's output for the same parameters.
- * Rate-controlled layers (PCRD) are NOT written here: they stay with the host. */
+ * + grk_compress + grk_compress_end (grok.h:1380-1420) for lossless J2K, HTJ2K lossless, all-passes
+ * 9/7 streams and single layers with a rate target, byte-identical to the stock encoder's output for
+ * the same parameters.  Not written here: several quality layers, POC, tile-part division, the
+ * digital-cinema profiles' per-component limits (those stay with the host behind grk_plugin_*). */
 typedef struct grkb_compress_params
 {
 	uint32_t width, height, numcomps, prec, sgnd;
@@ -542,6 +543,11 @@ typedef struct grkb_compress_params
 	uint32_t numgbits; /* guard bits; 0: the reference's default (2, HT: 1) */
 	uint8_t prec_w_exp[33], prec_h_exp[33]; /* log2 precinct size per resolution, lowest first (15: none) */
 	char comment[64]; /* COM marker text; empty: "Created by grok_b200" */
+	double rate; /* 0: keep every pass.  > 0: compression ratio of the single layer (-r of grk_compress):
+				  * the block coders also deliver every pass's distortion and the passes that go into
+				  * the layer are chosen by TileProcessor::pcrdBisectSimple's bisection of the slope
+				  * threshold on the reference's own packet accounting (tile/
+				  * TileProcessor.cpp:1195-1440, t2/T2Compress.cpp:58-110, :331-420) */
 } grkb_compress_params;
 
 typedef struct grkb_compressor grkb_compressor;

@@ -86,3 +86,38 @@ def test_configs2_ht_4k_encode_codestream_byte_identical(gpu):
     z.close()
     assert got.size == want.size and np.array_equal(got, want)
     assert st["t2_ms"] < 200
+
+
+@pytest.mark.parametrize("w,h,ncomp,prec,irr,nr,cblk,tile,rate,opts,kw", [
+    (320, 200, 3, 8, 1, 6, (64, 64), (0, 0), 12.0, "", {}),
+    (320, 200, 3, 8, 0, 6, (64, 64), (0, 0), 6.0, "", {}),
+    (257, 131, 1, 8, 0, 4, (32, 32), (0, 0), 4.0, "", {}),
+    (320, 200, 3, 12, 1, 6, (32, 32), (0, 0), 20.0, "prog=CPRL;prc=128x128", dict(prog="CPRL", precincts=[(128, 128)])),
+    (320, 200, 3, 12, 1, 5, (32, 32), (0, 0), 40.0, "sop;eph", dict(sop=True, eph=True)),
+    (250, 190, 3, 8, 1, 5, (32, 32), (128, 96), 10.0, "", {}),
+    (320, 200, 3, 12, 1, 6, (64, 64), (0, 0), 1.0, "", {}),
+])
+def test_rate_controlled_layer_is_byte_identical_to_the_stock_encoder(gpu, w, h, ncomp, prec, irr, nr, cblk, tile, rate,
+                                                                      opts, kw):
+    """the passes that go into a rate-controlled layer are chosen on our side, by the
+    reference's own bisection (pcrdBisectSimple) on its own packet accounting -> same truncation
+    points, same bytes, whole files compared"""
+    img = H.synth_image(w, h, ncomp, prec, seed=3 * w + h)
+    try:
+        O.ref_set_rate(rate)
+        O.ref_set_encode_options(opts)
+        want = O.ref_codec_encode(img, prec, irr, numres=nr, cblk=cblk, tile=tile)
+        O.ref_set_rate(0)
+        full = O.ref_codec_encode(img, prec, irr, numres=nr, cblk=cblk, tile=tile)
+    finally:
+        O.ref_set_rate(0)
+        O.ref_set_encode_options("")
+    z = CS.Compressor(w, h, ncomp, prec, reversible=not irr, numres=nr, cblk=cblk, tile=tile, rate=rate,
+                      comment=GROK_COMMENT, **kw)
+    got = z.encode(img)
+    z.close()
+    if rate > 1:
+        assert want.size < full.size
+    n = min(got.size, want.size)
+    assert got.size == want.size and np.array_equal(got, want), \
+        "sizes %d / %d, first difference at byte %d" % (got.size, want.size, int(np.argmax(got[:n] != want[:n])))
