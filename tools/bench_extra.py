@@ -499,9 +499,70 @@ def plugin_batch_decode(args):
                                    "frame identical: %s" % (ct * 1e3, same)}}), flush=True)
 
 
+def compress(args):
+    """The encode side of the codestream door (grkb_compress): frames in page-locked host memory in,
+    complete codestreams out -- T2, markers and (for the rate-controlled DCI frames) the reference's
+    PCRD bisection on our side.  One host thread and one compressor per frame in flight."""
+    import threading
+    from oracle import oracle as O
+    from grok_b200 import codestream as CS
+    from grok_b200 import tile as T
+    W, H = 4096, 2160
+    dci = not args.ht
+    base = [p >> 4 for p in synth(W, H, 16, 4096)]
+    pins = [T.PinnedArray((H, W), np.int32) for _ in range(3)]
+    for p_, b in zip(pins, base):
+        p_.array[:] = b
+    img = [p_.array for p_ in pins]
+    kw = dict(reversible=False, cblk=(32, 32), rate=W * H * 3 * 1.5 / 1302083.0) if dci else \
+        dict(reversible=True, ht=True, cblk=(64, 64))
+    nthreads = args.inflight or 8
+    zs = [CS.Compressor(W, H, 3, 12, numres=6, **kw) for _ in range(nthreads)]
+    outs = [z.encode(img) for z in zs]  # warm-up: encoders, pools
+    per = max(1, args.frames // nthreads)
+
+    def work(z):
+        for _ in range(per):
+            z.encode(img)
+
+    t0 = time.perf_counter()
+    th = [threading.Thread(target=work, args=(z,)) for z in zs]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    dt = time.perf_counter() - t0
+    n = per * nthreads
+    st = zs[0].stats()
+    line = {"metric": "encode_mpixels_per_s", "value": W * H / 1e6 * n / dt, "unit": "Mpixel/s", "n_gpus": 1,
+            "ms_per_frame": dt * 1e3 / n, "dtype": "f32" if dci else "i32", "data": "synthetic",
+            "config": {"workload": "grkb_compress_4096x2160_rgb12_" + ("97_ict_mq_cblk32_rate_cinema4k_bytes" if dci
+                                                                       else "53_rct_ht_lossless_cblk64"),
+                       "frames": n, "host_threads": nthreads, "coded_bytes_per_frame": int(outs[0].size),
+                       "scope": "int32 planes in page-locked host memory -> H2D -> DC shift, MCT, wavelet, quantiser, "
+                                "block coders on the device -> D2H of streams + pass records -> " +
+                                ("PCRD bisection + " if dci else "") + "packet headers, markers on the host; wall clock",
+                       "one_frame_alone": {"device_ms": st["device_ms"], "host_t2_ms": st["t2_ms"]}}}
+    if not args.no_cpu and O.have_ref():
+        try:
+            O.ref_set_rate(kw.get("rate", 0))
+            t = time.perf_counter()
+            ref = O.ref_codec_encode(base, 12, 0 if args.ht else 1, ht=bool(args.ht), numres=6, cblk=kw["cblk"],
+                                     threads=os.cpu_count())
+            ct = time.perf_counter() - t
+        finally:
+            O.ref_set_rate(0)
+        line["cpu_baseline"] = {"value": W * H / 1e6 / ct, "unit": "Mpixel/s", "cores": os.cpu_count(), "kind": "reference",
+                                "sample": "one frame, stock encoder on a memory stream, %.0f ms, %d bytes" % (ct * 1e3, ref.size)}
+    print(json.dumps(line), flush=True)
+    for z in zs:
+        z.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["ht_encode", "tiled", "mq_encode", "plugin_batch", "plugin_batch_decode"])
+    ap.add_argument("what", choices=["ht_encode", "tiled", "mq_encode", "plugin_batch", "plugin_batch_decode", "compress"])
+    ap.add_argument("--ht", action="store_true", help="compress: HTJ2K lossless frames instead of rate-controlled DCI-4K")
     ap.add_argument("--frames", type=int, default=8)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--inflight", type=int, default=None)
@@ -520,7 +581,7 @@ def main():
     if args.inflight is None and not args.what.startswith("plugin_batch"):
         args.inflight = 4 if args.what == "tiled" else 2
     {"ht_encode": ht_encode, "tiled": tiled, "mq_encode": mq_encode, "plugin_batch": plugin_batch,
-     "plugin_batch_decode": plugin_batch_decode}[args.what](args)
+     "plugin_batch_decode": plugin_batch_decode, "compress": compress}[args.what](args)
 
 
 if __name__ == "__main__":
