@@ -343,6 +343,8 @@ def run_ours(args, wl):
     numa_bound = shard.bind_to_device(local) if world > 1 else False
     dist = None
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keeps NCCL's banner off stdout: one JSON line only
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
