@@ -171,6 +171,36 @@ def cpu_reference_decode(cs, steps, warmup, threads):
     return W * H / 1e6 / dt, dt
 
 
+def cli_timings(wl):
+    """the stock grk_decompress BINARY (oracle/_ref/bin, built from the
+    reference's own CLI sources) on the workload's codestream, wall clock of the whole process
+    (file read, decode, 16-bit PPM write), all host threads and one"""
+    exe = os.path.join(ROOT, "oracle", "_ref", "bin", "grk_decompress")
+    if not os.path.exists(exe):
+        return None
+    import tempfile
+    d = tempfile.mkdtemp(prefix="grkb_cli_")
+    try:
+        src, dst = os.path.join(d, "f.j2k"), os.path.join(d, "f.ppm")
+        codestream(wl).tofile(src)
+        out = {}
+        for label, h in (("H_all", os.cpu_count() or 1), ("H_1", 1)):
+            t = time.perf_counter()
+            r = subprocess.run([exe, "-i", src, "-o", dst, "-H", str(h)], stdout=subprocess.DEVNULL,
+                               stderr=subprocess.DEVNULL, timeout=300)
+            if r.returncode != 0:
+                return {"error": "grk_decompress exited %d" % r.returncode}
+            out["grk_decompress_%s_ms" % label] = (time.perf_counter() - t) * 1e3
+        out["what"] = "stock CLI binary, whole process wall clock incl. file read and PPM write; H_all = %d threads" % (
+            os.cpu_count() or 1)
+        return out
+    except Exception as e:
+        return {"error": str(e)[:120]}
+    finally:
+        import shutil
+        shutil.rmtree(d, ignore_errors=True)
+
+
 def run_reference(args, wl):
     rank, local, world = dist_env()
     if rank != 0:
@@ -330,6 +360,65 @@ def plugin_legs(wl, args):
         return out
     except Exception as e:  # the plugin legs are extra keys; the line stands without them
         return {"e2e_plugin": {"value": None, "error": str(e)[:200]}}
+
+
+def encode_legs(args):
+    """N = 1 extras: the ENCODE side of the codestream door (grkb_compress) on the frames of BASELINE
+    configs[4] (DCI-4K 12-bit 9/7, 32x32 blocks, one layer at the cinema-4K byte budget: T1 with
+    distortions on the device, the reference's PCRD bisection + T2 + markers on the host) and
+    configs[2] (HTJ2K lossless), several host threads with a compressor each; wall clock."""
+    try:
+        from grok_b200 import codestream as CS
+        from grok_b200 import tile as T
+        from oracle import oracle as O
+        img = [a >> 4 for a in synth_frame(WORKLOADS["j2k97"])]
+        pins = [T.PinnedArray((H, W), np.int32) for _ in range(NCOMP)]
+        for p_, b in zip(pins, img):
+            p_.array[:] = b
+        planes = [p_.array for p_ in pins]
+        out = {}
+        nthreads = max(2, min(16, os.cpu_count() or 2))
+        for name, kw, nthr in (("dci4k_97_mq_cblk32_rate_cinema4k", dict(reversible=False, cblk=(32, 32),
+                                                                       rate=W * H * 3 * 1.5 / 1302083.0), nthreads),
+                               ("ht_lossless_cblk64", dict(reversible=True, ht=True, cblk=(64, 64)), min(8, nthreads))):
+            zs = [CS.Compressor(W, H, NCOMP, 12, numres=NUMRES, comment="Created by Grok     version 9.2.0", **kw)
+                  for _ in range(nthr)]
+            first = [z.encode(planes) for z in zs]
+            per = 2
+            ths = [threading.Thread(target=lambda z=z: [z.encode(planes) for _ in range(per)]) for z in zs]
+            t0 = time.perf_counter()
+            for t in ths:
+                t.start()
+            for t in ths:
+                t.join()
+            dt = (time.perf_counter() - t0) / (per * nthr)
+            st = zs[0].stats()
+            for z in zs:
+                z.close()
+            leg = {"value": W * H / 1e6 / dt, "unit": "Mpixel/s", "ms_per_frame": dt * 1e3, "host_threads": nthr,
+                   "coded_bytes": int(first[0].size),
+                   "one_frame_alone_ms": {"device_incl_copies": st["device_ms"], "host_t2_and_rate_allocation": st["t2_ms"]}}
+            if O.have_ref():
+                try:
+                    O.ref_set_rate(kw.get("rate", 0))
+                    t0 = time.perf_counter()
+                    ref = O.ref_codec_encode(img, 12, 0 if kw.get("ht") else 1, ht=bool(kw.get("ht")), numres=NUMRES,
+                                             cblk=kw["cblk"], threads=os.cpu_count())
+                    ct = time.perf_counter() - t0
+                finally:
+                    O.ref_set_rate(0)
+                leg["parity"] = {"byte_identical_to_stock_encoder": bool(ref.size == first[0].size and
+                                                                         np.array_equal(ref, first[0]))}
+                leg["cpu_baseline"] = {"value": W * H / 1e6 / ct, "unit": "Mpixel/s", "cores": os.cpu_count(),
+                                       "kind": "reference", "sample": "one frame, stock encoder, memory stream, %.0f ms" % (ct * 1e3)}
+                if not leg["parity"]["byte_identical_to_stock_encoder"]:
+                    raise SystemExit("bench.py: PARITY FAILURE: encode leg %s differs from the stock encoder" % name)
+            out[name] = leg
+        return out
+    except SystemExit:
+        raise
+    except Exception as e:  # extra keys only
+        return {"error": str(e)[:200]}
 
 
 def run_ours(args, wl):
@@ -498,16 +587,24 @@ def run_ours(args, wl):
             pl = plugin_legs(second, args)
             if pl:
                 line["ht"].update(pl)
+    if world == 1 and not args.no_encode:
+        line["encode"] = encode_legs(args)
     if world == 1 and not args.no_cpu_baseline and O.have_ref():
         threads = os.cpu_count() or 1
         v, dt = cpu_reference_decode(codestream(wl), 3, 1, threads)
         line["cpu_baseline"] = {"value": v, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
                                 "sample": "whole frame x3: stock grk decompress (public C API, memory stream, markers "
                                           "+ T2 + T1 + wavelet + MCT), %.0f ms/frame" % (dt * 1e3)}
+        cli = cli_timings(wl)
+        if cli:
+            line["cpu_baseline"]["cli"] = cli
         if second:
             v, dt = cpu_reference_decode(codestream(second), 3, 1, threads)
             line["ht"]["cpu_baseline"] = {"value": v, "unit": "Mpixel/s", "cores": threads, "kind": "reference",
                                           "sample": "whole frame x3, %.0f ms/frame" % (dt * 1e3)}
+            cli = cli_timings(second)
+            if cli:
+                line["ht"]["cpu_baseline"]["cli"] = cli
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
@@ -523,6 +620,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-plugin", action="store_true", help="skip the grk_plugin_* legs (N = 1 extras)")
     ap.add_argument("--no-ht", action="store_true", help="skip the configs[2] sub-line")
+    ap.add_argument("--no-encode", action="store_true", help="skip the encode legs (N = 1 extras)")
     ap.add_argument("--workload", default="j2k97", choices=["j2k97", "ht"])
     ap.add_argument("--inflight", type=int, default=None,
                     help="frames in flight on the e2e leg (default: 4 for the MQ workload, whose kernel tails "

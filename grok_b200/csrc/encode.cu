@@ -62,6 +62,22 @@ struct EncState
 			cudaStreamDestroy(stream);
 		stream = nullptr;
 	}
+	// the per-thread state of grkb_t1_encode_host goes with its thread (release() is idempotent; the
+	// encoder objects release theirs in grkb_encoder_destroy)
+	~EncState()
+	{
+		if(device >= 0 && (stream || blocks.p))
+		{
+			int cur = -1;
+			if(cudaGetDevice(&cur) == cudaSuccess && cudaSetDevice(device) == cudaSuccess)
+			{
+				release();
+				if(cur >= 0)
+					cudaSetDevice(cur);
+			}
+			cudaGetLastError();
+		}
+	}
 };
 
 constexpr uint32_t SLOT_LEAD = 16;
@@ -450,6 +466,18 @@ static int submit_any(grkb_encoder* e, const int32_t* const* image, uint32_t str
 		return -1;
 	e->have_last = false;
 	e->pending = true;
+	// a tile counts as in flight only once everything is enqueued: any early return below gives the
+	// encoder back
+	struct Guard
+	{
+		grkb_encoder* e;
+		bool ok = false;
+		~Guard()
+		{
+			if(!ok)
+				e->pending = false;
+		}
+	} guard{e};
 	e->p_nblocks = nblocks;
 	e->p_coded = coded;
 	e->p_passes = passes;
@@ -457,7 +485,10 @@ static int submit_any(grkb_encoder* e, const int32_t* const* image, uint32_t str
 	e->p_cap = cap;
 	e->h_total[0] = e->h_total[1] = 0;
 	if(nblocks == 0)
+	{
+		guard.ok = true;
 		return 0;
+	}
 	if(e->st.blocks.reserve((size_t)nblocks * sizeof(grkb_enc_cblk)) ||
 	   e->st.packed.reserve(cap ? cap : 16))
 	{
@@ -492,6 +523,7 @@ static int submit_any(grkb_encoder* e, const int32_t* const* image, uint32_t str
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(coded, l.coded, (size_t)nblocks * sizeof(grkb_coded),
 									cudaMemcpyDeviceToHost, s));
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(e->h_total, l.packed_used, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+	guard.ok = true;
 	return 0;
 }
 
