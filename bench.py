@@ -362,7 +362,83 @@ def plugin_legs(wl, args):
         return {"e2e_plugin": {"value": None, "error": str(e)[:200]}}
 
 
-def encode_legs(args):
+T8K, TILE8K = 8192, 1024
+
+
+def frame8k():
+    """BASELINE configs[3] input: 8192x8192x3 16-bit, built from one 2048x2048 synthetic field repeated
+    with a different shift per 2048-block (a full-size synth costs 25 s)"""
+    import synth as Hh
+    base = Hh.synth_image(2048, 2048, NCOMP, 16, 8192)
+    out = []
+    for c, p in enumerate(base):
+        rows = [np.concatenate([np.roll(p, (97 * (i + 4 * j + c), 31 * (i + j)), axis=(0, 1)) ^ (i * 257 + j)
+                                for i in range(4)], axis=1) for j in range(4)]
+        out.append(np.ascontiguousarray(np.concatenate(rows, axis=0)).astype(np.int32))
+    return out
+
+
+def codestream8k():
+    from oracle import oracle as O
+    wl = dict(prec=16, ht=True)
+    p = cache_path("cs8k", wl)
+    if os.path.exists(p):
+        return np.load(p)["cs"]
+    if not O.have_ref():
+        return None
+    t = time.time()
+    cs = O.ref_codec_encode(frame8k(), 16, 0, ht=True, numres=NUMRES, cblk=(64, 64), tile=(TILE8K, TILE8K),
+                            threads=os.cpu_count())
+    np.savez(p + ".tmp.npz", cs=cs)
+    os.replace(p + ".tmp.npz", p)
+    log("[bench] 8192x8192 tiled HTJ2K codestream written in %.1f s: %.1f MB" % (time.time() - t, cs.size / 1e6))
+    return cs
+
+
+def tiled_leg(args, local, rank, world, barrier):
+    """BASELINE configs[3]: 8192x8192 16-bit RGB HTJ2K in 64 tiles of 1024x1024, tile t on rank t mod N
+    (grkb_decompress_submit_tiles, no collective); codestream bytes in page-locked host memory in, this
+    rank's tiles as int32 rectangles of a page-locked image out, own T2 inside.  Returns this rank's
+    milliseconds per image (the ranks work on the same image: strong scaling)."""
+    from grok_b200 import codestream as CS
+    from grok_b200 import tile as T
+    cs_arr = codestream8k()
+    if cs_arr is None:
+        return None
+    pin = T.PinnedArray((cs_arr.size + 16,), np.uint8)
+    pin.array[:cs_arr.size] = cs_arr
+    cs = pin.array[:cs_arr.size]
+    out = [T.PinnedArray((T8K, T8K), np.int32).array for _ in range(NCOMP)]
+    dz = CS.Decompressor(local, slots=4)
+    steps = max(3, args.steps // 4)
+    for _ in range(2):
+        dz.submit_tiles(cs, out, rank, world)
+        dz.wait()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        dz.submit_tiles(cs, out, rank, world)
+        dz.wait()
+    ms = (time.perf_counter() - t0) * 1e3 / steps
+    barrier()
+    res = {"ms": ms, "rejected": dz.rejected, "tiles_this_rank": dz.stats()["tiles"], "coded_bytes": int(cs_arr.size)}
+    if rank == 0:
+        # lossless: this rank's tiles must be the image
+        img = frame8k()
+        nt = T8K // TILE8K
+        ok = True
+        for t in range(rank, nt * nt, world):
+            y, x = (t // nt) * TILE8K, (t % nt) * TILE8K
+            ok = ok and all(np.array_equal(out[c][y:y + TILE8K, x:x + TILE8K], img[c][y:y + TILE8K, x:x + TILE8K])
+                            for c in range(NCOMP))
+        res["parity_ok"] = bool(ok)
+        if not ok:
+            raise SystemExit("bench.py: PARITY FAILURE on the tiled 8192x8192 leg")
+    dz.close()
+    return res
+
+
+def encode_legs(args, local=0, world=1):
     """N = 1 extras: the ENCODE side of the codestream door (grkb_compress) on the frames of BASELINE
     configs[4] (DCI-4K 12-bit 9/7, 32x32 blocks, one layer at the cinema-4K byte budget: T1 with
     distortions on the device, the reference's PCRD bisection + T2 + markers on the host) and
@@ -377,12 +453,12 @@ def encode_legs(args):
             p_.array[:] = b
         planes = [p_.array for p_ in pins]
         out = {}
-        nthreads = max(2, min(16, os.cpu_count() or 2))
+        nthreads = max(2, min(16, (os.cpu_count() or 2) // world))
         for name, kw, nthr in (("dci4k_97_mq_cblk32_rate_cinema4k", dict(reversible=False, cblk=(32, 32),
                                                                        rate=W * H * 3 * 1.5 / 1302083.0), nthreads),
                                ("ht_lossless_cblk64", dict(reversible=True, ht=True, cblk=(64, 64)), min(8, nthreads))):
-            zs = [CS.Compressor(W, H, NCOMP, 12, numres=NUMRES, comment="Created by Grok     version 9.2.0", **kw)
-                  for _ in range(nthr)]
+            zs = [CS.Compressor(W, H, NCOMP, 12, numres=NUMRES, comment="Created by Grok     version 9.2.0", device=local,
+                                **kw) for _ in range(nthr)]
             first = [z.encode(planes) for z in zs]
             per = 2
             ths = [threading.Thread(target=lambda z=z: [z.encode(planes) for _ in range(per)]) for z in zs]
@@ -398,7 +474,7 @@ def encode_legs(args):
             leg = {"value": W * H / 1e6 / dt, "unit": "Mpixel/s", "ms_per_frame": dt * 1e3, "host_threads": nthr,
                    "coded_bytes": int(first[0].size),
                    "one_frame_alone_ms": {"device_incl_copies": st["device_ms"], "host_t2_and_rate_allocation": st["t2_ms"]}}
-            if O.have_ref():
+            if O.have_ref() and local == 0:
                 try:
                     O.ref_set_rate(kw.get("rate", 0))
                     t0 = time.perf_counter()
@@ -450,6 +526,8 @@ def run_ours(args, wl):
         codestream(wl)
         if second:
             codestream(second)
+        if not args.no_tiled:
+            codestream8k()
     barrier()
     sampler = ClockSampler(local)
     main = measure(wl, args, local, barrier)
@@ -458,6 +536,11 @@ def run_ours(args, wl):
         a2 = argparse.Namespace(**vars(args))
         a2.steps = max(5, args.steps // 2)
         sub = measure(second, a2, local, barrier)
+    # ---- extras on every rank: configs[3] tile-sharded over the ranks, configs[4] / [2] encode frame-sharded
+    tiled = None if args.no_tiled else tiled_leg(args, local, rank, world, barrier)
+    barrier()
+    enc = None if args.no_encode else encode_legs(args, local, world)
+    barrier()
     # ---- the link, all ranks at once
     import ctypes as C
     barrier()
@@ -472,6 +555,9 @@ def run_ours(args, wl):
         vals += [sub["tm"]["total_ms"]] + [sub[k] for k in keys]
     link = [h2d.value, d2h.value, dup[0], dup[1]]
     all_clocks = [clocks]
+    tiled_ms = tiled["ms"] if tiled else 0.0
+    enc_names = [k for k in (enc or {}) if isinstance(enc[k], dict) and "value" in enc[k]]
+    enc_vals = [enc[k]["value"] for k in enc_names]
     if dist is not None:
         import torch
         t = torch.tensor(vals, dtype=torch.float64, device="cuda")
@@ -480,6 +566,12 @@ def run_ours(args, wl):
         t = torch.tensor(link, dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         link = [float(x) for x in t]
+        t = torch.tensor([tiled_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        tiled_ms = float(t[0])
+        t = torch.tensor(enc_vals + [0.0], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        enc_vals = [float(x) for x in t][:len(enc_names)]
         all_clocks = [None] * world
         dist.all_gather_object(all_clocks, clocks)
     if rank != 0:
@@ -587,8 +679,21 @@ def run_ours(args, wl):
             pl = plugin_legs(second, args)
             if pl:
                 line["ht"].update(pl)
-    if world == 1 and not args.no_encode:
-        line["encode"] = encode_legs(args)
+    if enc is not None:
+        for k, v in zip(enc_names, enc_vals):
+            enc[k]["value_this_rank"] = enc[k]["value"]
+            enc[k]["value"] = v
+        enc["what"] = ("grkb_compress, frames sharded over the ranks (weak scaling): value = sum over ranks; host threads "
+                       "per rank = cores / ranks")
+        line["encode"] = enc
+    if tiled:
+        line["tiled_8k"] = {"value": T8K * T8K / 1e6 / (tiled_ms * 1e-3), "unit": "Mpixel/s", "ms_per_image": tiled_ms,
+                            "scaling": "strong: the 64 tiles of one image over the ranks, tile t on rank t mod N",
+                            "config": {"workload": "htj2k_decode_8192x8192_rgb16_53_rct_lossless_5lvl_cblk64_tiles1024",
+                                       "tiles": 64, "coded_bytes": tiled["coded_bytes"]},
+                            "boundary": "grkb_decompress_submit_tiles: codestream bytes in, int32 rectangles out, own T2 "
+                                        "inside; max over ranks", "parity_ok": tiled.get("parity_ok"),
+                            "d2h_bytes_per_image": T8K * T8K * NCOMP * 4}
     if world == 1 and not args.no_cpu_baseline and O.have_ref():
         threads = os.cpu_count() or 1
         v, dt = cpu_reference_decode(codestream(wl), 3, 1, threads)
@@ -620,7 +725,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-plugin", action="store_true", help="skip the grk_plugin_* legs (N = 1 extras)")
     ap.add_argument("--no-ht", action="store_true", help="skip the configs[2] sub-line")
-    ap.add_argument("--no-encode", action="store_true", help="skip the encode legs (N = 1 extras)")
+    ap.add_argument("--no-encode", action="store_true", help="skip the encode legs")
+    ap.add_argument("--no-tiled", action="store_true", help="skip the configs[3] tile-sharded leg")
     ap.add_argument("--workload", default="j2k97", choices=["j2k97", "ht"])
     ap.add_argument("--inflight", type=int, default=None,
                     help="frames in flight on the e2e leg (default: 4 for the MQ workload, whose kernel tails "

@@ -39,6 +39,7 @@ lib.grkb_decompressor_destroy.argtypes = [_vp]
 lib.grkb_decompressor_destroy.restype = None
 lib.grkb_decompress_submit.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _vp, _u32]
 lib.grkb_decompress_submit_window.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _u32, _u32, _u32, _u32, _vp, _u32]
+lib.grkb_decompress_submit_tiles.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _u32, _u32, _vp, _u32]
 lib.grkb_decompress_submit_packed.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _vp, _u32, C.c_size_t]
 lib.grkb_decompress_wait.argtypes = [_vp, C.POINTER(_u32)]
 lib.grkb_decompress.argtypes = [_vp, _vp, C.c_size_t, _u32, _u32, _vp, _u32, C.POINTER(_u32)]
@@ -128,6 +129,14 @@ class Decompressor:
         self._keep = (data, out, ptrs)
         check(lib.grkb_decompress_submit(self.h, data.ctypes.data, data.size, reduce, max_layers, ptrs,
                                          out[0].strides[0] // 4), "grkb_decompress_submit")
+
+    def submit_tiles(self, data, out, first_tile, tile_step, reduce=0, max_layers=0):
+        """tile sharding: only tiles first_tile, first_tile + tile_step, ... (rank, world of a multi-GPU decode)"""
+        nc = len(out)
+        ptrs = (_vp * nc)(*[o.ctypes.data for o in out])
+        self._keep = (data, out, ptrs)
+        check(lib.grkb_decompress_submit_tiles(self.h, data.ctypes.data, data.size, reduce, max_layers, first_tile,
+                                               tile_step, ptrs, out[0].strides[0] // 4), "grkb_decompress_submit_tiles")
 
     def decode_window(self, data, window, reduce=0, max_layers=0):
         """windowed decode: window = (x0, y0, x1, y1) relative to the image origin; returns int32 planes

@@ -209,7 +209,7 @@ int drain(grkb_decompressor* d, Slot& s)
 // or null for the whole image
 int submit_any(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce, uint32_t max_layers,
 			   int32_t* const* planes, uint32_t stride, void* out, uint32_t format, size_t row_bytes,
-			   const uint32_t* win = nullptr)
+			   const uint32_t* win = nullptr, uint32_t first_tile = 0, uint32_t tile_step = 1)
 {
 	if(!d || !data || (!planes && !out))
 	{
@@ -297,6 +297,8 @@ int submit_any(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t r
 	{
 		if(cs.tiles[t].parts.empty())
 			continue; // no data for this tile: its rectangle is left as the caller gave it
+		if(t < first_tile || (t - first_tile) % tile_step != 0)
+			continue; // another rank's tile (tile t -> GPU t mod G)
 		Slot& s = d->slots[next];
 		next = (next + 1) % (uint32_t)d->slots.size();
 		if(drain(d, s))
@@ -414,6 +416,18 @@ int grkb_decompress_submit_window(grkb_decompressor* d, const uint8_t* data, siz
 {
 	const uint32_t win[4] = {wx0, wy0, wx1, wy1};
 	return submit_any(d, data, len, reduce, max_layers, planes, stride, nullptr, 0, 0, win);
+}
+
+int grkb_decompress_submit_tiles(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,
+								 uint32_t max_layers, uint32_t first_tile, uint32_t tile_step, int32_t* const* planes,
+								 uint32_t stride)
+{
+	if(tile_step == 0)
+	{
+		grkb_set_error("grkb_decompress_submit_tiles: tile_step must be at least 1");
+		return -1;
+	}
+	return submit_any(d, data, len, reduce, max_layers, planes, stride, nullptr, 0, 0, nullptr, first_tile, tile_step);
 }
 
 int grkb_decompress_submit_packed(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,

@@ -506,6 +506,13 @@ int grkb_decompress_submit(grkb_decompressor* d, const uint8_t* data, size_t len
 int grkb_decompress_submit_window(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,
 								  uint32_t max_layers, uint32_t wx0, uint32_t wy0, uint32_t wx1, uint32_t wy1,
 								  int32_t* const* planes, uint32_t stride);
+/* Tile sharding (tile t -> GPU t mod G, no collective): decodes tiles first_tile,
+ * first_tile + tile_step, ... only; the other tiles' rectangles of `planes` are left alone.  Each
+ * rank of a multi-GPU decode calls it with its own decompressor, (rank, world) and the same
+ * codestream. */
+int grkb_decompress_submit_tiles(grkb_decompressor* d, const uint8_t* data, size_t len, uint32_t reduce,
+								 uint32_t max_layers, uint32_t first_tile, uint32_t tile_step, int32_t* const* planes,
+								 uint32_t stride);
 /* The same with the samples narrowed on the device (GRKB_SAMPLES_16 / _8, planar or interleaved;
  * opt-in): `out` holds grkb_samples_size(format, H, numcomps, row_bytes) bytes of the
  * whole (reduced) image. */

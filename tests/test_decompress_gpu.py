@@ -198,6 +198,38 @@ def test_configs2_ht_4k_codestream(dec, frame16):
         assert np.array_equal(got[c], want[c])
 
 
+@pytest.mark.parametrize("world", [2, 3])
+def test_tile_subsets_compose_the_full_decode(dec, world):
+    """SURVEY 8e at the codestream door: decompressor r takes tiles r, r + N, ... of the same bytes
+    (grkb_decompress_submit_tiles); the rectangles are disjoint and together they are the stock
+    decoder's image; the rule is grok_b200.shard.shard_units' (the gloo test's)"""
+    from grok_b200 import shard
+    img = H.synth_image(250, 190, 3, 8, seed=3)
+    cs = _encode(img, 8, 0, "off=3:5;torg=1:2", tile=(96, 64), numres=4, cblk=(32, 32))
+    want = _ref_decode(cs, 3)
+    c = CS.Codestream(cs)
+    ntiles = c.num_tiles
+    c.close()
+    tiles = shard.tile_grid(3, 5, 253, 195, 1, 2, 96, 64)
+    assert len(tiles) == ntiles
+    full = [np.zeros_like(p) for p in want]
+    for r in range(world):
+        out = [np.full(p.shape, -7, np.int32) for p in want]
+        dec.submit_tiles(cs, out, r, world)
+        dec.wait()
+        mine = set(shard.shard_units(ntiles, r, world))
+        for t, (x0, y0, x1, y1) in enumerate(tiles):
+            for k in range(3):
+                rect = out[k][y0 - 5:y1 - 5, x0 - 3:x1 - 3]
+                if t in mine:
+                    assert np.array_equal(rect, want[k][y0 - 5:y1 - 5, x0 - 3:x1 - 3]), (r, t)
+                    full[k][y0 - 5:y1 - 5, x0 - 3:x1 - 3] = rect
+                else:
+                    assert np.all(rect == -7), (r, t)  # not this rank's tile: untouched
+    for k in range(3):
+        assert np.array_equal(full[k], want[k])
+
+
 def test_configs3_8k_tiled_ht_codestream(dec, frame8k):
     """BASELINE configs[3]: 8192x8192 16-bit RGB HTJ2K in 64 tiles of 1024x1024, all tiles through
     one decompressor (three tile decoders in flight, one geometry), == stock decoder == image"""
