@@ -247,17 +247,6 @@ static __device__ __forceinline__ uint32_t mq_decode(Mq& q, uint32_t cxs, uint32
 
 constexpr uint32_t CX4_MAG = T1_CTX_MAG * 4, CX4_AGG = T1_CTX_AGG * 4, CX4_UNI = T1_CTX_UNI * 4;
 
-static __device__ __forceinline__ void reset_states(uint32_t cxs, uint32_t lane)
-{
-	// mqc_resetstates, mqc_dec.cpp:121-130
-	if(lane < T1_NCTX)
-	{
-		const uint32_t st = lane == T1_CTX_UNI ? 46u << 1 : lane == T1_CTX_AGG ? 3u << 1 : lane == T1_CTX_ZC ? 4u << 1 : 0u;
-		sts32(cxs + lane * 4, c_dec.mq[st]);
-	}
-	__syncwarp();
-}
-
 struct Blk
 {
 	uint32_t* fl; // state words, (w+2) x (nstripes+2)
@@ -266,8 +255,43 @@ struct Blk
 	uint32_t w, h, fs; // fs = w + 2
 	uint32_t zc; // offset of this band orientation's zero-coding table in c_dec.zc
 	bool vsc;
-	uint32_t lane;
+	uint32_t lane; // lane within the group that owns the block (LW lanes: the whole warp or half of it)
+	uint32_t gmask, gsh; // the group's lanes in the warp, and the first of them
 };
+
+// warp primitives restricted to the LW lanes that share a code block
+template<uint32_t LW>
+static __device__ __forceinline__ uint32_t g_ballot(const Blk& b, bool pred)
+{
+	if(LW == 32)
+		return __ballot_sync(FULL, pred);
+	return (__ballot_sync(b.gmask, pred) & b.gmask) >> b.gsh;
+}
+template<uint32_t LW>
+static __device__ __forceinline__ uint32_t g_shfl(const Blk& b, uint32_t v, uint32_t col)
+{
+	return LW == 32 ? __shfl_sync(FULL, v, col) : __shfl_sync(b.gmask, v, col, LW);
+}
+template<uint32_t LW>
+static __device__ __forceinline__ void g_sync(const Blk& b)
+{
+	if(LW == 32)
+		__syncwarp();
+	else
+		__syncwarp(b.gmask);
+}
+
+template<uint32_t LW>
+static __device__ __forceinline__ void reset_states(const Blk& b, uint32_t cxs)
+{
+	// mqc_resetstates, mqc_dec.cpp:121-130
+	for(uint32_t i = b.lane; i < T1_NCTX; i += LW)
+	{
+		const uint32_t st = i == T1_CTX_UNI ? 46u << 1 : i == T1_CTX_AGG ? 3u << 1 : i == T1_CTX_ZC ? 4u << 1 : 0u;
+		sts32(cxs + i * 4, c_dec.mq[st]);
+	}
+	g_sync<LW>(b);
+}
 
 // per-row 4-bit summaries of a state word
 static __device__ __forceinline__ uint32_t sig4(uint32_t f)
@@ -298,7 +322,7 @@ static inline uint32_t sc_index_tables(uint32_t j)
 		   (((j >> 4) & 1u) << 4) | (((j >> 6) & 1u) << 5) | ((j & 1u) << 6) | (((j >> 2) & 1u) << 7);
 }
 
-// One 32-column segment of a stripe: lane l holds the state word of column x0 + l in `f`.
+// One LW-column segment of a stripe: lane l holds the state word of column x0 + l in `f`.
 struct Seg
 {
 	uint32_t* fseg; // state word of the segment's first column (this stripe)
@@ -306,23 +330,25 @@ struct Seg
 };
 
 // state words of the west / east neighbours of segment column `col`, as of now
-static __device__ __forceinline__ void west_east(const Seg& g, uint32_t f, uint32_t col, uint32_t& fw,
-												   uint32_t& fe)
+template<uint32_t LW>
+static __device__ __forceinline__ void west_east(const Blk& b, const Seg& g, uint32_t f, uint32_t col,
+												   uint32_t& fw, uint32_t& fe)
 {
-	fw = __shfl_sync(FULL, f, (col + 31u) & 31u);
-	fe = __shfl_sync(FULL, f, (col + 1u) & 31u);
-	if(col == 0 || col == 31)
+	fw = g_shfl<LW>(b, f, (col + LW - 1u) & (LW - 1u));
+	fe = g_shfl<LW>(b, f, (col + 1u) & (LW - 1u));
+	if(col == 0 || col == LW - 1)
 	{
-		__syncwarp(); // the word may have been updated by another lane
+		g_sync<LW>(b); // the word may have been updated by another lane
 		if(col == 0)
 			fw = g.fseg[-1];
 		else
-			fe = g.fseg[32];
+			fe = g.fseg[LW];
 	}
 }
 
 // sample (segment column col, stripe row r) became significant with sign sgn and value val:
 // propagate to the neighbours (update_flags_macro, T1.cpp:209-233).  All lanes call this.
+template<uint32_t LW>
 static __device__ __forceinline__ void mark_significant(const Blk& b, const Seg& g, uint32_t& f,
 														 uint32_t col, uint32_t r, uint32_t sgn,
 														 int32_t val)
@@ -337,18 +363,18 @@ static __device__ __forceinline__ void mark_significant(const Blk& b, const Seg&
 	if(lane == col)
 		g.dseg[lane + r * b.ds] = val;
 	// columns outside the segment are in shared memory
-	if(col == 0 || col == 31)
+	if(col == 0 || col == LW - 1)
 	{
 		if(lane == col)
 		{
-			uint32_t* o = col ? g.fseg + 32 : g.fseg - 1;
+			uint32_t* o = col ? g.fseg + LW : g.fseg - 1;
 			*o |= (col ? 1u : 4u) << sh;
 		}
 	}
 	// row 4 of the stripe above / row -1 of the stripe below: lanes 0..2 take columns col-1..col+1
 	if((r == 0 && !b.vsc) || r == 3)
 	{
-		__syncwarp(); // successive events update overlapping words from different lanes
+		g_sync<LW>(b); // successive events update overlapping words from different lanes
 		if(lane < 3)
 		{
 			uint32_t* n = (r ? g.fseg + b.fs : g.fseg - b.fs) + col + lane - 1;
@@ -360,7 +386,7 @@ static __device__ __forceinline__ void mark_significant(const Blk& b, const Seg&
 }
 
 // sign of a newly significant sample (T1.cpp dec_*pass "sign" step) + the bookkeeping
-template<bool RAW>
+template<uint32_t LW, bool RAW>
 static __device__ __forceinline__ void code_sign(const Blk& b, const Seg& g, Mq& q, uint32_t cxs,
 												  uint32_t& f, uint32_t& fc,
 												  uint32_t col, uint32_t r, int32_t oph)
@@ -371,15 +397,16 @@ static __device__ __forceinline__ void code_sign(const Blk& b, const Seg& g, Mq&
 	else
 	{
 		uint32_t fw, fe;
-		west_east(g, f, col, fw, fe);
+		west_east<LW>(b, g, f, col, fw, fe);
 		const uint32_t e = c_dec.sc[sc_index(fc, fw, fe, r)];
 		v = mq_decode(q, cxs, e & 0x7Fu) ^ (e >> 7);
 	}
-	mark_significant(b, g, f, col, r, v, v ? -oph : oph);
+	mark_significant<LW>(b, g, f, col, r, v, v ? -oph : oph);
 	fc |= T1_SIG_C(r) | (v << (18 + r + 1));
 }
 
 // dec_clnpass, T1.cpp:934-1093
+template<uint32_t LW>
 static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t cxs,
 									 int bpno_plus_one, bool segsym)
 {
@@ -387,23 +414,23 @@ static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t cxs,
 	for(uint32_t k = 0, s = 0; k < b.h; k += 4, ++s)
 	{
 		const uint32_t rows = min(4u, b.h - k), rowmask = (1u << rows) - 1u;
-		for(uint32_t x0 = 0; x0 < b.w; x0 += 32)
+		for(uint32_t x0 = 0; x0 < b.w; x0 += LW)
 		{
 			Seg g;
 			g.fseg = b.fl + (s + 1) * b.fs + 1 + x0;
 			g.dseg = b.data + (size_t)k * b.ds + x0;
 			const bool act = x0 + b.lane < b.w;
-			__syncwarp();
+			g_sync<LW>(b);
 			uint32_t f = act ? g.fseg[b.lane] : 0u;
 			// rows still to code: not significant, not visited in this bit-plane
 			const uint32_t todo = act ? ~(sig4(f) | (f >> 24)) & rowmask : 0u;
-			uint32_t colmask = __ballot_sync(FULL, todo != 0);
+			uint32_t colmask = g_ballot<LW>(b, todo != 0);
 			while(colmask)
 			{
 				const uint32_t col = __ffs(colmask) - 1;
 				colmask &= colmask - 1;
-				uint32_t m = __shfl_sync(FULL, todo, col);
-				uint32_t fc = __shfl_sync(FULL, f, col);
+				uint32_t m = g_shfl<LW>(b, todo, col);
+				uint32_t fc = g_shfl<LW>(b, f, col);
 				bool sign_only = false;
 				if(rows == 4 && fc == 0)
 				{
@@ -421,7 +448,7 @@ static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t cxs,
 					if(!sign_only && !mq_decode(q, cxs, c_dec.zc[b.zc + ((fc >> (3 * r)) & T1_NEIGH)]))
 						continue;
 					sign_only = false;
-					code_sign<false>(b, g, q, cxs, f, fc, col, r, oph);
+					code_sign<LW, false>(b, g, q, cxs, f, fc, col, r, oph);
 				}
 			}
 			if(act)
@@ -437,7 +464,7 @@ static __device__ void cleanup_pass(const Blk& b, Mq& q, uint32_t cxs,
 }
 
 // dec_sigpass_mqc / dec_sigpass_raw, T1.cpp:1094-1245
-template<bool RAW>
+template<uint32_t LW, bool RAW>
 static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t cxs,
 								 int bpno_plus_one)
 {
@@ -445,26 +472,26 @@ static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t cxs,
 	for(uint32_t k = 0, s = 0; k < b.h; k += 4, ++s)
 	{
 		const uint32_t rows = min(4u, b.h - k), rowmask = (1u << rows) - 1u;
-		for(uint32_t x0 = 0; x0 < b.w; x0 += 32)
+		for(uint32_t x0 = 0; x0 < b.w; x0 += LW)
 		{
 			Seg g;
 			g.fseg = b.fl + (s + 1) * b.fs + 1 + x0;
 			g.dseg = b.data + (size_t)k * b.ds + x0;
 			const bool act = x0 + b.lane < b.w;
-			__syncwarp();
+			g_sync<LW>(b);
 			uint32_t f = act ? g.fseg[b.lane] : 0u;
 			// free = not significant and not visited; a free row is coded in this pass as soon
 			// as it has a significant neighbour -- which can happen during the pass
 			const uint32_t fr = act ? ~(sig4(f) | (f >> 24)) & rowmask : 0u;
 			uint32_t cand = fr & nz4(f);
-			uint32_t colmask = __ballot_sync(FULL, cand != 0);
+			uint32_t colmask = g_ballot<LW>(b, cand != 0);
 			while(colmask)
 			{
 				const uint32_t col = __ffs(colmask) - 1;
 				colmask &= colmask - 1;
-				uint32_t m = __shfl_sync(FULL, cand, col);
-				const uint32_t frc = __shfl_sync(FULL, fr, col);
-				uint32_t fc = __shfl_sync(FULL, f, col);
+				uint32_t m = g_shfl<LW>(b, cand, col);
+				const uint32_t frc = g_shfl<LW>(b, fr, col);
+				uint32_t fc = g_shfl<LW>(b, f, col);
 				uint32_t pi = 0, grown = 0;
 				while(m)
 				{
@@ -475,7 +502,7 @@ static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t cxs,
 											 : mq_decode(q, cxs, c_dec.zc[b.zc + ((fc >> (3 * r)) & T1_NEIGH)]);
 					if(!bit)
 						continue;
-					code_sign<RAW>(b, g, q, cxs, f, fc, col, r, oph);
+					code_sign<LW, RAW>(b, g, q, cxs, f, fc, col, r, oph);
 					m |= (2u << r) & frc; // the row below becomes a candidate
 					grown |= (7u << r) >> 1; // and rows r-1..r+1 of the next column
 				}
@@ -485,7 +512,7 @@ static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t cxs,
 				{
 					if(b.lane == col + 1)
 						cand |= grown & fr;
-					colmask |= __ballot_sync(FULL, cand != 0) & (2u << col);
+					colmask |= g_ballot<LW>(b, cand != 0) & (2u << col);
 				}
 			}
 			if(act)
@@ -495,14 +522,14 @@ static __device__ void sig_pass(const Blk& b, Mq& q, uint32_t cxs,
 }
 
 constexpr uint32_t CXS_LIST = 128; // byte offset of the refinement list behind the context words
-constexpr uint32_t CXS_BYTES = CXS_LIST + 128 * 2; // 19 context words (padded) + 128 list entries
+constexpr uint32_t CXS_BYTES = CXS_LIST + 128 * 2; // 19 context words (padded) + 4 x LW list entries
 
 // dec_refpass_mqc / dec_refpass_raw, T1.cpp:1246-1364.  Everything about this pass is known
 // before it starts -- which samples are refined (significant before this bit-plane) and with
 // which context -- so the lanes write the contexts of a segment's decisions, in scan order, to a
 // list; the decision chain walks the list and leaves the decoded bits in it; the lanes then
 // apply them to their own columns.
-template<bool RAW>
+template<uint32_t LW, bool RAW>
 static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t cxs,
 								 int bpno_plus_one)
 {
@@ -511,19 +538,19 @@ static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t cxs,
 	for(uint32_t k = 0, s = 0; k < b.h; k += 4, ++s)
 	{
 		const uint32_t rows = min(4u, b.h - k), rowmask = (1u << rows) - 1u;
-		for(uint32_t x0 = 0; x0 < b.w; x0 += 32)
+		for(uint32_t x0 = 0; x0 < b.w; x0 += LW)
 		{
 			Seg g;
 			g.fseg = b.fl + (s + 1) * b.fs + 1 + x0;
 			g.dseg = b.data + (size_t)k * b.ds + x0;
 			const bool act = x0 + b.lane < b.w;
-			__syncwarp();
+			g_sync<LW>(b);
 			const uint32_t f = act ? g.fseg[b.lane] : 0u;
 			const uint32_t todo = sig4(f) & ~(f >> 24) & rowmask;
 			// position of this column's first decision = decisions of the columns before it
 			const uint32_t cnt = __popc(todo);
-			const uint32_t b0 = __ballot_sync(FULL, cnt & 1u), b1 = __ballot_sync(FULL, cnt & 2u),
-						   b2 = __ballot_sync(FULL, cnt & 4u);
+			const uint32_t b0 = g_ballot<LW>(b, cnt & 1u), b1 = g_ballot<LW>(b, cnt & 2u),
+						   b2 = g_ballot<LW>(b, cnt & 4u);
 			const uint32_t total = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2);
 			if(total == 0)
 				continue;
@@ -539,11 +566,11 @@ static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t cxs,
 						sts16(at, (f & T1_MU(r)) ? CX4_MAG + 8 : ((nz >> r) & 1u) ? CX4_MAG + 4 : CX4_MAG);
 						at += 2;
 					}
-				__syncwarp();
+				g_sync<LW>(b);
 			}
 			for(uint32_t at = list, end = list + 2 * total; at != end; at += 2)
 				sts16(at, RAW ? raw_decode(q) : mq_decode(q, cxs, lds16(at)));
-			__syncwarp();
+			g_sync<LW>(b);
 			if(todo)
 			{
 				uint32_t at = mine;
@@ -562,27 +589,43 @@ static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t cxs,
 	}
 }
 
-constexpr int MQ_MAX_THREADS = 256; // up to 8 warps = 8 code blocks in flight per CTA
+// up to 8 warps per CTA, four CTAs per SM: 63 registers.  (More registers per thread save 12 % of the
+// instructions and lose more than that to the lower occupancy: (256,3) measured 537 vs 578 MP/s.)
 
-__global__ void __launch_bounds__(MQ_MAX_THREADS, 4)
+// LW = 32: one code block per warp.  LW = 16: each half of a warp owns a block and the two chains
+// share the warp's instruction issue wherever their control flow agrees (both halves start their
+// blocks together, so they are always in the same kind of pass).
+template<uint32_t LW>
+__global__ void __launch_bounds__(256, 4)
 	t1_mq_decode_kernel(const T1Launch l)
 {
+	constexpr uint32_t G = 32 / LW;
 	extern __shared__ __align__(16) uint8_t smem[];
-	uint8_t* warp_base = smem;
-	const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-	const size_t per_warp = CXS_BYTES + (size_t)l.max_flag_words * 4;
-	uint8_t* mine = warp_base + warp * per_warp;
+	const uint32_t warp = threadIdx.x >> 5, wlane = threadIdx.x & 31;
+	const uint32_t grp = wlane / LW, lane = wlane % LW;
+	const size_t per_slot = CXS_BYTES + (size_t)l.max_flag_words * 4;
+	uint8_t* mine = smem + (warp * G + grp) * per_slot;
 	const uint32_t cxs = (uint32_t)__cvta_generic_to_shared(mine); // context words + refinement list
 	uint32_t* fl = reinterpret_cast<uint32_t*>(mine + CXS_BYTES);
+	Blk b;
+	b.fl = fl;
+	b.ds = l.stride;
+	b.lane = lane;
+	b.gsh = grp * LW;
+	b.gmask = LW == 32 ? FULL : ((1u << LW) - 1u) << b.gsh;
 
 	for(;;)
 	{
+		__syncwarp(); // the groups of a warp start their blocks together
 		uint32_t item = 0;
-		if(lane == 0)
-			item = atomicAdd(l.counter, 1u);
+		if(wlane == 0)
+			item = atomicAdd(l.counter, G);
 		item = __shfl_sync(FULL, item, 0);
 		if(item >= l.nblocks)
 			break;
+		item += grp;
+		if(item >= l.nblocks)
+			continue;
 		const uint32_t bi = l.order ? l.order[item] : item;
 		const grkb_cblk cb = l.blocks[bi];
 		if(cb.cblk_sty & GRKB_CBLKSTY_HT)
@@ -594,24 +637,20 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS, 4)
 		const bool coded = cb.numsegs != 0 && !bad;
 		if(coded)
 		{
-			for(uint32_t i = lane; i < nfl; i += 32)
+			for(uint32_t i = lane; i < nfl; i += LW)
 				fl[i] = 0;
 			for(uint32_t y = 0; y < h; ++y)
-				for(uint32_t x = lane; x < w; x += 32)
+				for(uint32_t x = lane; x < w; x += LW)
 					blk_data[(size_t)y * l.stride + x] = 0;
-			__syncwarp();
-			Blk b;
-			b.fl = fl;
+			g_sync<LW>(b);
 			b.data = blk_data;
-			b.ds = l.stride;
 			b.w = w;
 			b.h = h;
 			b.fs = fs;
 			b.zc = 512u * cb.orient;
 			b.vsc = (cb.cblk_sty & GRKB_CBLKSTY_VSC) != 0;
-			b.lane = lane;
 			Mq q;
-			reset_states(cxs, lane);
+			reset_states<LW>(b, cxs);
 			int bp1 = (int)cb.numbps;
 			uint32_t passtype = 2;
 			const uint8_t* p = l.bytes + cb.data_off;
@@ -630,23 +669,23 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS, 4)
 					if(passtype == 0)
 					{
 						if(raw)
-							sig_pass<true>(b, q, cxs, bp1);
+							sig_pass<LW, true>(b, q, cxs, bp1);
 						else
-							sig_pass<false>(b, q, cxs, bp1);
+							sig_pass<LW, false>(b, q, cxs, bp1);
 					}
 					else if(passtype == 1)
 					{
 						if(raw)
-							ref_pass<true>(b, q, cxs, bp1);
+							ref_pass<LW, true>(b, q, cxs, bp1);
 						else
-							ref_pass<false>(b, q, cxs, bp1);
+							ref_pass<LW, false>(b, q, cxs, bp1);
 					}
 					else
-						cleanup_pass(b, q, cxs, bp1, (cb.cblk_sty & GRKB_CBLKSTY_SEGSYM) != 0);
+						cleanup_pass<LW>(b, q, cxs, bp1, (cb.cblk_sty & GRKB_CBLKSTY_SEGSYM) != 0);
 					if((cb.cblk_sty & GRKB_CBLKSTY_RESET) && !raw)
 					{
-						__syncwarp();
-						reset_states(cxs, lane);
+						g_sync<LW>(b);
+						reset_states<LW>(b, cxs);
 					}
 					if(++passtype == 3)
 					{
@@ -656,7 +695,7 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS, 4)
 				}
 			}
 		}
-		__syncwarp();
+		g_sync<LW>(b);
 		if(bad && lane == 0)
 			atomicAdd(l.status, 1u);
 		// dequantise + store: ShiftFilter (/2, C truncation) or ScaleFilter (x stepsize/2),
@@ -665,7 +704,7 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS, 4)
 		for(uint32_t y = 0; y < h; ++y)
 		{
 			int32_t* dst = blk_data + (size_t)y * l.stride;
-			for(uint32_t x = lane; x < w; x += 32)
+			for(uint32_t x = lane; x < w; x += LW)
 			{
 				int32_t v = coded ? dst[x] : 0;
 				int32_t mag = abs(v);
@@ -680,7 +719,6 @@ __global__ void __launch_bounds__(MQ_MAX_THREADS, 4)
 					dst[x] = __float_as_int(__fmul_rn((float)v, cb.scale));
 			}
 		}
-		__syncwarp();
 	}
 }
 
@@ -740,8 +778,7 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 		grkb_set_error("t1: cannot upload coding tables");
 		return -1;
 	}
-	const size_t per_warp = CXS_BYTES + (size_t)l.max_flag_words * 4;
-	const size_t fixed = 0;
+	const size_t per_slot = CXS_BYTES + (size_t)l.max_flag_words * 4;
 	int dev = 0, sms = 148;
 	if(cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
 	{
@@ -749,52 +786,76 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 		return -1;
 	}
 	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-	// warps per CTA: whatever packs most code blocks into the 227 KB of an SM
-	static int max_warps_sm = -1;
-	if(max_warps_sm < 0)
+	// Lanes per code block.  16 (two blocks per warp, the halves sharing the instruction issue where
+	// their control flow agrees) executes 0.70x the warp instructions of 32 but needs twice the blocks
+	// in flight for the same number of warps: it wins when the launch has enough blocks to fill the
+	// SMs' shared memory with pairs one and a half times over (a 4K frame of 32x32 blocks: 606 -> 745
+	// MP/s), and loses on a single 4K frame of 64x64 blocks (6 480 chains for 9 472 slots: 15.3 ->
+	// 18.7 ms).  GRKB_T1_MQ_GROUP = 32 | 16 forces one.
+	// (read at every launch so that the tests can exercise both)
+	int force_lw = 0, max_warps_sm = 32;
 	{
-		const char* e = getenv("GRKB_T1_MQ_WARPS");
+		const char* e = getenv("GRKB_T1_MQ_GROUP");
+		force_lw = e ? (atoi(e) == 32 ? 32 : atoi(e) == 16 ? 16 : 0) : 0;
+		e = getenv("GRKB_T1_MQ_WARPS");
 		max_warps_sm = e ? atoi(e) : 32;
 		if(max_warps_sm < 1 || max_warps_sm > 64)
 			max_warps_sm = 32;
 	}
-	int best_nw = 0, best_total = 0;
-	for(int nw = 1; nw <= MQ_MAX_THREADS / 32; ++nw)
-	{
-		const size_t need = fixed + per_warp * nw;
-		if(need > 227 * 1024)
-			break;
-		int per_sm = (int)((227 * 1024) / (need + 1024));
-		if(per_sm > 32)
-			per_sm = 32;
-		if(nw * per_sm > max_warps_sm)
-			per_sm = max_warps_sm / nw;
-		if(nw * per_sm >= best_total)
+	// warps per CTA: whatever packs most code blocks into the 227 KB of an SM
+	auto pack = [&](int G, int& nw_out) {
+		int best_nw = 0, best_total = 0;
+		for(int nw = 1; nw <= 256 / 32; ++nw)
 		{
-			best_total = nw * per_sm;
-			best_nw = nw;
+			const size_t need = per_slot * G * nw;
+			if(need > 227 * 1024)
+				break;
+			int per_sm = (int)((227 * 1024) / (need + 1024));
+			if(per_sm > 32)
+				per_sm = 32;
+			if(nw * per_sm > max_warps_sm)
+				per_sm = max_warps_sm / nw;
+			if(nw * per_sm >= best_total)
+			{
+				best_total = nw * per_sm;
+				best_nw = nw;
+			}
 		}
-	}
+		nw_out = best_nw;
+		return best_total;
+	};
+	int nw16 = 0, nw32 = 0;
+	const int total16 = pack(2, nw16), total32 = pack(1, nw32);
+	int lw = force_lw;
+	if(lw == 0)
+		lw = (total16 > 0 && (uint64_t)l.nblocks * 2 >= (uint64_t)3 * sms * total16 * 2) ? 16 : 32;
+	if(lw == 16 && total16 == 0)
+		lw = 32;
+	const int G = 32 / lw;
+	const int best_nw = lw == 16 ? nw16 : nw32, best_total = lw == 16 ? total16 : total32;
 	if(best_nw == 0)
 	{
-		grkb_set_error("t1: code block too large for shared memory (%zu bytes)", fixed + per_warp);
+		grkb_set_error("t1: code block too large for shared memory (%zu bytes)", per_slot * G);
 		return -1;
 	}
-	const size_t smem = fixed + per_warp * best_nw;
-	GRKB_ENSURE_SMEM(t1_mq_decode_kernel, smem);
+	const size_t smem = per_slot * G * best_nw;
+	auto kern = lw == 32 ? t1_mq_decode_kernel<32> : t1_mq_decode_kernel<16>;
+	if(lw == 32)
+		GRKB_ENSURE_SMEM(t1_mq_decode_kernel<32>, smem);
+	else
+		GRKB_ENSURE_SMEM(t1_mq_decode_kernel<16>, smem);
 	int resident = 0; // CTAs per SM once registers are counted too
-	GRKB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, t1_mq_decode_kernel,
-																   best_nw * 32, smem));
+	GRKB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, kern, best_nw * 32, smem));
 	if(resident < 1)
 		resident = 1;
 	if(resident > best_total / best_nw)
 		resident = best_total / best_nw;
 	uint32_t ctas = (uint32_t)(sms * resident);
-	const uint32_t need = (l.nblocks + best_nw - 1) / best_nw;
+	const uint32_t need = (l.nblocks + best_nw * G - 1) / (best_nw * G);
 	if(ctas > need)
 		ctas = need;
 	GRKB_CUDA_CHECK(cudaMemsetAsync(l.counter, 0, sizeof(uint32_t), s));
-	t1_mq_decode_kernel<<<ctas, best_nw * 32, smem, s>>>(l);
+	kern<<<ctas, best_nw * 32, smem, s>>>(l);
 	GRKB_CUDA_CHECK(cudaGetLastError());
 	return 0;
 }

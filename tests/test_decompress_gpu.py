@@ -185,6 +185,35 @@ def test_configs1_mq97_4k_codestream(dec, frame16):
         assert np.array_equal(got[c], want[c])
 
 
+@pytest.mark.parametrize("irr", [1, 0])
+def test_4k_frame_of_32x32_blocks_two_blocks_per_warp(dec, frame16, irr):
+    """a 4096x2160 12-bit frame in 32x32 code blocks and 256x256 precincts (the cinema profiles'
+    sizes): 26 280 blocks, enough for the MQ decoder to put two blocks on every warp (t1_mq_dec.cu
+    picks it by block count); == stock decoder"""
+    img = [p >> 4 for p in frame16]
+    cs = _encode(img, 12, irr, "prc=256x256", numres=6, cblk=(32, 32))
+    want = _ref_decode(cs, 3)
+    assert "GRKB_T1_MQ_GROUP" not in os.environ
+    got = dec.decode(cs)
+    assert dec.rejected == 0
+    for c in range(3):
+        assert np.array_equal(got[c], want[c])
+        assert irr or np.array_equal(got[c], img[c])
+
+
+def test_precincts_of_more_than_1024_blocks(dec, frame16):
+    """The same frame with maximal precincts: 64x34 = 2 176 blocks in a precinct of the finest bands.
+    The STOCK DECODER gets such streams wrong (cache/SparseCache.h:40-54: tryGet() of a chunk that does
+    not exist yet records its index but keeps the previous chunk's pointer, so block 1024 + i is read
+    into block i's object); ours gives the image back, so the stock ENCODER's stream is right."""
+    img = [p >> 4 for p in frame16]
+    cs = _encode(img, 12, 0, numres=6, cblk=(32, 32))
+    got = dec.decode(cs)
+    assert dec.rejected == 0
+    for c in range(3):
+        assert np.array_equal(got[c], img[c])
+
+
 def test_configs2_ht_4k_codestream(dec, frame16):
     img = [p >> 4 for p in frame16]
     cs = _encode(img, 12, 0, ht=True, numres=6, cblk=(64, 64))

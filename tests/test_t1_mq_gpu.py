@@ -15,6 +15,19 @@ pytestmark = pytest.mark.gpu
 G = os.path.join(os.path.dirname(__file__), "golden")
 
 
+@pytest.fixture(params=["32", "16"], autouse=True)
+def lanes_per_block(request):
+    """every test of this file runs with one code block per warp and with one per half-warp
+    (t1_mq_dec.cu: GRKB_T1_MQ_GROUP, read at every launch; without it the launcher picks by block count)"""
+    old = os.environ.get("GRKB_T1_MQ_GROUP")
+    os.environ["GRKB_T1_MQ_GROUP"] = request.param
+    yield request.param
+    if old is None:
+        del os.environ["GRKB_T1_MQ_GROUP"]
+    else:
+        os.environ["GRKB_T1_MQ_GROUP"] = old
+
+
 def _table(entries, plane_w):
     """entries: [(bytes, segs, numbps, w, h, orient, sty)] -> blocks stacked vertically in one plane"""
     blocks = np.zeros(len(entries), dtype=T.CBLK_DTYPE)
@@ -165,6 +178,8 @@ def test_simt_kernel_same_results(gpu):
     import sys
     if os.environ.get("GRKB_T1_MQ_KERNEL") == "simt":
         pytest.skip("already running under the SIMT kernel")
+    if os.environ.get("GRKB_T1_MQ_GROUP") == "16":
+        pytest.skip("once is enough")
     env = dict(os.environ, GRKB_T1_MQ_KERNEL="simt")
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-x", "-q", "-m", "gpu",
                         "-k", "golden or all_modes or arbitrary or tile_decode_matches_oracle"],

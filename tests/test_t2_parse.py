@@ -70,6 +70,21 @@ def test_sop_counters_after_a_tile_part_boundary(orc):
     assert all(np.array_equal(a, b) for a, b in zip(got, img))
 
 
+def test_precinct_with_more_than_1024_blocks(orc):
+    """64 x 34 = 2 176 code blocks in one precinct.  Our parser + the oracle give the image back; the
+    stock decoder does not (reference defect, cache/SparseCache.h:40-54: after tryGet() misses a chunk
+    the cached chunk pointer is stale and block 1024 + i lands in block i) -- so this case is pinned to
+    the image, not to the stock decoder."""
+    img = H.synth_image(2048, 1080, 1, 8, 3)
+    cs = O.ref_codec_encode(img, 8, 0, numres=6, cblk=(16, 16), threads=4)
+    got, tabs = H.decode_codestream_oracle(cs)
+    assert len(tabs[0]["blocks"]) > 8000
+    assert np.array_equal(got[0], img[0])
+    want = O.ref_codec_decode(cs, 1, 2048, 1080, threads=4)
+    if np.array_equal(want[0], img[0]):
+        pytest.fail("the stock decoder handles > 1024 blocks per precinct now: pin this case to it")
+
+
 def test_single_layer_is_zero_copy(orc):
     cs, tabs = _roundtrip(200, 150, 3, 8, 0, "")
     assert tabs[0]["zero_copy"] and tabs[0]["packets"] == 15
