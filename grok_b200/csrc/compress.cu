@@ -17,6 +17,7 @@
 #include "codestream.h"
 #include "geometry.h"
 #include "packet_order.h"
+#include "pcrd.h"
 #include <chrono>
 #include <math.h>
 #include <memory>
@@ -196,8 +197,15 @@ struct TileKit
 	grkb_pass* passes = nullptr;
 	uint8_t* bytes = nullptr;
 	size_t bytes_cap = 0;
+	// rate allocation on the device (pcrd.cu): tables of this geometry, results (page-locked)
+	grkb_pcrd* pcrd = nullptr;
+	uint32_t* npass_dev = nullptr;
+	PcrdResult* pcrd_result = nullptr;
 	~TileKit()
 	{
+		grkb_pcrd_destroy(pcrd);
+		grkb_host_free(npass_dev);
+		grkb_host_free(pcrd_result);
 		if(enc)
 			grkb_encoder_destroy(enc);
 		grkb_host_free(coded);
@@ -216,6 +224,7 @@ struct grkb_compressor
 	std::vector<std::unique_ptr<TileKit>> kits;
 	std::vector<uint8_t> hdr; // packet headers of the packet being written
 	double t2_ms = 0, device_ms = 0;
+	uint32_t pcrd_iterations = 0; // bisection steps of the last tile allocated on the device
 };
 
 namespace
@@ -223,6 +232,65 @@ namespace
 bool same_geometry(const grkb_tile_params& a, const grkb_tile_params& b)
 {
 	return memcmp(&a, &b, sizeof(a)) == 0;
+}
+
+// the packets of the tile's single layer in progression order, as the device allocator wants them
+// (pcrd.h): the same walk as packet_header() / simulate() below
+bool build_pcrd(grkb_compressor* z, TileKit* k)
+{
+	const grkb_compress_params& p = z->p;
+	const uint32_t nb = 3 * p.numres - 2;
+	PcrdLayout lay;
+	std::vector<grkb_cs::Poc> progs;
+	progs.push_back(grkb_cs::Poc{0, (uint8_t)p.numres, (uint8_t)p.prog_order, 0, (uint16_t)p.numcomps, 1});
+	grkb_cs::for_each_packet(progs, p.numres, p.numcomps, 1, k->idx, k->tp.x0, k->tp.y0, k->tp.x1, k->tp.y1,
+							 [&](uint32_t, uint32_t resno, uint32_t compno, uint64_t precinct) {
+		const grkb_layout_res& R = k->idx.res[resno];
+		PcrdPacket pk{};
+		pk.band_first = (uint32_t)lay.bands.size();
+		pk.leaf_first = (uint32_t)lay.leaf_block.size();
+		pk.node_first = lay.nnodes;
+		for(uint32_t band = 0; band < R.nbands; ++band)
+		{
+			const grkb_layout_pb& pb = k->idx.pb[(size_t)R.first_pb + (size_t)band * R.gw * R.gh + (size_t)precinct];
+			const uint32_t ncb = pb.cgw * pb.cgh;
+			if(ncb == 0 || pb.band_empty)
+				continue;
+			PcrdBand b{};
+			b.leaf_first = (uint32_t)lay.leaf_block.size();
+			b.cgw = pb.cgw;
+			b.cgh = pb.cgh;
+			b.band_bps = k->band_numbps[(size_t)compno * nb + (resno == 0 ? 0 : 3 * resno - 2) + band];
+			b.node_first = lay.nnodes;
+			b.packet = (uint32_t)lay.packets.size();
+			uint32_t lw = pb.cgw, lh = pb.cgh;
+			while(true)
+			{
+				lay.nnodes += lw * lh;
+				if(lw <= 1 && lh <= 1)
+					break;
+				lw = (lw + 1) >> 1;
+				lh = (lh + 1) >> 1;
+			}
+			for(uint32_t cb = 0; cb < ncb; ++cb)
+			{
+				const int32_t ti = k->table_of[pb.first + cb];
+				lay.leaf_block.push_back(ti >= 0 ? (int32_t)(compno * k->per_comp + (uint32_t)ti) : -1);
+				lay.leaf_band.push_back((uint32_t)lay.bands.size());
+			}
+			lay.bands.push_back(b);
+		}
+		pk.nbands = (uint32_t)lay.bands.size() - pk.band_first;
+		pk.nleaves = (uint32_t)lay.leaf_block.size() - pk.leaf_first;
+		pk.nnodes = lay.nnodes - pk.node_first;
+		lay.packets.push_back(pk);
+		return true;
+	});
+	if(grkb_pcrd_create(lay, (uint32_t)k->blocks.size(), &k->pcrd))
+		return false;
+	k->npass_dev = (uint32_t*)grkb_host_alloc(std::max<size_t>(k->blocks.size(), 1) * sizeof(uint32_t));
+	k->pcrd_result = (PcrdResult*)grkb_host_alloc(sizeof(PcrdResult));
+	return k->npass_dev && k->pcrd_result;
 }
 
 TileKit* kit_for(grkb_compressor* z, const grkb_tile_params& tp)
@@ -306,6 +374,8 @@ TileKit* kit_for(grkb_compressor* z, const grkb_tile_params& tp)
 	k->passes = (grkb_pass*)grkb_host_alloc(std::max<size_t>(n, 1) * GRKB_ENC_MAX_PASSES * sizeof(grkb_pass));
 	k->bytes = (uint8_t*)grkb_host_alloc(k->bytes_cap);
 	if(!k->coded || !k->passes || !k->bytes)
+		return nullptr;
+	if(p.rate > 0 && !build_pcrd(z, k.get()))
 		return nullptr;
 	z->kits.push_back(std::move(k));
 	return z->kits.back().get();
@@ -802,6 +872,26 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 		static const double norms_rev[3] = {1.732, .8292, .8292}, norms_irrev[3] = {1.732, 1.805, 1.573};
 		const bool rc = p.rate > 0;
 		const double* norms = (rc && p.mct) ? (p.reversible ? norms_rev : norms_irrev) : nullptr;
+		// the tile's byte budget as CodeStreamCompress::updateRates leaves it (:950-1018): its share of
+		// the target size minus its share of the main header, at least 30 bytes
+		double budget = 0;
+		if(rc)
+		{
+			const double pixels = (double)(g.x1 - g.x0) * (double)(g.y1 - g.y0);
+			budget = ((double)(p.numcomps * p.prec) * pixels) / (p.rate * 8.0);
+			budget -= (pixels * (double)header_size) / ((double)p.width * (double)p.height);
+			if(budget < 30.0)
+				budget = 30.0;
+		}
+		// the allocation runs on the device right behind the block coders (pcrd.cu); GRKB_PCRD=host
+		// keeps it on the host (rate_allocate below: same algorithm, same result)
+		static const bool pcrd_host = [] {
+			const char* e = getenv("GRKB_PCRD");
+			return e && e[0] == 'h';
+		}();
+		const bool on_device = rc && !pcrd_host && k->pcrd;
+		grkb_encoder_set_pcrd(k->enc, on_device ? k->pcrd : nullptr, (uint64_t)(uint32_t)ceil(budget), p.csty, k->npass_dev,
+							  k->pcrd_result);
 		if(grkb_encoder_encode(k->enc, src, stride, k->blocks.data(), (uint32_t)k->blocks.size(), norms, norms ? 3 : 0,
 							   rc ? 1 : 0, k->coded, k->passes, k->bytes, k->bytes_cap, &nbytes))
 			return -1;
@@ -815,17 +905,14 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 		k->npass.resize(k->blocks.size());
 		for(size_t i = 0; i < k->blocks.size(); ++i)
 			k->npass[i] = k->coded[i].numpasses;
-		if(rc)
+		if(on_device && k->pcrd_result->error == 0)
 		{
-			// the tile's byte budget as CodeStreamCompress::updateRates leaves it (:950-1018): its share of
-			// the target size minus its share of the main header, at least 30 bytes
-			const double pixels = (double)(g.x1 - g.x0) * (double)(g.y1 - g.y0);
-			double bytes = ((double)(p.numcomps * p.prec) * pixels) / (p.rate * 8.0);
-			bytes -= (pixels * (double)header_size) / ((double)p.width * (double)p.height);
-			if(bytes < 30.0)
-				bytes = 30.0;
-			rate_allocate(z, k, bytes);
+			for(size_t i = 0; i < k->blocks.size(); ++i)
+				k->npass[i] = k->npass_dev[i];
+			z->pcrd_iterations = k->pcrd_result->iterations;
 		}
+		else if(rc)
+			rate_allocate(z, k, budget);
 		std::string err;
 		if(!write_tile(z, k, t, o, err))
 		{

@@ -3,6 +3,7 @@
 //
 // Mirrors the reference's T1CompressScheduler (src/lib/jp2/t1/T1CompressScheduler.cpp:31-154):
 // one flat table of blocks for all components of a tile, one launch per coder.
+#include "pcrd.h"
 #include "pipeline.h"
 #include "t1.cuh"
 #include <new>
@@ -296,7 +297,23 @@ struct grkb_encoder
 	uint64_t* h_total = nullptr; // pinned
 	void* packed_in = nullptr; // narrow input (row N3), allocated on first use
 	size_t packed_in_cap = 0;
+	// rate allocation to run behind the block coders of the next tile (pcrd.h), null: none
+	grkb_pcrd* pcrd = nullptr;
+	uint64_t pcrd_max_bytes = 0;
+	uint32_t pcrd_csty = 0;
+	uint32_t* pcrd_npass = nullptr;
+	PcrdResult* pcrd_result = nullptr;
 };
+
+extern "C++" void grkb_encoder_set_pcrd(grkb_encoder* e, grkb_pcrd* p, uint64_t max_bytes, uint32_t csty,
+									   uint32_t* npass_host, PcrdResult* result_host)
+{
+	e->pcrd = p;
+	e->pcrd_max_bytes = max_bytes;
+	e->pcrd_csty = csty;
+	e->pcrd_npass = npass_host;
+	e->pcrd_result = result_host;
+}
 
 static int encoder_front(grkb_encoder* e, cudaStream_t s)
 {
@@ -523,6 +540,9 @@ static int submit_any(grkb_encoder* e, const int32_t* const* image, uint32_t str
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(coded, l.coded, (size_t)nblocks * sizeof(grkb_coded),
 									cudaMemcpyDeviceToHost, s));
 	GRKB_CUDA_CHECK(cudaMemcpyAsync(e->h_total, l.packed_used, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+	if(e->pcrd && grkb_pcrd_enqueue(e->pcrd, l.coded, l.passes, e->pcrd_max_bytes, e->pcrd_csty, e->pcrd_npass,
+									e->pcrd_result, s))
+		return -1;
 	guard.ok = true;
 	return 0;
 }
@@ -586,8 +606,12 @@ int grkb_encoder_wait(grkb_encoder* e, size_t* used)
 		GRKB_CUDA_CHECK(cudaMemcpyAsync(e->p_coded, l.coded, (size_t)e->p_nblocks * sizeof(grkb_coded),
 										cudaMemcpyDeviceToHost, s));
 		GRKB_CUDA_CHECK(cudaMemcpyAsync(e->h_total, l.packed_used, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+		if(e->pcrd && grkb_pcrd_enqueue(e->pcrd, l.coded, l.passes, e->pcrd_max_bytes, e->pcrd_csty, e->pcrd_npass,
+										e->pcrd_result, s))
+			return -1;
 		GRKB_CUDA_CHECK(cudaStreamSynchronize(s));
 	}
+	e->pcrd = nullptr;
 	const uint64_t total = e->h_total[0];
 	if(total == ~(uint64_t)0)
 	{
