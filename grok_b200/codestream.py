@@ -206,6 +206,7 @@ lib.grkb_compressor_destroy.argtypes = [_vp]
 lib.grkb_compressor_destroy.restype = None
 lib.grkb_compress.argtypes = [_vp, _vp, _u32, _vp, C.c_size_t, C.POINTER(C.c_size_t)]
 lib.grkb_compress_stats.argtypes = [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+lib.grkb_compress_allocation.argtypes = [_vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
 
 PROGS = {"LRCP": 0, "RLCP": 1, "RPCL": 2, "PCRL": 3, "CPRL": 4}
 
@@ -271,4 +272,7 @@ class Compressor:
     def stats(self):
         a, b = C.c_double(), C.c_double()
         check(lib.grkb_compress_stats(self.h, C.byref(a), C.byref(b)), "grkb_compress_stats")
-        return dict(device_ms=a.value, t2_ms=b.value)
+        d, h, n = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        check(lib.grkb_compress_allocation(self.h, C.byref(d), C.byref(h), C.byref(n)), "grkb_compress_allocation")
+        return dict(device_ms=a.value, t2_ms=b.value, tiles_allocated_on_device=d.value,
+                    tiles_allocated_on_host=h.value, bisection_steps=n.value)

@@ -225,6 +225,7 @@ struct grkb_compressor
 	std::vector<uint8_t> hdr; // packet headers of the packet being written
 	double t2_ms = 0, device_ms = 0;
 	uint32_t pcrd_iterations = 0; // bisection steps of the last tile allocated on the device
+	uint32_t tiles_dev = 0, tiles_host = 0; // tiles of the last call allocated on the device / host
 };
 
 namespace
@@ -843,6 +844,7 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 	write_main_header(z, o);
 	const size_t header_size = o.size();
 	z->t2_ms = z->device_ms = 0;
+	z->tiles_dev = z->tiles_host = 0;
 	for(uint32_t t = 0; t < ntx * nty; ++t)
 	{
 		const uint32_t tp = t % ntx, tq = t / ntx;
@@ -910,9 +912,13 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 			for(size_t i = 0; i < k->blocks.size(); ++i)
 				k->npass[i] = k->npass_dev[i];
 			z->pcrd_iterations = k->pcrd_result->iterations;
+			++z->tiles_dev;
 		}
 		else if(rc)
+		{
 			rate_allocate(z, k, budget);
+			++z->tiles_host;
+		}
 		std::string err;
 		if(!write_tile(z, k, t, o, err))
 		{
@@ -931,6 +937,20 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 		return -2;
 	}
 	memcpy(out, o.data(), o.size());
+	return 0;
+}
+
+int grkb_compress_allocation(const grkb_compressor* z, uint32_t* tiles_on_device, uint32_t* tiles_on_host,
+							 uint32_t* steps)
+{
+	if(!z)
+		return -1;
+	if(tiles_on_device)
+		*tiles_on_device = z->tiles_dev;
+	if(tiles_on_host)
+		*tiles_on_host = z->tiles_host;
+	if(steps)
+		*steps = z->pcrd_iterations;
 	return 0;
 }
 

@@ -554,7 +554,8 @@ typedef struct grkb_compress_params
 				  * the block coders also deliver every pass's distortion and the passes that go into
 				  * the layer are chosen by TileProcessor::pcrdBisectSimple's bisection of the slope
 				  * threshold on the reference's own packet accounting (tile/
-				  * TileProcessor.cpp:1195-1440, t2/T2Compress.cpp:58-110, :331-420) */
+				  * TileProcessor.cpp:1195-1440, t2/T2Compress.cpp:58-110, :331-420), on the device
+				  * behind the block coders (csrc/pcrd.cu; GRKB_PCRD=host: on the host) */
 } grkb_compress_params;
 
 typedef struct grkb_compressor grkb_compressor;
@@ -566,6 +567,10 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 				  size_t* used);
 /* milliseconds of the last call: device tile encodes (copies included), host T2 + markers */
 int grkb_compress_stats(const grkb_compressor* z, double* device_ms, double* t2_ms);
+/* rate allocation of the last call: tiles allocated on the device / on the host, bisection steps of the
+ * last tile allocated on the device */
+int grkb_compress_allocation(const grkb_compressor* z, uint32_t* tiles_on_device, uint32_t* tiles_on_host,
+							 uint32_t* steps);
 
 /* D. allocation-free door --------------------------------------------------------------------- */
 

@@ -96,6 +96,13 @@ def test_configs2_ht_4k_encode_codestream_byte_identical(gpu):
     (320, 200, 3, 12, 1, 5, (32, 32), (0, 0), 40.0, "sop;eph", dict(sop=True, eph=True)),
     (250, 190, 3, 8, 1, 5, (32, 32), (128, 96), 10.0, "", {}),
     (320, 200, 3, 12, 1, 6, (64, 64), (0, 0), 1.0, "", {}),
+    # codeword segments that end inside the layer (TERMALL; LAZY + RESET + SEGSYM): several lengths per block
+    (320, 200, 3, 8, 1, 5, (32, 32), (0, 0), 8.0, "sty=4", dict(cblk_sty=4)),
+    (320, 200, 3, 10, 1, 5, (64, 64), (0, 0), 5.0, "sty=35", dict(cblk_sty=35)),
+    # many small packets (a 64-thread CTA each) and few large ones (1024 threads, 3 x 1024 blocks in one)
+    (512, 384, 3, 8, 1, 5, (32, 32), (0, 0), 15.0, "prog=RPCL;prc=64x64;eph", dict(prog="RPCL", precincts=[(64, 64)], eph=True)),
+    (1024, 1024, 1, 8, 1, 2, (16, 16), (0, 0), 3.0, "", {}),
+    (1024, 768, 3, 12, 0, 3, (16, 16), (0, 0), 2.5, "sop", dict(sop=True)),
 ])
 def test_rate_controlled_layer_is_byte_identical_to_the_stock_encoder(gpu, w, h, ncomp, prec, irr, nr, cblk, tile, rate,
                                                                       opts, kw):
@@ -115,7 +122,10 @@ def test_rate_controlled_layer_is_byte_identical_to_the_stock_encoder(gpu, w, h,
     z = CS.Compressor(w, h, ncomp, prec, reversible=not irr, numres=nr, cblk=cblk, tile=tile, rate=rate,
                       comment=GROK_COMMENT, **kw)
     got = z.encode(img)
+    st = z.stats()
     z.close()
+    # allocated on the device (csrc/pcrd.cu), not by the host's copy of the same algorithm
+    assert st["tiles_allocated_on_host"] == 0 and st["tiles_allocated_on_device"] >= 1 and st["bisection_steps"] >= 1
     if rate > 1:
         assert want.size < full.size
     n = min(got.size, want.size)
