@@ -31,9 +31,21 @@ struct BitWriter
 {
 	std::vector<uint8_t>& out;
 	uint32_t buf = 0, ct = 8;
+	// The reference's rate allocation writes a packet header into a buffer of `limit` bytes (what is left
+	// of the layer's budget) and gives the layer up when the buffer fills (BitIO::writeByte: the byte that
+	// makes the count reach the size fails) -- but only where the caller looks at the result: the writes
+	// of the number of passes and of the Lblock comma code go unchecked (T2Compress.cpp:208, :228), the
+	// failed byte is written again with the next bit, the count runs past the limit for good and the
+	// remaining budget wraps: from there on everything "fits".  event: 0 none, 1 the header does not fit,
+	// 2 the limit was passed inside an unchecked field.  limit 0 never fails (the count starts at 1).
+	uint64_t limit = 0, count = 0;
+	bool unchecked = false;
+	int event = 0;
 	explicit BitWriter(std::vector<uint8_t>& o) : out(o) {}
-	inline void byteout()
+	inline void byteout(bool from_flush = false)
 	{
+		if(++count == limit && !event)
+			event = (from_flush || !unchecked) ? 1 : 2;
 		out.push_back((uint8_t)buf);
 		ct = buf == 0xFF ? 7 : 8;
 		buf = 0;
@@ -71,9 +83,9 @@ struct BitWriter
 	}
 	inline void flush()
 	{
-		byteout();
+		byteout(true);
 		if(ct == 7)
-			byteout();
+			byteout(true);
 	}
 };
 
@@ -463,13 +475,14 @@ void write_main_header(const grkb_compressor* z, std::vector<uint8_t>& o)
 // One packet: header bits into z->hdr (returns false on an inconsistent table).  The passes of a block
 // that go into the layer are k->npass[block].
 bool packet_header(grkb_compressor* z, TileKit* k, uint32_t resno, uint32_t compno, uint64_t precinct,
-				   TagTreeEnc& incl, TagTreeEnc& imsb, std::string& err)
+				   TagTreeEnc& incl, TagTreeEnc& imsb, std::string& err, uint64_t limit = 0, int* event = nullptr)
 {
 	const grkb_compress_params& p = z->p;
 	const uint32_t nb = 3 * p.numres - 2;
 	const grkb_layout_res& R = k->idx.res[resno];
 	z->hdr.clear();
 	BitWriter bw(z->hdr);
+	bw.limit = limit;
 	bw.bit(1); // the reference never writes the empty-packet form (T2Compress.cpp:150-153)
 	for(uint32_t band = 0; band < R.nbands; ++band)
 	{
@@ -503,7 +516,9 @@ bool packet_header(grkb_compressor* z, TileKit* k, uint32_t resno, uint32_t comp
 			if(!np)
 				continue;
 			imsb.compress(bw, cb, 0xFF);
+			bw.unchecked = true;
 			bw.numpasses(np);
+			bw.unchecked = false;
 			const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES;
 			// Lblock increment, then one length per codeword segment (T2Compress.cpp:213-256)
 			uint32_t numlenbits = 3, inc = 0, nump = 0, len = 0;
@@ -520,7 +535,9 @@ bool packet_header(grkb_compressor* z, TileKit* k, uint32_t resno, uint32_t comp
 					nump = 0;
 				}
 			}
+			bw.unchecked = true;
 			bw.comma(inc);
+			bw.unchecked = false;
 			numlenbits += inc;
 			for(uint32_t q = 0; q < np; ++q)
 			{
@@ -536,6 +553,8 @@ bool packet_header(grkb_compressor* z, TileKit* k, uint32_t resno, uint32_t comp
 		}
 	}
 	bw.flush();
+	if(event)
+		*event = bw.event;
 	return true;
 }
 
@@ -570,11 +589,14 @@ bool simulate(grkb_compressor* z, TileKit* k, uint64_t max_bytes, uint64_t* tota
 				avail -= 6;
 			bytes += 6;
 		}
-		if(!packet_header(z, k, resno, compno, precinct, incl, imsb, err) || (limited && z->hdr.size() >= avail))
+		int event = 0;
+		if(!packet_header(z, k, resno, compno, precinct, incl, imsb, err, limited ? avail : 0, &event) || event == 1)
 		{
 			fits = false;
 			return false;
 		}
+		if(event == 2)
+			return false; // the limit went by unnoticed: this and every later packet "fit"
 		bytes += z->hdr.size();
 		if(limited)
 			avail -= z->hdr.size();

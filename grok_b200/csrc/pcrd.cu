@@ -156,10 +156,13 @@ static __device__ Sel select_block(const grkb_pass* ps, uint32_t total, uint32_t
 	return r;
 }
 
+// Sinks for the bits of a packet header.  tag(true) .. tag(false) brackets the fields whose writes the
+// reference does not check against the remaining budget (number of passes, Lblock comma code).
 struct CountSink
 {
 	static constexpr bool WRITES = false;
 	uint32_t n = 0;
+	__device__ void tag(bool) {}
 	__device__ void put(uint32_t, uint32_t k)
 	{
 		n += k;
@@ -179,6 +182,7 @@ struct WriteSink
 	static constexpr bool WRITES = true;
 	uint32_t* buf;
 	uint64_t pos;
+	__device__ void tag(bool) {}
 	__device__ void put(uint32_t v, uint32_t k) // k in 1..32, v < 2^k
 	{
 		const uint32_t sh = (uint32_t)(pos & 31);
@@ -206,6 +210,33 @@ struct WriteSink
 	}
 };
 
+// which kind of field holds bit `target` of a leaf's header bits: 1 unchecked, 0 checked
+struct ClassifySink
+{
+	static constexpr bool WRITES = true;
+	uint32_t target, pos = 0;
+	int result = 0;
+	bool un = false;
+	__device__ void tag(bool u)
+	{
+		un = u;
+	}
+	__device__ void put(uint32_t, uint32_t k)
+	{
+		if(target >= pos && target < pos + k)
+			result = un ? 1 : 0;
+		pos += k;
+	}
+	__device__ void zeros(uint32_t k)
+	{
+		put(0, k);
+	}
+	__device__ void ones(uint32_t k)
+	{
+		put(0, k);
+	}
+};
+
 // what follows the tag-tree bits of an included block: number of passes, Lblock increment, one length
 // per codeword segment (T2Compress.cpp:205-256)
 template<class Sink>
@@ -225,7 +256,9 @@ static __device__ void put_numpasses(Sink& s, uint32_t np)
 template<class Sink>
 static __device__ void block_tail(Sink& s, const grkb_pass* ps, uint32_t np)
 {
+	s.tag(true);
 	put_numpasses(s, np);
+	s.tag(false);
 	uint32_t numlenbits = 3, inc = 0, nump = 0, len = 0;
 	for(uint32_t q = 0; q < np; ++q)
 	{
@@ -240,8 +273,10 @@ static __device__ void block_tail(Sink& s, const grkb_pass* ps, uint32_t np)
 			nump = 0;
 		}
 	}
+	s.tag(true);
 	s.ones(inc);
 	s.put(0, 1);
+	s.tag(false);
 	numlenbits += inc;
 	for(uint32_t q = 0; q < np; ++q)
 	{
@@ -318,9 +353,11 @@ static __device__ void leaf_header(Sink& s, const Args& a, const uint32_t* node_
 		s.zeros(sel.tailbits);
 	else if(sel.nsegs == 1 && 3u + sel.inc + sel.lognump <= 32)
 	{
+		s.tag(true);
 		put_numpasses(s, np);
 		s.ones(sel.inc);
 		s.put(0, 1);
+		s.tag(false);
 		const uint32_t n = 3u + sel.inc + sel.lognump;
 		s.put(n == 32 ? sel.seglen : sel.seglen & ((1u << n) - 1u), n);
 	}
@@ -334,7 +371,10 @@ struct State
 	double lower, upper, prev, thresh;
 	uint64_t layer_bytes;
 	uint32_t iter;
-	uint32_t go; // 1: evaluate the layer at thresh; 0: make the final layer at thresh; 2: finished
+	uint32_t go; // 1: evaluate the layer at thresh; 0: make the final layer at thresh; 2: finished;
+				 // 3: the step waits for the classification of one header bit (pend_*)
+	uint32_t pend_packet;
+	uint64_t pend_limit;
 	uint32_t err;
 	uint32_t counter; // CTAs that finished the current step
 	uint32_t counter0; // same for the slope-range kernel
@@ -424,7 +464,7 @@ __global__ void __launch_bounds__(INIT_T) pcrd_init_kernel(const Args a, State* 
 constexpr int SEL_T = 128;
 __global__ void __launch_bounds__(SEL_T) pcrd_select_kernel(const Args a, const State* st)
 {
-	if(st->go == 2)
+	if(st->go >= 2)
 		return;
 	const uint32_t bi = blockIdx.x * SEL_T + threadIdx.x;
 	if(bi >= a.nblocks)
@@ -486,9 +526,12 @@ static __device__ void stuffed_in_piece(const uint32_t* w, uint32_t total, uint3
 				uint32_t end = h + 8;
 				while(end < total && ((w[end >> 5] >> (31 - (end & 31))) & 1u))
 					++end;
-				hpos[j] = h;
-				hend[j] = end;
-				n = j + 1;
+				if(h + 8 <= total) // (a prefix of a longer header may end inside the eight ones)
+				{
+					hpos[j] = h;
+					hend[j] = end;
+					n = j + 1;
+				}
 			}
 		}
 #pragma unroll
@@ -500,7 +543,8 @@ static __device__ void stuffed_in_piece(const uint32_t* w, uint32_t total, uint3
 				uint32_t hit = 0xFFFFFFFFu, hit_end = 0;
 #pragma unroll
 				for(int j = 3; j >= 0; --j)
-					if(j < n && hpos[j] >= cur[e] && hend[j] - hpos[j] >= ((0u - (hpos[j] + stuffed[e])) & 7u) + 8u)
+					if(j < n && hpos[j] != 0xFFFFFFFFu && hpos[j] >= cur[e] &&
+					   hend[j] - hpos[j] >= ((0u - (hpos[j] + stuffed[e])) & 7u) + 8u)
 					{
 						hit = hpos[j];
 						hit_end = hend[j];
@@ -529,27 +573,28 @@ static __device__ void stuffed_in_piece(const uint32_t* w, uint32_t total, uint3
 		out[e] = stuffed[e] - (uint32_t)e;
 }
 
-// ---- one step of the bisection: a CTA per packet, then the last CTA to finish closes the step
+// shared memory of a packet's CTA
 template<int T>
-__global__ void __launch_bounds__(T) pcrd_step_kernel(const Args a, State* st)
+struct PacketShared
 {
-	__shared__ uint64_t s_sum[T], s_total;
-	__shared__ uint32_t s_scan[T / 32 + 1];
-	__shared__ uint32_t s_piece[T / 32][8];
-	__shared__ uint32_t s_fail, s_off;
-	__shared__ bool s_last;
-	const uint32_t go = st->go;
-	if(go == 2)
-		return;
-	const double th = st->thresh;
+	uint64_t sum[T], total_bytes;
+	uint32_t scan[T / 32 + 1];
+	uint32_t piece[T / 32][8];
+	uint32_t off, fail, key, word;
+	uint64_t limit;
+	bool last;
+};
+
+// B1 .. C for packet p: tag trees, bits of every leaf and their offsets (a.leaf_bits), the header bits
+// themselves at w (shared memory when it fits).  All threads of the CTA; false: no room for the bits.
+template<int T>
+static __device__ bool build_header(const Args& a, const PcrdPacket& pk, uint32_t p, uint32_t* dyn, PacketShared<T>& sh,
+									uint32_t*& w, uint32_t& total, uint64_t& body, uint32_t& err)
+{
 	const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-	const uint32_t p = blockIdx.x;
-	const PcrdPacket pk = a.packets[p];
 	const uint32_t gend = pk.leaf_first + pk.nleaves;
-	uint32_t err = 0;
 	// the packet's tag-tree nodes and header bits live in shared memory when they fit (the phases below
 	// hand them from thread to thread: from L2 every hand-over costs its latency)
-	extern __shared__ uint32_t dyn[];
 	uint32_t* node_min = a.node_min;
 	uint32_t* node_first = a.node_first;
 	uint32_t dyn_used = 0;
@@ -559,165 +604,219 @@ __global__ void __launch_bounds__(T) pcrd_step_kernel(const Args a, State* st)
 		node_first = dyn + pk.nnodes - pk.node_first;
 		dyn_used = 2 * pk.nnodes;
 	}
-	if(go == 1)
+	// B1: the two tag trees of every band as reductions, level by level (all bands of the packet in the
+	// same round)
+	for(uint32_t bj = pk.band_first; bj < pk.band_first + pk.nbands; ++bj)
 	{
-		// B1: the two tag trees of every band as reductions, level by level (all bands of the packet in
-		// the same round)
+		const PcrdBand b = a.bands[bj];
+		const uint32_t n0 = b.cgw * b.cgh;
+		for(uint32_t li = tid; li < n0; li += T)
+		{
+			const int32_t bi = a.leaf_block[b.leaf_first + li];
+			const uint32_t bps = bi >= 0 ? a.coded[bi].numbps : 0u;
+			if(bps > b.band_bps)
+				err = 1;
+			node_min[b.node_first + li] = b.band_bps - bps;
+			node_first[b.node_first + li] = (bi >= 0 && a.sel[bi].np) ? li : INF;
+		}
+	}
+	for(uint32_t lvl = 0;; ++lvl)
+	{
+		bool more = false;
+		__syncthreads();
 		for(uint32_t bj = pk.band_first; bj < pk.band_first + pk.nbands; ++bj)
 		{
 			const PcrdBand b = a.bands[bj];
-			const uint32_t n0 = b.cgw * b.cgh;
-			for(uint32_t li = tid; li < n0; li += T)
+			uint32_t off = 0, lw = b.cgw, lh = b.cgh;
+			for(uint32_t l = 0; l < lvl && !(lw <= 1 && lh <= 1); ++l)
 			{
-				const int32_t bi = a.leaf_block[b.leaf_first + li];
-				const uint32_t bps = bi >= 0 ? a.coded[bi].numbps : 0u;
-				if(bps > b.band_bps)
-					err = 1;
-				node_min[b.node_first + li] = b.band_bps - bps;
-				node_first[b.node_first + li] = (bi >= 0 && a.sel[bi].np) ? li : INF;
+				off += lw * lh;
+				lw = (lw + 1) >> 1;
+				lh = (lh + 1) >> 1;
 			}
-		}
-		for(uint32_t lvl = 0;; ++lvl)
-		{
-			bool more = false;
-			__syncthreads();
-			for(uint32_t bj = pk.band_first; bj < pk.band_first + pk.nbands; ++bj)
+			if(lw <= 1 && lh <= 1)
+				continue;
+			more = true;
+			const uint32_t pw = (lw + 1) >> 1, ph = (lh + 1) >> 1, poff = off + lw * lh;
+			for(uint32_t n = tid; n < pw * ph; n += T)
 			{
-				const PcrdBand b = a.bands[bj];
-				uint32_t off = 0, lw = b.cgw, lh = b.cgh;
-				for(uint32_t l = 0; l < lvl && !(lw <= 1 && lh <= 1); ++l)
-				{
-					off += lw * lh;
-					lw = (lw + 1) >> 1;
-					lh = (lh + 1) >> 1;
-				}
-				if(lw <= 1 && lh <= 1)
-					continue;
-				more = true;
-				const uint32_t pw = (lw + 1) >> 1, ph = (lh + 1) >> 1, poff = off + lw * lh;
-				for(uint32_t n = tid; n < pw * ph; n += T)
-				{
-					const uint32_t nx = n % pw, ny = n / pw;
-					uint32_t mn = INF, fi = INF;
+				const uint32_t nx = n % pw, ny = n / pw;
+				uint32_t mn = INF, fi = INF;
 #pragma unroll
-					for(uint32_t d = 0; d < 4; ++d)
-					{
-						const uint32_t cx = 2 * nx + (d & 1), cy = 2 * ny + (d >> 1);
-						if(cx < lw && cy < lh)
-						{
-							const uint32_t c = b.node_first + off + cy * lw + cx;
-							mn = min(mn, node_min[c]);
-							fi = min(fi, node_first[c]);
-						}
-					}
-					node_min[b.node_first + poff + n] = mn;
-					node_first[b.node_first + poff + n] = fi;
-				}
-			}
-			if(!more)
-				break;
-		}
-		if(tid == 0)
-			s_off = 1; // bit 0 is the "packet not empty" bit
-		__syncthreads();
-		// B2 + B3: bits of every leaf, their offsets in the packet, body bytes
-		uint64_t body = 0;
-		for(uint32_t g0 = pk.leaf_first; g0 < gend; g0 += T)
-		{
-			const uint32_t g = g0 + tid;
-			uint32_t bits = 0;
-			if(g < gend)
-			{
-				const PcrdBand& b = a.bands[a.leaf_band[g]];
-				const int32_t bi = a.leaf_block[g];
-				CountSink cs;
-				leaf_header(cs, a, node_min, node_first, b, g - b.leaf_first, bi);
-				bits = cs.n;
-				if(bi >= 0)
-					body += a.sel[bi].llen;
-			}
-			uint32_t inc = bits;
-			for(int o = 1; o < 32; o <<= 1)
-			{
-				const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-				if((int)lane >= o)
-					inc += t;
-			}
-			if(lane == 31)
-				s_scan[wid] = inc;
-			__syncthreads();
-			if(tid == 0)
-			{
-				uint32_t run = s_off;
-				for(int i = 0; i < T / 32; ++i)
+				for(uint32_t d = 0; d < 4; ++d)
 				{
-					const uint32_t t = s_scan[i];
-					s_scan[i] = run;
-					run += t;
+					const uint32_t cx = 2 * nx + (d & 1), cy = 2 * ny + (d >> 1);
+					if(cx < lw && cy < lh)
+					{
+						const uint32_t c = b.node_first + off + cy * lw + cx;
+						mn = min(mn, node_min[c]);
+						fi = min(fi, node_first[c]);
+					}
 				}
-				s_scan[T / 32] = run;
+				node_min[b.node_first + poff + n] = mn;
+				node_first[b.node_first + poff + n] = fi;
 			}
-			__syncthreads();
-			if(g < gend)
-				a.leaf_bits[g] = s_scan[wid] + inc - bits;
-			__syncthreads();
-			if(tid == 0)
-				s_off = s_scan[T / 32];
+		}
+		if(!more)
+			break;
+	}
+	if(tid == 0)
+		sh.off = 1; // bit 0 is the "packet not empty" bit
+	__syncthreads();
+	// B2 + B3: bits of every leaf, their offsets in the packet, body bytes
+	body = 0;
+	for(uint32_t g0 = pk.leaf_first; g0 < gend; g0 += T)
+	{
+		const uint32_t g = g0 + tid;
+		uint32_t bits = 0;
+		if(g < gend)
+		{
+			const PcrdBand& b = a.bands[a.leaf_band[g]];
+			const int32_t bi = a.leaf_block[g];
+			CountSink cs;
+			leaf_header(cs, a, node_min, node_first, b, g - b.leaf_first, bi);
+			bits = cs.n;
+			if(bi >= 0)
+				body += a.sel[bi].llen;
+		}
+		uint32_t inc = bits;
+		for(int o = 1; o < 32; o <<= 1)
+		{
+			const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+			if((int)lane >= o)
+				inc += t;
+		}
+		if(lane == 31)
+			sh.scan[wid] = inc;
+		__syncthreads();
+		if(tid == 0)
+		{
+			uint32_t run = sh.off;
+			for(int i = 0; i < T / 32; ++i)
+			{
+				const uint32_t t = sh.scan[i];
+				sh.scan[i] = run;
+				run += t;
+			}
+			sh.scan[T / 32] = run;
 		}
 		__syncthreads();
-		for(int o = 16; o; o >>= 1)
-			body += __shfl_xor_sync(0xffffffffu, body, o);
-		if(lane == 0)
-			s_sum[wid] = body;
+		if(g < gend)
+			a.leaf_bits[g] = sh.scan[wid] + inc - bits;
 		__syncthreads();
-		const uint32_t total = s_off;
-		uint32_t nbytes = 0;
-		const bool room = total + 64 <= a.pk_bitcap[p];
-		if(!room)
+		if(tid == 0)
+			sh.off = sh.scan[T / 32];
+	}
+	__syncthreads();
+	for(int o = 16; o; o >>= 1)
+		body += __shfl_xor_sync(0xffffffffu, body, o);
+	if(lane == 0)
+		sh.sum[wid] = body;
+	__syncthreads();
+	body = 0;
+	for(int i = 0; i < T / 32; ++i)
+		body += sh.sum[i];
+	total = sh.off;
+	if(total + 64 > a.pk_bitcap[p])
+		return false;
+	// Z: clear the bits in use; C: write them
+	const uint32_t words = (total + 63) / 32 + 1;
+	w = dyn_used + words <= a.dyn_words ? dyn + dyn_used : a.bitbuf + (a.pk_bitbase[p] >> 5);
+	for(uint32_t i = tid; i < words; i += T)
+		w[i] = 0;
+	__syncthreads();
+	for(uint32_t g = pk.leaf_first + tid; g < gend; g += T)
+	{
+		const PcrdBand& b = a.bands[a.leaf_band[g]];
+		WriteSink ws{w, a.leaf_bits[g]};
+		leaf_header(ws, a, node_min, node_first, b, g - b.leaf_first, a.leaf_block[g]);
+	}
+	if(tid == 0)
+		atomicOr(w, 0x80000000u);
+	__threadfence_block();
+	__syncthreads();
+	return true;
+}
+
+// D: bits stuffed into the first `total` bits at w, a piece per warp (all threads; same value in all)
+template<int T>
+static __device__ uint32_t cta_stuffed(const uint32_t* w, uint32_t total, PacketShared<T>& sh)
+{
+	const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+	const uint32_t hw = (total + 31) / 32, per = ((hw + T / 32 - 1) / (T / 32) + 31) & ~31u;
+	uint32_t cnt[8];
+	stuffed_in_piece(w, total, min(wid * per, hw), min((wid + 1) * per, hw), lane, cnt);
+	__syncthreads();
+	if(lane == 0)
+		for(int e = 0; e < 8; ++e)
+			sh.piece[wid][e] = cnt[e];
+	__syncthreads();
+	uint32_t stuffed = 0;
+	for(int i = 0; i < T / 32; ++i)
+		stuffed += sh.piece[i][stuffed & 7];
+	return stuffed;
+}
+
+// the bisection's next move once the layer at `th` is known to fit or not (one thread)
+static __device__ void finish_step(State* st, double th, bool fits, uint64_t layer_bytes)
+{
+	double lower = st->lower, upper = st->upper, thresh = th;
+	const uint32_t iter = st->iter + 1;
+	if(fits)
+	{
+		st->layer_bytes = layer_bytes;
+		upper = thresh;
+	}
+	else
+		lower = thresh;
+	uint32_t next_go = 1;
+	if(iter == 128 || __ldcg(&st->err))
+		next_go = 0;
+	else
+	{
+		// the reference makes the layer at the next threshold and then stops if it moved by less than
+		// 0.001; the layer it leaves is the one at `upper`
+		const double prev = thresh;
+		thresh = (upper == -1) ? lower : __ddiv_rn(__dadd_rn(lower, upper), 2.0);
+		st->prev = prev;
+		if(fabs(__dsub_rn(prev, thresh)) < 0.001)
+			next_go = 0;
+	}
+	st->lower = lower;
+	st->upper = upper;
+	st->thresh = next_go ? thresh : ((upper == -1) ? thresh : upper);
+	st->iter = iter;
+	st->go = next_go;
+	st->counter = 0;
+}
+
+// ---- one step of the bisection: a CTA per packet, then the last CTA to finish closes the step
+template<int T>
+__global__ void __launch_bounds__(T) pcrd_step_kernel(const Args a, State* st)
+{
+	__shared__ PacketShared<T> sh;
+	extern __shared__ uint32_t dyn[];
+	const uint32_t go = st->go;
+	if(go >= 2)
+		return;
+	const double th = st->thresh;
+	const uint32_t tid = threadIdx.x;
+	const uint32_t p = blockIdx.x;
+	uint32_t err = 0;
+	if(go == 1)
+	{
+		const PcrdPacket pk = a.packets[p];
+		uint32_t* w = nullptr;
+		uint32_t total = 0, nbytes = 0;
+		uint64_t body = 0;
+		if(!build_header<T>(a, pk, p, dyn, sh, w, total, body, err))
 			err = 2;
 		else
-		{
-			// Z: clear the bits in use; C: write them
-			const uint32_t words = (total + 63) / 32 + 1;
-			uint32_t* w = dyn_used + words <= a.dyn_words ? dyn + dyn_used : a.bitbuf + (a.pk_bitbase[p] >> 5);
-			for(uint32_t i = tid; i < words; i += T)
-				w[i] = 0;
-			__syncthreads();
-			for(uint32_t g = pk.leaf_first + tid; g < gend; g += T)
-			{
-				const PcrdBand& b = a.bands[a.leaf_band[g]];
-				WriteSink ws{w, a.leaf_bits[g]};
-				leaf_header(ws, a, node_min, node_first, b, g - b.leaf_first, a.leaf_block[g]);
-			}
-			if(tid == 0)
-				atomicOr(w, 0x80000000u);
-			__threadfence_block();
-			__syncthreads();
-			// D: header bytes with the stuffing, a piece of the header per warp
-			{
-				const uint32_t hw = (total + 31) / 32, per = ((hw + T / 32 - 1) / (T / 32) + 31) & ~31u;
-				uint32_t cnt[8];
-				stuffed_in_piece(w, total, min(wid * per, hw), min((wid + 1) * per, hw), lane, cnt);
-				if(lane == 0)
-					for(int e = 0; e < 8; ++e)
-						s_piece[wid][e] = cnt[e];
-			}
-			__syncthreads();
-			if(tid == 0)
-			{
-				uint32_t stuffed = 0;
-				for(int i = 0; i < T / 32; ++i)
-					stuffed += s_piece[i][stuffed & 7];
-				nbytes = (total + stuffed + 7) / 8;
-			}
-		}
+			nbytes = (total + cta_stuffed<T>(w, total, sh) + 7) / 8;
 		if(tid == 0)
 		{
-			uint64_t bsum = 0;
-			for(int i = 0; i < T / 32; ++i)
-				bsum += s_sum[i];
 			a.pk_hdr[p] = nbytes;
-			a.pk_body[p] = bsum;
+			a.pk_body[p] = body;
 		}
 	}
 	if(err)
@@ -727,11 +826,12 @@ __global__ void __launch_bounds__(T) pcrd_step_kernel(const Args a, State* st)
 	if(tid == 0)
 	{
 		__threadfence();
-		s_last = atomicAdd(&st->counter, 1u) == gridDim.x - 1;
-		s_fail = 0;
+		sh.last = atomicAdd(&st->counter, 1u) == gridDim.x - 1;
+		sh.fail = 0;
+		sh.key = 0xFFFFFFFFu;
 	}
 	__syncthreads();
-	if(!s_last)
+	if(!sh.last)
 		return;
 	__threadfence();
 	if(go == 0)
@@ -749,15 +849,17 @@ __global__ void __launch_bounds__(T) pcrd_step_kernel(const Args a, State* st)
 	}
 	// E: the running budget over the packets in progression order (compressPacketsSimulate).  In the
 	// reference's unsigned arithmetic what is left before packet p is max_bytes minus the bytes of the
-	// packets before it, so the packets can be checked independently once those sums are known.
+	// packets before it, so the packets can be checked independently once those sums are known; the
+	// first packet that runs into the budget decides.  A header that reaches the limit gives the layer
+	// up -- unless the byte that reaches it is completed by a bit of an unchecked field (see
+	// pcrd_classify_kernel), in which case the budget wraps and the whole layer "fits".
 	const uint32_t chunk = (a.npackets + T - 1) / T;
 	const uint32_t p0 = min(tid * chunk, a.npackets), p1 = min(p0 + chunk, a.npackets);
 	const uint64_t fixed = ((a.csty & 2) ? 6u : 0u) + ((a.csty & 4) ? 2u : 0u);
 	uint64_t sum = 0;
 	for(uint32_t q = p0; q < p1; ++q)
 		sum += fixed + __ldcg(a.pk_hdr + q) + __ldcg(a.pk_body + q);
-	__syncthreads();
-	s_sum[tid] = sum;
+	sh.sum[tid] = sum;
 	__syncthreads();
 	if(tid == 0)
 	{
@@ -765,65 +867,135 @@ __global__ void __launch_bounds__(T) pcrd_step_kernel(const Args a, State* st)
 		const uint32_t used = min((uint32_t)T, (a.npackets + chunk - 1) / chunk); // threads that have packets
 		for(uint32_t i = 0; i < used; ++i)
 		{
-			const uint64_t t = s_sum[i];
-			s_sum[i] = run;
+			const uint64_t t = sh.sum[i];
+			sh.sum[i] = run;
 			run += t;
 		}
-		s_total = run;
+		sh.total_bytes = run;
 	}
 	__syncthreads();
-	uint64_t before = s_sum[tid];
-	bool fail = false;
+	uint64_t before = sh.sum[tid], my_limit = 0;
+	uint32_t my_key = 0xFFFFFFFFu; // packet * 4 + kind of its event: 1 does not fit, 2 header limit inside the header
 	for(uint32_t q = p0; q < p1; ++q)
 	{
 		const uint64_t hdr = __ldcg(a.pk_hdr + q), body = __ldcg(a.pk_body + q);
 		uint64_t avail = a.max_bytes - before;
 		if(a.csty & 2)
 			avail -= 6;
-		if(hdr >= avail)
-			fail = true;
-		avail -= hdr;
-		if(a.csty & 4)
-			avail -= 2;
-		if(body > avail)
-			fail = true;
+		uint32_t ev = 0;
+		if(avail != 0 && hdr >= avail)
+			ev = hdr > avail ? 2 : 1; // reached by the last byte: at the flush, which is checked
+		else
+		{
+			uint64_t left = avail - hdr;
+			if(a.csty & 4)
+				left -= 2;
+			if(body > left)
+				ev = 1;
+		}
+		if(ev && my_key == 0xFFFFFFFFu)
+		{
+			my_key = q * 4 + ev;
+			my_limit = avail;
+		}
 		before += fixed + hdr + body;
 	}
-	if(fail)
-		atomicOr(&s_fail, 1u);
+	if(my_key != 0xFFFFFFFFu)
+		atomicMin(&sh.key, my_key);
+	__syncthreads();
+	if(my_key != 0xFFFFFFFFu && my_key == sh.key)
+		sh.limit = my_limit;
 	__syncthreads();
 	if(tid == 0)
 	{
-		const bool fits = s_fail == 0;
-		double lower = st->lower, upper = st->upper, thresh = th;
-		uint32_t iter = st->iter + 1;
-		if(fits)
-		{
-			st->layer_bytes = s_total;
-			upper = thresh;
-		}
-		else
-			lower = thresh;
-		uint32_t next_go = 1;
-		if(iter == 128 || __ldcg(&st->err))
-			next_go = 0;
+		const uint32_t key = sh.key;
+		if(key == 0xFFFFFFFFu)
+			finish_step(st, th, true, sh.total_bytes);
+		else if((key & 3) == 1)
+			finish_step(st, th, false, 0);
 		else
 		{
-			// the reference makes the layer at the next threshold and then stops if it moved by less than
-			// 0.001; the layer it leaves is the one at `upper`
-			const double prev = thresh;
-			thresh = (upper == -1) ? lower : __ddiv_rn(__dadd_rn(lower, upper), 2.0);
-			st->prev = prev;
-			if(fabs(__dsub_rn(prev, thresh)) < 0.001)
-				next_go = 0;
+			st->pend_packet = key >> 2;
+			st->pend_limit = sh.limit;
+			st->counter = 0;
+			st->go = 3;
 		}
-		st->lower = lower;
-		st->upper = upper;
-		st->thresh = next_go ? thresh : ((upper == -1) ? thresh : upper);
-		st->iter = iter;
-		st->go = next_go;
-		st->counter = 0;
 	}
+}
+
+// ---- a header reached the end of the budget before its last byte.  BitIO::writeByte fails on the
+// byte that makes the count reach the limit, and it is called when the first bit of the NEXT byte
+// arrives; T2Compress::compressHeader looks at the result for every field except the number of passes
+// and the Lblock comma code (T2Compress.cpp:208, :228).  There the failed byte is simply written again
+// with the following bit, the count runs past the limit, the budget left wraps around and every later
+// check passes: the layer "fits".  So: rebuild that packet's header, find the raw bit that opens byte
+// limit + 1 of the stuffed stream, and see which field it belongs to.
+template<int T>
+__global__ void __launch_bounds__(T) pcrd_classify_kernel(const Args a, State* st)
+{
+	__shared__ PacketShared<T> sh;
+	__shared__ int s_kind;
+	extern __shared__ uint32_t dyn[];
+	if(st->go != 3)
+		return;
+	const double th = st->thresh;
+	const uint32_t tid = threadIdx.x, p = st->pend_packet;
+	const uint64_t limit = st->pend_limit;
+	const PcrdPacket pk = a.packets[p];
+	uint32_t* w = nullptr;
+	uint32_t total = 0, err = 0;
+	uint64_t body = 0;
+	if(tid == 0)
+		s_kind = 0;
+	if(!build_header<T>(a, pk, p, dyn, sh, w, total, body, err))
+	{
+		if(tid == 0)
+		{
+			atomicOr(&st->err, 2u);
+			finish_step(st, th, false, 0);
+		}
+		return;
+	}
+	// smallest raw bit r whose place in the stuffed stream, r + (bits stuffed before it), is in byte
+	// limit + 1 or later
+	uint32_t lo = 1, hi = total; // r in [lo, hi]; hi == total: there is none
+	while(lo < hi)
+	{
+		const uint32_t mid = lo + (hi - lo) / 2;
+		const uint32_t s = cta_stuffed<T>(w, mid, sh);
+		if((uint64_t)mid + s >= 8 * limit)
+			hi = mid;
+		else
+			lo = mid + 1;
+	}
+	const uint32_t r = lo;
+	if(r < total)
+	{
+		// the leaf that holds bit r says what kind of field it is
+		const uint32_t gend = pk.leaf_first + pk.nleaves;
+		uint32_t* node_min = a.node_min;
+		uint32_t* node_first = a.node_first;
+		if(2 * pk.nnodes <= a.dyn_words)
+		{
+			node_min = dyn - pk.node_first;
+			node_first = dyn + pk.nnodes - pk.node_first;
+		}
+		for(uint32_t g = pk.leaf_first + tid; g < gend; g += T)
+		{
+			const uint32_t off = a.leaf_bits[g], next = g + 1 < gend ? a.leaf_bits[g + 1] : total;
+			if(r >= off && r < next)
+			{
+				const PcrdBand& b = a.bands[a.leaf_band[g]];
+				ClassifySink cs;
+				cs.target = r - off;
+				leaf_header(cs, a, node_min, node_first, b, g - b.leaf_first, a.leaf_block[g]);
+				s_kind = cs.result;
+			}
+		}
+	}
+	__syncthreads();
+	if(tid == 0)
+		finish_step(st, th, r < total && s_kind == 1, 0);
 }
 } // namespace
 
@@ -959,21 +1131,39 @@ int grkb_pcrd_enqueue(grkb_pcrd* p, const grkb_coded* coded, const grkb_pass* pa
 	const size_t dyn = p->dyn_bytes;
 	a.dyn_words = (uint32_t)(dyn / 4);
 	if(p->max_leaves <= 64)
+	{
 		GRKB_ENSURE_SMEM(pcrd_step_kernel<64>, dyn);
+		GRKB_ENSURE_SMEM(pcrd_classify_kernel<64>, dyn);
+	}
 	else if(p->max_leaves <= 256)
+	{
 		GRKB_ENSURE_SMEM(pcrd_step_kernel<256>, dyn);
+		GRKB_ENSURE_SMEM(pcrd_classify_kernel<256>, dyn);
+	}
 	else
+	{
 		GRKB_ENSURE_SMEM(pcrd_step_kernel<1024>, dyn);
+		GRKB_ENSURE_SMEM(pcrd_classify_kernel<1024>, dyn);
+	}
 	if(ctas)
 		for(int i = 0; i < 129; ++i)
 		{
 			pcrd_select_kernel<<<(p->nblocks + SEL_T - 1) / SEL_T, SEL_T, 0, s>>>(a, p->state);
 			if(p->max_leaves <= 64)
+			{
 				pcrd_step_kernel<64><<<ctas, 64, dyn, s>>>(a, p->state);
+				pcrd_classify_kernel<64><<<1, 64, dyn, s>>>(a, p->state);
+			}
 			else if(p->max_leaves <= 256)
+			{
 				pcrd_step_kernel<256><<<ctas, 256, dyn, s>>>(a, p->state);
+				pcrd_classify_kernel<256><<<1, 256, dyn, s>>>(a, p->state);
+			}
 			else
+			{
 				pcrd_step_kernel<1024><<<ctas, 1024, dyn, s>>>(a, p->state);
+				pcrd_classify_kernel<1024><<<1, 1024, dyn, s>>>(a, p->state);
+			}
 		}
 	else
 	{
