@@ -60,6 +60,7 @@ struct T1Launch
 	uint32_t max_flag_words; // max (w+2)*(ceil(h/4)+2) over MQ blocks
 	uint32_t max_ht_w; // max width over HT blocks
 	uint32_t ht_refine; // some HT block has more than one codeword segment (SigProp / MagRef)
+	uint32_t concurrent; // other tile decoders of this process with block decoding in flight on the device
 };
 // encode side: every block codes into its own slot of `slots`; a second kernel packs the
 // streams back to back (block order) into `packed` and fills coded[].data_off

@@ -26,6 +26,7 @@
 // Mallat coefficient plane.  Warps pull blocks from a global work counter, longest first.
 #include "t1.cuh"
 #include <mutex>
+#include <stdio.h>
 #include <stdlib.h>
 
 namespace
@@ -595,8 +596,8 @@ static __device__ void ref_pass(const Blk& b, Mq& q, uint32_t cxs,
 // LW = 32: one code block per warp.  LW = 16: each half of a warp owns a block and the two chains
 // share the warp's instruction issue wherever their control flow agrees (both halves start their
 // blocks together, so they are always in the same kind of pass).
-template<uint32_t LW>
-__global__ void __launch_bounds__(256, 4)
+template<uint32_t LW, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB)
 	t1_mq_decode_kernel(const T1Launch l)
 {
 	constexpr uint32_t G = 32 / LW;
@@ -803,9 +804,9 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 			max_warps_sm = 32;
 	}
 	// warps per CTA: whatever packs most code blocks into the 227 KB of an SM
-	auto pack = [&](int G, int& nw_out) {
+	auto pack = [&](int G, int max_nw, int& nw_out) {
 		int best_nw = 0, best_total = 0;
-		for(int nw = 1; nw <= 256 / 32; ++nw)
+		for(int nw = 1; nw <= max_nw; ++nw)
 		{
 			const size_t need = per_slot * G * nw;
 			if(need > 227 * 1024)
@@ -824,13 +825,36 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 		nw_out = best_nw;
 		return best_total;
 	};
-	int nw16 = 0, nw32 = 0;
-	const int total16 = pack(2, nw16), total32 = pack(1, nw32);
+	// two blocks per warp come in two builds: 63 registers and four CTAs of up to eight warps (small
+	// blocks: 32 warps per SM), or 80 registers and two CTAs of up to twelve (blocks whose state lets
+	// fewer than 28 warps of pairs onto an SM anyway: fewer instructions for the same occupancy)
+	int nw16 = 0, nw16w = 0, nw32 = 0;
+	int total16 = pack(2, 8, nw16);
+	const int total16w = pack(2, 12, nw16w), total32 = pack(1, 8, nw32);
+	const bool wide = total16 < 28 && total16w > 0;
+	if(wide)
+	{
+		total16 = total16w;
+		nw16 = nw16w;
+	}
 	int lw = force_lw;
 	if(lw == 0)
-		lw = (total16 > 0 && (uint64_t)l.nblocks * 2 >= (uint64_t)3 * sms * total16 * 2) ? 16 : 32;
+	{
+		// enough blocks to fill the SMs with pairs one and a half times over; or other frames in flight
+		// on this device (throughput over this frame's latency) and room for at least 20 warps of pairs
+		const bool many = (uint64_t)l.nblocks * 2 >= (uint64_t)3 * sms * total16 * 2;
+		static const uint32_t busy_at = [] {
+			const char* e = getenv("GRKB_T1_MQ_BUSY");
+			return e ? (uint32_t)atoi(e) : 1u;
+		}();
+		const bool busy = l.concurrent >= busy_at && total16 >= 20;
+		lw = (total16 > 0 && (many || busy)) ? 16 : 32;
+	}
 	if(lw == 16 && total16 == 0)
 		lw = 32;
+	if(getenv("GRKB_T1_MQ_DEBUG"))
+		fprintf(stderr, "t1_mq: %u blocks, %u others in flight, %d lanes per block%s\n", l.nblocks, l.concurrent, lw,
+				lw == 16 && wide ? " (wide)" : "");
 	const int G = 32 / lw;
 	const int best_nw = lw == 16 ? nw16 : nw32, best_total = lw == 16 ? total16 : total32;
 	if(best_nw == 0)
@@ -839,11 +863,22 @@ int grkb_launch_t1_mq_decode(const T1Launch& l, cudaStream_t s)
 		return -1;
 	}
 	const size_t smem = per_slot * G * best_nw;
-	auto kern = lw == 32 ? t1_mq_decode_kernel<32> : t1_mq_decode_kernel<16>;
+	void (*kern)(const T1Launch);
 	if(lw == 32)
-		GRKB_ENSURE_SMEM(t1_mq_decode_kernel<32>, smem);
+	{
+		kern = t1_mq_decode_kernel<32, 256, 4>;
+		GRKB_ENSURE_SMEM((t1_mq_decode_kernel<32, 256, 4>), smem);
+	}
+	else if(!wide)
+	{
+		kern = t1_mq_decode_kernel<16, 256, 4>;
+		GRKB_ENSURE_SMEM((t1_mq_decode_kernel<16, 256, 4>), smem);
+	}
 	else
-		GRKB_ENSURE_SMEM(t1_mq_decode_kernel<16>, smem);
+	{
+		kern = t1_mq_decode_kernel<16, 384, 2>;
+		GRKB_ENSURE_SMEM((t1_mq_decode_kernel<16, 384, 2>), smem);
+	}
 	int resident = 0; // CTAs per SM once registers are counted too
 	GRKB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, kern, best_nw * 32, smem));
 	if(resident < 1)

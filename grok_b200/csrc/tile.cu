@@ -15,6 +15,7 @@
 #include "t1.cuh"
 #include <vector>
 #include <string.h>
+#include <mutex>
 #include <new>
 
 struct grkb_decoder
@@ -41,6 +42,7 @@ struct grkb_decoder
 	uint32_t max_area = 0, max_flag_words = 0, max_ht_w = 0;
 	bool any_mq = false, any_ht = false, ht_refine = false;
 	cudaEvent_t ev[7] = {};
+	cudaEvent_t busy = nullptr; // recorded behind the block decoders of every tile
 	void* packed = nullptr; // narrow output (row N3), allocated on first use
 	size_t packed_cap = 0;
 };
@@ -167,6 +169,23 @@ int scan_blocks(grkb_decoder* d, const grkb_cblk* blocks, uint32_t nblocks, cons
 	return 0;
 }
 
+// The decoders of the process, so that one can tell whether others have block decoding in flight on
+// its device: with several frames in flight the EBCOT kernel trades a frame's latency for throughput
+// (t1_mq_dec.cu: two code blocks per warp).
+std::mutex g_registry_mu;
+std::vector<grkb_decoder*> g_registry;
+
+uint32_t others_in_flight(const grkb_decoder* me)
+{
+	std::lock_guard<std::mutex> lk(g_registry_mu);
+	uint32_t n = 0;
+	for(const grkb_decoder* o : g_registry)
+		if(o != me && o->device == me->device && o->busy && cudaEventQuery(o->busy) == cudaErrorNotReady)
+			++n;
+	(void)cudaGetLastError(); // (cudaErrorNotReady is not an error)
+	return n;
+}
+
 int run_device(grkb_decoder* d, void* const* coeff_planes, uint32_t stride, bool wavelet,
 			   cudaEvent_t* ev, uint32_t* launches)
 {
@@ -185,6 +204,7 @@ int run_device(grkb_decoder* d, void* const* coeff_planes, uint32_t stride, bool
 	l.max_flag_words = d->max_flag_words;
 	l.max_ht_w = d->max_ht_w;
 	l.ht_refine = d->ht_refine ? 1u : 0u;
+	l.concurrent = d->any_mq ? others_in_flight(d) : 0u;
 	if(ev)
 		cudaEventRecord(ev[0], d->stream);
 	if(d->any_mq)
@@ -205,6 +225,8 @@ int run_device(grkb_decoder* d, void* const* coeff_planes, uint32_t stride, bool
 	}
 	if(ev)
 		cudaEventRecord(ev[1], d->stream);
+	if(d->busy)
+		cudaEventRecord(d->busy, d->stream);
 	if(!wavelet)
 		return 0;
 	// wavelet + component transform: components 0..2 as one group when the MCT couples them,
@@ -297,11 +319,16 @@ int grkb_decoder_create(const grkb_tile_params* p, uint32_t max_blocks, size_t m
 	TRY(cudaMallocHost(&d->h_status, sizeof(uint32_t)));
 	for(auto& e : d->ev)
 		TRY(cudaEventCreate(&e));
+	TRY(cudaEventCreateWithFlags(&d->busy, cudaEventDisableTiming));
 #undef TRY
 	if(ensure(d, max_blocks ? max_blocks : 1, max_blocks ? max_blocks : 1, max_bytes))
 		return fail();
 	if(cudaStreamSynchronize(d->stream) != cudaSuccess)
 		return fail();
+	{
+		std::lock_guard<std::mutex> lk(g_registry_mu);
+		g_registry.push_back(d);
+	}
 	*out = d;
 	return 0;
 }
@@ -310,8 +337,19 @@ void grkb_decoder_destroy(grkb_decoder* d)
 {
 	if(!d)
 		return;
+	{
+		std::lock_guard<std::mutex> lk(g_registry_mu);
+		for(size_t i = 0; i < g_registry.size(); ++i)
+			if(g_registry[i] == d)
+			{
+				g_registry.erase(g_registry.begin() + (long)i);
+				break;
+			}
+	}
 	if(d->stream)
 		cudaStreamSynchronize(d->stream);
+	if(d->busy)
+		cudaEventDestroy(d->busy);
 	for(uint32_t c = 0; c < GRKB_MAX_COMPS; ++c)
 	{
 		cudaFree(d->coeff[c]);
