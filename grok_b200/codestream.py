@@ -198,7 +198,8 @@ class CompressParams(C.Structure):
                 ("tile_y0", _u32), ("numres", _u32), ("cblkw_exp", _u32), ("cblkh_exp", _u32),
                 ("cblk_sty", _u32), ("reversible", _u32), ("mct", _u32), ("prog_order", _u32), ("csty", _u32),
                 ("numgbits", _u32), ("prec_w_exp", C.c_uint8 * 33), ("prec_h_exp", C.c_uint8 * 33),
-                ("comment", C.c_char * 64), ("rate", C.c_double)]
+                ("comment", C.c_char * 64), ("rate", C.c_double), ("numlayers", _u32),
+                ("layer_rates", C.c_double * 100)]
 
 
 lib.grkb_compressor_create.argtypes = [C.c_int, C.POINTER(CompressParams), C.POINTER(_vp)]
@@ -216,7 +217,9 @@ class Compressor:
 
     def __init__(self, width, height, numcomps, prec, reversible=True, ht=False, numres=6, cblk=(64, 64),
                  tile=(0, 0), origin=(0, 0), tile_origin=None, prog="LRCP", precincts=None, sop=False, eph=False,
-                 cblk_sty=0, mct=None, sgnd=False, comment="", rate=0.0, device=0):
+                 cblk_sty=0, mct=None, sgnd=False, comment="", rate=0.0, rates=None, device=0):
+        """rate: compression ratio of a single layer (0: every pass).  rates: one ratio per quality layer
+        (decreasing, as -r a,b,c of grk_compress; 0: every remaining pass)"""
         p = CompressParams()
         p.width, p.height, p.numcomps, p.prec, p.sgnd = width, height, numcomps, prec, int(sgnd)
         p.x0, p.y0 = origin
@@ -244,6 +247,12 @@ class Compressor:
                 p.prec_h_exp[r] = max(h, 1).bit_length() - 1
         p.comment = comment.encode()
         p.rate = float(rate)
+        if rates:
+            p.numlayers = len(rates)
+            for i, r in enumerate(rates):
+                p.layer_rates[i] = float(r)
+            if len(rates) == 1:
+                p.rate = float(rates[0])
         self.params = p
         self.h = _vp()
         check(lib.grkb_compressor_create(device, C.byref(p), C.byref(self.h)), "grkb_compressor_create")

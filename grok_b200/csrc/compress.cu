@@ -204,6 +204,13 @@ struct TileKit
 	std::vector<uint32_t> band_numbps; // per (component, band in codestream order)
 	uint32_t per_comp = 0; // blocks per component in `blocks`
 	std::vector<uint32_t> npass; // coding passes of every block that go into the layer (rate allocation)
+	// several layers: passes of every block in each layer, passes in the layers already final (the
+	// reference's numPassesInPreviousPackets), and what a walk over the packets carries from layer to
+	// layer: passes written so far, Lblock, the tag trees of every (component, band, precinct)
+	std::vector<std::vector<uint32_t>> layer_np;
+	std::vector<uint32_t> prev_np, in_packet;
+	std::vector<uint8_t> lblock;
+	std::vector<TagTreeEnc> incl_trees, imsb_trees;
 	// results of the last encode (page-locked)
 	grkb_coded* coded = nullptr;
 	grkb_pass* passes = nullptr;
@@ -388,7 +395,7 @@ TileKit* kit_for(grkb_compressor* z, const grkb_tile_params& tp)
 	k->bytes = (uint8_t*)grkb_host_alloc(k->bytes_cap);
 	if(!k->coded || !k->passes || !k->bytes)
 		return nullptr;
-	if(p.rate > 0 && !build_pcrd(z, k.get()))
+	if(p.rate > 0 && p.numlayers <= 1 && !build_pcrd(z, k.get()))
 		return nullptr;
 	z->kits.push_back(std::move(k));
 	return z->kits.back().get();
@@ -440,7 +447,7 @@ void write_main_header(const grkb_compressor* z, std::vector<uint8_t>& o)
 	put16(o, 12 + (prt ? p.numres : 0));
 	o.push_back((uint8_t)((prt ? 1 : 0) | (p.csty & 6)));
 	o.push_back((uint8_t)p.prog_order);
-	put16(o, 1);
+	put16(o, p.numlayers > 1 ? p.numlayers : 1);
 	o.push_back((uint8_t)(p.mct ? 1 : 0));
 	o.push_back((uint8_t)(p.numres - 1));
 	o.push_back((uint8_t)(p.cblkw_exp - 2));
@@ -474,54 +481,89 @@ void write_main_header(const grkb_compressor* z, std::vector<uint8_t>& o)
 
 // One packet: header bits into z->hdr (returns false on an inconsistent table).  The passes of a block
 // that go into the layer are k->npass[block].
+// first and last byte (exclusive) of block bi's passes [from, from + np) in its stream
+inline void pass_span(const TileKit* k, size_t bi, uint32_t from, uint32_t np, uint32_t* b0, uint32_t* b1)
+{
+	const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES;
+	const uint32_t dl = k->coded[bi].data_len;
+	*b0 = from ? std::min<uint32_t>(ps[from - 1].rate, dl) : 0;
+	*b1 = np ? std::min<uint32_t>(ps[from + np - 1].rate, dl) : *b0;
+}
+
+// T2Compress::compressHeader (t2/T2Compress.cpp:113-258) for the packet (layno, resno, compno, precinct)
 bool packet_header(grkb_compressor* z, TileKit* k, uint32_t resno, uint32_t compno, uint64_t precinct,
-				   TagTreeEnc& incl, TagTreeEnc& imsb, std::string& err, uint64_t limit = 0, int* event = nullptr)
+				   TagTreeEnc& tmp_incl, TagTreeEnc& tmp_imsb, std::string& err, uint64_t limit = 0, int* event = nullptr,
+				   uint32_t layno = 0)
 {
 	const grkb_compress_params& p = z->p;
 	const uint32_t nb = 3 * p.numres - 2;
 	const grkb_layout_res& R = k->idx.res[resno];
+	const bool layered = !k->layer_np.empty();
+	const std::vector<uint32_t>& npl = layered ? k->layer_np[layno] : k->npass;
 	z->hdr.clear();
 	BitWriter bw(z->hdr);
 	bw.limit = limit;
 	bw.bit(1); // the reference never writes the empty-packet form (T2Compress.cpp:150-153)
 	for(uint32_t band = 0; band < R.nbands; ++band)
 	{
-		const grkb_layout_pb& pb = k->idx.pb[(size_t)R.first_pb + (size_t)band * R.gw * R.gh + (size_t)precinct];
+		const size_t pbi = (size_t)R.first_pb + (size_t)band * R.gw * R.gh + (size_t)precinct;
+		const grkb_layout_pb& pb = k->idx.pb[pbi];
 		const uint32_t ncb = pb.cgw * pb.cgh;
 		if(ncb == 0 || pb.band_empty)
 			continue;
 		const uint32_t band_bps = k->band_numbps[(size_t)compno * nb + (resno == 0 ? 0 : 3 * resno - 2) + band];
-		incl.init(pb.cgw, pb.cgh);
-		imsb.init(pb.cgw, pb.cgh);
-		for(uint32_t cb = 0; cb < ncb; ++cb)
+		// the trees live from the precinct's first layer to its last
+		TagTreeEnc& incl = layered ? k->incl_trees[(size_t)compno * k->idx.pb.size() + pbi] : tmp_incl;
+		TagTreeEnc& imsb = layered ? k->imsb_trees[(size_t)compno * k->idx.pb.size() + pbi] : tmp_imsb;
+		if(layno == 0)
 		{
-			const int32_t ti = k->table_of[pb.first + cb];
-			const size_t bi = ti >= 0 ? (size_t)compno * k->per_comp + (uint32_t)ti : 0;
-			const uint32_t bps = ti >= 0 ? k->coded[bi].numbps : 0;
-			if(bps > band_bps)
+			incl.init(pb.cgw, pb.cgh);
+			imsb.init(pb.cgw, pb.cgh);
+			for(uint32_t cb = 0; cb < ncb; ++cb)
 			{
-				err = "a code block has more bit planes than its band";
-				return false;
+				const int32_t ti = k->table_of[pb.first + cb];
+				const size_t bi = ti >= 0 ? (size_t)compno * k->per_comp + (uint32_t)ti : 0;
+				const uint32_t bps = ti >= 0 ? k->coded[bi].numbps : 0;
+				if(bps > band_bps)
+				{
+					err = "a code block has more bit planes than its band";
+					return false;
+				}
+				imsb.setvalue(cb, band_bps - bps);
+				if(layered && ti >= 0)
+					k->in_packet[bi] = 0;
 			}
-			imsb.setvalue(cb, band_bps - bps);
-			if(ti >= 0 && k->npass[bi])
-				incl.setvalue(cb, 0);
 		}
 		for(uint32_t cb = 0; cb < ncb; ++cb)
 		{
 			const int32_t ti = k->table_of[pb.first + cb];
 			const size_t bi = ti >= 0 ? (size_t)compno * k->per_comp + (uint32_t)ti : 0;
-			const uint32_t np = ti >= 0 ? k->npass[bi] : 0;
-			incl.compress(bw, cb, 1);
+			if(ti >= 0 && npl[bi] && !(layered && k->in_packet[bi]))
+				incl.setvalue(cb, layno);
+		}
+		for(uint32_t cb = 0; cb < ncb; ++cb)
+		{
+			const int32_t ti = k->table_of[pb.first + cb];
+			const size_t bi = ti >= 0 ? (size_t)compno * k->per_comp + (uint32_t)ti : 0;
+			const uint32_t np = ti >= 0 ? npl[bi] : 0;
+			const uint32_t before = (layered && ti >= 0) ? k->in_packet[bi] : 0;
+			if(!before)
+				incl.compress(bw, cb, layno + 1);
+			else
+				bw.bit(np != 0);
 			if(!np)
 				continue;
-			imsb.compress(bw, cb, 0xFF);
+			uint32_t numlenbits = 3;
+			if(!before)
+				imsb.compress(bw, cb, 0xFF);
+			else
+				numlenbits = k->lblock[bi];
 			bw.unchecked = true;
 			bw.numpasses(np);
 			bw.unchecked = false;
-			const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES;
+			const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES + before;
 			// Lblock increment, then one length per codeword segment (T2Compress.cpp:213-256)
-			uint32_t numlenbits = 3, inc = 0, nump = 0, len = 0;
+			uint32_t inc = 0, nump = 0, len = 0;
 			for(uint32_t q = 0; q < np; ++q)
 			{
 				++nump;
@@ -539,6 +581,8 @@ bool packet_header(grkb_compressor* z, TileKit* k, uint32_t resno, uint32_t comp
 			bw.comma(inc);
 			bw.unchecked = false;
 			numlenbits += inc;
+			if(layered)
+				k->lblock[bi] = (uint8_t)numlenbits;
 			for(uint32_t q = 0; q < np; ++q)
 			{
 				++nump;
@@ -559,8 +603,14 @@ bool packet_header(grkb_compressor* z, TileKit* k, uint32_t resno, uint32_t comp
 }
 
 // bytes of block bi that go into the layer: the rate of its last included pass
-inline uint32_t layer_len(const TileKit* k, size_t bi)
+inline uint32_t layer_len(const TileKit* k, size_t bi, uint32_t layno = 0)
 {
+	if(!k->layer_np.empty())
+	{
+		uint32_t b0, b1;
+		pass_span(k, bi, k->in_packet[bi], k->layer_np[layno][bi], &b0, &b1);
+		return b1 - b0;
+	}
 	const uint32_t np = k->npass[bi];
 	if(!np)
 		return 0;
@@ -570,18 +620,19 @@ inline uint32_t layer_len(const TileKit* k, size_t bi)
 // T2Compress::compressPacketsSimulate (t2/T2Compress.cpp:58-110, :331-420): would the packets of the
 // layer fit in max_bytes?  The reference's own accounting, packet by packet: a header must stay
 // strictly below what is left (BitIO::writeByte fails when it fills its buffer), a body may use it up.
-bool simulate(grkb_compressor* z, TileKit* k, uint64_t max_bytes, uint64_t* total)
+bool simulate(grkb_compressor* z, TileKit* k, uint64_t max_bytes, uint64_t* total, uint32_t layers = 1)
 {
 	const grkb_compress_params& p = z->p;
+	const bool layered = !k->layer_np.empty();
 	std::vector<grkb_cs::Poc> progs;
-	progs.push_back(grkb_cs::Poc{0, (uint8_t)p.numres, (uint8_t)p.prog_order, 0, (uint16_t)p.numcomps, 1});
+	progs.push_back(grkb_cs::Poc{0, (uint8_t)p.numres, (uint8_t)p.prog_order, 0, (uint16_t)p.numcomps, (uint16_t)layers});
 	TagTreeEnc incl, imsb;
 	bool fits = true;
 	const bool limited = max_bytes != UINT32_MAX;
 	uint64_t all = 0, left = max_bytes;
 	std::string err;
-	grkb_cs::for_each_packet(progs, p.numres, p.numcomps, 1, k->idx, k->tp.x0, k->tp.y0, k->tp.x1, k->tp.y1,
-							 [&](uint32_t, uint32_t resno, uint32_t compno, uint64_t precinct) {
+	grkb_cs::for_each_packet(progs, p.numres, p.numcomps, layers, k->idx, k->tp.x0, k->tp.y0, k->tp.x1, k->tp.y1,
+							 [&](uint32_t layno, uint32_t resno, uint32_t compno, uint64_t precinct) {
 		uint64_t avail = left, bytes = 0;
 		if(p.csty & 2)
 		{
@@ -590,7 +641,8 @@ bool simulate(grkb_compressor* z, TileKit* k, uint64_t max_bytes, uint64_t* tota
 			bytes += 6;
 		}
 		int event = 0;
-		if(!packet_header(z, k, resno, compno, precinct, incl, imsb, err, limited ? avail : 0, &event) || event == 1)
+		if(!packet_header(z, k, resno, compno, precinct, incl, imsb, err, limited ? avail : 0, &event, layno) ||
+		   event == 1)
 		{
 			fits = false;
 			return false;
@@ -617,14 +669,17 @@ bool simulate(grkb_compressor* z, TileKit* k, uint64_t max_bytes, uint64_t* tota
 				if(ti < 0)
 					continue;
 				const size_t bi = (size_t)compno * k->per_comp + (uint32_t)ti;
-				const uint32_t len = layer_len(k, bi);
-				if(!k->npass[bi])
+				const uint32_t np = layered ? k->layer_np[layno][bi] : k->npass[bi];
+				if(!np)
 					continue;
+				const uint32_t len = layer_len(k, bi, layno);
 				if(limited && len > avail)
 				{
 					fits = false;
 					break;
 				}
+				if(layered)
+					k->in_packet[bi] += np;
 				bytes += len;
 				if(limited)
 					avail -= len;
@@ -681,6 +736,110 @@ void make_layer(TileKit* k, double thresh)
 	}
 }
 
+// makeLayerSimple for layer `layno` of several: passes beyond those of the layers already final
+// (prev_np); with `final_attempt` the layer becomes final.  thresh 0 and makeLayerFinal: all that is left.
+void make_layer_n(TileKit* k, uint32_t layno, double thresh, bool final_attempt)
+{
+	std::vector<uint32_t>& out = k->layer_np[layno];
+	for(size_t bi = 0; bi < k->blocks.size(); ++bi)
+	{
+		const uint32_t total = k->coded[bi].numpasses, prev = k->prev_np[bi];
+		const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES;
+		uint32_t inc = prev;
+		if(thresh == 0)
+			inc = total;
+		else
+			for(uint32_t q = prev; q < total; ++q)
+			{
+				uint32_t dr;
+				double dd;
+				if(inc == 0)
+				{
+					dr = ps[q].rate;
+					dd = ps[q].distortion;
+				}
+				else
+				{
+					dr = ps[q].rate - ps[inc - 1].rate;
+					dd = ps[q].distortion - ps[inc - 1].distortion;
+				}
+				if(!dr)
+				{
+					if(dd != 0)
+						inc = q + 1;
+					continue;
+				}
+				const double slope = dd / dr;
+				if(thresh - slope < 2.2204460492503131e-16) // DBL_EPSILON
+					inc = q + 1;
+			}
+		if(inc < prev) // (thresh 0 with nothing left)
+			inc = prev;
+		out[bi] = inc - prev;
+		if(final_attempt)
+			k->prev_np[bi] = inc;
+	}
+}
+
+// pcrdBisectSimple over several layers (tile/TileProcessor.cpp:1277-1357): the layers are allocated
+// in turn against the bytes of all layers so far; a layer's search for the slope threshold starts
+// below the previous layer's lower bound (upperBound = lowerBound - 1); a layer without a rate takes
+// every pass that is left (makeLayerFinal)
+void rate_allocate_layers(grkb_compressor* z, TileKit* k, const std::vector<double>& layer_bytes)
+{
+	const uint32_t numlayers = (uint32_t)layer_bytes.size();
+	double min_slope = 1.7976931348623157e308, max_slope = -1;
+	for(size_t bi = 0; bi < k->blocks.size(); ++bi)
+	{
+		const grkb_pass* ps = k->passes + bi * GRKB_ENC_MAX_PASSES;
+		for(uint32_t q = 0; q < k->coded[bi].numpasses; ++q)
+		{
+			const int32_t dr = q ? (int32_t)(ps[q].rate - ps[q - 1].rate) : (int32_t)ps[q].rate;
+			const double dd = q ? ps[q].distortion - ps[q - 1].distortion : ps[q].distortion;
+			if(dr == 0)
+				continue;
+			const double sl = dd / dr;
+			if(sl < min_slope)
+				min_slope = sl;
+			if(sl > max_slope)
+				max_slope = sl;
+		}
+	}
+	k->layer_np.assign(numlayers, std::vector<uint32_t>(k->blocks.size(), 0));
+	k->prev_np.assign(k->blocks.size(), 0);
+	k->in_packet.assign(k->blocks.size(), 0);
+	k->lblock.assign(k->blocks.size(), 3);
+	k->incl_trees.resize((size_t)z->p.numcomps * k->idx.pb.size());
+	k->imsb_trees.resize((size_t)z->p.numcomps * k->idx.pb.size());
+	double upper = max_slope;
+	for(uint32_t layno = 0; layno < numlayers; ++layno)
+	{
+		if(!(layer_bytes[layno] > 0))
+		{
+			make_layer_n(k, layno, 0, true);
+			continue;
+		}
+		const uint64_t max_len = (uint64_t)(uint32_t)ceil(layer_bytes[layno]);
+		double lower = min_slope, prev = -1, thresh = 0;
+		for(uint32_t i = 0; i < 128; ++i)
+		{
+			thresh = (upper == -1) ? lower : (lower + upper) / 2;
+			make_layer_n(k, layno, thresh, false);
+			if(prev != -1 && fabs(prev - thresh) < 0.001)
+				break;
+			prev = thresh;
+			if(!simulate(z, k, max_len, nullptr, layno + 1))
+			{
+				lower = thresh;
+				continue;
+			}
+			upper = thresh;
+		}
+		make_layer_n(k, layno, (upper == -1) ? thresh : upper, true);
+		upper = lower - 1;
+	}
+}
+
 // TileProcessor::pcrdBisectSimple (tile/TileProcessor.cpp:1195-1357), one layer, rate target in bytes:
 // the slope threshold is bisected on the reference's own packet accounting until the layer fits.
 void rate_allocate(grkb_compressor* z, TileKit* k, double rate_bytes)
@@ -734,13 +893,15 @@ bool write_tile(grkb_compressor* z, TileKit* k, uint32_t tileno, std::vector<uin
 	o.push_back(0);
 	o.push_back(1);
 	put16(o, 0xFF93);
+	const bool layered = !k->layer_np.empty();
+	const uint32_t numlayers = layered ? (uint32_t)k->layer_np.size() : 1;
 	std::vector<grkb_cs::Poc> progs;
-	progs.push_back(grkb_cs::Poc{0, (uint8_t)numres, (uint8_t)p.prog_order, 0, (uint16_t)nc, 1});
+	progs.push_back(grkb_cs::Poc{0, (uint8_t)numres, (uint8_t)p.prog_order, 0, (uint16_t)nc, (uint16_t)numlayers});
 	TagTreeEnc incl, imsb;
 	uint32_t packet_no = 0;
 	bool ok = true;
-	grkb_cs::for_each_packet(progs, numres, nc, 1, k->idx, k->tp.x0, k->tp.y0, k->tp.x1, k->tp.y1,
-							 [&](uint32_t, uint32_t resno, uint32_t compno, uint64_t precinct) {
+	grkb_cs::for_each_packet(progs, numres, nc, numlayers, k->idx, k->tp.x0, k->tp.y0, k->tp.x1, k->tp.y1,
+							 [&](uint32_t layno, uint32_t resno, uint32_t compno, uint64_t precinct) {
 		const grkb_layout_res& R = k->idx.res[resno];
 		if(p.csty & 2) // SOP
 		{
@@ -748,7 +909,7 @@ bool write_tile(grkb_compressor* z, TileKit* k, uint32_t tileno, std::vector<uin
 			put16(o, 4);
 			put16(o, packet_no & 0xFFFF);
 		}
-		if(!packet_header(z, k, resno, compno, precinct, incl, imsb, err))
+		if(!packet_header(z, k, resno, compno, precinct, incl, imsb, err, 0, nullptr, layno))
 		{
 			ok = false;
 			return false;
@@ -768,6 +929,17 @@ bool write_tile(grkb_compressor* z, TileKit* k, uint32_t tileno, std::vector<uin
 				if(ti < 0)
 					continue;
 				const size_t bi = (size_t)compno * k->per_comp + (uint32_t)ti;
+				if(layered)
+				{
+					const uint32_t np = k->layer_np[layno][bi];
+					if(!np)
+						continue;
+					uint32_t b0, b1;
+					pass_span(k, bi, k->in_packet[bi], np, &b0, &b1);
+					o.insert(o.end(), k->bytes + k->coded[bi].data_off + b0, k->bytes + k->coded[bi].data_off + b1);
+					k->in_packet[bi] += np;
+					continue;
+				}
 				const uint32_t len = layer_len(k, bi);
 				if(len)
 					o.insert(o.end(), k->bytes + k->coded[bi].data_off, k->bytes + k->coded[bi].data_off + len);
@@ -813,6 +985,12 @@ int grkb_compressor_create(int device, const grkb_compress_params* p, grkb_compr
 	if(p->mct && p->numcomps < 3)
 	{
 		grkb_set_error("grkb_compressor_create: the component transform needs three components");
+		return -1;
+	}
+	if(p->numlayers > GRKB_MAX_LAYERS || (p->numlayers > 1 && ht))
+	{
+		grkb_set_error("grkb_compressor_create: %u layers (at most %u; HT blocks are written in one)", p->numlayers,
+					   (unsigned)GRKB_MAX_LAYERS);
 		return -1;
 	}
 	GRKB_CUDA_CHECK(cudaSetDevice(device));
@@ -894,18 +1072,44 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 		const auto t0 = std::chrono::steady_clock::now();
 		size_t nbytes = 0;
 		static const double norms_rev[3] = {1.732, .8292, .8292}, norms_irrev[3] = {1.732, 1.805, 1.573};
-		const bool rc = p.rate > 0;
+		const uint32_t numlayers = p.numlayers > 1 ? p.numlayers : 1;
+		bool rc = p.rate > 0;
+		if(numlayers > 1)
+		{
+			rc = false;
+			for(uint32_t l = 0; l < numlayers; ++l)
+				rc = rc || p.layer_rates[l] > 0;
+		}
 		const double* norms = (rc && p.mct) ? (p.reversible ? norms_rev : norms_irrev) : nullptr;
 		// the tile's byte budget as CodeStreamCompress::updateRates leaves it (:950-1018): its share of
 		// the target size minus its share of the main header, at least 30 bytes
 		double budget = 0;
+		std::vector<double> layer_bytes(numlayers, 0.0);
 		if(rc)
 		{
 			const double pixels = (double)(g.x1 - g.x0) * (double)(g.y1 - g.y0);
-			budget = ((double)(p.numcomps * p.prec) * pixels) / (p.rate * 8.0);
-			budget -= (pixels * (double)header_size) / ((double)p.width * (double)p.height);
-			if(budget < 30.0)
-				budget = 30.0;
+			const double sot_adjust = (pixels * (double)header_size) / ((double)p.width * (double)p.height);
+			for(uint32_t l = 0; l < numlayers; ++l)
+			{
+				const double r = numlayers > 1 ? p.layer_rates[l] : p.rate;
+				if(r > 0)
+					layer_bytes[l] = ((double)(p.numcomps * p.prec) * pixels) / (r * 8.0);
+			}
+			// first layer, the layers between, the last of several (:998-1021)
+			if(layer_bytes[0] > 0)
+			{
+				layer_bytes[0] -= sot_adjust;
+				if(layer_bytes[0] < 30.0)
+					layer_bytes[0] = 30.0;
+			}
+			for(uint32_t l = 1; l < numlayers; ++l)
+				if(layer_bytes[l] > 0)
+				{
+					layer_bytes[l] -= l + 1 == numlayers ? sot_adjust + 2.0 : sot_adjust;
+					if(layer_bytes[l] < layer_bytes[l - 1] + 10.0)
+						layer_bytes[l] = layer_bytes[l - 1] + 20.0;
+				}
+			budget = layer_bytes[0];
 		}
 		// the allocation runs on the device right behind the block coders (pcrd.cu); GRKB_PCRD=host
 		// keeps it on the host (rate_allocate below: same algorithm, same result)
@@ -913,7 +1117,7 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 			const char* e = getenv("GRKB_PCRD");
 			return e && e[0] == 'h';
 		}();
-		const bool on_device = rc && !pcrd_host && k->pcrd;
+		const bool on_device = rc && numlayers == 1 && !pcrd_host && k->pcrd;
 		grkb_encoder_set_pcrd(k->enc, on_device ? k->pcrd : nullptr, (uint64_t)(uint32_t)ceil(budget), p.csty, k->npass_dev,
 							  k->pcrd_result);
 		if(grkb_encoder_encode(k->enc, src, stride, k->blocks.data(), (uint32_t)k->blocks.size(), norms, norms ? 3 : 0,
@@ -929,7 +1133,13 @@ int grkb_compress(grkb_compressor* z, const int32_t* const* planes, uint32_t str
 		k->npass.resize(k->blocks.size());
 		for(size_t i = 0; i < k->blocks.size(); ++i)
 			k->npass[i] = k->coded[i].numpasses;
-		if(on_device && k->pcrd_result->error == 0)
+		k->layer_np.clear();
+		if(numlayers > 1)
+		{
+			rate_allocate_layers(z, k, layer_bytes);
+			++z->tiles_host;
+		}
+		else if(on_device && k->pcrd_result->error == 0)
 		{
 			for(size_t i = 0; i < k->blocks.size(); ++i)
 				k->npass[i] = k->npass_dev[i];

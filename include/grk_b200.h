@@ -536,6 +536,7 @@ int grkb_decompress_stats(const grkb_decompressor* d, double* t2_ms, uint32_t* t
  * 9/7 streams and single layers with a rate target, byte-identical to the stock encoder's output for
  * the same parameters.  Not written here: several quality layers, POC, tile-part division, the
  * digital-cinema profiles' per-component limits (those stay with the host behind grk_plugin_*). */
+#define GRKB_MAX_LAYERS 100 /* maxCompressLayersGRK */
 typedef struct grkb_compress_params
 {
 	uint32_t width, height, numcomps, prec, sgnd;
@@ -556,6 +557,11 @@ typedef struct grkb_compress_params
 				  * threshold on the reference's own packet accounting (tile/
 				  * TileProcessor.cpp:1195-1440, t2/T2Compress.cpp:58-110, :331-420), on the device
 				  * behind the block coders (csrc/pcrd.cu; GRKB_PCRD=host: on the host) */
+	uint32_t numlayers; /* 0 or 1: one layer at `rate`.  > 1: quality layers at layer_rates[] (-r a,b,c of
+						 * grk_compress: compression ratios, decreasing; 0: every remaining pass), allocated
+						 * layer by layer as pcrdBisectSimple does (each layer's search starts below the
+						 * previous layer's threshold), on the host */
+	double layer_rates[GRKB_MAX_LAYERS];
 } grkb_compress_params;
 
 typedef struct grkb_compressor grkb_compressor;

@@ -139,3 +139,40 @@ def test_rate_controlled_layer_is_byte_identical_to_the_stock_encoder(gpu, w, h,
     n = min(got.size, want.size)
     assert got.size == want.size and np.array_equal(got, want), \
         "sizes %d / %d, first difference at byte %d" % (got.size, want.size, int(np.argmax(got[:n] != want[:n])))
+
+
+@pytest.mark.parametrize("w,h,ncomp,prec,irr,nr,cblk,tile,rates,opts,kw", [
+    (320, 200, 3, 8, 1, 5, (32, 32), (0, 0), [40, 15, 5], "", {}),
+    (320, 200, 3, 8, 0, 5, (32, 32), (0, 0), [30, 10, 3], "", {}),
+    (320, 200, 3, 12, 1, 6, (64, 64), (0, 0), [60, 20], "prog=RLCP", dict(prog="RLCP")),
+    (512, 384, 3, 8, 1, 5, (32, 32), (0, 0), [50, 25, 12, 6], "prog=RPCL;prc=128x128", dict(prog="RPCL", precincts=[(128, 128)])),
+    (512, 384, 3, 8, 1, 5, (32, 32), (0, 0), [40, 10], "prog=CPRL;prc=64x64;sop;eph",
+     dict(prog="CPRL", precincts=[(64, 64)], sop=True, eph=True)),
+    (250, 190, 3, 8, 1, 5, (32, 32), (128, 96), [20, 8], "prog=PCRL", dict(prog="PCRL")),
+    (320, 200, 3, 8, 1, 5, (32, 32), (0, 0), [40, 15, 5], "sty=4", dict(cblk_sty=4)),
+    (257, 131, 1, 8, 0, 4, (32, 32), (0, 0), [12, 4, 1], "", {}),
+])
+def test_quality_layers_are_byte_identical_to_the_stock_encoder(gpu, w, h, ncomp, prec, irr, nr, cblk, tile, rates,
+                                                                opts, kw):
+    """several quality layers (-r a,b,c): allocated layer by layer as pcrdBisectSimple does, inclusion
+    tag trees and Lblock carried from layer to layer; whole files equal to the stock encoder's"""
+    img = H.synth_image(w, h, ncomp, prec, seed=5 * w + h)
+    o = "rates=" + ":".join(str(r) for r in rates) + (";" + opts if opts else "")
+    want = _stock(img, prec, irr, o, numres=nr, cblk=cblk, tile=tile)
+    z = CS.Compressor(w, h, ncomp, prec, reversible=not irr, numres=nr, cblk=cblk, tile=tile, rates=rates,
+                      comment=GROK_COMMENT, **kw)
+    got = z.encode(img)
+    z.close()
+    n = min(got.size, want.size)
+    assert got.size == want.size and np.array_equal(got, want), \
+        "sizes %d / %d, first difference at byte %d" % (got.size, want.size, int(np.argmax(got[:n] != want[:n])))
+    # and the layers decode: fewer layers, coarser image; all layers == the stock decoder's image
+    d = CS.Decompressor(0, slots=1)
+    full = d.decode(got)
+    one = d.decode(got, max_layers=1)
+    d.close()
+    ref = O.ref_codec_decode(got, ncomp, w, h)
+    assert all(np.array_equal(a, b) for a, b in zip(full, ref))
+    err_full = sum(float(np.abs(a.astype(np.int64) - b).sum()) for a, b in zip(full, img))
+    err_one = sum(float(np.abs(a.astype(np.int64) - b).sum()) for a, b in zip(one, img))
+    assert err_one > err_full
