@@ -454,8 +454,13 @@ def encode_legs(args, local=0, world=1):
         planes = [p_.array for p_ in pins]
         out = {}
         nthreads = max(2, min(16, (os.cpu_count() or 2) // world))
+        cinema_rate = W * H * 3 * 1.5 / 1302083.0  # the cinema-4K byte budget per frame at 24 fps
+        cinema_prc = [(256, 256)] * (NUMRES - 1) + [(128, 128)]  # and the profile's precincts and progression
         for name, kw, nthr in (("dci4k_97_mq_cblk32_rate_cinema4k", dict(reversible=False, cblk=(32, 32),
-                                                                       rate=W * H * 3 * 1.5 / 1302083.0), nthreads),
+                                                                       rate=cinema_rate), nthreads),
+                               ("dci4k_97_mq_cblk32_rate_cinema4k_cprl_prc256",
+                                dict(reversible=False, cblk=(32, 32), rate=cinema_rate, prog="CPRL", precincts=cinema_prc),
+                                nthreads),
                                ("ht_lossless_cblk64", dict(reversible=True, ht=True, cblk=(64, 64)), min(8, nthreads))):
             zs = [CS.Compressor(W, H, NCOMP, 12, numres=NUMRES, comment="Created by Grok     version 9.2.0", device=local,
                                 **kw) for _ in range(nthr)]
@@ -477,12 +482,15 @@ def encode_legs(args, local=0, world=1):
             if O.have_ref() and local == 0:
                 try:
                     O.ref_set_rate(kw.get("rate", 0))
+                    if "precincts" in kw:
+                        O.ref_set_encode_options("prog=%s;prc=%s" % (kw["prog"], ":".join("%dx%d" % p_ for p_ in kw["precincts"])))
                     t0 = time.perf_counter()
                     ref = O.ref_codec_encode(img, 12, 0 if kw.get("ht") else 1, ht=bool(kw.get("ht")), numres=NUMRES,
                                              cblk=kw["cblk"], threads=os.cpu_count())
                     ct = time.perf_counter() - t0
                 finally:
                     O.ref_set_rate(0)
+                    O.ref_set_encode_options("")
                 leg["parity"] = {"byte_identical_to_stock_encoder": bool(ref.size == first[0].size and
                                                                          np.array_equal(ref, first[0]))}
                 leg["cpu_baseline"] = {"value": W * H / 1e6 / ct, "unit": "Mpixel/s", "cores": os.cpu_count(),
