@@ -505,6 +505,17 @@ def encode_legs(args, local=0, world=1):
         return {"error": str(e)[:200]}
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """the one JSON line, on the process's real standard output"""
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(line), flush=True)
+
+
 def run_ours(args, wl):
     rank, local, world = dist_env()
     import grok_b200
@@ -518,6 +529,11 @@ def run_ours(args, wl):
     if world > 1:
         if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"  # keeps NCCL's banner off stdout: one JSON line only
+        # ... and whatever a library still writes to file descriptor 1 goes to stderr until the line is printed
+        global _REAL_STDOUT
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
@@ -718,7 +734,7 @@ def run_ours(args, wl):
             cli = cli_timings(second)
             if cli:
                 line["ht"]["cpu_baseline"]["cli"] = cli
-    print(json.dumps(line), flush=True)
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
     return 0
