@@ -614,6 +614,8 @@ __global__ void __launch_bounds__(MAXT, MINB)
 	b.lane = lane;
 	b.gsh = grp * LW;
 	b.gmask = LW == 32 ? FULL : ((1u << LW) - 1u) << b.gsh;
+	if(LW != 32) // kept in a register: rematerialised at every ballot / shuffle / syncwarp otherwise
+		asm volatile("mov.u32 %0, %0;" : "+r"(b.gmask));
 
 	for(;;)
 	{

@@ -1,3 +1,8 @@
+#!/usr/bin/env python3
+"""MQ decode throughput against the number of frames in flight and the code-block size:
+    python tools/bench_mq_inflight.py <cblk 32|64> <frames in flight>     (GRKB_T1_MQ_GROUP / _BUSY to force)
+One decompressor per frame in flight, the stock encoder's 4096x2160x3 16-bit 9/7 codestream, wall clock.
+The table in DESIGN.md section 4 (one block per warp vs two) comes from this."""
 import os, sys, time
 import numpy as np
 sys.path.insert(0, "/root/repo"); sys.path.insert(0, "/root/repo/tests")
