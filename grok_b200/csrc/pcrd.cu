@@ -1015,7 +1015,12 @@ int grkb_pcrd_create(const PcrdLayout& lay, uint32_t nblocks, grkb_pcrd** out)
 {
 	*out = nullptr;
 	auto* p = new grkb_pcrd();
-	GRKB_CUDA_CHECK(cudaGetDevice(&p->device));
+	if(cudaGetDevice(&p->device) != cudaSuccess)
+	{
+		grkb_set_error("pcrd: no current device");
+		delete p;
+		return -1;
+	}
 	p->nblocks = nblocks;
 	p->npackets = (uint32_t)lay.packets.size();
 	p->nbands = (uint32_t)lay.bands.size();

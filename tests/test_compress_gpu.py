@@ -102,6 +102,8 @@ def test_configs2_ht_4k_encode_codestream_byte_identical(gpu):
     # many small packets (a 64-thread CTA each) and few large ones (1024 threads, 3 x 1024 blocks in one)
     (512, 384, 3, 8, 1, 5, (32, 32), (0, 0), 15.0, "prog=RPCL;prc=64x64;eph", dict(prog="RPCL", precincts=[(64, 64)], eph=True)),
     (768, 768, 3, 8, 1, 2, (16, 16), (0, 0), 8.0, "", {}),
+    # one packet of 3 x 16 384 blocks: its tag trees and header bits do not fit in shared memory
+    (2048, 2048, 3, 8, 1, 2, (8, 8), (0, 0), 12.0, "", {}),
     # layers that run into the budget inside a packet HEADER: the reference does not check the writes of
     # the number of passes and of the Lblock comma code, the budget left wraps and the layer "fits" (its
     # files then exceed the target, these by 0.5 to 25 %): reproduced, on the device too
