@@ -103,7 +103,7 @@ def consistent(cs):
 
 
 # seeds whose parameters make the STOCK ENCODER abort (an assertion inside the reference library)
-STOCK_ABORTS = {215}  # (heap corruption: free(): invalid pointer)
+STOCK_ABORTS = {166, 215, 264}  # (heap corruption: free() / munmap_chunk(): invalid pointer, SIGSEGV)
 
 
 @pytest.fixture(scope="module")
@@ -113,7 +113,7 @@ def dec(gpu):
     d.close()
 
 
-@pytest.mark.parametrize("seed", range(100, 136))
+@pytest.mark.parametrize("seed", range(100, 200))
 def test_random_decode(dec, seed):
     c = draw(seed)
     r = c["r"]
@@ -131,6 +131,13 @@ def test_random_decode(dec, seed):
         pytest.skip("the stock encoder's tile lengths do not match its packets")
     reduce = int(r.integers(0, min(c["nr"], 3))) if r.integers(0, 3) == 0 else 0
     maxl = int(r.integers(1, 3)) if layers and r.integers(0, 2) else 0
+    if layers and (c["sty"] & 5) and c["prog"] != "LRCP":
+        # The stock decoder reads the headers of the packets it skips (layers beyond cp_layer, resolutions
+        # beyond cp_reduce) but only readPacketData() advances a segment's pass count, so the next header of
+        # a block with several codeword segments (LAZY, TERMALL) is split wrongly, the packet's length comes
+        # out wrong and everything after it is garbage (t2/T2Decompress.cpp:63-110, :390-440).  Harmless
+        # when the skipped packets come last (LRCP); otherwise there is nothing to compare with.
+        reduce, maxl = 0, 0
     cso = CS.Codestream(cs)
     rw, rh = cso.image_size(reduce)
     cso.close()
@@ -153,7 +160,7 @@ def test_random_decode(dec, seed):
             (seed, k, {x: c[x] for x in c if x != "r"}, layers, reduce, maxl)
 
 
-@pytest.mark.parametrize("seed", range(200, 236))
+@pytest.mark.parametrize("seed", range(200, 300))
 def test_random_encode(gpu, seed):
     c = draw(seed)
     r = c["r"]
