@@ -158,6 +158,17 @@ def test_random_decode(dec, seed):
         assert got[k].shape == want[k].shape
         assert np.array_equal(got[k][:vh, :vw], want[k][:vh, :vw]), \
             (seed, k, {x: c[x] for x in c if x != "r"}, layers, reduce, maxl)
+    # a window of the image is that region of the full decode (only the tiles and code blocks it depends on
+    # are decoded; compared with ourselves: the reference's windowed decode disagrees with its own full decode
+    # when the image origin is not (0, 0))
+    wx0, wy0 = int(r.integers(0, c["w"] - 8)), int(r.integers(0, c["h"] - 8))
+    wx1, wy1 = int(r.integers(wx0 + 1, c["w"] + 1)), int(r.integers(wy0 + 1, c["h"] + 1))
+    win = dec.decode_window(cs, (wx0, wy0, wx1, wy1), reduce=reduce, max_layers=maxl)
+    assert dec.rejected == 0
+    ox, oy = up(x0), up(y0)
+    for k in range(c["ncomp"]):
+        crop = got[k][up(y0 + wy0) - oy:up(y0 + wy1) - oy, up(x0 + wx0) - ox:up(x0 + wx1) - ox]
+        assert win[k].shape == crop.shape and np.array_equal(win[k], crop), (seed, k, (wx0, wy0, wx1, wy1), reduce, maxl)
 
 
 @pytest.mark.parametrize("seed", range(200, 300))
