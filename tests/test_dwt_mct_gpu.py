@@ -116,3 +116,31 @@ def test_custom_mct_matches_oracle(gpu, orc, nc):
         flts = [(rng.standard_normal(n) * 3000).astype(np.float32) for _ in range(nc)]
         for a, b in zip(orc.orc_mct_custom(flts, m, 0), gpu.stages.mct_custom(flts, m, 0)):
             assert same_bits(a, b)
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_dwt_random_geometries(gpu, orc, seed):
+    """drawn tile-component rectangles, half of them of the kind the strip kernels take (widths that are
+    multiples of 8 times a power of two at x0 = 0), both filters, both directions, fused and stage by stage"""
+    rng = np.random.default_rng(1000 + seed)
+    nr = int(rng.integers(1, 7))
+    if seed % 2:
+        w = int(rng.integers(1, 40)) * 8 << int(rng.integers(0, 4))
+        x0 = 0
+    else:
+        w, x0 = int(rng.integers(1, 700)), int(rng.integers(0, 40))
+    h, y0 = int(rng.integers(1, 400)), int(rng.integers(0, 40))
+    if min(h >> (nr - 1), 3) == 2 or (w >> (nr - 1)) == 0 or (h >> (nr - 1)) == 0:
+        nr = 1 + int(rng.integers(0, 2))  # (stay clear of the reference's degenerate-geometry defects, common.py)
+    for reversible in (1, 0):
+        p = plane(rng, w, h, reversible)
+        for forward in (0, 1):
+            want = orc.orc_dwt(p, x0, y0, nr, reversible, forward)
+            got = gpu.stages.dwt(p, x0, y0, nr, reversible, forward)
+            assert same_bits(want, got), (w, h, x0, y0, nr, reversible, forward)
+        pl = [plane(rng, w, h, reversible, amp=30000) for _ in range(3)]
+        sh, lo, hi = [32768] * 3, [0] * 3, [65535] * 3
+        stage = [orc.orc_dwt(q, x0, y0, nr, reversible, 0) for q in pl]
+        want = orc.orc_mct_inv([s_.view(np.int32) for s_ in stage], 0 if reversible else 1, 1, [16] * 3, [0] * 3, sh)
+        got = gpu.stages.idwt_mct(pl, x0, y0, nr, reversible, 1, sh, lo, hi)
+        assert all(same_bits(a, b) for a, b in zip(want, got)), (w, h, x0, y0, nr, reversible, "fused inverse")
