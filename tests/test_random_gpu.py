@@ -103,7 +103,9 @@ def consistent(cs):
 
 
 # seeds whose parameters make the STOCK ENCODER abort (an assertion inside the reference library)
-STOCK_ABORTS = {166, 215, 264}  # (heap corruption: free() / munmap_chunk(): invalid pointer, SIGSEGV)
+# (heap corruption -- free() / munmap_chunk(): invalid pointer, SIGSEGV -- found by running every seed's stock
+# encode in a process of its own; all of them have TERMALL or LAZY blocks in precincts of 64x64 or less)
+STOCK_ABORTS = {166, 215, 264, 1010, 1022, 1098, 2036, 2080, 2133}
 
 
 @pytest.fixture(scope="module")
@@ -113,7 +115,7 @@ def dec(gpu):
     d.close()
 
 
-@pytest.mark.parametrize("seed", range(100, 200))
+@pytest.mark.parametrize("seed", list(range(100, 200)) + list(range(1000, 1150)))
 def test_random_decode(dec, seed):
     c = draw(seed)
     r = c["r"]
@@ -163,6 +165,8 @@ def test_random_decode(dec, seed):
     # when the image origin is not (0, 0))
     wx0, wy0 = int(r.integers(0, c["w"] - 8)), int(r.integers(0, c["h"] - 8))
     wx1, wy1 = int(r.integers(wx0 + 1, c["w"] + 1)), int(r.integers(wy0 + 1, c["h"] + 1))
+    if up(x0 + wx1) == up(x0 + wx0) or up(y0 + wy1) == up(y0 + wy0):
+        return  # (no sample of the window at this resolution: the door says so)
     win = dec.decode_window(cs, (wx0, wy0, wx1, wy1), reduce=reduce, max_layers=maxl)
     assert dec.rejected == 0
     ox, oy = up(x0), up(y0)
@@ -171,7 +175,7 @@ def test_random_decode(dec, seed):
         assert win[k].shape == crop.shape and np.array_equal(win[k], crop), (seed, k, (wx0, wy0, wx1, wy1), reduce, maxl)
 
 
-@pytest.mark.parametrize("seed", range(200, 300))
+@pytest.mark.parametrize("seed", list(range(200, 300)) + list(range(2000, 2150)))
 def test_random_encode(gpu, seed):
     c = draw(seed)
     r = c["r"]
