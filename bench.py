@@ -264,29 +264,36 @@ def measure(wl, args, local, barrier, with_parity=True):
     barrier()
     # ---- the same with four frames in flight (a decoder and a stream each, everything resident): what the
     # device sustains when a frame's latency is not the point -- the block decoder then pairs code blocks
-    if not wl["ht"]:
-        import threading
-        more = [T.TileDecoder(params, len(blocks), data.size) for _ in range(3)]
-        for m in more:
-            m.decode(blocks, segs, data, out=out)
-        group = [dec] + more
-        n_each = max(3, args.steps // 2)
+    # (an extra, N = 1 only: no collective inside, and a failure costs the key, not the run)
+    if not wl["ht"] and dist_env()[2] == 1:
+        more = []
+        try:
+            import threading
+            more = [T.TileDecoder(params, len(blocks), data.size) for _ in range(3)]
+            for m in more:
+                m.decode(blocks, segs, data, out=out)
+            group = [dec] + more
+            n_each = max(3, args.steps // 2)
 
-        def spin(d_):
-            d_.time_device(n_each, 1)
-        ths = [threading.Thread(target=spin, args=(d_,)) for d_ in group]
-        barrier()
-        t0 = time.perf_counter()
-        for t_ in ths:
-            t_.start()
-        for t_ in ths:
-            t_.join()
-        # (grkb_decoder_time_device runs its warm-up, the timed passes, and the same passes again with events
-        # around the stages: 2 x n_each + 1 frames per decoder)
-        res["inflight4_ms"] = (time.perf_counter() - t0) * 1e3 / (len(group) * (2 * n_each + 1))
-        barrier()
+            def spin(d_):
+                d_.time_device(n_each, 1)
+            ths = [threading.Thread(target=spin, args=(d_,)) for d_ in group]
+            t0 = time.perf_counter()
+            for t_ in ths:
+                t_.start()
+            for t_ in ths:
+                t_.join()
+            # (grkb_decoder_time_device runs its warm-up, the timed passes, and the same passes again with events
+            # around the stages: 2 x n_each + 1 frames per decoder)
+            res["inflight4_ms"] = (time.perf_counter() - t0) * 1e3 / (len(group) * (2 * n_each + 1))
+        except Exception as e:
+            log("[bench] value_4_frames_in_flight skipped: %s" % str(e)[:200])
         for m in more:
-            m.close()
+            try:
+                m.close()
+            except Exception:
+                pass
+    barrier()
     # ---- e2e: the codestream door, K frames in flight (one decompressor each, one slot each)
     K = max(1, args.inflight if args.inflight else (2 if wl["ht"] else 4))
     dzs = [CS.Decompressor(local, slots=1) for _ in range(K)]
@@ -387,6 +394,7 @@ def plugin_legs(wl, args):
         return {"e2e_plugin": {"value": None, "error": str(e)[:200]}}
 
 
+ENCODE_LEGS = ("dci4k_97_mq_cblk32_rate_cinema4k", "dci4k_97_mq_cblk32_rate_cinema4k_cprl_prc256", "ht_lossless_cblk64")
 T8K, TILE8K = 8192, 1024
 
 
@@ -439,13 +447,11 @@ def tiled_leg(args, local, rank, world, barrier):
     for _ in range(2):
         dz.submit_tiles(cs, out, rank, world)
         dz.wait()
-    barrier()
     t0 = time.perf_counter()
     for _ in range(steps):
         dz.submit_tiles(cs, out, rank, world)
         dz.wait()
     ms = (time.perf_counter() - t0) * 1e3 / steps
-    barrier()
     res = {"ms": ms, "rejected": dz.rejected, "tiles_this_rank": dz.stats()["tiles"], "coded_bytes": int(cs_arr.size)}
     if rank == 0:
         # lossless: this rank's tiles must be the image
@@ -478,7 +484,7 @@ def encode_legs(args, local=0, world=1):
             p_.array[:] = b
         planes = [p_.array for p_ in pins]
         out = {}
-        nthreads = max(2, min(16, (os.cpu_count() or 2) // world))
+        nthreads = max(int(os.environ.get("GRKB_BENCH_ENCODE_THREADS", "2")), min(16, (os.cpu_count() or 2) // world))
         cinema_rate = W * H * 3 * 1.5 / 1302083.0  # the cinema-4K byte budget per frame at 24 fps
         cinema_prc = [(256, 256)] * (NUMRES - 1) + [(128, 128)]  # and the profile's precincts and progression
         for name, kw, nthr in (("dci4k_97_mq_cblk32_rate_cinema4k", dict(reversible=False, cblk=(32, 32),
@@ -562,7 +568,10 @@ def run_ours(args, wl):
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        # (a rank that dies takes the others down through torchrun; a rank that waits for one that never comes
+        # gives up after five minutes instead of NCCL's ten)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=300))
 
     def barrier():
         if dist is not None:
@@ -586,7 +595,15 @@ def run_ours(args, wl):
         a2.steps = max(5, args.steps // 2)
         sub = measure(second, a2, local, barrier)
     # ---- extras on every rank: configs[3] tile-sharded over the ranks, configs[4] / [2] encode frame-sharded
-    tiled = None if args.no_tiled else tiled_leg(args, local, rank, world, barrier)
+    # (no collective inside them; a leg that fails on a rank counts as zero there and is reported)
+    tiled = None
+    if not args.no_tiled:
+        try:
+            tiled = tiled_leg(args, local, rank, world, barrier)
+        except SystemExit:
+            raise
+        except Exception as e:
+            log("[bench] rank %d: tiled_8k failed: %s" % (rank, str(e)[:200]))
     barrier()
     enc = None if args.no_encode else encode_legs(args, local, world)
     barrier()
@@ -605,8 +622,10 @@ def run_ours(args, wl):
     link = [h2d.value, d2h.value, dup[0], dup[1]]
     all_clocks = [clocks]
     tiled_ms = tiled["ms"] if tiled else 0.0
-    enc_names = [k for k in (enc or {}) if isinstance(enc[k], dict) and "value" in enc[k]]
-    enc_vals = [enc[k]["value"] for k in enc_names]
+    # (a fixed list: every rank reduces vectors of the same length whatever happened on it)
+    enc_vals = [float(enc[k]["value"]) if enc and isinstance(enc.get(k), dict) and "value" in enc[k] else 0.0
+                for k in ENCODE_LEGS]
+    ms4_local = float(main.get("inflight4_ms", 0.0))
     if dist is not None:
         import torch
         t = torch.tensor(vals, dtype=torch.float64, device="cuda")
@@ -615,12 +634,19 @@ def run_ours(args, wl):
         t = torch.tensor(link, dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         link = [float(x) for x in t]
-        t = torch.tensor([tiled_ms], dtype=torch.float64, device="cuda")
+        t = torch.tensor([tiled_ms, ms4_local], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        tiled_ms = float(t[0])
-        t = torch.tensor(enc_vals + [0.0], dtype=torch.float64, device="cuda")
+        tiled_ms, ms4_local = float(t[0]), float(t[1])
+        ok_ranks = [1.0 if v > 0 else 0.0 for v in enc_vals] + [1.0 if main.get("inflight4_ms") else 0.0,
+                                                                1.0 if tiled else 0.0]
+        t = torch.tensor(enc_vals + ok_ranks, dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        enc_vals = [float(x) for x in t][:len(enc_names)]
+        got = [float(x) for x in t]
+        enc_vals, ok_ranks = got[:len(ENCODE_LEGS)], got[len(ENCODE_LEGS):]
+    else:
+        ok_ranks = [1.0 if v > 0 else 0.0 for v in enc_vals] + [1.0 if main.get("inflight4_ms") else 0.0,
+                                                                1.0 if tiled else 0.0]
+    if dist is not None:
         all_clocks = [None] * world
         dist.all_gather_object(all_clocks, clocks)
     if rank != 0:
@@ -705,13 +731,8 @@ def run_ours(args, wl):
     for k in ("e2e", "e2e_samples16", "pcie_bound", "e2e_over_pcie_bound", "roofline", "stages_ms", "t1", "parity",
               "detail"):
         line[k] = f[k]
-    if "inflight4_ms" in main:
-        ms4 = main["inflight4_ms"]
-        if dist is not None:
-            import torch
-            t = torch.tensor([ms4], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms4 = float(t[0])
+    if ms4_local > 0 and int(ok_ranks[len(ENCODE_LEGS)]) == world:
+        ms4 = ms4_local
         line["value_4_frames_in_flight"] = {
             "value": world * W * H / 1e6 / (ms4 * 1e-3), "unit": "Mpixel/s", "ms_per_frame": ms4,
             "what": "device-resident like `value`, four decoders on four streams per GPU, wall clock over their "
@@ -740,13 +761,15 @@ def run_ours(args, wl):
             if pl:
                 line["ht"].update(pl)
     if enc is not None:
-        for k, v in zip(enc_names, enc_vals):
-            enc[k]["value_this_rank"] = enc[k]["value"]
-            enc[k]["value"] = v
+        for i_, k in enumerate(ENCODE_LEGS):
+            if isinstance(enc.get(k), dict) and "value" in enc[k]:
+                enc[k]["value_this_rank"] = enc[k]["value"]
+                enc[k]["value"] = enc_vals[i_]
+                enc[k]["ranks_counted"] = int(ok_ranks[i_])
         enc["what"] = ("grkb_compress, frames sharded over the ranks (weak scaling): value = sum over ranks; host threads "
                        "per rank = cores / ranks")
         line["encode"] = enc
-    if tiled:
+    if tiled and int(ok_ranks[len(ENCODE_LEGS) + 1]) == world:
         line["tiled_8k"] = {"value": T8K * T8K / 1e6 / (tiled_ms * 1e-3), "unit": "Mpixel/s", "ms_per_image": tiled_ms,
                             "scaling": "strong: the 64 tiles of one image over the ranks, tile t on rank t mod N",
                             "config": {"workload": "htj2k_decode_8192x8192_rgb16_53_rct_lossless_5lvl_cblk64_tiles1024",
