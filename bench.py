@@ -621,31 +621,13 @@ def run_ours(args, wl):
         vals += [sub["tm"]["total_ms"]] + [sub[k] for k in keys]
     link = [h2d.value, d2h.value, dup[0], dup[1]]
     all_clocks = [clocks]
-    tiled_ms = tiled["ms"] if tiled else 0.0
-    # (a fixed list: every rank reduces vectors of the same length whatever happened on it)
-    enc_vals = [float(enc[k]["value"]) if enc and isinstance(enc.get(k), dict) and "value" in enc[k] else 0.0
-                for k in ENCODE_LEGS]
-    ms4_local = float(main.get("inflight4_ms", 0.0))
-    if dist is not None:
-        import torch
-        t = torch.tensor(vals, dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        vals = [float(x) for x in t]
-        t = torch.tensor(link, dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MIN)
-        link = [float(x) for x in t]
-        t = torch.tensor([tiled_ms, ms4_local], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        tiled_ms, ms4_local = float(t[0]), float(t[1])
-        ok_ranks = [1.0 if v > 0 else 0.0 for v in enc_vals] + [1.0 if main.get("inflight4_ms") else 0.0,
-                                                                1.0 if tiled else 0.0]
-        t = torch.tensor(enc_vals + ok_ranks, dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        got = [float(x) for x in t]
-        enc_vals, ok_ranks = got[:len(ENCODE_LEGS)], got[len(ENCODE_LEGS):]
-    else:
-        ok_ranks = [1.0 if v > 0 else 0.0 for v in enc_vals] + [1.0 if main.get("inflight4_ms") else 0.0,
-                                                                1.0 if tiled else 0.0]
+    # (shapes that do not depend on what happened on a rank: grok_b200/shard.py, tested with gloo)
+    leg_vals = {k: enc[k]["value"] for k in ENCODE_LEGS if enc and isinstance(enc.get(k), dict) and "value" in enc[k]}
+    extra_ms = {"tiled_8k": tiled["ms"] if tiled else 0.0, "inflight4": main.get("inflight4_ms", 0.0)}
+    vals, link, legs_red, extras_red = shard.reduce_bench_figures(world, "cuda" if dist is not None else None, vals, link,
+                                                                   leg_vals, ENCODE_LEGS, extra_ms, ("tiled_8k", "inflight4"))
+    tiled_ms, tiled_ranks = extras_red["tiled_8k"]
+    ms4_local, ms4_ranks = extras_red["inflight4"]
     if dist is not None:
         all_clocks = [None] * world
         dist.all_gather_object(all_clocks, clocks)
@@ -731,7 +713,7 @@ def run_ours(args, wl):
     for k in ("e2e", "e2e_samples16", "pcie_bound", "e2e_over_pcie_bound", "roofline", "stages_ms", "t1", "parity",
               "detail"):
         line[k] = f[k]
-    if ms4_local > 0 and int(ok_ranks[len(ENCODE_LEGS)]) == world:
+    if ms4_local > 0 and ms4_ranks == world:
         ms4 = ms4_local
         line["value_4_frames_in_flight"] = {
             "value": world * W * H / 1e6 / (ms4 * 1e-3), "unit": "Mpixel/s", "ms_per_frame": ms4,
@@ -764,12 +746,11 @@ def run_ours(args, wl):
         for i_, k in enumerate(ENCODE_LEGS):
             if isinstance(enc.get(k), dict) and "value" in enc[k]:
                 enc[k]["value_this_rank"] = enc[k]["value"]
-                enc[k]["value"] = enc_vals[i_]
-                enc[k]["ranks_counted"] = int(ok_ranks[i_])
+                enc[k]["value"], enc[k]["ranks_counted"] = legs_red[k]
         enc["what"] = ("grkb_compress, frames sharded over the ranks (weak scaling): value = sum over ranks; host threads "
                        "per rank = cores / ranks")
         line["encode"] = enc
-    if tiled and int(ok_ranks[len(ENCODE_LEGS) + 1]) == world:
+    if tiled and tiled_ranks == world:
         line["tiled_8k"] = {"value": T8K * T8K / 1e6 / (tiled_ms * 1e-3), "unit": "Mpixel/s", "ms_per_image": tiled_ms,
                             "scaling": "strong: the 64 tiles of one image over the ranks, tile t on rank t mod N",
                             "config": {"workload": "htj2k_decode_8192x8192_rgb16_53_rct_lossless_5lvl_cblk64_tiles1024",

@@ -100,3 +100,33 @@ def sum_over_ranks(value: float, world: int, device=None) -> float:
     t = torch.tensor([float(value)], dtype=torch.float64, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return float(t.item())
+
+
+def reduce_bench_figures(world: int, device, times_ms: Sequence[float], link_gbs: Sequence[float],
+                         leg_values: dict, leg_names: Sequence[str], extra_ms: dict, extra_names: Sequence[str]):
+    """The reductions of a bench run over the ranks, with shapes that do not depend on what happened on a
+    rank (a leg that failed somewhere must not leave the ranks reducing vectors of different lengths):
+    times_ms -> max, link_gbs -> min, leg_values[name] (throughputs; missing or None: 0) -> sum with the
+    number of ranks that have one, extra_ms[name] (times; missing or None: 0) -> max with that count.
+    Returns (times, link, {name: (sum, ranks)}, {name: (max, ranks)})."""
+    lv = [float(leg_values.get(k) or 0.0) for k in leg_names]
+    ev = [float(extra_ms.get(k) or 0.0) for k in extra_names]
+    have = [1.0 if v > 0 else 0.0 for v in lv + ev]
+    times, link = [float(x) for x in times_ms], [float(x) for x in link_gbs]
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        t = torch.tensor(times + ev, dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        got = [float(x) for x in t]
+        times, ev = got[:len(times)], got[len(times):]
+        t = torch.tensor(link, dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        link = [float(x) for x in t]
+        t = torch.tensor(lv + have, dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        got = [float(x) for x in t]
+        lv, have = got[:len(lv)], got[len(lv):]
+    legs = {k: (lv[i], int(have[i])) for i, k in enumerate(leg_names)}
+    extras = {k: (ev[i], int(have[len(lv) + i])) for i, k in enumerate(extra_names)}
+    return times, link, legs, extras

@@ -71,6 +71,15 @@ def _worker(rank, world, port, out_dir):
         assert ms == 10.0 + world - 1
         total = shard.sum_over_ranks(float(len(mine)), world)
         assert total == len(tiles)
+        # the bench's reductions keep their shape when a leg failed on one rank only (rank 1 has no second leg
+        # and no tiled figure): no rank waits for a vector of another length
+        legs = {"a": 100.0 + rank, "b": 50.0} if rank == 0 else {"a": 100.0 + rank, "b": None}
+        extra = {"tiled": 7.0 + rank, "inflight": 3.0} if rank == 0 else {"tiled": None}
+        times, link, lg, ex = shard.reduce_bench_figures(world, None, [10.0 + rank, 20.0 - rank], [5.0 + rank], legs,
+                                                         ("a", "b"), extra, ("tiled", "inflight"))
+        assert times == [10.0 + world - 1, 20.0] and link == [5.0]
+        assert lg["a"] == (sum(100.0 + r for r in range(world)), world) and lg["b"] == (50.0, 1)
+        assert ex["tiled"] == (7.0, 1) and ex["inflight"] == (3.0, 1)
     finally:
         dist.destroy_process_group()
 
