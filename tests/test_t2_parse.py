@@ -188,3 +188,38 @@ def test_truncated_codestream_does_not_crash(orc):
         t = c.parse_tile(0)
         assert t["truncated"]
         c.close()
+
+
+@pytest.mark.parametrize("seed", [100, 101, 103, 105, 107, 108, 110, 113, 117, 119, 122, 124, 127, 131, 1003, 1017, 1044, 1090])
+def test_drawn_combinations_on_the_host_path(orc, seed):
+    """the drawn sweep of tests/test_random_gpu.py, host half: stock codestream -> our marker + packet parser
+    -> the oracle's block decoders / wavelet / MCT == the stock decoder (layer- and resolution-limited too)"""
+    import test_random_gpu as R
+    c = R.draw(seed)
+    r = c["r"]
+    img = H.synth_image(c["w"], c["h"], c["ncomp"], c["prec"], seed=seed)
+    layers = ""
+    if not c["ht"] and r.integers(0, 2):
+        layers = "rates=" + ":".join(str(x) for x in sorted(r.choice([60, 40, 25, 12, 6, 3], size=int(r.integers(2, 4)),
+                                                                     replace=False).tolist(), reverse=True))
+    cs = R.stock_encode(img, c, R.stock_opts(c, layers))
+    if cs.size < 200 or not R.consistent(cs):
+        pytest.skip("nothing valid from the stock encoder for this combination")
+    reduce = int(r.integers(0, min(c["nr"], 3))) if r.integers(0, 3) == 0 else 0
+    maxl = int(r.integers(1, 3)) if layers and r.integers(0, 2) else 0
+    if layers and (c["sty"] & 5) and c["prog"] != "LRCP":
+        reduce, maxl = 0, 0  # (stock decoder defect, DESIGN.md section 8)
+    co = CS.Codestream(cs)
+    rw, rh = co.image_size(reduce)
+    co.close()
+    try:
+        O.ref_set_decode_options(reduce, maxl)
+        want = O.ref_codec_decode(cs, c["ncomp"], rw, rh, threads=4)
+    finally:
+        O.ref_set_decode_options(0, 0)
+    got, tabs = H.decode_codestream_oracle(cs, reduce, maxl)
+    x0, y0 = c["off"]
+    up = lambda v: (v + (1 << reduce) - 1) >> reduce  # noqa: E731
+    vw, vh = up(x0 + c["w"]) - up(x0), up(y0 + c["h"]) - up(y0)
+    for k in range(c["ncomp"]):
+        assert np.array_equal(got[k][:vh, :vw], want[k][:vh, :vw]), (seed, k, reduce, maxl)
