@@ -213,7 +213,7 @@ PROGS = {"LRCP": 0, "RLCP": 1, "RPCL": 2, "PCRL": 3, "CPRL": 4}
 
 
 class Compressor:
-    """grkb_compressor: images -> codestreams (one layer, every pass kept) on one device"""
+    """grkb_compressor: images -> codestreams on one device (every pass kept, or one / several rate-controlled layers)"""
 
     def __init__(self, width, height, numcomps, prec, reversible=True, ht=False, numres=6, cblk=(64, 64),
                  tile=(0, 0), origin=(0, 0), tile_origin=None, prog="LRCP", precincts=None, sop=False, eph=False,

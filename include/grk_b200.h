@@ -527,15 +527,16 @@ int grkb_decompress_stats(const grkb_decompressor* d, double* t2_ms, uint32_t* t
 
 /* ---- the encode side of the codestream level ---------------------------------------------------
  * Image planes in, a complete JPEG 2000 / HTJ2K codestream out: the device tile encoder
- * (grkb_encoder_*) plus, on the host, what the reference does around it for ONE quality layer that
- * keeps every coding pass -- main header (CodeStreamCompress::start and the marker writers,
+ * (grkb_encoder_*) plus what the reference does around it -- main header (CodeStreamCompress::start and
+ * the marker writers,
  * src/lib/jp2/codestream/CodeStreamCompress.cpp:640-1130), packet headers and bodies
  * (T2Compress::compressPacket / compressHeader, t2/T2Compress.cpp:112-330; TagTree::compress,
  * t2/TagTree.h:160-200), one tile part per tile.  It replaces grk_compress_init + grk_compress_start
  * + grk_compress + grk_compress_end (grok.h:1380-1420) for lossless J2K, HTJ2K lossless, all-passes
- * 9/7 streams and single layers with a rate target, byte-identical to the stock encoder's output for
- * the same parameters.  Not written here: several quality layers, POC, tile-part division, the
- * digital-cinema profiles' per-component limits (those stay with the host behind grk_plugin_*). */
+ * 9/7 streams, and one or several quality layers with rate targets (the reference's rate allocation,
+ * see `rate` below), byte-identical to the stock encoder's output for the same parameters.  Not
+ * written here: POC, tile-part division, TLM / PLT markers, the digital-cinema profiles' per-component
+ * limits (those stay with the host behind grk_plugin_*). */
 #define GRKB_MAX_LAYERS 100 /* maxCompressLayersGRK */
 typedef struct grkb_compress_params
 {
