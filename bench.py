@@ -537,6 +537,7 @@ def encode_legs(args, local=0, world=1):
 
 
 _REAL_STDOUT = None
+COLLECTIVE_BACKEND, COLLECTIVE_DEVICE = "nccl", "cuda"  # (tests/test_bench_flow.py runs the N > 1 flow over gloo)
 
 
 def emit(line):
@@ -567,11 +568,15 @@ def run_ours(args, wl):
         os.dup2(2, 1)
         import torch
         import torch.distributed as dist
-        torch.cuda.set_device(local)
         import datetime
         # (a rank that dies takes the others down through torchrun; a rank that waits for one that never comes
         # gives up after five minutes instead of NCCL's ten)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(seconds=300))
+        if COLLECTIVE_BACKEND == "nccl":
+            torch.cuda.set_device(local)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local),
+                                    timeout=datetime.timedelta(seconds=300))
+        else:
+            dist.init_process_group(COLLECTIVE_BACKEND, timeout=datetime.timedelta(seconds=300))
 
     def barrier():
         if dist is not None:
@@ -624,7 +629,7 @@ def run_ours(args, wl):
     # (shapes that do not depend on what happened on a rank: grok_b200/shard.py, tested with gloo)
     leg_vals = {k: enc[k]["value"] for k in ENCODE_LEGS if enc and isinstance(enc.get(k), dict) and "value" in enc[k]}
     extra_ms = {"tiled_8k": tiled["ms"] if tiled else 0.0, "inflight4": main.get("inflight4_ms", 0.0)}
-    vals, link, legs_red, extras_red = shard.reduce_bench_figures(world, "cuda" if dist is not None else None, vals, link,
+    vals, link, legs_red, extras_red = shard.reduce_bench_figures(world, COLLECTIVE_DEVICE if dist is not None else None, vals, link,
                                                                    leg_vals, ENCODE_LEGS, extra_ms, ("tiled_8k", "inflight4"))
     tiled_ms, tiled_ranks = extras_red["tiled_8k"]
     ms4_local, ms4_ranks = extras_red["inflight4"]
